@@ -1,0 +1,217 @@
+"""Generates tests/golden/*.npz by running the UNMODIFIED reference (imported from /root/reference via
+oracle/ref_import.py) on synthetic frames from 3dod_b200/tdod/synth.py.  Runs only in the build
+container (the GPU box has no /root/reference); the resulting fixtures are committed.
+
+Inputs are regenerated from (frame_id, H, W, n_obj) by synth.make_frame -- each fixture stores a SHA-256
+of the regenerated inputs so a drift in the generator is detected -- plus everything the reference
+computed: accepted standard normals, cubes, projected corners, boxes, every score, the argmax.
+
+    python tests/golden/make_golden.py
+"""
+import hashlib
+import os
+import pickle
+import random
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+sys.path.insert(0, os.path.join(ROOT, "3dod_b200"))
+
+import ref_import  # noqa: E402
+import tdod_oracle as O  # noqa: E402
+from tdod import synth  # noqa: E402
+
+R = ref_import.load()
+
+
+def digest(*arrays):
+    h = hashlib.sha256()
+    for a in arrays:
+        h.update(np.ascontiguousarray(a).tobytes())
+    return h.hexdigest()
+
+
+def frame_digest(f):
+    parts = [f.depth.numpy(), f.ground.numpy(), f.boxes.numpy(), f.prior_mean.numpy(),
+             f.prior_std.numpy(), f.K.numpy()]
+    if f.masks is not None:
+        parts.append(f.masks.numpy())
+    return digest(*parts)
+
+
+def ref_normal(f, seed):
+    """roi_heads.py:345-428 flavour: fp64 NumPy back-projection, Plane_np (== pyransac3d), rectify."""
+    pg, pn = O.backproject_np(f.depth.numpy(), f.K.numpy(), f.ground.numpy())
+    random.seed(seed)
+    eq, inl = R.plane.Plane_np().fit(pg, thresh=0.05, maxIteration=1000)
+    random.seed(seed)
+    ids = O.draw_sample_ids(len(pg), 1000, random)
+    nv = O.rectify_normal(np.array(eq[:-1]))
+    return pg, pn, ids, np.array(eq), np.asarray(inl), nv
+
+
+def ref_frame(f, n, seed, normal, W, H, mode_b_objs=()):
+    """Runs the reference's PRED-branch selection (roi_heads.py:493-505) for one frame."""
+    out = {}
+    boxes = R.Boxes(f.boxes)
+    torch.manual_seed(seed)
+    cubes, _, _ = R.proposals.propose(boxes, f.depth, (f.prior_mean, f.prior_std), (W, H), f.K,
+                                      number_of_proposals=n,
+                                      ground_normal=None if normal is None else torch.from_numpy(normal))
+    # accepted standard normals: re-run the oracle's sampler on the same stream (bit-equal cubes is
+    # asserted, so the noise is the one the reference consumed)
+    g = torch.Generator().manual_seed(seed)
+    o = O.propose(f.boxes, f.depth, f.prior_mean, f.prior_std, f.K, n,
+                  None if normal is None else torch.from_numpy(normal), g)
+    assert torch.equal(o["cubes"], cubes.tensor), "oracle sampler diverged from the reference"
+    out["noise"] = o["noise"].numpy()
+    if o["yaw_idx"] is not None:
+        out["yaw_idx"] = o["yaw_idx"].numpy().astype(np.int16)
+    out["tries"] = np.array(o["tries"])
+    out["cubes"] = cubes.tensor.numpy()
+    pb = R.conversions.cubes_to_box(cubes, f.K, (W, H))
+    out["boxes"] = np.stack([b.tensor.numpy() for b in pb])
+    N = len(boxes)
+    iou = np.zeros((N, n), np.float32); dim = np.zeros((N, n), np.float32); cor = np.zeros((N, n), np.float32)
+    comb = np.zeros((N, n), np.float32); best = np.zeros(N, np.int64)
+    rects = np.full((N, 4, 2), np.nan, np.float32)
+    c2d_all = cubes.get_bube_corners(f.K, (W, H))
+    out["corners2d_obj0"] = c2d_all[0].numpy()
+    for i in range(N):
+        c2d = cubes[i].get_bube_corners(f.K, (W, H))
+        s_iou = R.scorefunction.score_iou(boxes[i], pb[i])
+        s_dim = R.scorefunction.score_dimensions((f.prior_mean[i], f.prior_std[i]), cubes[i].dimensions[0],
+                                                 boxes[i], pb[i])
+        s_cor = R.scorefunction.score_corners(f.masks[i], c2d)
+        c = np.asarray(s_iou) * np.asarray(s_dim) * np.asarray(s_cor)
+        iou[i], dim[i], cor[i], comb[i] = s_iou.numpy(), s_dim.numpy(), s_cor.numpy(), c
+        best[i] = int(np.argmax(c))
+        r = O.mask_rect(f.masks[i].numpy().astype(np.uint8))
+        if r is not None:
+            rects[i] = r
+    out.update(iou=iou, dim=dim, cor=cor, combined=comb, best=best, rects=rects)
+    for i in mode_b_objs:
+        c2d = cubes[i].get_bube_corners(f.K, (W, H))
+        out["seg_%d" % i] = R.scorefunction.score_segmentation(f.masks[i], c2d).numpy()
+        out["modseg_%d" % i] = R.scorefunction.score_mod_segmentation(f.masks[i], c2d).numpy()
+    return out, cubes
+
+
+def main():
+    ver = O.versions()
+    # ---- G1: BASELINE config 1: 640x480, 5 boxes x 1000 cubes, mode A, ground normal from RANSAC ----
+    W, H, n = 640, 480, 1000
+    f = synth.make_frame(0, H, W, 5)
+    pg, pn, ids, eq, inl, nv = ref_normal(f, seed=0)
+    out, cubes = ref_frame(f, n, seed=13, normal=nv, W=W, H=H)
+    # point-cloud score of object 0 against the no-ground points (fp64), roi_heads.py:535
+    pc = R.scorefunction.score_point_cloud(torch.from_numpy(pn), cubes[0]).numpy()
+    np.savez_compressed(os.path.join(HERE, "c1_modeA.npz"), versions=ver, frame_id=0, H=H, W=W, n_obj=5, n=n,
+                        seed=13, ransac_seed=0, input_sha=frame_digest(f), plane_eq=eq, n_inliers=len(inl),
+                        inlier_sha=digest(inl.astype(np.int64)), sample_ids=ids.astype(np.int32),
+                        normal=nv, n_plane_pts=len(pg), n_noground_pts=len(pn), pc_obj0=pc, **out)
+
+    # ---- G2: mode B on a smaller proposal count (segmentation / mod-seg are slow in the reference) ----
+    n2 = 256
+    out2, cubes2 = ref_frame(f, n2, seed=21, normal=nv, W=W, H=H, mode_b_objs=(0, 1, 2, 3, 4))
+    pcs = np.stack([R.scorefunction.score_point_cloud(torch.from_numpy(pn), cubes2[i]).numpy() for i in range(5)])
+    np.savez_compressed(os.path.join(HERE, "c1_modeB.npz"), versions=ver, frame_id=0, H=H, W=W, n_obj=5, n=n2,
+                        seed=21, input_sha=frame_digest(f), normal=nv, pc=pcs, **out2)
+
+    # ---- G3: no ground normal -> random rotations (randn_orthobasis_torch), other frame / shape ----
+    W3, H3, n3 = 730, 530, 128
+    f3 = synth.make_frame(7, H3, W3, 3)
+    out3, _ = ref_frame(f3, n3, seed=5, normal=None, W=W3, H=H3, mode_b_objs=(0,))
+    np.savez_compressed(os.path.join(HERE, "c2_randrot.npz"), versions=ver, frame_id=7, H=H3, W=W3, n_obj=3, n=n3,
+                        seed=5, input_sha=frame_digest(f3), **out3)
+
+    # ---- G4: planes.  torch flavour (fp32 fit_parallel) on the synthetic frame; NumPy flavour and
+    #      fit_parallel on a fixed subsample of the reference's caixa.ply fixture (test_plane.py:29-35) ----
+    f4 = synth.make_frame(1, 480, 640, 5)
+    pts32 = O.backproject_torch(f4.depth, f4.K, f4.ground)
+    random.seed(3)
+    eq32, inl32 = R.plane.Plane().fit_parallel(pts32, 0.05, maxIteration=1000)
+    random.seed(3)
+    ids32 = O.draw_sample_ids(len(pts32), 1000, random)
+    raw = open(os.path.join(ref_import.REF_ROOT, "ProposalNetwork/utils/tests/caixa.ply"), "rb").read()
+    hd = raw.index(b"end_header\n") + len(b"end_header\n")
+    arr = np.frombuffer(raw[hd:], dtype=np.dtype([("p", "<f8", 3), ("c", "u1", 3)]))
+    caixa = np.ascontiguousarray(arr["p"])
+    random.seed(0)
+    eq_full, inl_full = R.plane.Plane_np().fit(caixa, thresh=0.01, maxIteration=1000)
+    sub = caixa[::6].copy()                                    # 7729 points, fp64
+    random.seed(1)
+    eq_sub, inl_sub = R.plane.Plane_np().fit(sub, thresh=0.01, maxIteration=1000)
+    random.seed(1)
+    ids_sub = O.draw_sample_ids(len(sub), 1000, random)
+    sub32 = torch.from_numpy(sub).float()
+    random.seed(1)
+    eq_sub32, inl_sub32 = R.plane.Plane().fit_parallel(sub32, 0.01, maxIteration=1000)
+    np.savez_compressed(os.path.join(HERE, "planes.npz"), versions=ver, frame_id=1, H=480, W=640, n_obj=5,
+                        input_sha=frame_digest(f4), torch_n_pts=len(pts32), torch_ids=ids32.astype(np.int32),
+                        torch_eq=eq32.numpy(), torch_inlier_sha=digest(inl32.numpy()), torch_n_inliers=len(inl32),
+                        caixa_full_eq=np.array(eq_full), caixa_full_n_inliers=len(inl_full),
+                        caixa_sub=sub, caixa_sub_ids=ids_sub.astype(np.int32), caixa_sub_eq=np.array(eq_sub),
+                        caixa_sub_n_inliers=len(inl_sub), caixa_sub_inlier_sha=digest(np.asarray(inl_sub, np.int64)),
+                        caixa_sub32_eq=eq_sub32.numpy(), caixa_sub32_n_inliers=len(inl_sub32))
+
+    # ---- G5: the reference's real SAM-HQ masks (ProposalNetwork/mask0.pkl, mask1.pkl) -> rectangle ----
+    real = {}
+    for name in ("mask0", "mask1"):
+        m = pickle.load(open(os.path.join(ref_import.REF_ROOT, "ProposalNetwork", name + ".pkl"), "rb"))
+        m = np.asarray(m).astype(bool).reshape(m.shape[-2], m.shape[-1])
+        real[name + "_shape"] = np.array(m.shape)
+        real[name + "_bits"] = np.packbits(m)
+        real[name + "_rect"] = O.mask_rect(m.astype(np.uint8))
+        # score_corners on a handful of synthetic projected corners through the reference
+        rs = np.random.RandomState(3)
+        c2d = torch.tensor(rs.uniform(0, max(m.shape), (1, 64, 8, 2)).astype(np.float32))
+        real[name + "_c2d"] = c2d[0].numpy()
+        real[name + "_cor"] = R.scorefunction.score_corners(torch.from_numpy(m), c2d).numpy()
+    np.savez_compressed(os.path.join(HERE, "real_masks.npz"), versions=ver, **real)
+
+    # ---- G6: degenerate semantics: empty mask (fallback rectangle), zero-height boxes -> NaN-first argmax,
+    #      cubes behind the camera (no z>0 guard), point-cloud known answer (scorefunction.py:199-201) ----
+    Wd, Hd = 320, 240
+    Kd = torch.tensor([[288.0, 0, 160.0], [0, 288.0, 120.0], [0, 0, 1]])
+    rs = np.random.RandomState(11)
+    nd = 64
+    t = np.zeros((1, nd, 15), np.float32)
+    t[0, :, 0:3] = rs.uniform([-1, -1, 1.5], [1, 1, 4], (nd, 3))
+    t[0, :, 3:6] = rs.uniform(0.2, 1.0, (nd, 3))
+    Rm = O.random_rotations(1, nd, torch.Generator().manual_seed(2))
+    t[0, :, 6:] = Rm.reshape(1, nd, 9).numpy()
+    t[0, 5, 2] = -2.0            # behind the camera
+    t[0, 9, 2] = 0.05            # straddles the image plane
+    t[0, 17, 0:3] = [30.0, 40.0, 1.0]   # projects far outside -> clamped to a zero-height box -> NaN score
+    t[0, 40, 0:3] = [30.0, 40.0, 1.0]
+    cub = R.spaces.Cubes(torch.from_numpy(t))
+    gt = R.Boxes(torch.tensor([[60.0, 50.0, 200.0, 170.0]]))
+    pbd = R.conversions.cubes_to_box(cub, Kd, (Wd, Hd))
+    c2d = cub.get_bube_corners(Kd, (Wd, Hd))
+    pm, ps = torch.tensor([0.6, 0.5, 0.7]), torch.tensor([0.2, 0.15, 0.25])
+    s_iou = R.scorefunction.score_iou(gt, pbd[0])
+    s_dim = R.scorefunction.score_dimensions((pm, ps), cub[0].dimensions[0], gt, pbd[0])
+    empty = torch.zeros((Hd, Wd), dtype=torch.bool)
+    s_cor = R.scorefunction.score_corners(empty, c2d)
+    comb = np.asarray(s_iou) * np.asarray(s_dim) * np.asarray(s_cor)
+    pts3 = torch.tensor([[0.1, 0.1, 0.1], [0.2, 0.2, 0.2], [-3, 0, 0]])
+    unit = torch.tensor([[[0.5, 0.5, 0.5, 1, 1, 1, 1, 0, 0, 0, 1, 0, 0, 0, 1]]], dtype=torch.float32)
+    pc_unit = R.scorefunction.score_point_cloud(pts3, R.spaces.Cubes(unit)).numpy()
+    np.savez_compressed(os.path.join(HERE, "degenerate.npz"), versions=ver, W=Wd, H=Hd, K=Kd.numpy(), cubes=t,
+                        ref_box=gt.tensor.numpy(), prior_mean=pm.numpy(), prior_std=ps.numpy(),
+                        boxes=pbd[0].tensor.numpy(), corners2d=c2d[0].numpy(), iou=s_iou.numpy(), dim=s_dim.numpy(),
+                        cor_emptymask=s_cor.numpy(), combined=comb, best=int(np.argmax(comb)),
+                        pc_points=pts3.numpy(), pc_cube=unit.numpy(), pc_count=pc_unit)
+    for fn in sorted(os.listdir(HERE)):
+        if fn.endswith(".npz"):
+            print(fn, os.path.getsize(os.path.join(HERE, fn)) // 1024, "KiB")
+
+
+if __name__ == "__main__":
+    main()
