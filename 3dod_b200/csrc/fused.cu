@@ -1,0 +1,517 @@
+// K-C: fused propose + project + score + select.  One thread-block cluster (1..8 CTAs) per object.
+//
+// Restates, per object, ProposalNetwork/proposals/proposals.py:338-424 (propose),
+// utils/spaces.py:192-245 (corners + projection), utils/conversions.py:25-48 (box),
+// scoring/scorefunction.py:47-49 (IoU), :144-160 (dims x aspect), :69-85 + :51-56 (chamfer to the mask
+// rectangle), cubercnn/modeling/roi_heads/roi_heads.py:499-502 (product + np.argmax).
+//
+// Nothing per-proposal goes to HBM in select mode: the n proposals of an object live in shared memory /
+// registers of its cluster; the three per-object reductions the reference's scores need (median+std of the
+// centre seeds, max aspect difference, max chamfer distance) and the argmax run over DSMEM.
+#include <cooperative_groups.h>
+#include "tdod_device.cuh"
+#include "tdod_internal.h"
+
+namespace cg = cooperative_groups;
+using namespace tdod;
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+constexpr int kMaxCluster = 8;
+
+struct Mail {               // per-CTA mailbox read by every CTA of the cluster through DSMEM
+    int hist[4][3][256];    // radix-select histograms, one buffer per pass (no WAR hazard)
+    double sum[3];          // sum of seeds
+    double m2[3];           // sum of squared deviations
+    double boxsum[4];       // fallback rectangle: sums of proposal box coordinates
+    float maxdiff, maxd;
+    int nanflag[3];
+    float am_v;
+    int am_i;
+};
+
+struct Shared {
+    Mail mail;
+    // block-level scratch
+    double red_d[kWarps][4];
+    float red_f[kWarps][2];
+    int red_i[kWarps];
+    uint32_t prefix[3];
+    int kth[3];
+    float med[3];
+    float rect[8];
+    float K[9];
+    float yaw[TDOD_NYAW * 9];
+};
+
+struct ObjCtx {
+    int obj, frame;
+    float bx0, by0, bx1, by1;      // sampling / aspect box
+    float lox, stepx, loy, stepy;  // vectorized_linspace parameters
+    float mu[3], sg[3];            // priors (w,h,l)
+    float sgh;                     // std_h * 1.1
+    float hi[3];                   // upper truncation per dimension
+};
+
+// accepted standard normals for (w,h,l) of proposal i
+__device__ __forceinline__ void draw_whl(const tdod_pss_args& a, const ObjCtx& c, int i, float& w, float& h, float& l) {
+    if (a.rng_mode == TDOD_RNG_HOST) {
+        const float* nz = a.noise + (size_t)c.obj * 6 * a.n_prop;
+        w = scale_normal(nz[i], c.mu[0], c.sg[0]);
+        h = scale_normal(nz[a.n_prop + i], c.mu[1], c.sgh);
+        l = scale_normal(nz[2 * a.n_prop + i], c.mu[2], c.sg[2]);
+        return;
+    }
+    // utils.py:49-58: invalid entries are replaced by fresh draws until all are in [0.05, mean + k std];
+    // per element that is an independent rejection loop (same distribution, Philox stream).
+    const Philox ph(a.seed);
+    const uint64_t gid = (uint64_t)(a.obj_id_base + c.obj);
+    bool okw = false, okh = false, okl = false;
+    w = h = l = 0.f;
+    for (uint32_t t = 0; t < 10001u && !(okw && okh && okl); ++t) {
+        const uint4 r = ph((uint32_t)i, (uint32_t)gid, (uint32_t)(gid >> 32) ^ 0x57484Cu, t);
+        const float2 n01 = box_muller(r.x, r.y), n23 = box_muller(r.z, r.w);
+        if (!okw) { w = scale_normal(n01.x, c.mu[0], c.sg[0]); okw = !(w < TDOD_MIN_PROP_S || w > c.hi[0]); }
+        if (!okh) { h = scale_normal(n01.y, c.mu[1], c.sgh);   okh = !(h < TDOD_MIN_PROP_S || h > c.hi[1]); }
+        if (!okl) { l = scale_normal(n23.x, c.mu[2], c.sg[2]); okl = !(l < TDOD_MIN_PROP_S || l > c.hi[2]); }
+    }
+}
+
+// standard normals for x,y,z and the rotation of proposal i -> q[0..2], q[6..14]
+__device__ __forceinline__ void draw_xyz_rot(const tdod_pss_args& a, const ObjCtx& c, const float* yaw, int i,
+                                             const float (&mean)[3], const float (&sd)[3], float* q) {
+    if (a.rng_mode == TDOD_RNG_HOST) {
+        const float* nz = a.noise + (size_t)c.obj * 6 * a.n_prop;
+        q[0] = scale_normal(nz[3 * a.n_prop + i], mean[0], sd[0]);
+        q[1] = scale_normal(nz[4 * a.n_prop + i], mean[1], sd[1]);
+        q[2] = scale_normal(nz[5 * a.n_prop + i], mean[2], sd[2]);
+        if (a.yaw_table) {
+            const int yi = a.yaw_idx[(size_t)c.obj * a.n_prop + i];
+#pragma unroll
+            for (int k = 0; k < 9; ++k) q[6 + k] = yaw[yi * 9 + k];
+        } else {
+            const float* r = a.rot + ((size_t)c.obj * a.n_prop + i) * 9;
+#pragma unroll
+            for (int k = 0; k < 9; ++k) q[6 + k] = r[k];
+        }
+        return;
+    }
+    const Philox ph(a.seed);
+    const uint64_t gid = (uint64_t)(a.obj_id_base + c.obj);
+    const uint4 r = ph((uint32_t)i, (uint32_t)gid, (uint32_t)(gid >> 32) ^ 0x58595Au, 0u);
+    const float2 n01 = box_muller(r.x, r.y);
+    q[0] = scale_normal(n01.x, mean[0], sd[0]);
+    q[1] = scale_normal(n01.y, mean[1], sd[1]);
+    if (a.yaw_table) {
+        const float2 n23 = box_muller(r.z, r.w);
+        q[2] = scale_normal(n23.x, mean[2], sd[2]);
+        const uint4 r2 = ph((uint32_t)i, (uint32_t)gid, (uint32_t)(gid >> 32) ^ 0x58595Au, 1u);
+        const int yi = (int)(r2.x % TDOD_NYAW);  // torch.randint(36, ...): u32 % 36
+#pragma unroll
+        for (int k = 0; k < 9; ++k) q[6 + k] = yaw[yi * 9 + k];
+    } else {
+        const float2 n23 = box_muller(r.z, r.w);
+        q[2] = scale_normal(n23.x, mean[2], sd[2]);
+        // utils.py:62-69 randn_orthobasis_torch: rows normalised, row0 = r1 x r2, row1 = r2 x row0
+        float m[9];
+#pragma unroll
+        for (int t = 0; t < 3; ++t) {
+            const uint4 s = ph((uint32_t)i, (uint32_t)gid, (uint32_t)(gid >> 32) ^ 0x524F54u, 1u + t);
+            const float2 a01 = box_muller(s.x, s.y), a23 = box_muller(s.z, s.w);
+            const float inv = rsqrtf(a01.x * a01.x + a01.y * a01.y + a23.x * a23.x);
+            m[3 * t] = a01.x * inv; m[3 * t + 1] = a01.y * inv; m[3 * t + 2] = a23.x * inv;
+        }
+        float c0 = m[4] * m[8] - m[5] * m[7], c1 = m[5] * m[6] - m[3] * m[8], c2 = m[3] * m[7] - m[4] * m[6];
+        float inv = rsqrtf(c0 * c0 + c1 * c1 + c2 * c2);
+        m[0] = c0 * inv; m[1] = c1 * inv; m[2] = c2 * inv;
+        c0 = m[7] * m[2] - m[8] * m[1]; c1 = m[8] * m[0] - m[6] * m[2]; c2 = m[6] * m[1] - m[7] * m[0];
+        inv = rsqrtf(c0 * c0 + c1 * c1 + c2 * c2);
+        m[3] = c0 * inv; m[4] = c1 * inv; m[5] = c2 * inv;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) q[6 + k] = m[k];
+    }
+}
+
+template <typename T>
+__device__ __forceinline__ T* remote(cg::cluster_group& cl, T* p, int rank) {
+    return cl.map_shared_rank(p, rank);
+}
+
+__global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a, const int n_loc) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    cg::cluster_group cl = cg::this_cluster();
+    const int S = (int)cl.num_blocks();
+    const int rank = (int)cl.block_rank();
+    const int obj = (int)(blockIdx.x / S);
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+
+    Shared& sh = *reinterpret_cast<Shared*>(smem_raw);
+    float* arr = reinterpret_cast<float*>(smem_raw + ((sizeof(Shared) + 15) & ~size_t(15)));
+    // seven per-proposal arrays of n_loc floats:
+    float* s_x = arr;                  // seed x        -> later: iou
+    float* s_y = arr + n_loc;          // seed y        -> later: dims gauss
+    float* s_z = arr + 2 * n_loc;      // seed z_tmp+l/2-> later: aspect difference
+    float* s_w = arr + 3 * n_loc;
+    float* s_h = arr + 4 * n_loc;
+    float* s_l = arr + 5 * n_loc;
+    float* s_d = arr + 6 * n_loc;      // chamfer distance
+
+    const int n = a.n_prop;
+    const int i0 = rank * n_loc;
+    const int cnt = max(0, min(n - i0, n_loc));
+
+    // ---------------- phase 0: object context ----------------
+    ObjCtx c;
+    c.obj = obj;
+    c.frame = a.obj_frame ? a.obj_frame[obj] : 0;
+    {
+        const float* b = a.boxes + (size_t)obj * 4;
+        c.bx0 = b[0]; c.by0 = b[1]; c.bx1 = b[2]; c.by1 = b[3];
+        const float bw = __fsub_rn(c.bx1, c.bx0), bh = __fsub_rn(c.by1, c.by0);
+        const float qx = __fdiv_rn(bw, 4.f), qy = __fdiv_rn(bh, 4.f);
+        c.lox = __fadd_rn(c.bx0, qx);
+        c.loy = __fadd_rn(c.by0, qy);
+        const float hix = __fsub_rn(c.bx1, qx), hiy = __fsub_rn(c.by1, qy);
+        c.stepx = __fdiv_rn(__fsub_rn(hix, c.lox), (float)(n - 1));
+        c.stepy = __fdiv_rn(__fsub_rn(hiy, c.loy), (float)(n - 1));
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            c.mu[k] = a.prior_mean[(size_t)obj * 3 + k];
+            c.sg[k] = a.prior_std[(size_t)obj * 3 + k];
+        }
+        c.sgh = __fmul_rn(c.sg[1], 1.1f);                                  // proposals.py:382
+        c.hi[0] = __fadd_rn(c.mu[0], __fmul_rn(2.f, c.sg[0]));             // :381
+        c.hi[1] = __fadd_rn(c.mu[1], __fmul_rn(2.2f, c.sg[1]));            // :382
+        c.hi[2] = __fadd_rn(c.mu[2], __fmul_rn(2.f, c.sg[2]));             // :383
+    }
+    if (tid < 9) sh.K[tid] = a.K[(size_t)c.frame * 9 + tid];
+    if (a.yaw_table)
+        for (int t = tid; t < TDOD_NYAW * 9; t += kThreads) sh.yaw[t] = a.yaw_table[(size_t)c.frame * TDOD_NYAW * 9 + t];
+    const bool has_rect = a.has_rect ? (a.has_rect[obj] != 0) : true;
+    if (tid < 8) sh.rect[tid] = has_rect ? a.rects[(size_t)obj * 8 + tid] : 0.f;
+    for (int t = tid; t < 4 * 3 * 256; t += kThreads) (&sh.mail.hist[0][0][0])[t] = 0;
+    if (tid < 3) { sh.prefix[tid] = 0u; sh.kth[tid] = (n - 1) / 2; sh.mail.nanflag[tid] = 0; }
+    __syncthreads();
+
+    // ---------------- phase 1: centre seeds + dimensions ----------------
+    const float* depth = a.depth + (size_t)c.frame * a.H * a.W;
+    const float fx = sh.K[0], cx = sh.K[2], cy = sh.K[5];
+    double lsum[3] = {0.0, 0.0, 0.0};
+    int lnan[3] = {0, 0, 0};
+    for (int j = tid; j < cnt; j += kThreads) {
+        const int i = i0 + j;
+        int gx = linspace_px(c.lox, c.stepx, i);
+        int gy = linspace_px(c.loy, c.stepy, i);
+        // torch indexing: negative indices wrap once; anything else out of range would raise in the
+        // reference -- we clamp instead of faulting.
+        int ix = gx < 0 ? gx + a.W : gx, iy = gy < 0 ? gy + a.H : gy;
+        ix = min(max(ix, 0), a.W - 1); iy = min(max(iy, 0), a.H - 1);
+        const float d = __ldg(depth + (size_t)iy * a.W + ix);
+        float x, y, zt, w, h, l;
+        centre_seed(gx, gy, d, fx, cx, cy, x, y, zt);
+        draw_whl(a, c, i, w, h, l);
+        const float z = __fadd_rn(zt, __fdiv_rn(l, 2.f));                  // proposals.py:394
+        s_x[j] = x; s_y[j] = y; s_z[j] = z; s_w[j] = w; s_h[j] = h; s_l[j] = l;
+        lsum[0] += (double)x; lsum[1] += (double)y; lsum[2] += (double)z;
+        lnan[0] |= (x != x); lnan[1] |= (y != y); lnan[2] |= (z != z);
+        atomicAdd(&sh.mail.hist[0][0][f2key(x) >> 24], 1);
+        atomicAdd(&sh.mail.hist[0][1][f2key(y) >> 24], 1);
+        atomicAdd(&sh.mail.hist[0][2][f2key(z) >> 24], 1);
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        lsum[k] = warp_sum_d(lsum[k]);
+        if (__any_sync(0xffffffffu, lnan[k]) && lane == 0) atomicOr(&sh.mail.nanflag[k], 1);
+    }
+    if (lane == 0) { sh.red_d[wid][0] = lsum[0]; sh.red_d[wid][1] = lsum[1]; sh.red_d[wid][2] = lsum[2]; }
+    __syncthreads();
+    if (tid < 3) {
+        double s = 0.0;
+        for (int w2 = 0; w2 < kWarps; ++w2) s += sh.red_d[w2][tid];
+        sh.mail.sum[tid] = s;
+    }
+    cl.sync();   // (1) pass-0 histograms, partial sums and NaN flags visible cluster-wide
+
+    // ---------------- exact lower median (torch.median) by 4-pass radix select over the cluster ----------------
+    for (int pass = 0; pass < 4; ++pass) {
+        if (pass > 0) {
+            const int shift = 24 - 8 * pass;
+            const uint32_t himask = 0xffffffffu << (shift + 8);
+            const uint32_t p0 = sh.prefix[0], p1 = sh.prefix[1], p2 = sh.prefix[2];
+            for (int j = tid; j < cnt; j += kThreads) {
+                const uint32_t kx = f2key(s_x[j]), ky = f2key(s_y[j]), kz = f2key(s_z[j]);
+                if ((kx & himask) == p0) atomicAdd(&sh.mail.hist[pass][0][(kx >> shift) & 255u], 1);
+                if ((ky & himask) == p1) atomicAdd(&sh.mail.hist[pass][1][(ky >> shift) & 255u], 1);
+                if ((kz & himask) == p2) atomicAdd(&sh.mail.hist[pass][2][(kz >> shift) & 255u], 1);
+            }
+            cl.sync();   // (2..4)
+        }
+        if (wid < 3) {   // warp `wid` resolves array `wid`: lane owns bins [8*lane, 8*lane+8)
+            int bins[8];
+#pragma unroll
+            for (int b = 0; b < 8; ++b) bins[b] = 0;
+            for (int r = 0; r < S; ++r) {
+                const int* hr = remote(cl, &sh.mail.hist[pass][wid][0], r);
+#pragma unroll
+                for (int b = 0; b < 8; ++b) bins[b] += hr[8 * lane + b];
+            }
+            int tot = 0;
+#pragma unroll
+            for (int b = 0; b < 8; ++b) tot += bins[b];
+            int incl = tot;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += v;
+            }
+            const int excl = incl - tot;
+            const int k = sh.kth[wid];
+            __syncwarp();
+            if (k >= excl && k < incl) {   // exactly one lane
+                int run = excl, b = 0;
+#pragma unroll
+                for (b = 0; b < 8; ++b) {
+                    if (k < run + bins[b]) break;
+                    run += bins[b];
+                }
+                sh.prefix[wid] |= (uint32_t)(8 * lane + b) << (24 - 8 * pass);
+                sh.kth[wid] = k - run;
+            }
+        }
+        __syncthreads();
+    }
+    if (tid < 3) {
+        int anynan = 0;
+        for (int r = 0; r < S; ++r) anynan |= *remote(cl, &sh.mail.nanflag[tid], r);
+        sh.med[tid] = anynan ? CUDART_NAN_F : key2f(sh.prefix[tid]);
+    }
+    // mean over the cluster, then squared deviations (two-pass, fp64: torch CPU accumulates std in double)
+    double mean[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        double s = 0.0;
+        for (int r = 0; r < S; ++r) s += *remote(cl, &sh.mail.sum[k], r);
+        mean[k] = s / (double)n;
+    }
+    double lm2[3] = {0.0, 0.0, 0.0};
+    for (int j = tid; j < cnt; j += kThreads) {
+        const double dx = (double)s_x[j] - mean[0], dy = (double)s_y[j] - mean[1], dz = (double)s_z[j] - mean[2];
+        lm2[0] += dx * dx; lm2[1] += dy * dy; lm2[2] += dz * dz;
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) lm2[k] = warp_sum_d(lm2[k]);
+    if (lane == 0) { sh.red_d[wid][0] = lm2[0]; sh.red_d[wid][1] = lm2[1]; sh.red_d[wid][2] = lm2[2]; }
+    __syncthreads();
+    if (tid < 3) {
+        double s = 0.0;
+        for (int w2 = 0; w2 < kWarps; ++w2) s += sh.red_d[w2][tid];
+        sh.mail.m2[tid] = s;
+    }
+    cl.sync();   // (5)
+    float smean[3], ssd[3];
+    {
+        const float coef_a[3] = {1.15f, 1.1f, 0.85f}, coef_b[3] = {0.f, 0.f, 0.35f}, coef_s[3] = {1.2f, 0.8f, 1.2f};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            double s = 0.0;
+            for (int r = 0; r < S; ++r) s += *remote(cl, &sh.mail.m2[k], r);
+            const float sd = (float)sqrt(s / (double)(n - 1));              // torch.std: unbiased
+            smean[k] = __fadd_rn(__fmul_rn(coef_a[k], sh.med[k]), coef_b[k]);   // lin_fun, proposals.py:16-18
+            ssd[k] = __fmul_rn(sd, coef_s[k]);
+        }
+    }
+    if (a.stats && rank == 0 && tid == 0) {
+        float* st = a.stats + (size_t)obj * 6;
+        st[0] = smean[0]; st[1] = ssd[0]; st[2] = smean[1]; st[3] = ssd[1]; st[4] = smean[2]; st[5] = ssd[2];
+    }
+
+    // ---------------- phase 2: cube -> corners -> projection -> box -> scores ----------------
+    const Clamp clampr = make_clamp(a.W, a.H);
+    const float* ib = a.iou_boxes ? a.iou_boxes + (size_t)obj * 4 : a.boxes + (size_t)obj * 4;
+    const float ib0 = ib[0], ib1 = ib[1], ib2 = ib[2], ib3 = ib[3];
+    const float r_ref = __fdiv_rn(__fsub_rn(c.bx1, c.bx0), __fsub_rn(c.by1, c.by0));   // scorefunction.py:154
+
+    for (int sweep = has_rect ? 1 : 0; sweep < 2; ++sweep) {
+        // sweep 0 (only without a mask rectangle): proposal boxes -> fallback rectangle (scorefunction.py:69-75)
+        double bsum[4] = {0.0, 0.0, 0.0, 0.0};
+        float lmaxdiff = -CUDART_INF_F, lmaxd = -CUDART_INF_F;
+        for (int j = tid; j < cnt; j += kThreads) {
+            const int i = i0 + j;
+            float q[15];
+            draw_xyz_rot(a, c, sh.yaw, i, smean, ssd, q);
+            q[3] = s_w[j]; q[4] = s_h[j]; q[5] = s_l[j];
+            float X[8], Y[8], Z[8], U[8], V[8];
+            cube_corners(q, X, Y, Z);
+            float x0 = CUDART_INF_F, y0 = CUDART_INF_F, x1 = -CUDART_INF_F, y1 = -CUDART_INF_F;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                project(sh.K, clampr, X[k], Y[k], Z[k], U[k], V[k]);
+                x0 = min_nan(x0, U[k]); x1 = max_nan(x1, U[k]);
+                y0 = min_nan(y0, V[k]); y1 = max_nan(y1, V[k]);
+            }
+            if (sweep == 0) {
+                bsum[0] += (double)x0; bsum[1] += (double)y0; bsum[2] += (double)x1; bsum[3] += (double)y1;
+                continue;
+            }
+            const float iou = iou_xyxy(ib0, ib1, ib2, ib3, x0, y0, x1, y1);
+            const float g = dims_gauss(q[3], q[4], q[5], c.mu, c.sg);
+            const float ratio = __fdiv_rn(__fsub_rn(x1, x0), __fsub_rn(y1, y0));
+            const float diff = fabsf(__fsub_rn(r_ref, ratio));
+            const float d = chamfer4x8(sh.rect, U, V);
+            s_x[j] = iou; s_y[j] = g; s_z[j] = diff; s_d[j] = d;
+            lmaxdiff = (lmaxdiff != lmaxdiff || diff != diff) ? CUDART_NAN_F : fmaxf(lmaxdiff, diff);
+            lmaxd = (lmaxd != lmaxd || d != d) ? CUDART_NAN_F : fmaxf(lmaxd, d);
+            if (a.all_cubes) {
+                float* oc = a.all_cubes + ((size_t)obj * n + i) * 15;
+#pragma unroll
+                for (int k = 0; k < 15; ++k) oc[k] = q[k];
+            }
+            if (a.all_boxes) {
+                float4* ob = reinterpret_cast<float4*>(a.all_boxes + ((size_t)obj * n + i) * 4);
+                *ob = make_float4(x0, y0, x1, y1);
+            }
+        }
+        if (sweep == 0) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) bsum[k] = warp_sum_d(bsum[k]);
+            if (lane == 0) { for (int k = 0; k < 4; ++k) sh.red_d[wid][k] = bsum[k]; }
+            __syncthreads();
+            if (tid < 4) {
+                double s = 0.0;
+                for (int w2 = 0; w2 < kWarps; ++w2) s += sh.red_d[w2][tid];
+                sh.mail.boxsum[tid] = s;
+            }
+            cl.sync();   // (5b)
+            if (tid == 0) {
+                double t4[4];
+                for (int k = 0; k < 4; ++k) {
+                    double s = 0.0;
+                    for (int r = 0; r < S; ++r) s += *remote(cl, &sh.mail.boxsum[k], r);
+                    t4[k] = (double)(float)(s / (double)n);   // torch .mean() of fp32 -> fp32
+                }
+                // [[x0,y0],[x1,y0],[x1,y1],[x0,y1]]
+                sh.rect[0] = (float)t4[0]; sh.rect[1] = (float)t4[1]; sh.rect[2] = (float)t4[2]; sh.rect[3] = (float)t4[1];
+                sh.rect[4] = (float)t4[2]; sh.rect[5] = (float)t4[3]; sh.rect[6] = (float)t4[0]; sh.rect[7] = (float)t4[3];
+            }
+            __syncthreads();
+            continue;
+        }
+        lmaxdiff = warp_max_nan(lmaxdiff);
+        lmaxd = warp_max_nan(lmaxd);
+        if (lane == 0) { sh.red_f[wid][0] = lmaxdiff; sh.red_f[wid][1] = lmaxd; }
+        __syncthreads();
+        if (tid < 2) {
+            float m = -CUDART_INF_F;
+            for (int w2 = 0; w2 < kWarps; ++w2) {
+                const float v = sh.red_f[w2][tid];
+                m = (m != m || v != v) ? CUDART_NAN_F : fmaxf(m, v);
+            }
+            if (tid == 0) sh.mail.maxdiff = m; else sh.mail.maxd = m;
+        }
+    }
+    cl.sync();   // (6)
+    float maxdiff = -CUDART_INF_F, maxd = -CUDART_INF_F;
+    for (int r = 0; r < S; ++r) {
+        const float v0 = *remote(cl, &sh.mail.maxdiff, r), v1 = *remote(cl, &sh.mail.maxd, r);
+        maxdiff = (maxdiff != maxdiff || v0 != v0) ? CUDART_NAN_F : fmaxf(maxdiff, v0);
+        maxd = (maxd != maxd || v1 != v1) ? CUDART_NAN_F : fmaxf(maxd, v1);
+    }
+
+    // ---------------- phase 3: final scores, argmax (np.argmax: first NaN, else first maximum) ----------------
+    ArgMax best;
+    best.v = -CUDART_INF_F; best.i = 0x7fffffff;
+    for (int j = tid; j < cnt; j += kThreads) {
+        const int i = i0 + j;
+        const float iou = s_x[j], g = s_y[j], diff = s_z[j], d = s_d[j];
+        const float dim = __fmul_rn(__fsub_rn(1.f, __fdiv_rn(diff, maxdiff)), g);     // scorefunction.py:160
+        const float cor = __fsub_rn(1.f, __fdiv_rn(d, maxd));                        // :85
+        const float comb = __fmul_rn(__fmul_rn(iou, dim), cor);                      // roi_heads.py:499
+        if (a.all_scores) {
+            float* os = a.all_scores + (size_t)obj * 4 * n;
+            os[i] = iou; os[n + i] = dim; os[2 * n + i] = cor; os[3 * n + i] = comb;
+        }
+        if (argmax_better(best.v, best.i, comb, i)) { best.v = comb; best.i = i; }
+    }
+    best = warp_argmax(best);
+    if (lane == 0) { sh.red_f[wid][0] = best.v; sh.red_i[wid] = best.i; }
+    __syncthreads();
+    if (tid == 0) {
+        ArgMax b; b.v = sh.red_f[0][0]; b.i = sh.red_i[0];
+        for (int w2 = 1; w2 < kWarps; ++w2)
+            if (argmax_better(b.v, b.i, sh.red_f[w2][0], sh.red_i[w2])) { b.v = sh.red_f[w2][0]; b.i = sh.red_i[w2]; }
+        sh.mail.am_v = b.v; sh.mail.am_i = b.i;
+    }
+    cl.sync();   // (7)
+    ArgMax win; win.v = -CUDART_INF_F; win.i = 0x7fffffff;
+    for (int r = 0; r < S; ++r) {
+        const float v = *remote(cl, &sh.mail.am_v, r);
+        const int ii = *remote(cl, &sh.mail.am_i, r);
+        if (argmax_better(win.v, win.i, v, ii)) { win.v = v; win.i = ii; }
+    }
+    // the CTA that owns the winner recomputes its cube and box and writes the 84-byte record
+    if (win.i >= i0 && win.i < i0 + cnt && tid == 0) {
+        const int j = win.i - i0;
+        float q[15];
+        draw_xyz_rot(a, c, sh.yaw, win.i, smean, ssd, q);
+        q[3] = s_w[j]; q[4] = s_h[j]; q[5] = s_l[j];
+        float X[8], Y[8], Z[8];
+        cube_corners(q, X, Y, Z);
+        float x0 = CUDART_INF_F, y0 = CUDART_INF_F, x1 = -CUDART_INF_F, y1 = -CUDART_INF_F;
+        for (int k = 0; k < 8; ++k) {
+            float u, v;
+            project(sh.K, clampr, X[k], Y[k], Z[k], u, v);
+            x0 = min_nan(x0, u); x1 = max_nan(x1, u); y0 = min_nan(y0, v); y1 = max_nan(y1, v);
+        }
+        a.best_idx[obj] = win.i;
+        a.best_score[obj] = win.v;
+        for (int k = 0; k < 15; ++k) a.best_cube[(size_t)obj * 15 + k] = q[k];
+        float* bb = a.best_box + (size_t)obj * 4;
+        bb[0] = x0; bb[1] = y0; bb[2] = x1; bb[3] = y1;
+    }
+    cl.sync();   // (8) nobody leaves while a peer may still read its mailbox
+}
+
+}  // namespace
+
+extern "C" int tdod_propose_score_select(const tdod_pss_args* ap, void* stream) {
+    if (!ap) return tdod_fail(TDOD_EINVAL, "args is NULL");
+    const tdod_pss_args& a = *ap;
+    if (a.n_obj == 0) return TDOD_OK;
+    if (a.n_obj < 0 || a.n_prop < 2) return tdod_fail(TDOD_EINVAL, "n_obj must be >= 0 and n_prop >= 2");
+    if (!a.depth || !a.K || !a.boxes || !a.prior_mean || !a.prior_std || !a.best_idx || !a.best_score ||
+        !a.best_cube || !a.best_box)
+        return tdod_fail(TDOD_EINVAL, "a required pointer is NULL");
+    if (!a.rects && !a.has_rect) return tdod_fail(TDOD_EINVAL, "rects is NULL and has_rect does not say so");
+    if (a.H <= 0 || a.W <= 0 || a.F <= 0) return tdod_fail(TDOD_EINVAL, "bad frame shape");
+    if (a.rng_mode == TDOD_RNG_HOST) {
+        if (!a.noise) return tdod_fail(TDOD_EINVAL, "rng_mode HOST needs noise");
+        if (a.yaw_table ? !a.yaw_idx : !a.rot) return tdod_fail(TDOD_EINVAL, "rng_mode HOST needs yaw_idx (with yaw_table) or rot");
+    } else if (a.rng_mode != TDOD_RNG_PHILOX) {
+        return tdod_fail(TDOD_EINVAL, "unknown rng_mode");
+    }
+    int S = a.cluster_size;
+    if (S == 0) {
+        // one CTA handles up to 2048 proposals comfortably; spread larger objects, and small batches, over a cluster
+        S = 1;
+        while (S < kMaxCluster && ((a.n_prop + S - 1) / S > 2048 || ((int64_t)a.n_obj * S < 148 && (a.n_prop / (2 * S)) >= 256))) S *= 2;
+    }
+    if (S != 1 && S != 2 && S != 4 && S != 8) return tdod_fail(TDOD_EINVAL, "cluster_size must be 0,1,2,4,8");
+    const int n_loc = (a.n_prop + S - 1) / S;
+    const size_t smem = ((sizeof(Shared) + 15) & ~size_t(15)) + (size_t)7 * n_loc * sizeof(float);
+    if (smem > 227 * 1024) return tdod_fail(TDOD_ERANGE, "n_prop too large for shared memory at this cluster size");
+    cudaError_t e = cudaFuncSetAttribute(pss_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)((int64_t)a.n_obj * S), 1, 1);
+    cfg.blockDim = dim3(kThreads, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = S; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    e = cudaLaunchKernelEx(&cfg, pss_kernel, a, n_loc);
+    return (int)e;
+}

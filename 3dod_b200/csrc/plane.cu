@@ -1,0 +1,341 @@
+// K-A: depth -> strided point cloud, RANSAC ground plane, up-vector rectification.
+//
+// Restates cubercnn/modeling/roi_heads/roi_heads.py:345-428 (NumPy / pyransac3d flavour, fp64) and :1084-1136
+// (torch flavour, fp32) with ProposalNetwork/utils/plane.py:79-134 (fit_parallel) / :154-209 (Plane_np.fit ==
+// pyransac3d.Plane.fit).  The 1000 x P distance matrix of fit_parallel is never materialised: every CTA keeps a
+// few points per thread in registers, streams the hypotheses from shared memory and counts inliers with
+// warp ballots.
+#include "tdod_device.cuh"
+#include "tdod_internal.h"
+
+using namespace tdod;
+
+namespace {
+
+// separately rounded arithmetic (each is its own NumPy / torch op in the reference)
+template <typename T> struct Ar;
+template <> struct Ar<float> {
+    static __device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
+    static __device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
+    static __device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
+    static __device__ __forceinline__ float div(float a, float b) { return __fdiv_rn(a, b); }
+    static __device__ __forceinline__ float sqrt(float a) { return __fsqrt_rn(a); }
+    static __device__ __forceinline__ float up(float a) { return nextafterf(a, CUDART_INF_F); }
+    static __device__ __forceinline__ float down(float a) { return nextafterf(a, -CUDART_INF_F); }
+};
+template <> struct Ar<double> {
+    static __device__ __forceinline__ double mul(double a, double b) { return __dmul_rn(a, b); }
+    static __device__ __forceinline__ double add(double a, double b) { return __dadd_rn(a, b); }
+    static __device__ __forceinline__ double sub(double a, double b) { return __dsub_rn(a, b); }
+    static __device__ __forceinline__ double div(double a, double b) { return __ddiv_rn(a, b); }
+    static __device__ __forceinline__ double sqrt(double a) { return __dsqrt_rn(a); }
+    static __device__ __forceinline__ double up(double a) { return nextafter(a, CUDART_INF); }
+    static __device__ __forceinline__ double down(double a) { return nextafter(a, -CUDART_INF); }
+};
+
+// ------------------------------------------------------------------------------------------------
+// back-projection with row-major ordered compaction (one CTA per frame)
+// ------------------------------------------------------------------------------------------------
+template <typename T, int FLAVOUR>
+__global__ void __launch_bounds__(1024) backproject_kernel(const float* __restrict__ depth,
+                                                           const uint8_t* __restrict__ ground,
+                                                           const float* __restrict__ Kall, int H, int W, int stride,
+                                                           T* __restrict__ plane_pts, T* __restrict__ other_pts,
+                                                           int32_t* __restrict__ counts) {
+    __shared__ int warp_on[32], warp_off[32];
+    __shared__ int base_on, base_off;
+    const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int Hs = (H + stride - 1) / stride, Ws = (W + stride - 1) / stride;
+    const int64_t P = (int64_t)Hs * Ws;
+    const float* K = Kall + (size_t)f * 9;
+    const float* dp = depth + (size_t)f * H * W;
+    const uint8_t* gp = ground ? ground + (size_t)f * H * W : nullptr;
+    T fx, fy, cx, cy;
+    if (FLAVOUR == TDOD_BACKPROJECT_NUMPY) {   // roi_heads.py:347-352: full-resolution intrinsics
+        fx = (T)K[0]; fy = (T)K[4]; cx = (T)K[2]; cy = (T)K[5];
+    } else {                                   // roi_heads.py:1089-1092: K // stride, centre of the strided grid
+        fx = (T)floorf(__fdiv_rn(K[0], (float)stride)); fy = (T)floorf(__fdiv_rn(K[4], (float)stride));
+        cx = (T)((double)Ws / 2.0); cy = (T)((double)Hs / 2.0);
+    }
+    T* po = plane_pts + (size_t)f * 3 * P;
+    T* oo = other_pts ? other_pts + (size_t)f * 3 * P : nullptr;
+    if (tid == 0) { base_on = 0; base_off = 0; }
+    __syncthreads();
+    for (int64_t start = 0; start < P; start += 1024) {
+        const int64_t idx = start + tid;
+        bool valid = idx < P, on = false;
+        T x = 0, y = 0, z = 0;
+        if (valid) {
+            const int v = (int)(idx / Ws), u = (int)(idx - (int64_t)v * Ws);
+            const size_t pix = (size_t)(v * stride) * W + (size_t)(u * stride);
+            z = (T)__ldg(dp + pix);
+            x = Ar<T>::div(Ar<T>::mul(Ar<T>::sub((T)u, cx), z), fx);
+            y = Ar<T>::div(Ar<T>::mul(Ar<T>::sub((T)v, cy), z), fy);
+            on = gp ? (__ldg(gp + pix) > 0) : true;
+        }
+        const unsigned m_on = __ballot_sync(0xffffffffu, valid && on);
+        const unsigned m_off = __ballot_sync(0xffffffffu, valid && !on);
+        if (lane == 0) { warp_on[wid] = __popc(m_on); warp_off[wid] = __popc(m_off); }
+        __syncthreads();
+        int pre_on = base_on, pre_off = base_off;
+        for (int w = 0; w < wid; ++w) { pre_on += warp_on[w]; pre_off += warp_off[w]; }
+        const unsigned lt = (1u << lane) - 1u;
+        if (valid && on) {
+            const int p = pre_on + __popc(m_on & lt);
+            po[p] = x; po[P + p] = y; po[2 * P + p] = z;
+        } else if (valid && oo) {
+            const int p = pre_off + __popc(m_off & lt);
+            oo[p] = x; oo[P + p] = y; oo[2 * P + p] = z;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            int a = 0, b = 0;
+            for (int w = 0; w < 32; ++w) { a += warp_on[w]; b += warp_off[w]; }
+            base_on += a; base_off += b;
+        }
+        __syncthreads();
+    }
+    if (tid == 0) { counts[2 * f] = base_on; counts[2 * f + 1] = base_off; }
+}
+
+// ------------------------------------------------------------------------------------------------
+// hypotheses: sample ids -> plane (a,b,c,k) and the largest |numerator| that is still an inlier
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+struct PlaneHyp {
+    T a, b, c, k, bound;   // inlier  <=>  |a x + b y + c z + k| <= bound   (bound folds the division by ||n||)
+};
+
+template <typename T>
+__global__ void hypotheses_kernel(const T* __restrict__ pts, const int32_t* __restrict__ n_pts, int64_t P_cap,
+                                  const int32_t* __restrict__ ids, uint64_t seed, int iters, T thresh,
+                                  PlaneHyp<T>* __restrict__ hyps, int32_t* __restrict__ counts) {
+    const int f = blockIdx.y;
+    const int it = blockIdx.x * blockDim.x + threadIdx.x;
+    if (it >= iters) return;
+    const int P = n_pts[f];
+    PlaneHyp<T> h;
+    counts[(size_t)f * iters + it] = 0;
+    if (P < 3) {   // random.sample would raise in the reference; report "no plane"
+        h.a = h.b = h.c = h.k = 0; h.bound = (T)-1;
+        hyps[(size_t)f * iters + it] = h;
+        return;
+    }
+    int i0, i1, i2;
+    if (ids) {
+        const int32_t* s = ids + ((size_t)f * iters + it) * 3;
+        i0 = s[0]; i1 = s[1]; i2 = s[2];
+    } else {   // three distinct uniform indices
+        const Philox ph(seed);
+        const uint4 r = ph((uint32_t)it, (uint32_t)f, 0x52414Eu, 0u);
+        i0 = (int)(r.x % (uint32_t)P);
+        i1 = (int)(r.y % (uint32_t)(P - 1)); if (i1 >= i0) ++i1;
+        i2 = (int)(r.z % (uint32_t)(P - 2));
+        const int lo = min(i0, i1), hi = max(i0, i1);
+        if (i2 >= lo) ++i2;
+        if (i2 >= hi) ++i2;
+    }
+    const T* X = pts + (size_t)f * 3 * P_cap;
+    const T* Y = X + P_cap;
+    const T* Z = Y + P_cap;
+    const T p0x = X[i0], p0y = Y[i0], p0z = Z[i0], p1x = X[i1], p1y = Y[i1], p1z = Z[i1], p2x = X[i2], p2y = Y[i2],
+            p2z = Z[i2];
+    typedef Ar<T> A;
+    const T ax = A::sub(p1x, p0x), ay = A::sub(p1y, p0y), az = A::sub(p1z, p0z);       // plane.py:104 / :180
+    const T bx = A::sub(p2x, p0x), by = A::sub(p2y, p0y), bz = A::sub(p2z, p0z);       // :105 / :181
+    T cx = A::sub(A::mul(ay, bz), A::mul(az, by));                                     // cross, :108 / :184
+    T cy = A::sub(A::mul(az, bx), A::mul(ax, bz));
+    T cz = A::sub(A::mul(ax, by), A::mul(ay, bx));
+    const T nrm = A::sqrt(A::add(A::add(A::mul(cx, cx), A::mul(cy, cy)), A::mul(cz, cz)));
+    cx = A::div(cx, nrm); cy = A::div(cy, nrm); cz = A::div(cz, nrm);                   // :112 / :188
+    const T k = -A::add(A::add(A::mul(cx, p1x), A::mul(cy, p1y)), A::mul(cz, p1z));    // :113 / :189
+    const T den = A::sqrt(A::add(A::add(A::mul(cx, cx), A::mul(cy, cy)), A::mul(cz, cz)));   // :119 / :197
+    // largest t with fl(t / den) <= thresh (IEEE division is monotone in the numerator)
+    T t = A::mul(thresh, den);
+    if (!(den == den) || !(t == t)) {
+        t = (T)-1;   // degenerate (collinear) sample: NaN plane, no inliers (NaN <= thresh is false)
+    } else {
+        for (int g = 0; g < 8 && A::div(t, den) > thresh; ++g) t = A::down(t);
+        for (int g = 0; g < 8 && A::div(A::up(t), den) <= thresh; ++g) t = A::up(t);
+    }
+    h.a = cx; h.b = cy; h.c = cz; h.k = k; h.bound = t;
+    hyps[(size_t)f * iters + it] = h;
+}
+
+// ------------------------------------------------------------------------------------------------
+// inlier counting: grid (point tiles, frames); PT points per thread in registers, hypotheses in smem
+// ------------------------------------------------------------------------------------------------
+template <typename T, int PT>
+__global__ void __launch_bounds__(256) count_kernel(const T* __restrict__ pts, const int32_t* __restrict__ n_pts,
+                                                    int64_t P_cap, const PlaneHyp<T>* __restrict__ hyps, int iters,
+                                                    int32_t* __restrict__ counts) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    PlaneHyp<T>* sh = reinterpret_cast<PlaneHyp<T>*>(smem);
+    int* scount = reinterpret_cast<int*>(sh + iters);
+    const int f = blockIdx.y, tid = threadIdx.x, lane = tid & 31;
+    const int P = n_pts[f];
+    const int tile0 = blockIdx.x * (256 * PT);
+    if (tile0 >= P) return;
+    for (int i = tid; i < iters; i += 256) { sh[i] = hyps[(size_t)f * iters + i]; scount[i] = 0; }
+    const T* X = pts + (size_t)f * 3 * P_cap;
+    const T* Y = X + P_cap;
+    const T* Z = Y + P_cap;
+    T px[PT], py[PT], pz[PT];
+    bool ok[PT];
+#pragma unroll
+    for (int q = 0; q < PT; ++q) {
+        const int i = tile0 + q * 256 + tid;
+        ok[q] = i < P;
+        px[q] = ok[q] ? X[i] : (T)0; py[q] = ok[q] ? Y[i] : (T)0; pz[q] = ok[q] ? Z[i] : (T)0;
+    }
+    __syncthreads();
+    typedef Ar<T> A;
+    for (int h = 0; h < iters; ++h) {
+        const PlaneHyp<T> p = sh[h];
+        int c = 0;
+#pragma unroll
+        for (int q = 0; q < PT; ++q) {
+            // plane.py:116-118 / :194-196: ((a x + b y) + c z) + k, every product and sum rounded on its own
+            const T s = A::add(A::add(A::add(A::mul(p.a, px[q]), A::mul(p.b, py[q])), A::mul(p.c, pz[q])), p.k);
+            const bool in = ok[q] && (fabs(s) <= p.bound);
+            c += __popc(__ballot_sync(0xffffffffu, in));
+        }
+        if (lane == 0 && c) atomicAdd(&scount[h], c);
+    }
+    __syncthreads();
+    for (int i = tid; i < iters; i += 256)
+        if (scount[i]) atomicAdd(&counts[(size_t)f * iters + i], scount[i]);
+}
+
+// ------------------------------------------------------------------------------------------------
+// best hypothesis (first maximum, plane.py:71 / :128 / :203) + rectification (roi_heads.py:411-428 / :1120-1136)
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) select_kernel(const PlaneHyp<T>* __restrict__ hyps,
+                                                     const int32_t* __restrict__ counts, int iters, int negate,
+                                                     T* __restrict__ out_eq, int32_t* __restrict__ out_best,
+                                                     int32_t* __restrict__ out_count, T* __restrict__ out_normal) {
+    __shared__ int sc[8], si[8];
+    const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    int bc = -1, bi = 0x7fffffff;
+    for (int i = tid; i < iters; i += 256) {
+        const int c = counts[(size_t)f * iters + i];
+        if (c > bc) { bc = c; bi = i; }   // ascending i per thread: keeps the first maximum
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const int c = __shfl_xor_sync(0xffffffffu, bc, o), i = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (c > bc || (c == bc && i < bi)) { bc = c; bi = i; }
+    }
+    if (lane == 0) { sc[wid] = bc; si[wid] = bi; }
+    __syncthreads();
+    if (tid == 0) {
+        for (int w = 1; w < 8; ++w)
+            if (sc[w] > bc || (sc[w] == bc && si[w] < bi)) { bc = sc[w]; bi = si[w]; }
+        const PlaneHyp<T> h = hyps[(size_t)f * iters + bi];
+        if (out_eq) { out_eq[4 * f] = h.a; out_eq[4 * f + 1] = h.b; out_eq[4 * f + 2] = h.c; out_eq[4 * f + 3] = h.k; }
+        if (out_best) out_best[f] = bi;
+        if (out_count) out_count[f] = bc;
+        if (out_normal) {
+            T n0 = h.a, n1 = h.b, n2 = h.c;
+            if (negate) { n0 = -n0; n1 = -n1; n2 = -n2; }   // fit_parallel returns -equation (plane.py:134)
+            if (fabs(n2) > fabs(n1)) { const T t1 = n2, t2 = -n1; n1 = t1; n2 = t2; }              // back wall
+            if (fabs(n0) > fabs(n1)) { const T t0 = -n2, t1 = n0, t2 = n1; n0 = t0; n1 = t1; n2 = t2; }   // side wall
+            if (n1 < (T)0) { n0 = -n0; n1 = -n1; n2 = -n2; }
+            out_normal[3 * f] = n0; out_normal[3 * f + 1] = n1; out_normal[3 * f + 2] = n2;
+        }
+    }
+}
+
+template <typename T>
+__global__ void inlier_mask_kernel(const T* __restrict__ pts, const int32_t* __restrict__ n_pts, int64_t P_cap,
+                                   const PlaneHyp<T>* __restrict__ hyps, const int32_t* __restrict__ best, int iters,
+                                   uint8_t* __restrict__ mask) {
+    const int f = blockIdx.y;
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P_cap) return;
+    uint8_t m = 0;
+    if (i < n_pts[f]) {
+        const PlaneHyp<T> p = hyps[(size_t)f * iters + best[f]];
+        const T* X = pts + (size_t)f * 3 * P_cap;
+        typedef Ar<T> A;
+        const T s = A::add(A::add(A::add(A::mul(p.a, X[i]), A::mul(p.b, X[P_cap + i])), A::mul(p.c, X[2 * P_cap + i])), p.k);
+        m = fabs(s) <= p.bound;
+    }
+    mask[(size_t)f * P_cap + i] = m;
+}
+
+template <typename T>
+int ransac_impl(const T* pts, const int32_t* n_pts, int F, int64_t P_cap, const int32_t* ids, uint64_t seed,
+                int iters, double thresh, T* out_eq, int32_t* out_best, int32_t* out_count, T* out_normal,
+                uint8_t* out_mask, void* ws, int64_t ws_bytes, cudaStream_t st, int negate) {
+    const size_t hyp_bytes = ((size_t)F * iters * sizeof(PlaneHyp<T>) + 255) & ~size_t(255);
+    const size_t need = hyp_bytes + (size_t)F * iters * 4 + (size_t)F * 4;
+    if ((size_t)ws_bytes < need) return tdod_fail(TDOD_EINVAL, "tdod_ransac_plane: workspace too small");
+    PlaneHyp<T>* hyps = reinterpret_cast<PlaneHyp<T>*>(ws);
+    int32_t* counts = reinterpret_cast<int32_t*>((char*)ws + hyp_bytes);
+    int32_t* best_tmp = counts + (size_t)F * iters;
+    if (!out_best) out_best = best_tmp;
+    hypotheses_kernel<T><<<dim3((iters + 127) / 128, F), 128, 0, st>>>(pts, n_pts, P_cap, ids, seed, iters, (T)thresh,
+                                                                      hyps, counts);
+    TDOD_CHECK_LAUNCH();
+    constexpr int PT = 4;
+    const size_t smem = (size_t)iters * (sizeof(PlaneHyp<T>) + sizeof(int));
+    if (smem > 200 * 1024) return tdod_fail(TDOD_ERANGE, "tdod_ransac_plane: too many iterations for shared memory");
+    cudaError_t e = cudaFuncSetAttribute(count_kernel<T, PT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    const unsigned tiles = (unsigned)((P_cap + 256 * PT - 1) / (256 * PT));
+    count_kernel<T, PT><<<dim3(tiles, F), 256, smem, st>>>(pts, n_pts, P_cap, hyps, iters, counts);
+    TDOD_CHECK_LAUNCH();
+    select_kernel<T><<<F, 256, 0, st>>>(hyps, counts, iters, negate, out_eq, out_best, out_count, out_normal);
+    TDOD_CHECK_LAUNCH();
+    if (out_mask) {
+        inlier_mask_kernel<T><<<dim3((unsigned)((P_cap + 255) / 256), F), 256, 0, st>>>(pts, n_pts, P_cap, hyps, out_best,
+                                                                                         iters, out_mask);
+        TDOD_CHECK_LAUNCH();
+    }
+    return TDOD_OK;
+}
+
+}  // namespace
+
+extern "C" int tdod_backproject(const float* depth, const uint8_t* ground, const float* K, int F, int H, int W,
+                                int stride, int flavour, void* plane_pts, void* other_pts, int32_t* counts,
+                                void* stream) {
+    if (F == 0) return TDOD_OK;
+    if (!depth || !K || !plane_pts || !counts || F < 0 || H <= 0 || W <= 0 || stride <= 0)
+        return tdod_fail(TDOD_EINVAL, "tdod_backproject: bad argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (flavour == TDOD_BACKPROJECT_NUMPY)
+        backproject_kernel<double, TDOD_BACKPROJECT_NUMPY><<<F, 1024, 0, st>>>(depth, ground, K, H, W, stride,
+                                                                                (double*)plane_pts, (double*)other_pts, counts);
+    else if (flavour == TDOD_BACKPROJECT_TORCH)
+        backproject_kernel<float, TDOD_BACKPROJECT_TORCH><<<F, 1024, 0, st>>>(depth, ground, K, H, W, stride,
+                                                                              (float*)plane_pts, (float*)other_pts, counts);
+    else
+        return tdod_fail(TDOD_EINVAL, "tdod_backproject: unknown flavour");
+    TDOD_CHECK_LAUNCH();
+    return TDOD_OK;
+}
+
+extern "C" int64_t tdod_ransac_workspace_bytes(int F, int iters, int pts_f64) {
+    const size_t hb = pts_f64 ? sizeof(PlaneHyp<double>) : sizeof(PlaneHyp<float>);
+    return (int64_t)((((size_t)F * iters * hb + 255) & ~size_t(255)) + (size_t)F * iters * 4 + (size_t)F * 4);
+}
+
+extern "C" int tdod_ransac_plane(const void* pts, int pts_f64, const int32_t* n_pts, int F, int64_t P_cap,
+                                 const int32_t* sample_ids, uint64_t seed, int iters, double thresh, void* out_eq,
+                                 int32_t* out_best_iter, int32_t* out_count, void* out_normal,
+                                 uint8_t* out_inlier_mask, void* workspace, int64_t workspace_bytes, void* stream) {
+    if (F == 0) return TDOD_OK;
+    if (!pts || !n_pts || !workspace || F < 0 || P_cap <= 0 || iters <= 0)
+        return tdod_fail(TDOD_EINVAL, "tdod_ransac_plane: bad argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (pts_f64)
+        return ransac_impl<double>((const double*)pts, n_pts, F, P_cap, sample_ids, seed, iters, thresh, (double*)out_eq,
+                                   out_best_iter, out_count, (double*)out_normal, out_inlier_mask, workspace,
+                                   workspace_bytes, st, /*negate=*/0);
+    return ransac_impl<float>((const float*)pts, n_pts, F, P_cap, sample_ids, seed, iters, thresh, (float*)out_eq,
+                              out_best_iter, out_count, (float*)out_normal, out_inlier_mask, workspace, workspace_bytes,
+                              st, /*negate=*/1);
+}

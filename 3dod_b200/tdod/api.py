@@ -1,0 +1,204 @@
+"""Tensor-level host API over libtdod (batched entry points).  Every function takes CUDA tensors, allocates
+the outputs with torch on the same device, launches on torch's current stream and returns without synchronising."""
+import ctypes as C
+
+import torch
+
+from . import lib as L
+
+f32, f64, i32, i64, u8, i16 = torch.float32, torch.float64, torch.int32, torch.int64, torch.uint8, torch.int16
+
+
+def _as_u8(t):
+    """bool masks are reinterpreted (no copy) as the 1-byte-per-pixel layout the kernels read"""
+    if t is None:
+        return None
+    if t.dtype == torch.bool:
+        return t.view(torch.uint8)
+    return t
+
+
+def cube_corners(cubes):
+    """Cubes.get_all_corners: [..., 15] -> [..., 8, 3]"""
+    flat = cubes.reshape(-1, 15)
+    out = torch.empty((flat.shape[0], 8, 3), dtype=f32, device=cubes.device)
+    L.check(L.lib().tdod_cube_corners(L.ptr(flat, f32, "cubes"), flat.shape[0], L.ptr(out), L.stream_ptr()))
+    return out.reshape(cubes.shape[:-1] + (8, 3))
+
+
+def project_cubes(cubes, K, W, H, corners=True, boxes=True):
+    """Cubes.get_bube_corners + cubes_to_box: [..., 15] -> ([..., 8, 2] | None, [..., 4] | None)"""
+    flat = cubes.reshape(-1, 15)
+    M = flat.shape[0]
+    c2d = torch.empty((M, 8, 2), dtype=f32, device=cubes.device) if corners else None
+    bx = torch.empty((M, 4), dtype=f32, device=cubes.device) if boxes else None
+    Kc = K.reshape(9).contiguous()
+    L.check(L.lib().tdod_project_cubes(L.ptr(flat, f32, "cubes"), M, L.ptr(Kc, f32, "K"), int(W), int(H),
+                                       L.ptr(c2d), L.ptr(bx), L.stream_ptr()))
+    lead = cubes.shape[:-1]
+    return (c2d.reshape(lead + (8, 2)) if corners else None, bx.reshape(lead + (4,)) if boxes else None)
+
+
+def score_iou(ref_box, boxes):
+    n = boxes.shape[0]
+    out = torch.empty(n, dtype=f32, device=boxes.device)
+    L.check(L.lib().tdod_score_iou(L.ptr(ref_box.reshape(4), f32, "ref_box"), L.ptr(boxes, f32, "boxes"), n,
+                                   L.ptr(out), L.stream_ptr()))
+    return out
+
+
+def score_dimensions(prior_mean, prior_std, dims, ref_box, boxes):
+    n = boxes.shape[0]
+    out = torch.empty(n, dtype=f32, device=boxes.device)
+    if dims.dim() != 2 or dims.shape[1] != 3 or dims.stride(1) != 1:
+        raise ValueError("dims must be [n,3] with unit inner stride")
+    if not dims.is_cuda or dims.dtype != f32:
+        raise ValueError("dims must be a CUDA fp32 tensor")
+    L.check(L.lib().tdod_score_dimensions(L.ptr(prior_mean, f32, "prior_mean"), L.ptr(prior_std, f32, "prior_std"),
+                                          dims.data_ptr(), dims.stride(0), L.ptr(ref_box.reshape(4), f32, "ref_box"),
+                                          L.ptr(boxes, f32, "boxes"), n, L.ptr(out), L.stream_ptr()))
+    return out
+
+
+def score_corners(rect, corners2d):
+    """rect: [4,2] CUDA fp32 or None (fallback rectangle of scorefunction.py:69-75)"""
+    n = corners2d.shape[0]
+    out = torch.empty(n, dtype=f32, device=corners2d.device)
+    L.check(L.lib().tdod_score_corners(L.ptr(rect, f32, "rect"), 0 if rect is None else 1,
+                                       L.ptr(corners2d, f32, "corners2d"), n, L.ptr(out), L.stream_ptr()))
+    return out
+
+
+def mask_rect(masks):
+    """masks [n,H,W] bool/uint8 -> (rects [n,4,2] fp32, has_rect [n] uint8)"""
+    m = _as_u8(masks)
+    n, H, W = m.shape
+    rects = torch.empty((n, 4, 2), dtype=f32, device=m.device)
+    has = torch.empty(n, dtype=u8, device=m.device)
+    wsb = L.lib().tdod_mask_rect_workspace_bytes(n, H, W)
+    ws = torch.empty(max(int(wsb), 16), dtype=u8, device=m.device)
+    L.check(L.lib().tdod_mask_rect(L.ptr(m, u8, "masks"), n, H, W, L.ptr(rects), L.ptr(has), L.ptr(ws), wsb,
+                                   L.stream_ptr()))
+    return rects, has
+
+
+def score_segmentation(mask, corners2d, power5=False):
+    m = _as_u8(mask)
+    H, W = m.shape
+    n = corners2d.shape[0]
+    out = torch.empty(n, dtype=f32, device=corners2d.device)
+    L.check(L.lib().tdod_score_segmentation(L.ptr(m, u8, "mask"), H, W, L.ptr(corners2d, f32, "corners2d"), n,
+                                            1 if power5 else 0, L.ptr(out), L.stream_ptr()))
+    return out
+
+
+def score_point_cloud(points, cubes):
+    if points.dtype not in (f32, f64):
+        raise ValueError("points must be fp32 or fp64")
+    n = cubes.shape[0]
+    out = torch.empty(n, dtype=i64, device=cubes.device)
+    L.check(L.lib().tdod_score_point_cloud(L.ptr(points, None, "points"), 1 if points.dtype == f64 else 0,
+                                           points.shape[0], L.ptr(cubes, f32, "cubes"), n, L.ptr(out), L.stream_ptr()))
+    return out
+
+
+def yaw_table(normals):
+    """normals [F,3] fp32/fp64 -> [F,36,3,3] fp32"""
+    F = normals.shape[0]
+    out = torch.empty((F, 36, 3, 3), dtype=f32, device=normals.device)
+    L.check(L.lib().tdod_yaw_table(L.ptr(normals, None, "normals"), 1 if normals.dtype == f64 else 0, F, L.ptr(out),
+                                   L.stream_ptr()))
+    return out
+
+
+def backproject(depth, ground, K, stride=5, flavour=L.BACKPROJECT_NUMPY, want_other=True):
+    """depth [F,H,W] fp32, ground [F,H,W] bool/u8 or None, K [F,3,3] ->
+    (plane_pts [F,3,P], other_pts [F,3,P] | None, counts [F,2] int32); fp64 for the NumPy flavour."""
+    F, H, W = depth.shape
+    P = ((H + stride - 1) // stride) * ((W + stride - 1) // stride)
+    dt = f64 if flavour == L.BACKPROJECT_NUMPY else f32
+    pts = torch.empty((F, 3, P), dtype=dt, device=depth.device)
+    other = torch.empty((F, 3, P), dtype=dt, device=depth.device) if (want_other and ground is not None) else None
+    counts = torch.empty((F, 2), dtype=i32, device=depth.device)
+    g = _as_u8(ground)
+    L.check(L.lib().tdod_backproject(L.ptr(depth, f32, "depth"), L.ptr(g, u8, "ground"),
+                                     L.ptr(K.reshape(F, 9).contiguous(), f32, "K"), F, H, W, stride, flavour,
+                                     L.ptr(pts), L.ptr(other), L.ptr(counts), L.stream_ptr()))
+    return pts, other, counts
+
+
+def ransac_plane(pts, n_pts, sample_ids=None, seed=0, iters=1000, thresh=0.05, want_mask=False):
+    """pts [F,3,P] fp32/fp64 SoA, n_pts [F] int32, sample_ids [F,iters,3] int32 or None (Philox).
+    Returns dict(eq [F,4], best_iter [F], count [F], normal [F,3], mask [F,P] | None)."""
+    F, _, P = pts.shape
+    is64 = pts.dtype == f64
+    dev = pts.device
+    eq = torch.empty((F, 4), dtype=pts.dtype, device=dev)
+    normal = torch.empty((F, 3), dtype=pts.dtype, device=dev)
+    best = torch.empty(F, dtype=i32, device=dev)
+    cnt = torch.empty(F, dtype=i32, device=dev)
+    mask = torch.empty((F, P), dtype=u8, device=dev) if want_mask else None
+    wsb = L.lib().tdod_ransac_workspace_bytes(F, iters, 1 if is64 else 0)
+    ws = torch.empty(int(wsb), dtype=u8, device=dev)
+    L.check(L.lib().tdod_ransac_plane(L.ptr(pts, None, "pts"), 1 if is64 else 0, L.ptr(n_pts, i32, "n_pts"), F, P,
+                                      L.ptr(sample_ids, i32, "sample_ids"), int(seed), int(iters), float(thresh),
+                                      L.ptr(eq), L.ptr(best), L.ptr(cnt), L.ptr(normal), L.ptr(mask), L.ptr(ws), wsb,
+                                      L.stream_ptr()))
+    return dict(eq=eq, best_iter=best, count=cnt, normal=normal, mask=mask)
+
+
+class PssOutputs:
+    __slots__ = ("best_idx", "best_score", "best_cube", "best_box", "all_cubes", "all_boxes", "all_scores", "stats")
+
+
+def propose_score_select(depth, K, boxes, prior_mean, prior_std, obj_frame, rects, has_rect, n_prop, yaw_tab=None,
+                         iou_boxes=None, noise=None, yaw_idx=None, rot=None, seed=None, obj_id_base=0,
+                         return_all=False, cluster_size=0, out=None):
+    """The fused hot path (csrc/fused.cu).  depth [F,H,W], K [F,3,3], boxes [N,4], priors [N,3], obj_frame [N] int32,
+    rects [N,4,2], has_rect [N] uint8 | None, yaw_tab [F,36,3,3] | None.
+    Parity RNG mode: noise [N,6,n] (+ yaw_idx [N,n] int16 | rot [N,n,9]); throughput mode: seed=int (Philox)."""
+    F, H, W = depth.shape
+    N = boxes.shape[0]
+    dev = depth.device
+    o = out if out is not None else PssOutputs()
+    if out is None:
+        o.best_idx = torch.empty(N, dtype=i32, device=dev)
+        o.best_score = torch.empty(N, dtype=f32, device=dev)
+        o.best_cube = torch.empty((N, 15), dtype=f32, device=dev)
+        o.best_box = torch.empty((N, 4), dtype=f32, device=dev)
+        o.all_cubes = torch.empty((N, n_prop, 15), dtype=f32, device=dev) if return_all else None
+        o.all_boxes = torch.empty((N, n_prop, 4), dtype=f32, device=dev) if return_all else None
+        o.all_scores = torch.empty((N, 4, n_prop), dtype=f32, device=dev) if return_all else None
+        o.stats = torch.empty((N, 6), dtype=f32, device=dev) if return_all else None
+    a = L.PssArgs()
+    a.depth = L.ptr(depth, f32, "depth")
+    a.K = L.ptr(K.reshape(F, 9), f32, "K")
+    a.yaw_table = L.ptr(yaw_tab, f32, "yaw_tab")
+    a.F, a.H, a.W = F, H, W
+    a.n_obj, a.n_prop = N, int(n_prop)
+    a.obj_frame = L.ptr(obj_frame, i32, "obj_frame")
+    a.boxes = L.ptr(boxes, f32, "boxes")
+    a.iou_boxes = L.ptr(iou_boxes, f32, "iou_boxes")
+    a.prior_mean = L.ptr(prior_mean, f32, "prior_mean")
+    a.prior_std = L.ptr(prior_std, f32, "prior_std")
+    a.rects = L.ptr(rects, f32, "rects")
+    a.has_rect = L.ptr(has_rect, u8, "has_rect")
+    if seed is None:
+        a.rng_mode = L.RNG_HOST
+        if noise is None or tuple(noise.shape) != (N, 6, n_prop):
+            raise ValueError("parity RNG mode needs noise [N,6,n_prop]")
+        a.noise = L.ptr(noise, f32, "noise")
+        a.yaw_idx = L.ptr(yaw_idx, i16, "yaw_idx")
+        a.rot = L.ptr(rot, f32, "rot")
+        a.seed = 0
+    else:
+        a.rng_mode = L.RNG_PHILOX
+        a.seed = int(seed)
+    a.obj_id_base = int(obj_id_base)
+    a.best_idx, a.best_score = L.ptr(o.best_idx), L.ptr(o.best_score)
+    a.best_cube, a.best_box = L.ptr(o.best_cube), L.ptr(o.best_box)
+    a.all_cubes, a.all_boxes = L.ptr(o.all_cubes), L.ptr(o.all_boxes)
+    a.all_scores, a.stats = L.ptr(o.all_scores), L.ptr(o.stats)
+    a.cluster_size = int(cluster_size)
+    L.check(L.lib().tdod_propose_score_select(C.byref(a), L.stream_ptr()))
+    return o

@@ -1,0 +1,155 @@
+/* libtdod -- C ABI of the B200-native (sm_100a) proposal-and-scoring path of luchsonice/3dod.
+ *
+ * The reference has no FFI on this path: it is a Python module API.  Each entry
+ * point below names the reference interface it replaces (file:line under /root/reference); the Python
+ * mirror in 3dod_b200/ProposalNetwork/ binds them with ctypes.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in _host; the caller allocates inputs and
+ *     outputs and keeps them alive until `stream` has drained; the library allocates nothing persistent
+ *   - fp32 row-major contiguous unless stated; masks are 1 byte per pixel (torch bool / uint8)
+ *   - `stream` is a cudaStream_t passed as void*; no entry point synchronises or copies to the host
+ *   - return value: 0 ok; < 0 argument / shape error (checked before any launch, see tdod_strerror);
+ *     > 0 a cudaError_t from the launch
+ *   - re-entrant and stateless: all state is in the arguments
+ */
+#ifndef TDOD_H
+#define TDOD_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TDOD_OK 0
+#define TDOD_EINVAL (-1)   /* null pointer / non-positive size */
+#define TDOD_ERANGE (-2)   /* size outside what the kernels support (see message) */
+
+#define TDOD_RNG_HOST 0    /* parity mode: standard normals + yaw ids drawn by the caller */
+#define TDOD_RNG_PHILOX 1  /* throughput mode: in-kernel Philox4x32-10 */
+
+#define TDOD_BACKPROJECT_NUMPY 0 /* roi_heads.py:346-371: fp64, full-res intrinsics on the strided grid */
+#define TDOD_BACKPROJECT_TORCH 1 /* roi_heads.py:1084-1112: fp32, K // stride, centre of the strided grid */
+
+int tdod_version(void);
+const char* tdod_strerror(int code);
+/* last argument-check message of the calling thread (empty string if none) */
+const char* tdod_last_error_string(void);
+
+/* ---- geometry ------------------------------------------------------------------------------------------ */
+
+/* Cubes.get_all_corners (ProposalNetwork/utils/spaces.py:192-204) ->
+ * cubercnn/util/math_util.py:142-245 get_cuboid_verts_faces.  cubes [M,15] -> out [M,8,3]. */
+int tdod_cube_corners(const float* cubes, int64_t M, float* out_corners3d, void* stream);
+
+/* Cubes.get_bube_corners(K, clamp=(W,H)) (spaces.py:224-245) and cubes_to_box (conversions.py:25-48).
+ * cubes [M,15], K [9]; out_corners2d [M,8,2] and out_boxes [M,4] may each be NULL. */
+int tdod_project_cubes(const float* cubes, int64_t M, const float* K, int clamp_w, int clamp_h,
+                       float* out_corners2d, float* out_boxes, void* stream);
+
+/* ---- scores (ProposalNetwork/scoring/scorefunction.py) ------------------------------------------------ */
+
+/* score_iou (scorefunction.py:47-49 -> utils.py:186-192 -> detectron2 pairwise_iou). */
+int tdod_score_iou(const float* ref_box /*[4]*/, const float* boxes /*[n,4]*/, int64_t n, float* out, void* stream);
+
+/* score_dimensions (scorefunction.py:144-160).  dims has row stride `dims_stride` floats (3 for a packed
+ * [n,3], 15 when pointing at column 3 of a cubes tensor). */
+int tdod_score_dimensions(const float* prior_mean, const float* prior_std, const float* dims, int64_t dims_stride,
+                          const float* ref_box, const float* boxes, int64_t n, float* out, void* stream);
+
+/* first half of score_corners (scorefunction.py:59-68): per mask, the largest external contour's minimum-area
+ * rectangle (cv2.findContours RETR_EXTERNAL -> max contourArea -> minAreaRect -> boxPoints).
+ * masks [n_masks,H,W] 1 B/px; out_rects [n_masks,4,2]; out_has_rect [n_masks] (0 when the mask is empty).
+ * workspace: tdod_mask_rect_workspace_bytes(n_masks,H,W) bytes of device scratch. */
+int64_t tdod_mask_rect_workspace_bytes(int64_t n_masks, int H, int W);
+int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int W, float* out_rects, uint8_t* out_has_rect,
+                   void* workspace, int64_t workspace_bytes, void* stream);
+
+/* second half of score_corners (scorefunction.py:69-85 + modified_chamfer_distance :51-56).
+ * rect [4,2] (ignored when has_rect == 0: the fallback rectangle of :69-75 is computed from the corners). */
+int tdod_score_corners(const float* rect, int has_rect, const float* corners2d /*[n,8,2]*/, int64_t n, float* out,
+                       void* stream);
+
+/* score_segmentation (scorefunction.py:88-106, mask_iou utils.py:230-239) when power5 == 0;
+ * score_mod_segmentation (:108-126, mod_mask_iou utils.py:241-250, int64 inter**5 wrap) when power5 != 0.
+ * mask [H,W] 1 B/px, corners2d [n,8,2]. */
+int tdod_score_segmentation(const uint8_t* mask, int H, int W, const float* corners2d, int64_t n, int power5,
+                            float* out, void* stream);
+
+/* score_point_cloud (scorefunction.py:9-43).  points [P,3] fp32 (points_f64 == 0) or fp64; cubes [n,15];
+ * out int64 [n]. */
+int tdod_score_point_cloud(const void* points, int points_f64, int64_t P, const float* cubes, int64_t n,
+                           int64_t* out, void* stream);
+
+/* ---- plane ---------------------------------------------------------------------------------------------- */
+
+/* Depth -> strided point cloud (roi_heads.py:346-371 / :1084-1112), row-major compaction.
+ * depth [F,H,W]; ground [F,H,W] 1 B/px or NULL; K [F,9].  Outputs per frame f, SoA, capacity
+ * P = ceil(H/stride)*ceil(W/stride): plane_pts [F,3,P] (ground>0 points, or all when ground NULL),
+ * other_pts [F,3,P] or NULL (ground==0 points), counts [F,2] int32.  fp64 when flavour == NUMPY else fp32. */
+int tdod_backproject(const float* depth, const uint8_t* ground, const float* K, int F, int H, int W, int stride,
+                     int flavour, void* plane_pts, void* other_pts, int32_t* counts, void* stream);
+
+/* Plane.fit_parallel (ProposalNetwork/utils/plane.py:79-134; fp32) / Plane_np.fit == pyransac3d.Plane.fit
+ * (plane.py:154-209, roi_heads.py:374-376; fp64), batched over F frames of SoA points [F,3,P_cap].
+ * sample_ids [F,iters,3] int32 (python random.sample stream) or NULL -> Philox ids from `seed`.
+ * Outputs: out_eq [F,4] (same dtype as the points; sign as the NumPy flavour, i.e. NOT negated),
+ * out_best_iter [F], out_count [F], out_normal [F,3] rectified up-vector (roi_heads.py:411-428), fp64/fp32,
+ * out_inlier_mask [F,P_cap] uint8 or NULL.  out_normal is rectified from -eq for fp32 points (fit_parallel
+ * returns the negated equation, plane.py:134) and from +eq for fp64 points (pyransac3d convention).
+ * workspace: tdod_ransac_workspace_bytes(F, iters, pts_f64) bytes of device scratch. */
+int64_t tdod_ransac_workspace_bytes(int F, int iters, int pts_f64);
+int tdod_ransac_plane(const void* pts, int pts_f64, const int32_t* n_pts, int F, int64_t P_cap,
+                      const int32_t* sample_ids, uint64_t seed, int iters, double thresh, void* out_eq,
+                      int32_t* out_best_iter, int32_t* out_count, void* out_normal, uint8_t* out_inlier_mask,
+                      void* workspace, int64_t workspace_bytes, void* stream);
+
+/* orthobasis_from_normal_t over linspace(0, pi, 36) (utils.py:112-146, proposals.py:405-406).
+ * normals [F,3] fp64 (normals_f64) or fp32 -> out_table [F,36,9] fp32 (row-major 3x3, columns x, n, n x x). */
+int tdod_yaw_table(const void* normals, int normals_f64, int F, float* out_table, void* stream);
+
+/* ---- fused propose + project + score + select (the hot kernel) --------------------------------------- */
+
+typedef struct tdod_pss_args {
+    /* frames */
+    const float* depth;        /* [F,H,W] */
+    const float* K;            /* [F,9] */
+    const float* yaw_table;    /* [F,36,9] or NULL -> random rotations (proposals.py:401-402) */
+    int32_t F, H, W;
+    /* objects */
+    int32_t n_obj, n_prop;
+    const int32_t* obj_frame;  /* [n_obj] */
+    const float* boxes;        /* [n_obj,4] xyxy: sampling range + aspect-ratio reference */
+    const float* iou_boxes;    /* [n_obj,4] or NULL (= boxes): IoU reference (roi_heads.py:466 vs :496) */
+    const float* prior_mean;   /* [n_obj,3] (w,h,l) */
+    const float* prior_std;    /* [n_obj,3] */
+    const float* rects;        /* [n_obj,4,2] from tdod_mask_rect */
+    const uint8_t* has_rect;   /* [n_obj] or NULL (all present) */
+    /* randomness */
+    int32_t rng_mode;          /* TDOD_RNG_HOST | TDOD_RNG_PHILOX */
+    const float* noise;        /* HOST mode: [n_obj,6,n_prop] accepted standard normals, order w,h,l,x,y,z */
+    const int16_t* yaw_idx;    /* HOST mode with yaw_table: [n_obj,n_prop] in [0,36) */
+    const float* rot;          /* HOST mode without yaw_table: [n_obj,n_prop,9] */
+    uint64_t seed;             /* PHILOX mode */
+    int64_t obj_id_base;       /* PHILOX mode: global id of object 0 (results independent of sharding) */
+    /* outputs: winners (always) */
+    int32_t* best_idx;         /* [n_obj] */
+    float* best_score;         /* [n_obj] */
+    float* best_cube;          /* [n_obj,15] */
+    float* best_box;           /* [n_obj,4] */
+    /* outputs: everything (each may be NULL) */
+    float* all_cubes;          /* [n_obj,n_prop,15] */
+    float* all_boxes;          /* [n_obj,n_prop,4] */
+    float* all_scores;         /* [n_obj,4,n_prop]: iou, dim, corners, combined */
+    float* stats;              /* [n_obj,6]: mean/std of the x, y, z samplers */
+    int32_t cluster_size;      /* CTAs per object: 0 = auto, else 1,2,4,8 */
+} tdod_pss_args;
+
+/* propose (proposals.py:338-424) + cubes_to_box + score_iou + score_dimensions + score_corners +
+ * combine/argmax (roi_heads.py:493-505) in one launch; one CTA cluster per object. */
+int tdod_propose_score_select(const tdod_pss_args* args_host, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TDOD_H */
