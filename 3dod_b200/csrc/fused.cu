@@ -25,7 +25,7 @@ struct Mail {               // per-CTA mailbox read by every CTA of the cluster 
     int hist[4][3][256];    // radix-select histograms, one buffer per pass (no WAR hazard)
     double sum[3];          // sum of seeds
     double m2[3];           // sum of squared deviations
-    double boxsum[4];       // fallback rectangle: sums of proposal box coordinates
+    float fb[8];            // fallback rectangle: min/max over proposals of vertex 0 and vertex 1 (x, y)
     float maxdiff, maxd;
     int nanflag[3];
     float am_v;
@@ -37,6 +37,7 @@ struct Shared {
     // block-level scratch
     double red_d[kWarps][4];
     float red_f[kWarps][2];
+    float red_fb[kWarps][8];
     int red_i[kWarps];
     uint32_t prefix[3];
     int kth[3];
@@ -189,8 +190,8 @@ __global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a,
     if (tid < 9) sh.K[tid] = a.K[(size_t)c.frame * 9 + tid];
     if (a.yaw_table)
         for (int t = tid; t < TDOD_NYAW * 9; t += kThreads) sh.yaw[t] = a.yaw_table[(size_t)c.frame * TDOD_NYAW * 9 + t];
-    const bool has_rect = a.has_rect ? (a.has_rect[obj] != 0) : true;
-    if (tid < 8) sh.rect[tid] = has_rect ? a.rects[(size_t)obj * 8 + tid] : 0.f;
+    const bool has_rect = a.propose_only ? true : (a.has_rect ? (a.has_rect[obj] != 0) : true);
+    if (tid < 8) sh.rect[tid] = (has_rect && a.rects) ? a.rects[(size_t)obj * 8 + tid] : 0.f;
     for (int t = tid; t < 4 * 3 * 256; t += kThreads) (&sh.mail.hist[0][0][0])[t] = 0;
     if (tid < 3) { sh.prefix[tid] = 0u; sh.kth[tid] = (n - 1) / 2; sh.mail.nanflag[tid] = 0; }
     __syncthreads();
@@ -333,9 +334,12 @@ __global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a,
     const float ib0 = ib[0], ib1 = ib[1], ib2 = ib[2], ib3 = ib[3];
     const float r_ref = __fdiv_rn(__fsub_rn(c.bx1, c.bx0), __fsub_rn(c.by1, c.by0));   // scorefunction.py:154
 
-    for (int sweep = has_rect ? 1 : 0; sweep < 2; ++sweep) {
-        // sweep 0 (only without a mask rectangle): proposal boxes -> fallback rectangle (scorefunction.py:69-75)
-        double bsum[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int sweep = (has_rect || a.propose_only) ? 1 : 0; sweep < 2; ++sweep) {
+        // sweep 0 (only without a mask rectangle): fallback rectangle of scorefunction.py:69-75.  With the callers'
+        // [1,n,8,2] corners, `bube_corners[:,:,0].min(1)[0].mean()` is the mean of (min over PROPOSALS of vertex 0's x,
+        // min over proposals of vertex 0's y); the 'y' values use vertex 1 the same way.
+        float fmn[4] = {CUDART_INF_F, CUDART_INF_F, CUDART_INF_F, CUDART_INF_F};      // v0x v0y v1x v1y
+        float fmx[4] = {-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F};
         float lmaxdiff = -CUDART_INF_F, lmaxd = -CUDART_INF_F;
         for (int j = tid; j < cnt; j += kThreads) {
             const int i = i0 + j;
@@ -352,9 +356,14 @@ __global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a,
                 y0 = min_nan(y0, V[k]); y1 = max_nan(y1, V[k]);
             }
             if (sweep == 0) {
-                bsum[0] += (double)x0; bsum[1] += (double)y0; bsum[2] += (double)x1; bsum[3] += (double)y1;
+                fmn[0] = min_nan(fmn[0], U[0]); fmn[1] = min_nan(fmn[1], V[0]);
+                fmn[2] = min_nan(fmn[2], U[1]); fmn[3] = min_nan(fmn[3], V[1]);
+                fmx[0] = max_nan(fmx[0], U[0]); fmx[1] = max_nan(fmx[1], V[0]);
+                fmx[2] = max_nan(fmx[2], U[1]); fmx[3] = max_nan(fmx[3], V[1]);
                 continue;
             }
+            if (a.propose_only) goto emit;   // uniform over the grid: proposals.propose / cubes_to_box only
+            {
             const float iou = iou_xyxy(ib0, ib1, ib2, ib3, x0, y0, x1, y1);
             const float g = dims_gauss(q[3], q[4], q[5], c.mu, c.sg);
             const float ratio = __fdiv_rn(__fsub_rn(x1, x0), __fsub_rn(y1, y0));
@@ -363,6 +372,8 @@ __global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a,
             s_x[j] = iou; s_y[j] = g; s_z[j] = diff; s_d[j] = d;
             lmaxdiff = (lmaxdiff != lmaxdiff || diff != diff) ? CUDART_NAN_F : fmaxf(lmaxdiff, diff);
             lmaxd = (lmaxd != lmaxd || d != d) ? CUDART_NAN_F : fmaxf(lmaxd, d);
+            }
+        emit:
             if (a.all_cubes) {
                 float* oc = a.all_cubes + ((size_t)obj * n + i) * 15;
 #pragma unroll
@@ -375,25 +386,39 @@ __global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a,
         }
         if (sweep == 0) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) bsum[k] = warp_sum_d(bsum[k]);
-            if (lane == 0) { for (int k = 0; k < 4; ++k) sh.red_d[wid][k] = bsum[k]; }
+            for (int k = 0; k < 4; ++k) {
+                fmn[k] = -warp_max_nan(-fmn[k]);
+                fmx[k] = warp_max_nan(fmx[k]);
+            }
+            if (lane == 0) {
+                for (int k = 0; k < 4; ++k) { sh.red_fb[wid][k] = fmn[k]; sh.red_fb[wid][4 + k] = fmx[k]; }
+            }
             __syncthreads();
-            if (tid < 4) {
-                double s = 0.0;
-                for (int w2 = 0; w2 < kWarps; ++w2) s += sh.red_d[w2][tid];
-                sh.mail.boxsum[tid] = s;
+            if (tid < 8) {
+                const int k = tid & 3;
+                float m = (tid < 4) ? CUDART_INF_F : -CUDART_INF_F;
+                for (int w2 = 0; w2 < kWarps; ++w2)
+                    m = (tid < 4) ? min_nan(m, sh.red_fb[w2][k]) : max_nan(m, sh.red_fb[w2][4 + k]);
+                // layout: fb[0..1] = min v0 (x,y), fb[2..3] = max v0, fb[4..5] = min v1, fb[6..7] = max v1
+                const int slot = (k < 2) ? ((tid < 4) ? k : 2 + k) : ((tid < 4) ? 4 + (k - 2) : 6 + (k - 2));
+                sh.mail.fb[slot] = m;
             }
             cl.sync();   // (5b)
             if (tid == 0) {
-                double t4[4];
-                for (int k = 0; k < 4; ++k) {
-                    double s = 0.0;
-                    for (int r = 0; r < S; ++r) s += *remote(cl, &sh.mail.boxsum[k], r);
-                    t4[k] = (double)(float)(s / (double)n);   // torch .mean() of fp32 -> fp32
+                float t8[8];
+                for (int k = 0; k < 8; ++k) {
+                    float m = (k & 2) ? -CUDART_INF_F : CUDART_INF_F;
+                    for (int r = 0; r < S; ++r) {
+                        const float v = *remote(cl, &sh.mail.fb[k], r);
+                        m = (k & 2) ? max_nan(m, v) : min_nan(m, v);
+                    }
+                    t8[k] = m;
                 }
+                const float fx0 = __fdiv_rn(__fadd_rn(t8[0], t8[1]), 2.f), fx1 = __fdiv_rn(__fadd_rn(t8[2], t8[3]), 2.f);
+                const float fy0 = __fdiv_rn(__fadd_rn(t8[4], t8[5]), 2.f), fy1 = __fdiv_rn(__fadd_rn(t8[6], t8[7]), 2.f);
                 // [[x0,y0],[x1,y0],[x1,y1],[x0,y1]]
-                sh.rect[0] = (float)t4[0]; sh.rect[1] = (float)t4[1]; sh.rect[2] = (float)t4[2]; sh.rect[3] = (float)t4[1];
-                sh.rect[4] = (float)t4[2]; sh.rect[5] = (float)t4[3]; sh.rect[6] = (float)t4[0]; sh.rect[7] = (float)t4[3];
+                sh.rect[0] = fx0; sh.rect[1] = fy0; sh.rect[2] = fx1; sh.rect[3] = fy0;
+                sh.rect[4] = fx1; sh.rect[5] = fy1; sh.rect[6] = fx0; sh.rect[7] = fy1;
             }
             __syncthreads();
             continue;
@@ -412,6 +437,7 @@ __global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a,
         }
     }
     cl.sync();   // (6)
+    if (a.propose_only) return;
     float maxdiff = -CUDART_INF_F, maxd = -CUDART_INF_F;
     for (int r = 0; r < S; ++r) {
         const float v0 = *remote(cl, &sh.mail.maxdiff, r), v1 = *remote(cl, &sh.mail.maxd, r);
@@ -480,10 +506,15 @@ extern "C" int tdod_propose_score_select(const tdod_pss_args* ap, void* stream) 
     const tdod_pss_args& a = *ap;
     if (a.n_obj == 0) return TDOD_OK;
     if (a.n_obj < 0 || a.n_prop < 2) return tdod_fail(TDOD_EINVAL, "n_obj must be >= 0 and n_prop >= 2");
-    if (!a.depth || !a.K || !a.boxes || !a.prior_mean || !a.prior_std || !a.best_idx || !a.best_score ||
-        !a.best_cube || !a.best_box)
+    if (!a.depth || !a.K || !a.boxes || !a.prior_mean || !a.prior_std)
         return tdod_fail(TDOD_EINVAL, "a required pointer is NULL");
-    if (!a.rects && !a.has_rect) return tdod_fail(TDOD_EINVAL, "rects is NULL and has_rect does not say so");
+    if (a.propose_only) {
+        if (!a.all_cubes && !a.all_boxes) return tdod_fail(TDOD_EINVAL, "propose_only needs all_cubes or all_boxes");
+    } else {
+        if (!a.best_idx || !a.best_score || !a.best_cube || !a.best_box)
+            return tdod_fail(TDOD_EINVAL, "a winner output pointer is NULL");
+        if (!a.rects && !a.has_rect) return tdod_fail(TDOD_EINVAL, "rects is NULL and has_rect does not say so");
+    }
     if (a.H <= 0 || a.W <= 0 || a.F <= 0) return tdod_fail(TDOD_EINVAL, "bad frame shape");
     if (a.rng_mode == TDOD_RNG_HOST) {
         if (!a.noise) return tdod_fail(TDOD_EINVAL, "rng_mode HOST needs noise");

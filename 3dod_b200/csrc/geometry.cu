@@ -96,36 +96,38 @@ __global__ void __launch_bounds__(1024) corners_kernel(const float* __restrict__
                                                        const float* __restrict__ c2d, int64_t n,
                                                        float* __restrict__ out) {
     __shared__ float red[32];
-    __shared__ double redd[32][4];
+    __shared__ float redf[32][8];
     __shared__ float rect[8];
     if (has_rect) {
         if (threadIdx.x < 8) rect[threadIdx.x] = rect_in[threadIdx.x];
     } else {
-        // scorefunction.py:69-75: mean over proposals of the per-proposal corner extents
-        double s[4] = {0, 0, 0, 0};
+        // scorefunction.py:69-75 as the callers' [1,n,8,2] corners make it behave: x0/x1 = mean of (min / max over
+        // PROPOSALS of vertex 0's x, of vertex 0's y); y0/y1 likewise from vertex 1 (see oracle fallback_rect)
+        float mn[4] = {CUDART_INF_F, CUDART_INF_F, CUDART_INF_F, CUDART_INF_F};
+        float mx4[4] = {-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F};
         for (int64_t i = threadIdx.x; i < n; i += blockDim.x) {
-            float x0 = CUDART_INF_F, y0 = CUDART_INF_F, x1 = -CUDART_INF_F, y1 = -CUDART_INF_F;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const float u = c2d[i * 16 + 2 * j], v = c2d[i * 16 + 2 * j + 1];
-                x0 = min_nan(x0, u); x1 = max_nan(x1, u); y0 = min_nan(y0, v); y1 = max_nan(y1, v);
+            for (int k = 0; k < 4; ++k) {
+                const float v = c2d[i * 16 + k];          // v0x, v0y, v1x, v1y
+                mn[k] = min_nan(mn[k], v); mx4[k] = max_nan(mx4[k], v);
             }
-            s[0] += x0; s[1] += y0; s[2] += x1; s[3] += y1;
         }
 #pragma unroll
-        for (int k = 0; k < 4; ++k) s[k] = warp_sum_d(s[k]);
+        for (int k = 0; k < 4; ++k) { mn[k] = -warp_max_nan(-mn[k]); mx4[k] = warp_max_nan(mx4[k]); }
         if ((threadIdx.x & 31) == 0)
-            for (int k = 0; k < 4; ++k) redd[threadIdx.x >> 5][k] = s[k];
+            for (int k = 0; k < 4; ++k) { redf[threadIdx.x >> 5][k] = mn[k]; redf[threadIdx.x >> 5][4 + k] = mx4[k]; }
         __syncthreads();
         if (threadIdx.x == 0) {
-            float t[4];
-            for (int k = 0; k < 4; ++k) {
-                double a = 0;
-                for (int w = 0; w < (int)(blockDim.x >> 5); ++w) a += redd[w][k];
-                t[k] = (float)(a / (double)n);
+            float t[8];
+            for (int k = 0; k < 8; ++k) {
+                float m = (k < 4) ? CUDART_INF_F : -CUDART_INF_F;
+                for (int w = 0; w < (int)(blockDim.x >> 5); ++w) m = (k < 4) ? min_nan(m, redf[w][k]) : max_nan(m, redf[w][k]);
+                t[k] = m;
             }
-            rect[0] = t[0]; rect[1] = t[1]; rect[2] = t[2]; rect[3] = t[1];
-            rect[4] = t[2]; rect[5] = t[3]; rect[6] = t[0]; rect[7] = t[3];
+            const float x0 = __fdiv_rn(__fadd_rn(t[0], t[1]), 2.f), x1 = __fdiv_rn(__fadd_rn(t[4], t[5]), 2.f);
+            const float y0 = __fdiv_rn(__fadd_rn(t[2], t[3]), 2.f), y1 = __fdiv_rn(__fadd_rn(t[6], t[7]), 2.f);
+            rect[0] = x0; rect[1] = y0; rect[2] = x1; rect[3] = y0;
+            rect[4] = x1; rect[5] = y1; rect[6] = x0; rect[7] = y1;
         }
     }
     __syncthreads();
@@ -143,12 +145,33 @@ __global__ void __launch_bounds__(1024) corners_kernel(const float* __restrict__
 }
 
 // ProposalNetwork/utils/utils.py:112-146 in the dtype of the normal (fp64 when it comes from the NumPy plane
-// fit); the yaw angles and their cos/sin are fp32 (torch.linspace(0, pi, 36) is fp32) and are promoted.
-__constant__ uint32_t kYawAngleBits[TDOD_NYAW] = {
-    0x00000000, 0x3db7d3fb, 0x3e37d3fb, 0x3e89defc, 0x3eb7d3fb, 0x3ee5c8fa, 0x3f09defc, 0x3f20d97c, 0x3f37d3fb,
-    0x3f4ece7a, 0x3f65c8fa, 0x3f7cc379, 0x3f89defc, 0x3f955c3c, 0x3fa0d97c, 0x3fac56bb, 0x3fb7d3fb, 0x3fc3513b,
-    0x3fcece7b, 0x3fda4bbb, 0x3fe5c8fb, 0x3ff1463a, 0x3ffcc37a, 0x4004205d, 0x4009defd, 0x400f9d9d, 0x40155c3c,
-    0x401b1adc, 0x4020d97c, 0x4026981c, 0x402c56bc, 0x4032155c, 0x4037d3fb, 0x403d929b, 0x4043513b, 0x40490fdb};
+// fit); the yaw angles torch.linspace(0, pi, 36) and their cos/sin are fp32 and are promoted.
+// cos / sin / (1 - cos) of the 36 angles as torch-CPU 2.11 evaluates them in fp32 (utils.py:138-139): the reference's
+// yaw table is built on the host, so its trigonometry is the CPU's, not libdevice's; pinning the 36 values makes
+// the table bit-comparable with the reference.
+__constant__ uint32_t kYawCosBits[TDOD_NYAW] = {
+    0x3f800000, 0x3f7ef82c, 0x3f7be2cf, 0x3f76c645, 0x3f6fad17, 0x3f66a5e5, 0x3f5bc34d, 0x3f4f1bbd, 0x3f40c94b,
+    0x3f30e97c, 0x3f1f9d07, 0x3f0d0796, 0x3ef29eeb, 0x3ec93a94, 0x3e9e3779, 0x3e63dc8a, 0x3e097473, 0x3d37c428,
+    0xbd37c440, 0xbe097479, 0xbe63dc90, 0xbe9e377b, 0xbec93a97, 0xbef29eee, 0xbf0d0798, 0xbf1f9d0a, 0xbf30e97b,
+    0xbf40c94b, 0xbf4f1bbd, 0xbf5bc34e, 0xbf66a5e6, 0xbf6fad18, 0xbf76c645, 0xbf7be2cf, 0xbf7ef82c, 0xbf800000};
+__constant__ uint32_t kYawSinBits[TDOD_NYAW] = {
+    0x00000000, 0x3db794d0, 0x3e36d79e, 0x3e8835fb, 0x3eb3e767, 0x3ede2603, 0x3f034d5e, 0x3f167918, 0x3f286eac,
+    0x3f390915, 0x3f48261c, 0x3f55a698, 0x3f616eb5, 0x3f6b662c, 0x3f737871, 0x3f7994e0, 0x3f7daee2, 0x3f7fbe02,
+    0x3f7fbe02, 0x3f7daee2, 0x3f7994e0, 0x3f737870, 0x3f6b662c, 0x3f616eb4, 0x3f55a696, 0x3f48261a, 0x3f390916,
+    0x3f286eac, 0x3f167917, 0x3f034d5c, 0x3ede25fe, 0x3eb3e761, 0x3e8835fc, 0x3e36d79d, 0x3db794ca, 0xb3bbbd2e};
+__constant__ uint32_t kYawOmcBits[TDOD_NYAW] = {
+    0x00000000, 0x3b83ea00, 0x3c83a620, 0x3d139bb0, 0x3d829748, 0x3dcad0d8, 0x3e10f2cc, 0x3e43910c, 0x3e7cdad4,
+    0x3e9e2d08, 0x3ec0c5f2, 0x3ee5f0d4, 0x3f06b08a, 0x3f1b62b6, 0x3f30e444, 0x3f4708de, 0x3f5da2e3, 0x3f7483be,
+    0x3f85be22, 0x3f912e8f, 0x3f9c7b92, 0x3fa78ddf, 0x3fb24ea6, 0x3fbca7bc, 0x3fc683cc, 0x3fcfce85, 0x3fd874be,
+    0x3fe064a6, 0x3fe78dde, 0x3fede1a7, 0x3ff352f3, 0x3ff7d68c, 0x3ffb6322, 0x3ffdf168, 0x3fff7c16, 0x40000000};
+
+// separately rounded products / sums (each is its own torch op in utils.py:134-146)
+__device__ __forceinline__ float mulr(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double mulr(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float addr(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ double addr(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ float subr(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ double subr(double a, double b) { return __dsub_rn(a, b); }
 
 template <typename T>
 __global__ void yaw_table_kernel(const T* __restrict__ normals, int F, float* __restrict__ out) {
@@ -160,21 +183,21 @@ __global__ void yaw_table_kernel(const T* __restrict__ normals, int F, float* __
         v0 = 0; v1 = c; v2 = -b;
     } else {
         // normalize_vector: the magnitude passes through an fp32 tensor (torch.max with tensor([1e-8]))
-        const T mag = sqrt(b * b + a * a);
+        const T mag = sqrt(addr(mulr(b, b), mulr(a, a)));
         const float magf = fmaxf((float)mag, 1e-8f);
         v0 = b / (T)magf; v1 = -a / (T)magf; v2 = 0;
     }
-    // torch.linspace(0, pi, 36) fp32 as torch-CPU 2.11 produces it (its vectorised kernel rounds two of the 36
-    // entries differently from start + i*step); the angles are constants, so the bit patterns are pinned here.
-    const float ang = __uint_as_float(kYawAngleBits[t]);
-    const T cs = (T)cosf(ang), sn = (T)sinf(ang);
-    const T omc = (T)(1.0f - cosf(ang));
-    const T k0 = b * v2 - c * v1, k1 = c * v0 - a * v2, k2 = a * v1 - b * v0;   // cross(normal, v)
-    const T kdv = a * v0 + b * v1 + c * v2;
-    const T x0 = v0 * cs + k0 * sn + (a * kdv) * omc;
-    const T x1 = v1 * cs + k1 * sn + (b * kdv) * omc;
-    const T x2 = v2 * cs + k2 * sn + (c * kdv) * omc;
-    const T y0 = b * x2 - c * x1, y1 = c * x0 - a * x2, y2 = a * x1 - b * x0;   // cross(normal, x)
+    const T cs = (T)__uint_as_float(kYawCosBits[t]), sn = (T)__uint_as_float(kYawSinBits[t]);
+    const T omc = (T)__uint_as_float(kYawOmcBits[t]);
+    // cross(normal, v), normal . v
+    const T k0 = subr(mulr(b, v2), mulr(c, v1)), k1 = subr(mulr(c, v0), mulr(a, v2)), k2 = subr(mulr(a, v1), mulr(b, v0));
+    const T kdv = addr(addr(mulr(a, v0), mulr(b, v1)), mulr(c, v2));
+    // Rodrigues (utils.py:141-146): (v cos + (k x v) sin) + k (k.v) (1 - cos)
+    const T x0 = addr(addr(mulr(v0, cs), mulr(k0, sn)), mulr(mulr(a, kdv), omc));
+    const T x1 = addr(addr(mulr(v1, cs), mulr(k1, sn)), mulr(mulr(b, kdv), omc));
+    const T x2 = addr(addr(mulr(v2, cs), mulr(k2, sn)), mulr(mulr(c, kdv), omc));
+    // cross(normal, x)
+    const T y0 = subr(mulr(b, x2), mulr(c, x1)), y1 = subr(mulr(c, x0), mulr(a, x2)), y2 = subr(mulr(a, x1), mulr(b, x0));
     float* o = out + ((size_t)f * TDOD_NYAW + t) * 9;   // rows of [x | n | y] columns
     o[0] = (float)x0; o[1] = (float)a; o[2] = (float)y0;
     o[3] = (float)x1; o[4] = (float)b; o[5] = (float)y1;

@@ -108,8 +108,8 @@ struct PlaneHyp {
 
 template <typename T>
 __global__ void hypotheses_kernel(const T* __restrict__ pts, const int32_t* __restrict__ n_pts, int64_t P_cap,
-                                  const int32_t* __restrict__ ids, uint64_t seed, int iters, T thresh,
-                                  PlaneHyp<T>* __restrict__ hyps, int32_t* __restrict__ counts) {
+                                  const int32_t* __restrict__ ids, uint64_t seed, int64_t frame_id_base, int iters,
+                                  T thresh, PlaneHyp<T>* __restrict__ hyps, int32_t* __restrict__ counts) {
     const int f = blockIdx.y;
     const int it = blockIdx.x * blockDim.x + threadIdx.x;
     if (it >= iters) return;
@@ -127,7 +127,8 @@ __global__ void hypotheses_kernel(const T* __restrict__ pts, const int32_t* __re
         i0 = s[0]; i1 = s[1]; i2 = s[2];
     } else {   // three distinct uniform indices
         const Philox ph(seed);
-        const uint4 r = ph((uint32_t)it, (uint32_t)f, 0x52414Eu, 0u);
+        const uint64_t gf = (uint64_t)(frame_id_base + f);   // global frame id: results do not depend on batching
+        const uint4 r = ph((uint32_t)it, (uint32_t)gf, (uint32_t)(gf >> 32) ^ 0x52414Eu, 0u);
         i0 = (int)(r.x % (uint32_t)P);
         i1 = (int)(r.y % (uint32_t)(P - 1)); if (i1 >= i0) ++i1;
         i2 = (int)(r.z % (uint32_t)(P - 2));
@@ -267,7 +268,7 @@ __global__ void inlier_mask_kernel(const T* __restrict__ pts, const int32_t* __r
 
 template <typename T>
 int ransac_impl(const T* pts, const int32_t* n_pts, int F, int64_t P_cap, const int32_t* ids, uint64_t seed,
-                int iters, double thresh, T* out_eq, int32_t* out_best, int32_t* out_count, T* out_normal,
+                int64_t frame_id_base, int iters, double thresh, T* out_eq, int32_t* out_best, int32_t* out_count, T* out_normal,
                 uint8_t* out_mask, void* ws, int64_t ws_bytes, cudaStream_t st, int negate) {
     const size_t hyp_bytes = ((size_t)F * iters * sizeof(PlaneHyp<T>) + 255) & ~size_t(255);
     const size_t need = hyp_bytes + (size_t)F * iters * 4 + (size_t)F * 4;
@@ -276,8 +277,8 @@ int ransac_impl(const T* pts, const int32_t* n_pts, int F, int64_t P_cap, const 
     int32_t* counts = reinterpret_cast<int32_t*>((char*)ws + hyp_bytes);
     int32_t* best_tmp = counts + (size_t)F * iters;
     if (!out_best) out_best = best_tmp;
-    hypotheses_kernel<T><<<dim3((iters + 127) / 128, F), 128, 0, st>>>(pts, n_pts, P_cap, ids, seed, iters, (T)thresh,
-                                                                      hyps, counts);
+    hypotheses_kernel<T><<<dim3((iters + 127) / 128, F), 128, 0, st>>>(pts, n_pts, P_cap, ids, seed, frame_id_base, iters,
+                                                                      (T)thresh, hyps, counts);
     TDOD_CHECK_LAUNCH();
     constexpr int PT = 4;
     const size_t smem = (size_t)iters * (sizeof(PlaneHyp<T>) + sizeof(int));
@@ -324,18 +325,18 @@ extern "C" int64_t tdod_ransac_workspace_bytes(int F, int iters, int pts_f64) {
 }
 
 extern "C" int tdod_ransac_plane(const void* pts, int pts_f64, const int32_t* n_pts, int F, int64_t P_cap,
-                                 const int32_t* sample_ids, uint64_t seed, int iters, double thresh, void* out_eq,
-                                 int32_t* out_best_iter, int32_t* out_count, void* out_normal,
+                                 const int32_t* sample_ids, uint64_t seed, int64_t frame_id_base, int iters, double thresh,
+                                 void* out_eq, int32_t* out_best_iter, int32_t* out_count, void* out_normal,
                                  uint8_t* out_inlier_mask, void* workspace, int64_t workspace_bytes, void* stream) {
     if (F == 0) return TDOD_OK;
     if (!pts || !n_pts || !workspace || F < 0 || P_cap <= 0 || iters <= 0)
         return tdod_fail(TDOD_EINVAL, "tdod_ransac_plane: bad argument");
     cudaStream_t st = (cudaStream_t)stream;
     if (pts_f64)
-        return ransac_impl<double>((const double*)pts, n_pts, F, P_cap, sample_ids, seed, iters, thresh, (double*)out_eq,
+        return ransac_impl<double>((const double*)pts, n_pts, F, P_cap, sample_ids, seed, frame_id_base, iters, thresh, (double*)out_eq,
                                    out_best_iter, out_count, (double*)out_normal, out_inlier_mask, workspace,
                                    workspace_bytes, st, /*negate=*/0);
-    return ransac_impl<float>((const float*)pts, n_pts, F, P_cap, sample_ids, seed, iters, thresh, (float*)out_eq,
+    return ransac_impl<float>((const float*)pts, n_pts, F, P_cap, sample_ids, seed, frame_id_base, iters, thresh, (float*)out_eq,
                               out_best_iter, out_count, (float*)out_normal, out_inlier_mask, workspace, workspace_bytes,
                               st, /*negate=*/1);
 }

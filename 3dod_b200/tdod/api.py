@@ -127,7 +127,7 @@ def backproject(depth, ground, K, stride=5, flavour=L.BACKPROJECT_NUMPY, want_ot
     return pts, other, counts
 
 
-def ransac_plane(pts, n_pts, sample_ids=None, seed=0, iters=1000, thresh=0.05, want_mask=False):
+def ransac_plane(pts, n_pts, sample_ids=None, seed=0, iters=1000, thresh=0.05, want_mask=False, frame_id_base=0):
     """pts [F,3,P] fp32/fp64 SoA, n_pts [F] int32, sample_ids [F,iters,3] int32 or None (Philox).
     Returns dict(eq [F,4], best_iter [F], count [F], normal [F,3], mask [F,P] | None)."""
     F, _, P = pts.shape
@@ -141,7 +141,8 @@ def ransac_plane(pts, n_pts, sample_ids=None, seed=0, iters=1000, thresh=0.05, w
     wsb = L.lib().tdod_ransac_workspace_bytes(F, iters, 1 if is64 else 0)
     ws = torch.empty(int(wsb), dtype=u8, device=dev)
     L.check(L.lib().tdod_ransac_plane(L.ptr(pts, None, "pts"), 1 if is64 else 0, L.ptr(n_pts, i32, "n_pts"), F, P,
-                                      L.ptr(sample_ids, i32, "sample_ids"), int(seed), int(iters), float(thresh),
+                                      L.ptr(sample_ids, i32, "sample_ids"), int(seed), int(frame_id_base), int(iters),
+                                      float(thresh),
                                       L.ptr(eq), L.ptr(best), L.ptr(cnt), L.ptr(normal), L.ptr(mask), L.ptr(ws), wsb,
                                       L.stream_ptr()))
     return dict(eq=eq, best_iter=best, count=cnt, normal=normal, mask=mask)
@@ -153,7 +154,7 @@ class PssOutputs:
 
 def propose_score_select(depth, K, boxes, prior_mean, prior_std, obj_frame, rects, has_rect, n_prop, yaw_tab=None,
                          iou_boxes=None, noise=None, yaw_idx=None, rot=None, seed=None, obj_id_base=0,
-                         return_all=False, cluster_size=0, out=None):
+                         return_all=False, cluster_size=0, out=None, propose_only=False):
     """The fused hot path (csrc/fused.cu).  depth [F,H,W], K [F,3,3], boxes [N,4], priors [N,3], obj_frame [N] int32,
     rects [N,4,2], has_rect [N] uint8 | None, yaw_tab [F,36,3,3] | None.
     Parity RNG mode: noise [N,6,n] (+ yaw_idx [N,n] int16 | rot [N,n,9]); throughput mode: seed=int (Philox)."""
@@ -161,14 +162,18 @@ def propose_score_select(depth, K, boxes, prior_mean, prior_std, obj_frame, rect
     N = boxes.shape[0]
     dev = depth.device
     o = out if out is not None else PssOutputs()
+    if propose_only:
+        return_all = True
     if out is None:
-        o.best_idx = torch.empty(N, dtype=i32, device=dev)
-        o.best_score = torch.empty(N, dtype=f32, device=dev)
-        o.best_cube = torch.empty((N, 15), dtype=f32, device=dev)
-        o.best_box = torch.empty((N, 4), dtype=f32, device=dev)
+        o.best_idx = o.best_score = o.best_cube = o.best_box = None
+        if not propose_only:
+            o.best_idx = torch.empty(N, dtype=i32, device=dev)
+            o.best_score = torch.empty(N, dtype=f32, device=dev)
+            o.best_cube = torch.empty((N, 15), dtype=f32, device=dev)
+            o.best_box = torch.empty((N, 4), dtype=f32, device=dev)
         o.all_cubes = torch.empty((N, n_prop, 15), dtype=f32, device=dev) if return_all else None
         o.all_boxes = torch.empty((N, n_prop, 4), dtype=f32, device=dev) if return_all else None
-        o.all_scores = torch.empty((N, 4, n_prop), dtype=f32, device=dev) if return_all else None
+        o.all_scores = torch.empty((N, 4, n_prop), dtype=f32, device=dev) if (return_all and not propose_only) else None
         o.stats = torch.empty((N, 6), dtype=f32, device=dev) if return_all else None
     a = L.PssArgs()
     a.depth = L.ptr(depth, f32, "depth")
@@ -200,5 +205,6 @@ def propose_score_select(depth, K, boxes, prior_mean, prior_std, obj_frame, rect
     a.all_cubes, a.all_boxes = L.ptr(o.all_cubes), L.ptr(o.all_boxes)
     a.all_scores, a.stats = L.ptr(o.all_scores), L.ptr(o.stats)
     a.cluster_size = int(cluster_size)
+    a.propose_only = 1 if propose_only else 0
     L.check(L.lib().tdod_propose_score_select(C.byref(a), L.stream_ptr()))
     return o

@@ -28,7 +28,7 @@ class PssArgs(C.Structure):
         ("seed", C.c_uint64), ("obj_id_base", C.c_int64),
         ("best_idx", C.c_void_p), ("best_score", C.c_void_p), ("best_cube", C.c_void_p), ("best_box", C.c_void_p),
         ("all_cubes", C.c_void_p), ("all_boxes", C.c_void_p), ("all_scores", C.c_void_p), ("stats", C.c_void_p),
-        ("cluster_size", C.c_int32),
+        ("cluster_size", C.c_int32), ("propose_only", C.c_int32),
     ]
 
 
@@ -50,7 +50,7 @@ SIGNATURES = {
     "tdod_score_point_cloud": (_I, [_P, _I, _L, _P, _L, _P, _P]),
     "tdod_backproject": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P]),
     "tdod_ransac_workspace_bytes": (_L, [_I, _I, _I]),
-    "tdod_ransac_plane": (_I, [_P, _I, _P, _I, _L, _P, _U64, _I, _D, _P, _P, _P, _P, _P, _P, _L, _P]),
+    "tdod_ransac_plane": (_I, [_P, _I, _P, _I, _L, _P, _U64, _L, _I, _D, _P, _P, _P, _P, _P, _P, _L, _P]),
     "tdod_yaw_table": (_I, [_P, _I, _I, _P, _P]),
     "tdod_propose_score_select": (_I, [C.POINTER(PssArgs), _P]),
 }

@@ -1,0 +1,205 @@
+"""Batched proposal-and-scoring over many frames: the fast entry SURVEY.md 8(b) calls an *addition* to the
+per-object drop-in functions.  One call covers what `ROIHeads_Boxer._forward_cube`
+(cubercnn/modeling/roi_heads/roi_heads.py:304-505) does frame by frame and object by object:
+
+    depth -> strided point cloud -> RANSAC ground plane -> y-up normal      (roi_heads.py:345-428)   K-A
+    normal -> 36-entry yaw table                                           (proposals.py:404-407)
+    object mask -> min-area rectangle of its largest contour               (scorefunction.py:59-68) K-B
+    propose + project + IoU x dims x corners + argmax, fused               (roi_heads.py:493-505)   K-C
+
+Everything runs on the GPU through libtdod; there is no CPU path.  `FrameBatch` holds device tensors,
+`HostBatch` pinned host tensors; `Pipeline.run_host` streams a HostBatch through the device in chunks of
+frames with the copies of chunk k+1 overlapping the kernels of chunk k.
+"""
+import torch
+
+from . import api
+from . import lib as L
+
+f32, i32, u8 = torch.float32, torch.int32, torch.uint8
+
+
+class FrameBatch:
+    """F frames and their N objects (CSR over frames), all on one device.
+
+    depth [F,H,W] f32 · ground [F,H,W] u8/bool or None · K [F,3,3] f32 · obj_off [F+1] (python list / CPU tensor)
+    boxes [N,4] f32 xyxy · prior_mean/prior_std [N,3] f32 (w,h,l) · obj_frame [N] i32 · masks [N,H,W] u8/bool"""
+    __slots__ = ("depth", "ground", "K", "boxes", "prior_mean", "prior_std", "obj_frame", "masks", "frame_ids")
+
+    def __init__(self, depth, ground, K, boxes, prior_mean, prior_std, obj_frame, masks, frame_ids=None):
+        self.depth, self.ground, self.K = depth, ground, K
+        self.boxes, self.prior_mean, self.prior_std = boxes, prior_mean, prior_std
+        self.obj_frame, self.masks, self.frame_ids = obj_frame, masks, frame_ids
+
+    @property
+    def n_frames(self):
+        return int(self.depth.shape[0])
+
+    @property
+    def n_obj(self):
+        return int(self.boxes.shape[0])
+
+    @property
+    def device(self):
+        return self.depth.device
+
+    def to(self, device, non_blocking=False):
+        mv = lambda t: None if t is None else t.to(device, non_blocking=non_blocking)
+        return FrameBatch(mv(self.depth), mv(self.ground), mv(self.K), mv(self.boxes), mv(self.prior_mean),
+                          mv(self.prior_std), mv(self.obj_frame), mv(self.masks), self.frame_ids)
+
+    def pin(self):
+        pm = lambda t: None if t is None else t.pin_memory()
+        return FrameBatch(pm(self.depth), pm(self.ground), pm(self.K), pm(self.boxes), pm(self.prior_mean),
+                          pm(self.prior_std), pm(self.obj_frame), pm(self.masks), self.frame_ids)
+
+    def input_bytes(self):
+        ts = (self.depth, self.ground, self.K, self.boxes, self.prior_mean, self.prior_std, self.obj_frame, self.masks)
+        return sum(t.numel() * t.element_size() for t in ts if t is not None)
+
+    @staticmethod
+    def from_frames(frames, device=None):
+        """stack `tdod.synth.Frame`s (or anything with the same fields) into one batch"""
+        dev = frames[0].depth.device if device is None else torch.device(device)
+        counts = [f.n_obj() for f in frames]
+        obj_frame = torch.repeat_interleave(torch.arange(len(frames), dtype=i32), torch.tensor(counts)).to(dev)
+        cat = lambda name: torch.cat([getattr(f, name) for f in frames if f.n_obj() > 0]).to(dev)
+        masks = None
+        if frames[0].masks is not None:
+            masks = torch.cat([f.masks for f in frames if f.n_obj() > 0]).to(dev)
+        ground = None if frames[0].ground is None else torch.stack([f.ground for f in frames]).to(dev)
+        return FrameBatch(torch.stack([f.depth for f in frames]).to(dev), ground,
+                          torch.stack([f.K for f in frames]).to(dev), cat("boxes"), cat("prior_mean"),
+                          cat("prior_std"), obj_frame, masks, [f.frame_id for f in frames])
+
+
+class Selection:
+    """winners per object (+ per-frame plane outputs)"""
+    __slots__ = ("best_idx", "best_score", "best_cube", "best_box", "normal", "plane_eq", "inlier_count", "rects",
+                 "has_rect", "all")
+
+
+def ground_normals(depth, ground, K, seed=0, sample_ids=None, iters=1000, thresh=0.05, stride=5,
+                   flavour=L.BACKPROJECT_NUMPY, want_other=False, frame_id_base=0):
+    """K-A for a stack of frames: (normal [F,3], eq [F,4], count [F], plane_pts, other_pts, n_pts [F,2]).
+    flavour NUMPY = the fp64 path ROIHeads_Boxer uses (roi_heads.py:345-428), TORCH = the fp32 path of
+    ROIHeads3DScore.normal_vector_from_maps (:1084-1136)."""
+    pts, other, counts = api.backproject(depth, ground, K, stride, flavour, want_other=want_other)
+    r = api.ransac_plane(pts, counts[:, 0].contiguous(), sample_ids, seed=seed, iters=iters, thresh=thresh,
+                         frame_id_base=frame_id_base)
+    return r["normal"], r["eq"], r["count"], pts, other, counts
+
+
+def select(batch, n_prop, seed=0, noise=None, yaw_idx=None, rot=None, sample_ids=None, use_ground=True,
+           ransac_iters=1000, ransac_thresh=0.05, flavour=L.BACKPROJECT_NUMPY, obj_id_base=0, frame_id_base=0,
+           return_all=False, cluster_size=0):
+    """Mode A (roi_heads.py:493-505) for every object of a device-resident batch.  Throughput RNG (in-kernel
+    Philox keyed by global object id) unless `noise` (+ `yaw_idx` / `rot`) hands in host-drawn numbers.
+    Launches only; does not synchronise."""
+    s = Selection()
+    yaw_tab = None
+    s.normal = s.plane_eq = s.inlier_count = None
+    if use_ground and batch.ground is not None:
+        s.normal, s.plane_eq, s.inlier_count, _, _, _ = ground_normals(
+            batch.depth, batch.ground, batch.K, seed=seed, sample_ids=sample_ids, iters=ransac_iters,
+            thresh=ransac_thresh, flavour=flavour, frame_id_base=frame_id_base)
+        yaw_tab = api.yaw_table(s.normal)
+    s.rects, s.has_rect = api.mask_rect(batch.masks)
+    o = api.propose_score_select(batch.depth, batch.K, batch.boxes, batch.prior_mean, batch.prior_std,
+                                 batch.obj_frame, s.rects, s.has_rect, n_prop, yaw_tab=yaw_tab, noise=noise,
+                                 yaw_idx=yaw_idx, rot=rot, seed=None if noise is not None else seed,
+                                 obj_id_base=obj_id_base, return_all=return_all, cluster_size=cluster_size)
+    s.best_idx, s.best_score, s.best_cube, s.best_box = o.best_idx, o.best_score, o.best_cube, o.best_box
+    s.all = o if return_all else None
+    return s
+
+
+# kernels launched by one `select` call (K-A: backproject, hypotheses, count, select; yaw table; K-B: 2 passes; K-C)
+LAUNCHES_PER_SELECT = 8
+LAUNCHES_PER_SELECT_NO_GROUND = 3
+
+
+class Pipeline:
+    """Streams pinned-host batches through one GPU: chunks of `chunk_frames` frames, two device slots, a copy
+    stream and a compute stream.  The result (winners [N, 15+4+1+1] packed as fp32) is read back per chunk."""
+
+    def __init__(self, H, W, n_prop, chunk_frames=32, max_obj_per_chunk=None, device="cuda", seed=0,
+                 use_ground=True):
+        self.H, self.W, self.n_prop = H, W, n_prop
+        self.dev = torch.device(device)
+        self.chunk = chunk_frames
+        self.max_obj = max_obj_per_chunk or chunk_frames * 40
+        self.seed = seed
+        self.use_ground = use_ground
+        self.copy_stream = torch.cuda.Stream(self.dev)
+        self.compute_stream = torch.cuda.Stream(self.dev)
+        d = self.dev
+        self.slots = []
+        for _ in range(2):
+            self.slots.append(dict(
+                depth=torch.empty((chunk_frames, H, W), dtype=f32, device=d),
+                ground=torch.empty((chunk_frames, H, W), dtype=u8, device=d),
+                K=torch.empty((chunk_frames, 3, 3), dtype=f32, device=d),
+                boxes=torch.empty((self.max_obj, 4), dtype=f32, device=d),
+                pm=torch.empty((self.max_obj, 3), dtype=f32, device=d),
+                ps=torch.empty((self.max_obj, 3), dtype=f32, device=d),
+                of=torch.empty((self.max_obj,), dtype=i32, device=d),
+                masks=torch.empty((self.max_obj, H, W), dtype=u8, device=d),
+                packed=torch.empty((self.max_obj, 21), dtype=f32, device=d),
+                copied=torch.cuda.Event(), done=torch.cuda.Event()))
+        self.launches = 0
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+    def run_host(self, hb, obj_off, out=None, obj_id_base=0, frame_id_base=0):
+        """hb: FrameBatch of PINNED host tensors; obj_off: python list [F+1] (CSR).  Returns a pinned host
+        tensor [N,21]: cube(15), box(4), score, index (as fp32; exact below 2^24).  Synchronises at the end."""
+        F, N = hb.n_frames, hb.n_obj
+        if out is None:
+            out = torch.empty((N, 21), dtype=f32).pin_memory()
+        masks_h = hb.masks.view(u8) if hb.masks.dtype == torch.bool else hb.masks
+        ground_h = None
+        if hb.ground is not None:
+            ground_h = hb.ground.view(u8) if hb.ground.dtype == torch.bool else hb.ground
+        k = 0
+        for f0 in range(0, F, self.chunk):
+            f1 = min(F, f0 + self.chunk)
+            o0, o1 = obj_off[f0], obj_off[f1]
+            nf, no = f1 - f0, o1 - o0
+            if no > self.max_obj:
+                raise ValueError("chunk holds %d objects, more than max_obj_per_chunk=%d" % (no, self.max_obj))
+            sl = self.slots[k & 1]
+            k += 1
+            with torch.cuda.stream(self.copy_stream):
+                self.copy_stream.wait_event(sl["done"])       # slot free again (previous use finished)
+                sl["depth"][:nf].copy_(hb.depth[f0:f1], non_blocking=True)
+                if ground_h is not None:
+                    sl["ground"][:nf].copy_(ground_h[f0:f1], non_blocking=True)
+                sl["K"][:nf].copy_(hb.K[f0:f1], non_blocking=True)
+                if no:
+                    sl["boxes"][:no].copy_(hb.boxes[o0:o1], non_blocking=True)
+                    sl["pm"][:no].copy_(hb.prior_mean[o0:o1], non_blocking=True)
+                    sl["ps"][:no].copy_(hb.prior_std[o0:o1], non_blocking=True)
+                    sl["of"][:no].copy_(hb.obj_frame[o0:o1], non_blocking=True)
+                    sl["masks"][:no].copy_(masks_h[o0:o1], non_blocking=True)
+                sl["copied"].record(self.copy_stream)
+            self.h2d_bytes += nf * self.H * self.W * (5 if ground_h is not None else 4) + nf * 36 + no * (44 + self.H * self.W)
+            if no == 0:
+                continue
+            with torch.cuda.stream(self.compute_stream):
+                self.compute_stream.wait_event(sl["copied"])
+                b = FrameBatch(sl["depth"][:nf], sl["ground"][:nf] if ground_h is not None else None, sl["K"][:nf],
+                               sl["boxes"][:no], sl["pm"][:no], sl["ps"][:no], sl["of"][:no] - f0, sl["masks"][:no])
+                s = select(b, self.n_prop, seed=self.seed, use_ground=self.use_ground,
+                           obj_id_base=obj_id_base + o0, frame_id_base=frame_id_base + f0)
+                p = sl["packed"][:no]
+                p[:, 0:15] = s.best_cube
+                p[:, 15:19] = s.best_box
+                p[:, 19] = s.best_score
+                p[:, 20] = s.best_idx.to(f32)
+                out[o0:o1].copy_(p, non_blocking=True)
+                sl["done"].record(self.compute_stream)
+            self.launches += LAUNCHES_PER_SELECT if (self.use_ground and ground_h is not None) else LAUNCHES_PER_SELECT_NO_GROUND
+            self.d2h_bytes += no * 21 * 4
+        self.compute_stream.synchronize()
+        return out

@@ -92,7 +92,8 @@ int tdod_backproject(const float* depth, const uint8_t* ground, const float* K, 
 
 /* Plane.fit_parallel (ProposalNetwork/utils/plane.py:79-134; fp32) / Plane_np.fit == pyransac3d.Plane.fit
  * (plane.py:154-209, roi_heads.py:374-376; fp64), batched over F frames of SoA points [F,3,P_cap].
- * sample_ids [F,iters,3] int32 (python random.sample stream) or NULL -> Philox ids from `seed`.
+ * sample_ids [F,iters,3] int32 (python random.sample stream) or NULL -> Philox ids keyed by (`seed`,
+ * frame_id_base + f, iteration), so a frame's plane does not depend on how frames are batched or sharded.
  * Outputs: out_eq [F,4] (same dtype as the points; sign as the NumPy flavour, i.e. NOT negated),
  * out_best_iter [F], out_count [F], out_normal [F,3] rectified up-vector (roi_heads.py:411-428), fp64/fp32,
  * out_inlier_mask [F,P_cap] uint8 or NULL.  out_normal is rectified from -eq for fp32 points (fit_parallel
@@ -100,8 +101,8 @@ int tdod_backproject(const float* depth, const uint8_t* ground, const float* K, 
  * workspace: tdod_ransac_workspace_bytes(F, iters, pts_f64) bytes of device scratch. */
 int64_t tdod_ransac_workspace_bytes(int F, int iters, int pts_f64);
 int tdod_ransac_plane(const void* pts, int pts_f64, const int32_t* n_pts, int F, int64_t P_cap,
-                      const int32_t* sample_ids, uint64_t seed, int iters, double thresh, void* out_eq,
-                      int32_t* out_best_iter, int32_t* out_count, void* out_normal, uint8_t* out_inlier_mask,
+                      const int32_t* sample_ids, uint64_t seed, int64_t frame_id_base, int iters, double thresh,
+                      void* out_eq, int32_t* out_best_iter, int32_t* out_count, void* out_normal, uint8_t* out_inlier_mask,
                       void* workspace, int64_t workspace_bytes, void* stream);
 
 /* orthobasis_from_normal_t over linspace(0, pi, 36) (utils.py:112-146, proposals.py:405-406).
@@ -143,6 +144,8 @@ typedef struct tdod_pss_args {
     float* all_scores;         /* [n_obj,4,n_prop]: iou, dim, corners, combined */
     float* stats;              /* [n_obj,6]: mean/std of the x, y, z samplers */
     int32_t cluster_size;      /* CTAs per object: 0 = auto, else 1,2,4,8 */
+    int32_t propose_only;      /* != 0: sample + project only (proposals.propose / cubes_to_box): fills all_cubes /
+                                  all_boxes / stats, needs no rects and writes no winners */
 } tdod_pss_args;
 
 /* propose (proposals.py:338-424) + cubes_to_box + score_iou + score_dimensions + score_corners +

@@ -136,10 +136,29 @@ def random_rotations(N, n, generator=None):
     return z
 
 
+def cubes_from_noise(boxes, depth, prior_mean, prior_std, K, n, noise, normal=None, yaw_idx=None, rot=None):
+    """The arithmetic of proposals.py:338-413 with the random numbers GIVEN: noise [6,N,n] accepted standard normals
+    in draw order (w,h,l,x,y,z); yaw_idx [N,n] (with `normal`) or rot [N,n,3,3].  torch.normal(mean_t, std_t) ==
+    z*std + mean with separately rounded multiply and add."""
+    x0, y0, z0 = centre_seeds(boxes, depth, K, n)
+    sc = lambda z, m, sd: z * sd[:, None] + m[:, None]
+    w = sc(noise[0], prior_mean[:, 0], prior_std[:, 0])
+    h = sc(noise[1], prior_mean[:, 1], prior_std[:, 1] * 1.1)
+    l = sc(noise[2], prior_mean[:, 2], prior_std[:, 2])
+    cx = torch.tensor([1.15, 0.0]); cy = torch.tensor([1.1, 0.0]); cz = torch.tensor([0.85, 0.35])
+    x = sc(noise[3], cx[0] * torch.median(x0, dim=1).values + cx[1], torch.std(x0, dim=1) * 1.2)
+    y = sc(noise[4], cy[0] * torch.median(y0, dim=1).values + cy[1], torch.std(y0, dim=1) * 0.8)
+    zt = z0 + l / 2
+    z = sc(noise[5], cz[0] * torch.median(zt, dim=1).values + cz[1], torch.std(zt, dim=1) * 1.2)
+    R = rot if normal is None else yaw_table(normal)[yaw_idx.long()]
+    xyzwhl = torch.stack([x, y, z, w, h, l], 2)
+    return torch.cat((xyzwhl, R.flatten(start_dim=2)), dim=2).to(torch.float32)          # spaces.py:143
+
+
 def propose(boxes, depth, prior_mean, prior_std, K, n, normal=None, generator=None):
     """proposals.py:338-424 `propose` on raw tensors.  Returns dict with
     cubes [N,n,15] fp32, noise [6,N,n] accepted standard normals in draw order (w,h,l,x,y,z),
-    yaw_idx [N,n] int64 (or None), rot_noise, tries [3]."""
+    yaw_idx [N,n] int64 (or None), rot [N,n,3,3] (or None), tries [3]."""
     N = boxes.shape[0]
     x0, y0, z0 = centre_seeds(boxes, depth, K, n)
     mw, mh, ml = prior_mean[:, 0], prior_mean[:, 1], prior_mean[:, 2]
@@ -158,15 +177,15 @@ def propose(boxes, depth, prior_mean, prior_std, K, n, normal=None, generator=No
                                 torch.std(zt, dim=1) * 1.2, n, generator=generator)
     xyzwhl = torch.stack([x, y, z, w, h, l], 2)
     yaw_idx = None
-    rot_noise = None
+    rot = None
     if normal is None:
-        R = random_rotations(N, n, generator)
+        R = rot = random_rotations(N, n, generator)
     else:
         tab = yaw_table(normal)
         yaw_idx = torch.randint(N_YAW, (N, n), generator=generator)
         R = tab[yaw_idx]
     cubes = torch.cat((xyzwhl, R.flatten(start_dim=2)), dim=2).to(torch.float32)  # spaces.py:143
-    return dict(cubes=cubes, noise=torch.stack([zw, zh, zl, zx, zy, zz], 0), yaw_idx=yaw_idx,
+    return dict(cubes=cubes, noise=torch.stack([zw, zh, zl, zx, zy, zz], 0), yaw_idx=yaw_idx, rot=rot,
                 tries=(tw, th, tl), seeds=(x0, y0, z0))
 
 
@@ -242,9 +261,14 @@ def mask_rect(mask_u8):
 
 
 def fallback_rect(c2d):
-    """scorefunction.py:69-75: mean over proposals of the projected-corner extents. c2d [n,8,2]."""
-    x0 = c2d[:, :, 0].min(1)[0].mean().numpy(); x1 = c2d[:, :, 0].max(1)[0].mean().numpy()
-    y0 = c2d[:, :, 1].min(1)[0].mean().numpy(); y1 = c2d[:, :, 1].max(1)[0].mean().numpy()
+    """scorefunction.py:69-75.  The callers pass bube_corners as [1,n,8,2] (roi_heads.py:465,495), so
+    `bube_corners[:,:,0]` is VERTEX 0 of every proposal ([1,n,2]), `.min(1)[0]` the minimum over the n
+    PROPOSALS of its (x, y), and `.mean()` the mean of those two numbers; likewise vertex 1 for the
+    'y' values.  Reproduced as is (the comment there says 'mean of the bube corners'; the arithmetic is not).
+    c2d [n,8,2] -> float32 [4,2]."""
+    b = c2d[None]
+    x0 = b[:, :, 0].min(1)[0].mean().numpy(); x1 = b[:, :, 0].max(1)[0].mean().numpy()
+    y0 = b[:, :, 1].min(1)[0].mean().numpy(); y1 = b[:, :, 1].max(1)[0].mean().numpy()
     return np.array([[x0, y0], [x1, y0], [x1, y1], [x0, y1]])
 
 

@@ -1,0 +1,481 @@
+"""GPU parity: libtdod (through the C ABI, via tdod.api) against the golden fixtures frozen from the unmodified
+reference and against the oracle on identical inputs.
+
+Bars (BASELINE.json north_star): integer / index results bit-exact; fp32 scores within 1e-5 relative (absolute
+floor 1e-7) when the kernels are fed the reference's own cubes; selected index identical wherever the reference's
+top-2 gap exceeds the tolerance.  The fused kernel re-derives the cube centres on the GPU, whose atan2f / sinf differ
+from torch-CPU's (SLEEF) in the last ulp; its centres are therefore compared at 1e-5 relative + 1e-6 m and its scores
+at 2e-5 (w, h, l and R, which involve no transcendental, are bit-exact)."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import tdod_oracle as O
+from tdod import api, pipeline, synth, lib as L
+
+pytestmark = pytest.mark.gpu
+
+RTOL, ATOL = 1e-5, 1e-7
+
+
+def dev():
+    return torch.device("cuda:0")
+
+
+def load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name))
+
+
+def frame_of(g):
+    return synth.make_frame(int(g["frame_id"]), int(g["H"]), int(g["W"]), int(g["n_obj"]))
+
+
+def assert_scores(got, ref, rtol=RTOL, atol=ATOL, what=""):
+    got = np.asarray(got, np.float64); ref = np.asarray(ref, np.float64)
+    assert np.array_equal(np.isnan(got), np.isnan(ref)), what + ": NaN pattern differs"
+    ok = np.abs(got - ref) <= atol + rtol * np.abs(ref)
+    ok |= np.isnan(ref)
+    assert ok.all(), "%s: %d / %d outside tolerance, worst abs %.3g" % (
+        what, int((~ok).sum()), ok.size, float(np.nanmax(np.abs(got - ref))))
+
+
+def run_fused(g, f, S, propose_only=False):
+    d = dev()
+    n, N = int(g["n"]), int(g["n_obj"])
+    noise = torch.from_numpy(g["noise"]).permute(1, 0, 2).contiguous().to(d)
+    yaw_tab = yaw_idx = rot = None
+    if "yaw_idx" in g.files:
+        yaw_tab = api.yaw_table(torch.from_numpy(g["normal"]).to(d)[None])
+        yaw_idx = torch.from_numpy(g["yaw_idx"]).to(d)
+    else:
+        rot = torch.from_numpy(g["cubes"][:, :, 6:]).contiguous().to(d)
+    rects = torch.from_numpy(g["rects"]).to(d)
+    has = torch.ones(N, dtype=torch.uint8, device=d)
+    o = api.propose_score_select(f.depth[None].to(d), f.K[None].to(d), f.boxes.to(d), f.prior_mean.to(d),
+                                 f.prior_std.to(d), torch.zeros(N, dtype=torch.int32, device=d),
+                                 None if propose_only else rects, None if propose_only else has, n, yaw_tab=yaw_tab,
+                                 noise=noise, yaw_idx=yaw_idx, rot=rot, return_all=True, cluster_size=S,
+                                 propose_only=propose_only)
+    torch.cuda.synchronize()
+    return o
+
+
+@pytest.mark.parametrize("name", ["c1_modeA.npz", "c1_modeB.npz", "c2_randrot.npz"])
+@pytest.mark.parametrize("S", [1, 2, 4, 8])
+def test_fused_kernel_against_reference_fixture(golden_dir, name, S):
+    g = load(golden_dir, name)
+    f = frame_of(g)
+    o = run_fused(g, f, S)
+    c, cg = o.all_cubes.cpu().numpy(), g["cubes"]
+    assert np.array_equal(c[..., 3:6], cg[..., 3:6]), "w,h,l must be bit-exact"
+    assert np.array_equal(c[..., 6:], cg[..., 6:]), "R must be bit-exact"
+    assert np.allclose(c[..., :3], cg[..., :3], rtol=1e-5, atol=1e-6), np.abs(c[..., :3] - cg[..., :3]).max()
+    assert np.allclose(o.all_boxes.cpu().numpy(), g["boxes"], rtol=1e-5, atol=2e-3)
+    sc = o.all_scores.cpu().numpy()
+    for k, nm in enumerate(["iou", "dim", "cor", "combined"]):
+        assert_scores(sc[:, k], g[nm], rtol=2e-5, atol=1e-6, what=nm)
+    best = o.best_idx.cpu().numpy()
+    for i in range(len(best)):
+        top2 = np.sort(g["combined"][i])[-2:]
+        if top2[1] - top2[0] > 2e-5 * abs(top2[1]):
+            assert best[i] == int(g["best"][i]), (i, best[i], int(g["best"][i]))
+        assert o.best_score[i].item() == sc[i, 3, best[i]]
+        assert np.array_equal(o.best_cube[i].cpu().numpy(), c[i, best[i]])
+        assert np.array_equal(o.best_box[i].cpu().numpy(), o.all_boxes[i, best[i]].cpu().numpy())
+
+
+def test_fused_results_do_not_depend_on_cluster_size(golden_dir):
+    g = load(golden_dir, "c1_modeA.npz")
+    f = frame_of(g)
+    ref = run_fused(g, f, 1)
+    for S in (2, 4, 8):
+        o = run_fused(g, f, S)
+        assert torch.equal(o.all_cubes, ref.all_cubes) and torch.equal(o.all_scores, ref.all_scores)
+        assert torch.equal(o.best_idx, ref.best_idx)
+
+
+def test_propose_only_mode(golden_dir):
+    g = load(golden_dir, "c1_modeB.npz")
+    f = frame_of(g)
+    full = run_fused(g, f, 1)
+    po = run_fused(g, f, 1, propose_only=True)
+    assert torch.equal(po.all_cubes, full.all_cubes) and torch.equal(po.all_boxes, full.all_boxes)
+    assert po.best_idx is None
+
+
+@pytest.mark.parametrize("name", ["c1_modeA.npz", "c1_modeB.npz", "c2_randrot.npz"])
+def test_per_function_kernels_on_reference_cubes(golden_dir, name):
+    """cubes_to_box / get_bube_corners / score_iou / score_dimensions / score_corners fed the reference's cubes"""
+    g = load(golden_dir, name)
+    f = frame_of(g)
+    d = dev()
+    H, W, N = int(g["H"]), int(g["W"]), int(g["n_obj"])
+    cubes = torch.from_numpy(g["cubes"]).to(d)
+    c2d, bx = api.project_cubes(cubes, f.K.to(d), W, H)
+    assert np.allclose(c2d[0].cpu().numpy(), g["corners2d_obj0"], rtol=1e-6, atol=1e-3)
+    assert np.allclose(bx.cpu().numpy(), g["boxes"], rtol=1e-6, atol=1e-3)
+    c3 = api.cube_corners(cubes)
+    assert np.allclose(c3.cpu().numpy(), O.cube_corners(torch.from_numpy(g["cubes"])).numpy(), rtol=1e-6, atol=1e-6)
+    rects, has = api.mask_rect(f.masks.to(d))
+    assert has.cpu().tolist() == [1] * N
+    for i in range(N):
+        gb = torch.from_numpy(g["boxes"][i]).to(d)          # the reference's boxes: isolates the score arithmetic
+        assert_scores(api.score_iou(f.boxes[i].to(d), gb).cpu().numpy(), g["iou"][i], what="iou")
+        dims = cubes[i, :, 3:6]
+        assert_scores(api.score_dimensions(f.prior_mean[i].to(d), f.prior_std[i].to(d), dims, f.boxes[i].to(d),
+                                           gb).cpu().numpy(), g["dim"][i], what="dim")
+        assert sorted(map(tuple, rects[i].cpu().tolist())) == sorted(map(tuple, g["rects"][i].tolist()))
+    c2d_ref = O.project_corners(O.cube_corners(torch.from_numpy(g["cubes"])), f.K, W, H)
+    for i in range(N):
+        s = api.score_corners(rects[i], c2d_ref[i].contiguous().to(d)).cpu().numpy()
+        assert_scores(s, g["cor"][i], what="corners")
+
+
+def test_yaw_table_bit_exact(golden_dir):
+    g = load(golden_dir, "c1_modeA.npz")
+    nv = torch.from_numpy(g["normal"])
+    tab = api.yaw_table(nv.to(dev())[None])[0].cpu()
+    ref = O.yaw_table(nv).to(torch.float32)
+    assert torch.equal(tab, ref), (tab - ref).abs().max()
+    for n32 in (torch.tensor([0.0, 1.0, 0.0]), torch.tensor([0.0, 0.6, 0.8]), torch.tensor([0.28, 0.96, 0.0])):
+        tab = api.yaw_table(n32.to(dev())[None])[0].cpu()
+        assert torch.allclose(tab, O.yaw_table(n32), rtol=0, atol=1e-7)
+
+
+def _sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def test_backproject_and_ransac_numpy_flavour(golden_dir):
+    g = load(golden_dir, "c1_modeA.npz")
+    f = frame_of(g)
+    d = dev()
+    pts, other, cnt = api.backproject(f.depth[None].to(d), f.ground[None].to(d), f.K[None].to(d), 5, L.BACKPROJECT_NUMPY)
+    pg, pn = O.backproject_np(f.depth.numpy(), f.K.numpy(), f.ground.numpy())
+    assert cnt.cpu().tolist() == [[len(pg), len(pn)]]
+    assert np.array_equal(pts[0, :, :len(pg)].t().cpu().numpy(), pg)          # fp64, bit-exact
+    assert np.array_equal(other[0, :, :len(pn)].t().cpu().numpy(), pn)
+    ids = torch.from_numpy(g["sample_ids"])[None].contiguous().to(d)
+    r = api.ransac_plane(pts, cnt[:, 0].contiguous(), ids, thresh=0.05, want_mask=True)
+    assert np.array_equal(r["eq"][0].cpu().numpy(), g["plane_eq"])
+    assert int(r["count"][0]) == int(g["n_inliers"])
+    inl = torch.where(r["mask"][0] > 0)[0].cpu().numpy().astype(np.int64)
+    assert _sha(inl) == str(g["inlier_sha"])
+    assert np.array_equal(r["normal"][0].cpu().numpy(), g["normal"])
+
+
+def test_backproject_and_ransac_torch_flavour_and_caixa(golden_dir):
+    g = load(golden_dir, "planes.npz")
+    f = frame_of(g)
+    d = dev()
+    pts, _, cnt = api.backproject(f.depth[None].to(d), f.ground[None].to(d), f.K[None].to(d), 5, L.BACKPROJECT_TORCH)
+    po = O.backproject_torch(f.depth, f.K, f.ground)
+    assert int(cnt[0, 0]) == int(g["torch_n_pts"]) == len(po)
+    assert torch.equal(pts[0, :, :len(po)].t().cpu(), po)
+    ids = torch.from_numpy(g["torch_ids"])[None].contiguous().to(d)
+    r = api.ransac_plane(pts, cnt[:, 0].contiguous(), ids, thresh=0.05, want_mask=True)
+    assert np.array_equal((-r["eq"][0]).cpu().numpy(), g["torch_eq"])       # fit_parallel returns -equation
+    assert int(r["count"][0]) == int(g["torch_n_inliers"])
+    assert _sha(torch.where(r["mask"][0] > 0)[0].cpu().numpy()) == str(g["torch_inlier_sha"])
+    # the reference's caixa.ply fixture (every 6th point), fp64 pyransac3d flavour and fp32 fit_parallel flavour
+    sub = torch.from_numpy(g["caixa_sub"]).t().contiguous()[None].to(d)
+    ids = torch.from_numpy(g["caixa_sub_ids"])[None].contiguous().to(d)
+    n_pts = torch.tensor([sub.shape[2]], dtype=torch.int32, device=d)
+    r = api.ransac_plane(sub, n_pts, ids, thresh=0.01, want_mask=True)
+    assert np.array_equal(r["eq"][0].cpu().numpy(), g["caixa_sub_eq"])
+    assert int(r["count"][0]) == int(g["caixa_sub_n_inliers"])
+    assert _sha(torch.where(r["mask"][0] > 0)[0].cpu().numpy().astype(np.int64)) == str(g["caixa_sub_inlier_sha"])
+    r = api.ransac_plane(sub.float(), n_pts, ids, thresh=0.01)
+    assert np.allclose((-r["eq"][0]).cpu().numpy(), g["caixa_sub32_eq"], rtol=0, atol=2e-7)
+    assert int(r["count"][0]) == int(g["caixa_sub32_n_inliers"])
+
+
+def _rect_dev(a, b):
+    return max(min(float(np.hypot(*(p - q))) for q in b) for p in a)
+
+
+def test_mask_rect_real_and_random_masks(golden_dir):
+    from scipy import ndimage as ndi
+    d = dev()
+    gr = load(golden_dir, "real_masks.npz")
+    for nm in ("mask0", "mask1"):          # the reference's own SAM-HQ masks (ProposalNetwork/mask0.pkl, mask1.pkl)
+        shp = tuple(gr[nm + "_shape"])
+        m = np.unpackbits(gr[nm + "_bits"])[:shp[0] * shp[1]].reshape(shp).astype(bool)
+        r, h = api.mask_rect(torch.from_numpy(m)[None].to(d))
+        assert int(h[0]) == 1 and _rect_dev(r[0].cpu().numpy(), gr[nm + "_rect"]) < 1e-3
+        s = api.score_corners(r[0], torch.from_numpy(gr[nm + "_c2d"]).to(d)).cpu().numpy()
+        assert_scores(s, gr[nm + "_cor"], what=nm)
+    rs = np.random.RandomState(0)
+    H, W = 200, 240
+    ms = []
+    for t in range(200):
+        k = t % 4
+        if k == 0:
+            m = ndi.gaussian_filter(rs.randn(H, W), rs.uniform(1.5, 8)) > rs.uniform(-0.05, 0.1)
+        elif k == 1:
+            m = np.zeros((H, W), bool)
+            for _ in range(rs.randint(1, 6)):
+                x, y, s = rs.randint(0, W), rs.randint(0, H), rs.randint(1, 14)
+                m[y:y + s, x:x + s] = True
+        elif k == 2:
+            m = ndi.gaussian_filter(rs.randn(H, W), 4) > 0
+            m &= rs.rand(H, W) < 0.97
+        else:
+            yy, xx = np.mgrid[0:H, 0:W]
+            cx, cy = rs.uniform(60, 180), rs.uniform(60, 140)
+            a, b = rs.uniform(10, 60), rs.uniform(10, 60) * 0.6
+            m = ((xx - cx) / a) ** 2 + ((yy - cy) / b) ** 2 <= 1
+            if t % 8 == 3:
+                m &= ~(((xx - cx) / (a * 0.5)) ** 2 + ((yy - cy) / (b * 0.5)) ** 2 <= 1)
+        ms.append(m)
+    ms.append(np.zeros((H, W), bool))                                          # empty mask -> has_rect 0
+    rects, has = api.mask_rect(torch.from_numpy(np.stack(ms)).to(d))
+    rects, has = rects.cpu().numpy(), has.cpu().numpy()
+    assert has[-1] == 0
+    bit = 0
+    for t, m in enumerate(ms[:-1]):
+        ref = O.mask_rect(m.astype(np.uint8))
+        assert has[t] in (0, 1), "mask %d: code %d" % (t, has[t])
+        assert (ref is None) == (has[t] == 0)
+        if ref is None:
+            continue
+        assert _rect_dev(rects[t], ref) < 1e-3, (t, rects[t], ref)
+        bit += sorted(map(tuple, rects[t].tolist())) == sorted(map(tuple, ref.tolist()))
+    assert bit >= 150
+
+
+def test_segmentation_and_point_cloud_scores_exact(golden_dir):
+    g = load(golden_dir, "c1_modeB.npz")
+    f = frame_of(g)
+    d = dev()
+    cubes = torch.from_numpy(g["cubes"])
+    c2d = O.project_corners(O.cube_corners(cubes), f.K, int(g["W"]), int(g["H"]))
+    for i in range(5):
+        for p5, nm in ((False, "seg_%d"), (True, "modseg_%d")):
+            s = api.score_segmentation(f.masks[i].to(d), c2d[i].contiguous().to(d), p5).cpu().numpy()
+            assert np.array_equal(s, g[nm % i]), nm % i
+    _, pn = O.backproject_np(f.depth.numpy(), f.K.numpy(), f.ground.numpy())
+    pts = torch.from_numpy(pn).to(d)
+    for i in range(5):
+        assert np.array_equal(api.score_point_cloud(pts, cubes[i].contiguous().to(d)).cpu().numpy(), g["pc"][i])
+    pc32 = api.score_point_cloud(pts.float(), cubes[0].contiguous().to(d)).cpu()
+    assert torch.equal(pc32, O.point_cloud_score(torch.from_numpy(pn).float(), cubes[0]))
+    g2 = load(golden_dir, "c2_randrot.npz")
+    f2 = frame_of(g2)
+    c2 = O.project_corners(O.cube_corners(torch.from_numpy(g2["cubes"])), f2.K, int(g2["W"]), int(g2["H"]))
+    for p5, nm in ((False, "seg_0"), (True, "modseg_0")):
+        s = api.score_segmentation(f2.masks[0].to(d), c2[0].contiguous().to(d), p5).cpu().numpy()
+        assert np.array_equal(s, g2[nm])
+
+
+def test_degenerate_semantics(golden_dir):
+    """cubes behind / across the image plane (no z>0 guard), zero-height boxes -> NaN scores, empty mask -> fallback
+    rectangle, the 3-point point-cloud vector"""
+    g = load(golden_dir, "degenerate.npz")
+    d = dev()
+    W, H = int(g["W"]), int(g["H"])
+    cubes = torch.from_numpy(g["cubes"]).to(d)
+    K = torch.from_numpy(g["K"]).to(d)
+    c2d, bx = api.project_cubes(cubes, K, W, H)
+    assert np.allclose(c2d[0].cpu().numpy(), g["corners2d"], rtol=1e-6, atol=1e-3)
+    gb = torch.from_numpy(g["boxes"]).to(d)
+    ref = torch.from_numpy(g["ref_box"]).to(d)
+    assert_scores(api.score_iou(ref, gb).cpu().numpy(), g["iou"], what="iou")
+    s_dim = api.score_dimensions(torch.from_numpy(g["prior_mean"]).to(d), torch.from_numpy(g["prior_std"]).to(d),
+                                 cubes[0, :, 3:6], ref, gb).cpu().numpy()
+    assert np.isnan(g["dim"]).any()
+    assert_scores(s_dim, g["dim"], what="dim")
+    s_cor = api.score_corners(None, torch.from_numpy(g["corners2d"]).to(d)).cpu().numpy()
+    assert_scores(s_cor, g["cor_emptymask"], what="corners (fallback rectangle)")
+    pc = api.score_point_cloud(torch.from_numpy(g["pc_points"]).to(d), torch.from_numpy(g["pc_cube"])[0].to(d))
+    assert pc.cpu().tolist() == g["pc_count"].tolist()
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# the drop-in mirror (3dod_b200/ProposalNetwork) called the way roi_heads.py:283-302, :493-505 call the reference
+# ------------------------------------------------------------------------------------------------------------------
+def _replay_draws(seed, mean, std, n, N, with_normal):
+    """the reference's RNG program order R1..R7 replayed with torch on the GPU: device generator for
+    the six normal tensors (utils.py:45,54), CPU generator for the rotation draw (utils.py:63, proposals.py:407)"""
+    from ProposalNetwork.utils import utils as U
+    torch.manual_seed(seed)
+    zs = [U._accepted_normals(mean[:, 0], std[:, 0], n, 0.05, mean[:, 0] + 2 * std[:, 0])[1],
+          U._accepted_normals(mean[:, 1], std[:, 1] * 1.1, n, 0.05, mean[:, 1] + 2.2 * std[:, 1])[1],
+          U._accepted_normals(mean[:, 2], std[:, 2], n, 0.05, mean[:, 2] + 2 * std[:, 2])[1]]
+    zs += [torch.randn((N, n), device=mean.device) for _ in range(3)]
+    if with_normal:
+        return torch.stack(zs, 0).cpu(), torch.randint(36, (N, n)), None
+    return torch.stack(zs, 0).cpu(), None, O.random_rotations(N, n)
+
+
+@pytest.mark.parametrize("with_normal", [True, False])
+def test_mirror_call_sites(golden_dir, with_normal):
+    import ProposalNetwork.proposals.proposals as proposals
+    from ProposalNetwork.scoring.scorefunction import (score_corners, score_dimensions, score_iou,
+                                                        score_mod_segmentation, score_point_cloud, score_segmentation)
+    from ProposalNetwork.utils.conversions import cubes_to_box
+    from ProposalNetwork.utils.spaces import Boxes, Cubes
+    g = load(golden_dir, "c1_modeA.npz")
+    f = frame_of(g)
+    d = dev()
+    W, H, n, N = 640, 480, 300, 5
+    nv = torch.from_numpy(g["normal"]) if with_normal else None
+    gt_boxes = Boxes(f.boxes.to(d))
+    pm, ps = f.prior_mean.to(d), f.prior_std.to(d)
+    K = f.K.to(d)
+    torch.manual_seed(99)
+    cubes, stats, ranges = proposals.propose(gt_boxes, f.depth.to(d), (pm, ps), (W, H), K, number_of_proposals=n,
+                                             ground_normal=None if nv is None else nv.to(d))
+    assert isinstance(cubes, Cubes) and tuple(cubes.tensor.shape) == (N, n, 15) and stats is None and ranges is None
+    # same generator streams, arithmetic by the oracle on the CPU
+    noise, yaw_idx, rot = _replay_draws(99, pm, ps, n, N, with_normal)
+    ref = O.cubes_from_noise(f.boxes, f.depth, f.prior_mean, f.prior_std, f.K, n, noise, nv, yaw_idx, rot)
+    c = cubes.tensor.cpu()
+    assert torch.equal(c[..., 3:], ref[..., 3:]), "w,h,l,R bit-exact"
+    assert torch.allclose(c[..., :3], ref[..., :3], rtol=1e-5, atol=1e-6)
+    pred_boxes = cubes_to_box(cubes, K, (W, H))
+    assert len(pred_boxes) == N and tuple(pred_boxes[0].tensor.shape) == (n, 4)
+    c2d_ref = O.project_corners(O.cube_corners(c), f.K, W, H)
+    pb_ref = O.boxes_from_corners(c2d_ref)
+    _, pn = O.backproject_np(f.depth.numpy(), f.K.numpy(), f.ground.numpy())
+    pts = torch.from_numpy(pn).to(d)
+    for i in (0, 3):
+        bube = cubes[i].get_bube_corners(K, (W, H))
+        assert tuple(bube.shape) == (1, n, 8, 2)
+        assert torch.allclose(bube[0].cpu(), c2d_ref[i], rtol=1e-6, atol=1e-3)
+        s_iou = score_iou(gt_boxes[i], pred_boxes[i])
+        s_dim = score_dimensions((pm[i], ps[i]), cubes[i].dimensions[0], gt_boxes[i], pred_boxes[i])
+        s_cor = score_corners(f.masks[i], bube)                 # CPU mask, as roi_heads.py:498 passes it
+        comb = np.array(s_iou.cpu()) * np.array(s_dim.cpu()) * np.array(s_cor.cpu())
+        r_iou = O.iou_score(f.boxes[i], pb_ref[i])
+        r_dim = O.dims_score(f.prior_mean[i], f.prior_std[i], c[i, :, 3:6], f.boxes[i], pb_ref[i])
+        r_cor = O.corners_score(f.masks[i], c2d_ref[i])
+        r_comb, r_best = O.select(r_iou, r_dim, r_cor)
+        assert_scores(s_iou.cpu().numpy(), r_iou.numpy(), what="iou")
+        assert_scores(s_dim.cpu().numpy(), r_dim.numpy(), what="dim")
+        assert_scores(s_cor.cpu().numpy(), r_cor.numpy(), what="corners")
+        top2 = np.sort(r_comb)[-2:]
+        if top2[1] - top2[0] > 1e-5 * top2[1]:
+            assert int(np.argmax(comb)) == r_best
+        if i == 0:
+            assert torch.equal(score_segmentation(f.masks[i].to(d), bube).cpu(),
+                               O.segmentation_score(f.masks[i], bube[0].cpu()))
+            assert torch.equal(score_mod_segmentation(f.masks[i].to(d), bube).cpu(),
+                               O.segmentation_score(f.masks[i], bube[0].cpu(), power5=True))
+            assert torch.equal(score_point_cloud(pts, cubes[i]).cpu(), O.point_cloud_score(torch.from_numpy(pn), c[i]))
+    assert torch.allclose(cubes.get_all_corners().cpu(), O.cube_corners(c), rtol=1e-6, atol=1e-6)
+
+
+def test_mirror_plane_api(golden_dir):
+    import random
+    from ProposalNetwork.utils.plane import Plane, Plane_np
+    g = load(golden_dir, "planes.npz")
+    sub = g["caixa_sub"]
+    random.seed(1)
+    eq, inl = Plane_np().fit(sub, thresh=0.01, maxIteration=1000)          # pyransac3d call shape
+    assert np.array_equal(np.array(eq), g["caixa_sub_eq"]) and len(inl) == int(g["caixa_sub_n_inliers"])
+    assert _sha(np.asarray(inl, np.int64)) == str(g["caixa_sub_inlier_sha"])
+    random.seed(1)
+    eq32, inl32 = Plane().fit_parallel(torch.from_numpy(sub).float().to(dev()), 0.01, maxIteration=1000)
+    assert np.allclose(eq32.cpu().numpy(), g["caixa_sub32_eq"], rtol=0, atol=2e-7)
+    assert len(inl32) == int(g["caixa_sub32_n_inliers"]) and inl32.dtype == torch.int64
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# batched pipeline + throughput RNG (in-kernel Philox): properties that hold at any size
+# ------------------------------------------------------------------------------------------------------------------
+def test_pipeline_matches_oracle_end_to_end(golden_dir):
+    """K-A -> yaw table -> K-B -> K-C on device-resident frames with host-drawn randomness == the oracle chain"""
+    g = load(golden_dir, "c1_modeA.npz")
+    f = frame_of(g)
+    d = dev()
+    batch = pipeline.FrameBatch.from_frames([f], d)
+    sel = pipeline.select(batch, int(g["n"]), noise=torch.from_numpy(g["noise"]).permute(1, 0, 2).contiguous().to(d),
+                          yaw_idx=torch.from_numpy(g["yaw_idx"]).to(d),
+                          sample_ids=torch.from_numpy(g["sample_ids"])[None].contiguous().to(d), return_all=True)
+    torch.cuda.synchronize()
+    assert np.array_equal(sel.normal[0].cpu().numpy(), g["normal"])
+    assert np.array_equal(sel.plane_eq[0].cpu().numpy(), g["plane_eq"])
+    assert sel.best_idx.cpu().tolist() == g["best"].tolist()
+    assert_scores(sel.all.all_scores[:, 3].cpu().numpy(), g["combined"], rtol=2e-5, atol=1e-6, what="combined")
+
+
+def _c2_batch(frame_ids, d):
+    c = synth.CONFIGS["C2"]
+    return pipeline.FrameBatch.from_frames(synth.make_frames("C2", frame_ids), d), c
+
+
+def test_philox_mode_is_deterministic_and_batching_invariant():
+    d = dev()
+    b, c = _c2_batch(range(6), d)
+    s1 = pipeline.select(b, 1000, seed=5)
+    s2 = pipeline.select(b, 1000, seed=5)
+    s3 = pipeline.select(b, 1000, seed=6)
+    torch.cuda.synchronize()
+    assert torch.equal(s1.best_idx, s2.best_idx) and torch.equal(s1.best_cube, s2.best_cube)
+    assert not torch.equal(s1.best_idx, s3.best_idx)
+    # frames 3..5 alone, told their global ids, reproduce their slice of the 6-frame run
+    fr = synth.make_frames("C2", range(3, 6))
+    o0 = int((b.obj_frame < 3).sum())
+    s4 = pipeline.select(pipeline.FrameBatch.from_frames(fr, d), 1000, seed=5, obj_id_base=o0, frame_id_base=3)
+    torch.cuda.synchronize()
+    assert torch.equal(s4.normal, s1.normal[3:])
+    assert torch.equal(s4.best_idx, s1.best_idx[o0:]) and torch.equal(s4.best_cube, s1.best_cube[o0:])
+    assert torch.equal(s4.best_score, s1.best_score[o0:])
+
+
+def test_philox_mode_winner_is_the_argmax_of_what_it_scored():
+    """size-independent properties at BASELINE config-2 shape: the winner record is consistent with the all-proposal
+    outputs; recomputing every score with the per-function kernels from the emitted cubes reproduces them; w,h,l
+    respect the truncation bounds of proposals.py:381-383"""
+    d = dev()
+    b, c = _c2_batch(range(4), d)
+    normal, _, _, _, _, _ = pipeline.ground_normals(b.depth, b.ground, b.K, seed=1)
+    rects, has = api.mask_rect(b.masks)
+    o = api.propose_score_select(b.depth, b.K, b.boxes, b.prior_mean, b.prior_std, b.obj_frame, rects, has, 1000,
+                                 yaw_tab=api.yaw_table(normal), seed=1, return_all=True)
+    torch.cuda.synchronize()
+    comb = o.all_scores[:, 3]
+    idx = o.best_idx.long()
+    assert torch.equal(comb.gather(1, idx[:, None])[:, 0], o.best_score)
+    assert (comb.nan_to_num(-1) <= o.best_score[:, None]).all()
+    assert torch.equal(o.all_cubes[torch.arange(len(idx)), idx], o.best_cube)
+    whl = o.all_cubes[..., 3:6]
+    hi = b.prior_mean + b.prior_std * torch.tensor([2.0, 2.2, 2.0], device=d)
+    assert (whl >= 0.05).all() and (whl <= hi[:, None, :] * (1 + 1e-6)).all()
+    W, H = c["W"], c["H"]
+    for i in (0, int(len(idx) // 2), len(idx) - 1):
+        f = int(b.obj_frame[i])
+        _, bx = api.project_cubes(o.all_cubes[i], b.K[f], W, H)
+        assert torch.equal(bx, o.all_boxes[i])
+        assert torch.equal(api.score_iou(b.boxes[i], bx), o.all_scores[i, 0])
+        assert torch.equal(api.score_dimensions(b.prior_mean[i], b.prior_std[i], o.all_cubes[i, :, 3:6], b.boxes[i], bx),
+                           o.all_scores[i, 1])
+        c2d, _ = api.project_cubes(o.all_cubes[i], b.K[f], W, H)
+        assert torch.equal(api.score_corners(rects[i], c2d), o.all_scores[i, 2])
+        # and the oracle agrees on that object's scores given the emitted cubes
+        cc = o.all_cubes[i].cpu()
+        c2 = O.project_corners(O.cube_corners(cc), b.K[f].cpu(), W, H)
+        pb = O.boxes_from_corners(c2)
+        r = O.select(O.iou_score(b.boxes[i].cpu(), pb),
+                     O.dims_score(b.prior_mean[i].cpu(), b.prior_std[i].cpu(), cc[:, 3:6], b.boxes[i].cpu(), pb),
+                     O.corners_score(b.masks[i].cpu(), c2))[0]
+        assert_scores(comb[i].cpu().numpy(), r, rtol=2e-5, atol=1e-6, what="combined vs oracle")
+
+
+def test_host_streaming_pipeline_equals_resident_run():
+    d = dev()
+    frames = synth.make_frames("C2", range(10))
+    hb = pipeline.FrameBatch.from_frames(frames, "cpu").pin()
+    off = [0]
+    for f in frames:
+        off.append(off[-1] + f.n_obj())
+    p = pipeline.Pipeline(530, 730, 1000, chunk_frames=4, seed=3)
+    out = p.run_host(hb, off)
+    s = pipeline.select(hb.to(d), 1000, seed=3)
+    torch.cuda.synchronize()
+    assert torch.equal(out[:, 0:15], s.best_cube.cpu()) and torch.equal(out[:, 20].int(), s.best_idx.cpu())
+    assert p.launches == 3 * pipeline.LAUNCHES_PER_SELECT and p.d2h_bytes == out.numel() * 4
