@@ -163,12 +163,12 @@ __device__ int scan_rows(int* row_off, int H, int* scratch /*[kT/32 + 1]*/) {
 
 // label the runs of `bm` (8-connectivity), accumulate twice the cell-formula area at each root.
 // returns the number of runs, or -1 if they exceed the capacity.
-__device__ int label_runs(const uint32_t* bm, int H, int W, int Wp, RunSet rs, int* scratch) {
+__device__ int label_runs(const uint32_t* bm, int H, int W, int Wp, RunSet rs, int* scratch, int cap) {
     for (int r = threadIdx.x; r < H; r += kT) rs.row_off[r] = row_runs(bm, Wp, W, r, nullptr, 0, 0);
     __syncthreads();
     const int R = scan_rows(rs.row_off, H, scratch);
-    if (R > kRunCap) return -1;
-    for (int r = threadIdx.x; r < H; r += kT) row_runs(bm, Wp, W, r, &rs, rs.row_off[r], kRunCap);
+    if (R > cap) return -1;
+    for (int r = threadIdx.x; r < H; r += kT) row_runs(bm, Wp, W, r, &rs, rs.row_off[r], cap);
     for (int i = threadIdx.x; i < R; i += kT) { rs.parent[i] = i; rs.area2[i] = 0; }
     __syncthreads();
     for (int i = threadIdx.x; i < R; i += kT) {
@@ -515,78 +515,108 @@ __device__ void flood_outside(const uint32_t* mask, uint32_t* out, int H, int W,
     }
 }
 
-template <bool kExact>
+// worst-case number of runs of an H x W mask, and the bytes of one global-memory run set of that capacity
+__host__ __device__ inline int64_t run_cap_global(int H, int W) { return (int64_t)H * ((W + 1) / 2); }
+__host__ __device__ inline size_t slot_bytes(int H, int W) { return align16((size_t)run_cap_global(H, W) * 14 + 64); }
+constexpr int kSlots = 32;        // CTAs (and workspace slots) of the overflow pass
+
+// kExact: fill holes before labelling.  kGlobal: the run arrays live in a workspace slot (masks with more runs than
+// shared memory holds -- speckle noise); the CTA then walks every mask whose state is 3.
+template <bool kExact, bool kGlobal>
 __global__ void __launch_bounds__(kT, 1) mask_rect_kernel(const uint8_t* __restrict__ masks, int64_t n_masks, int H, int W,
-                                                          float* __restrict__ out_rects, uint8_t* __restrict__ out_has) {
+                                                          float* __restrict__ out_rects, uint8_t* __restrict__ out_has,
+                                                          unsigned char* __restrict__ ws) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int64_t mi = blockIdx.x;
-    if (mi >= n_masks) return;
-    if (kExact && out_has[mi] != 2) return;      // pass 2 only revisits the masks pass 1 could not decide
     const int Wp = (W + 31) >> 5;
     Smem s;
     smem_layout(H, Wp, kExact, &s, smem_raw);
-    for (int i = threadIdx.x; i < H * Wp; i += kT) s.bmA[i] = 0u;
-    __syncthreads();
-    load_pack(masks + mi * (int64_t)H * W, H, W, Wp, s.bmA);
-    __syncthreads();
-    const uint32_t* comp_bm = s.bmA;
-    if (kExact) {
-        flood_outside(s.bmA, s.bmB, H, W, Wp, s.scratch + 30);
-        const uint32_t tail = (W & 31) ? ((1u << (W & 31)) - 1u) : 0xffffffffu;
-        for (int i = threadIdx.x; i < H * Wp; i += kT) {
-            const int w = i % Wp;
-            s.bmB[i] = ~s.bmB[i] & ((w == Wp - 1) ? tail : 0xffffffffu);    // M = not outside (foreground + holes)
-        }
+    int cap = kRunCap;
+    if (kGlobal) {
+        const int64_t c = run_cap_global(H, W);
+        unsigned char* b = ws + (size_t)blockIdx.x * slot_bytes(H, W);
+        s.rs.parent = (int*)b; s.rs.area2 = (int*)(b + 4 * c);
+        s.rs.xs = (uint16_t*)(b + 8 * c); s.rs.xe = (uint16_t*)(b + 10 * c); s.rs.row = (uint16_t*)(b + 12 * c);
+        cap = (int)c;
+    }
+    for (int64_t mi = blockIdx.x; mi < n_masks; mi += gridDim.x) {
+        __syncthreads();                             // previous mask's shared state is dead
+        const int state = out_has[mi];
+        if (kGlobal && state != 3) continue;         // overflow pass: only masks the shared-memory passes gave up on
+        if (!kGlobal && kExact && state != 2) continue;   // pass 2 only revisits the masks pass 1 could not decide
+        for (int i = threadIdx.x; i < H * Wp; i += kT) s.bmA[i] = 0u;
         __syncthreads();
-        comp_bm = s.bmB;
+        load_pack(masks + mi * (int64_t)H * W, H, W, Wp, s.bmA);
+        __syncthreads();
+        const uint32_t* comp_bm = s.bmA;
+        if (kExact) {
+            flood_outside(s.bmA, s.bmB, H, W, Wp, s.scratch + 30);
+            const uint32_t tail = (W & 31) ? ((1u << (W & 31)) - 1u) : 0xffffffffu;
+            for (int i = threadIdx.x; i < H * Wp; i += kT) {
+                const int w = i % Wp;
+                s.bmB[i] = ~s.bmB[i] & ((w == Wp - 1) ? tail : 0xffffffffu);    // M = not outside (foreground + holes)
+            }
+            __syncthreads();
+            comp_bm = s.bmB;
+        }
+        const int R = label_runs(comp_bm, H, W, Wp, s.rs, s.scratch, cap);
+        if (R == 0) {                                   // empty mask: scorefunction.py:69-75 fallback applies
+            if (threadIdx.x == 0) out_has[mi] = 0;
+            continue;
+        }
+        if (R < 0) {                                    // more runs than shared memory holds -> overflow pass
+            if (threadIdx.x == 0) out_has[mi] = 3;
+            continue;
+        }
+        bool ambiguous = false;
+        const int root = select_component(s.rs, R, !kExact, s.scratch, &ambiguous);
+        if (ambiguous) {
+            if (threadIdx.x == 0) out_has[mi] = 2;
+            continue;
+        }
+        component_rect(s.rs, R, root, H, s.rowL, s.rowR, s.hb, s.scratch + 26, s.out8);
+        if (threadIdx.x < 8) out_rects[mi * 8 + threadIdx.x] = s.out8[threadIdx.x];
+        if (threadIdx.x == 0) out_has[mi] = 1;
     }
-    const int R = label_runs(comp_bm, H, W, Wp, s.rs, s.scratch);
-    if (R == 0) {                                   // empty mask: scorefunction.py:69-75 fallback applies
-        if (threadIdx.x == 0) out_has[mi] = 0;
-        return;
-    }
-    if (R < 0) {                                    // more runs than shared memory holds
-        if (threadIdx.x == 0) out_has[mi] = 3;
-        return;
-    }
-    bool ambiguous = false;
-    const int root = select_component(s.rs, R, !kExact, s.scratch, &ambiguous);
-    if (ambiguous) {
-        if (threadIdx.x == 0) out_has[mi] = 2;
-        return;
-    }
-    component_rect(s.rs, R, root, H, s.rowL, s.rowR, s.hb, s.scratch + 26, s.out8);
-    if (threadIdx.x < 8) out_rects[mi * 8 + threadIdx.x] = s.out8[threadIdx.x];
-    if (threadIdx.x == 0) out_has[mi] = 1;
 }
 
 }  // namespace
 
 extern "C" int64_t tdod_mask_rect_workspace_bytes(int64_t n_masks, int H, int W) {
-    (void)n_masks; (void)H; (void)W;
-    return 16;   // everything lives in shared memory; kept in the ABI for masks that outgrow it
+    if (n_masks <= 0 || H <= 0 || W <= 0) return 16;
+    const int64_t slots = n_masks < kSlots ? n_masks : kSlots;
+    return (int64_t)(slots * slot_bytes(H, W));
 }
 
 extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int W, float* out_rects,
                               uint8_t* out_has_rect, void* workspace, int64_t workspace_bytes, void* stream) {
-    (void)workspace; (void)workspace_bytes;
     if (n_masks == 0) return TDOD_OK;
     if (!masks || !out_rects || !out_has_rect || n_masks < 0 || H <= 0 || W < 16)
         return tdod_fail(TDOD_EINVAL, "tdod_mask_rect: bad argument (W must be >= 16)");
     if (H > 32767 || W > 32767) return tdod_fail(TDOD_ERANGE, "tdod_mask_rect: image larger than 32767");
+    if (!workspace || workspace_bytes < tdod_mask_rect_workspace_bytes(n_masks, H, W))
+        return tdod_fail(TDOD_EINVAL, "tdod_mask_rect: workspace smaller than tdod_mask_rect_workspace_bytes()");
     const int Wp = (W + 31) >> 5;
     const size_t smem1 = smem_layout(H, Wp, false, nullptr, nullptr);
     const size_t smem2 = smem_layout(H, Wp, true, nullptr, nullptr);
     if (smem2 > 227 * 1024)
         return tdod_fail(TDOD_ERANGE, "tdod_mask_rect: mask does not fit in shared memory (H*ceil(W/32)*8 bytes + 60 KB <= 227 KB)");
     cudaStream_t st = (cudaStream_t)stream;
-    cudaError_t e = cudaFuncSetAttribute(mask_rect_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1);
+    cudaError_t e = cudaFuncSetAttribute(mask_rect_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1);
     if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(mask_rect_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+    e = cudaFuncSetAttribute(mask_rect_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
     if (e != cudaSuccess) return (int)e;
-    mask_rect_kernel<false><<<(unsigned)n_masks, kT, smem1, st>>>(masks, n_masks, H, W, out_rects, out_has_rect);
+    e = cudaFuncSetAttribute(mask_rect_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+    if (e != cudaSuccess) return (int)e;
+    // the state byte doubles as the work list of the later passes: every mask starts undecided
+    e = cudaMemsetAsync(out_has_rect, 0xff, (size_t)n_masks, st);
+    if (e != cudaSuccess) return (int)e;
+    mask_rect_kernel<false, false><<<(unsigned)n_masks, kT, smem1, st>>>(masks, n_masks, H, W, out_rects, out_has_rect, nullptr);
     TDOD_CHECK_LAUNCH();
-    mask_rect_kernel<true><<<(unsigned)n_masks, kT, smem2, st>>>(masks, n_masks, H, W, out_rects, out_has_rect);
+    mask_rect_kernel<true, false><<<(unsigned)n_masks, kT, smem2, st>>>(masks, n_masks, H, W, out_rects, out_has_rect, nullptr);
+    TDOD_CHECK_LAUNCH();
+    const unsigned slots = (unsigned)(n_masks < kSlots ? n_masks : kSlots);
+    mask_rect_kernel<true, true><<<slots, kT, smem2, st>>>(masks, n_masks, H, W, out_rects, out_has_rect,
+                                                           (unsigned char*)workspace);
     TDOD_CHECK_LAUNCH();
     return TDOD_OK;
 }

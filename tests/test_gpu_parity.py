@@ -142,7 +142,7 @@ def test_yaw_table_bit_exact(golden_dir):
     assert torch.equal(tab, ref), (tab - ref).abs().max()
     for n32 in (torch.tensor([0.0, 1.0, 0.0]), torch.tensor([0.0, 0.6, 0.8]), torch.tensor([0.28, 0.96, 0.0])):
         tab = api.yaw_table(n32.to(dev())[None])[0].cpu()
-        assert torch.allclose(tab, O.yaw_table(n32), rtol=0, atol=1e-7)
+        assert torch.allclose(tab, O.yaw_table(n32), rtol=0, atol=3e-7)      # fp32 normals: torch-CPU's cross may contract
 
 
 def _sha(a):
@@ -185,7 +185,9 @@ def test_backproject_and_ransac_torch_flavour_and_caixa(golden_dir):
     ids = torch.from_numpy(g["caixa_sub_ids"])[None].contiguous().to(d)
     n_pts = torch.tensor([sub.shape[2]], dtype=torch.int32, device=d)
     r = api.ransac_plane(sub, n_pts, ids, thresh=0.01, want_mask=True)
-    assert np.array_equal(r["eq"][0].cpu().numpy(), g["caixa_sub_eq"])
+    # NumPy's norm / dot go through BLAS (FMA, its own summation order): the equation agrees to the last few ulps,
+    # the selected hypothesis, the inlier count and the inlier set exactly
+    assert np.allclose(r["eq"][0].cpu().numpy(), g["caixa_sub_eq"], rtol=1e-13, atol=0)
     assert int(r["count"][0]) == int(g["caixa_sub_n_inliers"])
     assert _sha(torch.where(r["mask"][0] > 0)[0].cpu().numpy().astype(np.int64)) == str(g["caixa_sub_inlier_sha"])
     r = api.ransac_plane(sub.float(), n_pts, ids, thresh=0.01)
@@ -231,6 +233,8 @@ def test_mask_rect_real_and_random_masks(golden_dir):
             if t % 8 == 3:
                 m &= ~(((xx - cx) / (a * 0.5)) ** 2 + ((yy - cy) / (b * 0.5)) ** 2 <= 1)
         ms.append(m)
+    ms.append(rs.rand(H, W) < 0.5)                                             # speckle: > 3072 runs -> overflow pass
+    ms.append(rs.rand(H, W) < 0.08)
     ms.append(np.zeros((H, W), bool))                                          # empty mask -> has_rect 0
     rects, has = api.mask_rect(torch.from_numpy(np.stack(ms)).to(d))
     rects, has = rects.cpu().numpy(), has.cpu().numpy()
@@ -376,7 +380,7 @@ def test_mirror_plane_api(golden_dir):
     sub = g["caixa_sub"]
     random.seed(1)
     eq, inl = Plane_np().fit(sub, thresh=0.01, maxIteration=1000)          # pyransac3d call shape
-    assert np.array_equal(np.array(eq), g["caixa_sub_eq"]) and len(inl) == int(g["caixa_sub_n_inliers"])
+    assert np.allclose(np.array(eq), g["caixa_sub_eq"], rtol=1e-13, atol=0) and len(inl) == int(g["caixa_sub_n_inliers"])
     assert _sha(np.asarray(inl, np.int64)) == str(g["caixa_sub_inlier_sha"])
     random.seed(1)
     eq32, inl32 = Plane().fit_parallel(torch.from_numpy(sub).float().to(dev()), 0.01, maxIteration=1000)
@@ -403,6 +407,12 @@ def test_pipeline_matches_oracle_end_to_end(golden_dir):
     assert_scores(sel.all.all_scores[:, 3].cpu().numpy(), g["combined"], rtol=2e-5, atol=1e-6, what="combined")
 
 
+def eq_nan(a, b):
+    """bitwise-style equality that treats NaN == NaN (winner scores are NaN where the reference's are: a zero-height
+    projected box makes scorefunction.py:156-160 produce inf/inf, and np.argmax then picks the first NaN)"""
+    return a.shape == b.shape and bool(((a == b) | (a.isnan() & b.isnan())).all())
+
+
 def _c2_batch(frame_ids, d):
     c = synth.CONFIGS["C2"]
     return pipeline.FrameBatch.from_frames(synth.make_frames("C2", frame_ids), d), c
@@ -415,7 +425,7 @@ def test_philox_mode_is_deterministic_and_batching_invariant():
     s2 = pipeline.select(b, 1000, seed=5)
     s3 = pipeline.select(b, 1000, seed=6)
     torch.cuda.synchronize()
-    assert torch.equal(s1.best_idx, s2.best_idx) and torch.equal(s1.best_cube, s2.best_cube)
+    assert torch.equal(s1.best_idx, s2.best_idx) and eq_nan(s1.best_cube, s2.best_cube)
     assert not torch.equal(s1.best_idx, s3.best_idx)
     # frames 3..5 alone, told their global ids, reproduce their slice of the 6-frame run
     fr = synth.make_frames("C2", range(3, 6))
@@ -423,8 +433,8 @@ def test_philox_mode_is_deterministic_and_batching_invariant():
     s4 = pipeline.select(pipeline.FrameBatch.from_frames(fr, d), 1000, seed=5, obj_id_base=o0, frame_id_base=3)
     torch.cuda.synchronize()
     assert torch.equal(s4.normal, s1.normal[3:])
-    assert torch.equal(s4.best_idx, s1.best_idx[o0:]) and torch.equal(s4.best_cube, s1.best_cube[o0:])
-    assert torch.equal(s4.best_score, s1.best_score[o0:])
+    assert torch.equal(s4.best_idx, s1.best_idx[o0:]) and eq_nan(s4.best_cube, s1.best_cube[o0:])
+    assert eq_nan(s4.best_score, s1.best_score[o0:])
 
 
 def test_philox_mode_winner_is_the_argmax_of_what_it_scored():
@@ -440,9 +450,15 @@ def test_philox_mode_winner_is_the_argmax_of_what_it_scored():
     torch.cuda.synchronize()
     comb = o.all_scores[:, 3]
     idx = o.best_idx.long()
-    assert torch.equal(comb.gather(1, idx[:, None])[:, 0], o.best_score)
-    assert (comb.nan_to_num(-1) <= o.best_score[:, None]).all()
-    assert torch.equal(o.all_cubes[torch.arange(len(idx)), idx], o.best_cube)
+    assert eq_nan(comb.gather(1, idx[:, None])[:, 0], o.best_score)
+    # np.argmax semantics: the first NaN if any, else the first maximum
+    has_nan = comb.isnan().any(1)
+    assert has_nan.any() and not has_nan.all(), "the batch should exercise both branches"
+    first_nan = comb.isnan().float().argmax(1)
+    first_max = comb.nan_to_num(-1).argmax(1)
+    assert torch.equal(idx, torch.where(has_nan, first_nan, first_max))
+    assert torch.equal(o.best_score.isnan(), has_nan)
+    assert eq_nan(o.all_cubes[torch.arange(len(idx)), idx], o.best_cube)
     whl = o.all_cubes[..., 3:6]
     hi = b.prior_mean + b.prior_std * torch.tensor([2.0, 2.2, 2.0], device=d)
     assert (whl >= 0.05).all() and (whl <= hi[:, None, :] * (1 + 1e-6)).all()
@@ -450,12 +466,12 @@ def test_philox_mode_winner_is_the_argmax_of_what_it_scored():
     for i in (0, int(len(idx) // 2), len(idx) - 1):
         f = int(b.obj_frame[i])
         _, bx = api.project_cubes(o.all_cubes[i], b.K[f], W, H)
-        assert torch.equal(bx, o.all_boxes[i])
-        assert torch.equal(api.score_iou(b.boxes[i], bx), o.all_scores[i, 0])
-        assert torch.equal(api.score_dimensions(b.prior_mean[i], b.prior_std[i], o.all_cubes[i, :, 3:6], b.boxes[i], bx),
-                           o.all_scores[i, 1])
+        assert eq_nan(bx, o.all_boxes[i])
+        assert eq_nan(api.score_iou(b.boxes[i], bx), o.all_scores[i, 0])
+        assert eq_nan(api.score_dimensions(b.prior_mean[i], b.prior_std[i], o.all_cubes[i, :, 3:6], b.boxes[i], bx),
+                      o.all_scores[i, 1])
         c2d, _ = api.project_cubes(o.all_cubes[i], b.K[f], W, H)
-        assert torch.equal(api.score_corners(rects[i], c2d), o.all_scores[i, 2])
+        assert eq_nan(api.score_corners(rects[i], c2d), o.all_scores[i, 2])
         # and the oracle agrees on that object's scores given the emitted cubes
         cc = o.all_cubes[i].cpu()
         c2 = O.project_corners(O.cube_corners(cc), b.K[f].cpu(), W, H)
@@ -477,5 +493,6 @@ def test_host_streaming_pipeline_equals_resident_run():
     out = p.run_host(hb, off)
     s = pipeline.select(hb.to(d), 1000, seed=3)
     torch.cuda.synchronize()
-    assert torch.equal(out[:, 0:15], s.best_cube.cpu()) and torch.equal(out[:, 20].int(), s.best_idx.cpu())
+    assert eq_nan(out[:, 0:15], s.best_cube.cpu()) and torch.equal(out[:, 20].int(), s.best_idx.cpu())
+    assert eq_nan(out[:, 19], s.best_score.cpu())
     assert p.launches == 3 * pipeline.LAUNCHES_PER_SELECT and p.d2h_bytes == out.numel() * 4
