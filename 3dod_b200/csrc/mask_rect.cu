@@ -24,7 +24,7 @@ using namespace tdod;
 namespace {
 
 constexpr int kT = 512;
-constexpr int kRunCap = 3072;     // runs per mask held in shared memory
+constexpr int kRunCap = 2048;     // runs per mask held in shared memory (more -> the global-memory overflow pass)
 
 struct RunSet {                   // shared-memory views
     uint16_t* xs; uint16_t* xe; uint16_t* row;
@@ -201,13 +201,48 @@ __device__ int label_runs(const uint32_t* bm, int H, int W, int Wp, RunSet rs, i
     return R;
 }
 
-// ---- hull + rotating calipers of the component `root` (serial tail, run by warp 0) -----------------------
+// ---- hull + rotating calipers of the component `root` ----------------------------------------------------------
+// Only two things are inherently sequential: the monotone-chain stacks (one thread per chain, top of stack in
+// registers) and the calipers' walk around the hull (one thread, everything it reads precomputed in parallel).
+constexpr int kChainCap = 512;    // vertices of one strictly convex chain (a lattice polygon in a <=1024^2 grid has < 360)
+constexpr int kHullCap = 2 * kChainCap;
 struct HullBuf { int16_t* rx; int16_t* ry; int16_t* lx; int16_t* ly; float* hx; float* hy; float* vx; float* vy; float* inv; };
 
 // OpenCV rotatingCalipers (CALIPERS_MINAREARECT), fp32 with every product/sum rounded on its own (the x86
 // build has no FMA contraction), then minAreaRect's centre/size/angle and RotatedRect::points (boxPoints).
-__device__ void calipers_box(const HullBuf& hb, int n, float* out8) {
+// Called by all threads; `ext` = {left, right, top, bottom} start indices (first extreme in hull order).
+__device__ void calipers_box(const HullBuf& hb, int n, int* ext /*[4] smem*/, float* out8) {
     const float* px = hb.hx; const float* py = hb.hy;
+    const int tid = threadIdx.x;
+    if (n >= 3) {
+        // edge vectors and inverse lengths (double sqrt + divide each): one edge per thread
+        for (int i = tid; i < n; i += kT) {
+            const int j = (i + 1 < n) ? i + 1 : 0;
+            const double dx = (double)px[j] - (double)px[i], dy = (double)py[j] - (double)py[i];
+            hb.vx[i] = (float)dx; hb.vy[i] = (float)dy;
+            hb.inv[i] = (float)(1.0 / sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy))));
+        }
+        // extremes with the serial scan's semantics (strict compares from index 0: the FIRST extreme wins)
+        if (tid < 128) {
+            const int which = tid >> 5, lane = tid & 31;     // 0 left (min x), 1 right (max x), 2 top (max y), 3 bottom (min y)
+            const float* src = (which < 2) ? px : py;
+            const bool want_min = (which == 0 || which == 3);
+            float bv = src[0]; int bi = 0;
+            for (int i = lane; i < n; i += 32) {
+                const float v = src[i];
+                if (want_min ? (v < bv || (v == bv && i < bi)) : (v > bv || (v == bv && i < bi))) { bv = v; bi = i; }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float v = __shfl_xor_sync(0xffffffffu, bv, o);
+                const int i2 = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (want_min ? (v < bv || (v == bv && i2 < bi)) : (v > bv || (v == bv && i2 < bi))) { bv = v; bi = i2; }
+            }
+            if (lane == 0) ext[which] = bi;
+        }
+    }
+    __syncthreads();
+    if (tid != 0) return;
     if (n == 1) {
         for (int k = 0; k < 4; ++k) { out8[2 * k] = px[0]; out8[2 * k + 1] = py[0]; }
         return;
@@ -220,20 +255,7 @@ __device__ void calipers_box(const HullBuf& hb, int n, float* out8) {
         bw = (float)sqrt(dx * dx + dy * dy); bh = 0.f;
         ang_deg = (double)(float)((double)(float)atan2(dy, dx) * 180.0 / 3.14159265358979323846);
     } else {
-        int left = 0, bottom = 0, right = 0, top = 0;
-        float left_x = px[0], right_x = px[0], top_y = py[0], bottom_y = py[0];
-        float p0x = px[0], p0y = py[0];
-        for (int i = 0; i < n; ++i) {
-            if (p0x < left_x) { left_x = p0x; left = i; }
-            if (p0x > right_x) { right_x = p0x; right = i; }
-            if (p0y > top_y) { top_y = p0y; top = i; }
-            if (p0y < bottom_y) { bottom_y = p0y; bottom = i; }
-            const int j = (i + 1 < n) ? i + 1 : 0;
-            const double dx = (double)px[j] - (double)p0x, dy = (double)py[j] - (double)p0y;
-            hb.vx[i] = (float)dx; hb.vy[i] = (float)dy;
-            hb.inv[i] = (float)(1.0 / sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy))));
-            p0x = px[j]; p0y = py[j];
-        }
+        const int left = ext[0], right = ext[1], top = ext[2], bottom = ext[3];
         float orientation = 0.f;
         {
             double ax = hb.vx[n - 1], ay = hb.vy[n - 1];
@@ -246,28 +268,47 @@ __device__ void calipers_box(const HullBuf& hb, int n, float* out8) {
         }
         float base_a = orientation, base_b = 0.f;
         int seq[4] = {bottom, right, top, left};
+        // the four calipers' current edge (vx, vy, inv) and point (px, py) live in registers; only the caliper
+        // that advances reloads from shared memory
+        float evx[4], evy[4], einv[4], ppx[4], ppy[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            evx[k] = hb.vx[seq[k]]; evy[k] = hb.vy[seq[k]]; einv[k] = hb.inv[seq[k]];
+            ppx[k] = px[seq[k]]; ppy[k] = py[seq[k]];
+        }
         float minarea = 3.402823466e+38f;
         int b_left = 0, b_bottom = 0; float b_a = 0, b_w = 0, b_b = 0, b_h = 0;
         for (int k = 0; k < n; ++k) {
-            const float dp0 = __fadd_rn(__fmul_rn(base_a, hb.vx[seq[0]]), __fmul_rn(base_b, hb.vy[seq[0]]));
-            const float dp1 = __fadd_rn(__fmul_rn(-base_b, hb.vx[seq[1]]), __fmul_rn(base_a, hb.vy[seq[1]]));
-            const float dp2 = __fsub_rn(__fmul_rn(-base_a, hb.vx[seq[2]]), __fmul_rn(base_b, hb.vy[seq[2]]));
-            const float dp3 = __fsub_rn(__fmul_rn(base_b, hb.vx[seq[3]]), __fmul_rn(base_a, hb.vy[seq[3]]));
-            float maxcos = __fmul_rn(dp0, hb.inv[seq[0]]);
+            const float dp0 = __fadd_rn(__fmul_rn(base_a, evx[0]), __fmul_rn(base_b, evy[0]));
+            const float dp1 = __fadd_rn(__fmul_rn(-base_b, evx[1]), __fmul_rn(base_a, evy[1]));
+            const float dp2 = __fsub_rn(__fmul_rn(-base_a, evx[2]), __fmul_rn(base_b, evy[2]));
+            const float dp3 = __fsub_rn(__fmul_rn(base_b, evx[3]), __fmul_rn(base_a, evy[3]));
+            float maxcos = __fmul_rn(dp0, einv[0]);
             int main_el = 0;
-            float c1 = __fmul_rn(dp1, hb.inv[seq[1]]); if (c1 > maxcos) { main_el = 1; maxcos = c1; }
-            float c2 = __fmul_rn(dp2, hb.inv[seq[2]]); if (c2 > maxcos) { main_el = 2; maxcos = c2; }
-            float c3 = __fmul_rn(dp3, hb.inv[seq[3]]); if (c3 > maxcos) { main_el = 3; maxcos = c3; }
-            const int pi = seq[main_el];
-            const float lead_x = __fmul_rn(hb.vx[pi], hb.inv[pi]), lead_y = __fmul_rn(hb.vy[pi], hb.inv[pi]);
+            const float c1 = __fmul_rn(dp1, einv[1]); if (c1 > maxcos) { main_el = 1; maxcos = c1; }
+            const float c2 = __fmul_rn(dp2, einv[2]); if (c2 > maxcos) { main_el = 2; maxcos = c2; }
+            const float c3 = __fmul_rn(dp3, einv[3]); if (c3 > maxcos) { main_el = 3; maxcos = c3; }
+            float lvx = evx[0], lvy = evy[0], linv = einv[0];
+            if (main_el == 1) { lvx = evx[1]; lvy = evy[1]; linv = einv[1]; }
+            else if (main_el == 2) { lvx = evx[2]; lvy = evy[2]; linv = einv[2]; }
+            else if (main_el == 3) { lvx = evx[3]; lvy = evy[3]; linv = einv[3]; }
+            const float lead_x = __fmul_rn(lvx, linv), lead_y = __fmul_rn(lvy, linv);
             if (main_el == 0) { base_a = lead_x; base_b = lead_y; }
             else if (main_el == 1) { base_a = lead_y; base_b = -lead_x; }
             else if (main_el == 2) { base_a = -lead_x; base_b = -lead_y; }
             else { base_a = -lead_y; base_b = lead_x; }
-            seq[main_el] = (seq[main_el] + 1 == n) ? 0 : seq[main_el] + 1;
-            float dx = __fsub_rn(px[seq[1]], px[seq[3]]), dy = __fsub_rn(py[seq[1]], py[seq[3]]);
+            // advance that caliper and reload its edge / point
+            int nx;
+#pragma unroll
+            for (int m = 0; m < 4; ++m)
+                if (m == main_el) {
+                    nx = (seq[m] + 1 == n) ? 0 : seq[m] + 1;
+                    seq[m] = nx;
+                    evx[m] = hb.vx[nx]; evy[m] = hb.vy[nx]; einv[m] = hb.inv[nx]; ppx[m] = px[nx]; ppy[m] = py[nx];
+                }
+            float dx = __fsub_rn(ppx[1], ppx[3]), dy = __fsub_rn(ppy[1], ppy[3]);
             const float width = __fadd_rn(__fmul_rn(dx, base_a), __fmul_rn(dy, base_b));
-            dx = __fsub_rn(px[seq[2]], px[seq[0]]); dy = __fsub_rn(py[seq[2]], py[seq[0]]);
+            dx = __fsub_rn(ppx[2], ppx[0]); dy = __fsub_rn(ppy[2], ppy[0]);
             const float height = __fadd_rn(__fmul_rn(-dx, base_b), __fmul_rn(dy, base_a));
             const float area = __fmul_rn(width, height);
             if (area <= minarea) {
@@ -304,69 +345,114 @@ __device__ void calipers_box(const HullBuf& hb, int n, float* out8) {
 
 // Strict convex hull of the component `root` from its per-row extremes, in cv2.convexHull's output order
 // (start at (max x, max y), then image-clockwise), followed by the calipers.  Called by all threads.
-__device__ void component_rect(const RunSet& rs, int R, int root, int H, int* rowL, int* rowR, const HullBuf& hb,
-                               int* counts /*[3]*/, float* out8) {
-    for (int r = threadIdx.x; r < H; r += kT) { rowL[r] = 0x7fffffff; rowR[r] = -1; }
+// counts: int[8] shared scratch.  Returns false if a chain outgrew kChainCap (cannot happen below 1024^2 pixels).
+__device__ bool component_rect(const RunSet& rs, int R, int root, int H, int* rowL, int* rowR, const HullBuf& hb,
+                               int* counts, float* out8) {
+    const int tid = threadIdx.x;
+    if (tid == 0) { counts[0] = 0; counts[1] = 0; counts[2] = 0x7fffffff; counts[3] = -1; counts[7] = 0; }
+    for (int r = tid; r < H; r += kT) { rowL[r] = 0x7fffffff; rowR[r] = -1; }
     __syncthreads();
-    for (int i = threadIdx.x; i < R; i += kT)
-        if (rs.parent[i] == root) { atomicMin(&rowL[rs.row[i]], (int)rs.xs[i]); atomicMax(&rowR[rs.row[i]], (int)rs.xe[i]); }
+    for (int i = tid; i < R; i += kT)
+        if (rs.parent[i] == root) {
+            const int r = rs.row[i];
+            atomicMin(&rowL[r], (int)rs.xs[i]); atomicMax(&rowR[r], (int)rs.xe[i]);
+            atomicMin(&counts[2], r); atomicMax(&counts[3], r);
+        }
     __syncthreads();
-    if (threadIdx.x == 0 || threadIdx.x == 32) {
-        // tid 0: right chain, tid 32: left chain, both top -> bottom; pop while the turn is not strictly convex
-        const bool right = threadIdx.x == 0;
+    const int rmin = counts[2], rmax = counts[3];      // a connected component occupies every row in between
+    if (tid == 0 || tid == 32) {
+        // tid 0: right chain, tid 32: left chain, both top -> bottom; pop while the turn is not strictly convex.
+        // (ax,ay) / (bx,by) mirror the two topmost stack entries so that a push costs no shared-memory read.
+        const bool right = tid == 0;
         int16_t* X = right ? hb.rx : hb.lx; int16_t* Y = right ? hb.ry : hb.ly;
         const int* src = right ? rowR : rowL;
-        int n = 0;
-        for (int r = 0; r < H; ++r) {
-            if (rowR[r] < 0) continue;
+        int n = 0, ax = 0, ay = 0, bx = 0, by = 0;
+        bool ok = true;
+        for (int r = rmin; r <= rmax; ++r) {
             const int cx = src[r], cy = r;
             while (n >= 2) {
-                const int ax = X[n - 2], ay = Y[n - 2], bx = X[n - 1], by = Y[n - 1];
                 const int cr = (bx - ax) * (cy - by) - (by - ay) * (cx - bx);
-                if (right ? (cr <= 0) : (cr >= 0)) --n; else break;
+                if (right ? (cr <= 0) : (cr >= 0)) {
+                    --n; bx = ax; by = ay;
+                    if (n >= 2) { ax = X[n - 2]; ay = Y[n - 2]; }
+                } else break;
             }
+            if (n >= kChainCap) { ok = false; break; }
             X[n] = (int16_t)cx; Y[n] = (int16_t)cy; ++n;
+            ax = bx; ay = by; bx = cx; by = cy;
         }
         counts[right ? 0 : 1] = n;
+        if (!ok) counts[7] = 1;
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
-        const int nr = counts[0], nl = counts[1];
-        // cyclic order: right chain downward, then left chain upward (dropping duplicated end points)
-        int n = 0;
-        for (int i = 0; i < nr; ++i) { hb.hx[n] = (float)hb.rx[i]; hb.hy[n] = (float)hb.ry[i]; ++n; }
-        for (int i = nl - 1; i >= 0; --i) {
-            const bool dup_bottom = (i == nl - 1) && hb.lx[i] == hb.rx[nr - 1] && hb.ly[i] == hb.ry[nr - 1];
-            const bool dup_top = (i == 0) && hb.lx[0] == hb.rx[0] && hb.ly[0] == hb.ry[0];
-            if (dup_bottom || dup_top) continue;
-            hb.hx[n] = (float)hb.lx[i]; hb.hy[n] = (float)hb.ly[i]; ++n;
+    if (counts[7]) return false;
+    const int nr = counts[0], nl = counts[1];
+    // cyclic order: right chain downward, then left chain upward (dropping duplicated end points)
+    const bool dup_bottom = hb.lx[nl - 1] == hb.rx[nr - 1] && hb.ly[nl - 1] == hb.ry[nr - 1];
+    const bool dup_top = hb.lx[0] == hb.rx[0] && hb.ly[0] == hb.ry[0];
+    // left-chain entries kept: indices [lo, hi] walked downward from hi
+    const int hi = nl - 1 - (dup_bottom ? 1 : 0), lo = dup_top ? 1 : 0;
+    int n = nr + max(0, hi - lo + 1);
+    for (int i = tid; i < n; i += kT) {
+        if (i < nr) { hb.hx[i] = (float)hb.rx[i]; hb.hy[i] = (float)hb.ry[i]; }
+        else { const int k = hi - (i - nr); hb.hx[i] = (float)hb.lx[k]; hb.hy[i] = (float)hb.ly[k]; }
+    }
+    __syncthreads();
+    // collinear triples can only survive across the chain joins of degenerate (1- or 2-row, needle-like) components:
+    // detect in parallel, repair serially only then
+    int bad = 0;
+    if (n > 2)
+        for (int i = tid; i < n; i += kT) {
+            const int a = (i + n - 1) % n, c = (i + 1) % n;
+            const float cr = (hb.hx[i] - hb.hx[a]) * (hb.hy[c] - hb.hy[i]) - (hb.hy[i] - hb.hy[a]) * (hb.hx[c] - hb.hx[i]);
+            bad |= (cr == 0.f);
         }
-        // vertical runs of collinear points can survive at the chain joins (top/bottom rows); a 2-row or 1-row
-        // component degenerates to <= 2 distinct hull directions -- drop collinear triples across the joins
-        bool changed = n > 2;
-        while (changed) {
-            changed = false;
-            for (int i = 0; i < n && n > 2; ++i) {
-                const int a = (i + n - 1) % n, c = (i + 1) % n;
-                const float cr = (hb.hx[i] - hb.hx[a]) * (hb.hy[c] - hb.hy[i]) - (hb.hy[i] - hb.hy[a]) * (hb.hx[c] - hb.hx[i]);
-                if (cr == 0.f) {
-                    for (int k = i; k + 1 < n; ++k) { hb.hx[k] = hb.hx[k + 1]; hb.hy[k] = hb.hy[k + 1]; }
-                    --n; changed = true; break;
+    if (__syncthreads_or(bad)) {
+        if (tid == 0) {
+            bool changed = n > 2;
+            while (changed) {
+                changed = false;
+                for (int i = 0; i < n && n > 2; ++i) {
+                    const int a = (i + n - 1) % n, c = (i + 1) % n;
+                    const float cr = (hb.hx[i] - hb.hx[a]) * (hb.hy[c] - hb.hy[i]) - (hb.hy[i] - hb.hy[a]) * (hb.hx[c] - hb.hx[i]);
+                    if (cr == 0.f) {
+                        for (int k = i; k + 1 < n; ++k) { hb.hx[k] = hb.hx[k + 1]; hb.hy[k] = hb.hy[k + 1]; }
+                        --n; changed = true; break;
+                    }
                 }
             }
+            counts[4] = n;
         }
-        // rotate so that the start is (max x, max y among those)
-        int s = 0;
-        for (int i = 1; i < n; ++i)
-            if (hb.hx[i] > hb.hx[s] || (hb.hx[i] == hb.hx[s] && hb.hy[i] > hb.hy[s])) s = i;
-        if (s) {   // rotate left by s through the (unused) vx/vy scratch
-            for (int i = 0; i < n; ++i) { hb.vx[i] = hb.hx[(i + s) % n]; hb.vy[i] = hb.hy[(i + s) % n]; }
-            for (int i = 0; i < n; ++i) { hb.hx[i] = hb.vx[i]; hb.hy[i] = hb.vy[i]; }
+        __syncthreads();
+        n = counts[4];
+    }
+    // rotate so that the start is (max x, max y among those): first such index in a serial scan == the unique argmax
+    if (tid < 32) {
+        float bxv = hb.hx[0], byv = hb.hy[0]; int bi = 0;
+        for (int i = tid; i < n; i += 32) {
+            const float x = hb.hx[i], y = hb.hy[i];
+            if (x > bxv || (x == bxv && y > byv) || (x == bxv && y == byv && i < bi)) { bxv = x; byv = y; bi = i; }
         }
-        if (n == 2 && hb.hx[0] == hb.hx[1] && hb.hy[0] == hb.hy[1]) n = 1;
-        calipers_box(hb, n, out8);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float x = __shfl_xor_sync(0xffffffffu, bxv, o), y = __shfl_xor_sync(0xffffffffu, byv, o);
+            const int i2 = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (x > bxv || (x == bxv && y > byv) || (x == bxv && y == byv && i2 < bi)) { bxv = x; byv = y; bi = i2; }
+        }
+        if (tid == 0) counts[5] = bi;
     }
     __syncthreads();
+    const int s0 = counts[5];
+    if (s0) {   // rotate left by s0 through the (still unused) vx/vy scratch
+        for (int i = tid; i < n; i += kT) { hb.vx[i] = hb.hx[(i + s0) % n]; hb.vy[i] = hb.hy[(i + s0) % n]; }
+        __syncthreads();
+        for (int i = tid; i < n; i += kT) { hb.hx[i] = hb.vx[i]; hb.hy[i] = hb.vy[i]; }
+        __syncthreads();
+    }
+    if (n == 2 && hb.hx[0] == hb.hx[1] && hb.hy[0] == hb.hy[1]) n = 1;
+    calipers_box(hb, n, counts, out8);
+    __syncthreads();
+    return true;
 }
 
 struct Smem {
@@ -388,10 +474,10 @@ __host__ __device__ inline size_t smem_layout(int H, int Wp, bool two_bitmaps, S
     const size_t o_xs = take(kRunCap * 2), o_xe = take(kRunCap * 2), o_row = take(kRunCap * 2);
     const size_t o_par = take(kRunCap * 4), o_area = take(kRunCap * 4), o_roff = take((size_t)(H + 1) * 4);
     const size_t o_rowL = take((size_t)H * 4), o_rowR = take((size_t)H * 4);
-    const size_t o_rx = take((size_t)H * 2), o_ry = take((size_t)H * 2), o_lx = take((size_t)H * 2), o_ly = take((size_t)H * 2);
-    const size_t hn = (size_t)2 * H + 4;
+    const size_t o_rx = take(kChainCap * 2), o_ry = take(kChainCap * 2), o_lx = take(kChainCap * 2), o_ly = take(kChainCap * 2);
+    const size_t hn = (size_t)kHullCap;
     const size_t o_hx = take(hn * 4), o_hy = take(hn * 4), o_vx = take(hn * 4), o_vy = take(hn * 4), o_inv = take(hn * 4);
-    const size_t o_scr = take((kT / 32 + 24) * 4), o_out = take(8 * 4);
+    const size_t o_scr = take((kT / 32 + 32) * 4), o_out = take(8 * 4);
     if (s) {
         s->bmA = (uint32_t*)(base + o_bmA); s->bmB = two_bitmaps ? (uint32_t*)(base + o_bmB) : nullptr;
         s->rs.xs = (uint16_t*)(base + o_xs); s->rs.xe = (uint16_t*)(base + o_xe); s->rs.row = (uint16_t*)(base + o_row);
@@ -523,7 +609,7 @@ constexpr int kSlots = 32;        // CTAs (and workspace slots) of the overflow 
 // kExact: fill holes before labelling.  kGlobal: the run arrays live in a workspace slot (masks with more runs than
 // shared memory holds -- speckle noise); the CTA then walks every mask whose state is 3.
 template <bool kExact, bool kGlobal>
-__global__ void __launch_bounds__(kT, 1) mask_rect_kernel(const uint8_t* __restrict__ masks, int64_t n_masks, int H, int W,
+__global__ void __launch_bounds__(kT, kExact ? 1 : 2) mask_rect_kernel(const uint8_t* __restrict__ masks, int64_t n_masks, int H, int W,
                                                           float* __restrict__ out_rects, uint8_t* __restrict__ out_has,
                                                           unsigned char* __restrict__ ws) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -573,9 +659,9 @@ __global__ void __launch_bounds__(kT, 1) mask_rect_kernel(const uint8_t* __restr
             if (threadIdx.x == 0) out_has[mi] = 2;
             continue;
         }
-        component_rect(s.rs, R, root, H, s.rowL, s.rowR, s.hb, s.scratch + 26, s.out8);
-        if (threadIdx.x < 8) out_rects[mi * 8 + threadIdx.x] = s.out8[threadIdx.x];
-        if (threadIdx.x == 0) out_has[mi] = 1;
+        const bool ok = component_rect(s.rs, R, root, H, s.rowL, s.rowR, s.hb, s.scratch + 32, s.out8);
+        if (threadIdx.x < 8 && ok) out_rects[mi * 8 + threadIdx.x] = s.out8[threadIdx.x];
+        if (threadIdx.x == 0) out_has[mi] = ok ? 1 : 4;
     }
 }
 
@@ -612,7 +698,9 @@ extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int 
     if (e != cudaSuccess) return (int)e;
     mask_rect_kernel<false, false><<<(unsigned)n_masks, kT, smem1, st>>>(masks, n_masks, H, W, out_rects, out_has_rect, nullptr);
     TDOD_CHECK_LAUNCH();
-    mask_rect_kernel<true, false><<<(unsigned)n_masks, kT, smem2, st>>>(masks, n_masks, H, W, out_rects, out_has_rect, nullptr);
+    // passes 2 and 3 are persistent: a handful of CTAs walk the state bytes and almost always find nothing to do
+    mask_rect_kernel<true, false><<<(unsigned)(n_masks < 148 ? n_masks : 148), kT, smem2, st>>>(masks, n_masks, H, W, out_rects,
+                                                                                          out_has_rect, nullptr);
     TDOD_CHECK_LAUNCH();
     const unsigned slots = (unsigned)(n_masks < kSlots ? n_masks : kSlots);
     mask_rect_kernel<true, true><<<slots, kT, smem2, st>>>(masks, n_masks, H, W, out_rects, out_has_rect,
