@@ -12,10 +12,14 @@
 //     the component whose first pixel comes LAST in raster order;
 //   * minAreaRect = Sklansky hull (strict, start at (max x, max y), image-clockwise) -> fp32 rotating calipers.
 //
-// One CTA per mask.  The mask is streamed once from HBM with 16-byte loads and bit-packed into shared
-// memory; everything after that (run-length encoding, union-find over runs, areas, hull, calipers) runs out
-// of shared memory.  Pass 1 decides every mask whose winner is certain from bounds (area without hole filling
-// <= true area <= bounding box); pass 2 (flood.cu path below) fills holes exactly for the ambiguous rest.
+// Two kernels.  `pack_kernel` is the only one that touches the masks: it streams them once from HBM with 16-byte
+// loads and writes a 1-bit-per-pixel copy (rows padded to whole words) plus the occupied row range of every mask;
+// it is bandwidth-bound and sized to keep ~100 KB of loads in flight per SM.  `rect_kernel` then works per mask on
+// the bitmap (L2-resident, 1/8 of the bytes): run-length encoding, union-find over runs, cell-formula areas, strict
+// hull, rotating calipers.  Those steps are short dependent chains, so the kernel is built small (256 threads,
+// ~36 KB of shared memory) to keep 4+ masks per SM in flight and overlap their serial tails.  Pass 1 decides every
+// mask whose winner is certain from bounds (area without hole filling <= true area <= bounding box); pass 2 fills
+// holes exactly for the ambiguous rest; pass 3 handles speckle masks whose runs outgrow shared memory.
 #include "tdod_device.cuh"
 #include "tdod_internal.h"
 
@@ -23,7 +27,17 @@ using namespace tdod;
 
 namespace {
 
-constexpr int kT = 512;
+constexpr int kT = 256;          // threads of the rectangle kernels
+constexpr int kPackT = 256;      // threads of the pack kernel
+constexpr int kPackRows = 32;    // mask rows per pack tile
+
+// phase timers for tools/kb_phases.cu (compiled out of the library)
+#ifdef TDOD_KB_TIMING
+__device__ long long g_kb_t[16 * 8192];
+#define KB_T(k) do { if (threadIdx.x == 0 && blockIdx.x < 8192) g_kb_t[blockIdx.x * 16 + (k)] = clock64(); } while (0)
+#else
+#define KB_T(k) do { } while (0)
+#endif
 constexpr int kRunCap = 2048;     // runs per mask held in shared memory (more -> the global-memory overflow pass)
 
 struct RunSet {                   // shared-memory views
@@ -45,74 +59,64 @@ __device__ __forceinline__ uint32_t nz_bits16(const uint4 v) {
     return out;
 }
 
-// OR `nbits` bits (LSB first) into the row-packed bitmap at flat pixel index p (may straddle rows)
-__device__ __forceinline__ void scatter_bits(uint32_t* bm, int W, int Wp, int64_t p, uint32_t bits, int nbits) {
-    while (nbits > 0 && bits) {
-        const int r = (int)(p / W), c = (int)(p - (int64_t)r * W);
-        const int take = min(nbits, W - c);
-        const uint32_t seg = bits & ((take >= 32) ? 0xffffffffu : ((1u << take) - 1u));
-        if (seg) {
-            const int wi = c >> 5, sh = c & 31;
-            atomicOr(&bm[r * Wp + wi], seg << sh);
-            if (sh && (sh + take > 32)) atomicOr(&bm[r * Wp + wi + 1], seg >> (32 - sh));
+// ------------------------------------------------------------------------------------------------------------
+// pack: masks [n,H,W] bytes -> bitmap [n,H,Wp] words (bit c&31 of word c>>5 of a row) + occupied row range
+// ------------------------------------------------------------------------------------------------------------
+// A tile is kPackRows consecutive rows of one mask.  Its bytes are fetched as aligned 16-byte chunks of the flat
+// mask array (a row is W bytes, so tiles start at any alignment; the chunks that straddle the tile ends are shared
+// with the neighbouring tile), reduced to 16 bits each and laid down as a contiguous bit stream in shared memory
+// with plain half-word stores; every output word is then a 32-bit window of that stream (funnel shift).
+__global__ void __launch_bounds__(kPackT, 8) pack_kernel(const uint8_t* __restrict__ masks, int64_t n_masks, int H, int W, int Wp,
+                                                        uint32_t* __restrict__ bitmap, int* __restrict__ rowrange,
+                                                        int tiles_per_mask) {
+    extern __shared__ __align__(16) unsigned char pk_raw[];
+    uint16_t* sb16 = reinterpret_cast<uint16_t*>(pk_raw);
+    const uint32_t* sb32 = reinterpret_cast<const uint32_t*>(pk_raw);
+    __shared__ int s_lo, s_hi;
+    const int tid = threadIdx.x;
+    const uintptr_t base = reinterpret_cast<uintptr_t>(masks);
+    const int64_t mis = (int64_t)(base & 15);
+    const uint4* v = reinterpret_cast<const uint4*>(base - mis);
+    const int64_t HW = (int64_t)H * W;
+    const int64_t n_tiles = n_masks * tiles_per_mask;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int64_t m = tile / tiles_per_mask;
+        const int r0 = (int)(tile - m * tiles_per_mask) * kPackRows, r1 = min(H, r0 + kPackRows);
+        const int64_t b0 = mis + m * HW + (int64_t)r0 * W, b1 = mis + m * HW + (int64_t)r1 * W;
+        const int64_t c0 = b0 >> 4;
+        const int nch = (int)(((b1 + 15) >> 4) - c0);
+        if (tid == 0) { s_lo = 0x7fffffff; s_hi = -1; }
+        // bytes outside [b0, b1) that ride along in the first / last chunk are never selected below
+        int c = tid;
+        for (; c + 3 * kPackT < nch; c += 4 * kPackT) {
+            const uint4 a0 = __ldcs(v + c0 + c), a1 = __ldcs(v + c0 + c + kPackT), a2 = __ldcs(v + c0 + c + 2 * kPackT),
+                        a3 = __ldcs(v + c0 + c + 3 * kPackT);
+            sb16[c] = (uint16_t)nz_bits16(a0); sb16[c + kPackT] = (uint16_t)nz_bits16(a1);
+            sb16[c + 2 * kPackT] = (uint16_t)nz_bits16(a2); sb16[c + 3 * kPackT] = (uint16_t)nz_bits16(a3);
         }
-        bits = (take >= 32) ? 0u : (bits >> take);
-        nbits -= take; p += take;
-    }
-}
-
-// stream one mask (H*W bytes, any alignment) into the bitmap
-__device__ void load_pack(const uint8_t* __restrict__ m, int H, int W, int Wp, uint32_t* bm) {
-    const int64_t total = (int64_t)H * W;
-    const uintptr_t addr = reinterpret_cast<uintptr_t>(m);
-    const int64_t head_raw = (int64_t)((16 - (addr & 15)) & 15);
-    const int64_t head = head_raw < total ? head_raw : total;
-    for (int64_t i = threadIdx.x; i < head; i += kT)
-        if (m[i]) scatter_bits(bm, W, Wp, i, 1u, 1);
-    const int64_t nchunks = (total - head) / 16;
-    const uint4* v = reinterpret_cast<const uint4*>(m + head);
-    int64_t c = threadIdx.x;
-    for (; c + 3 * kT < nchunks; c += 4 * kT) {   // four independent 16-byte loads in flight per thread
-        const uint4 a0 = __ldcs(v + c), a1 = __ldcs(v + c + kT), a2 = __ldcs(v + c + 2 * kT), a3 = __ldcs(v + c + 3 * kT);
-        const uint32_t b0 = nz_bits16(a0), b1 = nz_bits16(a1), b2 = nz_bits16(a2), b3 = nz_bits16(a3);
-        if (b0) scatter_bits(bm, W, Wp, head + 16 * c, b0, 16);
-        if (b1) scatter_bits(bm, W, Wp, head + 16 * (c + kT), b1, 16);
-        if (b2) scatter_bits(bm, W, Wp, head + 16 * (c + 2 * kT), b2, 16);
-        if (b3) scatter_bits(bm, W, Wp, head + 16 * (c + 3 * kT), b3, 16);
-    }
-    for (; c < nchunks; c += kT) {
-        const uint32_t b = nz_bits16(__ldcs(v + c));
-        if (b) scatter_bits(bm, W, Wp, head + 16 * c, b, 16);
-    }
-    for (int64_t i = head + nchunks * 16 + threadIdx.x; i < total; i += kT)
-        if (m[i]) scatter_bits(bm, W, Wp, i, 1u, 1);
-}
-
-// number of runs in row r / emit them starting at index `base`
-__device__ int row_runs(const uint32_t* bm, int Wp, int W, int r, RunSet* rs, int base, int cap) {
-    int n = 0, start = 0;
-    uint32_t prev = 0;
-    for (int w = 0; w < Wp; ++w) {
-        const uint32_t m = bm[r * Wp + w];
-        uint32_t t = m ^ ((m << 1) | prev);
-        prev = m >> 31;
-        while (t) {
-            const int b = __ffs(t) - 1;
-            t &= t - 1;
-            const int pos = 32 * w + b;
-            if ((m >> b) & 1u) {
-                start = pos;
-            } else {
-                if (rs && base + n < cap) { rs->xs[base + n] = (uint16_t)start; rs->xe[base + n] = (uint16_t)(pos - 1); rs->row[base + n] = (uint16_t)r; }
-                ++n;
-            }
+        for (; c < nch; c += kPackT) sb16[c] = (uint16_t)nz_bits16(__ldcs(v + c0 + c));
+        if (tid < 4) sb16[nch + tid] = 0;                       // the funnel reads one word past the last chunk
+        __syncthreads();
+        const int nwords = (r1 - r0) * Wp;
+        int lo = 0x7fffffff, hi = -1;
+        for (int k = tid; k < nwords; k += kPackT) {
+            const int rr = k / Wp, w = k - rr * Wp, r = r0 + rr;
+            const int o = (int)(b0 - (c0 << 4)) + rr * W + 32 * w;          // bit offset of the window in the stream
+            uint32_t word = __funnelshift_r(sb32[o >> 5], sb32[(o >> 5) + 1], o & 31);
+            const int nb = W - 32 * w;
+            if (nb < 32) word &= (1u << nb) - 1u;
+            bitmap[((size_t)m * H + r) * Wp + w] = word;
+            if (word) { lo = min(lo, r); hi = max(hi, r); }
         }
+        lo = __reduce_min_sync(0xffffffffu, lo); hi = __reduce_max_sync(0xffffffffu, hi);
+        if ((tid & 31) == 0 && hi >= 0) { atomicMin(&s_lo, lo); atomicMax(&s_hi, hi); }
+        __syncthreads();
+        if (tid == 0 && s_hi >= 0) {                            // rowrange[m] = {first row, H-1-last row}, both via atomicMin
+            atomicMin(&rowrange[2 * m], s_lo);
+            atomicMin(&rowrange[2 * m + 1], H - 1 - s_hi);
+        }
+        __syncthreads();
     }
-    if (prev) {
-        if (rs && base + n < cap) { rs->xs[base + n] = (uint16_t)start; rs->xe[base + n] = (uint16_t)(W - 1); rs->row[base + n] = (uint16_t)r; }
-        ++n;
-    }
-    return n;
 }
 
 __device__ __forceinline__ int uf_find(const int* parent, int x) {
@@ -161,14 +165,111 @@ __device__ int scan_rows(int* row_off, int H, int* scratch /*[kT/32 + 1]*/) {
     return carry;
 }
 
-// label the runs of `bm` (8-connectivity), accumulate twice the cell-formula area at each root.
-// returns the number of runs, or -1 if they exceed the capacity.
-__device__ int label_runs(const uint32_t* bm, int H, int W, int Wp, RunSet rs, int* scratch, int cap) {
-    for (int r = threadIdx.x; r < H; r += kT) rs.row_off[r] = row_runs(bm, Wp, W, r, nullptr, 0, 0);
+// Runs of one bitmap row, one warp per row: lane l owns word l (+32, +64, ... for rows wider than 1024 px).  A run
+// starts where a set bit follows a clear one and ends where a set bit precedes a clear one; the k-th start of a row
+// pairs with its k-th end, so lanes can write starts and ends independently at prefix-summed positions.
+// emit == false: returns the row's run count (valid in every lane).
+template <bool kEmit>
+__device__ __forceinline__ int row_runs_warp(const uint32_t* __restrict__ bm, int Wp, int r, const RunSet& rs, int base, int cap) {
+    const int lane = threadIdx.x & 31;
+    int S = 0, E = 0;
+    uint32_t carry = 0;
+    for (int w0 = 0; w0 < Wp; w0 += 32) {
+        const int w = w0 + lane;
+        const uint32_t m = (w < Wp) ? bm[(size_t)r * Wp + w] : 0u;
+        uint32_t prev = __shfl_up_sync(0xffffffffu, m >> 31, 1);
+        if (lane == 0) prev = carry;
+        carry = __shfl_sync(0xffffffffu, m >> 31, 31);
+        const uint32_t starts = m & ~((m << 1) | prev);
+        const int ns = __popc(starts);
+        if (!kEmit) { S += ns; continue; }
+        uint32_t next = __shfl_down_sync(0xffffffffu, m & 1u, 1);
+        if (lane == 31) next = (w0 + 32 < Wp) ? (bm[(size_t)r * Wp + w0 + 32] & 1u) : 0u;
+        const uint32_t ends = m & ~((m >> 1) | (next << 31));
+        const int ne = __popc(ends);
+        int ps = ns, pe = ne;                                   // inclusive warp prefix sums
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int a = __shfl_up_sync(0xffffffffu, ps, o), b = __shfl_up_sync(0xffffffffu, pe, o);
+            if (lane >= o) { ps += a; pe += b; }
+        }
+        int ks = base + S + ps - ns, ke = base + E + pe - ne;
+        for (uint32_t t = starts; t; t &= t - 1, ++ks)
+            if (ks < cap) { rs.xs[ks] = (uint16_t)(32 * w + __ffs(t) - 1); rs.row[ks] = (uint16_t)r; }
+        for (uint32_t t = ends; t; t &= t - 1, ++ke)
+            if (ke < cap) rs.xe[ke] = (uint16_t)(32 * w + __ffs(t) - 1);
+        S += __shfl_sync(0xffffffffu, ps, 31);
+        E += __shfl_sync(0xffffffffu, pe, 31);
+    }
+    if (!kEmit) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) S += __shfl_xor_sync(0xffffffffu, S, o);
+    }
+    return S;
+}
+
+// label the runs of rows [r0, r1] of `bm` (8-connectivity; the rows outside are empty), accumulate twice the
+// cell-formula area at each root.  returns the number of runs, or -1 if they exceed the capacity.
+__device__ int label_runs(const uint32_t* bm, int H, int W, int Wp, RunSet rs, int* scratch, int cap, int r0, int r1) {
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int r = threadIdx.x; r <= H; r += kT) rs.row_off[r] = 0;
     __syncthreads();
-    const int R = scan_rows(rs.row_off, H, scratch);
+    constexpr int kWarps = kT / 32, kU = 8;                  // kU rows in flight per warp: the bitmap sits in L2 / HBM
+    if (Wp <= 32) {
+        for (int rb = r0 + wid * kU; rb <= r1; rb += kWarps * kU) {
+            uint32_t m[kU];
+#pragma unroll
+            for (int u = 0; u < kU; ++u) m[u] = (rb + u <= r1 && lane < Wp) ? bm[(size_t)(rb + u) * Wp + lane] : 0u;
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                uint32_t prev = __shfl_up_sync(0xffffffffu, m[u] >> 31, 1);
+                if (lane == 0) prev = 0u;
+                const int c = __reduce_add_sync(0xffffffffu, __popc(m[u] & ~((m[u] << 1) | prev)));
+                if (lane == 0 && rb + u <= r1) rs.row_off[rb + u] = c;
+            }
+        }
+    } else {
+        for (int r = r0 + wid; r <= r1; r += kWarps) {
+            const int c = row_runs_warp<false>(bm, Wp, r, rs, 0, 0);
+            if (lane == 0) rs.row_off[r] = c;
+        }
+    }
+    __syncthreads();
+    const int R = scan_rows(rs.row_off + r0, r1 - r0 + 1, scratch);     // rows outside [r0, r1] hold no runs
     if (R > cap) return -1;
-    for (int r = threadIdx.x; r < H; r += kT) row_runs(bm, Wp, W, r, &rs, rs.row_off[r], cap);
+    if (Wp <= 32) {
+        for (int rb = r0 + wid * kU; rb <= r1; rb += kWarps * kU) {
+            uint32_t m[kU];
+#pragma unroll
+            for (int u = 0; u < kU; ++u) m[u] = (rb + u <= r1 && lane < Wp) ? bm[(size_t)(rb + u) * Wp + lane] : 0u;
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                const int r = rb + u;
+                if (r > r1) break;
+                uint32_t prev = __shfl_up_sync(0xffffffffu, m[u] >> 31, 1);
+                if (lane == 0) prev = 0u;
+                uint32_t next = __shfl_down_sync(0xffffffffu, m[u] & 1u, 1);
+                if (lane == 31) next = 0u;
+                const uint32_t starts = m[u] & ~((m[u] << 1) | prev), ends = m[u] & ~((m[u] >> 1) | (next << 31));
+                if (!__any_sync(0xffffffffu, starts | ends)) continue;
+                const int ns = __popc(starts), ne = __popc(ends);
+                int ps = ns, pe = ne;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int a = __shfl_up_sync(0xffffffffu, ps, o), b = __shfl_up_sync(0xffffffffu, pe, o);
+                    if (lane >= o) { ps += a; pe += b; }
+                }
+                const int base = rs.row_off[r];
+                int ks = base + ps - ns, ke = base + pe - ne;
+                for (uint32_t t = starts; t; t &= t - 1, ++ks)
+                    if (ks < cap) { rs.xs[ks] = (uint16_t)(32 * lane + __ffs(t) - 1); rs.row[ks] = (uint16_t)r; }
+                for (uint32_t t = ends; t; t &= t - 1, ++ke)
+                    if (ke < cap) rs.xe[ke] = (uint16_t)(32 * lane + __ffs(t) - 1);
+            }
+        }
+    } else {
+        for (int r = r0 + wid; r <= r1; r += kWarps) row_runs_warp<true>(bm, Wp, r, rs, rs.row_off[r], cap);
+    }
     for (int i = threadIdx.x; i < R; i += kT) { rs.parent[i] = i; rs.area2[i] = 0; }
     __syncthreads();
     for (int i = threadIdx.x; i < R; i += kT) {
@@ -242,6 +343,7 @@ __device__ void calipers_box(const HullBuf& hb, int n, int* ext /*[4] smem*/, fl
         }
     }
     __syncthreads();
+    KB_T(8);
     if (tid != 0) return;
     if (n == 1) {
         for (int k = 0; k < 4; ++k) { out8[2 * k] = px[0]; out8[2 * k + 1] = py[0]; }
@@ -267,52 +369,54 @@ __device__ void calipers_box(const HullBuf& hb, int n, int* ext /*[4] smem*/, fl
             }
         }
         float base_a = orientation, base_b = 0.f;
-        int seq[4] = {bottom, right, top, left};
-        // the four calipers' current edge (vx, vy, inv) and point (px, py) live in registers; only the caliper
-        // that advances reloads from shared memory
-        float evx[4], evy[4], einv[4], ppx[4], ppy[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            evx[k] = hb.vx[seq[k]]; evy[k] = hb.vy[seq[k]]; einv[k] = hb.inv[seq[k]];
-            ppx[k] = px[seq[k]]; ppy[k] = py[seq[k]];
-        }
+        // the four calipers (0 bottom, 1 right, 2 top, 3 left): current vertex index, its edge (vx, vy, 1/len) and its
+        // coordinates, all in scalar registers; only the caliper that advances reloads from shared memory
+        int s0 = bottom, s1 = right, s2 = top, s3 = left;
+        float vx0 = hb.vx[s0], vy0 = hb.vy[s0], iv0 = hb.inv[s0], px0 = px[s0], py0 = py[s0];
+        float vx1 = hb.vx[s1], vy1 = hb.vy[s1], iv1 = hb.inv[s1], px1 = px[s1], py1 = py[s1];
+        float vx2 = hb.vx[s2], vy2 = hb.vy[s2], iv2 = hb.inv[s2], px2 = px[s2], py2 = py[s2];
+        float vx3 = hb.vx[s3], vy3 = hb.vy[s3], iv3 = hb.inv[s3], px3 = px[s3], py3 = py[s3];
         float minarea = 3.402823466e+38f;
         int b_left = 0, b_bottom = 0; float b_a = 0, b_w = 0, b_b = 0, b_h = 0;
         for (int k = 0; k < n; ++k) {
-            const float dp0 = __fadd_rn(__fmul_rn(base_a, evx[0]), __fmul_rn(base_b, evy[0]));
-            const float dp1 = __fadd_rn(__fmul_rn(-base_b, evx[1]), __fmul_rn(base_a, evy[1]));
-            const float dp2 = __fsub_rn(__fmul_rn(-base_a, evx[2]), __fmul_rn(base_b, evy[2]));
-            const float dp3 = __fsub_rn(__fmul_rn(base_b, evx[3]), __fmul_rn(base_a, evy[3]));
-            float maxcos = __fmul_rn(dp0, einv[0]);
+            const float dp0 = __fadd_rn(__fmul_rn(base_a, vx0), __fmul_rn(base_b, vy0));
+            const float dp1 = __fadd_rn(__fmul_rn(-base_b, vx1), __fmul_rn(base_a, vy1));
+            const float dp2 = __fsub_rn(__fmul_rn(-base_a, vx2), __fmul_rn(base_b, vy2));
+            const float dp3 = __fsub_rn(__fmul_rn(base_b, vx3), __fmul_rn(base_a, vy3));
+            float maxcos = __fmul_rn(dp0, iv0);
             int main_el = 0;
-            const float c1 = __fmul_rn(dp1, einv[1]); if (c1 > maxcos) { main_el = 1; maxcos = c1; }
-            const float c2 = __fmul_rn(dp2, einv[2]); if (c2 > maxcos) { main_el = 2; maxcos = c2; }
-            const float c3 = __fmul_rn(dp3, einv[3]); if (c3 > maxcos) { main_el = 3; maxcos = c3; }
-            float lvx = evx[0], lvy = evy[0], linv = einv[0];
-            if (main_el == 1) { lvx = evx[1]; lvy = evy[1]; linv = einv[1]; }
-            else if (main_el == 2) { lvx = evx[2]; lvy = evy[2]; linv = einv[2]; }
-            else if (main_el == 3) { lvx = evx[3]; lvy = evy[3]; linv = einv[3]; }
-            const float lead_x = __fmul_rn(lvx, linv), lead_y = __fmul_rn(lvy, linv);
-            if (main_el == 0) { base_a = lead_x; base_b = lead_y; }
-            else if (main_el == 1) { base_a = lead_y; base_b = -lead_x; }
-            else if (main_el == 2) { base_a = -lead_x; base_b = -lead_y; }
-            else { base_a = -lead_y; base_b = lead_x; }
-            // advance that caliper and reload its edge / point
+            const float c1 = __fmul_rn(dp1, iv1); if (c1 > maxcos) { main_el = 1; maxcos = c1; }
+            const float c2 = __fmul_rn(dp2, iv2); if (c2 > maxcos) { main_el = 2; maxcos = c2; }
+            const float c3 = __fmul_rn(dp3, iv3); if (c3 > maxcos) { main_el = 3; maxcos = c3; }
             int nx;
-#pragma unroll
-            for (int m = 0; m < 4; ++m)
-                if (m == main_el) {
-                    nx = (seq[m] + 1 == n) ? 0 : seq[m] + 1;
-                    seq[m] = nx;
-                    evx[m] = hb.vx[nx]; evy[m] = hb.vy[nx]; einv[m] = hb.inv[nx]; ppx[m] = px[nx]; ppy[m] = py[nx];
-                }
-            float dx = __fsub_rn(ppx[1], ppx[3]), dy = __fsub_rn(ppy[1], ppy[3]);
+            if (main_el == 0) {
+                const float lx = __fmul_rn(vx0, iv0), ly = __fmul_rn(vy0, iv0);
+                base_a = lx; base_b = ly;
+                nx = (s0 + 1 == n) ? 0 : s0 + 1; s0 = nx;
+                vx0 = hb.vx[nx]; vy0 = hb.vy[nx]; iv0 = hb.inv[nx]; px0 = px[nx]; py0 = py[nx];
+            } else if (main_el == 1) {
+                const float lx = __fmul_rn(vx1, iv1), ly = __fmul_rn(vy1, iv1);
+                base_a = ly; base_b = -lx;
+                nx = (s1 + 1 == n) ? 0 : s1 + 1; s1 = nx;
+                vx1 = hb.vx[nx]; vy1 = hb.vy[nx]; iv1 = hb.inv[nx]; px1 = px[nx]; py1 = py[nx];
+            } else if (main_el == 2) {
+                const float lx = __fmul_rn(vx2, iv2), ly = __fmul_rn(vy2, iv2);
+                base_a = -lx; base_b = -ly;
+                nx = (s2 + 1 == n) ? 0 : s2 + 1; s2 = nx;
+                vx2 = hb.vx[nx]; vy2 = hb.vy[nx]; iv2 = hb.inv[nx]; px2 = px[nx]; py2 = py[nx];
+            } else {
+                const float lx = __fmul_rn(vx3, iv3), ly = __fmul_rn(vy3, iv3);
+                base_a = -ly; base_b = lx;
+                nx = (s3 + 1 == n) ? 0 : s3 + 1; s3 = nx;
+                vx3 = hb.vx[nx]; vy3 = hb.vy[nx]; iv3 = hb.inv[nx]; px3 = px[nx]; py3 = py[nx];
+            }
+            float dx = __fsub_rn(px1, px3), dy = __fsub_rn(py1, py3);
             const float width = __fadd_rn(__fmul_rn(dx, base_a), __fmul_rn(dy, base_b));
-            dx = __fsub_rn(ppx[2], ppx[0]); dy = __fsub_rn(ppy[2], ppy[0]);
+            dx = __fsub_rn(px2, px0); dy = __fsub_rn(py2, py0);
             const float height = __fadd_rn(__fmul_rn(-dx, base_b), __fmul_rn(dy, base_a));
             const float area = __fmul_rn(width, height);
             if (area <= minarea) {
-                minarea = area; b_left = seq[3]; b_a = base_a; b_w = width; b_b = base_b; b_h = height; b_bottom = seq[0];
+                minarea = area; b_left = s3; b_a = base_a; b_w = width; b_b = base_b; b_h = height; b_bottom = s0;
             }
         }
         const float A1 = b_a, B1 = b_b, A2 = -b_b, B2 = b_a;
@@ -349,7 +453,7 @@ __device__ void calipers_box(const HullBuf& hb, int n, int* ext /*[4] smem*/, fl
 __device__ bool component_rect(const RunSet& rs, int R, int root, int H, int* rowL, int* rowR, const HullBuf& hb,
                                int* counts, float* out8) {
     const int tid = threadIdx.x;
-    if (tid == 0) { counts[0] = 0; counts[1] = 0; counts[2] = 0x7fffffff; counts[3] = -1; counts[7] = 0; }
+    if (tid == 0) { counts[0] = 0; counts[1] = 0; counts[2] = 0x7fffffff; counts[3] = -1; }
     for (int r = tid; r < H; r += kT) { rowL[r] = 0x7fffffff; rowR[r] = -1; }
     __syncthreads();
     for (int i = tid; i < R; i += kT)
@@ -360,16 +464,53 @@ __device__ bool component_rect(const RunSet& rs, int R, int root, int H, int* ro
         }
     __syncthreads();
     const int rmin = counts[2], rmax = counts[3];      // a connected component occupies every row in between
+    KB_T(4);
+    const int nrows = rmax - rmin + 1;
+    // Candidates of the two chains are the per-row extremes.  A candidate that lies on or inside ANY chord between two
+    // other candidates of its chain is not a strict hull vertex, so a cheap parallel sieve (chords to the rows
+    // +-1, 2, 4, ... 32 away) removes most of them exactly; the survivors are compacted in row order and the
+    // monotone-chain stack -- the only sequential step -- runs over those, in place, one thread per chain.
+    int* keep = rs.row_off;                            // [H+1] ints, free from here on: low half right, high half left
+    for (int r = tid; r < H + 1; r += kT) keep[r] = 0;
+    __syncthreads();
+    for (int it = tid; it < 2 * nrows; it += kT) {
+        const int side = it >= nrows;                  // 0 right chain, 1 left chain
+        const int r = rmin + (side ? it - nrows : it);
+        const int* src = side ? rowL : rowR;
+        const int xi = src[r];
+        bool kp = true;
+        if (r != rmin && r != rmax) {
+#pragma unroll
+            for (int d = 1; d <= 32; d <<= 1) {
+                const int a = max(r - d, rmin), c = min(r + d, rmax);
+                const int cr = (xi - src[a]) * (c - r) - (r - a) * (src[c] - xi);
+                kp &= side ? (cr < 0) : (cr > 0);      // same sign test as the stack's pop condition below
+            }
+        }
+        if (kp) atomicAdd(&keep[r - rmin], side ? 0x10000 : 1);
+    }
+    __syncthreads();
+    KB_T(5);
+    const int packed = scan_rows(keep, nrows, counts + 8);        // exclusive scan of both survivor counts at once
+    const int sr_ = packed & 0xffff, sl_ = packed >> 16;
+    for (int k = tid; k < nrows; k += kT) {
+        const int before = keep[k], after = keep[k + 1];
+        const int r = rmin + k;
+        if ((after & 0xffff) != (before & 0xffff)) { hb.rx[before & 0xffff] = (int16_t)rowR[r]; hb.ry[before & 0xffff] = (int16_t)r; }
+        if ((after >> 16) != (before >> 16)) { hb.lx[before >> 16] = (int16_t)rowL[r]; hb.ly[before >> 16] = (int16_t)r; }
+    }
+    __syncthreads();
+    KB_T(6);
     if (tid == 0 || tid == 32) {
-        // tid 0: right chain, tid 32: left chain, both top -> bottom; pop while the turn is not strictly convex.
-        // (ax,ay) / (bx,by) mirror the two topmost stack entries so that a push costs no shared-memory read.
+        // tid 0: right chain, tid 32: left chain, top -> bottom; pop while the turn is not strictly convex.  The stack
+        // is written over the survivor list itself (it never gets ahead of the read position); (ax,ay) / (bx,by)
+        // mirror its two topmost entries so that a push costs no shared-memory read.
         const bool right = tid == 0;
         int16_t* X = right ? hb.rx : hb.lx; int16_t* Y = right ? hb.ry : hb.ly;
-        const int* src = right ? rowR : rowL;
+        const int ns = right ? sr_ : sl_;
         int n = 0, ax = 0, ay = 0, bx = 0, by = 0;
-        bool ok = true;
-        for (int r = rmin; r <= rmax; ++r) {
-            const int cx = src[r], cy = r;
+        for (int k = 0; k < ns; ++k) {
+            const int cx = X[k], cy = Y[k];
             while (n >= 2) {
                 const int cr = (bx - ax) * (cy - by) - (by - ay) * (cx - bx);
                 if (right ? (cr <= 0) : (cr >= 0)) {
@@ -377,15 +518,13 @@ __device__ bool component_rect(const RunSet& rs, int R, int root, int H, int* ro
                     if (n >= 2) { ax = X[n - 2]; ay = Y[n - 2]; }
                 } else break;
             }
-            if (n >= kChainCap) { ok = false; break; }
             X[n] = (int16_t)cx; Y[n] = (int16_t)cy; ++n;
             ax = bx; ay = by; bx = cx; by = cy;
         }
         counts[right ? 0 : 1] = n;
-        if (!ok) counts[7] = 1;
     }
     __syncthreads();
-    if (counts[7]) return false;
+    if (counts[0] + counts[1] > kHullCap) return false;
     const int nr = counts[0], nl = counts[1];
     // cyclic order: right chain downward, then left chain upward (dropping duplicated end points)
     const bool dup_bottom = hb.lx[nl - 1] == hb.rx[nr - 1] && hb.ly[nl - 1] == hb.ry[nr - 1];
@@ -450,36 +589,51 @@ __device__ bool component_rect(const RunSet& rs, int R, int root, int H, int* ro
         __syncthreads();
     }
     if (n == 2 && hb.hx[0] == hb.hx[1] && hb.hy[0] == hb.hy[1]) n = 1;
+    KB_T(7);
     calipers_box(hb, n, counts, out8);
     __syncthreads();
+    KB_T(9);
+#ifdef TDOD_KB_TIMING
+    if (threadIdx.x == 0 && blockIdx.x < 8192) { g_kb_t[blockIdx.x * 16 + 10] = n; g_kb_t[blockIdx.x * 16 + 11] = nrows; g_kb_t[blockIdx.x * 16 + 12] = R; }
+#endif
     return true;
 }
 
 struct Smem {
-    uint32_t* bmA; uint32_t* bmB;
+    uint32_t* bmA; uint32_t* bmB;     // exact passes only: the mask's bitmap and the flood-fill result
     RunSet rs;
     int* rowL; int* rowR;
     HullBuf hb;
-    int* scratch;     // [kT/32 + 24]
+    int* scratch;                     // [2*kT/32 + 48]
     float* out8;
 };
 
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
 
+// Shared-memory carve-up.  The hull buffers alias the run arrays: once the selected component's per-row extremes are
+// in rowL/rowR the runs are dead (when the runs live in a global workspace slot the region simply holds the hull).
 __host__ __device__ inline size_t smem_layout(int H, int Wp, bool two_bitmaps, Smem* s, unsigned char* base) {
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off = align16(off + bytes); return o; };
-    const size_t o_bmA = take((size_t)H * Wp * 4);
+    const size_t o_bmA = two_bitmaps ? take((size_t)H * Wp * 4) : 0;
     const size_t o_bmB = two_bitmaps ? take((size_t)H * Wp * 4) : 0;
-    const size_t o_xs = take(kRunCap * 2), o_xe = take(kRunCap * 2), o_row = take(kRunCap * 2);
-    const size_t o_par = take(kRunCap * 4), o_area = take(kRunCap * 4), o_roff = take((size_t)(H + 1) * 4);
+    const size_t o_roff = take((size_t)(H + 1) * 4);
     const size_t o_rowL = take((size_t)H * 4), o_rowR = take((size_t)H * 4);
-    const size_t o_rx = take(kChainCap * 2), o_ry = take(kChainCap * 2), o_lx = take(kChainCap * 2), o_ly = take(kChainCap * 2);
+    const size_t o_scr = take((2 * (kT / 32) + 48) * 4), o_out = take(8 * 4);
+    const size_t region = off;
+    // view 1: runs
+    const size_t o_xs = take(kRunCap * 2), o_xe = take(kRunCap * 2), o_row = take(kRunCap * 2);
+    const size_t o_par = take(kRunCap * 4), o_area = take(kRunCap * 4);
+    const size_t end_runs = off;
+    // view 2: hull (chain candidates are at most one per row and side; the hull itself at most kHullCap vertices)
+    off = region;
+    const size_t o_rx = take((size_t)H * 2), o_ry = take((size_t)H * 2), o_lx = take((size_t)H * 2), o_ly = take((size_t)H * 2);
     const size_t hn = (size_t)kHullCap;
     const size_t o_hx = take(hn * 4), o_hy = take(hn * 4), o_vx = take(hn * 4), o_vy = take(hn * 4), o_inv = take(hn * 4);
-    const size_t o_scr = take((kT / 32 + 32) * 4), o_out = take(8 * 4);
+    const size_t end_hull = off;
+    off = end_runs > end_hull ? end_runs : end_hull;
     if (s) {
-        s->bmA = (uint32_t*)(base + o_bmA); s->bmB = two_bitmaps ? (uint32_t*)(base + o_bmB) : nullptr;
+        s->bmA = two_bitmaps ? (uint32_t*)(base + o_bmA) : nullptr; s->bmB = two_bitmaps ? (uint32_t*)(base + o_bmB) : nullptr;
         s->rs.xs = (uint16_t*)(base + o_xs); s->rs.xe = (uint16_t*)(base + o_xe); s->rs.row = (uint16_t*)(base + o_row);
         s->rs.parent = (int*)(base + o_par); s->rs.area2 = (int*)(base + o_area); s->rs.row_off = (int*)(base + o_roff);
         s->rowL = (int*)(base + o_rowL); s->rowR = (int*)(base + o_rowR);
@@ -606,12 +760,17 @@ __host__ __device__ inline int64_t run_cap_global(int H, int W) { return (int64_
 __host__ __device__ inline size_t slot_bytes(int H, int W) { return align16((size_t)run_cap_global(H, W) * 14 + 64); }
 constexpr int kSlots = 32;        // CTAs (and workspace slots) of the overflow pass
 
-// kExact: fill holes before labelling.  kGlobal: the run arrays live in a workspace slot (masks with more runs than
-// shared memory holds -- speckle noise); the CTA then walks every mask whose state is 3.
+// Workspace: [bitmap n*H*Wp words][rowrange n*2 ints][kSlots run-set slots for the overflow pass]
+__host__ __device__ inline size_t ws_bitmap_bytes(int64_t n, int H, int W) { return align16((size_t)n * H * ((W + 31) >> 5) * 4); }
+__host__ __device__ inline size_t ws_range_bytes(int64_t n) { return align16((size_t)n * 8); }
+
+// kExact: fill holes before labelling (bitmap staged in shared memory).  kGlobal: the run arrays live in a workspace
+// slot (masks with more runs than shared memory holds -- speckle noise).  Pass 1 (neither) launches one CTA per mask;
+// the other two are persistent and walk the state bytes: 2 = ambiguous without hole filling, 3 = run overflow.
 template <bool kExact, bool kGlobal>
-__global__ void __launch_bounds__(kT, kExact ? 1 : 2) mask_rect_kernel(const uint8_t* __restrict__ masks, int64_t n_masks, int H, int W,
-                                                          float* __restrict__ out_rects, uint8_t* __restrict__ out_has,
-                                                          unsigned char* __restrict__ ws) {
+__global__ void __launch_bounds__(kT, kExact ? 1 : 4) rect_kernel(const uint32_t* __restrict__ bitmap, const int* __restrict__ rowrange,
+                                                                  int64_t n_masks, int H, int W, float* __restrict__ out_rects,
+                                                                  uint8_t* __restrict__ out_has, unsigned char* __restrict__ slots) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int Wp = (W + 31) >> 5;
     Smem s;
@@ -619,7 +778,7 @@ __global__ void __launch_bounds__(kT, kExact ? 1 : 2) mask_rect_kernel(const uin
     int cap = kRunCap;
     if (kGlobal) {
         const int64_t c = run_cap_global(H, W);
-        unsigned char* b = ws + (size_t)blockIdx.x * slot_bytes(H, W);
+        unsigned char* b = slots + (size_t)blockIdx.x * slot_bytes(H, W);
         s.rs.parent = (int*)b; s.rs.area2 = (int*)(b + 4 * c);
         s.rs.xs = (uint16_t*)(b + 8 * c); s.rs.xe = (uint16_t*)(b + 10 * c); s.rs.row = (uint16_t*)(b + 12 * c);
         cap = (int)c;
@@ -627,14 +786,18 @@ __global__ void __launch_bounds__(kT, kExact ? 1 : 2) mask_rect_kernel(const uin
     for (int64_t mi = blockIdx.x; mi < n_masks; mi += gridDim.x) {
         __syncthreads();                             // previous mask's shared state is dead
         const int state = out_has[mi];
-        if (kGlobal && state != 3) continue;         // overflow pass: only masks the shared-memory passes gave up on
-        if (!kGlobal && kExact && state != 2) continue;   // pass 2 only revisits the masks pass 1 could not decide
-        for (int i = threadIdx.x; i < H * Wp; i += kT) s.bmA[i] = 0u;
-        __syncthreads();
-        load_pack(masks + mi * (int64_t)H * W, H, W, Wp, s.bmA);
-        __syncthreads();
-        const uint32_t* comp_bm = s.bmA;
+        if (kGlobal && state != 3) continue;
+        if (!kGlobal && kExact && state != 2) continue;
+        KB_T(0);
+        const int r0 = rowrange[2 * mi], r1 = H - 1 - rowrange[2 * mi + 1];
+        if (r0 > r1) {                               // empty mask: scorefunction.py:69-75 fallback applies
+            if (threadIdx.x == 0) out_has[mi] = 0;
+            continue;
+        }
+        const uint32_t* comp_bm = bitmap + (size_t)mi * H * Wp;
         if (kExact) {
+            for (int i = threadIdx.x; i < H * Wp; i += kT) s.bmA[i] = comp_bm[i];
+            __syncthreads();
             flood_outside(s.bmA, s.bmB, H, W, Wp, s.scratch + 30);
             const uint32_t tail = (W & 31) ? ((1u << (W & 31)) - 1u) : 0xffffffffu;
             for (int i = threadIdx.x; i < H * Wp; i += kT) {
@@ -644,17 +807,16 @@ __global__ void __launch_bounds__(kT, kExact ? 1 : 2) mask_rect_kernel(const uin
             __syncthreads();
             comp_bm = s.bmB;
         }
-        const int R = label_runs(comp_bm, H, W, Wp, s.rs, s.scratch, cap);
-        if (R == 0) {                                   // empty mask: scorefunction.py:69-75 fallback applies
-            if (threadIdx.x == 0) out_has[mi] = 0;
-            continue;
-        }
+        KB_T(1);
+        const int R = label_runs(comp_bm, H, W, Wp, s.rs, s.scratch, cap, r0, r1);
+        KB_T(2);
         if (R < 0) {                                    // more runs than shared memory holds -> overflow pass
             if (threadIdx.x == 0) out_has[mi] = 3;
             continue;
         }
         bool ambiguous = false;
         const int root = select_component(s.rs, R, !kExact, s.scratch, &ambiguous);
+        KB_T(3);
         if (ambiguous) {
             if (threadIdx.x == 0) out_has[mi] = 2;
             continue;
@@ -670,7 +832,7 @@ __global__ void __launch_bounds__(kT, kExact ? 1 : 2) mask_rect_kernel(const uin
 extern "C" int64_t tdod_mask_rect_workspace_bytes(int64_t n_masks, int H, int W) {
     if (n_masks <= 0 || H <= 0 || W <= 0) return 16;
     const int64_t slots = n_masks < kSlots ? n_masks : kSlots;
-    return (int64_t)(slots * slot_bytes(H, W));
+    return (int64_t)(ws_bitmap_bytes(n_masks, H, W) + ws_range_bytes(n_masks) + slots * slot_bytes(H, W));
 }
 
 extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int W, float* out_rects,
@@ -681,30 +843,43 @@ extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int 
     if (H > 32767 || W > 32767) return tdod_fail(TDOD_ERANGE, "tdod_mask_rect: image larger than 32767");
     if (!workspace || workspace_bytes < tdod_mask_rect_workspace_bytes(n_masks, H, W))
         return tdod_fail(TDOD_EINVAL, "tdod_mask_rect: workspace smaller than tdod_mask_rect_workspace_bytes()");
+    if ((reinterpret_cast<uintptr_t>(workspace) & 15) != 0)
+        return tdod_fail(TDOD_EINVAL, "tdod_mask_rect: workspace must be 16-byte aligned");
     const int Wp = (W + 31) >> 5;
     const size_t smem1 = smem_layout(H, Wp, false, nullptr, nullptr);
     const size_t smem2 = smem_layout(H, Wp, true, nullptr, nullptr);
     if (smem2 > 227 * 1024)
-        return tdod_fail(TDOD_ERANGE, "tdod_mask_rect: mask does not fit in shared memory (H*ceil(W/32)*8 bytes + 60 KB <= 227 KB)");
+        return tdod_fail(TDOD_ERANGE, "tdod_mask_rect: mask does not fit in shared memory (H*ceil(W/32)*8 bytes + 40 KB <= 227 KB)");
     cudaStream_t st = (cudaStream_t)stream;
-    cudaError_t e = cudaFuncSetAttribute(mask_rect_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1);
+    unsigned char* wsb = (unsigned char*)workspace;
+    uint32_t* bitmap = (uint32_t*)wsb;
+    int* rowrange = (int*)(wsb + ws_bitmap_bytes(n_masks, H, W));
+    unsigned char* slots = wsb + ws_bitmap_bytes(n_masks, H, W) + ws_range_bytes(n_masks);
+    cudaError_t e = cudaFuncSetAttribute(rect_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1);
     if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(mask_rect_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+    e = cudaFuncSetAttribute(rect_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
     if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(mask_rect_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+    e = cudaFuncSetAttribute(rect_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
     if (e != cudaSuccess) return (int)e;
-    // the state byte doubles as the work list of the later passes: every mask starts undecided
+    // the state byte doubles as the work list of the later passes: every mask starts undecided;
+    // rowrange = {0x7f7f7f7f, 0x7f7f7f7f} is "no row seen" for the two atomicMin's of the pack kernel
     e = cudaMemsetAsync(out_has_rect, 0xff, (size_t)n_masks, st);
     if (e != cudaSuccess) return (int)e;
-    mask_rect_kernel<false, false><<<(unsigned)n_masks, kT, smem1, st>>>(masks, n_masks, H, W, out_rects, out_has_rect, nullptr);
+    e = cudaMemsetAsync(rowrange, 0x7f, (size_t)n_masks * 8, st);
+    if (e != cudaSuccess) return (int)e;
+    const int tiles_per_mask = (H + kPackRows - 1) / kPackRows;
+    const int64_t n_tiles = n_masks * tiles_per_mask;
+    const size_t pk_smem = (size_t)(((int64_t)kPackRows * W + 30) / 16 + 8) * 2;
+    const unsigned pk_grid = (unsigned)(n_tiles < 148 * 8 * 4 ? n_tiles : 148 * 8 * 4);
+    pack_kernel<<<pk_grid, kPackT, pk_smem, st>>>(masks, n_masks, H, W, Wp, bitmap, rowrange, tiles_per_mask);
     TDOD_CHECK_LAUNCH();
-    // passes 2 and 3 are persistent: a handful of CTAs walk the state bytes and almost always find nothing to do
-    mask_rect_kernel<true, false><<<(unsigned)(n_masks < 148 ? n_masks : 148), kT, smem2, st>>>(masks, n_masks, H, W, out_rects,
-                                                                                          out_has_rect, nullptr);
+    rect_kernel<false, false><<<(unsigned)n_masks, kT, smem1, st>>>(bitmap, rowrange, n_masks, H, W, out_rects, out_has_rect, nullptr);
     TDOD_CHECK_LAUNCH();
-    const unsigned slots = (unsigned)(n_masks < kSlots ? n_masks : kSlots);
-    mask_rect_kernel<true, true><<<slots, kT, smem2, st>>>(masks, n_masks, H, W, out_rects, out_has_rect,
-                                                           (unsigned char*)workspace);
+    rect_kernel<true, false><<<(unsigned)(n_masks < 148 ? n_masks : 148), kT, smem2, st>>>(bitmap, rowrange, n_masks, H, W, out_rects,
+                                                                                         out_has_rect, nullptr);
+    TDOD_CHECK_LAUNCH();
+    const unsigned nslots = (unsigned)(n_masks < kSlots ? n_masks : kSlots);
+    rect_kernel<true, true><<<nslots, kT, smem2, st>>>(bitmap, rowrange, n_masks, H, W, out_rects, out_has_rect, slots);
     TDOD_CHECK_LAUNCH();
     return TDOD_OK;
 }

@@ -114,9 +114,10 @@ def select(batch, n_prop, seed=0, noise=None, yaw_idx=None, rot=None, sample_ids
     return s
 
 
-# kernels launched by one `select` call (K-A: backproject, hypotheses, count, select; yaw table; K-B: 3 passes; K-C)
-LAUNCHES_PER_SELECT = 9
-LAUNCHES_PER_SELECT_NO_GROUND = 4
+# kernels launched by one `select` call (K-A: backproject, hypotheses, count, select; yaw table; K-B: pack + 3 rectangle
+# passes; K-C)
+LAUNCHES_PER_SELECT = 10
+LAUNCHES_PER_SELECT_NO_GROUND = 5
 
 
 class Pipeline:
