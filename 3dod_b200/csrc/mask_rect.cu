@@ -33,8 +33,8 @@ constexpr int kPackRows = 32;    // mask rows per pack tile
 
 // phase timers for tools/kb_phases.cu (compiled out of the library)
 #ifdef TDOD_KB_TIMING
-__device__ long long g_kb_t[16 * 8192];
-#define KB_T(k) do { if (threadIdx.x == 0 && blockIdx.x < 8192) g_kb_t[blockIdx.x * 16 + (k)] = clock64(); } while (0)
+__device__ long long g_kb_t[32 * 8192];
+#define KB_T(k) do { if (threadIdx.x == 0 && blockIdx.x < 8192) g_kb_t[blockIdx.x * 32 + (k)] = clock64(); } while (0)
 #else
 #define KB_T(k) do { } while (0)
 #endif
@@ -68,7 +68,7 @@ __device__ __forceinline__ uint32_t nz_bits16(const uint4 v) {
 // with plain half-word stores; every output word is then a 32-bit window of that stream (funnel shift).
 __global__ void __launch_bounds__(kPackT, 8) pack_kernel(const uint8_t* __restrict__ masks, int64_t n_masks, int H, int W, int Wp,
                                                         uint32_t* __restrict__ bitmap, int* __restrict__ rowrange,
-                                                        int tiles_per_mask) {
+                                                        int* __restrict__ lists, int tiles_per_mask) {
     extern __shared__ __align__(16) unsigned char pk_raw[];
     uint16_t* sb16 = reinterpret_cast<uint16_t*>(pk_raw);
     const uint32_t* sb32 = reinterpret_cast<const uint32_t*>(pk_raw);
@@ -79,6 +79,7 @@ __global__ void __launch_bounds__(kPackT, 8) pack_kernel(const uint8_t* __restri
     const uint4* v = reinterpret_cast<const uint4*>(base - mis);
     const int64_t HW = (int64_t)H * W;
     const int64_t n_tiles = n_masks * tiles_per_mask;
+    if (blockIdx.x == 0 && tid < 4) lists[tid] = 0;       // work-list counters of the later passes
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const int64_t m = tile / tiles_per_mask;
         const int r0 = (int)(tile - m * tiles_per_mask) * kPackRows, r1 = min(H, r0 + kPackRows);
@@ -235,7 +236,9 @@ __device__ int label_runs(const uint32_t* bm, int H, int W, int Wp, RunSet rs, i
         }
     }
     __syncthreads();
-    const int R = scan_rows(rs.row_off + r0, r1 - r0 + 1, scratch);     // rows outside [r0, r1] hold no runs
+    KB_T(16);
+    const int R = scan_rows(rs.row_off + r0, r1 - r0 + 1, scratch);
+    KB_T(17);     // rows outside [r0, r1] hold no runs
     if (R > cap) return -1;
     if (Wp <= 32) {
         for (int rb = r0 + wid * kU; rb <= r1; rb += kWarps * kU) {
@@ -272,6 +275,7 @@ __device__ int label_runs(const uint32_t* bm, int H, int W, int Wp, RunSet rs, i
     }
     for (int i = threadIdx.x; i < R; i += kT) { rs.parent[i] = i; rs.area2[i] = 0; }
     __syncthreads();
+    KB_T(18);
     for (int i = threadIdx.x; i < R; i += kT) {
         const int r = rs.row[i];
         if (r == 0) continue;
@@ -282,8 +286,10 @@ __device__ int label_runs(const uint32_t* bm, int H, int W, int Wp, RunSet rs, i
         }
     }
     __syncthreads();
+    KB_T(19);
     for (int i = threadIdx.x; i < R; i += kT) rs.parent[i] = uf_find(rs.parent, i);
     __syncthreads();
+    KB_T(20);
     // cell formula on pairs of overlapping runs in adjacent rows: 2*full + (#3-corner end cells)
     for (int i = threadIdx.x; i < R; i += kT) {
         const int r = rs.row[i];
@@ -594,7 +600,7 @@ __device__ bool component_rect(const RunSet& rs, int R, int root, int H, int* ro
     __syncthreads();
     KB_T(9);
 #ifdef TDOD_KB_TIMING
-    if (threadIdx.x == 0 && blockIdx.x < 8192) { g_kb_t[blockIdx.x * 16 + 10] = n; g_kb_t[blockIdx.x * 16 + 11] = nrows; g_kb_t[blockIdx.x * 16 + 12] = R; }
+    if (threadIdx.x == 0 && blockIdx.x < 8192) { g_kb_t[blockIdx.x * 32 + 10] = n; g_kb_t[blockIdx.x * 32 + 11] = nrows; g_kb_t[blockIdx.x * 32 + 12] = R; }
 #endif
     return true;
 }
@@ -647,8 +653,8 @@ __host__ __device__ inline size_t smem_layout(int H, int Wp, bool two_bitmaps, S
 }
 
 // pick the component with the largest area2 (ties: the larger root index = later first pixel in raster order).
-// In bounds mode also reports whether any OTHER component's bounding-box area could reach the winner's
-// hole-free area (then hole filling could change the answer and pass 2 must decide).
+// In bounds mode also reports whether any OTHER component's hole-filled area could reach the winner's hole-free
+// area (then hole filling could change the answer and pass 2 must decide).
 __device__ int select_component(const RunSet& rs, int R, bool bounds_mode, int* scratch, bool* ambiguous) {
     // scratch[0] = best key hi (area2), scratch[1] = best root, via a two-step atomicMax on a packed 64-bit key
     unsigned long long* key = reinterpret_cast<unsigned long long*>(scratch + 20);   // 8-byte aligned slot
@@ -665,16 +671,25 @@ __device__ int select_component(const RunSet& rs, int R, bool bounds_mode, int* 
         // rowL/rowR-free scratch is not available here, so scan: a root's bbox is reduced by the threads that
         // own its runs through atomics on packed words stored in area2 of its FIRST non-root run ... too
         // intricate; simple exact alternative: for every non-best root, one thread walks all runs once.
+        // Upper bound on a rival's hole-filled area: filling holes never leaves the per-row extent [L_r, R_r] of the
+        // component, and the cell formula is monotone in the pixel set, so the area of the row-convexified component
+        // bounds it.  One thread per rival walks the runs (raster order) once.
         for (int i = threadIdx.x; i < R; i += kT) {
             if (rs.parent[i] != i || i == best) continue;
-            int x0 = 0x7fffffff, x1 = -1, y0 = 0x7fffffff, y1 = -1;
-            for (int j = i; j < R; ++j)
-                if (rs.parent[j] == i) {
-                    x0 = min(x0, (int)rs.xs[j]); x1 = max(x1, (int)rs.xe[j]);
-                    y0 = min(y0, (int)rs.row[j]); y1 = max(y1, (int)rs.row[j]);
-                }
-            const long long ub2 = 2ll * (x1 - x0) * (y1 - y0);
-            if (ub2 >= (long long)best_a2) atomicOr(&scratch[24], 1);
+            int pl = 0, pr = -1, cl = rs.xs[i], cr = rs.xe[i], crow = rs.row[i];
+            bool have_prev = false;
+            long long ub2 = 0;
+            for (int j = i + 1; j <= R; ++j) {
+                const bool mine = j < R && rs.parent[j] == i;
+                if (j < R && !mine) continue;
+                if (mine && (int)rs.row[j] == crow) { cl = min(cl, (int)rs.xs[j]); cr = max(cr, (int)rs.xe[j]); continue; }
+                // row `crow` is complete: pair it with the previous one
+                if (have_prev && pl <= cr && pr >= cl) ub2 += 2 * (min(cr, pr) - max(cl, pl)) + (cl != pl) + (cr != pr);
+                pl = cl; pr = cr; have_prev = true;
+                if (mine) { cl = rs.xs[j]; cr = rs.xe[j]; crow = rs.row[j]; }
+            }
+            // a rival that can at most TIE at area 0 cannot win either: ties go to the later component, which `best` is
+            if (ub2 > (long long)best_a2 || (ub2 == (long long)best_a2 && ub2 > 0)) atomicOr(&scratch[24], 1);
         }
         __syncthreads();
         *ambiguous = scratch[24] != 0;
@@ -763,6 +778,8 @@ constexpr int kSlots = 32;        // CTAs (and workspace slots) of the overflow 
 // Workspace: [bitmap n*H*Wp words][rowrange n*2 ints][kSlots run-set slots for the overflow pass]
 __host__ __device__ inline size_t ws_bitmap_bytes(int64_t n, int H, int W) { return align16((size_t)n * H * ((W + 31) >> 5) * 4); }
 __host__ __device__ inline size_t ws_range_bytes(int64_t n) { return align16((size_t)n * 8); }
+// work lists of passes 2 and 3: [count2, count3, pad, pad][list2 n ints][list3 n ints]
+__host__ __device__ inline size_t ws_list_bytes(int64_t n) { return align16(16 + (size_t)n * 8); }
 
 // kExact: fill holes before labelling (bitmap staged in shared memory).  kGlobal: the run arrays live in a workspace
 // slot (masks with more runs than shared memory holds -- speckle noise).  Pass 1 (neither) launches one CTA per mask;
@@ -770,7 +787,8 @@ __host__ __device__ inline size_t ws_range_bytes(int64_t n) { return align16((si
 template <bool kExact, bool kGlobal>
 __global__ void __launch_bounds__(kT, kExact ? 1 : 4) rect_kernel(const uint32_t* __restrict__ bitmap, const int* __restrict__ rowrange,
                                                                   int64_t n_masks, int H, int W, float* __restrict__ out_rects,
-                                                                  uint8_t* __restrict__ out_has, unsigned char* __restrict__ slots) {
+                                                                  uint8_t* __restrict__ out_has, unsigned char* __restrict__ slots,
+                                                                  int* __restrict__ lists) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int Wp = (W + 31) >> 5;
     Smem s;
@@ -783,11 +801,12 @@ __global__ void __launch_bounds__(kT, kExact ? 1 : 4) rect_kernel(const uint32_t
         s.rs.xs = (uint16_t*)(b + 8 * c); s.rs.xe = (uint16_t*)(b + 10 * c); s.rs.row = (uint16_t*)(b + 12 * c);
         cap = (int)c;
     }
-    for (int64_t mi = blockIdx.x; mi < n_masks; mi += gridDim.x) {
+    int* list2 = lists + 4;
+    int* list3 = lists + 4 + n_masks;
+    const int64_t n_work = (!kExact && !kGlobal) ? n_masks : (int64_t)lists[kGlobal ? 1 : 0];
+    for (int64_t wk = blockIdx.x; wk < n_work; wk += gridDim.x) {
         __syncthreads();                             // previous mask's shared state is dead
-        const int state = out_has[mi];
-        if (kGlobal && state != 3) continue;
-        if (!kGlobal && kExact && state != 2) continue;
+        const int64_t mi = (!kExact && !kGlobal) ? wk : (int64_t)(kGlobal ? list3 : list2)[wk];
         KB_T(0);
         const int r0 = rowrange[2 * mi], r1 = H - 1 - rowrange[2 * mi + 1];
         if (r0 > r1) {                               // empty mask: scorefunction.py:69-75 fallback applies
@@ -811,14 +830,14 @@ __global__ void __launch_bounds__(kT, kExact ? 1 : 4) rect_kernel(const uint32_t
         const int R = label_runs(comp_bm, H, W, Wp, s.rs, s.scratch, cap, r0, r1);
         KB_T(2);
         if (R < 0) {                                    // more runs than shared memory holds -> overflow pass
-            if (threadIdx.x == 0) out_has[mi] = 3;
+            if (threadIdx.x == 0) { out_has[mi] = 3; list3[atomicAdd(&lists[1], 1)] = (int)mi; }
             continue;
         }
         bool ambiguous = false;
         const int root = select_component(s.rs, R, !kExact, s.scratch, &ambiguous);
         KB_T(3);
         if (ambiguous) {
-            if (threadIdx.x == 0) out_has[mi] = 2;
+            if (threadIdx.x == 0) { out_has[mi] = 2; list2[atomicAdd(&lists[0], 1)] = (int)mi; }
             continue;
         }
         const bool ok = component_rect(s.rs, R, root, H, s.rowL, s.rowR, s.hb, s.scratch + 32, s.out8);
@@ -832,7 +851,7 @@ __global__ void __launch_bounds__(kT, kExact ? 1 : 4) rect_kernel(const uint32_t
 extern "C" int64_t tdod_mask_rect_workspace_bytes(int64_t n_masks, int H, int W) {
     if (n_masks <= 0 || H <= 0 || W <= 0) return 16;
     const int64_t slots = n_masks < kSlots ? n_masks : kSlots;
-    return (int64_t)(ws_bitmap_bytes(n_masks, H, W) + ws_range_bytes(n_masks) + slots * slot_bytes(H, W));
+    return (int64_t)(ws_bitmap_bytes(n_masks, H, W) + ws_range_bytes(n_masks) + ws_list_bytes(n_masks) + slots * slot_bytes(H, W));
 }
 
 extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int W, float* out_rects,
@@ -854,7 +873,8 @@ extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int 
     unsigned char* wsb = (unsigned char*)workspace;
     uint32_t* bitmap = (uint32_t*)wsb;
     int* rowrange = (int*)(wsb + ws_bitmap_bytes(n_masks, H, W));
-    unsigned char* slots = wsb + ws_bitmap_bytes(n_masks, H, W) + ws_range_bytes(n_masks);
+    int* lists = (int*)(wsb + ws_bitmap_bytes(n_masks, H, W) + ws_range_bytes(n_masks));
+    unsigned char* slots = wsb + ws_bitmap_bytes(n_masks, H, W) + ws_range_bytes(n_masks) + ws_list_bytes(n_masks);
     cudaError_t e = cudaFuncSetAttribute(rect_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1);
     if (e != cudaSuccess) return (int)e;
     e = cudaFuncSetAttribute(rect_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
@@ -871,15 +891,16 @@ extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int 
     const int64_t n_tiles = n_masks * tiles_per_mask;
     const size_t pk_smem = (size_t)(((int64_t)kPackRows * W + 30) / 16 + 8) * 2;
     const unsigned pk_grid = (unsigned)(n_tiles < 148 * 8 * 4 ? n_tiles : 148 * 8 * 4);
-    pack_kernel<<<pk_grid, kPackT, pk_smem, st>>>(masks, n_masks, H, W, Wp, bitmap, rowrange, tiles_per_mask);
+    pack_kernel<<<pk_grid, kPackT, pk_smem, st>>>(masks, n_masks, H, W, Wp, bitmap, rowrange, lists, tiles_per_mask);
     TDOD_CHECK_LAUNCH();
-    rect_kernel<false, false><<<(unsigned)n_masks, kT, smem1, st>>>(bitmap, rowrange, n_masks, H, W, out_rects, out_has_rect, nullptr);
+    rect_kernel<false, false><<<(unsigned)n_masks, kT, smem1, st>>>(bitmap, rowrange, n_masks, H, W, out_rects, out_has_rect, nullptr,
+                                                                 lists);
     TDOD_CHECK_LAUNCH();
     rect_kernel<true, false><<<(unsigned)(n_masks < 148 ? n_masks : 148), kT, smem2, st>>>(bitmap, rowrange, n_masks, H, W, out_rects,
-                                                                                         out_has_rect, nullptr);
+                                                                                         out_has_rect, nullptr, lists);
     TDOD_CHECK_LAUNCH();
     const unsigned nslots = (unsigned)(n_masks < kSlots ? n_masks : kSlots);
-    rect_kernel<true, true><<<nslots, kT, smem2, st>>>(bitmap, rowrange, n_masks, H, W, out_rects, out_has_rect, slots);
+    rect_kernel<true, true><<<nslots, kT, smem2, st>>>(bitmap, rowrange, n_masks, H, W, out_rects, out_has_rect, slots, lists);
     TDOD_CHECK_LAUNCH();
     return TDOD_OK;
 }

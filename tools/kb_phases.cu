@@ -34,19 +34,26 @@ int main(int argc, char** argv) {
         float ms; cudaEventElapsedTime(&ms, e0, e1);
         printf("rc=%d  %d masks  %.3f ms  (%.1f GB/s)\n", rc, N, ms, (double)h.size() / ms / 1e6);
     }
-    std::vector<long long> t(16 * 8192);
-    cudaMemcpyFromSymbol(t.data(), g_kb_t, sizeof(long long) * 16 * 8192);
+    std::vector<long long> t(32 * 8192);
+    cudaMemcpyFromSymbol(t.data(), g_kb_t, sizeof(long long) * 32 * 8192);
     const int M = N < 8192 ? N : 8192;
     const char* names[9] = {"row range", "label_runs", "select_component", "rowL/R+extent", "chain sieve", "scan+compact",
                             "stacks+assemble", "calipers pre", "calipers walk"};
     double tot = 0, acc[9] = {0};
     double hv = 0, rows = 0, runs = 0;
     for (int m = 0; m < M; ++m) {
-        for (int k = 0; k < 9; ++k) acc[k] += (double)(t[m * 16 + k + 1] - t[m * 16 + k]);
-        tot += (double)(t[m * 16 + 9] - t[m * 16]);
-        hv += t[m * 16 + 10]; rows += t[m * 16 + 11]; runs += t[m * 16 + 12];
+        for (int k = 0; k < 9; ++k) acc[k] += (double)(t[m * 32 + k + 1] - t[m * 32 + k]);
+        tot += (double)(t[m * 32 + 9] - t[m * 16]);
+        hv += t[m * 32 + 10]; rows += t[m * 32 + 11]; runs += t[m * 32 + 12];
     }
     printf("mean hull vertices %.1f, rows %.1f, runs %.1f; mean cycles per mask (CTA view) %.0f\n", hv / M, rows / M, runs / M, tot / M);
     for (int k = 0; k < 9; ++k) printf("  %-18s %9.0f cycles  %5.1f%%\n", names[k], acc[k] / M, 100 * acc[k] / tot);
+    const char* ln[6] = {"  label: count pass", "  label: scan", "  label: emit+init", "  label: union", "  label: find", "  label: area"};
+    const int a[6] = {1, 16, 17, 18, 19, 20}, b[6] = {16, 17, 18, 19, 20, 2};
+    for (int k = 0; k < 6; ++k) {
+        double d = 0;
+        for (int m = 0; m < M; ++m) d += (double)(t[m * 32 + b[k]] - t[m * 32 + a[k]]);
+        printf("  %-22s %9.0f cycles\n", ln[k], d / M);
+    }
     return 0;
 }
