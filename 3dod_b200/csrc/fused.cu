@@ -57,7 +57,9 @@ struct ObjCtx {
 };
 
 // accepted standard normals for (w,h,l) of proposal i
-__device__ __forceinline__ void draw_whl(const tdod_pss_args& a, const ObjCtx& c, int i, float& w, float& h, float& l) {
+// `xn`: Philox mode only -- the standard normal of the x draw (fourth normal of the first try's Philox block)
+__device__ __forceinline__ void draw_whl(const tdod_pss_args& a, const ObjCtx& c, int i, float& w, float& h, float& l, float& xn) {
+    xn = 0.f;
     if (a.rng_mode == TDOD_RNG_HOST) {
         const float* nz = a.noise + (size_t)c.obj * 6 * a.n_prop;
         w = scale_normal(nz[i], c.mu[0], c.sg[0]);
@@ -74,6 +76,7 @@ __device__ __forceinline__ void draw_whl(const tdod_pss_args& a, const ObjCtx& c
     for (uint32_t t = 0; t < 10001u && !(okw && okh && okl); ++t) {
         const uint4 r = ph((uint32_t)i, (uint32_t)gid, (uint32_t)(gid >> 32) ^ 0x57484Cu, t);
         const float2 n01 = box_muller(r.x, r.y), n23 = box_muller(r.z, r.w);
+        if (t == 0) xn = n23.y;
         if (!okw) { w = scale_normal(n01.x, c.mu[0], c.sg[0]); okw = !(w < TDOD_MIN_PROP_S || w > c.hi[0]); }
         if (!okh) { h = scale_normal(n01.y, c.mu[1], c.sgh);   okh = !(h < TDOD_MIN_PROP_S || h > c.hi[1]); }
         if (!okl) { l = scale_normal(n23.x, c.mu[2], c.sg[2]); okl = !(l < TDOD_MIN_PROP_S || l > c.hi[2]); }
@@ -82,7 +85,7 @@ __device__ __forceinline__ void draw_whl(const tdod_pss_args& a, const ObjCtx& c
 
 // standard normals for x,y,z and the rotation of proposal i -> q[0..2], q[6..14]
 __device__ __forceinline__ void draw_xyz_rot(const tdod_pss_args& a, const ObjCtx& c, const float* yaw, int i,
-                                             const float (&mean)[3], const float (&sd)[3], float* q) {
+                                             const float (&mean)[3], const float (&sd)[3], float xn, float* q) {
     if (a.rng_mode == TDOD_RNG_HOST) {
         const float* nz = a.noise + (size_t)c.obj * 6 * a.n_prop;
         q[0] = scale_normal(nz[3 * a.n_prop + i], mean[0], sd[0]);
@@ -101,20 +104,17 @@ __device__ __forceinline__ void draw_xyz_rot(const tdod_pss_args& a, const ObjCt
     }
     const Philox ph(a.seed);
     const uint64_t gid = (uint64_t)(a.obj_id_base + c.obj);
+    // one Philox block: two uniforms -> (y, z) normals, one -> yaw bin; the x normal came with the (w,h,l) block
     const uint4 r = ph((uint32_t)i, (uint32_t)gid, (uint32_t)(gid >> 32) ^ 0x58595Au, 0u);
     const float2 n01 = box_muller(r.x, r.y);
-    q[0] = scale_normal(n01.x, mean[0], sd[0]);
-    q[1] = scale_normal(n01.y, mean[1], sd[1]);
+    q[0] = scale_normal(xn, mean[0], sd[0]);
+    q[1] = scale_normal(n01.x, mean[1], sd[1]);
+    q[2] = scale_normal(n01.y, mean[2], sd[2]);
     if (a.yaw_table) {
-        const float2 n23 = box_muller(r.z, r.w);
-        q[2] = scale_normal(n23.x, mean[2], sd[2]);
-        const uint4 r2 = ph((uint32_t)i, (uint32_t)gid, (uint32_t)(gid >> 32) ^ 0x58595Au, 1u);
-        const int yi = (int)(r2.x % TDOD_NYAW);  // torch.randint(36, ...): u32 % 36
+        const int yi = (int)(r.z % TDOD_NYAW);  // torch.randint(36, ...): u32 % 36
 #pragma unroll
         for (int k = 0; k < 9; ++k) q[6 + k] = yaw[yi * 9 + k];
     } else {
-        const float2 n23 = box_muller(r.z, r.w);
-        q[2] = scale_normal(n23.x, mean[2], sd[2]);
         // utils.py:62-69 randn_orthobasis_torch: rows normalised, row0 = r1 x r2, row1 = r2 x row0
         float m[9];
 #pragma unroll
@@ -135,16 +135,29 @@ __device__ __forceinline__ void draw_xyz_rot(const tdod_pss_args& a, const ObjCt
     }
 }
 
-template <typename T>
-__device__ __forceinline__ T* remote(cg::cluster_group& cl, T* p, int rank) {
-    return cl.map_shared_rank(p, rank);
-}
+// The per-object reductions run over the CTAs of a cluster through DSMEM.  With one CTA per object (the common
+// case: n <= 2048 proposals) the same code runs on plain CTA barriers and local pointers.
+template <bool kCluster> struct ClusterCtx;
+template <> struct ClusterCtx<true> {
+    cg::cluster_group cl = cg::this_cluster();
+    __device__ __forceinline__ int size() { return (int)cl.num_blocks(); }
+    __device__ __forceinline__ int rank() { return (int)cl.block_rank(); }
+    __device__ __forceinline__ void sync() { cl.sync(); }
+    template <typename T> __device__ __forceinline__ T* remote(T* p, int r) { return cl.map_shared_rank(p, r); }
+};
+template <> struct ClusterCtx<false> {
+    __device__ __forceinline__ int size() { return 1; }
+    __device__ __forceinline__ int rank() { return 0; }
+    __device__ __forceinline__ void sync() { __syncthreads(); }
+    template <typename T> __device__ __forceinline__ T* remote(T* p, int) { return p; }
+};
 
+template <bool kCluster>
 __global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a, const int n_loc) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    cg::cluster_group cl = cg::this_cluster();
-    const int S = (int)cl.num_blocks();
-    const int rank = (int)cl.block_rank();
+    ClusterCtx<kCluster> cl;
+    const int S = cl.size();
+    const int rank = cl.rank();
     const int obj = (int)(blockIdx.x / S);
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
 
@@ -210,9 +223,10 @@ __global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a,
         int ix = gx < 0 ? gx + a.W : gx, iy = gy < 0 ? gy + a.H : gy;
         ix = min(max(ix, 0), a.W - 1); iy = min(max(iy, 0), a.H - 1);
         const float d = __ldg(depth + (size_t)iy * a.W + ix);
-        float x, y, zt, w, h, l;
+        float x, y, zt, w, h, l, xn;
         centre_seed(gx, gy, d, fx, cx, cy, x, y, zt);
-        draw_whl(a, c, i, w, h, l);
+        draw_whl(a, c, i, w, h, l, xn);
+        s_d[j] = xn;                                                       // parked until phase 2 reads it back
         const float z = __fadd_rn(zt, __fdiv_rn(l, 2.f));                  // proposals.py:394
         s_x[j] = x; s_y[j] = y; s_z[j] = z; s_w[j] = w; s_h[j] = h; s_l[j] = l;
         lsum[0] += (double)x; lsum[1] += (double)y; lsum[2] += (double)z;
@@ -254,7 +268,7 @@ __global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a,
 #pragma unroll
             for (int b = 0; b < 8; ++b) bins[b] = 0;
             for (int r = 0; r < S; ++r) {
-                const int* hr = remote(cl, &sh.mail.hist[pass][wid][0], r);
+                const int* hr = cl.remote(&sh.mail.hist[pass][wid][0], r);
 #pragma unroll
                 for (int b = 0; b < 8; ++b) bins[b] += hr[8 * lane + b];
             }
@@ -285,7 +299,7 @@ __global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a,
     }
     if (tid < 3) {
         int anynan = 0;
-        for (int r = 0; r < S; ++r) anynan |= *remote(cl, &sh.mail.nanflag[tid], r);
+        for (int r = 0; r < S; ++r) anynan |= *cl.remote(&sh.mail.nanflag[tid], r);
         sh.med[tid] = anynan ? CUDART_NAN_F : key2f(sh.prefix[tid]);
     }
     // mean over the cluster, then squared deviations (two-pass, fp64: torch CPU accumulates std in double)
@@ -293,7 +307,7 @@ __global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a,
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         double s = 0.0;
-        for (int r = 0; r < S; ++r) s += *remote(cl, &sh.mail.sum[k], r);
+        for (int r = 0; r < S; ++r) s += *cl.remote(&sh.mail.sum[k], r);
         mean[k] = s / (double)n;
     }
     double lm2[3] = {0.0, 0.0, 0.0};
@@ -317,7 +331,7 @@ __global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a,
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
             double s = 0.0;
-            for (int r = 0; r < S; ++r) s += *remote(cl, &sh.mail.m2[k], r);
+            for (int r = 0; r < S; ++r) s += *cl.remote(&sh.mail.m2[k], r);
             const float sd = (float)sqrt(s / (double)(n - 1));              // torch.std: unbiased
             smean[k] = __fadd_rn(__fmul_rn(coef_a[k], sh.med[k]), coef_b[k]);   // lin_fun, proposals.py:16-18
             ssd[k] = __fmul_rn(sd, coef_s[k]);
@@ -344,7 +358,7 @@ __global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a,
         for (int j = tid; j < cnt; j += kThreads) {
             const int i = i0 + j;
             float q[15];
-            draw_xyz_rot(a, c, sh.yaw, i, smean, ssd, q);
+            draw_xyz_rot(a, c, sh.yaw, i, smean, ssd, s_d[j], q);
             q[3] = s_w[j]; q[4] = s_h[j]; q[5] = s_l[j];
             float X[8], Y[8], Z[8], U[8], V[8];
             cube_corners(q, X, Y, Z);
@@ -409,7 +423,7 @@ __global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a,
                 for (int k = 0; k < 8; ++k) {
                     float m = (k & 2) ? -CUDART_INF_F : CUDART_INF_F;
                     for (int r = 0; r < S; ++r) {
-                        const float v = *remote(cl, &sh.mail.fb[k], r);
+                        const float v = *cl.remote(&sh.mail.fb[k], r);
                         m = (k & 2) ? max_nan(m, v) : min_nan(m, v);
                     }
                     t8[k] = m;
@@ -440,7 +454,7 @@ __global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a,
     if (a.propose_only) return;
     float maxdiff = -CUDART_INF_F, maxd = -CUDART_INF_F;
     for (int r = 0; r < S; ++r) {
-        const float v0 = *remote(cl, &sh.mail.maxdiff, r), v1 = *remote(cl, &sh.mail.maxd, r);
+        const float v0 = *cl.remote(&sh.mail.maxdiff, r), v1 = *cl.remote(&sh.mail.maxd, r);
         maxdiff = (maxdiff != maxdiff || v0 != v0) ? CUDART_NAN_F : fmaxf(maxdiff, v0);
         maxd = (maxd != maxd || v1 != v1) ? CUDART_NAN_F : fmaxf(maxd, v1);
     }
@@ -472,15 +486,21 @@ __global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a,
     cl.sync();   // (7)
     ArgMax win; win.v = -CUDART_INF_F; win.i = 0x7fffffff;
     for (int r = 0; r < S; ++r) {
-        const float v = *remote(cl, &sh.mail.am_v, r);
-        const int ii = *remote(cl, &sh.mail.am_i, r);
+        const float v = *cl.remote(&sh.mail.am_v, r);
+        const int ii = *cl.remote(&sh.mail.am_i, r);
         if (argmax_better(win.v, win.i, v, ii)) { win.v = v; win.i = ii; }
     }
     // the CTA that owns the winner recomputes its cube and box and writes the 84-byte record
     if (win.i >= i0 && win.i < i0 + cnt && tid == 0) {
         const int j = win.i - i0;
         float q[15];
-        draw_xyz_rot(a, c, sh.yaw, win.i, smean, ssd, q);
+        float xn = 0.f;
+        if (a.rng_mode == TDOD_RNG_PHILOX) {                               // s_d[j] now holds the chamfer distance
+            const uint64_t gid = (uint64_t)(a.obj_id_base + c.obj);
+            const uint4 r0 = Philox(a.seed)((uint32_t)win.i, (uint32_t)gid, (uint32_t)(gid >> 32) ^ 0x57484Cu, 0u);
+            xn = box_muller(r0.z, r0.w).y;
+        }
+        draw_xyz_rot(a, c, sh.yaw, win.i, smean, ssd, xn, q);
         q[3] = s_w[j]; q[4] = s_h[j]; q[5] = s_l[j];
         float X[8], Y[8], Z[8];
         cube_corners(q, X, Y, Z);
@@ -532,7 +552,14 @@ extern "C" int tdod_propose_score_select(const tdod_pss_args* ap, void* stream) 
     const int n_loc = (a.n_prop + S - 1) / S;
     const size_t smem = ((sizeof(Shared) + 15) & ~size_t(15)) + (size_t)7 * n_loc * sizeof(float);
     if (smem > 227 * 1024) return tdod_fail(TDOD_ERANGE, "n_prop too large for shared memory at this cluster size");
-    cudaError_t e = cudaFuncSetAttribute(pss_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e;
+    if (S == 1) {
+        e = cudaFuncSetAttribute(pss_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+        pss_kernel<false><<<(unsigned)a.n_obj, kThreads, smem, (cudaStream_t)stream>>>(a, n_loc);
+        return (int)cudaGetLastError();
+    }
+    e = cudaFuncSetAttribute(pss_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)((int64_t)a.n_obj * S), 1, 1);
@@ -543,6 +570,6 @@ extern "C" int tdod_propose_score_select(const tdod_pss_args* ap, void* stream) 
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = S; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
-    e = cudaLaunchKernelEx(&cfg, pss_kernel, a, n_loc);
+    e = cudaLaunchKernelEx(&cfg, pss_kernel<true>, a, n_loc);
     return (int)e;
 }

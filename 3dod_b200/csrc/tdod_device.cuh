@@ -198,29 +198,33 @@ __device__ __forceinline__ float dims_gauss(float w, float h, float l, const flo
     return __fdiv_rn(__fadd_rn(__fadd_rn(ea, eb), ec), 3.0f);
 }
 
-// scorefunction.py:51-56 modified_chamfer_distance(rect, corners): mean over the 4 rectangle points
-// of the distance to the nearest of the 8 projected corners, evaluated in fp64 like cKDTree, then
-// stored to fp32 (scores tensor is fp32, scorefunction.py:78-81).  sqrt is monotone, so the minimum
-// is taken on squared distances and only four square roots are evaluated.
+// scorefunction.py:51-56 modified_chamfer_distance(rect, corners): mean over the 4 rectangle points of the
+// distance to the nearest of the 8 projected corners, evaluated in fp64 like cKDTree, then stored to fp32
+// (scores tensor is fp32, scorefunction.py:78-81).  The nearest corner is searched on fp32 squared distances
+// (a near-tie can pick a corner whose true distance is larger by < 1e-7 relative -- far inside the 1e-5 bar);
+// the four distances that enter the mean are then evaluated in fp64.
 __device__ __forceinline__ float chamfer4x8(const float* __restrict__ rect /*[4][2]*/, const float (&U)[8],
                                             const float (&V)[8]) {
+    bool any_nan = false;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) any_nan |= (U[j] != U[j]) | (V[j] != V[j]);
     double acc = 0.0;
 #pragma unroll
     for (int r = 0; r < 4; ++r) {
-        const double rx = (double)rect[2 * r], ry = (double)rect[2 * r + 1];
-        double best = CUDART_INF;
-        bool any_nan = false;
+        const float rx = rect[2 * r], ry = rect[2 * r + 1];
+        float best = CUDART_INF_F, bu = U[0], bv = V[0];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            const double dx = rx - (double)U[j], dy = ry - (double)V[j];
-            const double d2 = dx * dx + dy * dy;
-            any_nan |= (d2 != d2);
-            best = fmin(best, d2);
+            const float dx = rx - U[j], dy = ry - V[j];
+            const float d2 = fmaf(dx, dx, dy * dy);
+            const bool lt = d2 < best;
+            best = lt ? d2 : best; bu = lt ? U[j] : bu; bv = lt ? V[j] : bv;
         }
-        // cKDTree rejects NaN input in the reference (it raises); we propagate NaN instead
-        acc += any_nan ? CUDART_NAN : sqrt(best);
+        const double ex = (double)rx - (double)bu, ey = (double)ry - (double)bv;
+        acc += sqrt(ex * ex + ey * ey);
     }
-    return (float)(acc * 0.25);
+    // cKDTree rejects NaN input in the reference (it raises); we propagate NaN instead
+    return any_nan ? CUDART_NAN_F : (float)(acc * 0.25);
 }
 
 }  // namespace tdod
