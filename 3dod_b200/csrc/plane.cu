@@ -5,6 +5,7 @@
 // pyransac3d.Plane.fit).  The 1000 x P distance matrix of fit_parallel is never materialised: every CTA keeps a
 // few points per thread in registers, streams the hypotheses from shared memory and counts inliers with
 // warp ballots.
+#include <cstdlib>
 #include "tdod_device.cuh"
 #include "tdod_internal.h"
 
@@ -209,6 +210,173 @@ __global__ void __launch_bounds__(256) count_kernel(const T* __restrict__ pts, c
 }
 
 // ------------------------------------------------------------------------------------------------
+// inlier counting, filtered: fp32 FMA evaluation with a rigorous error band, exact re-evaluation of the rare
+// (hypothesis, tile) pairs that have a point inside the band.  Same counts as count_kernel, bit for bit.
+//
+// Layout: a CTA owns one tile of <= kTilePts points of one frame (fp32 copies in shared memory, each value
+// duplicated so that it feeds both halves of a packed f32x2 FMA) and ALL hypotheses of the frame, four per thread in
+// registers.  The inner loop broadcasts one point to the CTA and every thread advances its four hypotheses:
+//   s   = a x + b y + c z + k                      (FFMA2: two hypotheses per instruction)
+//   t   = sat((bound^2 - s^2) * G + 1/2)           1 = certainly in, 0 = certainly out, between = inside the band
+//   S  += t ; S2 += t*t                            S - S2 > 0 only if some t was fractional
+// The band: the fp32 value differs from the separately rounded fp64 / fp32 value of the reference by at most
+// E = 5e-7 (max|x|+|y|+|z| + max|k| + bound) (inputs rounded once, three fused operations, |a|,|b|,|c| <= 1);
+// with e = 2E and 1/(2G) = 2 bound e - e^2, |s| <= bound - e gives t = 1, |s| >= bound + e gives t = 0, and any t
+// outside [1/4, 3/4] already decides the point; a tile whose S - S2 stays below 0.05 therefore has no undecided point
+// and rint(S) is its count (sums of <= 1024 terms).  Tiles that fail the test are recounted exactly.
+// ------------------------------------------------------------------------------------------------
+constexpr int kTilePts = 1024;     // points per CTA tile
+constexpr int kFiltT = 256;        // threads
+constexpr int kHypT = 4;           // hypotheses per thread per pass
+
+__device__ __forceinline__ float2 ffma2(const float2 a, const float2 b, const float2 c) {
+    float2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;"
+        : "=l"(reinterpret_cast<unsigned long long&>(d))
+        : "l"(reinterpret_cast<const unsigned long long&>(a)), "l"(reinterpret_cast<const unsigned long long&>(b)),
+          "l"(reinterpret_cast<const unsigned long long&>(c)));
+    return d;
+}
+__device__ __forceinline__ float2 fmul2(const float2 a, const float2 b) {
+    float2 d;
+    asm("mul.rn.f32x2 %0, %1, %2;"
+        : "=l"(reinterpret_cast<unsigned long long&>(d))
+        : "l"(reinterpret_cast<const unsigned long long&>(a)), "l"(reinterpret_cast<const unsigned long long&>(b)));
+    return d;
+}
+__device__ __forceinline__ float2 fadd2(const float2 a, const float2 b) {
+    float2 d;
+    asm("add.rn.f32x2 %0, %1, %2;"
+        : "=l"(reinterpret_cast<unsigned long long&>(d))
+        : "l"(reinterpret_cast<const unsigned long long&>(a)), "l"(reinterpret_cast<const unsigned long long&>(b)));
+    return d;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kFiltT) count_filter_kernel(const T* __restrict__ pts, const int32_t* __restrict__ n_pts,
+                                                             int64_t P_cap, const PlaneHyp<T>* __restrict__ hyps,
+                                                             int iters, int32_t* __restrict__ counts) {
+    __shared__ float4 s_xy[kTilePts];      // (x, x, y, y)
+    __shared__ float2 s_z[kTilePts];       // (z, z)
+    __shared__ int s_list[kFiltT * kHypT];
+    __shared__ int s_nlist, s_mmax, s_kmax;
+    __shared__ int s_cnt[kFiltT / 32];
+    const int f = blockIdx.y, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int P = n_pts[f];
+    const int tile0 = blockIdx.x * kTilePts;
+    if (tile0 >= P) return;
+    const int np = min(kTilePts, P - tile0);
+    const T* X = pts + (size_t)f * 3 * P_cap;
+    const T* Y = X + P_cap;
+    const T* Z = Y + P_cap;
+    const PlaneHyp<T>* hf = hyps + (size_t)f * iters;
+    if (tid == 0) { s_mmax = 0; s_kmax = 0; }
+    __syncthreads();
+    // ---- the tile's points, rounded once to fp32 ----
+    float mmax = 0.f;
+    for (int i = tid; i < np; i += kFiltT) {
+        const float x = (float)X[tile0 + i], y = (float)Y[tile0 + i], z = (float)Z[tile0 + i];
+        s_xy[i] = make_float4(x, x, y, y);
+        s_z[i] = make_float2(z, z);
+        float m = fabsf(x) + fabsf(y) + fabsf(z);
+        if (!(m == m)) m = CUDART_INF_F;
+        mmax = fmaxf(mmax, m);
+    }
+    // |k| + bound over ALL hypotheses of the frame (not only this pass): one band width per CTA
+    float kmax = 0.f;
+    for (int i = tid; i < iters; i += kFiltT) {
+        const float k = fabsf((float)hf[i].k), b = (float)hf[i].bound;
+        if (b >= 0.f) kmax = fmaxf(kmax, k + b);    // NaN / "no plane" hypotheses never count and do not widen the band
+    }
+    mmax = fmaxf(mmax, __shfl_xor_sync(0xffffffffu, mmax, 16)); kmax = fmaxf(kmax, __shfl_xor_sync(0xffffffffu, kmax, 16));
+    mmax = fmaxf(mmax, __shfl_xor_sync(0xffffffffu, mmax, 8));  kmax = fmaxf(kmax, __shfl_xor_sync(0xffffffffu, kmax, 8));
+    mmax = fmaxf(mmax, __shfl_xor_sync(0xffffffffu, mmax, 4));  kmax = fmaxf(kmax, __shfl_xor_sync(0xffffffffu, kmax, 4));
+    mmax = fmaxf(mmax, __shfl_xor_sync(0xffffffffu, mmax, 2));  kmax = fmaxf(kmax, __shfl_xor_sync(0xffffffffu, kmax, 2));
+    mmax = fmaxf(mmax, __shfl_xor_sync(0xffffffffu, mmax, 1));  kmax = fmaxf(kmax, __shfl_xor_sync(0xffffffffu, kmax, 1));
+    if (lane == 0) { atomicMax(&s_mmax, __float_as_int(mmax)); atomicMax(&s_kmax, __float_as_int(kmax)); }   // non-negative floats
+    __syncthreads();
+    const float e = 1.0e-6f * (__int_as_float(s_mmax) + __int_as_float(s_kmax)) + 1e-30f;
+
+    for (int h0 = 0; h0 < iters; h0 += kFiltT * kHypT) {
+        if (tid == 0) s_nlist = 0;
+        // ---- this thread's hypotheses: h0 + tid + j * kFiltT ----
+        float2 a2[kHypT / 2], b2[kHypT / 2], c2[kHypT / 2], k2[kHypT / 2], S[kHypT / 2], S2[kHypT / 2];
+        float nG[kHypT], C[kHypT];
+#pragma unroll
+        for (int j = 0; j < kHypT; ++j) {
+            const int h = h0 + tid + j * kFiltT;
+            float a = 0.f, b = 0.f, c = 0.f, k = 0.f, bd = -1.f;
+            if (h < iters) {
+                const PlaneHyp<T> p = hf[h];
+                a = (float)p.a; b = (float)p.b; c = (float)p.c; k = (float)p.k; bd = (float)p.bound;
+            }
+            (j & 1 ? a2[j / 2].y : a2[j / 2].x) = a; (j & 1 ? b2[j / 2].y : b2[j / 2].x) = b;
+            (j & 1 ? c2[j / 2].y : c2[j / 2].x) = c; (j & 1 ? k2[j / 2].y : k2[j / 2].x) = k;
+            const float D = 2.f * bd * e - e * e;                 // 1 / (2G)
+            if (bd < 0.f) { nG[j] = 0.f; C[j] = 0.f; }            // no plane: t = 0 everywhere
+            else if (!(bd > 2.f * e) || !(D > 0.f) || !(e < CUDART_INF_F)) { nG[j] = 0.f; C[j] = 0.5f; }   // no usable band: recount
+            else { const float G = 0.5f / D; nG[j] = -G; C[j] = fmaf(bd * bd, G, 0.5f); }
+        }
+#pragma unroll
+        for (int j = 0; j < kHypT / 2; ++j) { S[j] = make_float2(0.f, 0.f); S2[j] = make_float2(0.f, 0.f); }
+        __syncthreads();
+        // ---- main loop: broadcast a point, advance four hypotheses ----
+#pragma unroll 4
+        for (int i = 0; i < np; ++i) {
+            const float4 q = s_xy[i];
+            const float2 z = s_z[i];
+            const float2 qx = make_float2(q.x, q.y), qy = make_float2(q.z, q.w);
+#pragma unroll
+            for (int j = 0; j < kHypT / 2; ++j) {
+                float2 s = ffma2(c2[j], z, k2[j]);
+                s = ffma2(b2[j], qy, s);
+                s = ffma2(a2[j], qx, s);
+                const float2 w = fmul2(s, s);
+                float2 t;
+                t.x = __saturatef(fmaf(w.x, nG[2 * j], C[2 * j]));
+                t.y = __saturatef(fmaf(w.y, nG[2 * j + 1], C[2 * j + 1]));
+                S[j] = fadd2(S[j], t);
+                S2[j] = ffma2(t, t, S2[j]);
+            }
+        }
+        // ---- decided hypotheses go straight to the counters; the others are queued for the exact recount ----
+#pragma unroll
+        for (int j = 0; j < kHypT; ++j) {
+            const int h = h0 + tid + j * kFiltT;
+            const float s1 = (j & 1) ? S[j / 2].y : S[j / 2].x, s2 = (j & 1) ? S2[j / 2].y : S2[j / 2].x;
+            if (h < iters) {
+                if (s1 - s2 > 0.05f) s_list[atomicAdd(&s_nlist, 1)] = h;
+                else {
+                    const int c = __float2int_rn(s1);
+                    if (c) atomicAdd(&counts[(size_t)f * iters + h], c);
+                }
+            }
+        }
+        __syncthreads();
+        const int nl = s_nlist;
+        typedef Ar<T> A;
+        for (int l = 0; l < nl; ++l) {
+            const int h = s_list[l];
+            const PlaneHyp<T> p = hf[h];
+            int c = 0;
+            for (int i = tid; i < np; i += kFiltT) {
+                const T s = A::add(A::add(A::add(A::mul(p.a, X[tile0 + i]), A::mul(p.b, Y[tile0 + i])), A::mul(p.c, Z[tile0 + i])), p.k);
+                c += (fabs(s) <= p.bound) ? 1 : 0;
+            }
+            c = __reduce_add_sync(0xffffffffu, c);
+            if (lane == 0) s_cnt[wid] = c;
+            __syncthreads();
+            if (tid == 0) {
+                int tot = 0;
+                for (int w = 0; w < kFiltT / 32; ++w) tot += s_cnt[w];
+                if (tot) atomicAdd(&counts[(size_t)f * iters + h], tot);
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // best hypothesis (first maximum, plane.py:71 / :128 / :203) + rectification (roi_heads.py:411-428 / :1120-1136)
 // ------------------------------------------------------------------------------------------------
 template <typename T>
@@ -280,13 +448,19 @@ int ransac_impl(const T* pts, const int32_t* n_pts, int F, int64_t P_cap, const 
     hypotheses_kernel<T><<<dim3((iters + 127) / 128, F), 128, 0, st>>>(pts, n_pts, P_cap, ids, seed, frame_id_base, iters,
                                                                       (T)thresh, hyps, counts);
     TDOD_CHECK_LAUNCH();
-    constexpr int PT = 4;
-    const size_t smem = (size_t)iters * (sizeof(PlaneHyp<T>) + sizeof(int));
-    if (smem > 200 * 1024) return tdod_fail(TDOD_ERANGE, "tdod_ransac_plane: too many iterations for shared memory");
-    cudaError_t e = cudaFuncSetAttribute(count_kernel<T, PT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return (int)e;
-    const unsigned tiles = (unsigned)((P_cap + 256 * PT - 1) / (256 * PT));
-    count_kernel<T, PT><<<dim3(tiles, F), 256, smem, st>>>(pts, n_pts, P_cap, hyps, iters, counts);
+    const bool exact_only = getenv("TDOD_RANSAC_EXACT") != nullptr;   // A/B switch (tests, profiling): unfiltered kernel
+    if (exact_only) {
+        constexpr int PT = 4;
+        const size_t smem = (size_t)iters * (sizeof(PlaneHyp<T>) + sizeof(int));
+        if (smem > 200 * 1024) return tdod_fail(TDOD_ERANGE, "tdod_ransac_plane: too many iterations for shared memory");
+        cudaError_t e = cudaFuncSetAttribute(count_kernel<T, PT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+        const unsigned tiles = (unsigned)((P_cap + 256 * PT - 1) / (256 * PT));
+        count_kernel<T, PT><<<dim3(tiles, F), 256, smem, st>>>(pts, n_pts, P_cap, hyps, iters, counts);
+    } else {
+        const unsigned tiles = (unsigned)((P_cap + kTilePts - 1) / kTilePts);
+        count_filter_kernel<T><<<dim3(tiles, F), kFiltT, 0, st>>>(pts, n_pts, P_cap, hyps, iters, counts);
+    }
     TDOD_CHECK_LAUNCH();
     select_kernel<T><<<F, 256, 0, st>>>(hyps, counts, iters, negate, out_eq, out_best, out_count, out_normal);
     TDOD_CHECK_LAUNCH();

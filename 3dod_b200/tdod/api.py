@@ -127,7 +127,8 @@ def backproject(depth, ground, K, stride=5, flavour=L.BACKPROJECT_NUMPY, want_ot
     return pts, other, counts
 
 
-def ransac_plane(pts, n_pts, sample_ids=None, seed=0, iters=1000, thresh=0.05, want_mask=False, frame_id_base=0):
+def ransac_plane(pts, n_pts, sample_ids=None, seed=0, iters=1000, thresh=0.05, want_mask=False, frame_id_base=0,
+                 want_counts=False):
     """pts [F,3,P] fp32/fp64 SoA, n_pts [F] int32, sample_ids [F,iters,3] int32 or None (Philox).
     Returns dict(eq [F,4], best_iter [F], count [F], normal [F,3], mask [F,P] | None)."""
     F, _, P = pts.shape
@@ -145,7 +146,11 @@ def ransac_plane(pts, n_pts, sample_ids=None, seed=0, iters=1000, thresh=0.05, w
                                       float(thresh),
                                       L.ptr(eq), L.ptr(best), L.ptr(cnt), L.ptr(normal), L.ptr(mask), L.ptr(ws), wsb,
                                       L.stream_ptr()))
-    return dict(eq=eq, best_iter=best, count=cnt, normal=normal, mask=mask)
+    r = dict(eq=eq, best_iter=best, count=cnt, normal=normal, mask=mask)
+    if want_counts:   # per-hypothesis inlier counts live in the workspace right after the (256-byte aligned) hypotheses
+        hyp_bytes = (F * iters * (5 * pts.element_size()) + 255) & ~255
+        r["counts"] = ws[hyp_bytes:hyp_bytes + F * iters * 4].view(i32).reshape(F, iters)
+    return r
 
 
 class PssOutputs:

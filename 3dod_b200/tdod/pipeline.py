@@ -90,25 +90,64 @@ def ground_normals(depth, ground, K, seed=0, sample_ids=None, iters=1000, thresh
     return r["normal"], r["eq"], r["count"], pts, other, counts
 
 
+_SIDE = {}
+
+
+def _side_stream(dev):
+    """one auxiliary stream per device: K-A (ALU-bound) runs there while K-B (HBM-bound) runs on the caller's stream"""
+    key = (dev.type, dev.index if dev.index is not None else torch.cuda.current_device())
+    if key not in _SIDE:
+        _SIDE[key] = torch.cuda.Stream(dev)
+    return _SIDE[key]
+
+
 def select(batch, n_prop, seed=0, noise=None, yaw_idx=None, rot=None, sample_ids=None, use_ground=True,
            ransac_iters=1000, ransac_thresh=0.05, flavour=L.BACKPROJECT_NUMPY, obj_id_base=0, frame_id_base=0,
-           return_all=False, cluster_size=0):
+           return_all=False, cluster_size=0, overlap=True, marks=None):
     """Mode A (roi_heads.py:493-505) for every object of a device-resident batch.  Throughput RNG (in-kernel
     Philox keyed by global object id) unless `noise` (+ `yaw_idx` / `rot`) hands in host-drawn numbers.
-    Launches only; does not synchronise."""
+    Launches only; does not synchronise.
+
+    K-A (depth -> plane -> yaw table) and K-B (masks -> rectangles) are independent until K-C needs both: with
+    `overlap` K-A is launched on an auxiliary stream so that its FP-bound hypothesis scoring shares the SMs with
+    K-B's bandwidth-bound mask pass.  `marks`: optional dict that receives CUDA events
+    (kb0/kb1 around K-B and kc0/kc1 around K-C on the caller's stream, ka0/ka1 around K-A on its stream)."""
     s = Selection()
     yaw_tab = None
     s.normal = s.plane_eq = s.inlier_count = None
-    if use_ground and batch.ground is not None:
-        s.normal, s.plane_eq, s.inlier_count, _, _, _ = ground_normals(
-            batch.depth, batch.ground, batch.K, seed=seed, sample_ids=sample_ids, iters=ransac_iters,
-            thresh=ransac_thresh, flavour=flavour, frame_id_base=frame_id_base)
-        yaw_tab = api.yaw_table(s.normal)
+    main = torch.cuda.current_stream(batch.device)
+
+    def mark(name, stream):
+        if marks is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(stream)
+            marks[name] = ev
+
+    with_plane = use_ground and batch.ground is not None
+    side = _side_stream(batch.device) if (with_plane and overlap) else main
+    if with_plane:
+        if side is not main:
+            side.wait_stream(main)
+        with torch.cuda.stream(side):
+            mark("ka0", side)
+            s.normal, s.plane_eq, s.inlier_count, _, _, _ = ground_normals(
+                batch.depth, batch.ground, batch.K, seed=seed, sample_ids=sample_ids, iters=ransac_iters,
+                thresh=ransac_thresh, flavour=flavour, frame_id_base=frame_id_base)
+            yaw_tab = api.yaw_table(s.normal)
+            mark("ka1", side)
+    mark("kb0", main)
     s.rects, s.has_rect = api.mask_rect(batch.masks)
+    mark("kb1", main)
+    if with_plane and side is not main:
+        main.wait_stream(side)
+        for t in (s.normal, s.plane_eq, s.inlier_count, yaw_tab):
+            t.record_stream(main)        # allocated on the auxiliary stream, consumed on the caller's
+    mark("kc0", main)
     o = api.propose_score_select(batch.depth, batch.K, batch.boxes, batch.prior_mean, batch.prior_std,
                                  batch.obj_frame, s.rects, s.has_rect, n_prop, yaw_tab=yaw_tab, noise=noise,
                                  yaw_idx=yaw_idx, rot=rot, seed=None if noise is not None else seed,
                                  obj_id_base=obj_id_base, return_all=return_all, cluster_size=cluster_size)
+    mark("kc1", main)
     s.best_idx, s.best_score, s.best_cube, s.best_box = o.best_idx, o.best_score, o.best_cube, o.best_box
     s.all = o if return_all else None
     return s

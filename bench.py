@@ -30,6 +30,9 @@ import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
 WORKLOAD = "C2"
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of this workload
+# (profiles/r01_c2_full_summary.csv): pack_kernel 1.4929 GB + 0.1340 GB, rect_kernel passes 0.0938 GB + 0.0035 GB
+TRAFFIC = {"K-B mask_rect": 1.4929e9 + 0.1340e9 + 0.0938e9 + 0.0035e9}
 N_PROP = 1000
 METRIC = "scored cube proposals/sec"
 UNIT = "proposals/s"
@@ -226,30 +229,26 @@ def run_tdod(args):
 
     stream = torch.cuda.current_stream(dev)
     stage_names = list(abytes)
-    n_ev = len(stage_names) + 1
+    stage_marks = [("ka0", "ka1"), ("kb0", "kb1"), ("kc0", "kc1")]
 
-    def step(evs=None):
-        """one pass: K-A -> yaw table -> K-B -> K-C, all on the current stream; evs = events between stages"""
-        if evs: evs[0].record(stream)
-        normal, _, _, _, _, _ = pipeline.ground_normals(batch.depth, batch.ground, batch.K, seed=7, frame_id_base=rank * F)
-        yaw = api.yaw_table(normal)
-        if evs: evs[1].record(stream)
-        rects, has = api.mask_rect(batch.masks)
-        if evs: evs[2].record(stream)
-        o = api.propose_score_select(batch.depth, batch.K, batch.boxes, batch.prior_mean, batch.prior_std,
-                                     batch.obj_frame, rects, has, N_PROP, yaw_tab=yaw, seed=7, obj_id_base=obj_base)
-        if evs: evs[3].record(stream)
-        return o
+    def step(marks=None, overlap=True):
+        """one pass of the hot path (tdod.pipeline.select): K-A -> yaw table on the auxiliary stream, K-B on the current
+        stream, then K-C; overlap=False keeps everything on one stream (stage times without contention)"""
+        return pipeline.select(batch, N_PROP, seed=7, obj_id_base=obj_base, frame_id_base=rank * F, overlap=overlap,
+                               marks=marks)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    def stage_times(all_marks):
+        return [float(np.mean([m[a].elapsed_time(m[b]) for m in all_marks])) for a, b in stage_marks]
+
     for _ in range(max(args.warmup, 3)):
         o = step()
     barrier()
-    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(n_ev)] for _ in range(args.steps)]
+    marks = [dict() for _ in range(args.steps)]
     t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clk:
         barrier()
@@ -257,13 +256,24 @@ def run_tdod(args):
             torch.cuda.profiler.start()
         t_start.record(stream)
         for k in range(args.steps):
-            o = step(evs[k])
+            o = step(marks[k])
         t_end.record(stream)
         barrier()
         if args.profile:
             torch.cuda.profiler.stop()
     total_ms = t_start.elapsed_time(t_end)
-    stage_ms = [float(np.mean([evs[k][j].elapsed_time(evs[k][j + 1]) for k in range(args.steps)])) for j in range(n_ev - 1)]
+    stage_ms = stage_times(marks)                     # inside the timed region, each on its own stream (K-A overlaps K-B)
+    # the same K steps once more on ONE stream: stage times free of contention, and the cost of not overlapping
+    marks_serial = [dict() for _ in range(args.steps)]
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    s0.record(stream)
+    for k in range(args.steps):
+        step(marks_serial[k], overlap=False)
+    s1.record(stream)
+    barrier()
+    serial_ms_step = s0.elapsed_time(s1) / args.steps
+    stage_ms_serial = stage_times(marks_serial)
     # np.argmax returns the first NaN (roi_heads.py:501): objects whose proposals include a zero-height projected box
     # have a NaN winner in the reference too; everything else must be finite
     winners_nan = int(torch.isnan(o.best_score).sum().item())
@@ -320,8 +330,9 @@ def run_tdod(args):
                        "l2": "inputs (%.2f GB per pass) are larger than the 126 MB L2" % (batch.input_bytes() / 1e9)},
             "gpu_launches": pipeline.LAUNCHES_PER_SELECT * args.steps,
             "stages_ms": dict(zip(stage_names, stage_ms)),
+            "stages_ms_serial": dict(zip(stage_names, stage_ms_serial)), "ms_per_step_serial": serial_ms_step,
             "roofline": {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                         "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": abytes[dom],
+                         "traffic": TRAFFIC.get(dom), "peak_source": peak_src, "algorithmic_bytes_per_launch": abytes[dom],
                          "all_stages_frac": {n: abytes[n] / (m * 1e-3) / 1e9 / peak for n, m in zip(stage_names, stage_ms)}},
             "clocks": clk.summary(), "winners_ok": winners_ok, "winners_nan": winners_nan,
             "final_gather": {"records": int(gathered.shape[0]), "bytes": int(gathered.numel() * 4), "ms": gather_ms},

@@ -199,6 +199,58 @@ def _rect_dev(a, b):
     return max(min(float(np.hypot(*(p - q))) for q in b) for p in a)
 
 
+def _counts_both_ways(pts, n_pts, **kw):
+    """per-hypothesis inlier counts from the filtered kernel and from the unfiltered one (TDOD_RANSAC_EXACT)"""
+    r1 = api.ransac_plane(pts, n_pts, want_counts=True, want_mask=True, **kw)
+    torch.cuda.synchronize()
+    c1, b1, m1 = r1["counts"].clone(), r1["best_iter"].clone(), r1["mask"].clone()
+    os.environ["TDOD_RANSAC_EXACT"] = "1"
+    try:
+        r2 = api.ransac_plane(pts, n_pts, want_counts=True, want_mask=True, **kw)
+        torch.cuda.synchronize()
+    finally:
+        del os.environ["TDOD_RANSAC_EXACT"]
+    return (c1, b1, m1), (r2["counts"], r2["best_iter"], r2["mask"])
+
+
+@pytest.mark.parametrize("flavour", [L.BACKPROJECT_NUMPY, L.BACKPROJECT_TORCH])
+def test_filtered_inlier_count_equals_exact_count(flavour):
+    """The fp32-filtered counter must reproduce the separately rounded fp64 / fp32 counts of every hypothesis:
+    synthetic C2 frames, then adversarial clouds (points sitting exactly on the inlier band, far outliers that
+    widen the error band, NaN / Inf coordinates, a threshold below the band width, fewer than 3 points)."""
+    d = dev()
+    c = synth.CONFIGS["C2"]
+    frames = [synth.make_frame(i, c["H"], c["W"], c["n_obj"], device=d, with_masks=False) for i in range(6)]
+    depth = torch.stack([f.depth for f in frames]); ground = torch.stack([f.ground for f in frames])
+    K = torch.stack([f.K for f in frames])
+    pts, _, cnt = api.backproject(depth, ground, K, 5, flavour, want_other=False)
+    a, b = _counts_both_ways(pts, cnt[:, 0].contiguous(), seed=3, iters=1000, thresh=0.05)
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
+    assert int(a[0].max()) > 1000
+    # adversarial: a plane z = 1 sampled on a lattice, copies shifted by exactly +-thresh (and one ulp either side)
+    dt = pts.dtype
+    g = torch.Generator().manual_seed(0)
+    P = 3000
+    xy = (torch.rand((2, P), generator=g, dtype=torch.float64) * 4 - 2)
+    z = torch.ones(P, dtype=torch.float64)
+    th = 0.05
+    off = torch.tensor([0.0, th, -th, th * (1 + 2e-16), th * (1 - 2e-16), th * (1 + 1e-7), th * (1 - 1e-7), 0.3],
+                       dtype=torch.float64)
+    z = z + off[torch.randint(0, len(off), (P,), generator=g)]
+    cloud = torch.cat([xy, z[None]], 0)
+    far = cloud.clone(); far[:, 5] = torch.tensor([4.0e5, -3.0e5, 2.0e5], dtype=torch.float64)      # widens the band
+    bad = cloud.clone(); bad[0, 7] = float("nan"); bad[2, 11] = float("inf")                          # no usable band
+    tiny = cloud.clone()
+    allc = torch.stack([cloud, far, bad, tiny]).to(dt).contiguous().to(d)
+    n = torch.tensor([P, P, P, 2], dtype=torch.int32, device=d)
+    for thresh in (th, 1e-7):
+        a, b = _counts_both_ways(allc, n, seed=9, iters=1500, thresh=thresh)
+        for x, y in zip(a, b):
+            assert torch.equal(x, y)
+    assert int(a[0][3].max()) == 0            # fewer than 3 points: no plane
+
+
 def test_mask_rect_real_and_random_masks(golden_dir):
     from scipy import ndimage as ndi
     d = dev()
