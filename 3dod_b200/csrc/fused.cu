@@ -54,7 +54,23 @@ struct ObjCtx {
     float mu[3], sg[3];            // priors (w,h,l)
     float sgh;                     // std_h * 1.1
     float hi[3];                   // upper truncation per dimension
+    float nx0, nsx, ny0, nsy;      // PATCH centre modes: vectorized_linspace in normalised image space
+    float rh, rl;                  // DIMS_ASPECT ratios
 };
+
+// proposals.py:12-14 rescale_interval(u, MIN_PROP_S, 2) = (0.05 - 2) * u + 2, product and sum rounded separately
+__device__ __forceinline__ float rescale_dim(float u) { return __fadd_rn(__fmul_rn(u, -1.95f), 2.f); }
+// U[0,1) from 24 random bits
+__device__ __forceinline__ float u01(uint32_t r) { return (float)(r & 0xffffffu) * 5.9604644775390625e-8f; }
+
+// Philox mode: the standard normal behind the x centre of proposal i.  With prior dimensions it is the fourth normal of
+// the first (w,h,l) try; the uniform-dimension modes spend that block on w,h,l and take it from the next block.
+__device__ __forceinline__ float philox_xn(const tdod_pss_args& a, const ObjCtx& c, int i) {
+    const uint64_t gid = (uint64_t)(a.obj_id_base + c.obj);
+    const uint4 r = Philox(a.seed)((uint32_t)i, (uint32_t)gid, (uint32_t)(gid >> 32) ^ 0x57484Cu,
+                                   a.dims_mode == TDOD_DIMS_PRIOR ? 0u : 1u);
+    return box_muller(r.z, r.w).y;
+}
 
 // accepted standard normals for (w,h,l) of proposal i
 // `xn`: Philox mode only -- the standard normal of the x draw (fourth normal of the first try's Philox block)
@@ -62,9 +78,25 @@ __device__ __forceinline__ void draw_whl(const tdod_pss_args& a, const ObjCtx& c
     xn = 0.f;
     if (a.rng_mode == TDOD_RNG_HOST) {
         const float* nz = a.noise + (size_t)c.obj * 6 * a.n_prop;
-        w = scale_normal(nz[i], c.mu[0], c.sg[0]);
-        h = scale_normal(nz[a.n_prop + i], c.mu[1], c.sgh);
-        l = scale_normal(nz[2 * a.n_prop + i], c.mu[2], c.sg[2]);
+        if (a.dims_mode == TDOD_DIMS_PRIOR) {
+            w = scale_normal(nz[i], c.mu[0], c.sg[0]);
+            h = scale_normal(nz[a.n_prop + i], c.mu[1], c.sgh);
+            l = scale_normal(nz[2 * a.n_prop + i], c.mu[2], c.sg[2]);
+        } else if (a.dims_mode == TDOD_DIMS_UNIFORM) {                       // proposals.py:28-30
+            w = rescale_dim(nz[i]); h = rescale_dim(nz[a.n_prop + i]); l = rescale_dim(nz[2 * a.n_prop + i]);
+        } else {                                                            // proposals.py:230-239
+            w = rescale_dim(nz[i]); h = __fmul_rn(w, c.rh); l = __fmul_rn(w, c.rl);
+        }
+        return;
+    }
+    if (a.dims_mode != TDOD_DIMS_PRIOR) {
+        const Philox ph(a.seed);
+        const uint64_t gid = (uint64_t)(a.obj_id_base + c.obj);
+        const uint4 r = ph((uint32_t)i, (uint32_t)gid, (uint32_t)(gid >> 32) ^ 0x57484Cu, 0u);
+        w = rescale_dim(u01(r.x));
+        if (a.dims_mode == TDOD_DIMS_UNIFORM) { h = rescale_dim(u01(r.y)); l = rescale_dim(u01(r.z)); }
+        else { h = __fmul_rn(w, c.rh); l = __fmul_rn(w, c.rl); }
+        xn = philox_xn(a, c, i);
         return;
     }
     // utils.py:49-58: invalid entries are replaced by fresh draws until all are in [0.05, mean + k std];
@@ -88,9 +120,20 @@ __device__ __forceinline__ void draw_xyz_rot(const tdod_pss_args& a, const ObjCt
                                              const float (&mean)[3], const float (&sd)[3], float xn, float* q) {
     if (a.rng_mode == TDOD_RNG_HOST) {
         const float* nz = a.noise + (size_t)c.obj * 6 * a.n_prop;
-        q[0] = scale_normal(nz[3 * a.n_prop + i], mean[0], sd[0]);
-        q[1] = scale_normal(nz[4 * a.n_prop + i], mean[1], sd[1]);
-        q[2] = scale_normal(nz[5 * a.n_prop + i], mean[2], sd[2]);
+        if (a.centre_mode == TDOD_CENTRE_DEPTH) {
+            q[0] = scale_normal(nz[3 * a.n_prop + i], mean[0], sd[0]);
+            q[1] = scale_normal(nz[4 * a.n_prop + i], mean[1], sd[1]);
+            q[2] = scale_normal(nz[5 * a.n_prop + i], mean[2], sd[2]);
+        } else if (a.centre_mode == TDOD_CENTRE_UNIFORM) {                   // proposals.py:23-25
+            q[0] = __fsub_rn(__fmul_rn(nz[3 * a.n_prop + i], 4.f), 2.f);
+            q[1] = __fsub_rn(__fmul_rn(nz[4 * a.n_prop + i], 2.f), 1.f);
+            q[2] = __fadd_rn(__fmul_rn(nz[5 * a.n_prop + i], 4.f), 1.f);
+        } else {                                                            // proposals.py:59-62 / :106-115
+            q[0] = __fadd_rn(__fmul_rn((float)i, c.nsx), c.nx0);
+            q[1] = __fadd_rn(__fmul_rn((float)i, c.nsy), c.ny0);
+            const float zc = nz[5 * a.n_prop + i];
+            q[2] = (a.centre_mode == TDOD_CENTRE_PATCH) ? __fadd_rn(__fmul_rn(zc, 4.f), 1.f) : zc;
+        }
         if (a.yaw_table) {
             const int yi = a.yaw_idx[(size_t)c.obj * a.n_prop + i];
 #pragma unroll
@@ -106,10 +149,20 @@ __device__ __forceinline__ void draw_xyz_rot(const tdod_pss_args& a, const ObjCt
     const uint64_t gid = (uint64_t)(a.obj_id_base + c.obj);
     // one Philox block: two uniforms -> (y, z) normals, one -> yaw bin; the x normal came with the (w,h,l) block
     const uint4 r = ph((uint32_t)i, (uint32_t)gid, (uint32_t)(gid >> 32) ^ 0x58595Au, 0u);
-    const float2 n01 = box_muller(r.x, r.y);
-    q[0] = scale_normal(xn, mean[0], sd[0]);
-    q[1] = scale_normal(n01.x, mean[1], sd[1]);
-    q[2] = scale_normal(n01.y, mean[2], sd[2]);
+    if (a.centre_mode == TDOD_CENTRE_DEPTH) {
+        const float2 n01 = box_muller(r.x, r.y);
+        q[0] = scale_normal(xn, mean[0], sd[0]);
+        q[1] = scale_normal(n01.x, mean[1], sd[1]);
+        q[2] = scale_normal(n01.y, mean[2], sd[2]);
+    } else if (a.centre_mode == TDOD_CENTRE_UNIFORM) {
+        q[0] = __fsub_rn(__fmul_rn(u01(r.x), 4.f), 2.f);
+        q[1] = __fsub_rn(__fmul_rn(u01(r.y), 2.f), 1.f);
+        q[2] = __fadd_rn(__fmul_rn(u01(r.w), 4.f), 1.f);
+    } else {                                                                // PATCH (PATCH_Z needs the caller's ramp)
+        q[0] = __fadd_rn(__fmul_rn((float)i, c.nsx), c.nx0);
+        q[1] = __fadd_rn(__fmul_rn((float)i, c.nsy), c.ny0);
+        q[2] = __fadd_rn(__fmul_rn(u01(r.w), 4.f), 1.f);
+    }
     if (a.yaw_table) {
         const int yi = (int)(r.z % TDOD_NYAW);  // torch.randint(36, ...): u32 % 36
 #pragma unroll
@@ -199,6 +252,20 @@ __global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a,
         c.hi[0] = __fadd_rn(c.mu[0], __fmul_rn(2.f, c.sg[0]));             // :381
         c.hi[1] = __fadd_rn(c.mu[1], __fmul_rn(2.2f, c.sg[1]));            // :382
         c.hi[2] = __fadd_rn(c.mu[2], __fmul_rn(2.f, c.sg[2]));             // :383
+        c.nx0 = c.nsx = c.ny0 = c.nsy = 0.f;
+        if (a.centre_mode >= TDOD_CENTRE_PATCH) {
+            // conversions.py:50-67 pixel_to_normalised_space: (p - 0.5*old) * (new/old), python-float constants cast
+            // to fp32; x uses (im_w, 3), y uses (im_h, 2) (proposals.py:56-57)
+            const int iw = a.im_w > 0 ? a.im_w : a.W, ih = a.im_h > 0 ? a.im_h : a.H;
+            const float hx = (float)(0.5 * (double)iw), sx = (float)(3.0 / (double)iw);
+            const float hy = (float)(0.5 * (double)ih), sy = (float)(2.0 / (double)ih);
+            const float x0n = __fmul_rn(__fsub_rn(c.lox, hx), sx), x1n = __fmul_rn(__fsub_rn(hix, hx), sx);
+            const float y0n = __fmul_rn(__fsub_rn(c.loy, hy), sy), y1n = __fmul_rn(__fsub_rn(hiy, hy), sy);
+            c.nx0 = x0n; c.nsx = __fdiv_rn(__fsub_rn(x1n, x0n), (float)(n - 1));
+            c.ny0 = y0n; c.nsy = __fdiv_rn(__fsub_rn(y1n, y0n), (float)(n - 1));
+        }
+        c.rh = c.rl = 1.f;
+        if (a.dims_mode == TDOD_DIMS_ASPECT) { c.rh = a.aux[(size_t)obj * 2]; c.rl = a.aux[(size_t)obj * 2 + 1]; }
     }
     if (tid < 9) sh.K[tid] = a.K[(size_t)c.frame * 9 + tid];
     if (a.yaw_table)
@@ -222,9 +289,11 @@ __global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a,
         // reference -- we clamp instead of faulting.
         int ix = gx < 0 ? gx + a.W : gx, iy = gy < 0 ? gy + a.H : gy;
         ix = min(max(ix, 0), a.W - 1); iy = min(max(iy, 0), a.H - 1);
-        const float d = __ldg(depth + (size_t)iy * a.W + ix);
-        float x, y, zt, w, h, l, xn;
-        centre_seed(gx, gy, d, fx, cx, cy, x, y, zt);
+        float x = 0.f, y = 0.f, zt = 0.f, w, h, l, xn;
+        if (a.centre_mode == TDOD_CENTRE_DEPTH) {
+            const float d = __ldg(depth + (size_t)iy * a.W + ix);
+            centre_seed(gx, gy, d, fx, cx, cy, x, y, zt);
+        }
         draw_whl(a, c, i, w, h, l, xn);
         s_d[j] = xn;                                                       // parked until phase 2 reads it back
         const float z = __fadd_rn(zt, __fdiv_rn(l, 2.f));                  // proposals.py:394
@@ -495,11 +564,7 @@ __global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a,
         const int j = win.i - i0;
         float q[15];
         float xn = 0.f;
-        if (a.rng_mode == TDOD_RNG_PHILOX) {                               // s_d[j] now holds the chamfer distance
-            const uint64_t gid = (uint64_t)(a.obj_id_base + c.obj);
-            const uint4 r0 = Philox(a.seed)((uint32_t)win.i, (uint32_t)gid, (uint32_t)(gid >> 32) ^ 0x57484Cu, 0u);
-            xn = box_muller(r0.z, r0.w).y;
-        }
+        if (a.rng_mode == TDOD_RNG_PHILOX) xn = philox_xn(a, c, win.i);    // s_d[j] now holds the chamfer distance
         draw_xyz_rot(a, c, sh.yaw, win.i, smean, ssd, xn, q);
         q[3] = s_w[j]; q[4] = s_h[j]; q[5] = s_l[j];
         float X[8], Y[8], Z[8];
@@ -542,6 +607,11 @@ extern "C" int tdod_propose_score_select(const tdod_pss_args* ap, void* stream) 
     } else if (a.rng_mode != TDOD_RNG_PHILOX) {
         return tdod_fail(TDOD_EINVAL, "unknown rng_mode");
     }
+    if (a.centre_mode < TDOD_CENTRE_DEPTH || a.centre_mode > TDOD_CENTRE_PATCH_Z) return tdod_fail(TDOD_EINVAL, "unknown centre_mode");
+    if (a.dims_mode < TDOD_DIMS_PRIOR || a.dims_mode > TDOD_DIMS_ASPECT) return tdod_fail(TDOD_EINVAL, "unknown dims_mode");
+    if (a.dims_mode == TDOD_DIMS_ASPECT && !a.aux) return tdod_fail(TDOD_EINVAL, "dims_mode ASPECT needs aux [n_obj,2]");
+    if (a.centre_mode == TDOD_CENTRE_PATCH_Z && a.rng_mode != TDOD_RNG_HOST)
+        return tdod_fail(TDOD_EINVAL, "centre_mode PATCH_Z takes its z ramp from the caller (rng_mode HOST)");
     int S = a.cluster_size;
     if (S == 0) {
         // one CTA handles up to 2048 proposals comfortably; spread larger objects, and small batches, over a cluster

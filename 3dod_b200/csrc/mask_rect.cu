@@ -788,11 +788,14 @@ template <bool kExact, bool kGlobal>
 __global__ void __launch_bounds__(kT, kExact ? 1 : 4) rect_kernel(const uint32_t* __restrict__ bitmap, const int* __restrict__ rowrange,
                                                                   int64_t n_masks, int H, int W, float* __restrict__ out_rects,
                                                                   uint8_t* __restrict__ out_has, unsigned char* __restrict__ slots,
-                                                                  int* __restrict__ lists) {
+                                                                  int* __restrict__ lists, uint32_t* __restrict__ fill_slots) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int Wp = (W + 31) >> 5;
     Smem s;
-    smem_layout(H, Wp, kExact, &s, smem_raw);
+    // masks too large for two shared-memory bitmaps (above ~0.75 Mpx): the flood reads the packed mask where it lies and
+    // keeps its state in a per-CTA workspace slot (L2-resident); only the rare exact passes pay for it
+    const bool bm_global = kExact && fill_slots != nullptr;
+    smem_layout(H, Wp, kExact && !bm_global, &s, smem_raw);
     int cap = kRunCap;
     if (kGlobal) {
         const int64_t c = run_cap_global(H, W);
@@ -815,7 +818,12 @@ __global__ void __launch_bounds__(kT, kExact ? 1 : 4) rect_kernel(const uint32_t
         }
         const uint32_t* comp_bm = bitmap + (size_t)mi * H * Wp;
         if (kExact) {
-            for (int i = threadIdx.x; i < H * Wp; i += kT) s.bmA[i] = comp_bm[i];
+            if (bm_global) {
+                s.bmA = const_cast<uint32_t*>(comp_bm);
+                s.bmB = fill_slots + (size_t)blockIdx.x * (align16((size_t)H * Wp * 4) / 4);
+            } else {
+                for (int i = threadIdx.x; i < H * Wp; i += kT) s.bmA[i] = comp_bm[i];
+            }
             __syncthreads();
             flood_outside(s.bmA, s.bmB, H, W, Wp, s.scratch + 30);
             const uint32_t tail = (W & 31) ? ((1u << (W & 31)) - 1u) : 0xffffffffu;
@@ -848,10 +856,19 @@ __global__ void __launch_bounds__(kT, kExact ? 1 : 4) rect_kernel(const uint32_t
 
 }  // namespace
 
+constexpr int kExactCtas = 148;   // persistent CTAs of the exact pass
+
+// true when the exact passes cannot hold two H x Wp bitmaps in shared memory
+static bool exact_needs_global(int H, int W) { return smem_layout(H, (W + 31) >> 5, true, nullptr, nullptr) > 227 * 1024; }
+static size_t ws_fill_bytes(int H, int W) {
+    return exact_needs_global(H, W) ? (size_t)kExactCtas * align16((size_t)H * ((W + 31) >> 5) * 4) : 0;
+}
+
 extern "C" int64_t tdod_mask_rect_workspace_bytes(int64_t n_masks, int H, int W) {
     if (n_masks <= 0 || H <= 0 || W <= 0) return 16;
     const int64_t slots = n_masks < kSlots ? n_masks : kSlots;
-    return (int64_t)(ws_bitmap_bytes(n_masks, H, W) + ws_range_bytes(n_masks) + ws_list_bytes(n_masks) + slots * slot_bytes(H, W));
+    return (int64_t)(ws_bitmap_bytes(n_masks, H, W) + ws_range_bytes(n_masks) + ws_list_bytes(n_masks) + slots * slot_bytes(H, W) +
+                     ws_fill_bytes(H, W));
 }
 
 extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int W, float* out_rects,
@@ -866,15 +883,17 @@ extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int 
         return tdod_fail(TDOD_EINVAL, "tdod_mask_rect: workspace must be 16-byte aligned");
     const int Wp = (W + 31) >> 5;
     const size_t smem1 = smem_layout(H, Wp, false, nullptr, nullptr);
-    const size_t smem2 = smem_layout(H, Wp, true, nullptr, nullptr);
-    if (smem2 > 227 * 1024)
-        return tdod_fail(TDOD_ERANGE, "tdod_mask_rect: mask does not fit in shared memory (H*ceil(W/32)*8 bytes + 40 KB <= 227 KB)");
+    const bool big = exact_needs_global(H, W);
+    const size_t smem2 = big ? smem1 : smem_layout(H, Wp, true, nullptr, nullptr);
+    if (smem1 > 227 * 1024) return tdod_fail(TDOD_ERANGE, "tdod_mask_rect: image too tall for the per-row tables in shared memory");
     cudaStream_t st = (cudaStream_t)stream;
     unsigned char* wsb = (unsigned char*)workspace;
     uint32_t* bitmap = (uint32_t*)wsb;
     int* rowrange = (int*)(wsb + ws_bitmap_bytes(n_masks, H, W));
     int* lists = (int*)(wsb + ws_bitmap_bytes(n_masks, H, W) + ws_range_bytes(n_masks));
     unsigned char* slots = wsb + ws_bitmap_bytes(n_masks, H, W) + ws_range_bytes(n_masks) + ws_list_bytes(n_masks);
+    const int64_t n_run_slots = n_masks < kSlots ? n_masks : kSlots;
+    uint32_t* fill_slots = big ? (uint32_t*)(slots + n_run_slots * slot_bytes(H, W)) : nullptr;
     cudaError_t e = cudaFuncSetAttribute(rect_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1);
     if (e != cudaSuccess) return (int)e;
     e = cudaFuncSetAttribute(rect_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
@@ -894,13 +913,14 @@ extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int 
     pack_kernel<<<pk_grid, kPackT, pk_smem, st>>>(masks, n_masks, H, W, Wp, bitmap, rowrange, lists, tiles_per_mask);
     TDOD_CHECK_LAUNCH();
     rect_kernel<false, false><<<(unsigned)n_masks, kT, smem1, st>>>(bitmap, rowrange, n_masks, H, W, out_rects, out_has_rect, nullptr,
-                                                                 lists);
+                                                                 lists, nullptr);
     TDOD_CHECK_LAUNCH();
-    rect_kernel<true, false><<<(unsigned)(n_masks < 148 ? n_masks : 148), kT, smem2, st>>>(bitmap, rowrange, n_masks, H, W, out_rects,
-                                                                                         out_has_rect, nullptr, lists);
+    rect_kernel<true, false><<<(unsigned)(n_masks < kExactCtas ? n_masks : kExactCtas), kT, smem2, st>>>(
+        bitmap, rowrange, n_masks, H, W, out_rects, out_has_rect, nullptr, lists, fill_slots);
     TDOD_CHECK_LAUNCH();
     const unsigned nslots = (unsigned)(n_masks < kSlots ? n_masks : kSlots);
-    rect_kernel<true, true><<<nslots, kT, smem2, st>>>(bitmap, rowrange, n_masks, H, W, out_rects, out_has_rect, slots, lists);
+    rect_kernel<true, true><<<nslots, kT, smem2, st>>>(bitmap, rowrange, n_masks, H, W, out_rects, out_has_rect, slots, lists,
+                                                      fill_slots);
     TDOD_CHECK_LAUNCH();
     return TDOD_OK;
 }

@@ -159,7 +159,8 @@ class PssOutputs:
 
 def propose_score_select(depth, K, boxes, prior_mean, prior_std, obj_frame, rects, has_rect, n_prop, yaw_tab=None,
                          iou_boxes=None, noise=None, yaw_idx=None, rot=None, seed=None, obj_id_base=0,
-                         return_all=False, cluster_size=0, out=None, propose_only=False):
+                         return_all=False, cluster_size=0, out=None, propose_only=False, centre_mode=L.CENTRE_DEPTH,
+                         dims_mode=L.DIMS_PRIOR, aux=None, im_shape=None):
     """The fused hot path (csrc/fused.cu).  depth [F,H,W], K [F,3,3], boxes [N,4], priors [N,3], obj_frame [N] int32,
     rects [N,4,2], has_rect [N] uint8 | None, yaw_tab [F,36,3,3] | None.
     Parity RNG mode: noise [N,6,n] (+ yaw_idx [N,n] int16 | rot [N,n,9]); throughput mode: seed=int (Philox)."""
@@ -211,5 +212,11 @@ def propose_score_select(depth, K, boxes, prior_mean, prior_std, obj_frame, rect
     a.all_scores, a.stats = L.ptr(o.all_scores), L.ptr(o.stats)
     a.cluster_size = int(cluster_size)
     a.propose_only = 1 if propose_only else 0
+    # ablation samplers (proposals.py:20-336): where centres / dimensions come from; im_shape = (width, height)
+    a.centre_mode, a.dims_mode = int(centre_mode), int(dims_mode)
+    a.im_w, a.im_h = (int(im_shape[0]), int(im_shape[1])) if im_shape is not None else (0, 0)
+    if aux is not None and tuple(aux.shape) != (N, 2):
+        raise ValueError("aux must be [N,2]")
+    a.aux = L.ptr(aux, f32, "aux")
     L.check(L.lib().tdod_propose_score_select(C.byref(a), L.stream_ptr()))
     return o

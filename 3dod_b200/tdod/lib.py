@@ -11,6 +11,8 @@ LIB_PATH = os.path.join(_HERE, "libtdod.so")
 
 RNG_HOST, RNG_PHILOX = 0, 1
 BACKPROJECT_NUMPY, BACKPROJECT_TORCH = 0, 1
+CENTRE_DEPTH, CENTRE_UNIFORM, CENTRE_PATCH, CENTRE_PATCH_Z = 0, 1, 2, 3
+DIMS_PRIOR, DIMS_UNIFORM, DIMS_ASPECT = 0, 1, 2
 
 _lib = None
 
@@ -29,6 +31,8 @@ class PssArgs(C.Structure):
         ("best_idx", C.c_void_p), ("best_score", C.c_void_p), ("best_cube", C.c_void_p), ("best_box", C.c_void_p),
         ("all_cubes", C.c_void_p), ("all_boxes", C.c_void_p), ("all_scores", C.c_void_p), ("stats", C.c_void_p),
         ("cluster_size", C.c_int32), ("propose_only", C.c_int32),
+        ("centre_mode", C.c_int32), ("dims_mode", C.c_int32), ("im_w", C.c_int32), ("im_h", C.c_int32),
+        ("aux", C.c_void_p),
     ]
 
 

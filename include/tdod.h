@@ -28,6 +28,19 @@ extern "C" {
 #define TDOD_RNG_HOST 0    /* parity mode: standard normals + yaw ids drawn by the caller */
 #define TDOD_RNG_PHILOX 1  /* throughput mode: in-kernel Philox4x32-10 */
 
+/* where the cube centres come from (tdod_pss_args.centre_mode) */
+#define TDOD_CENTRE_DEPTH 0    /* proposals.py:350-396 (propose, propose_random_dim, propose_aspect_ratio,
+                                  propose_random_rotation): depth gather + pinhole trig seeds, median / std, normal draws */
+#define TDOD_CENTRE_UNIFORM 1  /* proposals.py:22-25 (propose_random): x = u*4-2, y = u*2-1, z = u*4+1 */
+#define TDOD_CENTRE_PATCH 2    /* proposals.py:51-64 (propose_xy_patch): x, y = vectorized_linspace over the inner half
+                                  of the box in normalised image space (conversions.py:50-67), z = u*4+1 */
+#define TDOD_CENTRE_PATCH_Z 3  /* proposals.py:98-115 (propose_z): x, y as PATCH; z handed in by the caller (the
+                                  per-object torch.quantile / torch.linspace ramp), noise channel 5 taken as is */
+/* where the cube dimensions come from (tdod_pss_args.dims_mode) */
+#define TDOD_DIMS_PRIOR 0      /* proposals.py:377-383: truncated normals around the class priors */
+#define TDOD_DIMS_UNIFORM 1    /* proposals.py:28-30 rescale_interval(u, 0.05, 2) for w, h, l */
+#define TDOD_DIMS_ASPECT 2     /* proposals.py:230-239 (propose_aspect_ratio): w uniform, h = w*aux[0], l = w*aux[1] */
+
 #define TDOD_BACKPROJECT_NUMPY 0 /* roi_heads.py:346-371: fp64, full-res intrinsics on the strided grid */
 #define TDOD_BACKPROJECT_TORCH 1 /* roi_heads.py:1084-1112: fp32, K // stride, centre of the strided grid */
 
@@ -128,7 +141,8 @@ typedef struct tdod_pss_args {
     const uint8_t* has_rect;   /* [n_obj] or NULL (all present) */
     /* randomness */
     int32_t rng_mode;          /* TDOD_RNG_HOST | TDOD_RNG_PHILOX */
-    const float* noise;        /* HOST mode: [n_obj,6,n_prop] accepted standard normals, order w,h,l,x,y,z */
+    const float* noise;        /* HOST mode: [n_obj,6,n_prop], order w,h,l,x,y,z: accepted standard normals, or U[0,1)
+                                  draws for the channels an ablation mode samples uniformly (unused channels ignored) */
     const int16_t* yaw_idx;    /* HOST mode with yaw_table: [n_obj,n_prop] in [0,36) */
     const float* rot;          /* HOST mode without yaw_table: [n_obj,n_prop,9] */
     uint64_t seed;             /* PHILOX mode */
@@ -146,6 +160,11 @@ typedef struct tdod_pss_args {
     int32_t cluster_size;      /* CTAs per object: 0 = auto, else 1,2,4,8 */
     int32_t propose_only;      /* != 0: sample + project only (proposals.propose / cubes_to_box): fills all_cubes /
                                   all_boxes / stats, needs no rects and writes no winners */
+    /* ablation samplers (proposals.py:20-336); all zero = the production sampler `propose` */
+    int32_t centre_mode;       /* TDOD_CENTRE_* */
+    int32_t dims_mode;         /* TDOD_DIMS_* */
+    int32_t im_w, im_h;        /* im_shape of pixel_to_normalised_space (PATCH modes); 0 -> W, H */
+    const float* aux;          /* [n_obj,2]: DIMS_ASPECT (ratio_h, ratio_l); NULL otherwise */
 } tdod_pss_args;
 
 /* propose (proposals.py:338-424) + cubes_to_box + score_iou + score_dimensions + score_corners +

@@ -138,7 +138,11 @@ def load():
     # the product mirror is also called `ProposalNetwork`; make sure the reference wins here
     for k in [k for k in sys.modules if k == "ProposalNetwork" or k.startswith("ProposalNetwork.")]:
         del sys.modules[k]
-    sys.path.insert(0, REF_ROOT)
+    # the reference's ProposalNetwork has no __init__.py (a namespace package): a regular package of the same name
+    # anywhere on sys.path (the mirror under 3dod_b200/) would win whatever the order, so hide those entries meanwhile
+    hidden = [p for p in sys.path if p != REF_ROOT and os.path.isfile(os.path.join(p or ".", "ProposalNetwork", "__init__.py"))]
+    saved_path = list(sys.path)
+    sys.path[:] = [REF_ROOT] + [p for p in sys.path if p not in hidden]
     try:
         r = Ref()
         r.proposals = importlib.import_module("ProposalNetwork.proposals.proposals")
@@ -150,7 +154,7 @@ def load():
         r.Boxes = _Boxes
         r.pairwise_iou = _pairwise_iou
     finally:
-        sys.path.remove(REF_ROOT)
+        sys.path[:] = saved_path
         # leave the names importable only through the returned namespace
         for k in [k for k in sys.modules if k == "ProposalNetwork" or k.startswith("ProposalNetwork.")]:
             del sys.modules[k]

@@ -190,6 +190,110 @@ def propose(boxes, depth, prior_mean, prior_std, K, n, normal=None, generator=No
 
 
 # ----------------------------------------------------------------------------------------------
+# ablation samplers (proposals.py:20-336): same output contract as `propose`, different marginals.
+# Each returns dict(cubes [N,n,15], noise [6,N,n] in (w,h,l,x,y,z) order -- standard normals or U[0,1)
+# draws as the variant uses them, zeros for channels it does not draw --, rot [N,n,3,3], aux [N,2] | None)
+# ----------------------------------------------------------------------------------------------
+RATIOS = [0.33, 0.66, 1, 1.33, 1.67, 2, 3]   # proposals.py:232
+
+
+def _rescale(u):
+    """proposals.py:12-14 rescale_interval(u, MIN_PROP_S, 2)"""
+    return (MIN_PROP_S - 2) * u + 2
+
+
+def normalised_ramps(boxes, im_shape, n):
+    """proposals.py:51-62 / :98-107: the inner half of the box in normalised image space
+    (conversions.py:50-67: (p - 0.5*old) * (new/old); x with (im_w, 3), y with (im_h, 2)), then vectorized_linspace."""
+    bw = boxes[:, 2] - boxes[:, 0]
+    bh = boxes[:, 3] - boxes[:, 1]
+
+    def norm(lo, hi, old, new):
+        p = torch.stack([lo, hi], dim=1).to(torch.float32)
+        for i in range(2):
+            p[:, i] -= 0.5 * old
+            p[:, i] *= new / old
+        return p
+    xt = norm(boxes[:, 0] + bw / 4, boxes[:, 2] - bw / 4, im_shape[0], 3)
+    yt = norm(boxes[:, 1] + bh / 4, boxes[:, 3] - bh / 4, im_shape[1], 2)
+    return linspace_rows(xt[:, 0], xt[:, 1], n), linspace_rows(yt[:, 0], yt[:, 1], n)
+
+
+def _seeded_centres(boxes, depth, K, n, l, generator):
+    """proposals.py:179-191 (= :386-396): median / std of the seeds, three untruncated normal draws"""
+    x0, y0, z0 = centre_seeds(boxes, depth, K, n)
+    cx = torch.tensor([1.15, 0.0]); cy = torch.tensor([1.1, 0.0]); cz = torch.tensor([0.85, 0.35])
+    x, zx, _ = draw_normal_rows(cx[0] * torch.median(x0, dim=1).values + cx[1], torch.std(x0, dim=1) * 1.2, n,
+                                generator=generator)
+    y, zy, _ = draw_normal_rows(cy[0] * torch.median(y0, dim=1).values + cy[1], torch.std(y0, dim=1) * 0.8, n,
+                                generator=generator)
+    zt = z0 + l / 2
+    z, zz, _ = draw_normal_rows(cz[0] * torch.median(zt, dim=1).values + cz[1], torch.std(zt, dim=1) * 1.2, n,
+                                generator=generator)
+    return (x, y, z), (zx, zy, zz)
+
+
+def _pack(x, y, z, w, h, l, R, noise, aux=None):
+    xyzwhl = torch.stack([x, y, z, w, h, l], 2)
+    cubes = torch.cat((xyzwhl, R.flatten(start_dim=2)), dim=2).to(torch.float32)
+    return dict(cubes=cubes, noise=torch.stack(noise, 0), rot=R, aux=aux)
+
+
+def propose_variant(name, boxes, depth, prior_mean, prior_std, K, im_shape, n, generator=None):
+    """name in random | xy | z | dim | aspect | rotation (the `proposal_function` strings of roi_heads.py:286-299)."""
+    N = boxes.shape[0]
+    U = lambda: torch.rand((N, n), generator=generator)
+    zero = torch.zeros((N, n))
+    if name == "random":                                    # proposals.py:20-45
+        ux, uy, uz = U(), U(), U()
+        x, y, z = ux * 4 - 2, uy * 2 - 1, uz * 4 + 1
+        uw, uh, ul = U(), U(), U()
+        R = random_rotations(N, n, generator)
+        return _pack(x, y, z, _rescale(uw), _rescale(uh), _rescale(ul), R, [uw, uh, ul, ux, uy, uz])
+    if name == "xy":                                        # :47-91
+        x, y = normalised_ramps(boxes, im_shape, n)
+        uz = U()
+        z = uz * 4 + 1
+        uw, uh, ul = U(), U(), U()
+        R = random_rotations(N, n, generator)
+        return _pack(x, y, z, _rescale(uw), _rescale(uh), _rescale(ul), R, [uw, uh, ul, zero, zero, uz])
+    if name == "z":                                         # :93-135
+        x, y = normalised_ramps(boxes, im_shape, n)
+        z = torch.zeros_like(x)
+        for i in range(N):
+            patch = depth[int(boxes[i, 1]):int(boxes[i, 3]), int(boxes[i, 0]):int(boxes[i, 2])]
+            q = torch.quantile(patch, torch.tensor([0.1, 0.9]), dim=None)
+            z[i] = torch.linspace(q[0], q[1], n)
+        uw, uh, ul = U(), U(), U()
+        R = random_rotations(N, n, generator)
+        return _pack(x, y, z, _rescale(uw), _rescale(uh), _rescale(ul), R, [uw, uh, ul, zero, zero, z])
+    if name == "dim":                                       # :137-197
+        uw, uh, ul = U(), U(), U()
+        w, h, l = _rescale(uw), _rescale(uh), _rescale(ul)
+        (x, y, z), (zx, zy, zz) = _seeded_centres(boxes, depth, K, n, l, generator)
+        R = random_rotations(N, n, generator)
+        return _pack(x, y, z, w, h, l, R, [uw, uh, ul, zx, zy, zz])
+    if name == "aspect":                                    # :199-269
+        uw = U()
+        w = _rescale(uw)
+        h = torch.zeros_like(w); l = torch.zeros_like(w)
+        aux = torch.zeros((N, 2))
+        for i in range(N):
+            r1 = torch.randperm(len(RATIOS), generator=generator)[0]
+            r2 = torch.randperm(len(RATIOS), generator=generator)[0]
+            h[i] = w[i] * RATIOS[r1]
+            l[i] = w[i] * RATIOS[r2]
+            aux[i, 0], aux[i, 1] = RATIOS[r1], RATIOS[r2]
+        (x, y, z), (zx, zy, zz) = _seeded_centres(boxes, depth, K, n, l, generator)
+        R = random_rotations(N, n, generator)
+        return _pack(x, y, z, w, h, l, R, [uw, zero, zero, zx, zy, zz], aux)
+    if name == "rotation":                                  # :272-336 == propose without a ground normal
+        o = propose(boxes, depth, prior_mean, prior_std, K, n, None, generator)
+        return dict(cubes=o["cubes"], noise=o["noise"], rot=o["rot"], aux=None)
+    raise ValueError(name)
+
+
+# ----------------------------------------------------------------------------------------------
 # geometry  (cubercnn/util/math_util.py:142-245, ProposalNetwork/utils/spaces.py:192-245,
 #            ProposalNetwork/utils/conversions.py:25-48)
 # ----------------------------------------------------------------------------------------------

@@ -208,10 +208,41 @@ def main():
                         boxes=pbd[0].tensor.numpy(), corners2d=c2d[0].numpy(), iou=s_iou.numpy(), dim=s_dim.numpy(),
                         cor_emptymask=s_cor.numpy(), combined=comb, best=int(np.argmax(comb)),
                         pc_points=pts3.numpy(), pc_cube=unit.numpy(), pc_count=pc_unit)
+    make_variants(ver)
     for fn in sorted(os.listdir(HERE)):
         if fn.endswith(".npz"):
             print(fn, os.path.getsize(os.path.join(HERE, fn)) // 1024, "KiB")
 
 
+VARIANTS = ("random", "xy", "z", "dim", "aspect", "rotation")
+
+
+def make_variants(ver):
+    """the six ablation samplers (proposals.py:20-336) of the UNMODIFIED reference on one C1-shaped frame; the random
+    numbers each consumed are recovered by re-running the oracle's restatement on the same seed (bit-equal cubes asserted)"""
+    fid, H, W, nobj, n = 11, 480, 640, 5, 400
+    f = synth.make_frame(fid, H, W, nobj)
+    fn = dict(random=R.proposals.propose_random, xy=R.proposals.propose_xy_patch, z=R.proposals.propose_z,
+              dim=R.proposals.propose_random_dim, aspect=R.proposals.propose_aspect_ratio,
+              rotation=R.proposals.propose_random_rotation)
+    out = dict(versions=ver, frame_id=fid, H=H, W=W, n_obj=nobj, n=n, input_sha=frame_digest(f))
+    for k, name in enumerate(VARIANTS):
+        seed = 500 + k
+        torch.manual_seed(seed)
+        cubes, _, _ = fn[name](R.Boxes(f.boxes), f.depth, (f.prior_mean, f.prior_std), (W, H), f.K, number_of_proposals=n)
+        torch.manual_seed(seed)
+        o = O.propose_variant(name, f.boxes, f.depth, f.prior_mean, f.prior_std, f.K, (W, H), n)
+        assert torch.equal(o["cubes"], cubes.tensor), "oracle %s diverged from the reference" % name
+        out[name + "_cubes"] = cubes.tensor.numpy()
+        out[name + "_noise"] = o["noise"].numpy()
+        out[name + "_rot"] = o["rot"].numpy()
+        if o["aux"] is not None:
+            out[name + "_aux"] = o["aux"].numpy()
+    np.savez_compressed(os.path.join(HERE, "variants.npz"), **out)
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "variants":
+        make_variants(np.array(str(O.versions())))
+    else:
+        main()

@@ -106,6 +106,71 @@ def test_propose_only_mode(golden_dir):
     assert po.best_idx is None
 
 
+VARIANT_MODES = {"random": (L.CENTRE_UNIFORM, L.DIMS_UNIFORM), "xy": (L.CENTRE_PATCH, L.DIMS_UNIFORM),
+                 "z": (L.CENTRE_PATCH_Z, L.DIMS_UNIFORM), "dim": (L.CENTRE_DEPTH, L.DIMS_UNIFORM),
+                 "aspect": (L.CENTRE_DEPTH, L.DIMS_ASPECT), "rotation": (L.CENTRE_DEPTH, L.DIMS_PRIOR)}
+
+
+@pytest.mark.parametrize("name", sorted(VARIANT_MODES))
+@pytest.mark.parametrize("S", [1, 4])
+def test_ablation_samplers_against_reference_fixture(golden_dir, name, S):
+    """proposals.py:20-336 through the fused kernel's centre / dimension modes, fed the random numbers the reference
+    consumed.  Everything that involves no transcendental is bit-exact (uniform centres, ramps, all dimensions,
+    rotations); depth-seeded centres carry the last-ulp atan2f / sinf difference of the fused kernel (module docstring)."""
+    g = load(golden_dir, "variants.npz")
+    f = frame_of(g)
+    d = dev()
+    n, N = int(g["n"]), int(g["n_obj"])
+    cm, dm = VARIANT_MODES[name]
+    noise = torch.from_numpy(g[name + "_noise"]).permute(1, 0, 2).contiguous().to(d)
+    rot = torch.from_numpy(g[name + "_rot"]).reshape(N, n, 9).contiguous().to(d)
+    aux = torch.from_numpy(g[name + "_aux"]).to(d) if (name + "_aux") in g.files else None
+    o = api.propose_score_select(f.depth[None].to(d), f.K[None].to(d), f.boxes.to(d), f.prior_mean.to(d),
+                                 f.prior_std.to(d), torch.zeros(N, dtype=torch.int32, device=d), None, None, n,
+                                 noise=noise, rot=rot, propose_only=True, cluster_size=S, centre_mode=cm, dims_mode=dm,
+                                 aux=aux, im_shape=(int(g["W"]), int(g["H"])))
+    torch.cuda.synchronize()
+    got, ref = o.all_cubes.cpu().numpy(), g[name + "_cubes"]
+    assert np.array_equal(got[..., 3:], ref[..., 3:]), "dimensions / rotations must be bit-exact"
+    if cm == L.CENTRE_DEPTH:
+        assert np.allclose(got[..., :3], ref[..., :3], rtol=1e-5, atol=1e-6)
+    else:
+        assert np.array_equal(got[..., :3], ref[..., :3]), "centres must be bit-exact"
+
+
+def test_ablation_sampler_mirror_signatures(golden_dir):
+    """the drop-in functions with the argument patterns of roi_heads.py:286-297 (None for what a variant ignores)"""
+    import ProposalNetwork.proposals.proposals as proposals
+    from ProposalNetwork.utils.spaces import boxes_cls
+    g = load(golden_dir, "variants.npz")
+    f = frame_of(g)
+    d = dev()
+    B = boxes_cls()(f.boxes.to(d))
+    n, W, H = 64, int(g["W"]), int(g["H"])
+    K, depth, pri = f.K.to(d), f.depth.to(d), (f.prior_mean.to(d), f.prior_std.to(d))
+    outs = [proposals.propose_random(B, None, None, None, None, number_of_proposals=n),
+            proposals.propose_xy_patch(B, None, None, (W, H), K, number_of_proposals=n),
+            proposals.propose_z(B, depth, None, (W, H), None, number_of_proposals=n),
+            proposals.propose_random_dim(B, depth, pri, None, K, number_of_proposals=n),
+            proposals.propose_random_rotation(B, depth, pri, None, K, number_of_proposals=n),
+            proposals.propose_aspect_ratio(B, depth, pri, None, K, number_of_proposals=n)]
+    for cubes, stats, ranges in outs:
+        assert cubes.tensor.shape == (f.n_obj(), n, 15) and stats is None and ranges is None
+        assert torch.isfinite(cubes.tensor[..., 3:]).all()
+        R = cubes.rotations.reshape(-1, 3, 3)
+        eye = torch.eye(3, device=d).expand_as(R)
+        assert torch.allclose(R @ R.transpose(1, 2), eye, atol=1e-4)
+    # uniform dimensions stay in [MIN_PROP_S, 2]; aspect-ratio rows are w times one of the seven ratios
+    dims = outs[0][0].dimensions
+    assert float(dims.min()) >= 0.05 and float(dims.max()) <= 2.0
+    asp = outs[5][0].dimensions
+    ratio = (asp[..., 1] / asp[..., 0])
+    assert all(min(abs(float(ratio[i, 0]) - r) for r in proposals.RATIOS) < 1e-5 for i in range(f.n_obj()))
+    # propose_z: z ramps between the 10 % and 90 % depth quantiles of the box
+    zc = outs[2][0].centers[..., 2]
+    assert bool((zc[:, 1:] >= zc[:, :-1] - 1e-6).all())
+
+
 @pytest.mark.parametrize("name", ["c1_modeA.npz", "c1_modeB.npz", "c2_randrot.npz"])
 def test_per_function_kernels_on_reference_cubes(golden_dir, name):
     """cubes_to_box / get_bube_corners / score_iou / score_dimensions / score_corners fed the reference's cubes"""
@@ -303,6 +368,37 @@ def test_mask_rect_real_and_random_masks(golden_dir):
     assert bit >= 150
 
 
+@pytest.mark.parametrize("H,W", [(768, 1024), (1080, 1920)])
+def test_mask_rect_large_frames(H, W):
+    """frames whose bitmap no longer fits twice in shared memory (BASELINE configs 3 and 5 shapes): ring-shaped masks
+    with a rival blob force the exact hole-filling pass, speckle forces the overflow pass; all against cv2"""
+    from scipy import ndimage as ndi
+    d = dev()
+    rs = np.random.RandomState(1)
+    yy, xx = np.mgrid[0:H, 0:W]
+    ms = []
+    for t in range(6):
+        cx, cy = rs.uniform(0.3, 0.7) * W, rs.uniform(0.3, 0.7) * H
+        a, b = rs.uniform(0.1, 0.28) * W, rs.uniform(0.1, 0.28) * H
+        ring = (((xx - cx) / a) ** 2 + ((yy - cy) / b) ** 2 <= 1) & ~(((xx - cx) / (0.8 * a)) ** 2 + ((yy - cy) / (0.8 * b)) ** 2 <= 1)
+        m = ring.copy()
+        # a solid rival whose area lies between the ring's hole-free and hole-filled areas
+        s = int(np.sqrt(0.6 * np.pi * a * b))
+        x0 = 0 if cx > W / 2 else W - s
+        m[0:min(s, H), x0:x0 + s] = True
+        ms.append(m)
+    ms.append(ndi.gaussian_filter(rs.randn(H, W), 6) > 0)
+    ms.append(rs.rand(H, W) < 0.3)                                            # speckle -> overflow pass
+    full = np.ones((H, W), bool); full[H // 2, W // 2] = False
+    ms.append(full)                                                           # every row and column occupied
+    rects, has = api.mask_rect(torch.from_numpy(np.stack(ms)).to(d))
+    rects, has = rects.cpu().numpy(), has.cpu().numpy()
+    for t, m in enumerate(ms):
+        ref = O.mask_rect(m.astype(np.uint8))
+        assert has[t] == 1, "mask %d: code %d" % (t, has[t])
+        assert _rect_dev(rects[t], ref) < 1e-3, (t, rects[t], ref)
+
+
 def test_segmentation_and_point_cloud_scores_exact(golden_dir):
     g = load(golden_dir, "c1_modeB.npz")
     f = frame_of(g)
@@ -457,6 +553,98 @@ def test_pipeline_matches_oracle_end_to_end(golden_dir):
     assert np.array_equal(sel.plane_eq[0].cpu().numpy(), g["plane_eq"])
     assert sel.best_idx.cpu().tolist() == g["best"].tolist()
     assert_scores(sel.all.all_scores[:, 3].cpu().numpy(), g["combined"], rtol=2e-5, atol=1e-6, what="combined")
+
+
+def _oracle_chain(f, n, W, H, seed, iters=1000):
+    """the reference's per-frame chain (roi_heads.py:345-505) through the oracle: plane -> normal -> proposals -> mode-A
+    scores -> argmax; returns what the CUDA path needs to replay it with the same random numbers"""
+    import random
+    pg, _ = O.backproject_np(f.depth.numpy(), f.K.numpy(), f.ground.numpy())
+    ids = O.draw_sample_ids(len(pg), iters, random.Random(seed))
+    eq, inl, _ = O.ransac_np(pg, ids, 0.05)
+    nv = O.rectify_normal(np.array(eq[:3]))
+    o = O.propose(f.boxes, f.depth, f.prior_mean, f.prior_std, f.K, n, torch.from_numpy(nv), torch.Generator().manual_seed(seed))
+    c2d = O.project_corners(O.cube_corners(o["cubes"]), f.K, W, H)
+    pb = O.boxes_from_corners(c2d)
+    comb, best = [], []
+    for i in range(f.n_obj()):
+        c, b = O.select(O.iou_score(f.boxes[i], pb[i]),
+                        O.dims_score(f.prior_mean[i], f.prior_std[i], o["cubes"][i, :, 3:6], f.boxes[i], pb[i]),
+                        O.corners_score(f.masks[i], c2d[i]))
+        comb.append(c); best.append(b)
+    return dict(ids=ids, eq=np.array(eq), n_inl=len(inl), normal=nv, noise=o["noise"], yaw_idx=o["yaw_idx"],
+                comb=np.stack(comb), best=best)
+
+
+@pytest.mark.parametrize("cfg,n_obj,n", [("C1", 5, 1000), ("C2", "poisson15", 1000), ("C3", 3, 10000), ("C4", "poisson15", 1000)])
+def test_selection_parity_on_the_named_configs(cfg, n_obj, n):
+    """BASELINE.json configs 1-4 at their frame shapes and proposal counts (C3 with 3 of its 50 objects: the oracle's
+    per-proposal loops take ~1 s per 1000 proposals): scores within 2e-5, identical argmax wherever the oracle's top-2
+    gap exceeds the tolerance, NaN-first semantics identical.  C3's n = 10 000 runs on the 8-CTA cluster path."""
+    c = synth.CONFIGS[cfg]
+    H, W = c["H"], c["W"]
+    fid = {"C1": 21, "C2": 22, "C3": 23, "C4": 9999}[cfg]
+    f = synth.make_frame(fid, H, W, n_obj)
+    r = _oracle_chain(f, n, W, H, seed=fid)
+    d = dev()
+    batch = pipeline.FrameBatch.from_frames([f], d)
+    sel = pipeline.select(batch, n, noise=r["noise"].permute(1, 0, 2).contiguous().to(d),
+                          yaw_idx=r["yaw_idx"].to(torch.int16).to(d),
+                          sample_ids=torch.from_numpy(r["ids"].astype(np.int32))[None].contiguous().to(d), return_all=True)
+    torch.cuda.synchronize()
+    assert int(sel.inlier_count[0]) == r["n_inl"]
+    assert np.allclose(sel.plane_eq[0].cpu().numpy(), r["eq"], rtol=1e-13, atol=0)     # NumPy's norm goes through BLAS
+    assert np.allclose(sel.normal[0].cpu().numpy(), r["normal"], rtol=0, atol=1e-12)
+    comb = sel.all.all_scores[:, 3].cpu().numpy()
+    assert_scores(comb, r["comb"], rtol=2e-5, atol=1e-6, what=cfg + " combined")
+    got = sel.best_idx.cpu().tolist()
+    for i in range(f.n_obj()):
+        ref = r["comb"][i]
+        if np.isnan(ref).any():
+            assert got[i] == int(np.argmax(np.isnan(ref))), "first NaN wins (np.argmax)"
+            continue
+        top2 = np.sort(ref)[-2:]
+        if top2[1] - top2[0] > 2e-5 * abs(top2[1]):
+            assert got[i] == r["best"][i], (cfg, i, got[i], r["best"][i])
+
+
+def test_c5_plane_fit_parity_at_1080p():
+    """BASELINE.json config 5 (back-projection + RANSAC alone at 1920x1080): both flavours against the oracle with the
+    same hypothesis stream -- identical points, best hypothesis, inlier count and normal"""
+    import random
+    c = synth.CONFIGS["C5"]
+    H, W = c["H"], c["W"]
+    d = dev()
+    frames = [synth.make_frame(40 + k, H, W, 6, with_masks=False) for k in range(2)]
+    depth = torch.stack([f.depth for f in frames]).to(d); ground = torch.stack([f.ground for f in frames]).to(d)
+    K = torch.stack([f.K for f in frames]).to(d)
+    # NumPy / pyransac3d flavour (fp64)
+    pts, _, cnt = api.backproject(depth, ground, K, 5, L.BACKPROJECT_NUMPY, want_other=False)
+    ids_all, refs = [], []
+    for k, f in enumerate(frames):
+        pg, _ = O.backproject_np(f.depth.numpy(), f.K.numpy(), f.ground.numpy())
+        assert int(cnt[k, 0]) == len(pg)
+        assert np.array_equal(pts[k, :, :len(pg)].t().cpu().numpy(), pg)
+        ids = O.draw_sample_ids(len(pg), 1000, random.Random(k))
+        eq, inl, best = O.ransac_np(pg, ids, 0.05)
+        ids_all.append(ids); refs.append((np.array(eq), len(inl), O.rectify_normal(np.array(eq[:3]))))
+    ids_t = torch.from_numpy(np.stack(ids_all).astype(np.int32)).contiguous().to(d)
+    r = api.ransac_plane(pts, cnt[:, 0].contiguous(), ids_t, thresh=0.05)
+    for k in range(2):
+        assert np.allclose(r["eq"][k].cpu().numpy(), refs[k][0], rtol=1e-13, atol=0)
+        assert int(r["count"][k]) == refs[k][1]
+        assert np.allclose(r["normal"][k].cpu().numpy(), refs[k][2], rtol=0, atol=1e-12)
+    # torch flavour (fp32, fit_parallel)
+    pts32, _, cnt32 = api.backproject(depth, ground, K, 5, L.BACKPROJECT_TORCH, want_other=False)
+    for k, f in enumerate(frames):
+        po = O.backproject_torch(f.depth, f.K, f.ground)
+        assert int(cnt32[k, 0]) == len(po) and torch.equal(pts32[k, :, :len(po)].t().cpu(), po)
+        ids = O.draw_sample_ids(len(po), 1000, random.Random(100 + k))
+        eq, inl, best, _ = O.ransac_parallel(po, ids, 0.05)
+        r32 = api.ransac_plane(pts32[k:k + 1].contiguous(), cnt32[k:k + 1, 0].contiguous(),
+                               torch.from_numpy(ids.astype(np.int32))[None].contiguous().to(d), thresh=0.05)
+        assert int(r32["count"][0]) == len(inl)
+        assert int(r32["best_iter"][0]) == int(best)
 
 
 def eq_nan(a, b):

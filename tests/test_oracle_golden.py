@@ -138,3 +138,18 @@ def test_degenerate_semantics(golden_dir):
     # the fixture holds what the unmodified reference returns, and that is what parity means here
     pc = O.point_cloud_score(torch.from_numpy(g["pc_points"]), torch.from_numpy(g["pc_cube"])[0])
     assert pc.numpy().tolist() == g["pc_count"].tolist() == [0]
+
+
+VARIANTS = ("random", "xy", "z", "dim", "aspect", "rotation")
+
+
+@pytest.mark.parametrize("k", range(len(VARIANTS)))
+def test_ablation_samplers(golden_dir, k):
+    """proposals.py:20-336: the oracle's restatement reproduces the reference's cubes bit for bit from the same seed"""
+    name = VARIANTS[k]
+    g = _load(golden_dir, "variants.npz")
+    f = _frame(g)
+    torch.manual_seed(500 + k)
+    o = O.propose_variant(name, f.boxes, f.depth, f.prior_mean, f.prior_std, f.K, (int(g["W"]), int(g["H"])), int(g["n"]))
+    assert np.array_equal(o["cubes"].numpy(), g[name + "_cubes"])
+    assert np.array_equal(o["noise"].numpy(), g[name + "_noise"])
