@@ -14,6 +14,9 @@ FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std
          "-Xcompiler", "-fPIC", "-Wno-deprecated-gpu-targets"]   # IEEE div/sqrt, no fast-math: parity first
 
 
+EXTRA = os.environ.get("TDOD_NVCC_FLAGS", "").split()   # experiments only, e.g. -DTDOD_PSS_MINBLOCKS=3
+
+
 def sources():
     return sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cu"))
 
@@ -35,7 +38,7 @@ def build(force=False, verbose=False):
     procs = []
     for src in sources():
         obj = os.path.join(bdir, os.path.basename(src)[:-3] + ".o")
-        cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
+        cmd = [NVCC] + FLAGS + EXTRA + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
         objs.append(obj)
     for src, p in procs:

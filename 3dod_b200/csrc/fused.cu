@@ -20,6 +20,9 @@ namespace {
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
 constexpr int kMaxCluster = 8;
+#ifndef TDOD_PSS_MINBLOCKS
+#define TDOD_PSS_MINBLOCKS 3
+#endif
 
 struct Mail {               // per-CTA mailbox read by every CTA of the cluster through DSMEM
     int hist[4][3][256];    // radix-select histograms, one buffer per pass (no WAR hazard)
@@ -206,7 +209,7 @@ template <> struct ClusterCtx<false> {
 };
 
 template <bool kCluster>
-__global__ void __launch_bounds__(kThreads, 2) pss_kernel(const tdod_pss_args a, const int n_loc) {
+__global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const tdod_pss_args a, const int n_loc) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     ClusterCtx<kCluster> cl;
     const int S = cl.size();

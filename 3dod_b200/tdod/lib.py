@@ -7,7 +7,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libtdod.so")
+LIB_PATH = os.environ.get("TDOD_LIB", os.path.join(_HERE, "libtdod.so"))   # TDOD_LIB: A/B builds while tuning
 
 RNG_HOST, RNG_PHILOX = 0, 1
 BACKPROJECT_NUMPY, BACKPROJECT_TORCH = 0, 1

@@ -8,6 +8,8 @@ import sys
 rep = sys.argv[1]
 top = int(sys.argv[2]) if len(sys.argv) > 2 else 20
 flt = sys.argv[3] if len(sys.argv) > 3 else ""
+col = sys.argv[4] if len(sys.argv) > 4 else "# Samples"     # e.g. "Instructions Executed"
+kflt = sys.argv[5] if len(sys.argv) > 5 else ""           # substring of the kernel name
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
 secs, cur = [], None
@@ -23,9 +25,9 @@ for r in rows:
     elif cur is not None:
         cur["rows"].append(r)
 for s in secs:
-    if "hdr" not in s or flt not in s["file"]:
+    if "hdr" not in s or flt not in s["file"] or kflt not in s.get("fn", ""):
         continue
-    H = s["hdr"]; si = H.index("# Samples")
+    H = s["hdr"]; si = H.index(col)
     agg = collections.OrderedDict()
     for r in s["rows"]:
         if len(r) <= si or not r[si].isdigit() or not r[0]:
