@@ -6,6 +6,7 @@
 // few points per thread in registers, streams the hypotheses from shared memory and counts inliers with
 // warp ballots.
 #include <cstdlib>
+#include <cooperative_groups.h>
 #include "tdod_device.cuh"
 #include "tdod_internal.h"
 
@@ -35,22 +36,77 @@ template <> struct Ar<double> {
 };
 
 // ------------------------------------------------------------------------------------------------
-// back-projection with row-major ordered compaction (one CTA per frame)
+// back-projection with row-major ordered compaction: one cluster of kBpCluster CTAs per frame.
+// CTA `rank` owns the contiguous slice [rank * per, (rank + 1) * per) of the strided grid.  Pass A reads only the
+// ground samples and counts "on" / "off" points per (iteration, warp); the slice totals are exchanged through
+// distributed shared memory, so every CTA knows where its slice starts in the two compacted outputs; pass B reads
+// depth (once) and ground (again, now from L1/L2), back-projects and writes each point at its final position.
 // ------------------------------------------------------------------------------------------------
+constexpr int kBpCluster = 8;
+constexpr int kBpT = 512;
+
 template <typename T, int FLAVOUR>
-__global__ void __launch_bounds__(1024) backproject_kernel(const float* __restrict__ depth,
-                                                           const uint8_t* __restrict__ ground,
-                                                           const float* __restrict__ Kall, int H, int W, int stride,
-                                                           T* __restrict__ plane_pts, T* __restrict__ other_pts,
-                                                           int32_t* __restrict__ counts) {
-    __shared__ int warp_on[32], warp_off[32];
-    __shared__ int base_on, base_off;
-    const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+__global__ void __cluster_dims__(kBpCluster, 1, 1) __launch_bounds__(kBpT)
+    backproject_kernel(const float* __restrict__ depth, const uint8_t* __restrict__ ground, const float* __restrict__ Kall,
+                       int H, int W, int stride, int iters, T* __restrict__ plane_pts, T* __restrict__ other_pts,
+                       int32_t* __restrict__ counts) {
+    extern __shared__ int bp_cnt[];            // [iters][kBpT/32] "on" counts, then the same for "off"; later their exclusive scans
+    __shared__ int s_tot[2];                   // this CTA's totals, read by the whole cluster
+    __shared__ int s_base[2];
+    namespace cgx = cooperative_groups;
+    cgx::cluster_group cl = cgx::this_cluster();
+    constexpr int kW = kBpT / 32;
+    const int rank = (int)cl.block_rank();
+    const int f = blockIdx.x / kBpCluster, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int Hs = (H + stride - 1) / stride, Ws = (W + stride - 1) / stride;
     const int64_t P = (int64_t)Hs * Ws;
+    const int64_t per = (int64_t)iters * kBpT;
+    const int64_t lo = rank * per, hi = min(P, lo + per);
     const float* K = Kall + (size_t)f * 9;
     const float* dp = depth + (size_t)f * H * W;
     const uint8_t* gp = ground ? ground + (size_t)f * H * W : nullptr;
+    int* c_on = bp_cnt;
+    int* c_off = bp_cnt + iters * kW;
+    // ---- pass A: counts ----
+    for (int it = 0; it < iters; ++it) {
+        const int64_t idx = lo + (int64_t)it * kBpT + tid;
+        const bool valid = idx < hi;
+        bool on = valid;
+        if (valid && gp) {
+            const int v = (int)(idx / Ws), u = (int)(idx - (int64_t)v * Ws);
+            on = __ldg(gp + (size_t)(v * stride) * W + (size_t)(u * stride)) > 0;
+        }
+        const unsigned m_on = __ballot_sync(0xffffffffu, valid && on), m_off = __ballot_sync(0xffffffffu, valid && !on);
+        if (lane == 0) { c_on[it * kW + wid] = __popc(m_on); c_off[it * kW + wid] = __popc(m_off); }
+    }
+    __syncthreads();
+    // exclusive scan of the iters * kW entries of each list: warp 0 scans "on", warp 1 scans "off"
+    if (wid < 2) {
+        int* c = wid == 0 ? c_on : c_off;
+        const int n = iters * kW;
+        int carry = 0;
+        for (int b0 = 0; b0 < n; b0 += 32) {
+            const int v = (b0 + lane < n) ? c[b0 + lane] : 0;
+            int inc = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += t;
+            }
+            if (b0 + lane < n) c[b0 + lane] = carry + inc - v;
+            carry += __shfl_sync(0xffffffffu, inc, 31);
+        }
+        if (lane == 0) s_tot[wid] = carry;
+    }
+    cl.sync();
+    if (tid < 2) {
+        int base = 0;
+        for (int r = 0; r < rank; ++r) base += *cl.map_shared_rank(&s_tot[tid], r);
+        s_base[tid] = base;
+        if (rank == kBpCluster - 1) counts[2 * f + tid] = base + s_tot[tid];
+    }
+    __syncthreads();
+    // ---- pass B: back-project and write in place ----
     T fx, fy, cx, cy;
     if (FLAVOUR == TDOD_BACKPROJECT_NUMPY) {   // roi_heads.py:347-352: full-resolution intrinsics
         fx = (T)K[0]; fy = (T)K[4]; cx = (T)K[2]; cy = (T)K[5];
@@ -60,43 +116,33 @@ __global__ void __launch_bounds__(1024) backproject_kernel(const float* __restri
     }
     T* po = plane_pts + (size_t)f * 3 * P;
     T* oo = other_pts ? other_pts + (size_t)f * 3 * P : nullptr;
-    if (tid == 0) { base_on = 0; base_off = 0; }
-    __syncthreads();
-    for (int64_t start = 0; start < P; start += 1024) {
-        const int64_t idx = start + tid;
-        bool valid = idx < P, on = false;
+    const int base_on = s_base[0], base_off = s_base[1];
+    const unsigned lt = (1u << lane) - 1u;
+    for (int it = 0; it < iters; ++it) {
+        const int64_t idx = lo + (int64_t)it * kBpT + tid;
+        const bool valid = idx < hi;
+        bool on = valid;
         T x = 0, y = 0, z = 0;
         if (valid) {
             const int v = (int)(idx / Ws), u = (int)(idx - (int64_t)v * Ws);
             const size_t pix = (size_t)(v * stride) * W + (size_t)(u * stride);
-            z = (T)__ldg(dp + pix);
-            x = Ar<T>::div(Ar<T>::mul(Ar<T>::sub((T)u, cx), z), fx);
-            y = Ar<T>::div(Ar<T>::mul(Ar<T>::sub((T)v, cy), z), fy);
-            on = gp ? (__ldg(gp + pix) > 0) : true;
+            if (gp) on = __ldg(gp + pix) > 0;
+            if (on || oo) {
+                z = (T)__ldg(dp + pix);
+                x = Ar<T>::div(Ar<T>::mul(Ar<T>::sub((T)u, cx), z), fx);
+                y = Ar<T>::div(Ar<T>::mul(Ar<T>::sub((T)v, cy), z), fy);
+            }
         }
-        const unsigned m_on = __ballot_sync(0xffffffffu, valid && on);
-        const unsigned m_off = __ballot_sync(0xffffffffu, valid && !on);
-        if (lane == 0) { warp_on[wid] = __popc(m_on); warp_off[wid] = __popc(m_off); }
-        __syncthreads();
-        int pre_on = base_on, pre_off = base_off;
-        for (int w = 0; w < wid; ++w) { pre_on += warp_on[w]; pre_off += warp_off[w]; }
-        const unsigned lt = (1u << lane) - 1u;
+        const unsigned m_on = __ballot_sync(0xffffffffu, valid && on), m_off = __ballot_sync(0xffffffffu, valid && !on);
         if (valid && on) {
-            const int p = pre_on + __popc(m_on & lt);
+            const int p = base_on + c_on[it * kW + wid] + __popc(m_on & lt);
             po[p] = x; po[P + p] = y; po[2 * P + p] = z;
         } else if (valid && oo) {
-            const int p = pre_off + __popc(m_off & lt);
+            const int p = base_off + c_off[it * kW + wid] + __popc(m_off & lt);
             oo[p] = x; oo[P + p] = y; oo[2 * P + p] = z;
         }
-        __syncthreads();
-        if (tid == 0) {
-            int a = 0, b = 0;
-            for (int w = 0; w < 32; ++w) { a += warp_on[w]; b += warp_off[w]; }
-            base_on += a; base_off += b;
-        }
-        __syncthreads();
     }
-    if (tid == 0) { counts[2 * f] = base_on; counts[2 * f + 1] = base_off; }
+    cl.sync();   // nobody leaves while a peer may still read its totals
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -481,14 +527,25 @@ extern "C" int tdod_backproject(const float* depth, const uint8_t* ground, const
     if (!depth || !K || !plane_pts || !counts || F < 0 || H <= 0 || W <= 0 || stride <= 0)
         return tdod_fail(TDOD_EINVAL, "tdod_backproject: bad argument");
     cudaStream_t st = (cudaStream_t)stream;
-    if (flavour == TDOD_BACKPROJECT_NUMPY)
-        backproject_kernel<double, TDOD_BACKPROJECT_NUMPY><<<F, 1024, 0, st>>>(depth, ground, K, H, W, stride,
-                                                                                (double*)plane_pts, (double*)other_pts, counts);
-    else if (flavour == TDOD_BACKPROJECT_TORCH)
-        backproject_kernel<float, TDOD_BACKPROJECT_TORCH><<<F, 1024, 0, st>>>(depth, ground, K, H, W, stride,
-                                                                              (float*)plane_pts, (float*)other_pts, counts);
-    else
+    const int64_t P = (int64_t)((H + stride - 1) / stride) * ((W + stride - 1) / stride);
+    const int iters = (int)((P + (int64_t)kBpCluster * kBpT - 1) / ((int64_t)kBpCluster * kBpT));
+    const size_t smem = (size_t)2 * iters * (kBpT / 32) * sizeof(int);
+    if (smem > 200 * 1024) return tdod_fail(TDOD_ERANGE, "tdod_backproject: frame too large for the per-slice count tables");
+    const unsigned grid = (unsigned)F * kBpCluster;
+    cudaError_t e;
+    if (flavour == TDOD_BACKPROJECT_NUMPY) {
+        e = cudaFuncSetAttribute(backproject_kernel<double, TDOD_BACKPROJECT_NUMPY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+        backproject_kernel<double, TDOD_BACKPROJECT_NUMPY><<<grid, kBpT, smem, st>>>(depth, ground, K, H, W, stride, iters,
+                                                                                      (double*)plane_pts, (double*)other_pts, counts);
+    } else if (flavour == TDOD_BACKPROJECT_TORCH) {
+        e = cudaFuncSetAttribute(backproject_kernel<float, TDOD_BACKPROJECT_TORCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+        backproject_kernel<float, TDOD_BACKPROJECT_TORCH><<<grid, kBpT, smem, st>>>(depth, ground, K, H, W, stride, iters,
+                                                                                    (float*)plane_pts, (float*)other_pts, counts);
+    } else {
         return tdod_fail(TDOD_EINVAL, "tdod_backproject: unknown flavour");
+    }
     TDOD_CHECK_LAUNCH();
     return TDOD_OK;
 }

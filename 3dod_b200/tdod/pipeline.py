@@ -103,7 +103,7 @@ def _side_stream(dev):
 
 def select(batch, n_prop, seed=0, noise=None, yaw_idx=None, rot=None, sample_ids=None, use_ground=True,
            ransac_iters=1000, ransac_thresh=0.05, flavour=L.BACKPROJECT_NUMPY, obj_id_base=0, frame_id_base=0,
-           return_all=False, cluster_size=0, overlap=True, marks=None):
+           return_all=False, cluster_size=0, overlap=True, marks=None, iou_boxes=None):
     """Mode A (roi_heads.py:493-505) for every object of a device-resident batch.  Throughput RNG (in-kernel
     Philox keyed by global object id) unless `noise` (+ `yaw_idx` / `rot`) hands in host-drawn numbers.
     Launches only; does not synchronise.
@@ -146,7 +146,8 @@ def select(batch, n_prop, seed=0, noise=None, yaw_idx=None, rot=None, sample_ids
     o = api.propose_score_select(batch.depth, batch.K, batch.boxes, batch.prior_mean, batch.prior_std,
                                  batch.obj_frame, s.rects, s.has_rect, n_prop, yaw_tab=yaw_tab, noise=noise,
                                  yaw_idx=yaw_idx, rot=rot, seed=None if noise is not None else seed,
-                                 obj_id_base=obj_id_base, return_all=return_all, cluster_size=cluster_size)
+                                 obj_id_base=obj_id_base, return_all=return_all, cluster_size=cluster_size,
+                                 iou_boxes=iou_boxes)
     mark("kc1", main)
     s.best_idx, s.best_score, s.best_cube, s.best_box = o.best_idx, o.best_score, o.best_cube, o.best_box
     s.all = o if return_all else None

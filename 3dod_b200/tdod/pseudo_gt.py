@@ -1,0 +1,137 @@
+"""Pseudo-ground-truth generation on top of the batched path.
+
+`forward_pseudo` is the batched form of the `pseudo_gt == 'pseudo'` branch of ROIHeads_Boxer._forward_cube
+(cubercnn/modeling/roi_heads/roi_heads.py:453-489): one `pipeline.select` call for many frames instead of a Python loop
+over objects, returning per frame the fields the reference stores on its `Instances` (:480-487).
+
+`PseudoGTWriter` streams those winners into the Omni3D annotation schema the reference dumps in one piece at the end of
+`tools/eval_boxes.py:622-662` (image record :646, annotation record :648-653) -- here frame by frame into a JSON-lines
+part file with a resume point, so an interrupted 10k-frame run continues where it stopped; `finalize` writes the same
+single JSON document ({info, categories, images, annotations}) the training data loader reads
+(cubercnn/data/datasets.py:418-432)."""
+import json
+import os
+
+import torch
+
+from . import api, pipeline
+
+
+def forward_pseudo(batch, n_prop, seed=0, iou_boxes=None, box_from_object0=True, obj_id_base=0, frame_id_base=0, **kw):
+    """batch: pipeline.FrameBatch on the device.  Returns (fields, selection) where fields is a dict of device tensors
+    over all N objects: pred_boxes [N,4], scores [N], pred_bbox3D [N,8,3], pred_center_cam [N,3], pred_dimensions [N,3],
+    pred_pose [N,3,3], pred_center_2D [N,2] (roi_heads.py:480-487).
+
+    iou_boxes: [N,4] boxes the IoU term is scored against (the reference projects the GT cube, :466); default = the
+    2D boxes.  box_from_object0 reproduces the reference's quirk that the winner's 2D box is read from the proposals of
+    the frame's FIRST object at the winning index (`pred_boxes[0][highest_score]`, :476); False returns the winner's own."""
+    need_all = bool(box_from_object0)
+    sel = pipeline.select(batch, n_prop, seed=seed, obj_id_base=obj_id_base, frame_id_base=frame_id_base,
+                          return_all=need_all, iou_boxes=iou_boxes, **kw)
+    cubes = sel.best_cube
+    boxes = sel.best_box
+    if box_from_object0:
+        # first object of each object's frame: objects are stored frame by frame, so it is the first index with that frame id
+        of = batch.obj_frame.long()
+        first = torch.zeros(batch.n_frames, dtype=torch.long, device=of.device)
+        idx = torch.arange(of.numel(), device=of.device)
+        first.scatter_reduce_(0, of, idx, reduce="amin", include_self=False)
+        boxes = sel.all.all_boxes[first[of], sel.best_idx.long()]
+    fields = dict(pred_boxes=boxes, scores=sel.best_score, pred_bbox3D=api.cube_corners(cubes),
+                  pred_center_cam=cubes[:, 0:3], pred_dimensions=cubes[:, 3:6], pred_pose=cubes[:, 6:15].reshape(-1, 3, 3),
+                  pred_center_2D=(boxes[:, :2] + boxes[:, 2:]) / 2)
+    return fields, sel
+
+
+def annotation(ann_id, image_id, dataset_id, category_id, category_name, bbox2d, center, dims, bbox3d, rot):
+    """one record of tools/eval_boxes.py:648-653 (field names, constants and order as the reference writes them)"""
+    return {'behind_camera': False, 'truncation': 0, 'bbox2D_proj': bbox2d, 'bbox2D_tight': -1, 'visibility': 1.0,
+            'segmentation_pts': -1, 'lidar_pts': -1, 'valid3D': True, 'category_id': category_id,
+            'category_name': category_name, 'id': ann_id, 'image_id': image_id, 'dataset_id': dataset_id,
+            'depth_error': -1, 'center_cam': center, 'dimensions': dims, 'bbox3D_cam': bbox3d, 'R_cam': rot}
+
+
+def image_record(image_id, width, height, file_path, K):
+    """tools/eval_boxes.py:646"""
+    return {'width': width, 'height': height, 'file_path': file_path, 'K': K, 'src_90_rotate': False,
+            'src_flagged': False, 'incomplete': False, 'id': image_id, 'dataset_id': 12}
+
+
+class PseudoGTWriter:
+    """Append-only part file `<path>.part.jsonl` (one line per frame: {"image": ..., "annotations": [...]}), fsync'ed per
+    flush; `done_images` is the resume point.  Annotation ids continue from the part file (reference: one global
+    counter starting at 1, eval_boxes.py:622)."""
+
+    def __init__(self, path, info, categories, resume=True):
+        self.path = path
+        self.part = path + ".part.jsonl"
+        self.info, self.categories = info, categories
+        self.done_images = []
+        self.next_id = 1
+        if resume and os.path.exists(self.part):
+            good = 0
+            with open(self.part, "rb") as f:
+                for line in f:
+                    try:
+                        rec = json.loads(line)
+                    except ValueError:
+                        break                      # torn last line of an interrupted run
+                    if not line.endswith(b"\n"):
+                        break
+                    self.done_images.append(rec["image"]["id"])
+                    if rec["annotations"]:
+                        self.next_id = rec["annotations"][-1]["id"] + 1
+                    good += len(line)
+            with open(self.part, "r+b") as f:      # drop a torn tail
+                f.truncate(good)
+        elif os.path.exists(self.part):
+            os.remove(self.part)
+        self._f = open(self.part, "ab")
+
+    def add_frame(self, image, anns):
+        """image: image_record(...); anns: list of dicts from `annotation` WITHOUT ids (assigned here, in order)"""
+        for a in anns:
+            a['id'] = self.next_id
+            self.next_id += 1
+        self._f.write((json.dumps({"image": image, "annotations": anns}) + "\n").encode())
+        self.done_images.append(image["id"])
+
+    def flush(self):
+        self._f.flush()
+        os.fsync(self._f.fileno())
+
+    def finalize(self):
+        """the reference's single document (eval_boxes.py:658-661)"""
+        self.flush()
+        self._f.close()
+        images, anns = [], []
+        with open(self.part, "rb") as f:
+            for line in f:
+                rec = json.loads(line)
+                images.append(rec["image"])
+                anns.extend(rec["annotations"])
+        doc = {"categories": self.categories, "info": self.info, "images": images, "annotations": anns}
+        tmp = self.path + ".tmp"
+        with open(tmp, "w") as f:
+            json.dump(doc, f)
+        os.replace(tmp, self.path)
+        os.remove(self.part)
+        return doc
+
+
+def write_frames(writer, fields, obj_off, frame_meta, class_ids, class_names, dataset_id=12):
+    """fields: forward_pseudo's dict (device tensors, N objects); obj_off: CSR [F+1]; frame_meta: list of
+    dict(id, width, height, file_path, K) per frame; class_ids / class_names: per-object category id / name.
+    One device->host copy per field for the whole batch, then pure Python."""
+    host = {k: v.detach().cpu().tolist() for k, v in fields.items()}
+    done = set(writer.done_images)
+    for f, meta in enumerate(frame_meta):
+        if meta["id"] in done:
+            continue
+        anns = []
+        for i in range(obj_off[f], obj_off[f + 1]):
+            anns.append(annotation(None, meta["id"], dataset_id, class_ids[i], class_names[i], host["pred_boxes"][i],
+                                   host["pred_center_cam"][i], host["pred_dimensions"][i], host["pred_bbox3D"][i],
+                                   host["pred_pose"][i]))
+        writer.add_frame(image_record(meta["id"], meta["width"], meta["height"], meta["file_path"], meta["K"]), anns)
+    writer.flush()

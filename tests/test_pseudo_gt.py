@@ -1,0 +1,91 @@
+"""Pseudo-GT wire format and resume: schema of tools/eval_boxes.py:646-661, append / torn-tail /
+resume behaviour of the writer on CPU; the batched forward that feeds it is checked on the GPU against the per-object
+path (roi_heads.py:453-489)."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from tdod import pseudo_gt as PG
+
+ANN_KEYS = ['behind_camera', 'truncation', 'bbox2D_proj', 'bbox2D_tight', 'visibility', 'segmentation_pts', 'lidar_pts',
+            'valid3D', 'category_id', 'category_name', 'id', 'image_id', 'dataset_id', 'depth_error', 'center_cam',
+            'dimensions', 'bbox3D_cam', 'R_cam']          # eval_boxes.py:648-653, in the reference's order
+IMG_KEYS = ['width', 'height', 'file_path', 'K', 'src_90_rotate', 'src_flagged', 'incomplete', 'id', 'dataset_id']
+
+
+def _fake_fields(n, seed):
+    g = torch.Generator().manual_seed(seed)
+    r = lambda *s: torch.rand(*s, generator=g)
+    return dict(pred_boxes=r(n, 4), scores=r(n), pred_bbox3D=r(n, 8, 3), pred_center_cam=r(n, 3),
+                pred_dimensions=r(n, 3), pred_pose=r(n, 3, 3), pred_center_2D=r(n, 2))
+
+
+def _meta(fid):
+    return dict(id=1000 + fid, width=730, height=530, file_path="SUNRGBD/%05d.jpg" % fid, K=[[657.0, 0, 365.0], [0, 657.0, 265.0], [0, 0, 1]])
+
+
+def _run(path, frames, resume, stop_after=None):
+    w = PG.PseudoGTWriter(path, {"id": 12, "name": "SUNRGBD Train"}, [{"id": 18, "name": "chair"}], resume=resume)
+    for k, fid in enumerate(frames):
+        if stop_after is not None and k == stop_after:
+            w.flush()
+            return None
+        n = 2 + fid % 3
+        PG.write_frames(w, _fake_fields(n, fid), [0, n], [_meta(fid)], [18] * n, ["chair"] * n)
+    return w.finalize()
+
+
+def test_schema_matches_the_reference_records(tmp_path):
+    doc = _run(str(tmp_path / "a.json"), range(4), resume=False)
+    assert list(doc) == ["categories", "info", "images", "annotations"]
+    assert all(list(a) == ANN_KEYS for a in doc["annotations"])
+    assert all(list(i) == IMG_KEYS for i in doc["images"])
+    assert [a["id"] for a in doc["annotations"]] == list(range(1, len(doc["annotations"]) + 1))   # one global counter from 1
+    a = doc["annotations"][0]
+    assert np.array(a["bbox3D_cam"]).shape == (8, 3) and np.array(a["R_cam"]).shape == (3, 3)
+    assert len(a["center_cam"]) == 3 and len(a["dimensions"]) == 3 and len(a["bbox2D_proj"]) == 4
+    assert json.load(open(tmp_path / "a.json")) == doc
+    assert not os.path.exists(str(tmp_path / "a.json") + ".part.jsonl")
+
+
+def test_resume_after_interruption_gives_the_same_document(tmp_path):
+    whole = _run(str(tmp_path / "w.json"), range(7), resume=False)
+    p = str(tmp_path / "r.json")
+    assert _run(p, range(7), resume=False, stop_after=3) is None
+    with open(p + ".part.jsonl", "ab") as f:                 # a torn line, as a killed process leaves it
+        f.write(b'{"image": {"id": 99')
+    w = PG.PseudoGTWriter(p, {}, [], resume=True)
+    assert w.done_images == [1000, 1001, 1002]
+    w._f.close()
+    resumed = _run(p, range(7), resume=True)                  # frames 0-2 are skipped, ids continue
+    assert resumed == whole
+
+
+@pytest.mark.gpu
+def test_batched_forward_equals_per_object_path():
+    """forward_pseudo over several frames == roi_heads.py:453-489 frame by frame (same Philox keys), including the
+    `pred_boxes[0][highest_score]` quirk for the 2D box"""
+    from tdod import api, pipeline, synth
+    d = torch.device("cuda:0")
+    frames = synth.make_frames("C2", range(3))
+    batch = pipeline.FrameBatch.from_frames(frames, d)
+    off = np.cumsum([0] + [f.n_obj() for f in frames]).tolist()
+    fields, sel = PG.forward_pseudo(batch, 1000, seed=4)
+    own, _ = PG.forward_pseudo(batch, 1000, seed=4, box_from_object0=False)
+    torch.cuda.synchronize()
+    assert torch.equal(own["pred_center_cam"], fields["pred_center_cam"])
+    for f in range(3):
+        b1 = pipeline.FrameBatch.from_frames([frames[f]], d)
+        s1 = pipeline.select(b1, 1000, seed=4, obj_id_base=off[f], frame_id_base=f, return_all=True)
+        torch.cuda.synchronize()
+        sl = slice(off[f], off[f + 1])
+        assert torch.equal(s1.best_idx, sel.best_idx[sl])
+        assert torch.equal(s1.best_cube[:, :3], fields["pred_center_cam"][sl])
+        assert torch.equal(api.cube_corners(s1.best_cube), fields["pred_bbox3D"][sl])
+        quirk = s1.all.all_boxes[0, s1.best_idx.long()]                      # object 0's proposals at each winner's index
+        assert torch.equal(quirk, fields["pred_boxes"][sl])
+        eq = (s1.best_box == own["pred_boxes"][sl]) | (s1.best_box.isnan() & own["pred_boxes"][sl].isnan())
+        assert bool(eq.all())
