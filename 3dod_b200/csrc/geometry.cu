@@ -268,3 +268,36 @@ extern "C" int tdod_yaw_table(const void* normals, int normals_f64, int F, float
     TDOD_CHECK_LAUNCH();
     return TDOD_OK;
 }
+
+// ---- depth / ground map ingest: PIL NEAREST resize on the device (cubercnn/data/dataset_mapper.py:125-147) --------------
+// Pillow's nearest resize steps through the source with a double-precision accumulator (xx = 0.5*s; xx += s); the caller
+// builds the two index tables that way on the host (tdod/ingest.py) and the kernel is a pure gather: every output
+// element written once, coalesced; the source rows it touches are read through L1/L2.
+namespace {
+template <typename E>
+__global__ void __launch_bounds__(256) resize_nearest_kernel(const E* __restrict__ src, int h, int w, const int32_t* __restrict__ xmap,
+                                                             const int32_t* __restrict__ ymap, E* __restrict__ dst, int H, int W) {
+    const int f = blockIdx.z, y = blockIdx.y;
+    const E* s = src + ((size_t)f * h + ymap[y]) * w;
+    E* d = dst + ((size_t)f * H + y) * W;
+    for (int x = blockIdx.x * blockDim.x + threadIdx.x; x < W; x += gridDim.x * blockDim.x) d[x] = __ldg(s + xmap[x]);
+}
+}  // namespace
+
+extern "C" int tdod_resize_nearest(const void* src, int elem_bytes, int F, int h, int w, const int32_t* xmap, const int32_t* ymap,
+                                   void* dst, int H, int W, void* stream) {
+    if (F == 0) return TDOD_OK;
+    if (!src || !dst || !xmap || !ymap || F < 0 || h <= 0 || w <= 0 || H <= 0 || W <= 0)
+        return tdod_fail(TDOD_EINVAL, "tdod_resize_nearest: bad argument");
+    if (H > 65535 || F > 65535) return tdod_fail(TDOD_ERANGE, "tdod_resize_nearest: H and F are grid dimensions (<= 65535)");
+    const dim3 grid((unsigned)((W + 255) / 256), (unsigned)H, (unsigned)F);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (elem_bytes == 4)
+        resize_nearest_kernel<uint32_t><<<grid, 256, 0, st>>>((const uint32_t*)src, h, w, xmap, ymap, (uint32_t*)dst, H, W);
+    else if (elem_bytes == 1)
+        resize_nearest_kernel<uint8_t><<<grid, 256, 0, st>>>((const uint8_t*)src, h, w, xmap, ymap, (uint8_t*)dst, H, W);
+    else
+        return tdod_fail(TDOD_EINVAL, "tdod_resize_nearest: elem_bytes must be 1 or 4");
+    TDOD_CHECK_LAUNCH();
+    return TDOD_OK;
+}

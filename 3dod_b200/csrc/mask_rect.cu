@@ -20,6 +20,7 @@
 // ~36 KB of shared memory) to keep 4+ masks per SM in flight and overlap their serial tails.  Pass 1 decides every
 // mask whose winner is certain from bounds (area without hole filling <= true area <= bounding box); pass 2 fills
 // holes exactly for the ambiguous rest; pass 3 handles speckle masks whose runs outgrow shared memory.
+#include <cstdlib>
 #include "tdod_device.cuh"
 #include "tdod_internal.h"
 
@@ -27,7 +28,16 @@ using namespace tdod;
 
 namespace {
 
-constexpr int kT = 256;          // threads of the rectangle kernels
+#ifndef TDOD_KB_T
+#define TDOD_KB_T 256
+#endif
+#ifndef TDOD_KB_MINB
+#define TDOD_KB_MINB 4
+#endif
+#ifndef TDOD_KB_RUNCAP
+#define TDOD_KB_RUNCAP 2048
+#endif
+constexpr int kT = TDOD_KB_T;    // threads of the rectangle kernels
 constexpr int kPackT = 256;      // threads of the pack kernel
 constexpr int kPackRows = 32;    // mask rows per pack tile
 
@@ -38,7 +48,7 @@ __device__ long long g_kb_t[32 * 8192];
 #else
 #define KB_T(k) do { } while (0)
 #endif
-constexpr int kRunCap = 2048;     // runs per mask held in shared memory (more -> the global-memory overflow pass)
+constexpr int kRunCap = TDOD_KB_RUNCAP;     // runs per mask held in shared memory (more -> the global-memory overflow pass)
 
 struct RunSet {                   // shared-memory views
     uint16_t* xs; uint16_t* xe; uint16_t* row;
@@ -47,16 +57,19 @@ struct RunSet {                   // shared-memory views
 };
 
 __device__ __forceinline__ uint32_t nz_bits16(const uint4 v) {
-    // 16 mask bytes -> 16 bits (bit i = byte i != 0)
-    uint32_t out = 0;
+    // 16 mask bytes -> 16 bits (bit i = byte i != 0).  Per word: bit 7 of every byte := (byte != 0) (three logic / add
+    // operations), then one multiply gathers the four flags into the top nibble: flag j sits at bit 8j+7 and the
+    // multiplier 2^21 + 2^14 + 2^7 + 1 moves it to bit 28+j; all partial products land on distinct bits, so no carry
+    // reaches the nibble.
     const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t p[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         const uint32_t t = w[k];
         const uint32_t hi = (t | ((t & 0x7f7f7f7fu) + 0x7f7f7f7fu)) & 0x80808080u;
-        out |= ((((hi >> 7) * 0x00204081u) >> 21) & 0xFu) << (4 * k);
+        p[k] = hi * 0x00204081u;
     }
-    return out;
+    return (p[0] >> 28) | ((p[1] >> 24) & 0xF0u) | ((p[2] >> 20) & 0xF00u) | ((p[3] >> 16) & 0xF000u);
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -113,6 +126,115 @@ __global__ void __launch_bounds__(kPackT, 8) pack_kernel(const uint8_t* __restri
         if ((tid & 31) == 0 && hi >= 0) { atomicMin(&s_lo, lo); atomicMax(&s_hi, hi); }
         __syncthreads();
         if (tid == 0 && s_hi >= 0) {                            // rowrange[m] = {first row, H-1-last row}, both via atomicMin
+            atomicMin(&rowrange[2 * m], s_lo);
+            atomicMin(&rowrange[2 * m + 1], H - 1 - s_hi);
+        }
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// pack, TMA-staged: the same tiles, but the raw bytes of tile k+1 are brought into shared memory by one bulk
+// asynchronous copy (cp.async.bulk, completion on an mbarrier) while the CTA turns tile k into bits.  Loads are no
+// longer tied to registers or to the instruction stream of the packing code, so HBM stays busy across the barriers
+// of the packing phases.  Two raw buffers per CTA; used whenever they fit in shared memory.
+// ------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* b, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_load(void* dst, const void* src, uint32_t bytes, uint64_t* b) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(b))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(b)),
+        "r"(parity)
+        : "memory");
+}
+
+__global__ void __launch_bounds__(kPackT) pack_tma_kernel(const uint8_t* __restrict__ masks, int64_t n_masks, int H, int W, int Wp,
+                                                         uint32_t* __restrict__ bitmap, int* __restrict__ rowrange,
+                                                         int* __restrict__ lists, int tiles_per_mask, int raw_cap /*bytes, x16*/) {
+    extern __shared__ __align__(128) unsigned char pk_raw[];
+    unsigned char* raw0 = pk_raw;
+    unsigned char* raw1 = pk_raw + raw_cap;
+    uint16_t* sb16 = reinterpret_cast<uint16_t*>(pk_raw + 2 * (size_t)raw_cap);
+    const uint32_t* sb32 = reinterpret_cast<const uint32_t*>(sb16);
+    __shared__ __align__(8) uint64_t mbar[2];
+    __shared__ int s_lo, s_hi;
+    const int tid = threadIdx.x;
+    const uintptr_t base = reinterpret_cast<uintptr_t>(masks);
+    const int64_t mis = (int64_t)(base & 15);
+    const unsigned char* vbase = reinterpret_cast<const unsigned char*>(base - mis);
+    const int64_t HW = (int64_t)H * W;
+    const int64_t n_tiles = n_masks * tiles_per_mask;
+    if (blockIdx.x == 0 && tid < 4) lists[tid] = 0;       // work-list counters of the later passes
+
+    auto geometry = [&](int64_t tile, int64_t& m, int& r0, int& r1, int64_t& b0, int64_t& c0, int& nch) {
+        m = tile / tiles_per_mask;
+        r0 = (int)(tile - m * tiles_per_mask) * kPackRows; r1 = min(H, r0 + kPackRows);
+        b0 = mis + m * HW + (int64_t)r0 * W;
+        const int64_t b1 = mis + m * HW + (int64_t)r1 * W;
+        c0 = b0 >> 4;
+        nch = (int)(((b1 + 15) >> 4) - c0);
+    };
+    if (tid == 0) { mbar_init(&mbar[0], 1); mbar_init(&mbar[1], 1); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncthreads();
+    if (tid == 0 && (int64_t)blockIdx.x < n_tiles) {
+        int64_t m, b0, c0; int r0, r1, nch;
+        geometry(blockIdx.x, m, r0, r1, b0, c0, nch);
+        mbar_expect_tx(&mbar[0], (uint32_t)nch * 16u);
+        bulk_load(raw0, vbase + (c0 << 4), (uint32_t)nch * 16u, &mbar[0]);
+    }
+    int k = 0;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++k) {
+        const int cur = k & 1;
+        int64_t m, b0, c0; int r0, r1, nch;
+        geometry(tile, m, r0, r1, b0, c0, nch);
+        if (tid == 0) {
+            s_lo = 0x7fffffff; s_hi = -1;
+            const int64_t nxt = tile + gridDim.x;
+            if (nxt < n_tiles) {   // buffer cur^1 was last read two barriers ago
+                int64_t m2, b02, c02; int r02, r12, nch2;
+                geometry(nxt, m2, r02, r12, b02, c02, nch2);
+                mbar_expect_tx(&mbar[cur ^ 1], (uint32_t)nch2 * 16u);
+                bulk_load(cur ? raw0 : raw1, vbase + (c02 << 4), (uint32_t)nch2 * 16u, &mbar[cur ^ 1]);
+            }
+        }
+        mbar_wait(&mbar[cur], (uint32_t)(k >> 1) & 1u);
+        const uint4* rv = reinterpret_cast<const uint4*>(cur ? raw1 : raw0);
+        for (int c = tid; c < nch; c += kPackT) sb16[c] = (uint16_t)nz_bits16(rv[c]);
+        if (tid < 4) sb16[nch + tid] = 0;                       // the funnel reads one word past the last chunk
+        __syncthreads();
+        const int nwords = (r1 - r0) * Wp;
+        int lo = 0x7fffffff, hi = -1;
+        for (int q = tid; q < nwords; q += kPackT) {
+            const int rr = q / Wp, w = q - rr * Wp, r = r0 + rr;
+            const int o = (int)(b0 - (c0 << 4)) + rr * W + 32 * w;          // bit offset of the window in the stream
+            uint32_t word = __funnelshift_r(sb32[o >> 5], sb32[(o >> 5) + 1], o & 31);
+            const int nb = W - 32 * w;
+            if (nb < 32) word &= (1u << nb) - 1u;
+            bitmap[((size_t)m * H + r) * Wp + w] = word;
+            if (word) { lo = min(lo, r); hi = max(hi, r); }
+        }
+        lo = __reduce_min_sync(0xffffffffu, lo); hi = __reduce_max_sync(0xffffffffu, hi);
+        if ((tid & 31) == 0 && hi >= 0) { atomicMin(&s_lo, lo); atomicMax(&s_hi, hi); }
+        __syncthreads();
+        if (tid == 0 && s_hi >= 0) {
             atomicMin(&rowrange[2 * m], s_lo);
             atomicMin(&rowrange[2 * m + 1], H - 1 - s_hi);
         }
@@ -785,7 +907,7 @@ __host__ __device__ inline size_t ws_list_bytes(int64_t n) { return align16(16 +
 // slot (masks with more runs than shared memory holds -- speckle noise).  Pass 1 (neither) launches one CTA per mask;
 // the other two are persistent and walk the state bytes: 2 = ambiguous without hole filling, 3 = run overflow.
 template <bool kExact, bool kGlobal>
-__global__ void __launch_bounds__(kT, kExact ? 1 : 4) rect_kernel(const uint32_t* __restrict__ bitmap, const int* __restrict__ rowrange,
+__global__ void __launch_bounds__(kT, kExact ? 1 : TDOD_KB_MINB) rect_kernel(const uint32_t* __restrict__ bitmap, const int* __restrict__ rowrange,
                                                                   int64_t n_masks, int H, int W, float* __restrict__ out_rects,
                                                                   uint8_t* __restrict__ out_has, unsigned char* __restrict__ slots,
                                                                   int* __restrict__ lists, uint32_t* __restrict__ fill_slots) {
@@ -871,56 +993,107 @@ extern "C" int64_t tdod_mask_rect_workspace_bytes(int64_t n_masks, int H, int W)
                      ws_fill_bytes(H, W));
 }
 
-extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int W, float* out_rects,
-                              uint8_t* out_has_rect, void* workspace, int64_t workspace_bytes, void* stream) {
-    if (n_masks == 0) return TDOD_OK;
-    if (!masks || !out_rects || !out_has_rect || n_masks < 0 || H <= 0 || W < 16)
-        return tdod_fail(TDOD_EINVAL, "tdod_mask_rect: bad argument (W must be >= 16)");
-    if (H > 32767 || W > 32767) return tdod_fail(TDOD_ERANGE, "tdod_mask_rect: image larger than 32767");
+namespace {
+struct KbPlan {
+    int Wp; size_t smem1, smem2; bool big;
+    uint32_t* bitmap; int* rowrange; int* lists; unsigned char* slots; uint32_t* fill_slots;
+};
+
+int kb_plan(int64_t n_masks, int H, int W, void* workspace, int64_t workspace_bytes, KbPlan* p, const char* who) {
+    if (n_masks < 0 || H <= 0 || W < 16) return tdod_fail(TDOD_EINVAL, "tdod_mask_*: bad argument (W must be >= 16)");
+    if (H > 32767 || W > 32767) return tdod_fail(TDOD_ERANGE, "tdod_mask_*: image larger than 32767");
     if (!workspace || workspace_bytes < tdod_mask_rect_workspace_bytes(n_masks, H, W))
-        return tdod_fail(TDOD_EINVAL, "tdod_mask_rect: workspace smaller than tdod_mask_rect_workspace_bytes()");
+        return tdod_fail(TDOD_EINVAL, "tdod_mask_*: workspace smaller than tdod_mask_rect_workspace_bytes()");
     if ((reinterpret_cast<uintptr_t>(workspace) & 15) != 0)
-        return tdod_fail(TDOD_EINVAL, "tdod_mask_rect: workspace must be 16-byte aligned");
-    const int Wp = (W + 31) >> 5;
-    const size_t smem1 = smem_layout(H, Wp, false, nullptr, nullptr);
-    const bool big = exact_needs_global(H, W);
-    const size_t smem2 = big ? smem1 : smem_layout(H, Wp, true, nullptr, nullptr);
-    if (smem1 > 227 * 1024) return tdod_fail(TDOD_ERANGE, "tdod_mask_rect: image too tall for the per-row tables in shared memory");
-    cudaStream_t st = (cudaStream_t)stream;
+        return tdod_fail(TDOD_EINVAL, "tdod_mask_*: workspace must be 16-byte aligned");
+    (void)who;
+    p->Wp = (W + 31) >> 5;
+    p->smem1 = smem_layout(H, p->Wp, false, nullptr, nullptr);
+    p->big = exact_needs_global(H, W);
+    p->smem2 = p->big ? p->smem1 : smem_layout(H, p->Wp, true, nullptr, nullptr);
+    if (p->smem1 > 227 * 1024) return tdod_fail(TDOD_ERANGE, "tdod_mask_*: image too tall for the per-row tables in shared memory");
     unsigned char* wsb = (unsigned char*)workspace;
-    uint32_t* bitmap = (uint32_t*)wsb;
-    int* rowrange = (int*)(wsb + ws_bitmap_bytes(n_masks, H, W));
-    int* lists = (int*)(wsb + ws_bitmap_bytes(n_masks, H, W) + ws_range_bytes(n_masks));
-    unsigned char* slots = wsb + ws_bitmap_bytes(n_masks, H, W) + ws_range_bytes(n_masks) + ws_list_bytes(n_masks);
+    p->bitmap = (uint32_t*)wsb;
+    p->rowrange = (int*)(wsb + ws_bitmap_bytes(n_masks, H, W));
+    p->lists = (int*)(wsb + ws_bitmap_bytes(n_masks, H, W) + ws_range_bytes(n_masks));
+    p->slots = wsb + ws_bitmap_bytes(n_masks, H, W) + ws_range_bytes(n_masks) + ws_list_bytes(n_masks);
     const int64_t n_run_slots = n_masks < kSlots ? n_masks : kSlots;
-    uint32_t* fill_slots = big ? (uint32_t*)(slots + n_run_slots * slot_bytes(H, W)) : nullptr;
-    cudaError_t e = cudaFuncSetAttribute(rect_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1);
-    if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(rect_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
-    if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(rect_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
-    if (e != cudaSuccess) return (int)e;
-    // the state byte doubles as the work list of the later passes: every mask starts undecided;
+    p->fill_slots = p->big ? (uint32_t*)(p->slots + n_run_slots * slot_bytes(H, W)) : nullptr;
+    return TDOD_OK;
+}
+}  // namespace
+
+extern "C" int tdod_mask_pack(const uint8_t* masks, int64_t n_masks, int H, int W, void* workspace, int64_t workspace_bytes,
+                              void* stream) {
+    if (n_masks == 0) return TDOD_OK;
+    if (!masks) return tdod_fail(TDOD_EINVAL, "tdod_mask_pack: masks is NULL");
+    KbPlan p;
+    const int rc = kb_plan(n_masks, H, W, workspace, workspace_bytes, &p, "pack");
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
     // rowrange = {0x7f7f7f7f, 0x7f7f7f7f} is "no row seen" for the two atomicMin's of the pack kernel
-    e = cudaMemsetAsync(out_has_rect, 0xff, (size_t)n_masks, st);
-    if (e != cudaSuccess) return (int)e;
-    e = cudaMemsetAsync(rowrange, 0x7f, (size_t)n_masks * 8, st);
+    cudaError_t e = cudaMemsetAsync(p.rowrange, 0x7f, (size_t)n_masks * 8, st);
     if (e != cudaSuccess) return (int)e;
     const int tiles_per_mask = (H + kPackRows - 1) / kPackRows;
     const int64_t n_tiles = n_masks * tiles_per_mask;
     const size_t pk_smem = (size_t)(((int64_t)kPackRows * W + 30) / 16 + 8) * 2;
-    const unsigned pk_grid = (unsigned)(n_tiles < 148 * 8 * 4 ? n_tiles : 148 * 8 * 4);
-    pack_kernel<<<pk_grid, kPackT, pk_smem, st>>>(masks, n_masks, H, W, Wp, bitmap, rowrange, lists, tiles_per_mask);
-    TDOD_CHECK_LAUNCH();
-    rect_kernel<false, false><<<(unsigned)n_masks, kT, smem1, st>>>(bitmap, rowrange, n_masks, H, W, out_rects, out_has_rect, nullptr,
-                                                                 lists, nullptr);
-    TDOD_CHECK_LAUNCH();
-    rect_kernel<true, false><<<(unsigned)(n_masks < kExactCtas ? n_masks : kExactCtas), kT, smem2, st>>>(
-        bitmap, rowrange, n_masks, H, W, out_rects, out_has_rect, nullptr, lists, fill_slots);
-    TDOD_CHECK_LAUNCH();
-    const unsigned nslots = (unsigned)(n_masks < kSlots ? n_masks : kSlots);
-    rect_kernel<true, true><<<nslots, kT, smem2, st>>>(bitmap, rowrange, n_masks, H, W, out_rects, out_has_rect, slots, lists,
-                                                      fill_slots);
+    // TMA-staged variant: two raw tile buffers (+ the bit stream) per CTA, as many CTAs per SM as shared memory allows
+    const int max_chunks = (int)(((int64_t)kPackRows * W + 30) / 16 + 1);
+    const int raw_cap = ((max_chunks * 16 + 127) / 128) * 128;
+    const size_t tma_smem = 2 * (size_t)raw_cap + pk_smem + 16;
+    const bool use_tma = tma_smem <= 100 * 1024 && getenv("TDOD_PACK_NO_TMA") == nullptr;
+    if (use_tma) {
+        e = cudaFuncSetAttribute(pack_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tma_smem);
+        if (e != cudaSuccess) return (int)e;
+        int per_sm = (int)((220 * 1024) / (tma_smem + 1024));
+        per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
+        const int64_t cap = (int64_t)148 * per_sm;
+        const unsigned grid = (unsigned)(n_tiles < cap ? n_tiles : cap);
+        pack_tma_kernel<<<grid, kPackT, tma_smem, st>>>(masks, n_masks, H, W, p.Wp, p.bitmap, p.rowrange, p.lists, tiles_per_mask,
+                                                       raw_cap);
+    } else {
+        const unsigned pk_grid = (unsigned)(n_tiles < 148 * 8 * 4 ? n_tiles : 148 * 8 * 4);
+        pack_kernel<<<pk_grid, kPackT, pk_smem, st>>>(masks, n_masks, H, W, p.Wp, p.bitmap, p.rowrange, p.lists, tiles_per_mask);
+    }
     TDOD_CHECK_LAUNCH();
     return TDOD_OK;
+}
+
+extern "C" int tdod_mask_rect_packed(int64_t n_masks, int H, int W, float* out_rects, uint8_t* out_has_rect, void* workspace,
+                                     int64_t workspace_bytes, void* stream) {
+    if (n_masks == 0) return TDOD_OK;
+    if (!out_rects || !out_has_rect) return tdod_fail(TDOD_EINVAL, "tdod_mask_rect_packed: an output pointer is NULL");
+    KbPlan p;
+    const int rc = kb_plan(n_masks, H, W, workspace, workspace_bytes, &p, "rect");
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaError_t e = cudaFuncSetAttribute(rect_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem1);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(rect_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem2);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(rect_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem2);
+    if (e != cudaSuccess) return (int)e;
+    // the state byte doubles as the work list of the later passes: every mask starts undecided
+    e = cudaMemsetAsync(out_has_rect, 0xff, (size_t)n_masks, st);
+    if (e != cudaSuccess) return (int)e;
+    rect_kernel<false, false><<<(unsigned)n_masks, kT, p.smem1, st>>>(p.bitmap, p.rowrange, n_masks, H, W, out_rects, out_has_rect,
+                                                                   nullptr, p.lists, nullptr);
+    TDOD_CHECK_LAUNCH();
+    rect_kernel<true, false><<<(unsigned)(n_masks < kExactCtas ? n_masks : kExactCtas), kT, p.smem2, st>>>(
+        p.bitmap, p.rowrange, n_masks, H, W, out_rects, out_has_rect, nullptr, p.lists, p.fill_slots);
+    TDOD_CHECK_LAUNCH();
+    const unsigned nslots = (unsigned)(n_masks < kSlots ? n_masks : kSlots);
+    rect_kernel<true, true><<<nslots, kT, p.smem2, st>>>(p.bitmap, p.rowrange, n_masks, H, W, out_rects, out_has_rect, p.slots,
+                                                        p.lists, p.fill_slots);
+    TDOD_CHECK_LAUNCH();
+    return TDOD_OK;
+}
+
+extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int W, float* out_rects,
+                              uint8_t* out_has_rect, void* workspace, int64_t workspace_bytes, void* stream) {
+    if (n_masks == 0) return TDOD_OK;
+    if (!masks || !out_rects || !out_has_rect) return tdod_fail(TDOD_EINVAL, "tdod_mask_rect: a pointer is NULL");
+    const int rc = tdod_mask_pack(masks, n_masks, H, W, workspace, workspace_bytes, stream);
+    if (rc) return rc;
+    return tdod_mask_rect_packed(n_masks, H, W, out_rects, out_has_rect, workspace, workspace_bytes, stream);
 }

@@ -49,6 +49,8 @@ SIGNATURES = {
     "tdod_score_dimensions": (_I, [_P, _P, _P, _L, _P, _P, _L, _P, _P]),
     "tdod_mask_rect_workspace_bytes": (_L, [_L, _I, _I]),
     "tdod_mask_rect": (_I, [_P, _L, _I, _I, _P, _P, _P, _L, _P]),
+    "tdod_mask_pack": (_I, [_P, _L, _I, _I, _P, _L, _P]),
+    "tdod_mask_rect_packed": (_I, [_L, _I, _I, _P, _P, _P, _L, _P]),
     "tdod_score_corners": (_I, [_P, _I, _P, _L, _P, _P]),
     "tdod_score_segmentation": (_I, [_P, _I, _I, _P, _L, _I, _P, _P]),
     "tdod_score_point_cloud": (_I, [_P, _I, _L, _P, _L, _P, _P]),
@@ -56,6 +58,7 @@ SIGNATURES = {
     "tdod_ransac_workspace_bytes": (_L, [_I, _I, _I]),
     "tdod_ransac_plane": (_I, [_P, _I, _P, _I, _L, _P, _U64, _L, _I, _D, _P, _P, _P, _P, _P, _P, _L, _P]),
     "tdod_yaw_table": (_I, [_P, _I, _I, _P, _P]),
+    "tdod_resize_nearest": (_I, [_P, _I, _I, _I, _I, _P, _P, _P, _I, _I, _P]),
     "tdod_propose_score_select": (_I, [C.POINTER(PssArgs), _P]),
 }
 

@@ -136,7 +136,7 @@ def select(batch, n_prop, seed=0, noise=None, yaw_idx=None, rot=None, sample_ids
             yaw_tab = api.yaw_table(s.normal)
             mark("ka1", side)
     mark("kb0", main)
-    s.rects, s.has_rect = api.mask_rect(batch.masks)
+    s.rects, s.has_rect = api.mask_rect(batch.masks, mark=(lambda name: mark(name, main)) if marks is not None else None)
     mark("kb1", main)
     if with_plane and side is not main:
         main.wait_stream(side)

@@ -78,6 +78,15 @@ int64_t tdod_mask_rect_workspace_bytes(int64_t n_masks, int H, int W);
 int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int W, float* out_rects, uint8_t* out_has_rect,
                    void* workspace, int64_t workspace_bytes, void* stream);
 
+/* The two halves of tdod_mask_rect as separate entry points, for callers that want to time them or reuse the packed
+ * masks: tdod_mask_pack streams the 1 B/px masks once from HBM into the workspace's 1 bit/px bitmap (+ the occupied
+ * row range of every mask); tdod_mask_rect_packed computes the rectangles from a workspace tdod_mask_pack filled for
+ * the same (n_masks, H, W).  tdod_mask_rect == pack followed by rect_packed. */
+int tdod_mask_pack(const uint8_t* masks, int64_t n_masks, int H, int W, void* workspace, int64_t workspace_bytes,
+                   void* stream);
+int tdod_mask_rect_packed(int64_t n_masks, int H, int W, float* out_rects, uint8_t* out_has_rect, void* workspace,
+                          int64_t workspace_bytes, void* stream);
+
 /* second half of score_corners (scorefunction.py:69-85 + modified_chamfer_distance :51-56).
  * rect [4,2] (ignored when has_rect == 0: the fallback rectangle of :69-75 is computed from the corners). */
 int tdod_score_corners(const float* rect, int has_rect, const float* corners2d /*[n,8,2]*/, int64_t n, float* out,
@@ -121,6 +130,14 @@ int tdod_ransac_plane(const void* pts, int pts_f64, const int32_t* n_pts, int F,
 /* orthobasis_from_normal_t over linspace(0, pi, 36) (utils.py:112-146, proposals.py:405-406).
  * normals [F,3] fp64 (normals_f64) or fp32 -> out_table [F,36,9] fp32 (row-major 3x3, columns x, n, n x x). */
 int tdod_yaw_table(const void* normals, int normals_f64, int F, float* out_table, void* stream);
+
+/* ---- ingest ---------------------------------------------------------------------------------------------- */
+
+/* Depth / ground map resize to the network resolution, PIL Image.resize(.., NEAREST) semantics
+ * (cubercnn/data/dataset_mapper.py:127-128, :141-142).  src [F,h,w] of 1- or 4-byte elements -> dst [F,H,W];
+ * xmap [W], ymap [H] int32 source indices (Pillow's accumulating double-precision stepping, built by the caller). */
+int tdod_resize_nearest(const void* src, int elem_bytes, int F, int h, int w, const int32_t* xmap, const int32_t* ymap,
+                        void* dst, int H, int W, void* stream);
 
 /* ---- fused propose + project + score + select (the hot kernel) --------------------------------------- */
 
