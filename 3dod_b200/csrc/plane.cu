@@ -103,7 +103,7 @@ __global__ void __cluster_dims__(kBpCluster, 1, 1) __launch_bounds__(kBpT)
         int base = 0;
         for (int r = 0; r < rank; ++r) base += *cl.map_shared_rank(&s_tot[tid], r);
         s_base[tid] = base;
-        if (rank == kBpCluster - 1) counts[2 * f + tid] = base + s_tot[tid];
+        if (rank == kBpCluster - 1) counts[(size_t)tid * (gridDim.x / kBpCluster) + f] = base + s_tot[tid];   // [2,F]
     }
     __syncthreads();
     // ---- pass B: back-project and write in place ----

@@ -160,40 +160,61 @@ __device__ int hull8(const float* U, const float* V, int* hx, int* hy) {
     return k;
 }
 
-__global__ void __launch_bounds__(kT) seg_kernel(const uint8_t* __restrict__ mask, int H, int W,
-                                                 const float* __restrict__ c2d, int64_t n, int power5,
-                                                 float* __restrict__ out) {
+// One warp per proposal, kSegWarps proposals per CTA.  The CTA first builds the row prefix sums of the sampled mask
+// (one warp per row, ballot + popc); each warp then builds its proposal's hull, lanes 0..7 one edge each (shared
+// memory), and the lanes split the sampled rows; the two integer sums reduce over the warp (order-free, exact).
+constexpr int kSegWarps = 8;
+
+__global__ void __launch_bounds__(kSegWarps * 32) seg_kernel(const uint8_t* __restrict__ mask, int H, int W,
+                                                             const float* __restrict__ c2d, int64_t n, int power5,
+                                                             float* __restrict__ out) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int Hs = (H + 3) >> 2, Ws = (W + 3) >> 2, stride = Ws + 1;
     uint16_t* pre = reinterpret_cast<uint16_t*>(smem_raw);   // [Hs][Ws+1] exclusive row prefix sums of mask[4r][4c]
     __shared__ int mask_total;
+    __shared__ Edge s_edges[kSegWarps][8];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if (threadIdx.x == 0) mask_total = 0;
     __syncthreads();
-    for (int r = threadIdx.x; r < Hs; r += kT) {
+    for (int r = wid; r < Hs; r += kSegWarps) {
         const uint8_t* row = mask + (size_t)(4 * r) * W;
-        int acc = 0;
-        pre[r * stride] = 0;
-        for (int c = 0; c < Ws; ++c) { acc += row[4 * c] != 0; pre[r * stride + c + 1] = (uint16_t)acc; }
-        atomicAdd(&mask_total, acc);
+        int base = 0;
+        if (lane == 0) pre[r * stride] = 0;
+        for (int c0 = 0; c0 < Ws; c0 += 32) {
+            const int c = c0 + lane;
+            const bool bit = c < Ws && row[4 * c] != 0;
+            const unsigned m = __ballot_sync(0xffffffffu, bit);
+            if (c < Ws) pre[r * stride + c + 1] = (uint16_t)(base + __popc(m & (0xffffffffu >> (31 - lane))));
+            base += __popc(m);
+        }
+        if (lane == 0 && base) atomicAdd(&mask_total, base);
     }
     __syncthreads();
-    const int64_t i = (int64_t)blockIdx.x * kT + threadIdx.x;
-    if (i >= n) return;
+    const int64_t i = (int64_t)blockIdx.x * kSegWarps + wid;
+    if (i >= n) return;                                   // warp-uniform
     float U[8], V[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) { U[j] = c2d[i * 16 + 2 * j]; V[j] = c2d[i * 16 + 2 * j + 1]; }
     int hx[8], hy[8];
-    const int nv = hull8(U, V, hx, hy);
-    Edge ed[8];
+    const int nv = hull8(U, V, hx, hy);                   // every lane, same result
+    Edge* ed = s_edges[wid];
     int ymin = 0x7fffffff, ymax = -0x7fffffff;
-    for (int k = 0; k < nv; ++k) {
-        const int p = (k + nv - 1) % nv;
-        make_edge(W, H, hx[p], hy[p], hx[k], hy[k], ed[k]);
-        ymin = min(ymin, hy[k]); ymax = max(ymax, hy[k]);
+    for (int k = 0; k < nv; ++k) { ymin = min(ymin, hy[k]); ymax = max(ymax, hy[k]); }
+    if (lane < nv) {
+        int px = hx[0], py = hy[0], qx = hx[0], qy = hy[0];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {                     // register arrays: select without dynamic indexing
+            if (k == lane) { qx = hx[k]; qy = hy[k]; }
+            if (k == (lane + nv - 1) % nv) { px = hx[k]; py = hy[k]; }
+        }
+        Edge e;
+        make_edge(W, H, px, py, qx, qy, e);
+        ed[lane] = e;
     }
+    __syncwarp();
     i64 inter = 0, poly = 0;
     const int r0 = max(0, (ymin + 3) >> 2), r1 = min(Hs - 1, ymax >> 2);
-    for (int r = r0; r <= r1 && ymax >= 0; ++r) {
+    for (int r = r0 + lane; r <= r1 && ymax >= 0; r += 32) {
         const int y = 4 * r;
         // intervals in sample-index space [clo, chi]
         int clo[12], chi[12];
@@ -240,6 +261,12 @@ __global__ void __launch_bounds__(kT) seg_kernel(const uint8_t* __restrict__ mas
             if (a < m) { cl = clo[a]; ch = chi[a]; }
         }
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        inter += __shfl_xor_sync(0xffffffffu, inter, o);
+        poly += __shfl_xor_sync(0xffffffffu, poly, o);
+    }
+    if (lane != 0) return;
     float res = 0.f;
     if (inter != 0) {
         const i64 uni = (i64)mask_total + poly - inter;
@@ -265,7 +292,7 @@ extern "C" int tdod_score_segmentation(const uint8_t* mask, int H, int W, const 
     if (smem > 200 * 1024) return tdod_fail(TDOD_ERANGE, "tdod_score_segmentation: sampled mask does not fit in shared memory");
     cudaError_t e = cudaFuncSetAttribute(seg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
-    seg_kernel<<<(unsigned)((n + kT - 1) / kT), kT, smem, (cudaStream_t)stream>>>(mask, H, W, corners2d, n, power5, out);
+    seg_kernel<<<(unsigned)((n + kSegWarps - 1) / kSegWarps), kSegWarps * 32, smem, (cudaStream_t)stream>>>(mask, H, W, corners2d, n, power5, out);
     TDOD_CHECK_LAUNCH();
     return TDOD_OK;
 }

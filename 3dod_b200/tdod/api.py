@@ -116,17 +116,19 @@ def yaw_table(normals):
 
 def backproject(depth, ground, K, stride=5, flavour=L.BACKPROJECT_NUMPY, want_other=True):
     """depth [F,H,W] fp32, ground [F,H,W] bool/u8 or None, K [F,3,3] ->
-    (plane_pts [F,3,P], other_pts [F,3,P] | None, counts [F,2] int32); fp64 for the NumPy flavour."""
+    (plane_pts [F,3,P], other_pts [F,3,P] | None, counts [F,2] int32 (a view of the [2,F] buffer)); fp64 for the
+    NumPy flavour."""
     F, H, W = depth.shape
     P = ((H + stride - 1) // stride) * ((W + stride - 1) // stride)
     dt = f64 if flavour == L.BACKPROJECT_NUMPY else f32
     pts = torch.empty((F, 3, P), dtype=dt, device=depth.device)
     other = torch.empty((F, 3, P), dtype=dt, device=depth.device) if (want_other and ground is not None) else None
-    counts = torch.empty((F, 2), dtype=i32, device=depth.device)
+    counts2 = torch.empty((2, F), dtype=i32, device=depth.device)   # [2,F] in memory; returned as its [F,2] view, so
+    counts = counts2.t()                                            # counts[:, 0] is contiguous (n_pts of ransac_plane)
     g = _as_u8(ground)
     L.check(L.lib().tdod_backproject(L.ptr(depth, f32, "depth"), L.ptr(g, u8, "ground"),
                                      L.ptr(K.reshape(F, 9).contiguous(), f32, "K"), F, H, W, stride, flavour,
-                                     L.ptr(pts), L.ptr(other), L.ptr(counts), L.stream_ptr()))
+                                     L.ptr(pts), L.ptr(other), L.ptr(counts2), L.stream_ptr()))
     return pts, other, counts
 
 

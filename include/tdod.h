@@ -108,7 +108,8 @@ int tdod_score_point_cloud(const void* points, int points_f64, int64_t P, const 
 /* Depth -> strided point cloud (roi_heads.py:346-371 / :1084-1112), row-major compaction.
  * depth [F,H,W]; ground [F,H,W] 1 B/px or NULL; K [F,9].  Outputs per frame f, SoA, capacity
  * P = ceil(H/stride)*ceil(W/stride): plane_pts [F,3,P] (ground>0 points, or all when ground NULL),
- * other_pts [F,3,P] or NULL (ground==0 points), counts [F,2] int32.  fp64 when flavour == NUMPY else fp32. */
+ * other_pts [F,3,P] or NULL (ground==0 points), counts [2,F] int32 (row 0: plane points per frame --
+ * directly usable as tdod_ransac_plane's n_pts --, row 1: the others).  fp64 when flavour == NUMPY else fp32. */
 int tdod_backproject(const float* depth, const uint8_t* ground, const float* K, int F, int H, int W, int stride,
                      int flavour, void* plane_pts, void* other_pts, int32_t* counts, void* stream);
 

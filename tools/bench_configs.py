@@ -68,6 +68,42 @@ def run_select(name, steps, dev, flush, frames=None):
             "l2": "512 MB buffer rewritten between timed iterations"}
 
 
+def run_mode_b(steps, dev, flush):
+    """C1 shape, mode B scores (MABO branch, roi_heads.py:512-582): segmentation / mod-segmentation IoU and points-in-cube
+    for 5 objects x 1000 proposals through the per-function entry points the reference's call sites use"""
+    c = synth.CONFIGS["C1"]
+    H, W, n = c["H"], c["W"], c["n_prop"]
+    f = synth.make_frame(0, H, W, c["n_obj"], device=dev)
+    batch = pipeline.FrameBatch.from_frames([f], dev)
+    sel = pipeline.select(batch, n, seed=7, return_all=True)
+    pts, other, cnt = api.backproject(batch.depth, batch.ground, batch.K, 5, L.BACKPROJECT_NUMPY, want_other=True)
+    torch.cuda.synchronize()
+    P_other = int(cnt[0, 1])
+    cloud = other[0, :, :P_other].t().contiguous()
+    cubes = sel.all.all_cubes
+    N = cubes.shape[0]
+    c2d = [api.project_cubes(cubes[i], batch.K[0], W, H, boxes=False)[0] for i in range(N)]
+
+    def seg():
+        for i in range(N):
+            api.score_segmentation(batch.masks[i], c2d[i])
+
+    def modseg():
+        for i in range(N):
+            api.score_segmentation(batch.masks[i], c2d[i], power5=True)
+
+    def pc():
+        for i in range(N):
+            api.score_point_cloud(cloud, cubes[i])
+    out = {"config": "C1 mode B", "objects": N, "n_prop": n, "points": P_other}
+    for nm, fn in (("score_segmentation", seg), ("score_mod_segmentation", modseg), ("score_point_cloud", pc)):
+        ms = timed(fn, steps, flush)
+        out[nm + "_ms"] = ms
+        out[nm + "_proposals_per_s"] = N * n / (ms * 1e-3)
+    out["pc_compares_per_s"] = 6.0 * P_other * N * n / (out["score_point_cloud_ms"] * 1e-3)
+    return out
+
+
 def run_c5(steps, dev, flush, frames=None):
     c = synth.CONFIGS["C5"]
     F = frames or c["frames"]
@@ -107,7 +143,7 @@ def run_c5(steps, dev, flush, frames=None):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("configs", nargs="*", default=["C1", "C3", "C5"])
+    ap.add_argument("configs", nargs="*", default=["C1", "C1B", "C3", "C5"])
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--frames", type=int, default=None)
     a = ap.parse_args()
@@ -115,7 +151,9 @@ def main():
     L.lib()
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
     for name in a.configs:
-        if name == "C5":
+        if name == "C1B":
+            print(json.dumps(run_mode_b(a.steps, dev, flush)), flush=True)
+        elif name == "C5":
             for line in run_c5(a.steps, dev, flush, a.frames):
                 print(json.dumps(line), flush=True)
         else:
