@@ -69,13 +69,16 @@ def score_corners(rect, corners2d):
     return out
 
 
-def mask_rect(masks, mark=None):
+def mask_rect(masks, mark=None, out=None):
     """masks [n,H,W] bool/uint8 -> (rects [n,4,2] fp32, has_rect [n] uint8).  Two launches groups: the streaming pack
     (mask bytes -> bitmap) and the rectangle passes; `mark(name)` is called between them ("kb_mid") when given."""
     m = _as_u8(masks)
     n, H, W = m.shape
-    rects = torch.empty((n, 4, 2), dtype=f32, device=m.device)
-    has = torch.empty(n, dtype=u8, device=m.device)
+    if out is not None:
+        rects, has = out                      # preallocated [n,4,2] fp32 / [n] uint8 (slices of larger tensors are fine)
+    else:
+        rects = torch.empty((n, 4, 2), dtype=f32, device=m.device)
+        has = torch.empty(n, dtype=u8, device=m.device)
     wsb = L.lib().tdod_mask_rect_workspace_bytes(n, H, W)
     ws = torch.empty(max(int(wsb), 16), dtype=u8, device=m.device)
     L.check(L.lib().tdod_mask_pack(L.ptr(m, u8, "masks"), n, H, W, L.ptr(ws), wsb, L.stream_ptr()))

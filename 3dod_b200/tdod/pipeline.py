@@ -101,9 +101,62 @@ def _side_stream(dev):
     return _SIDE[key]
 
 
+_SPLIT = {}
+
+
+def _split_streams(dev, k):
+    key = (dev.type, dev.index if dev.index is not None else torch.cuda.current_device())
+    pool = _SPLIT.setdefault(key, [])
+    while len(pool) < k:
+        pool.append(torch.cuda.Stream(dev))
+    return pool[:k]
+
+
+def _select_split(batch, n_prop, seed, yaw_tab, side, main, obj_id_base, cluster_size, iou_boxes, splits):
+    """K-B and K-C of `splits` object ranges on as many streams (optional; the latency-bound rectangle passes of one
+    range can run beside the fused kernel and the pack of another -- on C2 the smaller launches cost more than that gains).  Results are written into slices of the
+    same output tensors; Philox keys are global object ids, so the winners equal the unsplit run's."""
+    dev = batch.device
+    N = batch.n_obj
+    o = api.PssOutputs()
+    o.best_idx = torch.empty(N, dtype=i32, device=dev)
+    o.best_score = torch.empty(N, dtype=f32, device=dev)
+    o.best_cube = torch.empty((N, 15), dtype=f32, device=dev)
+    o.best_box = torch.empty((N, 4), dtype=f32, device=dev)
+    o.all_cubes = o.all_boxes = o.all_scores = o.stats = None
+    rects = torch.empty((N, 4, 2), dtype=f32, device=dev)
+    has = torch.empty(N, dtype=u8, device=dev)
+    masks = batch.masks.view(u8) if batch.masks.dtype == torch.bool else batch.masks
+    bounds = [N * g // splits for g in range(splits + 1)]
+    streams = [main] + _split_streams(dev, splits - 1)
+    for g, st in enumerate(streams):
+        a, b = bounds[g], bounds[g + 1]
+        if a == b:
+            continue
+        if st is not main:
+            st.wait_stream(main)
+        with torch.cuda.stream(st):
+            api.mask_rect(masks[a:b], out=(rects[a:b], has[a:b]))
+            if side is not None and side is not st:
+                st.wait_stream(side)
+            if yaw_tab is not None:
+                yaw_tab.record_stream(st)
+            og = api.PssOutputs()
+            og.best_idx, og.best_score = o.best_idx[a:b], o.best_score[a:b]
+            og.best_cube, og.best_box = o.best_cube[a:b], o.best_box[a:b]
+            og.all_cubes = og.all_boxes = og.all_scores = og.stats = None
+            api.propose_score_select(batch.depth, batch.K, batch.boxes[a:b], batch.prior_mean[a:b], batch.prior_std[a:b],
+                                     batch.obj_frame[a:b], rects[a:b], has[a:b], n_prop, yaw_tab=yaw_tab, seed=seed,
+                                     obj_id_base=obj_id_base + a, cluster_size=cluster_size, out=og,
+                                     iou_boxes=None if iou_boxes is None else iou_boxes[a:b])
+    for st in streams[1:]:
+        main.wait_stream(st)
+    return o, rects, has
+
+
 def select(batch, n_prop, seed=0, noise=None, yaw_idx=None, rot=None, sample_ids=None, use_ground=True,
            ransac_iters=1000, ransac_thresh=0.05, flavour=L.BACKPROJECT_NUMPY, obj_id_base=0, frame_id_base=0,
-           return_all=False, cluster_size=0, overlap=True, marks=None, iou_boxes=None):
+           return_all=False, cluster_size=0, overlap=True, marks=None, iou_boxes=None, splits=None):
     """Mode A (roi_heads.py:493-505) for every object of a device-resident batch.  Throughput RNG (in-kernel
     Philox keyed by global object id) unless `noise` (+ `yaw_idx` / `rot`) hands in host-drawn numbers.
     Launches only; does not synchronise.
@@ -135,6 +188,19 @@ def select(batch, n_prop, seed=0, noise=None, yaw_idx=None, rot=None, sample_ids
                 thresh=ransac_thresh, flavour=flavour, frame_id_base=frame_id_base)
             yaw_tab = api.yaw_table(s.normal)
             mark("ka1", side)
+    if splits is None:       # measured on C2 (B200): two ranges in flight 1.42 ms vs one range 1.34 ms -> off by default
+        splits = 1
+    if splits > 1:
+        if noise is not None or return_all:
+            raise ValueError("splits > 1 needs the throughput RNG and select mode (no return_all)")
+        if with_plane and side is not main:
+            for t in (s.normal, s.plane_eq, s.inlier_count, yaw_tab):
+                t.record_stream(main)
+        o, s.rects, s.has_rect = _select_split(batch, n_prop, seed, yaw_tab, side if with_plane else None, main,
+                                               obj_id_base, cluster_size, iou_boxes, splits)
+        s.best_idx, s.best_score, s.best_cube, s.best_box = o.best_idx, o.best_score, o.best_cube, o.best_box
+        s.all = None
+        return s
     mark("kb0", main)
     s.rects, s.has_rect = api.mask_rect(batch.masks, mark=(lambda name: mark(name, main)) if marks is not None else None)
     mark("kb1", main)
@@ -158,6 +224,14 @@ def select(batch, n_prop, seed=0, noise=None, yaw_idx=None, rot=None, sample_ids
 # passes; K-C)
 LAUNCHES_PER_SELECT = 10
 LAUNCHES_PER_SELECT_NO_GROUND = 5
+
+
+def launches_per_select(n_obj, with_plane=True, splits=None):
+    """libtdod kernels one `select` call launches: K-A 5 (back-projection, hypotheses, count, best, yaw table) + per
+    object range 5 (pack, three rectangle passes, fused kernel)"""
+    if splits is None:
+        splits = 1
+    return (5 if with_plane else 0) + 5 * splits
 
 
 class Pipeline:

@@ -253,7 +253,6 @@ def run_tdod(args):
     for _ in range(max(args.warmup, 3)):
         o = step()
     barrier()
-    marks = [dict() for _ in range(args.steps)]
     t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clk:
         barrier()
@@ -261,14 +260,14 @@ def run_tdod(args):
             torch.cuda.profiler.start()
         t_start.record(stream)
         for k in range(args.steps):
-            o = step(marks[k])
+            o = step()
         t_end.record(stream)
         barrier()
         if args.profile:
             torch.cuda.profiler.stop()
     total_ms = t_start.elapsed_time(t_end)
-    stage_ms = stage_times(marks)                     # inside the timed region, each on its own stream (K-A overlaps K-B)
-    # the same K steps once more on ONE stream: stage times free of contention, and the cost of not overlapping
+    # the same K steps once more on ONE stream with events between the stages: stage times free of contention (inside the
+    # timed region K-A runs on an auxiliary stream and two object ranges are in flight on two more, so kernels overlap)
     marks_serial = [dict() for _ in range(args.steps)]
     s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -337,14 +336,12 @@ def run_tdod(args):
                                    % (F, W, H, N, N_PROP),
                        "frames_per_gpu": F, "objects_rank0": N, "rng": "in-kernel Philox4x32-10",
                        "l2": "inputs (%.2f GB per pass) are larger than the 126 MB L2" % (batch.input_bytes() / 1e9)},
-            "gpu_launches": pipeline.LAUNCHES_PER_SELECT * args.steps,
-            "stages_ms": dict(zip(stage_names, stage_ms)),
+            "gpu_launches": pipeline.launches_per_select(N) * args.steps,
             "stages_ms_serial": dict(zip(stage_names, stage_ms_serial)), "ms_per_step_serial": serial_ms_step,
             "roofline": {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                          "traffic": TRAFFIC.get(dom), "peak_source": peak_src, "algorithmic_bytes_per_launch": abytes[dom],
-                         "timed": "stages_ms_serial (the same K steps on one stream); inside the overlapped timed region the "
-                                  "stage shares the SMs with K-A, see stages_ms",
-                         "frac_in_overlapped_region": abytes[dom] / (stage_ms[j] * 1e-3) / 1e9 / peak,
+                         "timed": "stages_ms_serial: the same K steps once more on one stream, CUDA events between the stages "
+                                  "(in the timed region the stages overlap on several streams)",
                          "step_algorithmic_bytes": step_bytes, "step_frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak,
                          "all_stages": {n: {"ms": m, "bound": BOUND[n], "hbm_frac": abytes[n] / (m * 1e-3) / 1e9 / peak}
                                         for n, m in zip(stage_names, stage_ms_serial)}},

@@ -677,6 +677,19 @@ def test_philox_mode_is_deterministic_and_batching_invariant():
     assert eq_nan(s4.best_score, s1.best_score[o0:])
 
 
+def test_split_stream_select_equals_single_stream_select():
+    """two object ranges on two streams (pipeline.select's default for large batches) == one range on one stream"""
+    d = dev()
+    b, c = _c2_batch(range(8), d)
+    s1 = pipeline.select(b, 1000, seed=5, splits=1, overlap=False)
+    for k in (2, 3):
+        s2 = pipeline.select(b, 1000, seed=5, splits=k)
+        torch.cuda.synchronize()
+        assert torch.equal(s1.best_idx, s2.best_idx) and eq_nan(s1.best_score, s2.best_score)
+        assert eq_nan(s1.best_cube, s2.best_cube) and eq_nan(s1.best_box, s2.best_box)
+        assert torch.equal(s1.rects, s2.rects) and torch.equal(s1.has_rect, s2.has_rect)
+
+
 def test_philox_mode_winner_is_the_argmax_of_what_it_scored():
     """size-independent properties at BASELINE config-2 shape: the winner record is consistent with the all-proposal
     outputs; recomputing every score with the per-function kernels from the emitted cubes reproduces them; w,h,l
