@@ -456,8 +456,8 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
             const float diff = fabsf(__fsub_rn(r_ref, ratio));
             const float d = chamfer4x8(sh.rect, U, V);
             s_x[j] = iou; s_y[j] = g; s_z[j] = diff; s_d[j] = d;
-            lmaxdiff = (lmaxdiff != lmaxdiff || diff != diff) ? CUDART_NAN_F : fmaxf(lmaxdiff, diff);
-            lmaxd = (lmaxd != lmaxd || d != d) ? CUDART_NAN_F : fmaxf(lmaxd, d);
+            lmaxdiff = max_nan(lmaxdiff, diff);
+            lmaxd = max_nan(lmaxd, d);
             }
         emit:
             if (a.all_cubes) {
@@ -517,7 +517,7 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
             float m = -CUDART_INF_F;
             for (int w2 = 0; w2 < kWarps; ++w2) {
                 const float v = sh.red_f[w2][tid];
-                m = (m != m || v != v) ? CUDART_NAN_F : fmaxf(m, v);
+                m = max_nan(m, v);
             }
             if (tid == 0) sh.mail.maxdiff = m; else sh.mail.maxd = m;
         }
@@ -527,8 +527,8 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
     float maxdiff = -CUDART_INF_F, maxd = -CUDART_INF_F;
     for (int r = 0; r < S; ++r) {
         const float v0 = *cl.remote(&sh.mail.maxdiff, r), v1 = *cl.remote(&sh.mail.maxd, r);
-        maxdiff = (maxdiff != maxdiff || v0 != v0) ? CUDART_NAN_F : fmaxf(maxdiff, v0);
-        maxd = (maxd != maxd || v1 != v1) ? CUDART_NAN_F : fmaxf(maxd, v1);
+        maxdiff = max_nan(maxdiff, v0);
+        maxd = max_nan(maxd, v1);
     }
 
     // ---------------- phase 3: final scores, argmax (np.argmax: first NaN, else first maximum) ----------------

@@ -13,13 +13,21 @@ namespace tdod {
 // ------------------------------------------------------------------------------------------
 // warp / block reductions
 // ------------------------------------------------------------------------------------------
+// NaN-propagating min / max (torch.min / torch.max / torch.clamp semantics) in one instruction each: FMNMX.NAN
+__device__ __forceinline__ float min_nan(float a, float b) {
+    float r;
+    asm("min.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ float max_nan(float a, float b) {
+    float r;
+    asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
+}
 __device__ __forceinline__ float warp_max_nan(float v) {
     // torch.max semantics: NaN propagates
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        float w = __shfl_xor_sync(0xffffffffu, v, o);
-        v = (v != v || w != w) ? CUDART_NAN_F : fmaxf(v, w);
-    }
+    for (int o = 16; o > 0; o >>= 1) v = max_nan(v, __shfl_xor_sync(0xffffffffu, v, o));
     return v;
 }
 
@@ -120,7 +128,8 @@ struct Philox {
 __device__ __forceinline__ float2 box_muller(uint32_t a, uint32_t b) {
     const float u1 = ((float)a + 1.0f) * 2.3283064365386963e-10f;  // (0,1]
     const float u2 = (float)b * 2.3283064365386963e-10f;           // [0,1)
-    const float rad = sqrtf(-2.0f * __logf(u1));
+    float rad;                                                     // throughput-mode draws: approximate sqrt is enough
+    asm("sqrt.approx.f32 %0, %1;" : "=f"(rad) : "f"(-2.0f * __logf(u1)));
     float s, c;
     __sincosf(6.283185307179586f * u2, &s, &c);
     return make_float2(rad * c, rad * s);
@@ -160,8 +169,8 @@ __host__ __device__ __forceinline__ Clamp make_clamp(int W, int H) {
     c.yhi = (float)(H - 1 + H);
     return c;
 }
-__device__ __forceinline__ float clamp_nan(float v, float lo, float hi) {
-    return (v != v) ? v : fminf(fmaxf(v, lo), hi);
+__device__ __forceinline__ float clamp_nan(float v, float lo, float hi) {   // lo, hi are never NaN
+    return min_nan(max_nan(v, lo), hi);
 }
 __device__ __forceinline__ void project(const float* __restrict__ K, const Clamp& cl, float X, float Y, float Z,
                                         float& u, float& v) {
@@ -172,9 +181,7 @@ __device__ __forceinline__ void project(const float* __restrict__ K, const Clamp
     v = clamp_nan(__fdiv_rn(py, pz), cl.ylo, cl.yhi);
 }
 
-// torch.min / torch.max over the 8 corners propagate NaN (conversions.py:38-41)
-__device__ __forceinline__ float min_nan(float a, float b) { return (a != a || b != b) ? CUDART_NAN_F : fminf(a, b); }
-__device__ __forceinline__ float max_nan(float a, float b) { return (a != a || b != b) ? CUDART_NAN_F : fmaxf(a, b); }
+// (torch.min / torch.max over the 8 corners propagate NaN, conversions.py:38-41: min_nan / max_nan above)
 
 // detectron2 pairwise_iou (public formula; call site ProposalNetwork/utils/utils.py:186-192)
 __device__ __forceinline__ float iou_xyxy(float ax0, float ay0, float ax1, float ay1, float bx0, float by0,
