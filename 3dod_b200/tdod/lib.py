@@ -60,6 +60,12 @@ SIGNATURES = {
     "tdod_yaw_table": (_I, [_P, _I, _I, _P, _P]),
     "tdod_resize_nearest": (_I, [_P, _I, _I, _I, _I, _P, _P, _P, _I, _I, _P]),
     "tdod_propose_score_select": (_I, [C.POINTER(PssArgs), _P]),
+    "tdod_cube_box_fwd": (_I, [_P, _P, _P, _P, _L, _P, _P, _P, _P, _P, _P, _P]),
+    "tdod_cube_box_bwd": (_I, [_P, _P, _P, _P, _L, _P, _P, _P, _P, _P, _P, _P]),
+    "tdod_z_sweep": (_I, [_P, _P, _P, _P, _P, _P, _I, _L, _P, _P]),
+    "tdod_hull": (_I, [_P, _L, _P, _P, _P]),
+    "tdod_hull_fill_moments": (_I, [_P, _P, _P, _P, _L, _I, _I, _P, _P]),
+    "tdod_hull_fill_grad": (_I, [_P, _P, _P, _P, _L, _I, _I, _P, _P, _P, _P]),
 }
 
 

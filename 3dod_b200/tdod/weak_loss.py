@@ -1,0 +1,207 @@
+"""Weak-loss geometry of ROIHeads3DScore on the device: the differentiable consumers of
+Cubes / cubes_to_box in the training path of the reference (cubercnn/modeling/roi_heads/roi_heads.py).
+
+    project_boxes   Cubes -> 8 corners -> K -> clamp -> box (+ GIoU)         roi_heads.py:1571-1583, :1599
+    z_loss          50-step depth sweep                                        :1151-1194
+    segment_loss    jarvis_march + fill_polygon + focal / bce / dice           :1030-1052, utils.py:424-507
+    normal_vector_from_maps  batched Plane.fit_parallel + wall rectification   :1076-1149
+
+Each is one or two kernel launches for the whole batch of cubes (the reference loops over cubes in Python and lets
+autograd record hundreds of small kernels per cube); gradients come from hand-written backward kernels wrapped in
+`torch.autograd.Function`, so the results plug into the reference's loss code unchanged.  CUDA tensors only."""
+import math
+
+import numpy as np
+import torch
+
+from . import lib as L
+from . import pipeline
+
+f32, f64, i32 = torch.float32, torch.float64, torch.int32
+
+
+def _im_wh(im_sizes, n, dev):
+    """[(w, h)] * n, one (w, h) pair, or an [n,2] tensor -> int32 [n,2] on the device"""
+    if isinstance(im_sizes, torch.Tensor):
+        t = im_sizes.to(device=dev, dtype=i32)
+    else:
+        a = np.asarray(im_sizes, dtype=np.float64).reshape(-1, 2)
+        t = torch.as_tensor(a.astype(np.int32), device=dev)       # int(w): the reference truncates (spaces.py:241)
+    if t.shape[0] == 1 and n != 1:
+        t = t.expand(n, 2)
+    if t.shape != (n, 2):
+        raise ValueError("im_sizes must give one (width, height) per cube")
+    return t.contiguous()
+
+
+def _per_object_K(K, n):
+    K = K.to(f32)
+    if K.dim() == 2:
+        K = K[None].expand(n, 3, 3)
+    if K.shape != (n, 3, 3):
+        raise ValueError("K must be [3,3] or [N,3,3]")
+    return K.contiguous()
+
+
+class _CubeBox(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, cubes, K, im_wh, gt):
+        n, dev = cubes.shape[0], cubes.device
+        cubes = cubes.detach().contiguous()
+        corners = torch.empty((n, 8, 2), dtype=f32, device=dev)
+        seg = torch.empty((n, 8, 2), dtype=f32, device=dev)
+        boxes = torch.empty((n, 4), dtype=f32, device=dev)
+        arg = torch.empty((n, 4), dtype=i32, device=dev)
+        giou = torch.empty((n,), dtype=f32, device=dev) if gt is not None else None
+        dgiou = torch.empty((n, 4), dtype=f32, device=dev) if gt is not None else None
+        L.check(L.lib().tdod_cube_box_fwd(L.ptr(cubes, f32, "cubes"), L.ptr(K, f32, "K"), L.ptr(im_wh, i32, "im_sizes"),
+                                          L.ptr(gt, f32, "gt_boxes"), n, L.ptr(corners), L.ptr(seg), L.ptr(boxes),
+                                          L.ptr(arg), L.ptr(giou), L.ptr(dgiou), L.stream_ptr()))
+        ctx.save_for_backward(cubes, K, im_wh, arg, dgiou)
+        ctx.has_gt = gt is not None
+        if gt is None:
+            giou = torch.zeros((0,), dtype=f32, device=dev)
+        ctx.mark_non_differentiable(arg)
+        return corners, seg, boxes, giou, arg
+
+    @staticmethod
+    def backward(ctx, g_corners, g_seg, g_boxes, g_giou, _g_arg):
+        cubes, K, im_wh, arg, dgiou = ctx.saved_tensors
+        n = cubes.shape[0]
+        c = lambda g: None if g is None else g.to(f32).contiguous()
+        g_corners, g_seg, g_boxes = c(g_corners), c(g_seg), c(g_boxes)
+        g_giou = c(g_giou) if ctx.has_gt else None
+        out = torch.empty((n, 15), dtype=f32, device=cubes.device)
+        L.check(L.lib().tdod_cube_box_bwd(L.ptr(cubes), L.ptr(K), L.ptr(im_wh), L.ptr(arg), n, L.ptr(g_corners),
+                                          L.ptr(g_seg), L.ptr(g_boxes), L.ptr(g_giou), L.ptr(dgiou), L.ptr(out),
+                                          L.stream_ptr()))
+        return out, None, None, None
+
+
+def project_boxes(cubes, K, im_sizes, gt_boxes=None):
+    """cubes [N,15] (requires_grad allowed), K [N,3,3] or [3,3], im_sizes (w,h) per cube.  Returns a dict:
+    corners [N,8,2] (get_bube_corners, spaces.py:224-245), seg_corners [N,8,2] (clamped to the image,
+    roi_heads.py:1574-1575), boxes [N,4] (cubes_to_box, conversions.py:25-48) and, when gt_boxes [N,4] is given,
+    loss_iou [N] = generalized_box_iou_loss(gt, boxes, reduction='none') (:1599).  All four are differentiable."""
+    if cubes.dim() != 2 or cubes.shape[1] != 15:
+        raise ValueError("cubes must be [N,15]")
+    n, dev = cubes.shape[0], cubes.device
+    Kc, im = _per_object_K(K, n), _im_wh(im_sizes, n, dev)
+    gt = None if gt_boxes is None else gt_boxes.detach().to(f32).contiguous()
+    if gt is not None and gt.shape != (n, 4):
+        raise ValueError("gt_boxes must be [N,4]")
+    corners, seg, boxes, giou, _ = _CubeBox.apply(cubes.to(f32), Kc, im, gt)
+    out = dict(corners=corners, seg_corners=seg, boxes=boxes)
+    if gt is not None:
+        out["loss_iou"] = giou
+    return out
+
+
+def z_loss(gt_boxes, cubes, K, im_sizes, proj_boxes, max_count=50):
+    """ROIHeads3DScore.z_loss (roi_heads.py:1151-1194) for all cubes in one launch.  The reference's value
+    |z - (z +- v)| does not depend on z, so its gradient is identically zero; the result is returned detached."""
+    n, dev = cubes.shape[0], cubes.device
+    Kc, im = _per_object_K(K, n), _im_wh(im_sizes, n, dev)
+    values = torch.linspace(0.0, (max_count - 1) / 10, max_count, device=dev)           # :1168
+    out = torch.empty((n,), dtype=f32, device=dev)
+    L.check(L.lib().tdod_z_sweep(L.ptr(gt_boxes.detach().to(f32).contiguous(), f32, "gt_boxes"),
+                                 L.ptr(cubes.detach().to(f32).contiguous(), f32, "cubes"), L.ptr(Kc), L.ptr(im),
+                                 L.ptr(proj_boxes.detach().to(f32).contiguous(), f32, "proj_boxes"), L.ptr(values),
+                                 int(max_count), n, L.ptr(out), L.stream_ptr()))
+    return out
+
+
+def hull(corners):
+    """jarvis_march (utils.py:424-468) of n x 8 points: (hull [n,8,2], meta [n,9] = m, corner index per vertex)"""
+    n = corners.shape[0]
+    pts = corners.detach().to(f32).contiguous()
+    h = torch.empty((n, 8, 2), dtype=f32, device=pts.device)
+    meta = torch.empty((n, 9), dtype=i32, device=pts.device)
+    L.check(L.lib().tdod_hull(L.ptr(pts, f32, "corners"), n, L.ptr(h), L.ptr(meta), L.stream_ptr()))
+    return h, meta
+
+
+class _HullMoments(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, corners, masks, mask_idx):
+        n, dev = corners.shape[0], corners.device
+        H, W = masks.shape[-2:]
+        h, meta = hull(corners)
+        mom = torch.empty((n, 12), dtype=f64, device=dev)
+        L.check(L.lib().tdod_hull_fill_moments(L.ptr(masks), L.ptr(mask_idx, i32, "mask_idx"), L.ptr(h), L.ptr(meta), n,
+                                               int(H), int(W), L.ptr(mom), L.stream_ptr()))
+        ctx.save_for_backward(masks, mask_idx, h, meta)
+        return mom
+
+    @staticmethod
+    def backward(ctx, g_mom):
+        masks, mask_idx, h, meta = ctx.saved_tensors
+        n, dev = h.shape[0], h.device
+        H, W = masks.shape[-2:]
+        g = g_mom.to(f64).contiguous()
+        ws = torch.empty((n, 24), dtype=f64, device=dev)
+        out = torch.empty((n, 8, 2), dtype=f32, device=dev)
+        L.check(L.lib().tdod_hull_fill_grad(L.ptr(masks), L.ptr(mask_idx), L.ptr(h), L.ptr(meta), n, int(H), int(W),
+                                            L.ptr(g), L.ptr(ws), L.ptr(out), L.stream_ptr()))
+        return out, None, None
+
+
+def hull_fill_moments(masks, corners, mask_idx):
+    """masks [M,H,W] bool / uint8 on the device, corners [n,8,2] (differentiable), mask_idx [n].  Returns [n,12] fp64:
+    sum over pixels of t^k, k = 0..4, for mask == 0 then mask == 1, then sum sigmoid(t) for mask == 0, mask == 1, where
+    t is the reference's soft hull mask convex_hull(mask, corners) (utils.py:504-507)."""
+    if masks.dim() != 3:
+        raise ValueError("masks must be [M,H,W]")
+    if masks.dtype == torch.bool:
+        masks = masks.view(torch.uint8)
+    if masks.dtype != torch.uint8 or not masks.is_contiguous():
+        raise ValueError("masks must be a contiguous bool / uint8 tensor")
+    idx = torch.as_tensor(mask_idx, device=corners.device).to(i32).contiguous()
+    if idx.numel() != corners.shape[0]:
+        raise ValueError("one mask index per cube")
+    return _HullMoments.apply(corners.to(f32), masks, idx)
+
+
+def _focal_polynomials(alpha=0.25, gamma=2):
+    """sigmoid_focal_loss(inputs=x, targets=t) for x in {0, 1} as polynomials in t (coefficients of t^0..t^4)"""
+    P = np.polynomial.polynomial
+    out = []
+    for x in (0.0, 1.0):
+        p = 1.0 / (1.0 + math.exp(-x))
+        ce = [x + math.log1p(math.exp(-x)), -x]                  # (1 - t) x + log(1 + exp(-x))
+        one_minus_pt = [p, -(2 * p - 1)]                         # 1 - (p t + (1 - p)(1 - t))
+        alpha_t = [1 - alpha, 2 * alpha - 1]
+        poly = P.polymul(P.polymul(alpha_t, ce), P.polypow(one_minus_pt, gamma))
+        out.append(np.pad(poly, (0, 5 - len(poly))))
+    return np.stack(out)
+
+
+_FOCAL = _focal_polynomials()
+
+
+def segment_loss(gt_mask, bube_corners, at_which_mask_idx, loss='focal'):
+    """ROIHeads3DScore.segment_loss (roi_heads.py:1030-1052).  gt_mask: [M,H,W] device tensor, or the reference's list
+    of [1,H,W] masks (stacked here); bube_corners [n,8,2] on the device, already clamped to the image (:1574-1575).
+    'focal' / 'bce' return [n]; 'dice' one scalar over the batch (dice_loss :1013-1028).  As in the reference the mask
+    is the `inputs` (logits) argument and the hull fill the `targets`."""
+    if isinstance(gt_mask, (list, tuple)):
+        gt_mask = torch.stack([m.reshape(m.shape[-2:]) for m in gt_mask])
+    H, W = gt_mask.shape[-2:]
+    S = hull_fill_moments(gt_mask, bube_corners, at_which_mask_idx)          # [n,12] fp64
+    if loss == 'focal':
+        c = torch.as_tensor(_FOCAL.reshape(10), dtype=f64, device=S.device)
+        return ((S[:, :10] * c).sum(1) / (H * W)).to(f32)
+    if loss == 'bce':
+        # x = 0: log 2;  x = 1: (1 - t) + log(1 + exp(-1))
+        return ((math.log(2.0) * S[:, 0] + (1 + math.log1p(math.exp(-1.0))) * S[:, 5] - S[:, 6]) / (H * W)).to(f32)
+    if loss == 'dice':
+        inter, s_sum, y_sum = S[:, 11].sum(), S[:, 10].sum() + S[:, 11].sum(), S[:, 5].sum()
+        return (1 - (2. * inter + 1) / (s_sum + y_sum + 1)).to(f32)
+    raise ValueError("loss must be 'focal', 'bce' or 'dice'")
+
+
+def normal_vector_from_maps(ground_maps, depth_maps, Ks, use_nth=5, seed=0, sample_ids=None):
+    """ROIHeads3DScore.normal_vector_from_maps (roi_heads.py:1076-1149) for a stack of equally sized frames in two
+    launches: depth_maps [F,H,W], ground_maps [F,H,W] or None, Ks [F,3,3] -> rectified up-vectors [F,3] fp32."""
+    return pipeline.ground_normals(depth_maps, ground_maps, Ks, seed=seed, sample_ids=sample_ids, stride=use_nth,
+                                   flavour=L.BACKPROJECT_TORCH)[0]

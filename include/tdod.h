@@ -189,6 +189,49 @@ typedef struct tdod_pss_args {
  * combine/argmax (roi_heads.py:493-505) in one launch; one CTA cluster per object. */
 int tdod_propose_score_select(const tdod_pss_args* args_host, void* stream);
 
+/* ---- weak-loss geometry of ROIHeads3DScore -------------------------------------------- */
+
+/* Forward of the loop roi_heads.py:1571-1583 (+ :1599) for N objects, each with its own K [N,9] and image size
+ * im_wh [N,2] int32 (width, height): Cubes.get_bube_corners (spaces.py:224-245) -> out_corners [N,8,2] (clamped to
+ * the wide range of :241-242); the second clamp to the image (roi_heads.py:1574-1575) -> out_seg_corners [N,8,2] or
+ * NULL; cubes_to_box (conversions.py:25-48) -> out_boxes [N,4]; out_arg [N,4] int32 = corner index of each box
+ * coordinate (torch.min / torch.max along the corner dim: first occurrence, NaN first) for the backward.
+ * gt_boxes [N,4] or NULL: torchvision.ops.generalized_box_iou_loss(gt, box, reduction='none') -> out_giou [N] and its
+ * derivative with respect to the box out_dgiou [N,4]. */
+int tdod_cube_box_fwd(const float* cubes, const float* K, const int32_t* im_wh, const float* gt_boxes, int64_t N,
+                      float* out_corners, float* out_seg_corners, float* out_boxes, int32_t* out_arg, float* out_giou,
+                      float* out_dgiou, void* stream);
+
+/* Backward of tdod_cube_box_fwd (what torch.autograd builds for the loop above): incoming gradients with respect to
+ * out_corners, out_seg_corners, out_boxes [N,4], out_giou [N] (each may be NULL) -> out_g_cubes [N,15]
+ * (centre, w h l, R row-major).  clamp passes the gradient on the closed interval, min / max to the index in `arg`. */
+int tdod_cube_box_bwd(const float* cubes, const float* K, const int32_t* im_wh, const int32_t* arg, int64_t N,
+                      const float* g_corners, const float* g_seg_corners, const float* g_boxes, const float* g_giou,
+                      const float* dgiou, float* out_g_cubes, void* stream);
+
+/* z_loss (roi_heads.py:1151-1194): per cube the depth is moved in `steps` steps of values[s] (torch.linspace(0, 4.9,
+ * 50)) away from / towards the camera until the projected box area is closest to the ground-truth box area;
+ * out [N] = |z - z_best| / 2, or 0.1 * steps / 2 when the centre test of :1166-1167 fails (reproduced as written). */
+int tdod_z_sweep(const float* gt_boxes, const float* cubes, const float* K, const int32_t* im_wh, const float* proj_boxes,
+                 const float* values, int steps, int64_t N, float* out, void* stream);
+
+/* jarvis_march (ProposalNetwork/utils/utils.py:424-468, with findDuplicates :397-422) on n sets of 8 points [n,8,2]:
+ * out_hull [n,8,2] hull vertices in the order the reference returns them, out_meta [n,9] int32 = {m, corner index of
+ * vertex 0..m-1, -1 padding}. */
+int tdod_hull(const float* corners2d, int64_t n, float* out_hull, int32_t* out_meta, void* stream);
+
+/* fill_polygon (utils.py:470-502) + the pixel sums every loss of segment_loss (roi_heads.py:1030-1052) is made of:
+ * with t = soft hull mask at a pixel and x = masks[mask_idx[i]] at it (masks [M,H,W] 1 B/px), out_moments [n,12] fp64 =
+ * sum t^k over x==0 (k=0..4), sum t^k over x==1 (k=0..4), sum sigmoid(t) over x==0, over x==1.  The H x W soft mask
+ * is never written. */
+int tdod_hull_fill_moments(const uint8_t* masks, const int32_t* mask_idx, const float* hull, const int32_t* meta,
+                           int64_t n, int H, int W, double* out_moments, void* stream);
+
+/* Backward of the sums above to the 8 corners: g_moments [n,12] fp64 -> out_g_corners [n,8,2] fp32.
+ * workspace: n * 24 doubles of device scratch. */
+int tdod_hull_fill_grad(const uint8_t* masks, const int32_t* mask_idx, const float* hull, const int32_t* meta, int64_t n,
+                        int H, int W, const double* g_moments, double* workspace, float* out_g_corners, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -241,8 +241,94 @@ def make_variants(ver):
     np.savez_compressed(os.path.join(HERE, "variants.npz"), **out)
 
 
+def _ref_methods(names):
+    """the UNMODIFIED source of methods of ROIHeads3DScore (cubercnn/modeling/roi_heads/roi_heads.py), exec'd from the
+    file where it lies (the module itself needs detectron2 / pytorch3d / segment_anything, absent here)"""
+    import ast
+    import textwrap
+    import torch.nn.functional as F
+    from torchvision.ops import sigmoid_focal_loss
+    path = os.path.join(ref_import.REF_ROOT, "cubercnn/modeling/roi_heads/roi_heads.py")
+    src = open(path).read()
+    tree = ast.parse(src)
+    cls = [n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "ROIHeads3DScore"][0]
+    ns = {"torch": torch, "F": F, "Boxes": R.Boxes, "Cubes": R.spaces.Cubes, "cubes_to_box": R.conversions.cubes_to_box,
+          "convex_hull": R.utils.convex_hull, "sigmoid_focal_loss": sigmoid_focal_loss}
+    for fn in cls.body:
+        if isinstance(fn, ast.FunctionDef) and fn.name in names:
+            exec(textwrap.dedent(ast.get_source_segment(src, fn)), ns)
+
+    class Self:
+        pass
+    me = Self()
+    for n in names:
+        setattr(me, n, ns[n].__get__(me))
+    return me
+
+
+def make_weak_loss(ver):
+    """cubes_to_box with autograd, GIoU loss, z_loss, segment_loss of the UNMODIFIED reference on
+    the winners-like cubes of a small frame (120x160 so that the fixture stays small)."""
+    from torchvision.ops import generalized_box_iou_loss
+    me = _ref_methods(["l1_loss", "dice_loss", "segment_loss", "z_loss"])
+    H, W, n = 120, 160, 14
+    f = synth.make_frame(21, H, W, n, with_masks=True)
+    N = f.boxes.shape[0]
+    g = torch.Generator().manual_seed(5)
+    cubes = O.propose(f.boxes, f.depth, f.prior_mean, f.prior_std, f.K, 4, normal=torch.tensor([0.05, 0.99, 0.1]),
+                      generator=g)["cubes"]
+    cubes = cubes[:, 1].float().clone()                                   # one proposal per object, [N,15]
+    cubes[0, 2] = 0.2          # straddles the camera plane: projections blow up and clamp
+    cubes[1, 0] += 3.0         # far to the right: clamped on x
+    cubes[2, 3:6] *= 0.05      # tiny cube: corners nearly coincide
+    Ks = f.K[None].repeat(N, 1, 1).clone()
+    Ks[:, 0, 2] += torch.arange(N) * 0.5                                  # per-object intrinsics (roi_heads.py:1539)
+    ims = [(W, H)] * N
+    cubes.requires_grad_(True)
+    wb = torch.rand((N, 4), generator=g)
+    wl = torch.rand(N, generator=g)
+    # roi_heads.py:1571-1583
+    corners, segc, boxes = [], [], []
+    for i in range(N):
+        cb = R.spaces.Cubes(cubes[i][None, None])
+        bc = cb.get_bube_corners(Ks[i], ims[i])
+        corners.append(bc[0, 0])
+        x = torch.clamp(bc[..., 0], 0, int(ims[i][0] - 1))
+        y = torch.clamp(bc[..., 1], 0, int(ims[i][1] - 1))
+        segc.append(torch.stack((x, y), dim=-1)[0, 0])
+        boxes.append(R.conversions.cubes_to_box(cb, Ks[i], ims[i])[0].tensor[0])
+    corners, segc, boxes = torch.stack(corners), torch.stack(segc), torch.stack(boxes)
+    gt = R.Boxes(f.boxes)
+    out = {"versions": ver, "frame": np.array([21, H, W, n]), "inputs_sha256": np.array(frame_digest(f)),
+           "cubes": cubes.detach().numpy(), "Ks": Ks.numpy(), "wb": wb.numpy(), "wl": wl.numpy(),
+           "corners": corners.detach().numpy(), "seg_corners": segc.detach().numpy(), "boxes": boxes.detach().numpy()}
+    out["grad_box"] = torch.autograd.grad((boxes * wb).sum(), cubes, retain_graph=True)[0].numpy()
+    giou = generalized_box_iou_loss(gt.tensor, boxes, reduction='none').view(N, -1).mean(dim=1)        # :1599
+    out["giou"] = giou.detach().numpy()
+    out["grad_giou"] = torch.autograd.grad((giou * wl).sum(), cubes, retain_graph=True)[0].numpy()
+    z = me.z_loss(gt, R.spaces.Cubes(cubes[:, None]), Ks, ims, R.Boxes(boxes.detach()))
+    out["z_loss"] = z.detach().numpy()
+    masks = [m[None] for m in f.masks]
+    idx = list(range(N))
+    for kind in ("focal", "bce", "dice"):
+        sl = me.segment_loss(masks, segc, idx, loss=kind)
+        out["seg_" + kind] = sl.detach().numpy()
+        wv = wl if sl.dim() else torch.tensor(1.0)
+        gc, gq = torch.autograd.grad((sl * wv).sum(), (segc, cubes), retain_graph=True, allow_unused=True)
+        out["grad_seg_%s_corners" % kind] = gc.numpy()
+        out["grad_seg_%s_cubes" % kind] = gq.numpy()
+    hulls = [R.utils.jarvis_march(segc[i].detach()) for i in range(N)]
+    out["hull_len"] = np.array([len(h) for h in hulls])
+    out["hull"] = np.stack([np.pad(h.numpy(), ((0, 8 - len(h)), (0, 0))) for h in hulls])
+    np.savez_compressed(os.path.join(HERE, "weak_loss.npz"), **out)
+    print("weak_loss.npz", {k: getattr(v, "shape", None) for k, v in out.items() if k.startswith(("seg_", "z_", "giou"))})
+    print("hull_len", out["hull_len"], "z", out["z_loss"], "focal", out["seg_focal"], "dice", out["seg_dice"])
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "variants":
         make_variants(np.array(str(O.versions())))
+    elif len(sys.argv) > 1 and sys.argv[1] == "weak_loss":
+        make_weak_loss(np.array(str(O.versions())))
     else:
         main()
