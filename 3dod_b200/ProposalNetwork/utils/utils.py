@@ -1,12 +1,14 @@
 """ProposalNetwork/utils/utils.py -- the helpers that sit on the proposal-and-scoring path.
 
 The random draws stay torch calls in the reference's program order (the proposal set is defined by
-torch's generator streams); everything arithmetic goes through libtdod.  Plotting helpers, iou_3d (pytorch3d,
-evaluation only) and the autograd hull of the weak loss are out of scope and absent."""
+torch's generator streams); everything arithmetic goes through libtdod.  Plotting helpers and iou_3d (pytorch3d,
+evaluation only) are out of scope and absent; the differentiable hull of the weak loss (jarvis_march, fill_polygon,
+convex_hull, utils.py:424-507) is served by tdod.weak_loss."""
 import numpy as np
 import torch
 
 from tdod import api
+from tdod.weak_loss import jarvis_march, fill_polygon, convex_hull  # noqa: F401  (utils.py:424-507)
 
 N_YAW = 36
 

@@ -304,17 +304,34 @@ __global__ void __launch_bounds__(kT) hull_kernel(const float* __restrict__ pts,
 struct Edges {
     float v1x[8], v1y[8], ex[8], ey[8];
     int m;
+    int bx0, bx1, by0, by1;    // pixels outside this box have a zero soft mask (see load_edges); empty when bx1 < bx0
 };
 
+// The soft mask is the product of clamp(e_i, 0, 1); a pixel where it (or any product leaving one edge out times the
+// indicator 0 <= e_i <= 1) is non-zero lies in the closed intersection of the left half-planes of a closed chain of
+// edges, hence inside the convex hull of the vertices, hence inside their bounding box: everything else is skipped.
 __device__ __forceinline__ void load_edges(const float* __restrict__ hull, const int32_t* __restrict__ meta, int64_t i,
-                                           Edges& E) {
+                                           int H, int W, Edges& E) {
     E.m = meta[i * 9];
+    float lox = CUDART_INF_F, loy = CUDART_INF_F, hix = -CUDART_INF_F, hiy = -CUDART_INF_F;
+    bool bad = false;
     for (int t = 0; t < 8; ++t) {
         const int t2 = (t + 1 < E.m) ? t + 1 : 0;
         const float ax = hull[i * 16 + 2 * t], ay = hull[i * 16 + 2 * t + 1];
         E.v1x[t] = ax; E.v1y[t] = ay;
         E.ex[t] = hull[i * 16 + 2 * t2] - ax;
         E.ey[t] = hull[i * 16 + 2 * t2 + 1] - ay;
+        if (t < E.m) {
+            bad |= !(fabsf(ax) < 1e9f) || !(fabsf(ay) < 1e9f);
+            lox = fminf(lox, ax); hix = fmaxf(hix, ax); loy = fminf(loy, ay); hiy = fmaxf(hiy, ay);
+        }
+    }
+    if (bad) {                 // NaN / huge vertices: no shortcut, every pixel is evaluated
+        E.bx0 = 0; E.bx1 = W - 1; E.by0 = 0; E.by1 = H - 1;
+    } else {
+        E.bx0 = max(0, (int)floorf(lox)); E.bx1 = min(W - 1, (int)ceilf(hix));
+        E.by0 = max(0, (int)floorf(loy)); E.by1 = min(H - 1, (int)ceilf(hiy));
+        if (E.m < 3) E.bx1 = E.bx0 - 1;     // one or two vertices: e and -e (or e = 0) -> the product is zero everywhere
     }
 }
 
@@ -324,49 +341,76 @@ __device__ __forceinline__ float edge_fn(const Edges& E, int t, float X, float Y
 }
 __device__ __forceinline__ float clamp01(float e) { return min_nan(max_nan(e, 0.f), 1.f); }
 
-// forward: per object the sums over pixels of t^k (k = 0..4) and sigmoid(t), split by mask value x
+// number of non-zero bytes in [p, p + n): word loads where the address allows
+__device__ __forceinline__ int count_nonzero(const uint8_t* __restrict__ p, int64_t n, int tid, int nthreads) {
+    int c = 0;
+    const int64_t head = min(n, (int64_t)((4 - ((uintptr_t)p & 3)) & 3));
+    for (int64_t k = tid; k < head; k += nthreads) c += p[k] != 0;
+    const uint32_t* w = (const uint32_t*)(p + head);
+    const int64_t nw = (n - head) >> 2;
+    for (int64_t k = tid; k < nw; k += nthreads) {
+        const uint32_t t = w[k];
+        c += __popc((t | ((t & 0x7f7f7f7fu) + 0x7f7f7f7fu)) & 0x80808080u);
+    }
+    for (int64_t k = head + (nw << 2) + tid; k < n; k += nthreads) c += p[k] != 0;
+    return c;
+}
+
+// forward: per object the sums over pixels of t^k (k = 0..4) and sigmoid(t), split by mask value x.  gridDim.x CTAs
+// per object: each counts the set pixels of one slice of the whole mask (the t = 0 terms: t^0 and sigmoid(0) = 1/2)
+// and evaluates the soft mask on one band of rows of the hull's bounding box.
+template <bool SIG>
 __global__ void __launch_bounds__(kFillT) hull_moments_kernel(const uint8_t* __restrict__ masks,
                                                               const int32_t* __restrict__ mask_idx,
                                                               const float* __restrict__ hull,
-                                                              const int32_t* __restrict__ meta, int H, int W, int rows,
+                                                              const int32_t* __restrict__ meta, int H, int W,
                                                               double* __restrict__ mom) {
     __shared__ Edges E;
     __shared__ double s_red[kFillT / 32][kMom];
     const int64_t obj = blockIdx.y;
-    if (threadIdx.x == 0) load_edges(hull, meta, obj, E);
+    if (threadIdx.x == 0) load_edges(hull, meta, obj, H, W, E);
     __syncthreads();
     const uint8_t* mk = masks + (int64_t)mask_idx[obj] * H * W;
-    const int r0 = blockIdx.x * rows, r1 = min(H, r0 + rows);
-    // sums over all pixels and over the pixels with mask == 1 (registers only: no indexing by the mask value)
+    const int64_t HW = (int64_t)H * W;
+    const int64_t slice = cdiv64(HW, gridDim.x);
+    const int64_t s0 = min(HW, slice * blockIdx.x), s1 = min(HW, s0 + slice);
+    const int cnt_one = count_nonzero(mk + s0, s1 - s0, threadIdx.x, kFillT);
+    // sums over the pixels with t > 0: all of them, and those with mask == 1 (registers only)
     double all[5] = {0.0, 0.0, 0.0, 0.0, 0.0}, one[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
-    int cnt_all = 0, cnt_one = 0, zero_all = 0, zero_one = 0;
+    int pos_all = 0, pos_one = 0;
     const int m = E.m;
-    for (int y = r0; y < r1; ++y) {
-        const float Y = (float)y;
-        for (int x = threadIdx.x; x < W; x += kFillT) {
-            const int b = mk[(int64_t)y * W + x] != 0;
-            ++cnt_all;
-            cnt_one += b;
-            const float X = (float)x;
+    const int bw = E.bx1 - E.bx0 + 1, bh = E.by1 - E.by0 + 1;
+    if (bw > 0 && bh > 0) {
+        const int band = (int)cdiv64(bh, gridDim.x);
+        const int r0 = E.by0 + band * blockIdx.x, r1 = min(E.by1 + 1, r0 + band);
+        const int npx = max(0, r1 - r0) * bw;
+        for (int k = threadIdx.x; k < npx; k += kFillT) {
+            const int y = r0 + k / bw, x = E.bx0 + k % bw;
+            const float X = (float)x, Y = (float)y;
             float t = 1.f;
             for (int e = 0; e < m; ++e) {
                 t = __fmul_rn(t, clamp01(edge_fn(E, e, X, Y)));
                 if (t == 0.f) break;
             }
-            if (t == 0.f) { ++zero_all; zero_one += b; continue; }
+            if (t == 0.f) continue;
+            const int b = mk[(int64_t)y * W + x] != 0;
+            ++pos_all;
+            pos_one += b;
             const double td = (double)t, t2 = td * td, bd = (double)b;
-            const double p[5] = {td, t2, t2 * td, t2 * t2, 1.0 / (1.0 + exp(-td))};
+            const double p[5] = {td, t2, t2 * td, t2 * t2, SIG ? (double)__fdiv_rn(1.f, 1.f + expf(-t)) : 0.0};
 #pragma unroll
-            for (int k = 0; k < 5; ++k) { all[k] += p[k]; one[k] += bd * p[k]; }
+            for (int q = 0; q < 5; ++q) { all[q] += p[q]; one[q] += bd * p[q]; }
         }
     }
+    // pixels with t == 0 contribute t^0 = 1 and sigmoid(0) = 1/2: they come from the slice counts
+    const double c1 = (double)cnt_one, slice_px = threadIdx.x == 0 ? (double)(s1 - s0) : 0.0;
     double v[kMom];
-    v[0] = (double)(cnt_all - cnt_one);
-    v[5] = (double)cnt_one;
+    v[0] = slice_px - c1;
+    v[5] = c1;
 #pragma unroll
     for (int k = 1; k < 5; ++k) { v[k] = all[k - 1] - one[k - 1]; v[5 + k] = one[k - 1]; }
-    v[10] = (all[4] - one[4]) + 0.5 * (double)(zero_all - zero_one);
-    v[11] = one[4] + 0.5 * (double)zero_one;
+    v[10] = (all[4] - one[4]) + 0.5 * (slice_px - c1) - 0.5 * (double)(pos_all - pos_one);
+    v[11] = one[4] + 0.5 * c1 - 0.5 * (double)pos_one;
 #pragma unroll
     for (int k = 0; k < kMom; ++k) {
 #pragma unroll
@@ -375,53 +419,86 @@ __global__ void __launch_bounds__(kFillT) hull_moments_kernel(const uint8_t* __r
     }
     __syncthreads();
     if (threadIdx.x < kMom) {
-        double s = 0.0;
-        for (int w = 0; w < kFillT / 32; ++w) s += s_red[w][threadIdx.x];
-        atomicAdd(mom + obj * kMom + threadIdx.x, s);
+        double sum = 0.0;
+        for (int w = 0; w < kFillT / 32; ++w) sum += s_red[w][threadIdx.x];
+        atomicAdd(mom + obj * kMom + threadIdx.x, sum);
     }
 }
 
-// backward: d(sum_k G[x][k] S[x][k]) / d(edge function) accumulated per edge as (sum g, sum g X, sum g Y)
-__global__ void __launch_bounds__(kFillT) hull_grad_kernel(const uint8_t* __restrict__ masks,
-                                                           const int32_t* __restrict__ mask_idx,
-                                                           const float* __restrict__ hull, const int32_t* __restrict__ meta,
-                                                           int H, int W, int rows, const double* __restrict__ gmom,
-                                                           double* __restrict__ edge_acc) {
+// convex_hull(mask, coords) itself (utils.py:504-507): the dense soft mask, for callers that want the image
+__global__ void __launch_bounds__(kFillT) hull_fill_kernel(const float* __restrict__ hull, const int32_t* __restrict__ meta,
+                                                           int H, int W, int rows, float* __restrict__ out) {
     __shared__ Edges E;
-    __shared__ double s_acc[8][3];
-    __shared__ double s_g[kMom];
     const int64_t obj = blockIdx.y;
-    if (threadIdx.x == 0) load_edges(hull, meta, obj, E);
-    if (threadIdx.x < 24) s_acc[threadIdx.x / 3][threadIdx.x % 3] = 0.0;
-    if (threadIdx.x >= 32 && threadIdx.x < 32 + kMom) s_g[threadIdx.x - 32] = gmom[obj * kMom + threadIdx.x - 32];
+    if (threadIdx.x == 0) load_edges(hull, meta, obj, H, W, E);
     __syncthreads();
-    const uint8_t* mk = masks + (int64_t)mask_idx[obj] * H * W;
     const int r0 = blockIdx.x * rows, r1 = min(H, r0 + rows);
     const int m = E.m;
     for (int y = r0; y < r1; ++y) {
         const float Y = (float)y;
+        const bool row_in = y >= E.by0 && y <= E.by1;
         for (int x = threadIdx.x; x < W; x += kFillT) {
-            const float X = (float)x;
+            float t = (m == 0) ? 1.f : 0.f;
+            if (row_in && x >= E.bx0 && x <= E.bx1) {
+                t = 1.f;
+                for (int e = 0; e < m; ++e) t = __fmul_rn(t, clamp01(edge_fn(E, e, (float)x, Y)));
+            }
+            out[(obj * H + y) * W + x] = t;
+        }
+    }
+}
+
+// backward: d(sum_k G[x][k] S[x][k]) / d(edge function) -- or, DENSE, of sum_pixels g[pixel] t[pixel] -- accumulated
+// per edge as (sum g, sum g X, sum g Y)
+template <bool DENSE>
+__global__ void __launch_bounds__(kFillT) hull_grad_kernel(const uint8_t* __restrict__ masks,
+                                                           const int32_t* __restrict__ mask_idx,
+                                                           const float* __restrict__ hull, const int32_t* __restrict__ meta,
+                                                           int H, int W, const double* __restrict__ gmom,
+                                                           const float* __restrict__ gdense, double* __restrict__ edge_acc) {
+    __shared__ Edges E;
+    __shared__ double s_acc[8][3];
+    __shared__ double s_g[kMom];
+    const int64_t obj = blockIdx.y;
+    if (threadIdx.x == 0) load_edges(hull, meta, obj, H, W, E);
+    if (threadIdx.x < 24) s_acc[threadIdx.x / 3][threadIdx.x % 3] = 0.0;
+    if (!DENSE && threadIdx.x >= 32 && threadIdx.x < 32 + kMom) s_g[threadIdx.x - 32] = gmom[obj * kMom + threadIdx.x - 32];
+    __syncthreads();
+    const uint8_t* mk = DENSE ? nullptr : masks + (int64_t)mask_idx[obj] * H * W;
+    const int m = E.m;
+    const int bw = E.bx1 - E.bx0 + 1, bh = E.by1 - E.by0 + 1;
+    const int band = (bw > 0 && bh > 0) ? (int)cdiv64(bh, gridDim.x) : 0;
+    const int r0 = E.by0 + band * blockIdx.x, r1 = min(E.by1 + 1, r0 + band);
+    const int npx = (band > 0 ? max(0, r1 - r0) : 0) * bw;
+    for (int k = threadIdx.x; k < npx; k += kFillT) {
+        const int y = r0 + k / bw, x = E.bx0 + k % bw;
+        {
+            const float X = (float)x, Y = (float)y;
             float c[8], w[8];
             int zeros = 0;
-            bool band = false;
+            bool inband = false;
             for (int e = 0; e < m; ++e) {
                 const float f = edge_fn(E, e, X, Y);
                 c[e] = clamp01(f);
                 // max(f, 0) then min(., 1): ties route half of the gradient (derivatives.yaml maximum / minimum)
                 w[e] = (f > 0.f && f < 1.f) ? 1.f : ((f == 0.f || f == 1.f) ? 0.5f : 0.f);
                 zeros += c[e] == 0.f;
-                band |= w[e] != 0.f;
+                inband |= w[e] != 0.f;
                 if (zeros >= 2) break;
             }
-            if (zeros >= 2 || !band) continue;
+            if (zeros >= 2 || !inband) continue;
             float t = 1.f;
             for (int e = 0; e < m; ++e) t = __fmul_rn(t, c[e]);
-            const int b = mk[(int64_t)y * W + x] != 0;
-            const double td = (double)t;
-            const double sg = 1.0 / (1.0 + exp(-td));
-            const double* G = s_g + b * 5;
-            const double dLdt = G[1] + td * (2.0 * G[2] + td * (3.0 * G[3] + td * 4.0 * G[4])) + s_g[10 + b] * sg * (1.0 - sg);
+            double dLdt;
+            if (DENSE) {
+                dLdt = (double)gdense[(obj * H + y) * W + x];
+            } else {
+                const int b = mk[(int64_t)y * W + x] != 0;
+                const double td = (double)t;
+                const double sg = s_g[10 + b] != 0.0 ? (double)__fdiv_rn(1.f, 1.f + expf(-t)) : 0.0;
+                const double* G = s_g + b * 5;
+                dLdt = G[1] + td * (2.0 * G[2] + td * (3.0 * G[3] + td * 4.0 * G[4])) + s_g[10 + b] * sg * (1.0 - sg);
+            }
             if (dLdt == 0.0) continue;
             for (int e = 0; e < m; ++e) {
                 if (w[e] == 0.f) continue;
@@ -532,7 +609,8 @@ extern "C" int tdod_hull(const float* corners2d, int64_t n, float* out_hull, int
 }
 
 extern "C" int tdod_hull_fill_moments(const uint8_t* masks, const int32_t* mask_idx, const float* hull,
-                                      const int32_t* meta, int64_t n, int H, int W, double* out_moments, void* stream) {
+                                      const int32_t* meta, int64_t n, int H, int W, int with_sigmoid,
+                                      double* out_moments, void* stream) {
     if (n == 0) return TDOD_OK;
     if (!masks || !mask_idx || !hull || !meta || !out_moments || n < 0 || H <= 0 || W <= 0 || n > 65535)
         return tdod_fail(TDOD_EINVAL, "tdod_hull_fill_moments: bad argument (n <= 65535)");
@@ -540,7 +618,10 @@ extern "C" int tdod_hull_fill_moments(const uint8_t* masks, const int32_t* mask_
     if (e != cudaSuccess) return (int)e;
     const int rows = fill_rows(n, H);
     dim3 grid((unsigned)cdiv64(H, rows), (unsigned)n);
-    hull_moments_kernel<<<grid, kFillT, 0, (cudaStream_t)stream>>>(masks, mask_idx, hull, meta, H, W, rows, out_moments);
+    if (with_sigmoid)
+        hull_moments_kernel<true><<<grid, kFillT, 0, (cudaStream_t)stream>>>(masks, mask_idx, hull, meta, H, W, out_moments);
+    else
+        hull_moments_kernel<false><<<grid, kFillT, 0, (cudaStream_t)stream>>>(masks, mask_idx, hull, meta, H, W, out_moments);
     TDOD_CHECK_LAUNCH();
     return TDOD_OK;
 }
@@ -556,8 +637,37 @@ extern "C" int tdod_hull_fill_grad(const uint8_t* masks, const int32_t* mask_idx
     if (e != cudaSuccess) return (int)e;
     const int rows = fill_rows(n, H);
     dim3 grid((unsigned)cdiv64(H, rows), (unsigned)n);
-    hull_grad_kernel<<<grid, kFillT, 0, (cudaStream_t)stream>>>(masks, mask_idx, hull, meta, H, W, rows, g_moments,
-                                                               workspace);
+    hull_grad_kernel<false><<<grid, kFillT, 0, (cudaStream_t)stream>>>(masks, mask_idx, hull, meta, H, W, g_moments,
+                                                                      nullptr, workspace);
+    TDOD_CHECK_LAUNCH();
+    hull_grad_finish_kernel<<<blocks_for(n, kT), kT, 0, (cudaStream_t)stream>>>(hull, meta, workspace, n, out_g_corners);
+    TDOD_CHECK_LAUNCH();
+    return TDOD_OK;
+}
+
+extern "C" int tdod_hull_fill(const float* hull, const int32_t* meta, int64_t n, int H, int W, float* out_mask,
+                              void* stream) {
+    if (n == 0) return TDOD_OK;
+    if (!hull || !meta || !out_mask || n < 0 || H <= 0 || W <= 0 || n > 65535)
+        return tdod_fail(TDOD_EINVAL, "tdod_hull_fill: bad argument (n <= 65535)");
+    const int rows = fill_rows(n, H);
+    dim3 grid((unsigned)cdiv64(H, rows), (unsigned)n);
+    hull_fill_kernel<<<grid, kFillT, 0, (cudaStream_t)stream>>>(hull, meta, H, W, rows, out_mask);
+    TDOD_CHECK_LAUNCH();
+    return TDOD_OK;
+}
+
+extern "C" int tdod_hull_fill_dense_grad(const float* hull, const int32_t* meta, int64_t n, int H, int W,
+                                         const float* g_mask, double* workspace, float* out_g_corners, void* stream) {
+    if (n == 0) return TDOD_OK;
+    if (!hull || !meta || !g_mask || !workspace || !out_g_corners || n < 0 || H <= 0 || W <= 0 || n > 65535)
+        return tdod_fail(TDOD_EINVAL, "tdod_hull_fill_dense_grad: bad argument (n <= 65535)");
+    cudaError_t e = cudaMemsetAsync(workspace, 0, sizeof(double) * 24 * n, (cudaStream_t)stream);
+    if (e != cudaSuccess) return (int)e;
+    const int rows = fill_rows(n, H);
+    dim3 grid((unsigned)cdiv64(H, rows), (unsigned)n);
+    hull_grad_kernel<true><<<grid, kFillT, 0, (cudaStream_t)stream>>>(nullptr, nullptr, hull, meta, H, W, nullptr,
+                                                                     g_mask, workspace);
     TDOD_CHECK_LAUNCH();
     hull_grad_finish_kernel<<<blocks_for(n, kT), kT, 0, (cudaStream_t)stream>>>(hull, meta, workspace, n, out_g_corners);
     TDOD_CHECK_LAUNCH();

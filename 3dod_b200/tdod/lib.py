@@ -64,8 +64,10 @@ SIGNATURES = {
     "tdod_cube_box_bwd": (_I, [_P, _P, _P, _P, _L, _P, _P, _P, _P, _P, _P, _P]),
     "tdod_z_sweep": (_I, [_P, _P, _P, _P, _P, _P, _I, _L, _P, _P]),
     "tdod_hull": (_I, [_P, _L, _P, _P, _P]),
-    "tdod_hull_fill_moments": (_I, [_P, _P, _P, _P, _L, _I, _I, _P, _P]),
+    "tdod_hull_fill_moments": (_I, [_P, _P, _P, _P, _L, _I, _I, _I, _P, _P]),
     "tdod_hull_fill_grad": (_I, [_P, _P, _P, _P, _L, _I, _I, _P, _P, _P, _P]),
+    "tdod_hull_fill": (_I, [_P, _P, _L, _I, _I, _P, _P]),
+    "tdod_hull_fill_dense_grad": (_I, [_P, _P, _L, _I, _I, _P, _P, _P, _P]),
 }
 
 

@@ -123,13 +123,13 @@ def hull(corners):
 
 class _HullMoments(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, corners, masks, mask_idx):
+    def forward(ctx, corners, masks, mask_idx, with_sigmoid):
         n, dev = corners.shape[0], corners.device
         H, W = masks.shape[-2:]
         h, meta = hull(corners)
         mom = torch.empty((n, 12), dtype=f64, device=dev)
         L.check(L.lib().tdod_hull_fill_moments(L.ptr(masks), L.ptr(mask_idx, i32, "mask_idx"), L.ptr(h), L.ptr(meta), n,
-                                               int(H), int(W), L.ptr(mom), L.stream_ptr()))
+                                               int(H), int(W), int(bool(with_sigmoid)), L.ptr(mom), L.stream_ptr()))
         ctx.save_for_backward(masks, mask_idx, h, meta)
         return mom
 
@@ -143,10 +143,10 @@ class _HullMoments(torch.autograd.Function):
         out = torch.empty((n, 8, 2), dtype=f32, device=dev)
         L.check(L.lib().tdod_hull_fill_grad(L.ptr(masks), L.ptr(mask_idx), L.ptr(h), L.ptr(meta), n, int(H), int(W),
                                             L.ptr(g), L.ptr(ws), L.ptr(out), L.stream_ptr()))
-        return out, None, None
+        return out, None, None, None
 
 
-def hull_fill_moments(masks, corners, mask_idx):
+def hull_fill_moments(masks, corners, mask_idx, with_sigmoid=True):
     """masks [M,H,W] bool / uint8 on the device, corners [n,8,2] (differentiable), mask_idx [n].  Returns [n,12] fp64:
     sum over pixels of t^k, k = 0..4, for mask == 0 then mask == 1, then sum sigmoid(t) for mask == 0, mask == 1, where
     t is the reference's soft hull mask convex_hull(mask, corners) (utils.py:504-507)."""
@@ -159,7 +159,62 @@ def hull_fill_moments(masks, corners, mask_idx):
     idx = torch.as_tensor(mask_idx, device=corners.device).to(i32).contiguous()
     if idx.numel() != corners.shape[0]:
         raise ValueError("one mask index per cube")
-    return _HullMoments.apply(corners.to(f32), masks, idx)
+    return _HullMoments.apply(corners.to(f32), masks, idx, with_sigmoid)
+
+
+class _DenseFill(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pts, H, W, march, m):
+        n, dev = pts.shape[0], pts.device
+        if march:
+            h, meta = hull(pts)
+        else:                                       # the polygon as given: vertex t is point t
+            h = pts.detach().to(f32).contiguous()
+            meta = torch.full((n, 9), -1, dtype=i32, device=dev)
+            meta[:, 0] = m
+            meta[:, 1:1 + m] = torch.arange(m, dtype=i32, device=dev)
+        out = torch.empty((n, H, W), dtype=f32, device=dev)
+        L.check(L.lib().tdod_hull_fill(L.ptr(h), L.ptr(meta), n, int(H), int(W), L.ptr(out), L.stream_ptr()))
+        ctx.save_for_backward(h, meta)
+        ctx.hw = (int(H), int(W))
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        h, meta = ctx.saved_tensors
+        n, dev = h.shape[0], h.device
+        H, W = ctx.hw
+        ws = torch.empty((n, 24), dtype=f64, device=dev)
+        out = torch.empty((n, 8, 2), dtype=f32, device=dev)
+        L.check(L.lib().tdod_hull_fill_dense_grad(L.ptr(h), L.ptr(meta), n, H, W, L.ptr(g.to(f32).contiguous()),
+                                                  L.ptr(ws), L.ptr(out), L.stream_ptr()))
+        return out, None, None, None, None
+
+
+def jarvis_march(points):
+    """utils.py:424-468 for one set of 8 points [8,2]: the hull vertices [m,2] in the reference's order (values only)"""
+    h, meta = hull(points.reshape(1, 8, 2))
+    return h[0, :int(meta[0, 0])]
+
+
+def fill_polygon(mask, polygon):
+    """utils.py:470-502: soft mask [h,w] of a polygon with at most 8 vertices [m,2]; differentiable in the vertices"""
+    m = polygon.shape[0]
+    if not 1 <= m <= 8:
+        raise ValueError("fill_polygon: 1 to 8 vertices")
+    pts = torch.cat((polygon.to(f32), polygon.new_zeros((8 - m, 2), dtype=f32)))[None]
+    return _DenseFill.apply(pts, mask.shape[-2], mask.shape[-1], False, m)[0]
+
+
+def convex_hull(mask, coords):
+    """utils.py:504-507: fill_polygon(mask, jarvis_march(coords)) for coords [8,2] or a batch [n,8,2] (-> [n,h,w]);
+    only the shape of `mask` is used, as in the reference.  segment_loss does not go through this dense form."""
+    batch = coords.dim() == 3
+    pts = coords.to(f32) if batch else coords.to(f32)[None]
+    if pts.shape[1:] != (8, 2):
+        raise ValueError("convex_hull: coords must be [8,2] or [n,8,2]")
+    out = _DenseFill.apply(pts, mask.shape[-2], mask.shape[-1], True, 0)
+    return out if batch else out[0]
 
 
 def _focal_polynomials(alpha=0.25, gamma=2):
@@ -187,7 +242,9 @@ def segment_loss(gt_mask, bube_corners, at_which_mask_idx, loss='focal'):
     if isinstance(gt_mask, (list, tuple)):
         gt_mask = torch.stack([m.reshape(m.shape[-2:]) for m in gt_mask])
     H, W = gt_mask.shape[-2:]
-    S = hull_fill_moments(gt_mask, bube_corners, at_which_mask_idx)          # [n,12] fp64
+    if loss not in ('focal', 'bce', 'dice'):
+        raise ValueError("loss must be 'focal', 'bce' or 'dice'")
+    S = hull_fill_moments(gt_mask, bube_corners, at_which_mask_idx, with_sigmoid=(loss == 'dice'))   # [n,12] fp64
     if loss == 'focal':
         c = torch.as_tensor(_FOCAL.reshape(10), dtype=f64, device=S.device)
         return ((S[:, :10] * c).sum(1) / (H * W)).to(f32)
@@ -197,7 +254,6 @@ def segment_loss(gt_mask, bube_corners, at_which_mask_idx, loss='focal'):
     if loss == 'dice':
         inter, s_sum, y_sum = S[:, 11].sum(), S[:, 10].sum() + S[:, 11].sum(), S[:, 5].sum()
         return (1 - (2. * inter + 1) / (s_sum + y_sum + 1)).to(f32)
-    raise ValueError("loss must be 'focal', 'bce' or 'dice'")
 
 
 def normal_vector_from_maps(ground_maps, depth_maps, Ks, use_nth=5, seed=0, sample_ids=None):

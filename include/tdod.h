@@ -222,15 +222,22 @@ int tdod_hull(const float* corners2d, int64_t n, float* out_hull, int32_t* out_m
 
 /* fill_polygon (utils.py:470-502) + the pixel sums every loss of segment_loss (roi_heads.py:1030-1052) is made of:
  * with t = soft hull mask at a pixel and x = masks[mask_idx[i]] at it (masks [M,H,W] 1 B/px), out_moments [n,12] fp64 =
- * sum t^k over x==0 (k=0..4), sum t^k over x==1 (k=0..4), sum sigmoid(t) over x==0, over x==1.  The H x W soft mask
- * is never written. */
+ * sum t^k over x==0 (k=0..4), sum t^k over x==1 (k=0..4), sum sigmoid(t) over x==0, over x==1 (the last two only
+ * when with_sigmoid != 0 -- dice_loss needs them --, else the t == 0 pixels' 1/2 alone).  The H x W soft mask is never
+ * written. */
 int tdod_hull_fill_moments(const uint8_t* masks, const int32_t* mask_idx, const float* hull, const int32_t* meta,
-                           int64_t n, int H, int W, double* out_moments, void* stream);
+                           int64_t n, int H, int W, int with_sigmoid, double* out_moments, void* stream);
 
 /* Backward of the sums above to the 8 corners: g_moments [n,12] fp64 -> out_g_corners [n,8,2] fp32.
  * workspace: n * 24 doubles of device scratch. */
 int tdod_hull_fill_grad(const uint8_t* masks, const int32_t* mask_idx, const float* hull, const int32_t* meta, int64_t n,
                         int H, int W, const double* g_moments, double* workspace, float* out_g_corners, void* stream);
+
+/* convex_hull(mask, coords) itself (utils.py:504-507): the dense soft mask out_mask [n,H,W] fp32 of n hulls, and the
+ * backward of sum(g_mask * out_mask) to the 8 corners (workspace: n * 24 doubles). */
+int tdod_hull_fill(const float* hull, const int32_t* meta, int64_t n, int H, int W, float* out_mask, void* stream);
+int tdod_hull_fill_dense_grad(const float* hull, const int32_t* meta, int64_t n, int H, int W, const float* g_mask,
+                              double* workspace, float* out_g_corners, void* stream);
 
 #ifdef __cplusplus
 }

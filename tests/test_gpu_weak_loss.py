@@ -226,3 +226,37 @@ def test_normal_vector_from_maps_is_the_fp32_plane_path():
         assert abs(float(n.norm()) - 1.0) < 1e-5 and float(n[1]) > 0
     with pytest.raises(ValueError):
         WL.project_boxes(torch.zeros((2, 15)), torch.eye(3), [(10, 10)] * 2)          # CPU tensors are refused
+
+
+def test_dense_convex_hull_and_fill_polygon_mirror():
+    """ProposalNetwork.utils.utils.convex_hull / fill_polygon / jarvis_march (utils.py:424-507) as dense images"""
+    from ProposalNetwork.utils import utils as U
+    d = dev()
+    H, W = 90, 120
+    g = torch.Generator().manual_seed(4)
+    pts = torch.rand((5, 8, 2), generator=g) * torch.tensor([W - 1., H - 1.])
+    pts[1, 3] = pts[1, 0]                                  # a duplicate
+    pts[2] = pts[2].round()                                # integer vertices: exact 0 / 1 edge values
+    wgt = torch.rand((5, H, W), generator=g)
+    mask = torch.zeros((H, W), dtype=torch.bool)
+    ref_in = pts.clone().requires_grad_(True)
+    ref = torch.stack([WO.convex_hull((H, W), ref_in[i]) for i in range(5)])
+    ref_g = torch.autograd.grad((ref * wgt).sum(), ref_in)[0]
+    x = pts.to(d).requires_grad_(True)
+    got = U.convex_hull(mask.to(d), x)
+    assert got.shape == (5, H, W)
+    np.testing.assert_array_equal(got.detach().cpu().numpy(), ref.detach().numpy())       # same fp32 products, same order
+    gg = torch.autograd.grad((got * wgt.to(d)).sum(), x)[0]
+    close(gg.cpu(), ref_g, 1e-4, atol_rel=1e-4, what="dense hull grad")
+    one = U.convex_hull(mask.to(d), pts[0].to(d))
+    np.testing.assert_array_equal(one.cpu().numpy(), ref[0].detach().numpy())
+    hull0 = U.jarvis_march(pts[0].to(d))
+    np.testing.assert_array_equal(hull0.cpu().numpy(), WO.jarvis_march(pts[0])[0].numpy())
+    tri = torch.tensor([[10., 10.], [100., 20.], [50., 80.]])
+    ref_t = tri.clone().requires_grad_(True)
+    rf = WO.fill_polygon((H, W), ref_t)
+    rg = torch.autograd.grad((rf * wgt[0]).sum(), ref_t)[0]
+    xt = tri.to(d).requires_grad_(True)
+    gf = U.fill_polygon(mask.to(d), xt)
+    np.testing.assert_array_equal(gf.detach().cpu().numpy(), rf.detach().numpy())
+    close(torch.autograd.grad((gf * wgt[0].to(d)).sum(), xt)[0].cpu(), rg, 1e-4, atol_rel=1e-4, what="fill_polygon grad")

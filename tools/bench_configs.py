@@ -6,6 +6,7 @@ One JSON line per config, device-resident inputs, CUDA events on the launching s
   C1  one 640x480 frame, 5 objects x 1000 proposals (the reference's CPU-runnable case)
   C3  one 1024x768 frame, 50 objects x 10 000 proposals (8-CTA cluster path of the fused kernel)
   C5  back-projection + RANSAC alone at 1920x1080 (K-A only; value in frames/s); both flavours
+  WL  weak-loss geometry, forward + backward for the cubes of 8 C2-shaped frames
 Algorithmic bytes follow SURVEY.md 8(d)."""
 import argparse
 import json
@@ -104,6 +105,58 @@ def run_mode_b(steps, dev, flush):
     return out
 
 
+def run_weak_loss(steps, dev, flush, n_img=8):
+    """SURVEY 8(f) row 4 at the C2 frame shape: forward + backward of the weak-loss geometry for the cubes of n_img frames
+    (project_boxes + GIoU + z_loss + focal segment_loss), next to the oracle (the reference's torch ops on the CPU) on a
+    bounded sample"""
+    import time
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import tdod_oracle as O
+    import weak_loss_oracle as WO
+    from tdod import weak_loss as WL
+    c = synth.CONFIGS["C2"]
+    H, W = c["H"], c["W"]
+    fr = [synth.make_frame(i, H, W, c["n_obj"]) for i in range(n_img)]
+    cubes, Ks, boxes, masks = [], [], [], []
+    for f in fr:
+        g = torch.Generator().manual_seed(f.frame_id)
+        cubes.append(O.propose(f.boxes, f.depth, f.prior_mean, f.prior_std, f.K, 2, normal=torch.tensor([0., 1., 0.05]),
+                               generator=g)["cubes"][:, 0].float())
+        Ks.append(f.K[None].repeat(f.boxes.shape[0], 1, 1)); boxes.append(f.boxes); masks.append(f.masks)
+    cubes, Ks, boxes, masks = torch.cat(cubes), torch.cat(Ks), torch.cat(boxes), torch.cat(masks)
+    N = cubes.shape[0]
+    ims = [(W, H)] * N
+    idx = list(range(N))
+    dc, dK, db, dm = cubes.to(dev), Ks.to(dev), boxes.to(dev), masks.to(dev)
+    im_t = torch.tensor(ims, dtype=torch.int32, device=dev)
+    idx_t = torch.tensor(idx, dtype=torch.int32, device=dev)
+
+    def step():
+        x = dc.clone().requires_grad_(True)
+        o = WL.project_boxes(x, dK, im_t, gt_boxes=db)
+        seg = WL.segment_loss(dm, o["seg_corners"], idx_t)
+        z = WL.z_loss(db, x, dK, im_t, o["boxes"])
+        (o["loss_iou"].mean() + seg.mean() + z.mean()).backward()
+        return x.grad
+    ms = timed(step, steps, flush)
+    # CPU: the same losses through the oracle on the first few cubes
+    ns = min(N, 6)
+    t0 = time.perf_counter()
+    x = cubes[:ns].clone().requires_grad_(True)
+    cs = WO.bube_corners(x, Ks[:ns], ims[:ns])
+    bx = WO.cubes_to_box(x, Ks[:ns], ims[:ns])
+    loss = WO.giou_loss(boxes[:ns], bx).mean() + WO.segment_loss(masks, WO.segment_corners(cs, ims[:ns]), idx[:ns]).mean() + \
+        WO.z_loss(boxes[:ns], x, Ks[:ns], ims[:ns], bx.detach()).mean()
+    loss.backward()
+    cpu_s = time.perf_counter() - t0
+    ab = 2 * N * H * W                                   # every mask read once forward and once backward
+    return {"config": "weak-loss geometry (8f-4), C2 frame shape", "images": n_img, "cubes": N, "ms_per_step": ms,
+            "value": N / (ms * 1e-3), "unit": "cubes/s (forward + backward)", "algorithmic_bytes": ab,
+            "hbm_frac_step": ab / (ms * 1e-3) / 1e9 / peak(), "launches_per_step": "8 libtdod kernels + torch glue",
+            "cpu_oracle": {"cubes": ns, "seconds": cpu_s, "cubes_per_s": ns / cpu_s, "threads": torch.get_num_threads()},
+            "l2": "512 MB buffer rewritten between timed iterations"}
+
+
 def run_c5(steps, dev, flush, frames=None):
     c = synth.CONFIGS["C5"]
     F = frames or c["frames"]
@@ -143,7 +196,7 @@ def run_c5(steps, dev, flush, frames=None):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("configs", nargs="*", default=["C1", "C1B", "C3", "C5"])
+    ap.add_argument("configs", nargs="*", default=["C1", "C1B", "C3", "C5", "WL"])
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--frames", type=int, default=None)
     a = ap.parse_args()
@@ -153,6 +206,8 @@ def main():
     for name in a.configs:
         if name == "C1B":
             print(json.dumps(run_mode_b(a.steps, dev, flush)), flush=True)
+        elif name == "WL":
+            print(json.dumps(run_weak_loss(a.steps, dev, flush)), flush=True)
         elif name == "C5":
             for line in run_c5(a.steps, dev, flush, a.frames):
                 print(json.dumps(line), flush=True)
