@@ -22,6 +22,11 @@ import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
+
+# The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner to fd 1 when
+# NCCL_DEBUG is set on the box), so fd 1 is pointed at stderr for the whole process and the line goes to the saved fd.
+_JSON_OUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
 for p in (os.path.join(ROOT, "3dod_b200"), os.path.join(ROOT, "oracle")):
     if p not in sys.path:
         sys.path.insert(0, p)
@@ -184,7 +189,7 @@ def run_reference(args):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_JSON_OUT, flush=True)
 
 
 # ----------------------------------------------------------------------------------------------------------------------
@@ -353,7 +358,7 @@ def run_tdod(args):
                            "d2h_bytes_per_step": e2e["d2h"], "ms_per_step": e_ms_max, "same_winners_as_resident": e2e["same_winners"]}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_single()
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_JSON_OUT, flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
