@@ -303,6 +303,7 @@ __global__ void __launch_bounds__(kT) hull_kernel(const float* __restrict__ pts,
 
 struct Edges {
     float v1x[8], v1y[8], ex[8], ey[8];
+    float del[8];              // bound on |fp32 edge function - exact edge function| anywhere in the image
     int m;
     int bx0, bx1, by0, by1;    // pixels outside this box have a zero soft mask (see load_edges); empty when bx1 < bx0
 };
@@ -321,6 +322,8 @@ __device__ __forceinline__ void load_edges(const float* __restrict__ hull, const
         E.v1x[t] = ax; E.v1y[t] = ay;
         E.ex[t] = hull[i * 16 + 2 * t2] - ax;
         E.ey[t] = hull[i * 16 + 2 * t2 + 1] - ay;
+        // three roundings of relative size 2^-24 on products no larger than these: 1.8e-7 * B; 1e-6 * B is used
+        E.del[t] = 1e-6f * (((float)W + fabsf(ax)) * fabsf(E.ey[t]) + ((float)H + fabsf(ay)) * fabsf(E.ex[t])) + 1e-30f;
         if (t < E.m) {
             bad |= !(fabsf(ax) < 1e9f) || !(fabsf(ay) < 1e9f);
             lox = fminf(lox, ax); hix = fmaxf(hix, ax); loy = fminf(loy, ay); hiy = fmaxf(hiy, ay);
@@ -328,6 +331,7 @@ __device__ __forceinline__ void load_edges(const float* __restrict__ hull, const
     }
     if (bad) {                 // NaN / huge vertices: no shortcut, every pixel is evaluated
         E.bx0 = 0; E.bx1 = W - 1; E.by0 = 0; E.by1 = H - 1;
+        for (int t = 0; t < 8; ++t) E.del[t] = CUDART_INF_F;
     } else {
         E.bx0 = max(0, (int)floorf(lox)); E.bx1 = min(W - 1, (int)ceilf(hix));
         E.by0 = max(0, (int)floorf(loy)); E.by1 = min(H - 1, (int)ceilf(hiy));
@@ -340,6 +344,27 @@ __device__ __forceinline__ float edge_fn(const Edges& E, int t, float X, float Y
     return __fsub_rn(__fmul_rn(X - E.v1x[t], E.ey[t]), __fmul_rn(Y - E.v1y[t], E.ex[t]));
 }
 __device__ __forceinline__ float clamp01(float e) { return min_nan(max_nan(e, 0.f), 1.f); }
+
+// Hierarchical evaluation: the bounding box is cut into 32 x 8 pixel tiles, one warp per tile.  An edge function is
+// affine, so over a tile it lies between its values at the four corners; lane i < m evaluates edge i there.
+//   some edge below -2 del at all corners  -> its fp32 value is negative at every pixel: the product is exactly 0
+//   every edge above 1 + 2 del everywhere  -> every factor clamps to exactly 1: the product is exactly 1 (no gradient)
+// and only the remaining tiles (those the hull's boundary passes through) are evaluated pixel by pixel.
+constexpr int kTileW = 32, kTileH = 8;
+enum { TILE_OUT = 0, TILE_IN = 1, TILE_MIXED = 2 };
+__device__ __forceinline__ int classify_tile(const Edges& E, int m, int lane, int x0, int y0, int x1, int y1) {
+    bool out_e = false, in_e = false;
+    if (lane < m) {
+        const float a = edge_fn(E, lane, (float)x0, (float)y0), b = edge_fn(E, lane, (float)x1, (float)y0);
+        const float c = edge_fn(E, lane, (float)x0, (float)y1), d = edge_fn(E, lane, (float)x1, (float)y1);
+        const float lo = fminf(fminf(a, b), fminf(c, d)), hi = fmaxf(fmaxf(a, b), fmaxf(c, d));
+        const float dl = E.del[lane];
+        out_e = hi < -2.f * dl;                      // comparisons with NaN / inf are false: such tiles stay MIXED
+        in_e = lo > 1.f + 2.f * dl;                  // strictly above 1: also no tie of min(e, 1) in such a tile
+    }
+    if (__ballot_sync(0xffffffffu, out_e)) return TILE_OUT;
+    return __ballot_sync(0xffffffffu, in_e) == ((1u << m) - 1u) ? TILE_IN : TILE_MIXED;
+}
 
 // number of non-zero bytes in [p, p + n): word loads where the address allows
 __device__ __forceinline__ int count_nonzero(const uint8_t* __restrict__ p, int64_t n, int tid, int nthreads) {
@@ -377,16 +402,30 @@ __global__ void __launch_bounds__(kFillT) hull_moments_kernel(const uint8_t* __r
     const int cnt_one = count_nonzero(mk + s0, s1 - s0, threadIdx.x, kFillT);
     // sums over the pixels with t > 0: all of them, and those with mask == 1 (registers only)
     double all[5] = {0.0, 0.0, 0.0, 0.0, 0.0}, one[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
-    int pos_all = 0, pos_one = 0;
+    int pos_all = 0, pos_one = 0, in_all = 0, in_one = 0;       // in_*: pixels of tiles where t is exactly 1
     const int m = E.m;
     const int bw = E.bx1 - E.bx0 + 1, bh = E.by1 - E.by0 + 1;
-    if (bw > 0 && bh > 0) {
-        const int band = (int)cdiv64(bh, gridDim.x);
-        const int r0 = E.by0 + band * blockIdx.x, r1 = min(E.by1 + 1, r0 + band);
-        const int npx = max(0, r1 - r0) * bw;
-        for (int k = threadIdx.x; k < npx; k += kFillT) {
-            const int y = r0 + k / bw, x = E.bx0 + k % bw;
-            const float X = (float)x, Y = (float)y;
+    const int lane = threadIdx.x & 31;
+    const int ntx = (bw + kTileW - 1) / kTileW, nty = (bh + kTileH - 1) / kTileH;
+    const int ntiles = (bw > 0 && bh > 0) ? ntx * nty : 0;
+    for (int tile = blockIdx.x * (kFillT / 32) + (threadIdx.x >> 5); tile < ntiles; tile += gridDim.x * (kFillT / 32)) {
+        // columns rotated by the tile row: with a fixed stride a warp would own whole tile columns, and the warps owning
+        // the columns of the hull's left / right boundary would do all the per-pixel work of the CTA
+        const int ty = tile / ntx, tx = (tile - ty * ntx + 5 * ty) % ntx;
+        const int x0 = E.bx0 + tx * kTileW, y0 = E.by0 + ty * kTileH;
+        const int x1 = min(x0 + kTileW - 1, E.bx1), y1 = min(y0 + kTileH - 1, E.by1);
+        const int cls = classify_tile(E, m, lane, x0, y0, x1, y1);
+        if (cls == TILE_OUT) continue;
+        const int x = x0 + lane;
+        if (x > x1) continue;
+        const float X = (float)x;
+        for (int y = y0; y <= y1; ++y) {
+            if (cls == TILE_IN) {
+                ++in_all;
+                in_one += mk[(int64_t)y * W + x] != 0;
+                continue;
+            }
+            const float Y = (float)y;
             float t = 1.f;
             for (int e = 0; e < m; ++e) {
                 t = __fmul_rn(t, clamp01(edge_fn(E, e, X, Y)));
@@ -401,6 +440,14 @@ __global__ void __launch_bounds__(kFillT) hull_moments_kernel(const uint8_t* __r
 #pragma unroll
             for (int q = 0; q < 5; ++q) { all[q] += p[q]; one[q] += bd * p[q]; }
         }
+    }
+    {   // t == 1 pixels: every power is 1
+        const double sg1 = SIG ? (double)__fdiv_rn(1.f, 1.f + expf(-1.f)) : 0.0;
+        const double na = (double)in_all, no = (double)in_one;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) { all[q] += na; one[q] += no; }
+        all[4] += sg1 * na; one[4] += sg1 * no;
+        pos_all += in_all; pos_one += in_one;
     }
     // pixels with t == 0 contribute t^0 = 1 and sigmoid(0) = 1/2: they come from the slice counts
     const double c1 = (double)cnt_one, slice_px = threadIdx.x == 0 ? (double)(s1 - s0) : 0.0;
@@ -457,65 +504,93 @@ __global__ void __launch_bounds__(kFillT) hull_grad_kernel(const uint8_t* __rest
                                                            int H, int W, const double* __restrict__ gmom,
                                                            const float* __restrict__ gdense, double* __restrict__ edge_acc) {
     __shared__ Edges E;
-    __shared__ double s_acc[8][3];
+    __shared__ double s_acc[kFillT / 32][8][3];     // one set of accumulators per warp: no contention between warps
     __shared__ double s_g[kMom];
     const int64_t obj = blockIdx.y;
     if (threadIdx.x == 0) load_edges(hull, meta, obj, H, W, E);
-    if (threadIdx.x < 24) s_acc[threadIdx.x / 3][threadIdx.x % 3] = 0.0;
+    for (int k = threadIdx.x; k < (kFillT / 32) * 24; k += kFillT) (&s_acc[0][0][0])[k] = 0.0;
     if (!DENSE && threadIdx.x >= 32 && threadIdx.x < 32 + kMom) s_g[threadIdx.x - 32] = gmom[obj * kMom + threadIdx.x - 32];
     __syncthreads();
     const uint8_t* mk = DENSE ? nullptr : masks + (int64_t)mask_idx[obj] * H * W;
     const int m = E.m;
     const int bw = E.bx1 - E.bx0 + 1, bh = E.by1 - E.by0 + 1;
-    const int band = (bw > 0 && bh > 0) ? (int)cdiv64(bh, gridDim.x) : 0;
-    const int r0 = E.by0 + band * blockIdx.x, r1 = min(E.by1 + 1, r0 + band);
-    const int npx = (band > 0 ? max(0, r1 - r0) : 0) * bw;
-    for (int k = threadIdx.x; k < npx; k += kFillT) {
-        const int y = r0 + k / bw, x = E.bx0 + k % bw;
-        {
-            const float X = (float)x, Y = (float)y;
+    const int lane = threadIdx.x & 31;
+    const int ntx = (bw + kTileW - 1) / kTileW, nty = (bh + kTileH - 1) / kTileH;
+    const int ntiles = (bw > 0 && bh > 0) ? ntx * nty : 0;
+    for (int tile = blockIdx.x * (kFillT / 32) + (threadIdx.x >> 5); tile < ntiles; tile += gridDim.x * (kFillT / 32)) {
+        // columns rotated by the tile row: with a fixed stride a warp would own whole tile columns, and the warps owning
+        // the columns of the hull's left / right boundary would do all the per-pixel work of the CTA
+        const int ty = tile / ntx, tx = (tile - ty * ntx + 5 * ty) % ntx;
+        const int x0 = E.bx0 + tx * kTileW, y0 = E.by0 + ty * kTileH;
+        const int x1 = min(x0 + kTileW - 1, E.bx1), y1 = min(y0 + kTileH - 1, E.by1);
+        // a tile with t == 0 or with every edge function above 1 has no pixel with 0 <= e_i <= 1: no gradient
+        if (classify_tile(E, m, lane, x0, y0, x1, y1) != TILE_MIXED) continue;
+        const int x = x0 + lane;
+        const bool live = x <= x1;
+        const float X = (float)x;
+        for (int y = y0; y <= y1; ++y) {               // warp-uniform: contributions are reduced over the warp
+            const float Y = (float)y;
             float c[8], w[8];
-            int zeros = 0;
-            bool inband = false;
-            for (int e = 0; e < m; ++e) {
-                const float f = edge_fn(E, e, X, Y);
-                c[e] = clamp01(f);
-                // max(f, 0) then min(., 1): ties route half of the gradient (derivatives.yaml maximum / minimum)
-                w[e] = (f > 0.f && f < 1.f) ? 1.f : ((f == 0.f || f == 1.f) ? 0.5f : 0.f);
-                zeros += c[e] == 0.f;
-                inband |= w[e] != 0.f;
-                if (zeros >= 2) break;
+            bool ok = live;
+            if (ok) {
+                int zeros = 0;
+                bool inband = false;
+                for (int e = 0; e < m; ++e) {
+                    const float f = edge_fn(E, e, X, Y);
+                    // a strictly negative edge function zeroes its own weight and every product leaving another edge out
+                    if (f < 0.f) { zeros = 2; break; }
+                    c[e] = clamp01(f);
+                    // max(f, 0) then min(., 1): ties route half of the gradient (derivatives.yaml maximum / minimum)
+                    w[e] = (f > 0.f && f < 1.f) ? 1.f : ((f == 0.f || f == 1.f) ? 0.5f : 0.f);
+                    zeros += c[e] == 0.f;
+                    inband |= w[e] != 0.f;
+                    if (zeros >= 2) break;
+                }
+                ok = zeros < 2 && inband;
             }
-            if (zeros >= 2 || !inband) continue;
-            float t = 1.f;
-            for (int e = 0; e < m; ++e) t = __fmul_rn(t, c[e]);
-            double dLdt;
-            if (DENSE) {
-                dLdt = (double)gdense[(obj * H + y) * W + x];
-            } else {
-                const int b = mk[(int64_t)y * W + x] != 0;
-                const double td = (double)t;
-                const double sg = s_g[10 + b] != 0.0 ? (double)__fdiv_rn(1.f, 1.f + expf(-t)) : 0.0;
-                const double* G = s_g + b * 5;
-                dLdt = G[1] + td * (2.0 * G[2] + td * (3.0 * G[3] + td * 4.0 * G[4])) + s_g[10 + b] * sg * (1.0 - sg);
+            double dLdt = 0.0;
+            if (ok) {
+                if (DENSE) {
+                    dLdt = (double)gdense[(obj * H + y) * W + x];
+                } else {
+                    float t = 1.f;
+                    for (int e = 0; e < m; ++e) t = __fmul_rn(t, c[e]);
+                    const int b = mk[(int64_t)y * W + x] != 0;
+                    const double td = (double)t;
+                    const double sg = s_g[10 + b] != 0.0 ? (double)__fdiv_rn(1.f, 1.f + expf(-t)) : 0.0;
+                    const double* G = s_g + b * 5;
+                    dLdt = G[1] + td * (2.0 * G[2] + td * (3.0 * G[3] + td * 4.0 * G[4])) + s_g[10 + b] * sg * (1.0 - sg);
+                }
+                ok = dLdt != 0.0;
             }
-            if (dLdt == 0.0) continue;
+            if (!__any_sync(0xffffffffu, ok)) continue;
             for (int e = 0; e < m; ++e) {
-                if (w[e] == 0.f) continue;
-                float P = 1.f;
-                for (int o = 0; o < m; ++o)
-                    if (o != e) P *= c[o];
-                if (P == 0.f) continue;
-                const double g = dLdt * (double)P * (double)w[e];
-                atomicAdd(&s_acc[e][0], g);
-                atomicAdd(&s_acc[e][1], g * (double)X);
-                atomicAdd(&s_acc[e][2], g * (double)Y);
+                double g = 0.0;
+                if (ok && w[e] != 0.f) {
+                    float P = 1.f;
+                    for (int o = 0; o < m; ++o)
+                        if (o != e) P *= c[o];
+                    g = dLdt * (double)P * (double)w[e];
+                }
+                if (!__any_sync(0xffffffffu, g != 0.0)) continue;
+                double g0 = g, g1 = g * (double)X, g2 = g * (double)Y;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    g0 += __shfl_xor_sync(0xffffffffu, g0, o);
+                    g1 += __shfl_xor_sync(0xffffffffu, g1, o);
+                    g2 += __shfl_xor_sync(0xffffffffu, g2, o);
+                }
+                if (lane == 0) {                       // this warp's own accumulators
+                    double* acc = s_acc[threadIdx.x >> 5][e];
+                    acc[0] += g0; acc[1] += g1; acc[2] += g2;
+                }
             }
         }
     }
     __syncthreads();
     if (threadIdx.x < 24) {
-        const double v = s_acc[threadIdx.x / 3][threadIdx.x % 3];
+        double v = 0.0;
+        for (int w = 0; w < kFillT / 32; ++w) v += (&s_acc[w][0][0])[threadIdx.x];
         if (v != 0.0) atomicAdd(edge_acc + obj * 24 + threadIdx.x, v);
     }
 }
