@@ -183,9 +183,13 @@ __global__ void __launch_bounds__(kPackT) pack_tma_kernel(const uint8_t* __restr
     const int64_t n_tiles = n_masks * tiles_per_mask;
     if (blockIdx.x == 0 && tid < 4) lists[tid] = 0;       // work-list counters of the later passes
 
+    // every thread needs the tile geometry of every tile: 32-bit division (the entry point bounds n_tiles), and the
+    // word -> (row, column) split of the inner loop by a multiply-high with a precomputed reciprocal of Wp
+    const uint32_t wp_magic = (uint32_t)((0x100000000ull + (uint32_t)Wp - 1u) / (uint32_t)Wp);   // exact for q * Wp < 2^32
     auto geometry = [&](int64_t tile, int64_t& m, int& r0, int& r1, int64_t& b0, int64_t& c0, int& nch) {
-        m = tile / tiles_per_mask;
-        r0 = (int)(tile - m * tiles_per_mask) * kPackRows; r1 = min(H, r0 + kPackRows);
+        const uint32_t mm = (uint32_t)tile / (uint32_t)tiles_per_mask;
+        m = mm;
+        r0 = (int)((uint32_t)tile - mm * (uint32_t)tiles_per_mask) * kPackRows; r1 = min(H, r0 + kPackRows);
         b0 = mis + m * HW + (int64_t)r0 * W;
         const int64_t b1 = mis + m * HW + (int64_t)r1 * W;
         c0 = b0 >> 4;
@@ -223,7 +227,7 @@ __global__ void __launch_bounds__(kPackT) pack_tma_kernel(const uint8_t* __restr
         const int nwords = (r1 - r0) * Wp;
         int lo = 0x7fffffff, hi = -1;
         for (int q = tid; q < nwords; q += kPackT) {
-            const int rr = q / Wp, w = q - rr * Wp, r = r0 + rr;
+            const int rr = (int)__umulhi((uint32_t)q, wp_magic), w = q - rr * Wp, r = r0 + rr;
             const int o = (int)(b0 - (c0 << 4)) + rr * W + 32 * w;          // bit offset of the window in the stream
             uint32_t word = __funnelshift_r(sb32[o >> 5], sb32[(o >> 5) + 1], o & 31);
             const int nb = W - 32 * w;
@@ -1076,7 +1080,8 @@ extern "C" int tdod_mask_pack(const uint8_t* masks, int64_t n_masks, int H, int 
     const int max_chunks = (int)(((int64_t)kPackRows * W + 30) / 16 + 1);
     const int raw_cap = ((max_chunks * 16 + 127) / 128) * 128;
     const size_t tma_smem = 2 * (size_t)raw_cap + pk_smem + 16;
-    const bool use_tma = tma_smem <= 100 * 1024 && getenv("TDOD_PACK_NO_TMA") == nullptr;
+    const bool use_tma = tma_smem <= 100 * 1024 && n_tiles + 148 * 8 < 0x7fffffffll &&    // tile ids are divided in 32 bits
+                         getenv("TDOD_PACK_NO_TMA") == nullptr;
     if (use_tma) {
         e = cudaFuncSetAttribute(pack_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tma_smem);
         if (e != cudaSuccess) return (int)e;
