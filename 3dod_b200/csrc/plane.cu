@@ -73,7 +73,7 @@ __global__ void __cluster_dims__(kBpCluster, 1, 1) __launch_bounds__(kBpT)
         const bool valid = idx < hi;
         bool on = valid;
         if (valid && gp) {
-            const int v = (int)(idx / Ws), u = (int)(idx - (int64_t)v * Ws);
+            const int v = (int)((uint32_t)idx / (uint32_t)Ws), u = (int)((uint32_t)idx - (uint32_t)v * (uint32_t)Ws);   // idx < P < 2^31 (counts are int32)
             on = __ldg(gp + (size_t)(v * stride) * W + (size_t)(u * stride)) > 0;
         }
         const unsigned m_on = __ballot_sync(0xffffffffu, valid && on), m_off = __ballot_sync(0xffffffffu, valid && !on);
@@ -124,7 +124,7 @@ __global__ void __cluster_dims__(kBpCluster, 1, 1) __launch_bounds__(kBpT)
         bool on = valid;
         T x = 0, y = 0, z = 0;
         if (valid) {
-            const int v = (int)(idx / Ws), u = (int)(idx - (int64_t)v * Ws);
+            const int v = (int)((uint32_t)idx / (uint32_t)Ws), u = (int)((uint32_t)idx - (uint32_t)v * (uint32_t)Ws);   // idx < P < 2^31 (counts are int32)
             const size_t pix = (size_t)(v * stride) * W + (size_t)(u * stride);
             if (gp) on = __ldg(gp + pix) > 0;
             if (on || oo) {
