@@ -381,7 +381,7 @@ __device__ __forceinline__ int count_nonzero(const uint8_t* __restrict__ p, int6
     return c;
 }
 
-// forward: per object the sums over pixels of t^k (k = 0..4) and sigmoid(t), split by mask value x.  gridDim.x CTAs
+// forward: per object the sums over pixels of t^k (k = 0..4) and sigmoid(t), split by mask value x.  gridDim.y CTAs
 // per object: each counts the set pixels of one slice of the whole mask (the t = 0 terms: t^0 and sigmoid(0) = 1/2)
 // and evaluates the soft mask on one band of rows of the hull's bounding box.
 template <bool SIG>
@@ -392,13 +392,13 @@ __global__ void __launch_bounds__(kFillT) hull_moments_kernel(const uint8_t* __r
                                                               double* __restrict__ mom) {
     __shared__ Edges E;
     __shared__ double s_red[kFillT / 32][kMom];
-    const int64_t obj = blockIdx.y;
+    const int64_t obj = blockIdx.x;
     if (threadIdx.x == 0) load_edges(hull, meta, obj, H, W, E);
     __syncthreads();
     const uint8_t* mk = masks + (int64_t)mask_idx[obj] * H * W;
     const int64_t HW = (int64_t)H * W;
-    const int64_t slice = cdiv64(HW, gridDim.x);
-    const int64_t s0 = min(HW, slice * blockIdx.x), s1 = min(HW, s0 + slice);
+    const int64_t slice = cdiv64(HW, gridDim.y);
+    const int64_t s0 = min(HW, slice * blockIdx.y), s1 = min(HW, s0 + slice);
     const int cnt_one = count_nonzero(mk + s0, s1 - s0, threadIdx.x, kFillT);
     // sums over the pixels with t > 0: all of them, and those with mask == 1 (registers only)
     double all[5] = {0.0, 0.0, 0.0, 0.0, 0.0}, one[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
@@ -408,7 +408,7 @@ __global__ void __launch_bounds__(kFillT) hull_moments_kernel(const uint8_t* __r
     const int lane = threadIdx.x & 31;
     const int ntx = (bw + kTileW - 1) / kTileW, nty = (bh + kTileH - 1) / kTileH;
     const int ntiles = (bw > 0 && bh > 0) ? ntx * nty : 0;
-    for (int tile = blockIdx.x * (kFillT / 32) + (threadIdx.x >> 5); tile < ntiles; tile += gridDim.x * (kFillT / 32)) {
+    for (int tile = blockIdx.y * (kFillT / 32) + (threadIdx.x >> 5); tile < ntiles; tile += gridDim.y * (kFillT / 32)) {
         // columns rotated by the tile row: with a fixed stride a warp would own whole tile columns, and the warps owning
         // the columns of the hull's left / right boundary would do all the per-pixel work of the CTA
         const int ty = tile / ntx, tx = (tile - ty * ntx + 5 * ty) % ntx;
@@ -476,10 +476,10 @@ __global__ void __launch_bounds__(kFillT) hull_moments_kernel(const uint8_t* __r
 __global__ void __launch_bounds__(kFillT) hull_fill_kernel(const float* __restrict__ hull, const int32_t* __restrict__ meta,
                                                            int H, int W, int rows, float* __restrict__ out) {
     __shared__ Edges E;
-    const int64_t obj = blockIdx.y;
+    const int64_t obj = blockIdx.x;
     if (threadIdx.x == 0) load_edges(hull, meta, obj, H, W, E);
     __syncthreads();
-    const int r0 = blockIdx.x * rows, r1 = min(H, r0 + rows);
+    const int r0 = blockIdx.y * rows, r1 = min(H, r0 + rows);
     const int m = E.m;
     for (int y = r0; y < r1; ++y) {
         const float Y = (float)y;
@@ -506,7 +506,7 @@ __global__ void __launch_bounds__(kFillT) hull_grad_kernel(const uint8_t* __rest
     __shared__ Edges E;
     __shared__ double s_acc[kFillT / 32][8][3];     // one set of accumulators per warp: no contention between warps
     __shared__ double s_g[kMom];
-    const int64_t obj = blockIdx.y;
+    const int64_t obj = blockIdx.x;
     if (threadIdx.x == 0) load_edges(hull, meta, obj, H, W, E);
     for (int k = threadIdx.x; k < (kFillT / 32) * 24; k += kFillT) (&s_acc[0][0][0])[k] = 0.0;
     if (!DENSE && threadIdx.x >= 32 && threadIdx.x < 32 + kMom) s_g[threadIdx.x - 32] = gmom[obj * kMom + threadIdx.x - 32];
@@ -517,7 +517,7 @@ __global__ void __launch_bounds__(kFillT) hull_grad_kernel(const uint8_t* __rest
     const int lane = threadIdx.x & 31;
     const int ntx = (bw + kTileW - 1) / kTileW, nty = (bh + kTileH - 1) / kTileH;
     const int ntiles = (bw > 0 && bh > 0) ? ntx * nty : 0;
-    for (int tile = blockIdx.x * (kFillT / 32) + (threadIdx.x >> 5); tile < ntiles; tile += gridDim.x * (kFillT / 32)) {
+    for (int tile = blockIdx.y * (kFillT / 32) + (threadIdx.x >> 5); tile < ntiles; tile += gridDim.y * (kFillT / 32)) {
         // columns rotated by the tile row: with a fixed stride a warp would own whole tile columns, and the warps owning
         // the columns of the hull's left / right boundary would do all the per-pixel work of the CTA
         const int ty = tile / ntx, tx = (tile - ty * ntx + 5 * ty) % ntx;
@@ -687,12 +687,12 @@ extern "C" int tdod_hull_fill_moments(const uint8_t* masks, const int32_t* mask_
                                       const int32_t* meta, int64_t n, int H, int W, int with_sigmoid,
                                       double* out_moments, void* stream) {
     if (n == 0) return TDOD_OK;
-    if (!masks || !mask_idx || !hull || !meta || !out_moments || n < 0 || H <= 0 || W <= 0 || n > 65535)
-        return tdod_fail(TDOD_EINVAL, "tdod_hull_fill_moments: bad argument (n <= 65535)");
+    if (!masks || !mask_idx || !hull || !meta || !out_moments || n < 0 || H <= 0 || W <= 0)
+        return tdod_fail(TDOD_EINVAL, "tdod_hull_fill_moments: bad argument");
     cudaError_t e = cudaMemsetAsync(out_moments, 0, sizeof(double) * kMom * n, (cudaStream_t)stream);
     if (e != cudaSuccess) return (int)e;
     const int rows = fill_rows(n, H);
-    dim3 grid((unsigned)cdiv64(H, rows), (unsigned)n);
+    dim3 grid((unsigned)n, (unsigned)cdiv64(H, rows));     // objects along x: no 65535 limit
     if (with_sigmoid)
         hull_moments_kernel<true><<<grid, kFillT, 0, (cudaStream_t)stream>>>(masks, mask_idx, hull, meta, H, W, out_moments);
     else
@@ -706,12 +706,12 @@ extern "C" int tdod_hull_fill_grad(const uint8_t* masks, const int32_t* mask_idx
                                    float* out_g_corners, void* stream) {
     if (n == 0) return TDOD_OK;
     if (!masks || !mask_idx || !hull || !meta || !g_moments || !workspace || !out_g_corners || n < 0 || H <= 0 ||
-        W <= 0 || n > 65535)
-        return tdod_fail(TDOD_EINVAL, "tdod_hull_fill_grad: bad argument (n <= 65535)");
+        W <= 0)
+        return tdod_fail(TDOD_EINVAL, "tdod_hull_fill_grad: bad argument");
     cudaError_t e = cudaMemsetAsync(workspace, 0, sizeof(double) * 24 * n, (cudaStream_t)stream);
     if (e != cudaSuccess) return (int)e;
     const int rows = fill_rows(n, H);
-    dim3 grid((unsigned)cdiv64(H, rows), (unsigned)n);
+    dim3 grid((unsigned)n, (unsigned)cdiv64(H, rows));     // objects along x: no 65535 limit
     hull_grad_kernel<false><<<grid, kFillT, 0, (cudaStream_t)stream>>>(masks, mask_idx, hull, meta, H, W, g_moments,
                                                                       nullptr, workspace);
     TDOD_CHECK_LAUNCH();
@@ -723,10 +723,10 @@ extern "C" int tdod_hull_fill_grad(const uint8_t* masks, const int32_t* mask_idx
 extern "C" int tdod_hull_fill(const float* hull, const int32_t* meta, int64_t n, int H, int W, float* out_mask,
                               void* stream) {
     if (n == 0) return TDOD_OK;
-    if (!hull || !meta || !out_mask || n < 0 || H <= 0 || W <= 0 || n > 65535)
-        return tdod_fail(TDOD_EINVAL, "tdod_hull_fill: bad argument (n <= 65535)");
+    if (!hull || !meta || !out_mask || n < 0 || H <= 0 || W <= 0)
+        return tdod_fail(TDOD_EINVAL, "tdod_hull_fill: bad argument");
     const int rows = fill_rows(n, H);
-    dim3 grid((unsigned)cdiv64(H, rows), (unsigned)n);
+    dim3 grid((unsigned)n, (unsigned)cdiv64(H, rows));     // objects along x: no 65535 limit
     hull_fill_kernel<<<grid, kFillT, 0, (cudaStream_t)stream>>>(hull, meta, H, W, rows, out_mask);
     TDOD_CHECK_LAUNCH();
     return TDOD_OK;
@@ -735,12 +735,12 @@ extern "C" int tdod_hull_fill(const float* hull, const int32_t* meta, int64_t n,
 extern "C" int tdod_hull_fill_dense_grad(const float* hull, const int32_t* meta, int64_t n, int H, int W,
                                          const float* g_mask, double* workspace, float* out_g_corners, void* stream) {
     if (n == 0) return TDOD_OK;
-    if (!hull || !meta || !g_mask || !workspace || !out_g_corners || n < 0 || H <= 0 || W <= 0 || n > 65535)
-        return tdod_fail(TDOD_EINVAL, "tdod_hull_fill_dense_grad: bad argument (n <= 65535)");
+    if (!hull || !meta || !g_mask || !workspace || !out_g_corners || n < 0 || H <= 0 || W <= 0)
+        return tdod_fail(TDOD_EINVAL, "tdod_hull_fill_dense_grad: bad argument");
     cudaError_t e = cudaMemsetAsync(workspace, 0, sizeof(double) * 24 * n, (cudaStream_t)stream);
     if (e != cudaSuccess) return (int)e;
     const int rows = fill_rows(n, H);
-    dim3 grid((unsigned)cdiv64(H, rows), (unsigned)n);
+    dim3 grid((unsigned)n, (unsigned)cdiv64(H, rows));     // objects along x: no 65535 limit
     hull_grad_kernel<true><<<grid, kFillT, 0, (cudaStream_t)stream>>>(nullptr, nullptr, hull, meta, H, W, nullptr,
                                                                      g_mask, workspace);
     TDOD_CHECK_LAUNCH();
