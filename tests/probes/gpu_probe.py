@@ -1,7 +1,7 @@
 """Diagnostic (not a pytest): prints max deviations of the CUDA path from the golden fixtures / oracle."""
 import os, sys, hashlib
 import numpy as np, torch
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.join(ROOT, "3dod_b200")); sys.path.insert(0, os.path.join(ROOT, "oracle"))
 from tdod import api, synth, lib as L
 import tdod_oracle as O

@@ -1,7 +1,7 @@
 """Diagnostic: mask_rect / segmentation / point-cloud kernels vs golden fixtures and cv2 on the box."""
 import os, sys, time
 import numpy as np, torch
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.join(ROOT, "3dod_b200")); sys.path.insert(0, os.path.join(ROOT, "oracle"))
 from tdod import api, synth
 import tdod_oracle as O

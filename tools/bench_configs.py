@@ -107,29 +107,21 @@ def run_mode_b(steps, dev, flush):
 
 def run_weak_loss(steps, dev, flush, n_img=8):
     """SURVEY 8(f) row 4 at the C2 frame shape: forward + backward of the weak-loss geometry for the cubes of n_img frames
-    (project_boxes + GIoU + z_loss + focal segment_loss), next to the oracle (the reference's torch ops on the CPU) on a
-    bounded sample"""
-    import time
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import tdod_oracle as O
-    import weak_loss_oracle as WO
+    (project_boxes + GIoU + z_loss + focal segment_loss).  The cubes are proposals of the product path itself; the
+    oracle stays test infrastructure (its CPU time for the same losses: `cpu_oracle` in profiles/r01_e_bench_configs.jsonl,
+    recorded once from a test session)."""
     from tdod import weak_loss as WL
     c = synth.CONFIGS["C2"]
     H, W = c["H"], c["W"]
-    fr = [synth.make_frame(i, H, W, c["n_obj"]) for i in range(n_img)]
-    cubes, Ks, boxes, masks = [], [], [], []
-    for f in fr:
-        g = torch.Generator().manual_seed(f.frame_id)
-        cubes.append(O.propose(f.boxes, f.depth, f.prior_mean, f.prior_std, f.K, 2, normal=torch.tensor([0., 1., 0.05]),
-                               generator=g)["cubes"][:, 0].float())
-        Ks.append(f.K[None].repeat(f.boxes.shape[0], 1, 1)); boxes.append(f.boxes); masks.append(f.masks)
-    cubes, Ks, boxes, masks = torch.cat(cubes), torch.cat(Ks), torch.cat(boxes), torch.cat(masks)
-    N = cubes.shape[0]
-    ims = [(W, H)] * N
-    idx = list(range(N))
-    dc, dK, db, dm = cubes.to(dev), Ks.to(dev), boxes.to(dev), masks.to(dev)
-    im_t = torch.tensor(ims, dtype=torch.int32, device=dev)
-    idx_t = torch.tensor(idx, dtype=torch.int32, device=dev)
+    fr = [synth.make_frame(i, H, W, c["n_obj"], device=dev) for i in range(n_img)]
+    batch = pipeline.FrameBatch.from_frames(fr, dev)
+    sel = pipeline.select(batch, 8, seed=3, return_all=True)
+    dc = sel.all.all_cubes[:, 0].contiguous()
+    N = dc.shape[0]
+    dK = batch.K[batch.obj_frame.long()].contiguous()
+    db, dm = batch.boxes, batch.masks
+    im_t = torch.tensor([(W, H)] * N, dtype=torch.int32, device=dev)
+    idx_t = torch.arange(N, dtype=torch.int32, device=dev)
 
     def step():
         x = dc.clone().requires_grad_(True)
@@ -139,21 +131,10 @@ def run_weak_loss(steps, dev, flush, n_img=8):
         (o["loss_iou"].mean() + seg.mean() + z.mean()).backward()
         return x.grad
     ms = timed(step, steps, flush)
-    # CPU: the same losses through the oracle on the first few cubes
-    ns = min(N, 6)
-    t0 = time.perf_counter()
-    x = cubes[:ns].clone().requires_grad_(True)
-    cs = WO.bube_corners(x, Ks[:ns], ims[:ns])
-    bx = WO.cubes_to_box(x, Ks[:ns], ims[:ns])
-    loss = WO.giou_loss(boxes[:ns], bx).mean() + WO.segment_loss(masks, WO.segment_corners(cs, ims[:ns]), idx[:ns]).mean() + \
-        WO.z_loss(boxes[:ns], x, Ks[:ns], ims[:ns], bx.detach()).mean()
-    loss.backward()
-    cpu_s = time.perf_counter() - t0
     ab = 2 * N * H * W                                   # every mask read once forward and once backward
     return {"config": "weak-loss geometry (8f-4), C2 frame shape", "images": n_img, "cubes": N, "ms_per_step": ms,
             "value": N / (ms * 1e-3), "unit": "cubes/s (forward + backward)", "algorithmic_bytes": ab,
             "hbm_frac_step": ab / (ms * 1e-3) / 1e9 / peak(), "launches_per_step": "8 libtdod kernels + torch glue",
-            "cpu_oracle": {"cubes": ns, "seconds": cpu_s, "cubes_per_s": ns / cpu_s, "threads": torch.get_num_threads()},
             "l2": "512 MB buffer rewritten between timed iterations"}
 
 

@@ -1,18 +1,16 @@
+"""Stage times of the weak-loss geometry on the cubes of 8 C2-shaped frames: CUDA events around
+project_boxes / segment_loss / z_loss / backward, and the two fill kernels alone.  python tools/weakloss_stages.py"""
 import os, sys, json
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))  # tools/ -> repo root
-sys.path.insert(0, os.path.join(ROOT, "3dod_b200")); sys.path.insert(0, os.path.join(ROOT, "oracle"))
+sys.path.insert(0, os.path.join(ROOT, "3dod_b200"))
 import torch
-import tdod_oracle as O
-from tdod import synth, weak_loss as WL, lib as L
+from tdod import pipeline, synth, weak_loss as WL, lib as L
 dev = torch.device("cuda:0")
 c = synth.CONFIGS["C2"]; H, W = c["H"], c["W"]
-fr = [synth.make_frame(i, H, W, c["n_obj"]) for i in range(8)]
-cubes, Ks, boxes, masks = [], [], [], []
-for f in fr:
-    g = torch.Generator().manual_seed(f.frame_id)
-    cubes.append(O.propose(f.boxes, f.depth, f.prior_mean, f.prior_std, f.K, 2, normal=torch.tensor([0., 1., 0.05]), generator=g)["cubes"][:, 0].float())
-    Ks.append(f.K[None].repeat(f.boxes.shape[0], 1, 1)); boxes.append(f.boxes); masks.append(f.masks)
-dc, dK, db, dm = [torch.cat(t).to(dev) for t in (cubes, Ks, boxes, masks)]
+fr = [synth.make_frame(i, H, W, c["n_obj"], device=dev) for i in range(8)]
+batch = pipeline.FrameBatch.from_frames(fr, dev)
+dc = pipeline.select(batch, 8, seed=3, return_all=True).all.all_cubes[:, 0].contiguous()    # proposals of the product path
+dK, db, dm = batch.K[batch.obj_frame.long()].contiguous(), batch.boxes, batch.masks
 N = dc.shape[0]
 im_t = torch.tensor([(W, H)] * N, dtype=torch.int32, device=dev); idx_t = torch.arange(N, dtype=torch.int32, device=dev)
 def ev(): return torch.cuda.Event(enable_timing=True)
