@@ -32,7 +32,7 @@ namespace {
 #define TDOD_KB_T 256
 #endif
 #ifndef TDOD_KB_MINB
-#define TDOD_KB_MINB 4
+#define TDOD_KB_MINB 5
 #endif
 #ifndef TDOD_KB_RUNCAP
 #define TDOD_KB_RUNCAP 2048
@@ -474,10 +474,11 @@ __device__ int label_runs(const uint32_t* bm, int H, int W, int Wp, RunSet rs, i
 // registers) and the calipers' walk around the hull (one thread, everything it reads precomputed in parallel).
 constexpr int kChainCap = 512;    // vertices of one strictly convex chain (a lattice polygon in a <=1024^2 grid has < 360)
 constexpr int kHullCap = 2 * kChainCap;
-struct HullBuf { int16_t* rx; int16_t* ry; int16_t* lx; int16_t* ly; float* hx; float* hy; float* vx; float* vy; float* inv; };
+struct HullBuf { int16_t* rx; int16_t* ry; int16_t* lx; int16_t* ly; float* hx; float* hy; float* vx; float* vy; float* invf; double* inv; };
 
-// OpenCV rotatingCalipers (CALIPERS_MINAREARECT), fp32 with every product/sum rounded on its own (the x86
-// build has no FMA contraction), then minAreaRect's centre/size/angle and RotatedRect::points (boxPoints).
+// OpenCV rotatingCalipers (CALIPERS_MINAREARECT) as the installed 4.13 computes it: edge vectors, inverse lengths
+// and the cosines that decide which caliper advances in double, everything else fp32 with every product / sum
+// rounded on its own (no FMA contraction), then minAreaRect's centre/size/angle and RotatedRect::points (boxPoints).
 // Called by all threads; `ext` = {left, right, top, bottom} start indices (first extreme in hull order).
 __device__ void calipers_box(const HullBuf& hb, int n, int* ext /*[4] smem*/, float* out8) {
     const float* px = hb.hx; const float* py = hb.hy;
@@ -488,7 +489,8 @@ __device__ void calipers_box(const HullBuf& hb, int n, int* ext /*[4] smem*/, fl
             const int j = (i + 1 < n) ? i + 1 : 0;
             const double dx = (double)px[j] - (double)px[i], dy = (double)py[j] - (double)py[i];
             hb.vx[i] = (float)dx; hb.vy[i] = (float)dy;
-            hb.inv[i] = (float)(1.0 / sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy))));
+            const double iv = 1.0 / sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+            hb.inv[i] = iv; hb.invf[i] = (float)iv;
         }
         // extremes with the serial scan's semantics (strict compares from index 0: the FIRST extreme wins)
         if (tid < 128) {
@@ -539,43 +541,49 @@ __device__ void calipers_box(const HullBuf& hb, int n, int* ext /*[4] smem*/, fl
         // the four calipers (0 bottom, 1 right, 2 top, 3 left): current vertex index, its edge (vx, vy, 1/len) and its
         // coordinates, all in scalar registers; only the caliper that advances reloads from shared memory
         int s0 = bottom, s1 = right, s2 = top, s3 = left;
-        float vx0 = hb.vx[s0], vy0 = hb.vy[s0], iv0 = hb.inv[s0], px0 = px[s0], py0 = py[s0];
-        float vx1 = hb.vx[s1], vy1 = hb.vy[s1], iv1 = hb.inv[s1], px1 = px[s1], py1 = py[s1];
-        float vx2 = hb.vx[s2], vy2 = hb.vy[s2], iv2 = hb.inv[s2], px2 = px[s2], py2 = py[s2];
-        float vx3 = hb.vx[s3], vy3 = hb.vy[s3], iv3 = hb.inv[s3], px3 = px[s3], py3 = py[s3];
+        // cv2 4.13 keeps the edge vectors and inverse lengths in double and forms the four cosines in double; the base
+        // vector, width, height and area stay float (established against the installed library, oracle/cv_spec.py)
+        double id0 = hb.inv[s0], id1 = hb.inv[s1], id2 = hb.inv[s2], id3 = hb.inv[s3];
+        float vx0 = hb.vx[s0], vy0 = hb.vy[s0], iv0 = hb.invf[s0], px0 = px[s0], py0 = py[s0];
+        float vx1 = hb.vx[s1], vy1 = hb.vy[s1], iv1 = hb.invf[s1], px1 = px[s1], py1 = py[s1];
+        float vx2 = hb.vx[s2], vy2 = hb.vy[s2], iv2 = hb.invf[s2], px2 = px[s2], py2 = py[s2];
+        float vx3 = hb.vx[s3], vy3 = hb.vy[s3], iv3 = hb.invf[s3], px3 = px[s3], py3 = py[s3];
         float minarea = 3.402823466e+38f;
         int b_left = 0, b_bottom = 0; float b_a = 0, b_w = 0, b_b = 0, b_h = 0;
         for (int k = 0; k < n; ++k) {
-            const float dp0 = __fadd_rn(__fmul_rn(base_a, vx0), __fmul_rn(base_b, vy0));
-            const float dp1 = __fadd_rn(__fmul_rn(-base_b, vx1), __fmul_rn(base_a, vy1));
-            const float dp2 = __fsub_rn(__fmul_rn(-base_a, vx2), __fmul_rn(base_b, vy2));
-            const float dp3 = __fsub_rn(__fmul_rn(base_b, vx3), __fmul_rn(base_a, vy3));
-            float maxcos = __fmul_rn(dp0, iv0);
+            // which caliper advances is decided by double-precision cosines (centrally symmetric hulls make two of them
+            // mathematically equal at almost every step, so an fp32 pre-test would rarely settle it)
+            const double da = (double)base_a, db = (double)base_b;       // float x float products are exact in double
+            const double dp0 = __dadd_rn(__dmul_rn(da, (double)vx0), __dmul_rn(db, (double)vy0));
+            const double dp1 = __dadd_rn(__dmul_rn(-db, (double)vx1), __dmul_rn(da, (double)vy1));
+            const double dp2 = __dsub_rn(__dmul_rn(-da, (double)vx2), __dmul_rn(db, (double)vy2));
+            const double dp3 = __dsub_rn(__dmul_rn(db, (double)vx3), __dmul_rn(da, (double)vy3));
+            double maxcos = __dmul_rn(dp0, id0);
             int main_el = 0;
-            const float c1 = __fmul_rn(dp1, iv1); if (c1 > maxcos) { main_el = 1; maxcos = c1; }
-            const float c2 = __fmul_rn(dp2, iv2); if (c2 > maxcos) { main_el = 2; maxcos = c2; }
-            const float c3 = __fmul_rn(dp3, iv3); if (c3 > maxcos) { main_el = 3; maxcos = c3; }
+            const double c1 = __dmul_rn(dp1, id1); if (c1 > maxcos) { main_el = 1; maxcos = c1; }
+            const double c2 = __dmul_rn(dp2, id2); if (c2 > maxcos) { main_el = 2; maxcos = c2; }
+            const double c3 = __dmul_rn(dp3, id3); if (c3 > maxcos) { main_el = 3; maxcos = c3; }
             int nx;
             if (main_el == 0) {
                 const float lx = __fmul_rn(vx0, iv0), ly = __fmul_rn(vy0, iv0);
                 base_a = lx; base_b = ly;
                 nx = (s0 + 1 == n) ? 0 : s0 + 1; s0 = nx;
-                vx0 = hb.vx[nx]; vy0 = hb.vy[nx]; iv0 = hb.inv[nx]; px0 = px[nx]; py0 = py[nx];
+                vx0 = hb.vx[nx]; vy0 = hb.vy[nx]; iv0 = hb.invf[nx]; id0 = hb.inv[nx]; px0 = px[nx]; py0 = py[nx];
             } else if (main_el == 1) {
                 const float lx = __fmul_rn(vx1, iv1), ly = __fmul_rn(vy1, iv1);
                 base_a = ly; base_b = -lx;
                 nx = (s1 + 1 == n) ? 0 : s1 + 1; s1 = nx;
-                vx1 = hb.vx[nx]; vy1 = hb.vy[nx]; iv1 = hb.inv[nx]; px1 = px[nx]; py1 = py[nx];
+                vx1 = hb.vx[nx]; vy1 = hb.vy[nx]; iv1 = hb.invf[nx]; id1 = hb.inv[nx]; px1 = px[nx]; py1 = py[nx];
             } else if (main_el == 2) {
                 const float lx = __fmul_rn(vx2, iv2), ly = __fmul_rn(vy2, iv2);
                 base_a = -lx; base_b = -ly;
                 nx = (s2 + 1 == n) ? 0 : s2 + 1; s2 = nx;
-                vx2 = hb.vx[nx]; vy2 = hb.vy[nx]; iv2 = hb.inv[nx]; px2 = px[nx]; py2 = py[nx];
+                vx2 = hb.vx[nx]; vy2 = hb.vy[nx]; iv2 = hb.invf[nx]; id2 = hb.inv[nx]; px2 = px[nx]; py2 = py[nx];
             } else {
                 const float lx = __fmul_rn(vx3, iv3), ly = __fmul_rn(vy3, iv3);
                 base_a = -ly; base_b = lx;
                 nx = (s3 + 1 == n) ? 0 : s3 + 1; s3 = nx;
-                vx3 = hb.vx[nx]; vy3 = hb.vy[nx]; iv3 = hb.inv[nx]; px3 = px[nx]; py3 = py[nx];
+                vx3 = hb.vx[nx]; vy3 = hb.vy[nx]; iv3 = hb.invf[nx]; id3 = hb.inv[nx]; px3 = px[nx]; py3 = py[nx];
             }
             float dx = __fsub_rn(px1, px3), dy = __fsub_rn(py1, py3);
             const float width = __fadd_rn(__fmul_rn(dx, base_a), __fmul_rn(dy, base_b));
@@ -796,7 +804,7 @@ __host__ __device__ inline size_t smem_layout(int H, int Wp, bool two_bitmaps, S
     off = region;
     const size_t o_rx = take((size_t)H * 2), o_ry = take((size_t)H * 2), o_lx = take((size_t)H * 2), o_ly = take((size_t)H * 2);
     const size_t hn = (size_t)kHullCap;
-    const size_t o_hx = take(hn * 4), o_hy = take(hn * 4), o_vx = take(hn * 4), o_vy = take(hn * 4), o_inv = take(hn * 4);
+    const size_t o_hx = take(hn * 4), o_hy = take(hn * 4), o_vx = take(hn * 4), o_vy = take(hn * 4), o_invf = take(hn * 4), o_inv = take(hn * 8);
     const size_t end_hull = off;
     off = end_runs > end_hull ? end_runs : end_hull;
     if (s) {
@@ -807,7 +815,7 @@ __host__ __device__ inline size_t smem_layout(int H, int Wp, bool two_bitmaps, S
         s->hb.rx = (int16_t*)(base + o_rx); s->hb.ry = (int16_t*)(base + o_ry);
         s->hb.lx = (int16_t*)(base + o_lx); s->hb.ly = (int16_t*)(base + o_ly);
         s->hb.hx = (float*)(base + o_hx); s->hb.hy = (float*)(base + o_hy);
-        s->hb.vx = (float*)(base + o_vx); s->hb.vy = (float*)(base + o_vy); s->hb.inv = (float*)(base + o_inv);
+        s->hb.vx = (float*)(base + o_vx); s->hb.vy = (float*)(base + o_vy); s->hb.inv = (double*)(base + o_inv); s->hb.invf = (float*)(base + o_invf);
         s->scratch = (int*)(base + o_scr); s->out8 = (float*)(base + o_out);
     }
     return off;

@@ -202,7 +202,12 @@ def hull_int(pts):
 
 
 def rotating_calipers(pts):
-    """OpenCV rotatingCalipers(CALIPERS_MINAREARECT) in fp32 with separately rounded products and sums."""
+    """OpenCV rotatingCalipers(CALIPERS_MINAREARECT) as the installed cv2 4.13 evaluates it.  Established black-box
+    (the OpenCV source is not in this image): of the 16 assignments of float / double to {edge vectors + inverse
+    lengths, dot products + cosines, base vector, width / height / area} exactly one reproduces cv2.minAreaRect on
+    722 hulls of seven mask families including lattice images of rotated rectangles, whose near-parallel hull edges
+    make the choice of the advancing caliper sensitive to the last bits: inverse lengths and cosines in double, base
+    vector and areas in float (tests/test_cv_spec.py::test_calipers_near_ties_match_cv2)."""
     n = len(pts)
     px = [f32(p[0]) for p in pts]
     py = [f32(p[1]) for p in pts]
@@ -218,8 +223,8 @@ def rotating_calipers(pts):
         if p0y < bottom_y: bottom_y, bottom = p0y, i
         j = i + 1 if i + 1 < n else 0
         dx, dy = float(px[j]) - float(p0x), float(py[j]) - float(p0y)
-        vx[i], vy[i] = f32(dx), f32(dy)
-        inv[i] = f32(1.0 / math.sqrt(dx * dx + dy * dy))
+        vx[i], vy[i] = f32(dx), f32(dy)                     # differences of pixel coordinates: exact either way
+        inv[i] = 1.0 / math.sqrt(dx * dx + dy * dy)         # kept in double (see the docstring)
         p0x, p0y = px[j], py[j]
     orientation = f32(0)
     ax, ay = float(vx[n - 1]), float(vy[n - 1])
@@ -235,15 +240,17 @@ def rotating_calipers(pts):
     minarea = f32(np.finfo(np.float32).max)
     buf = None
     for _ in range(n):
-        dp = [base_a * vx[seq[0]] + base_b * vy[seq[0]], -base_b * vx[seq[1]] + base_a * vy[seq[1]],
-              -base_a * vx[seq[2]] - base_b * vy[seq[2]], base_b * vx[seq[3]] - base_a * vy[seq[3]]]
+        a, b = float(base_a), float(base_b)
+        X = [float(vx[seq[i]]) for i in range(4)]
+        Y = [float(vy[seq[i]]) for i in range(4)]
+        dp = [a * X[0] + b * Y[0], -b * X[1] + a * Y[1], -a * X[2] - b * Y[2], b * X[3] - a * Y[3]]     # double
         maxcos, main = dp[0] * inv[seq[0]], 0
         for i in range(1, 4):
             c = dp[i] * inv[seq[i]]
             if c > maxcos:
                 main, maxcos = i, c
         pi = seq[main]
-        lead_x, lead_y = vx[pi] * inv[pi], vy[pi] * inv[pi]
+        lead_x, lead_y = vx[pi] * f32(inv[pi]), vy[pi] * f32(inv[pi])                                  # float again
         if main == 0: base_a, base_b = lead_x, lead_y
         elif main == 1: base_a, base_b = lead_y, -lead_x
         elif main == 2: base_a, base_b = -lead_x, -lead_y

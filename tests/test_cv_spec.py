@@ -114,3 +114,25 @@ def test_mask_rect_spec_matches_cv2():
         else:
             pytest.fail("rectangle differs by %.3f px on blob %d" % (dev, t))
     assert exact > 100
+
+
+def test_calipers_near_ties_match_cv2():
+    """lattice images of rotated rectangles (near-parallel hull edges, near-tied candidate rectangles) at the C2 frame
+    shape: the spec must reproduce cv2.minAreaRect + boxPoints, which pins the float / double split of
+    cv_spec.rotating_calipers (a pure fp32 walk fails about a third of these)"""
+    H, W = 530, 730
+    rs = np.random.RandomState(5)
+    yy, xx = np.mgrid[0:H, 0:W]
+    exact = 0
+    for t in range(40):
+        cx, cy, th = rs.uniform(0.3, 0.7) * W, rs.uniform(0.3, 0.7) * H, rs.uniform(0, np.pi)
+        u = (xx - cx) * np.cos(th) + (yy - cy) * np.sin(th)
+        v = -(xx - cx) * np.sin(th) + (yy - cy) * np.cos(th)
+        m = ((np.abs(u) < rs.uniform(3, 0.3 * W)) & (np.abs(v) < rs.uniform(1, 0.2 * H))).astype(np.uint8)
+        contours, _ = cv2.findContours(m, cv2.RETR_EXTERNAL, cv2.CHAIN_APPROX_SIMPLE)
+        ref = cv2.boxPoints(cv2.minAreaRect(max(contours, key=cv2.contourArea)))
+        r = S.mask_rect_spec(m)
+        dev = max(min(float(np.hypot(*(p - q))) for q in ref) for p in r)
+        assert dev < 1e-3, (t, dev)
+        exact += sorted(map(tuple, r.tolist())) == sorted(map(tuple, ref.tolist()))
+    assert exact >= 36
