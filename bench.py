@@ -36,8 +36,8 @@ import torch  # noqa: E402
 
 WORKLOAD = "C2"
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of this workload
-# (profiles/r01_e_ncu_full_raw_c2.csv): pack_tma_kernel 1.4879 GB + 0.1806 GB, rect_kernel passes 0.0939 GB + 0.0030 GB
-TRAFFIC = {"K-B pack": 1.4879e9 + 0.1806e9, "K-B rect": 0.0939e9 + 0.0030e9}
+# (profiles/r01_f_ncu_full_raw_c2.csv): pack_tma_kernel 1.4878 GB + 0.1818 GB, rect_kernel passes 0.0955 GB + 0.0041 GB
+TRAFFIC = {"K-B pack": 1.4878e9 + 0.1818e9, "K-B rect": 0.0955e9 + 0.0041e9}
 # what binds each stage: only the pack kernel moves gigabytes; the others are issue- / latency-bound
 BOUND = {"K-A backproject+ransac": "fp32 fma issue (hypothesis scoring)", "K-B pack": "hbm",
          "K-B rect": "latency (serial hull / calipers chains on L2-resident bitmaps)",
