@@ -472,7 +472,10 @@ __device__ int label_runs(const uint32_t* bm, int H, int W, int Wp, RunSet rs, i
 // ---- hull + rotating calipers of the component `root` ----------------------------------------------------------
 // Only two things are inherently sequential: the monotone-chain stacks (one thread per chain, top of stack in
 // registers) and the calipers' walk around the hull (one thread, everything it reads precomputed in parallel).
-constexpr int kChainCap = 512;    // vertices of one strictly convex chain (a lattice polygon in a <=1024^2 grid has < 360)
+#ifndef TDOD_KB_CHAINCAP
+#define TDOD_KB_CHAINCAP 512
+#endif
+constexpr int kChainCap = TDOD_KB_CHAINCAP;    // vertices of one strictly convex chain (a lattice polygon in a <=1024^2 grid has < 360)
 constexpr int kHullCap = 2 * kChainCap;
 struct HullBuf { int16_t* rx; int16_t* ry; int16_t* lx; int16_t* ly; float* hx; float* hy; float* vx; float* vy; float* invf; double* inv; };
 
