@@ -382,11 +382,20 @@ __device__ int label_runs(const uint32_t* bm, int H, int W, int Wp, RunSet rs, i
                 const uint32_t starts = m[u] & ~((m[u] << 1) | prev), ends = m[u] & ~((m[u] >> 1) | (next << 31));
                 if (!__any_sync(0xffffffffu, starts | ends)) continue;
                 const int ns = __popc(starts), ne = __popc(ends);
-                int ps = ns, pe = ne;
+                int ps, pe;                                       // inclusive prefix sums over the lanes
+                if (!__any_sync(0xffffffffu, (ns | ne) > 1)) {
+                    // the usual row: no word holds more than one run start or end -> two ballots instead of a scan
+                    const unsigned le = (2u << lane) - 1u;        // lanes 0..lane
+                    ps = __popc(__ballot_sync(0xffffffffu, ns != 0) & le);
+                    pe = __popc(__ballot_sync(0xffffffffu, ne != 0) & le);
+                } else {
+                    int pk = ns | (ne << 16);                     // a word has at most 16 runs, a row at most 512
 #pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const int a = __shfl_up_sync(0xffffffffu, ps, o), b = __shfl_up_sync(0xffffffffu, pe, o);
-                    if (lane >= o) { ps += a; pe += b; }
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const int a = __shfl_up_sync(0xffffffffu, pk, o);
+                        if (lane >= o) pk += a;
+                    }
+                    ps = pk & 0xffff; pe = pk >> 16;
                 }
                 const int base = rs.row_off[r];
                 int ks = base + ps - ns, ke = base + pe - ne;
