@@ -1,0 +1,204 @@
+// Depth order statistics of ROIHeads3DScore's pseudo-ground-truth losses (the losses that read the
+// depth map instead of the cube geometry):
+//   mode 0  pseudo_gt_z_box_loss   (cubercnn/modeling/roi_heads/roi_heads.py:1196-1231)  median of the depth crop under
+//           the clipped 2D box; boxes with no area fall back to the depth at the clamped box centre
+//   mode 1  pseudo_gt_z_point_loss (:1256-1277)  depth at the clamped predicted centre
+//   mode 2  depth_range_loss       (:1279-1305)  quantile(0.9) - quantile(0.1) of the depth under the segmentation mask,
+//           of the depth crop under the 2D box when the mask is empty
+// The reference slices one crop per box in a Python loop and sorts it (torch.median / torch.quantile); here one CTA per
+// box selects the wanted ranks with an 8-bit-per-pass radix select over the crop as it lies in the depth map (no copy, no
+// sort).  Values are selected, never averaged, so the median is bit-exact; the quantile's interpolation follows
+// at::lerp as the CUDA build of torch evaluates it.
+#include <cstdint>
+
+#include "tdod_device.cuh"
+#include "tdod_internal.h"
+
+using namespace tdod;
+
+namespace {
+
+constexpr int kSelT = 256;
+
+struct Region {                 // pixels (y0 + r, x0 + c), r < rows, c < cols, of one H x W frame; m == nullptr: all of them
+    const float* d;
+    const uint8_t* m;
+    int x0, y0, cols, rows, W;
+};
+
+__device__ __forceinline__ unsigned key_of(float v) {          // order-preserving map float -> unsigned
+    const unsigned b = __float_as_uint(v);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float val_of(unsigned k) {
+    return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
+struct SelShared {
+    unsigned hist[257];         // bin 256 swallows the lanes that have no pixel
+    unsigned sel[2];
+    unsigned cnt[2];            // pixels in the region, NaNs among them
+};
+
+// pixels in the region (under the mask) and how many of them are NaN; every thread returns the same pair
+__device__ void region_count(const Region& R, SelShared& s, unsigned& n, unsigned& n_nan) {
+    if (threadIdx.x < 2) s.cnt[threadIdx.x] = 0;
+    __syncthreads();
+    const unsigned total = (unsigned)R.rows * (unsigned)R.cols;
+    unsigned c = 0, cn = 0;
+    for (unsigned i = threadIdx.x; i < total; i += kSelT) {
+        const unsigned r = i / (unsigned)R.cols, col = i - r * (unsigned)R.cols;
+        const size_t idx = (size_t)(R.y0 + (int)r) * R.W + R.x0 + (int)col;
+        if (R.m && !R.m[idx]) continue;
+        const float v = R.d[idx];
+        c++;
+        cn += (v != v);
+    }
+    c = __reduce_add_sync(0xffffffffu, c);
+    cn = __reduce_add_sync(0xffffffffu, cn);
+    if ((threadIdx.x & 31) == 0) { atomicAdd(&s.cnt[0], c); atomicAdd(&s.cnt[1], cn); }
+    __syncthreads();
+    n = s.cnt[0];
+    n_nan = s.cnt[1];
+    __syncthreads();
+}
+
+// k-th smallest (0-based) of the region's values: four passes, most significant byte first
+__device__ float region_select(const Region& R, unsigned k, SelShared& s) {
+    const unsigned total = (unsigned)R.rows * (unsigned)R.cols;
+    unsigned prefix = 0, known = 0;
+    for (int shift = 24; shift >= 0; shift -= 8) {
+        for (int i = threadIdx.x; i < 257; i += kSelT) s.hist[i] = 0;
+        __syncthreads();
+        for (unsigned base = 0; base < total; base += kSelT) {
+            const unsigned i = base + threadIdx.x;
+            unsigned bin = 256;
+            if (i < total) {
+                const unsigned r = i / (unsigned)R.cols, col = i - r * (unsigned)R.cols;
+                const size_t idx = (size_t)(R.y0 + (int)r) * R.W + R.x0 + (int)col;
+                if (!R.m || R.m[idx]) {
+                    const unsigned key = key_of(R.d[idx]);
+                    if ((key & known) == prefix) bin = (key >> shift) & 255u;
+                }
+            }
+            // neighbouring depths share their leading bytes: one shared-memory add per distinct bin of the warp
+            const unsigned peers = __match_any_sync(0xffffffffu, bin);
+            if (bin < 256 && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) atomicAdd(&s.hist[bin], __popc(peers));
+        }
+        __syncthreads();
+        if (threadIdx.x < 32) {                     // first bin whose running count passes k
+            const int lane = threadIdx.x;
+            unsigned mine = 0;
+            for (int j = 0; j < 8; j++) mine += s.hist[lane * 8 + j];
+            unsigned inc = mine;
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned a = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += a;
+            }
+            const unsigned hit = __ballot_sync(0xffffffffu, inc > k);
+            const int owner = __ffs(hit) - 1;       // never -1: k < number of values with this prefix
+            if (lane == owner) {
+                unsigned acc = inc - mine;
+                int b = lane * 8;
+                while (acc + s.hist[b] <= k) acc += s.hist[b++];
+                s.sel[0] = (unsigned)b;
+                s.sel[1] = k - acc;
+            }
+        }
+        __syncthreads();
+        prefix |= s.sel[0] << shift;
+        known |= 0xffu << shift;
+        k = s.sel[1];
+        __syncthreads();
+    }
+    return val_of(prefix);
+}
+
+// at::lerp (aten/src/ATen/native/Lerp.h) the way nvcc contracts it in torch's CUDA build
+__device__ __forceinline__ float torch_lerp(float a, float b, float w) {
+    const float diff = __fsub_rn(b, a);
+    return (fabsf(w) < 0.5f) ? __fmaf_rn(w, diff, a) : __fmaf_rn(-diff, __fsub_rn(1.0f, w), b);
+}
+
+// torch.quantile(x, q) with linear interpolation (aten/src/ATen/native/Sorting.cpp, quantile_compute): rank = q * (n - 1)
+// in fp32, the two neighbouring order statistics, lerp by the fractional rank
+__device__ float region_quantile(const Region& R, unsigned n, float q, SelShared& s) {
+    const float rank = __fmul_rn(q, (float)(n - 1));
+    const float lo = floorf(rank), hi = ceilf(rank);
+    const float below = region_select(R, (unsigned)lo, s);
+    const float above = (hi == lo) ? below : region_select(R, (unsigned)hi, s);
+    return torch_lerp(below, above, __fsub_rn(rank, lo));
+}
+
+__device__ __forceinline__ float clampf(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
+
+// depth at (clamp(x, 10, W-11), clamp(y, 10, H-11)), truncated: roi_heads.py:1224-1227 and :1272-1274
+__device__ __forceinline__ float point_depth(const float* d, float x, float y, int H, int W) {
+    const int xi = (int)clampf(x, 10.0f, (float)(W - 11)), yi = (int)clampf(y, 10.0f, (float)(H - 11));
+    return d[(size_t)min(max(yi, 0), H - 1) * W + min(max(xi, 0), W - 1)];
+}
+
+__global__ void __launch_bounds__(kSelT)
+depth_select_kernel(const float* __restrict__ depth, const int32_t* __restrict__ frame, const float* __restrict__ boxes,
+                    const uint8_t* __restrict__ masks, const int32_t* __restrict__ mask_idx, int mode, int H, int W,
+                    float* __restrict__ out, int32_t* __restrict__ flag) {
+    __shared__ SelShared s;
+    const int item = blockIdx.x;
+    const float* d = depth + (size_t)frame[item] * H * W;
+    const float bx1 = boxes[item * 4 + 0], by1 = boxes[item * 4 + 1], bx2 = boxes[item * 4 + 2], by2 = boxes[item * 4 + 3];
+    const float nan = __uint_as_float(0x7fc00000u);
+    float res;
+    int fl = 0;
+    if (mode == 1) {
+        res = point_depth(d, bx1, by1, H, W);
+    } else if (mode == 0) {
+        // Boxes.clip((h, w)) then area() > 0 (:1209-1212)
+        const float x1 = clampf(bx1, 0.0f, (float)W), y1 = clampf(by1, 0.0f, (float)H);
+        const float x2 = clampf(bx2, 0.0f, (float)W), y2 = clampf(by2, 0.0f, (float)H);
+        if (__fmul_rn(__fsub_rn(x2, x1), __fsub_rn(y2, y1)) > 0.0f) {
+            fl = 1;
+            Region R{d, nullptr, (int)x1, (int)y1, (int)x2 - (int)x1, (int)y2 - (int)y1, W};
+            unsigned n, n_nan;
+            region_count(R, s, n, n_nan);
+            // an empty slice raises in the reference; a NaN anywhere makes torch.median NaN
+            res = (n == 0 || n_nan) ? nan : region_select(R, (n - 1) >> 1, s);
+        } else {
+            res = point_depth(d, __fmul_rn(__fadd_rn(x1, x2), 0.5f), __fmul_rn(__fadd_rn(y1, y2), 0.5f), H, W);
+        }
+    } else {
+        Region R{d, masks + (size_t)mask_idx[item] * H * W, 0, 0, W, H, W};
+        unsigned n, n_nan;
+        region_count(R, s, n, n_nan);
+        fl = 1;
+        if (n == 0) {                               // no mask pixel: the slice under the 2D box (:1296-1297)
+            fl = 0;
+            const int x1 = min(max((int)bx1, 0), W), x2 = min(max((int)bx2, 0), W);
+            const int y1 = min(max((int)by1, 0), H), y2 = min(max((int)by2, 0), H);
+            R = Region{d, nullptr, x1, y1, max(x2 - x1, 0), max(y2 - y1, 0), W};
+            region_count(R, s, n, n_nan);
+        }
+        if (n == 0 || n_nan) res = nan;
+        else res = __fsub_rn(region_quantile(R, n, 0.9f, s), region_quantile(R, n, 0.1f, s));
+    }
+    if (threadIdx.x == 0) {
+        out[item] = res;
+        if (flag) flag[item] = fl;
+    }
+}
+
+}  // namespace
+
+extern "C" int tdod_depth_select(const float* depth, int64_t F, int H, int W, const int32_t* frame, const float* boxes,
+                                 const uint8_t* masks, const int32_t* mask_idx, int mode, int64_t n, float* out,
+                                 int32_t* out_flag, void* stream) {
+    if (n == 0) return TDOD_OK;
+    if (!depth || !frame || !boxes || !out || n < 0 || F <= 0 || H <= 0 || W <= 0 || mode < 0 || mode > 2 ||
+        (int64_t)H * W >= (1ll << 31))
+        return tdod_fail(TDOD_EINVAL, "tdod_depth_select: bad argument");
+    if (mode == 2 && (!masks || !mask_idx)) return tdod_fail(TDOD_EINVAL, "tdod_depth_select: mode 2 needs masks and mask_idx");
+    if (n > 0x7fffffff) return tdod_fail(TDOD_EINVAL, "tdod_depth_select: too many boxes");
+    depth_select_kernel<<<(unsigned)n, kSelT, 0, (cudaStream_t)stream>>>(depth, frame, boxes, masks, mask_idx, mode, H, W,
+                                                                         out, out_flag);
+    TDOD_CHECK_LAUNCH();
+    return TDOD_OK;
+}

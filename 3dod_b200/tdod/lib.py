@@ -68,6 +68,7 @@ SIGNATURES = {
     "tdod_hull_fill_grad": (_I, [_P, _P, _P, _P, _L, _I, _I, _P, _P, _P, _P]),
     "tdod_hull_fill": (_I, [_P, _P, _L, _I, _I, _P, _P]),
     "tdod_hull_fill_dense_grad": (_I, [_P, _P, _L, _I, _I, _P, _P, _P, _P]),
+    "tdod_depth_select": (_I, [_P, _L, _I, _I, _P, _P, _P, _P, _I, _L, _P, _P, _P]),
 }
 
 

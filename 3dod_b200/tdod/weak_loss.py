@@ -5,6 +5,7 @@ Cubes / cubes_to_box in the training path of the reference (cubercnn/modeling/ro
     z_loss          50-step depth sweep                                        :1151-1194
     segment_loss    jarvis_march + fill_polygon + focal / bce / dice           :1030-1052, utils.py:424-507
     normal_vector_from_maps  batched Plane.fit_parallel + wall rectification   :1076-1149
+    pseudo_gt_z_box_loss / pseudo_gt_z_point_loss / depth_range_loss          :1196-1231, :1256-1305
 
 Each is one or two kernel launches for the whole batch of cubes (the reference loops over cubes in Python and lets
 autograd record hundreds of small kernels per cube); gradients come from hand-written backward kernels wrapped in
@@ -254,6 +255,104 @@ def segment_loss(gt_mask, bube_corners, at_which_mask_idx, loss='focal'):
     if loss == 'dice':
         inter, s_sum, y_sum = S[:, 11].sum(), S[:, 10].sum() + S[:, 11].sum(), S[:, 5].sum()
         return (1 - (2. * inter + 1) / (s_sum + y_sum + 1)).to(f32)
+
+
+def _depth_stack(depth_maps):
+    """[F,H,W] tensor, or the reference's iterable of equally sized [H,W] maps -> contiguous fp32 [F,H,W]"""
+    if not isinstance(depth_maps, torch.Tensor):
+        depth_maps = torch.stack([d.reshape(d.shape[-2:]) for d in depth_maps])
+    if depth_maps.dim() != 3:
+        raise ValueError("depth_maps must be [F,H,W]")
+    return depth_maps.detach().to(f32).contiguous()
+
+
+def depth_select(depth_maps, frame, boxes, mode, masks=None, mask_idx=None):
+    """One depth order statistic per box in one launch (tdod_depth_select, include/tdod.h): (values [n], flags [n])."""
+    depth = _depth_stack(depth_maps)
+    F_, H, W = depth.shape
+    dev = depth.device
+    boxes = boxes.detach().to(device=dev, dtype=f32).contiguous()
+    n = boxes.shape[0]
+    frame = torch.as_tensor(frame, device=dev).to(i32).contiguous()
+    if boxes.shape != (n, 4) or frame.shape != (n,):
+        raise ValueError("boxes must be [n,4] with one frame index per box")
+    if masks is not None:
+        if masks.dtype == torch.bool:
+            masks = masks.view(torch.uint8)
+        if masks.dtype != torch.uint8 or not masks.is_contiguous() or tuple(masks.shape[-2:]) != (H, W):
+            raise ValueError("masks must be a contiguous bool / uint8 [M,H,W] tensor of the depth maps' size")
+        mask_idx = torch.as_tensor(mask_idx, device=dev).to(i32).contiguous()
+        if mask_idx.shape != (n,):
+            raise ValueError("one mask index per box")
+    out = torch.empty((n,), dtype=f32, device=dev)
+    flag = torch.empty((n,), dtype=i32, device=dev)
+    L.check(L.lib().tdod_depth_select(L.ptr(depth, f32, "depth_maps"), F_, H, W, L.ptr(frame), L.ptr(boxes),
+                                      L.ptr(masks), L.ptr(mask_idx), int(mode), n, L.ptr(out), L.ptr(flag),
+                                      L.stream_ptr()))
+    return out, flag
+
+
+def _l1(vals, target):
+    return torch.nn.functional.smooth_l1_loss(vals, target, reduction='none', beta=0.0)      # roi_heads.py:962-963
+
+
+def pseudo_gt_z_box_loss(depth_maps, proposal_boxes, pred_z):
+    """ROIHeads3DScore.pseudo_gt_z_box_loss (roi_heads.py:1196-1231): |pred_z - median depth under each proposal box|
+    for all boxes of all frames in one launch.  depth_maps [F,H,W] (or F maps of one size), proposal_boxes: F tensors
+    [Ni,4].  As in the reference the pseudo ground truth of a frame lists the boxes with area first and the boxes
+    without (centre samples) after them, whatever their order in proposal_boxes."""
+    counts = [int(b.shape[0]) for b in proposal_boxes]
+    boxes = torch.cat([b.reshape(-1, 4) for b in proposal_boxes])
+    frame = torch.repeat_interleave(torch.arange(len(counts), device=boxes.device),
+                                    torch.as_tensor(counts, device=boxes.device))
+    gt, has_area = depth_select(depth_maps, frame, boxes, 0)
+    order = torch.argsort(frame * 2 + (1 - has_area), stable=True)                           # :1216-1227
+    return _l1(pred_z, gt[order])
+
+
+def pseudo_gt_z_point_loss(depth_maps, pred_xy, pred_z, num_boxes_per_image):
+    """ROIHeads3DScore.pseudo_gt_z_point_loss (roi_heads.py:1256-1277): |pred_z - depth at the predicted centre|."""
+    counts = torch.as_tensor(list(num_boxes_per_image), device=pred_xy.device)
+    frame = torch.repeat_interleave(torch.arange(counts.numel(), device=pred_xy.device), counts)
+    xy = pred_xy.detach().to(f32)
+    gt, _ = depth_select(depth_maps, frame, torch.cat((xy, xy), 1), 1)
+    return _l1(pred_z, gt)
+
+
+def depth_extent(cubes):
+    """max - min depth of the 8 corners of cubes [N,15] (roi_heads.py:1286-1288).  The value comes from the corner
+    kernel behind Cubes.get_all_corners; the gradient from the same expression written with torch operators."""
+    from ProposalNetwork.utils.spaces import Cubes
+    t = cubes.to(f32)
+    with torch.no_grad():
+        z = Cubes(t.detach().reshape(-1, 1, 15)).get_all_corners()[:, 0, :, 2]
+        value = z.max(1)[0] - z.min(1)[0]
+    if not t.requires_grad:
+        return value
+    sx = t.new_tensor([-1, 1, 1, -1, -1, 1, 1, -1])                                          # math_util.py:198-207
+    sy = t.new_tensor([-1, -1, 1, 1, -1, -1, 1, 1])
+    sz = t.new_tensor([-1, -1, -1, -1, 1, 1, 1, 1])
+    d, r2 = t[:, 3:6], t[:, 12:15]
+    zt = (r2[:, 0:1] * sx * d[:, 2:3] + r2[:, 1:2] * sy * d[:, 1:2] + r2[:, 2:3] * sz * d[:, 0:1]) / 2 + t[:, 2:3]
+    soft = zt.max(1)[0] - zt.min(1)[0]
+    return value + (soft - soft.detach())
+
+
+def depth_range_loss(gt_mask, at_which_mask_idx, depth_maps, cubes, gt_boxes, num_instances):
+    """ROIHeads3DScore.depth_range_loss (roi_heads.py:1279-1305): |q90 - q10 of the depth under each object's mask -
+    depth extent of its cube|.  gt_mask [M,H,W] (or the reference's list of [1,H,W]) at the depth maps' size (the
+    reference's bilinear resize with align_corners=True is then the identity), cubes [N,15] or a Cubes of N x 1,
+    gt_boxes [N,4] (tensor or Boxes), num_instances: cubes per frame."""
+    if isinstance(gt_mask, (list, tuple)):
+        gt_mask = torch.stack([m.reshape(m.shape[-2:]) for m in gt_mask])
+    gt_mask = gt_mask.reshape(-1, *gt_mask.shape[-2:])
+    t = cubes.tensor if hasattr(cubes, "tensor") else cubes
+    t = t.reshape(-1, 15)
+    boxes = gt_boxes.tensor if hasattr(gt_boxes, "tensor") else gt_boxes
+    counts = torch.as_tensor(list(num_instances), device=t.device)
+    frame = torch.repeat_interleave(torch.arange(counts.numel(), device=t.device), counts)
+    gt, _ = depth_select(depth_maps, frame, boxes, 2, masks=gt_mask.contiguous(), mask_idx=at_which_mask_idx)
+    return _l1(gt, depth_extent(t))
 
 
 def normal_vector_from_maps(ground_maps, depth_maps, Ks, use_nth=5, seed=0, sample_ids=None):

@@ -239,6 +239,19 @@ int tdod_hull_fill(const float* hull, const int32_t* meta, int64_t n, int H, int
 int tdod_hull_fill_dense_grad(const float* hull, const int32_t* meta, int64_t n, int H, int W, const float* g_mask,
                               double* workspace, float* out_g_corners, void* stream);
 
+/* Depth order statistics of the pseudo-ground-truth losses, one value per box (n boxes, box i in frame frame[i] of
+ * depth [F,H,W] fp32, boxes [n,4] fp32 x1 y1 x2 y2):
+ *   mode 0  pseudo_gt_z_box_loss (roi_heads.py:1196-1231): torch.median of the depth crop under the box clipped to the
+ *           image; out_flag = 1.  Boxes whose clipped area is not positive: the depth at their clamped centre, out_flag = 0
+ *           (the caller orders the values as the reference does, medians before centre samples within a frame).
+ *   mode 1  pseudo_gt_z_point_loss (:1256-1277): depth at (clamp(x1,10,W-11), clamp(y1,10,H-11)); x2, y2 unused.
+ *   mode 2  depth_range_loss (:1279-1305): torch.quantile(.,0.9) - torch.quantile(.,0.1) of the depth under
+ *           masks[mask_idx[i]] ([M,H,W] uint8, out_flag = 1), of the crop under the box when the mask is empty (0).
+ * An empty crop (the reference raises) and a crop that holds a NaN give NaN.  out_flag may be NULL. */
+int tdod_depth_select(const float* depth, int64_t F, int H, int W, const int32_t* frame, const float* boxes,
+                      const uint8_t* masks, const int32_t* mask_idx, int mode, int64_t n, float* out, int32_t* out_flag,
+                      void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -67,6 +67,13 @@ class _Boxes:
     def get_centers(self):
         return (self.tensor[:, :2] + self.tensor[:, 2:]) / 2
 
+    def clip(self, box_size):
+        assert torch.isfinite(self.tensor).all(), "Box tensor contains infinite or NaN!"
+        h, w = box_size
+        x1, y1 = self.tensor[:, 0].clamp(min=0, max=w), self.tensor[:, 1].clamp(min=0, max=h)
+        x2, y2 = self.tensor[:, 2].clamp(min=0, max=w), self.tensor[:, 3].clamp(min=0, max=h)
+        self.tensor = torch.stack((x1, y1, x2, y2), dim=-1)
+
     @classmethod
     def cat(cls, boxes_list):
         if len(boxes_list) == 0:

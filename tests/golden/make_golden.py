@@ -325,8 +325,34 @@ def make_weak_loss(ver):
     print("hull_len", out["hull_len"], "z", out["z_loss"], "focal", out["seg_focal"], "dice", out["seg_dice"])
 
 
+def make_depth_losses(ver):
+    """SURVEY 8(f) row 4, the losses that read the depth map: pseudo_gt_z_box_loss, pseudo_gt_z_point_loss and
+    depth_range_loss of the UNMODIFIED reference (roi_heads.py:1196-1231, :1256-1305)."""
+    me = _ref_methods(["l1_loss", "pseudo_gt_z_box_loss", "pseudo_gt_z_point_loss", "depth_range_loss"])
+    sys.path.insert(0, HERE)
+    from depth_case import depth_loss_case
+    c = depth_loss_case()
+    ok = [b.clone() for b in c["boxes"]]
+    ok[1] = torch.cat((ok[1][:3], ok[1][4:]))                          # the reference raises on the empty slice
+    keep = torch.ones(sum(c["counts"]), dtype=torch.bool)
+    keep[c["counts"][0] + 3] = False
+    out = {"versions": ver, "keep": keep.numpy()}
+    out["z_box"] = me.pseudo_gt_z_box_loss(list(c["depth"]), ok, c["pred_z"][keep]).numpy()
+    out["z_point"] = me.pseudo_gt_z_point_loss(list(c["depth"]), c["pred_xy"], c["pred_z"], c["counts"]).numpy()
+    cubes = c["cubes"].clone().requires_grad_(True)
+    dr = me.depth_range_loss(c["masks"][:, None], c["mask_idx"].tolist(), list(c["depth"]),
+                             R.spaces.Cubes(cubes[:, None]), R.Boxes(c["gt_boxes"]), c["counts"])
+    out["depth_range"] = dr.detach().numpy()
+    out["grad_depth_range"] = torch.autograd.grad(dr.sum(), cubes)[0].numpy()
+    np.savez_compressed(os.path.join(HERE, "depth_losses.npz"), **out)
+    print("depth_losses.npz", {k: (v.shape, v.dtype) for k, v in out.items() if k != "versions"})
+    print("z_box", out["z_box"][:8], "depth_range", out["depth_range"][:8])
+
+
 if __name__ == "__main__":
-    if len(sys.argv) > 1 and sys.argv[1] == "variants":
+    if len(sys.argv) > 1 and sys.argv[1] == "depth_losses":
+        make_depth_losses(np.array(str(O.versions())))
+    elif len(sys.argv) > 1 and sys.argv[1] == "variants":
         make_variants(np.array(str(O.versions())))
     elif len(sys.argv) > 1 and sys.argv[1] == "weak_loss":
         make_weak_loss(np.array(str(O.versions())))

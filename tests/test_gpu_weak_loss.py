@@ -260,3 +260,76 @@ def test_dense_convex_hull_and_fill_polygon_mirror():
     gf = U.fill_polygon(mask.to(d), xt)
     np.testing.assert_array_equal(gf.detach().cpu().numpy(), rf.detach().numpy())
     close(torch.autograd.grad((gf * wgt[0].to(d)).sum(), xt)[0].cpu(), rg, 1e-4, atol_rel=1e-4, what="fill_polygon grad")
+
+
+# ---- the losses that read the depth map (roi_heads.py:1196-1231, :1256-1305) ------------------------------------------
+def _depth_case(golden_dir):
+    import sys
+    if golden_dir not in sys.path:
+        sys.path.insert(0, golden_dir)
+    from depth_case import depth_loss_case
+    return depth_loss_case(), np.load(os.path.join(golden_dir, "depth_losses.npz"), allow_pickle=True)
+
+
+def test_depth_map_losses_match_reference(golden_dir):
+    c, D = _depth_case(golden_dir)
+    d = dev()
+    depth = c["depth"].to(d)
+    # all boxes, the one with an empty slice included: NaN for it, the reference's values for the others
+    z = WL.pseudo_gt_z_box_loss(depth, [b.to(d) for b in c["boxes"]], c["pred_z"].to(d)).cpu()
+    zo = WO.pseudo_gt_z_box_loss(list(c["depth"]), c["boxes"], c["pred_z"])
+    assert int(torch.isnan(z).sum()) == 1
+    assert np.array_equal(z.numpy(), zo.numpy(), equal_nan=True)
+    # the reference's own run (without that box): bit-equal
+    keep = torch.tensor(D["keep"])
+    n1 = c["counts"][0]
+    ok = [b.clone() for b in c["boxes"]]
+    ok[1] = ok[1][keep[n1:n1 + c["counts"][1]]]
+    pz = c["pred_z"][keep].to(d).requires_grad_(True)
+    z = WL.pseudo_gt_z_box_loss(list(depth), [b.to(d) for b in ok], pz)
+    assert np.array_equal(z.detach().cpu().numpy(), D["z_box"])
+    z.sum().backward()
+    assert torch.all(pz.grad.abs() == 1)
+    zp = WL.pseudo_gt_z_point_loss(depth, c["pred_xy"].to(d), c["pred_z"].to(d), c["counts"])
+    assert np.array_equal(zp.cpu().numpy(), D["z_point"])
+    cubes = c["cubes"].to(d).requires_grad_(True)
+    dr = WL.depth_range_loss(c["masks"].to(d), c["mask_idx"].tolist(), depth, cubes, c["gt_boxes"].to(d), c["counts"])
+    close(dr.detach().cpu().numpy(), D["depth_range"], rtol=0, atol=2e-6, what="depth_range_loss")
+    dr.sum().backward()
+    close(cubes.grad.cpu().numpy(), D["grad_depth_range"], rtol=1e-6, atol=1e-6, what="depth_range_loss gradient")
+
+
+def test_depth_select_matches_torch_on_large_crops():
+    """medians bit-equal to torch.median and quantile ranges within an ulp of torch.quantile on the device, at the frame
+    size of the bench (730 x 530), duplicate-heavy depths and negative values included"""
+    d = dev()
+    g = torch.Generator().manual_seed(3)
+    F_, H, W = 3, 530, 730
+    depth = torch.rand((F_, H, W), generator=g) * 8 - 1
+    depth[1] = torch.round(depth[1] * 4) / 4                              # 36 distinct values: long runs of ties
+    depth = depth.to(d)
+    n = 40
+    x1 = torch.rand(n, generator=g) * W * 0.8; y1 = torch.rand(n, generator=g) * H * 0.8
+    boxes = torch.stack((x1, y1, x1 + torch.rand(n, generator=g) * W * 0.6 + 2, y1 + torch.rand(n, generator=g) * H * 0.6 + 2), 1)
+    boxes[0] = torch.tensor([-5.0, -5.0, W + 5.0, H + 5.0])                # the whole frame
+    boxes[1] = torch.tensor([7.2, 9.9, 8.1, 11.0])                         # one pixel
+    frame = torch.arange(n) % F_
+    got, flag = WL.depth_select(depth, frame, boxes.to(d), 0)
+    assert bool(flag.all())
+    for i in range(n):
+        b = boxes[i]
+        xs = [int(b[0].clamp(0, W)), int(b[2].clamp(0, W))]; ys = [int(b[1].clamp(0, H)), int(b[3].clamp(0, H))]
+        ref = torch.median(depth[frame[i], ys[0]:ys[1], xs[0]:xs[1]])
+        assert got[i].item() == ref.item(), i
+    yy, xx = torch.meshgrid(torch.arange(H), torch.arange(W), indexing="ij")
+    masks = torch.stack([((xx - 100 - 13 * i) ** 2 + (yy - 90 - 9 * i) ** 2 < (20 + 11 * i) ** 2) for i in range(n)]).to(d)
+    masks[5] = False
+    got, flag = WL.depth_select(depth, frame, boxes.to(d), 2, masks=masks, mask_idx=torch.arange(n))
+    assert flag.tolist() == [0 if i == 5 else 1 for i in range(n)]
+    for i in range(n):
+        v = depth[frame[i]][masks[i]]
+        if i == 5:
+            b = boxes[i].long()
+            v = depth[frame[i], b[1]:b[3], b[0]:b[2]].reshape(-1)
+        ref = torch.quantile(v, 0.9) - torch.quantile(v, 0.1)
+        assert abs(got[i].item() - ref.item()) <= 1e-6 * max(1.0, abs(ref.item())), (i, got[i].item(), ref.item())

@@ -76,3 +76,31 @@ def test_segment_loss_gradient_reaches_the_cubes():
     g = torch.autograd.grad((sl * torch.tensor(G["wl"])).sum(), cubes)[0]
     ref = G["grad_seg_focal_cubes"]
     np.testing.assert_allclose(g.numpy(), ref, rtol=1e-3, atol=1e-5 * max(1.0, float(np.abs(ref).max())))
+
+
+def _depth_case():
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    from depth_case import depth_loss_case
+    return depth_loss_case(), np.load(os.path.join(ROOT, "tests", "golden", "depth_losses.npz"), allow_pickle=True)
+
+
+def test_depth_map_losses_match_the_reference():
+    """pseudo_gt_z_box_loss / pseudo_gt_z_point_loss / depth_range_loss (roi_heads.py:1196-1231, :1256-1305) against
+    tests/golden/depth_losses.npz (`python tests/golden/make_golden.py depth_losses`)"""
+    c, D = _depth_case()
+    keep = torch.tensor(D["keep"])
+    n1 = c["counts"][0]
+    ok = [b.clone() for b in c["boxes"]]
+    ok[1] = ok[1][keep[n1:n1 + c["counts"][1]]]
+    z = WO.pseudo_gt_z_box_loss(list(c["depth"]), ok, c["pred_z"][keep])
+    assert np.array_equal(z.numpy(), D["z_box"])
+    # with the box whose slice is empty (the reference raises there) the restatement gives NaN for it alone
+    zf = WO.pseudo_gt_z_box(list(c["depth"]), c["boxes"])
+    assert int(torch.isnan(zf).sum()) == 1
+    zp = WO.pseudo_gt_z_point_loss(list(c["depth"]), c["pred_xy"], c["pred_z"], c["counts"])
+    assert np.array_equal(zp.numpy(), D["z_point"])
+    cubes = c["cubes"].clone().requires_grad_(True)
+    dr = WO.depth_range_loss(c["masks"], c["mask_idx"].tolist(), list(c["depth"]), cubes, c["gt_boxes"], c["counts"])
+    np.testing.assert_allclose(dr.detach().numpy(), D["depth_range"], rtol=0, atol=2e-6)
+    g = torch.autograd.grad(dr.sum(), cubes)[0]
+    np.testing.assert_allclose(g.numpy(), D["grad_depth_range"], rtol=1e-6, atol=1e-6)
