@@ -18,7 +18,7 @@ using namespace tdod;
 
 namespace {
 
-constexpr int kSelT = 256;
+constexpr int kSelT = 1024;
 
 struct Region {                 // pixels (y0 + r, x0 + c), r < rows, c < cols, of one H x W frame; m == nullptr: all of them
     const float* d;
@@ -37,54 +37,81 @@ __device__ __forceinline__ float val_of(unsigned k) {
 struct SelShared {
     unsigned hist[257];         // bin 256 swallows the lanes that have no pixel
     unsigned sel[2];
-    unsigned cnt[2];            // pixels in the region, NaNs among them
+    unsigned cnt[2];            // pixels in the region, NaNs among them; later: values <= v, smallest key above v
+    int box[4];                 // bounding box of the mask pixels
 };
 
-// pixels in the region (under the mask) and how many of them are NaN; every thread returns the same pair
-__device__ void region_count(const Region& R, SelShared& s, unsigned& n, unsigned& n_nan) {
-    if (threadIdx.x < 2) s.cnt[threadIdx.x] = 0;
-    __syncthreads();
-    const unsigned total = (unsigned)R.rows * (unsigned)R.cols;
-    unsigned c = 0, cn = 0;
-    for (unsigned i = threadIdx.x; i < total; i += kSelT) {
-        const unsigned r = i / (unsigned)R.cols, col = i - r * (unsigned)R.cols;
-        const size_t idx = (size_t)(R.y0 + (int)r) * R.W + R.x0 + (int)col;
-        if (R.m && !R.m[idx]) continue;
-        const float v = R.d[idx];
-        c++;
-        cn += (v != v);
+// Calls fn(valid, value, r, c) for every pixel of the region, warp-uniformly (all 32 lanes enter every call, so fn may
+// use full-mask warp intrinsics): a warp per row, 128 columns per step with the four loads of a lane issued together.
+template <class Fn>
+__device__ __forceinline__ void region_scan(const Region& R, Fn fn) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int r = warp; r < R.rows; r += kSelT / 32) {
+        const size_t row = (size_t)(R.y0 + r) * R.W + R.x0;
+        for (int c0 = 0; c0 < R.cols; c0 += 128) {
+            float v[4];
+            bool ok[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int c = c0 + u * 32 + lane;
+                const bool in = c < R.cols;
+                v[u] = in ? R.d[row + c] : 0.0f;
+                ok[u] = in && (!R.m || R.m[row + c]);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) fn(ok[u], v[u], r, c0 + u * 32 + lane);
+        }
     }
+}
+
+// pixels in the region (under the mask) and how many of them are NaN; with a mask the region shrinks to the bounding box
+// of its pixels.  Every thread returns the same pair.
+__device__ void region_count(Region& R, SelShared& s, unsigned& n, unsigned& n_nan) {
+    if (threadIdx.x < 2) s.cnt[threadIdx.x] = 0;
+    if (threadIdx.x == 0) { s.box[0] = s.box[1] = 0x7fffffff; s.box[2] = s.box[3] = -1; }
+    __syncthreads();
+    unsigned c = 0, cn = 0;
+    int bx0 = 0x7fffffff, by0 = 0x7fffffff, bx1 = -1, by1 = -1;
+    region_scan(R, [&](bool ok, float v, int r, int col) {
+        if (ok) {
+            c++;
+            cn += (v != v);
+            bx0 = min(bx0, col); bx1 = max(bx1, col); by0 = min(by0, r); by1 = max(by1, r);
+        }
+    });
     c = __reduce_add_sync(0xffffffffu, c);
     cn = __reduce_add_sync(0xffffffffu, cn);
-    if ((threadIdx.x & 31) == 0) { atomicAdd(&s.cnt[0], c); atomicAdd(&s.cnt[1], cn); }
+    if (R.m) {
+        bx0 = __reduce_min_sync(0xffffffffu, bx0); by0 = __reduce_min_sync(0xffffffffu, by0);
+        bx1 = __reduce_max_sync(0xffffffffu, bx1); by1 = __reduce_max_sync(0xffffffffu, by1);
+    }
+    if ((threadIdx.x & 31) == 0 && c) {
+        atomicAdd(&s.cnt[0], c); atomicAdd(&s.cnt[1], cn);
+        if (R.m) { atomicMin(&s.box[0], bx0); atomicMin(&s.box[1], by0); atomicMax(&s.box[2], bx1); atomicMax(&s.box[3], by1); }
+    }
     __syncthreads();
     n = s.cnt[0];
     n_nan = s.cnt[1];
+    if (R.m && n) {
+        R.x0 += s.box[0]; R.y0 += s.box[1];
+        R.cols = s.box[2] - s.box[0] + 1; R.rows = s.box[3] - s.box[1] + 1;
+    }
     __syncthreads();
 }
 
 // k-th smallest (0-based) of the region's values: four passes, most significant byte first
 __device__ float region_select(const Region& R, unsigned k, SelShared& s) {
-    const unsigned total = (unsigned)R.rows * (unsigned)R.cols;
     unsigned prefix = 0, known = 0;
     for (int shift = 24; shift >= 0; shift -= 8) {
         for (int i = threadIdx.x; i < 257; i += kSelT) s.hist[i] = 0;
         __syncthreads();
-        for (unsigned base = 0; base < total; base += kSelT) {
-            const unsigned i = base + threadIdx.x;
-            unsigned bin = 256;
-            if (i < total) {
-                const unsigned r = i / (unsigned)R.cols, col = i - r * (unsigned)R.cols;
-                const size_t idx = (size_t)(R.y0 + (int)r) * R.W + R.x0 + (int)col;
-                if (!R.m || R.m[idx]) {
-                    const unsigned key = key_of(R.d[idx]);
-                    if ((key & known) == prefix) bin = (key >> shift) & 255u;
-                }
-            }
+        region_scan(R, [&](bool ok, float v, int, int) {
+            const unsigned key = key_of(v);
+            const unsigned bin = (ok && (key & known) == prefix) ? ((key >> shift) & 255u) : 256u;
             // neighbouring depths share their leading bytes: one shared-memory add per distinct bin of the warp
             const unsigned peers = __match_any_sync(0xffffffffu, bin);
             if (bin < 256 && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) atomicAdd(&s.hist[bin], __popc(peers));
-        }
+        });
         __syncthreads();
         if (threadIdx.x < 32) {                     // first bin whose running count passes k
             const int lane = threadIdx.x;
@@ -114,6 +141,29 @@ __device__ float region_select(const Region& R, unsigned k, SelShared& s) {
     return val_of(prefix);
 }
 
+// the order statistic of rank k + 1, given v = the one of rank k: v again when more than k + 1 values are <= v, else the
+// smallest value above v (one pass instead of four)
+__device__ float region_next(const Region& R, unsigned k, float v, SelShared& s) {
+    if (threadIdx.x == 0) { s.cnt[0] = 0; s.cnt[1] = 0xffffffffu; }
+    __syncthreads();
+    const unsigned kv = key_of(v);
+    unsigned le = 0, up = 0xffffffffu;
+    region_scan(R, [&](bool ok, float x, int, int) {
+        const unsigned key = key_of(x);
+        if (ok) {
+            if (key <= kv) le++;
+            else up = min(up, key);
+        }
+    });
+    le = __reduce_add_sync(0xffffffffu, le);
+    up = __reduce_min_sync(0xffffffffu, up);
+    if ((threadIdx.x & 31) == 0) { atomicAdd(&s.cnt[0], le); atomicMin(&s.cnt[1], up); }
+    __syncthreads();
+    const float res = (s.cnt[0] > k + 1) ? v : val_of(s.cnt[1]);
+    __syncthreads();
+    return res;
+}
+
 // at::lerp (aten/src/ATen/native/Lerp.h) the way nvcc contracts it in torch's CUDA build
 __device__ __forceinline__ float torch_lerp(float a, float b, float w) {
     const float diff = __fsub_rn(b, a);
@@ -126,7 +176,7 @@ __device__ float region_quantile(const Region& R, unsigned n, float q, SelShared
     const float rank = __fmul_rn(q, (float)(n - 1));
     const float lo = floorf(rank), hi = ceilf(rank);
     const float below = region_select(R, (unsigned)lo, s);
-    const float above = (hi == lo) ? below : region_select(R, (unsigned)hi, s);
+    const float above = (hi == lo) ? below : region_next(R, (unsigned)lo, below, s);
     return torch_lerp(below, above, __fsub_rn(rank, lo));
 }
 

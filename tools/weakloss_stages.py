@@ -47,3 +47,17 @@ def t(fn, n=20):
     b.record(); torch.cuda.synchronize(); return a.elapsed_time(b) / n
 print("moments kernel ms", t(lambda: L.check(L.lib().tdod_hull_fill_moments(L.ptr(mu8), L.ptr(idx_t), L.ptr(h), L.ptr(meta), N, H, W, 0, L.ptr(mom), L.stream_ptr()))))
 print("grad kernels ms", t(lambda: L.check(L.lib().tdod_hull_fill_grad(L.ptr(mu8), L.ptr(idx_t), L.ptr(h), L.ptr(meta), N, H, W, L.ptr(gm), L.ptr(ws), L.ptr(gout), L.stream_ptr()))))
+# the depth-map losses: one launch for all boxes against the reference's per-box loop of torch.median / torch.quantile
+depth, fidx = batch.depth, batch.obj_frame
+print("depth_select median (mode 0) ms", t(lambda: WL.depth_select(depth, fidx, db, 0)))
+print("depth_select q90-q10 under masks (mode 2) ms", t(lambda: WL.depth_select(depth, fidx, db, 2, masks=mu8, mask_idx=idx_t)))
+def torch_loop():
+    bl = db.long()
+    return [torch.median(depth[fidx[i], bl[i, 1]:bl[i, 3], bl[i, 0]:bl[i, 2]]) for i in range(N)]
+def torch_loop_q():
+    out = []
+    for i in range(N):
+        v = depth[fidx[i]][dm[i]]
+        out.append(torch.quantile(v, 0.9) - torch.quantile(v, 0.1))
+    return out
+print("torch per-box median loop ms", t(torch_loop, 5), " torch per-mask quantile loop ms", t(torch_loop_q, 5), " boxes", N)
