@@ -35,9 +35,9 @@ __device__ __forceinline__ float val_of(unsigned k) {
 }
 
 struct SelShared {
-    unsigned hist[257];         // bin 256 swallows the lanes that have no pixel
-    unsigned sel[2];
-    unsigned cnt[2];            // pixels in the region, NaNs among them; later: values <= v, smallest key above v
+    unsigned hist[514];         // two histograms of 257: bin 256 of the second swallows the lanes that have no pixel
+    unsigned sel[4];
+    unsigned cnt[4];            // pixels in the region, NaNs among them; later: values <= v, smallest key above v (x2)
     int box[4];                 // bounding box of the mask pixels
 };
 
@@ -141,43 +141,96 @@ __device__ float region_select(const Region& R, unsigned k, SelShared& s) {
     return val_of(prefix);
 }
 
-// the order statistic of rank k + 1, given v = the one of rank k: v again when more than k + 1 values are <= v, else the
-// smallest value above v (one pass instead of four)
-__device__ float region_next(const Region& R, unsigned k, float v, SelShared& s) {
-    if (threadIdx.x == 0) { s.cnt[0] = 0; s.cnt[1] = 0xffffffffu; }
-    __syncthreads();
-    const unsigned kv = key_of(v);
-    unsigned le = 0, up = 0xffffffffu;
-    region_scan(R, [&](bool ok, float x, int, int) {
-        const unsigned key = key_of(x);
-        if (ok) {
-            if (key <= kv) le++;
-            else up = min(up, key);
-        }
-    });
-    le = __reduce_add_sync(0xffffffffu, le);
-    up = __reduce_min_sync(0xffffffffu, up);
-    if ((threadIdx.x & 31) == 0) { atomicAdd(&s.cnt[0], le); atomicMin(&s.cnt[1], up); }
-    __syncthreads();
-    const float res = (s.cnt[0] > k + 1) ? v : val_of(s.cnt[1]);
-    __syncthreads();
-    return res;
-}
-
 // at::lerp (aten/src/ATen/native/Lerp.h) the way nvcc contracts it in torch's CUDA build
 __device__ __forceinline__ float torch_lerp(float a, float b, float w) {
     const float diff = __fsub_rn(b, a);
     return (fabsf(w) < 0.5f) ? __fmaf_rn(w, diff, a) : __fmaf_rn(-diff, __fsub_rn(1.0f, w), b);
 }
 
+// one warp: the first bin of h[0..255] whose running count passes k -> sel[0], and k's rank inside that bin -> sel[1]
+__device__ __forceinline__ void find_bin(const unsigned* h, unsigned k, unsigned* sel) {
+    const int lane = threadIdx.x & 31;
+    unsigned mine = 0;
+    for (int j = 0; j < 8; j++) mine += h[lane * 8 + j];
+    unsigned inc = mine;
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned a = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += a;
+    }
+    const int owner = __ffs(__ballot_sync(0xffffffffu, inc > k)) - 1;
+    if (lane == owner) {
+        unsigned acc = inc - mine;
+        int b = lane * 8;
+        while (acc + h[b] <= k) acc += h[b++];
+        sel[0] = (unsigned)b;
+        sel[1] = k - acc;
+    }
+}
+
+// the order statistics of ranks ka and kb in the same four passes: a pixel counts in a's histogram, in b's, or, while the
+// two prefixes still coincide, in the one they share
+__device__ void region_select2(const Region& R, unsigned ka, unsigned kb, SelShared& s, float& va, float& vb) {
+    unsigned pa = 0, pb = 0, known = 0;
+    for (int shift = 24; shift >= 0; shift -= 8) {
+        for (int i = threadIdx.x; i < 514; i += kSelT) s.hist[i] = 0;
+        __syncthreads();
+        region_scan(R, [&](bool ok, float v, int, int) {
+            const unsigned key = key_of(v), top = key & known, dig = (key >> shift) & 255u;
+            const unsigned bin = !ok ? 513u : (top == pa) ? dig : (top == pb) ? 257u + dig : 513u;
+            const unsigned peers = __match_any_sync(0xffffffffu, bin);
+            if (bin < 513 && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) atomicAdd(&s.hist[bin], __popc(peers));
+        });
+        __syncthreads();
+        if (threadIdx.x < 32) find_bin(s.hist, ka, s.sel);
+        else if (threadIdx.x < 64) find_bin(pa == pb ? s.hist : s.hist + 257, kb, s.sel + 2);
+        __syncthreads();
+        pa |= s.sel[0] << shift; ka = s.sel[1];
+        pb |= s.sel[2] << shift; kb = s.sel[3];
+        known |= 0xffu << shift;
+        __syncthreads();
+    }
+    va = val_of(pa);
+    vb = val_of(pb);
+}
+
+// the order statistics of ranks ka + 1 and kb + 1, given va and vb of ranks ka and kb, in one pass: v again when more than
+// k + 1 values are <= v, else the smallest value above v
+__device__ void region_next2(const Region& R, unsigned ka, float va, unsigned kb, float vb, SelShared& s, float& na, float& nb) {
+    if (threadIdx.x < 4) s.cnt[threadIdx.x] = (threadIdx.x & 1) ? 0xffffffffu : 0u;
+    __syncthreads();
+    const unsigned kva = key_of(va), kvb = key_of(vb);
+    unsigned lea = 0, upa = 0xffffffffu, leb = 0, upb = 0xffffffffu;
+    region_scan(R, [&](bool ok, float x, int, int) {
+        const unsigned key = key_of(x);
+        if (ok) {
+            if (key <= kva) lea++; else upa = min(upa, key);
+            if (key <= kvb) leb++; else upb = min(upb, key);
+        }
+    });
+    lea = __reduce_add_sync(0xffffffffu, lea); upa = __reduce_min_sync(0xffffffffu, upa);
+    leb = __reduce_add_sync(0xffffffffu, leb); upb = __reduce_min_sync(0xffffffffu, upb);
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&s.cnt[0], lea); atomicMin(&s.cnt[1], upa);
+        atomicAdd(&s.cnt[2], leb); atomicMin(&s.cnt[3], upb);
+    }
+    __syncthreads();
+    na = (s.cnt[0] > ka + 1) ? va : val_of(s.cnt[1]);
+    nb = (s.cnt[2] > kb + 1) ? vb : val_of(s.cnt[3]);
+    __syncthreads();
+}
+
 // torch.quantile(x, q) with linear interpolation (aten/src/ATen/native/Sorting.cpp, quantile_compute): rank = q * (n - 1)
-// in fp32, the two neighbouring order statistics, lerp by the fractional rank
-__device__ float region_quantile(const Region& R, unsigned n, float q, SelShared& s) {
-    const float rank = __fmul_rn(q, (float)(n - 1));
-    const float lo = floorf(rank), hi = ceilf(rank);
-    const float below = region_select(R, (unsigned)lo, s);
-    const float above = (hi == lo) ? below : region_next(R, (unsigned)lo, below, s);
-    return torch_lerp(below, above, __fsub_rn(rank, lo));
+// in fp32, the two neighbouring order statistics, lerp by the fractional rank.  Returns quantile(qb) - quantile(qa), qa < qb.
+__device__ float region_quantile_range(const Region& R, unsigned n, float qa, float qb, SelShared& s) {
+    const float ra = __fmul_rn(qa, (float)(n - 1)), rb = __fmul_rn(qb, (float)(n - 1));
+    const float la = floorf(ra), lb = floorf(rb);
+    float va, vb, na, nb;
+    region_select2(R, (unsigned)la, (unsigned)lb, s, va, vb);
+    na = va; nb = vb;
+    if (ceilf(ra) != la || ceilf(rb) != lb) region_next2(R, (unsigned)la, va, (unsigned)lb, vb, s, na, nb);
+    if (ceilf(ra) == la) na = va;          // an integral rank interpolates to itself (its weight is 0; keeps NaN-free)
+    if (ceilf(rb) == lb) nb = vb;
+    return __fsub_rn(torch_lerp(vb, nb, __fsub_rn(rb, lb)), torch_lerp(va, na, __fsub_rn(ra, la)));
 }
 
 __device__ __forceinline__ float clampf(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
@@ -228,7 +281,7 @@ depth_select_kernel(const float* __restrict__ depth, const int32_t* __restrict__
             region_count(R, s, n, n_nan);
         }
         if (n == 0 || n_nan) res = nan;
-        else res = __fsub_rn(region_quantile(R, n, 0.9f, s), region_quantile(R, n, 0.1f, s));
+        else res = region_quantile_range(R, n, 0.1f, 0.9f, s);
     }
     if (threadIdx.x == 0) {
         out[item] = res;
