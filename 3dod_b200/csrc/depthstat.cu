@@ -37,13 +37,13 @@ __device__ __forceinline__ float val_of(unsigned k) {
 struct SelShared {
     unsigned hist[514];         // two histograms of 257: bin 256 of the second swallows the lanes that have no pixel
     unsigned sel[4];
-    unsigned cnt[4];            // pixels in the region, NaNs among them; later: values <= v, smallest key above v (x2)
+    unsigned cnt[5];            // pixels in the region, NaNs among them; later: values <= v, smallest key above v (x2)
     int box[4];                 // bounding box of the mask pixels
 };
 
 // Calls fn(valid, value, r, c) for every pixel of the region, warp-uniformly (all 32 lanes enter every call, so fn may
 // use full-mask warp intrinsics): a warp per row, 128 columns per step with the four loads of a lane issued together.
-template <class Fn>
+template <bool kDepth = true, class Fn>
 __device__ __forceinline__ void region_scan(const Region& R, Fn fn) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int r = warp; r < R.rows; r += kSelT / 32) {
@@ -55,7 +55,7 @@ __device__ __forceinline__ void region_scan(const Region& R, Fn fn) {
             for (int u = 0; u < 4; u++) {
                 const int c = c0 + u * 32 + lane;
                 const bool in = c < R.cols;
-                v[u] = in ? R.d[row + c] : 0.0f;
+                v[u] = (kDepth && in) ? R.d[row + c] : 0.0f;
                 ok[u] = in && (!R.m || R.m[row + c]);
             }
 #pragma unroll
@@ -64,21 +64,23 @@ __device__ __forceinline__ void region_scan(const Region& R, Fn fn) {
     }
 }
 
-// pixels in the region (under the mask) and how many of them are NaN; with a mask the region shrinks to the bounding box
-// of its pixels.  Every thread returns the same pair.
+// pixels in the region and how many of them are NaN; with a mask only the mask is read (n_nan = 0, see region_next2) and
+// the region shrinks to the bounding box of its pixels.  Every thread returns the same pair.
 __device__ void region_count(Region& R, SelShared& s, unsigned& n, unsigned& n_nan) {
     if (threadIdx.x < 2) s.cnt[threadIdx.x] = 0;
     if (threadIdx.x == 0) { s.box[0] = s.box[1] = 0x7fffffff; s.box[2] = s.box[3] = -1; }
     __syncthreads();
     unsigned c = 0, cn = 0;
     int bx0 = 0x7fffffff, by0 = 0x7fffffff, bx1 = -1, by1 = -1;
-    region_scan(R, [&](bool ok, float v, int r, int col) {
-        if (ok) {
-            c++;
-            cn += (v != v);
-            bx0 = min(bx0, col); bx1 = max(bx1, col); by0 = min(by0, r); by1 = max(by1, r);
-        }
-    });
+    if (R.m) {                                      // the mask bytes alone: region_next2 reports the NaNs under the mask
+        region_scan<false>(R, [&](bool ok, float, int r, int col) {
+            if (ok) { c++; bx0 = min(bx0, col); bx1 = max(bx1, col); by0 = min(by0, r); by1 = max(by1, r); }
+        });
+    } else {
+        region_scan(R, [&](bool ok, float v, int, int) {
+            if (ok) { c++; cn += (v != v); }
+        });
+    }
     c = __reduce_add_sync(0xffffffffu, c);
     cn = __reduce_add_sync(0xffffffffu, cn);
     if (R.m) {
@@ -195,28 +197,33 @@ __device__ void region_select2(const Region& R, unsigned ka, unsigned kb, SelSha
 
 // the order statistics of ranks ka + 1 and kb + 1, given va and vb of ranks ka and kb, in one pass: v again when more than
 // k + 1 values are <= v, else the smallest value above v
-__device__ void region_next2(const Region& R, unsigned ka, float va, unsigned kb, float vb, SelShared& s, float& na, float& nb) {
-    if (threadIdx.x < 4) s.cnt[threadIdx.x] = (threadIdx.x & 1) ? 0xffffffffu : 0u;
+__device__ unsigned region_next2(const Region& R, unsigned ka, float va, unsigned kb, float vb, SelShared& s, float& na, float& nb) {
+    if (threadIdx.x < 5) s.cnt[threadIdx.x] = (threadIdx.x & 1) ? 0xffffffffu : 0u;
     __syncthreads();
     const unsigned kva = key_of(va), kvb = key_of(vb);
-    unsigned lea = 0, upa = 0xffffffffu, leb = 0, upb = 0xffffffffu;
+    unsigned lea = 0, upa = 0xffffffffu, leb = 0, upb = 0xffffffffu, cn = 0;
     region_scan(R, [&](bool ok, float x, int, int) {
         const unsigned key = key_of(x);
         if (ok) {
+            cn += (x != x);
             if (key <= kva) lea++; else upa = min(upa, key);
             if (key <= kvb) leb++; else upb = min(upb, key);
         }
     });
     lea = __reduce_add_sync(0xffffffffu, lea); upa = __reduce_min_sync(0xffffffffu, upa);
     leb = __reduce_add_sync(0xffffffffu, leb); upb = __reduce_min_sync(0xffffffffu, upb);
+    cn = __reduce_add_sync(0xffffffffu, cn);
     if ((threadIdx.x & 31) == 0) {
         atomicAdd(&s.cnt[0], lea); atomicMin(&s.cnt[1], upa);
         atomicAdd(&s.cnt[2], leb); atomicMin(&s.cnt[3], upb);
+        if (cn) atomicAdd(&s.cnt[4], cn);
     }
     __syncthreads();
     na = (s.cnt[0] > ka + 1) ? va : val_of(s.cnt[1]);
     nb = (s.cnt[2] > kb + 1) ? vb : val_of(s.cnt[3]);
+    const unsigned n_nan = s.cnt[4];
     __syncthreads();
+    return n_nan;
 }
 
 // torch.quantile(x, q) with linear interpolation (aten/src/ATen/native/Sorting.cpp, quantile_compute): rank = q * (n - 1)
@@ -226,8 +233,8 @@ __device__ float region_quantile_range(const Region& R, unsigned n, float qa, fl
     const float la = floorf(ra), lb = floorf(rb);
     float va, vb, na, nb;
     region_select2(R, (unsigned)la, (unsigned)lb, s, va, vb);
-    na = va; nb = vb;
-    if (ceilf(ra) != la || ceilf(rb) != lb) region_next2(R, (unsigned)la, va, (unsigned)lb, vb, s, na, nb);
+    // always run: the pass also reports the NaNs of the region, which make torch.quantile NaN
+    if (region_next2(R, (unsigned)la, va, (unsigned)lb, vb, s, na, nb)) return __uint_as_float(0x7fc00000u);
     if (ceilf(ra) == la) na = va;          // an integral rank interpolates to itself (its weight is 0; keeps NaN-free)
     if (ceilf(rb) == lb) nb = vb;
     return __fsub_rn(torch_lerp(vb, nb, __fsub_rn(rb, lb)), torch_lerp(va, na, __fsub_rn(ra, la)));
