@@ -6,6 +6,13 @@ from tdod import api
 from .spaces import _require_cuda, boxes_cls
 
 
+def cube_to_box(cube, K):
+    """conversions.py:5-23: tight box around the 8 projected corners of ONE `Cube` -> Boxes[1] (no clamp)."""
+    c = cube.get_bube_corners(K)
+    lo, hi = c.min(dim=0)[0], c.max(dim=0)[0]
+    return boxes_cls()(torch.stack((lo[0], lo[1], hi[0], hi[1]))[None])
+
+
 def cubes_to_box(cubes, K, im_shape):
     """conversions.py:25-48.  cubes: Cubes [N,n,15]; K [3,3]; im_shape = (width, height) -> list of N Boxes[n]."""
     _require_cuda(cubes.tensor, "cubes")

@@ -2,8 +2,9 @@
 
 `Plane` keeps the torch API (fit / fit_parallel return the NEGATED equation, plane.py:77,134); `Plane_np` keeps the
 NumPy / pyransac3d API used at cubercnn/modeling/roi_heads/roi_heads.py:374-376 (returns +equation, fp64).
-Sample ids are drawn with python's `random.sample` exactly as plane.py:95 / :171 do, so a seeded run selects the
-same hypotheses as the reference."""
+Sample ids are drawn exactly as the reference draws them -- python's `random.sample` in fit_parallel / Plane_np.fit
+(plane.py:95, :171), `torch.randperm(n)[:3]` from torch's default CPU generator in the sequential Plane.fit (:41) --
+so a seeded run selects the same hypotheses as the reference."""
 import random
 
 import numpy as np
@@ -16,8 +17,15 @@ def _draw_ids(n_points, iters):
     return [random.sample(range(0, n_points), 3) for _ in range(iters)]
 
 
-def _fit(pts_soa, n_points, thresh, iters):
-    ids = torch.tensor(_draw_ids(n_points, iters), dtype=torch.int32).to(pts_soa.device, non_blocking=True)[None]
+def _draw_ids_randperm(n_points, iters):
+    """plane.py:41: one full torch.randperm(n_points) per iteration, first three entries kept"""
+    return torch.stack([torch.randperm(n_points)[:3] for _ in range(iters)]).to(torch.int32)
+
+
+def _fit(pts_soa, n_points, thresh, iters, ids=None):
+    if ids is None:
+        ids = torch.tensor(_draw_ids(n_points, iters), dtype=torch.int32)
+    ids = ids.to(pts_soa.device, non_blocking=True)[None]
     n = torch.tensor([n_points], dtype=torch.int32, device=pts_soa.device)
     return api.ransac_plane(pts_soa, n, ids.contiguous(), iters=iters, thresh=thresh, want_mask=True)
 
@@ -38,9 +46,16 @@ class Plane:
         return -self.equation, self.inliers
 
     def fit(self, pts, thresh=0.05, minPoints=100, maxIteration=1000):
-        """plane.py:22-77: the sequential form keeps the first hypothesis with a strictly larger inlier count,
-        which is the first maximum -- the same winner fit_parallel's argmax picks."""
-        return self.fit_parallel(pts, thresh, minPoints, maxIteration)
+        """plane.py:22-77: the sequential form draws `torch.randperm(n)[:3]` per iteration (:41) and keeps the first
+        hypothesis with a strictly larger inlier count, i.e. the first maximum -- what the kernel's argmax picks.
+        The plane arithmetic (:53-66) is the same chain of fp32 torch ops as fit_parallel's."""
+        if not pts.is_cuda:
+            raise ValueError("pts must be a CUDA tensor (no CPU path)")
+        soa = pts.to(torch.float32).t().contiguous()[None]
+        r = _fit(soa, pts.shape[0], thresh, maxIteration, ids=_draw_ids_randperm(pts.shape[0], maxIteration))
+        self.equation = r["eq"][0]
+        self.inliers = torch.where(r["mask"][0] > 0)[0]
+        return -self.equation, self.inliers
 
 
 class Plane_np:

@@ -71,6 +71,44 @@ def _require_cuda(t, what):
         raise ValueError("%s requires grad: the CUDA path is forward-only (weak-loss training is out of scope)" % what)
 
 
+class Cube:
+    """spaces.py:16-93: the single-cube container some callers still import (`cube_to_box`, conversions.py:5-23).
+    tensor [6] = (x, y, z, w, h, l), R [3,3]; corners and the unclamped projection come from libtdod."""
+
+    def __init__(self, tensor, R, score=None, label=None):
+        self.tensor = tensor
+        self.center = tensor[:3]
+        self.dimensions = tensor[3:6]
+        self.rotation = R
+        self.score = score
+        self.label = label
+
+    def _row(self):
+        _require_cuda(self.tensor, "Cube.tensor")
+        return torch.cat((self.tensor[:6].to(torch.float32), self.rotation.to(torch.float32).reshape(9)))[None].contiguous()
+
+    def get_all_corners(self):
+        """[8,3] (math_util.py:142-245 vertex order)"""
+        return api.cube_corners(self._row())[0]
+
+    def get_bube_corners(self, K):
+        """[8,2]: K @ corner, divided by depth, no clamp (spaces.py:69-72)"""
+        p = self.get_all_corners() @ K.to(self.tensor.device, torch.float32).t()
+        return p[:, :2] / p[:, 2].unsqueeze(1)
+
+    def get_volume(self):
+        return self.dimensions.prod().item()
+
+    def __repr__(self):
+        return f"Cube({self.center}, {self.dimensions}, {self.rotation})"
+
+    def to_device(self, device):
+        self.tensor = self.tensor.to(device)
+        self.center, self.dimensions = self.center.to(device), self.dimensions.to(device)
+        self.rotation = self.rotation.to(device)
+        return self
+
+
 class Cubes:
     """spaces.py:95-328.  `scores` / `labels` are auxiliary side fields exactly as in the reference."""
 

@@ -77,10 +77,15 @@ __device__ __forceinline__ float philox_xn(const tdod_pss_args& a, const ObjCtx&
 
 // accepted standard normals for (w,h,l) of proposal i
 // `xn`: Philox mode only -- the standard normal of the x draw (fourth normal of the first try's Philox block)
-__device__ __forceinline__ void draw_whl(const tdod_pss_args& a, const ObjCtx& c, int i, float& w, float& h, float& l, float& xn) {
+// `zn`: the three numbers behind (w,h,l) as HOST mode would be fed them (accepted standard normals, or the U[0,1) draws of
+// the uniform-dimension modes) -- what out_noise records so that a PHILOX run can be replayed in HOST mode
+__device__ __forceinline__ void draw_whl(const tdod_pss_args& a, const ObjCtx& c, int i, float& w, float& h, float& l, float& xn,
+                                         float (&zn)[3]) {
     xn = 0.f;
+    zn[0] = zn[1] = zn[2] = 0.f;
     if (a.rng_mode == TDOD_RNG_HOST) {
         const float* nz = a.noise + (size_t)c.obj * 6 * a.n_prop;
+        zn[0] = nz[i]; zn[1] = nz[a.n_prop + i]; zn[2] = nz[2 * a.n_prop + i];
         if (a.dims_mode == TDOD_DIMS_PRIOR) {
             w = scale_normal(nz[i], c.mu[0], c.sg[0]);
             h = scale_normal(nz[a.n_prop + i], c.mu[1], c.sgh);
@@ -97,7 +102,8 @@ __device__ __forceinline__ void draw_whl(const tdod_pss_args& a, const ObjCtx& c
         const uint64_t gid = (uint64_t)(a.obj_id_base + c.obj);
         const uint4 r = ph((uint32_t)i, (uint32_t)gid, (uint32_t)(gid >> 32) ^ 0x57484Cu, 0u);
         w = rescale_dim(u01(r.x));
-        if (a.dims_mode == TDOD_DIMS_UNIFORM) { h = rescale_dim(u01(r.y)); l = rescale_dim(u01(r.z)); }
+        zn[0] = u01(r.x);
+        if (a.dims_mode == TDOD_DIMS_UNIFORM) { h = rescale_dim(u01(r.y)); l = rescale_dim(u01(r.z)); zn[1] = u01(r.y); zn[2] = u01(r.z); }
         else { h = __fmul_rn(w, c.rh); l = __fmul_rn(w, c.rl); }
         xn = philox_xn(a, c, i);
         return;
@@ -112,16 +118,23 @@ __device__ __forceinline__ void draw_whl(const tdod_pss_args& a, const ObjCtx& c
         const uint4 r = ph((uint32_t)i, (uint32_t)gid, (uint32_t)(gid >> 32) ^ 0x57484Cu, t);
         const float2 n01 = box_muller(r.x, r.y), n23 = box_muller(r.z, r.w);
         if (t == 0) xn = n23.y;
-        if (!okw) { w = scale_normal(n01.x, c.mu[0], c.sg[0]); okw = !(w < TDOD_MIN_PROP_S || w > c.hi[0]); }
-        if (!okh) { h = scale_normal(n01.y, c.mu[1], c.sgh);   okh = !(h < TDOD_MIN_PROP_S || h > c.hi[1]); }
-        if (!okl) { l = scale_normal(n23.x, c.mu[2], c.sg[2]); okl = !(l < TDOD_MIN_PROP_S || l > c.hi[2]); }
+        if (!okw) { zn[0] = n01.x; w = scale_normal(n01.x, c.mu[0], c.sg[0]); okw = !(w < TDOD_MIN_PROP_S || w > c.hi[0]); }
+        if (!okh) { zn[1] = n01.y; h = scale_normal(n01.y, c.mu[1], c.sgh);   okh = !(h < TDOD_MIN_PROP_S || h > c.hi[1]); }
+        if (!okl) { zn[2] = n23.x; l = scale_normal(n23.x, c.mu[2], c.sg[2]); okl = !(l < TDOD_MIN_PROP_S || l > c.hi[2]); }
     }
 }
 
 // standard normals for x,y,z and the rotation of proposal i -> q[0..2], q[6..14]
+// `rec`: out_noise / out_yaw_idx are written when true (the winner's recomputation passes false)
 __device__ __forceinline__ void draw_xyz_rot(const tdod_pss_args& a, const ObjCtx& c, const float* yaw, int i,
-                                             const float (&mean)[3], const float (&sd)[3], float xn, float* q) {
+                                             const float (&mean)[3], const float (&sd)[3], float xn, float* q, bool rec) {
+    float* on = (rec && a.out_noise) ? a.out_noise + (size_t)c.obj * 6 * a.n_prop : nullptr;
     if (a.rng_mode == TDOD_RNG_HOST) {
+        if (on) {
+            const float* nz = a.noise + (size_t)c.obj * 6 * a.n_prop;
+            on[3 * a.n_prop + i] = nz[3 * a.n_prop + i]; on[4 * a.n_prop + i] = nz[4 * a.n_prop + i];
+            on[5 * a.n_prop + i] = nz[5 * a.n_prop + i];
+        }
         const float* nz = a.noise + (size_t)c.obj * 6 * a.n_prop;
         if (a.centre_mode == TDOD_CENTRE_DEPTH) {
             q[0] = scale_normal(nz[3 * a.n_prop + i], mean[0], sd[0]);
@@ -139,6 +152,7 @@ __device__ __forceinline__ void draw_xyz_rot(const tdod_pss_args& a, const ObjCt
         }
         if (a.yaw_table) {
             const int yi = a.yaw_idx[(size_t)c.obj * a.n_prop + i];
+            if (rec && a.out_yaw_idx) a.out_yaw_idx[(size_t)c.obj * a.n_prop + i] = (int16_t)yi;
 #pragma unroll
             for (int k = 0; k < 9; ++k) q[6 + k] = yaw[yi * 9 + k];
         } else {
@@ -157,17 +171,21 @@ __device__ __forceinline__ void draw_xyz_rot(const tdod_pss_args& a, const ObjCt
         q[0] = scale_normal(xn, mean[0], sd[0]);
         q[1] = scale_normal(n01.x, mean[1], sd[1]);
         q[2] = scale_normal(n01.y, mean[2], sd[2]);
+        if (on) { on[3 * a.n_prop + i] = xn; on[4 * a.n_prop + i] = n01.x; on[5 * a.n_prop + i] = n01.y; }
     } else if (a.centre_mode == TDOD_CENTRE_UNIFORM) {
         q[0] = __fsub_rn(__fmul_rn(u01(r.x), 4.f), 2.f);
         q[1] = __fsub_rn(__fmul_rn(u01(r.y), 2.f), 1.f);
         q[2] = __fadd_rn(__fmul_rn(u01(r.w), 4.f), 1.f);
+        if (on) { on[3 * a.n_prop + i] = u01(r.x); on[4 * a.n_prop + i] = u01(r.y); on[5 * a.n_prop + i] = u01(r.w); }
     } else {                                                                // PATCH (PATCH_Z needs the caller's ramp)
         q[0] = __fadd_rn(__fmul_rn((float)i, c.nsx), c.nx0);
         q[1] = __fadd_rn(__fmul_rn((float)i, c.nsy), c.ny0);
         q[2] = __fadd_rn(__fmul_rn(u01(r.w), 4.f), 1.f);
+        if (on) { on[3 * a.n_prop + i] = 0.f; on[4 * a.n_prop + i] = 0.f; on[5 * a.n_prop + i] = u01(r.w); }
     }
     if (a.yaw_table) {
         const int yi = (int)(r.z % TDOD_NYAW);  // torch.randint(36, ...): u32 % 36
+        if (rec && a.out_yaw_idx) a.out_yaw_idx[(size_t)c.obj * a.n_prop + i] = (int16_t)yi;
 #pragma unroll
         for (int k = 0; k < 9; ++k) q[6 + k] = yaw[yi * 9 + k];
     } else {
@@ -273,7 +291,8 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
     if (tid < 9) sh.K[tid] = a.K[(size_t)c.frame * 9 + tid];
     if (a.yaw_table)
         for (int t = tid; t < TDOD_NYAW * 9; t += kThreads) sh.yaw[t] = a.yaw_table[(size_t)c.frame * TDOD_NYAW * 9 + t];
-    const bool has_rect = a.propose_only ? true : (a.has_rect ? (a.has_rect[obj] != 0) : true);
+    // only code 1 is a rectangle; 0 (empty mask) and the error codes 3 / 4 of tdod_mask_rect take the fallback of :69-75
+    const bool has_rect = a.propose_only ? true : (a.has_rect ? (a.has_rect[obj] == 1) : true);
     if (tid < 8) sh.rect[tid] = (has_rect && a.rects) ? a.rects[(size_t)obj * 8 + tid] : 0.f;
     for (int t = tid; t < 4 * 3 * 256; t += kThreads) (&sh.mail.hist[0][0][0])[t] = 0;
     if (tid < 3) { sh.prefix[tid] = 0u; sh.kth[tid] = (n - 1) / 2; sh.mail.nanflag[tid] = 0; }
@@ -297,9 +316,18 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
             const float d = __ldg(depth + (size_t)iy * a.W + ix);
             centre_seed(gx, gy, d, fx, cx, cy, x, y, zt);
         }
-        draw_whl(a, c, i, w, h, l, xn);
+        float zn[3];
+        draw_whl(a, c, i, w, h, l, xn, zn);
         s_d[j] = xn;                                                       // parked until phase 2 reads it back
         const float z = __fadd_rn(zt, __fdiv_rn(l, 2.f));                  // proposals.py:394
+        if (a.out_noise) {
+            float* on = a.out_noise + (size_t)obj * 6 * n;
+            on[i] = zn[0]; on[n + i] = zn[1]; on[2 * n + i] = zn[2];
+        }
+        if (a.out_seeds) {
+            float* os = a.out_seeds + (size_t)obj * 3 * n;
+            os[i] = x; os[n + i] = y; os[2 * n + i] = z;
+        }
         s_x[j] = x; s_y[j] = y; s_z[j] = z; s_w[j] = w; s_h[j] = h; s_l[j] = l;
         lsum[0] += (double)x; lsum[1] += (double)y; lsum[2] += (double)z;
         lnan[0] |= (x != x); lnan[1] |= (y != y); lnan[2] |= (z != z);
@@ -430,7 +458,7 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
         for (int j = tid; j < cnt; j += kThreads) {
             const int i = i0 + j;
             float q[15];
-            draw_xyz_rot(a, c, sh.yaw, i, smean, ssd, s_d[j], q);
+            draw_xyz_rot(a, c, sh.yaw, i, smean, ssd, s_d[j], q, sweep == 1);
             q[3] = s_w[j]; q[4] = s_h[j]; q[5] = s_l[j];
             float X[8], Y[8], Z[8], U[8], V[8];
             cube_corners(q, X, Y, Z);
@@ -568,7 +596,7 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
         float q[15];
         float xn = 0.f;
         if (a.rng_mode == TDOD_RNG_PHILOX) xn = philox_xn(a, c, win.i);    // s_d[j] now holds the chamfer distance
-        draw_xyz_rot(a, c, sh.yaw, win.i, smean, ssd, xn, q);
+        draw_xyz_rot(a, c, sh.yaw, win.i, smean, ssd, xn, q, false);
         q[3] = s_w[j]; q[4] = s_h[j]; q[5] = s_l[j];
         float X[8], Y[8], Z[8];
         cube_corners(q, X, Y, Z);

@@ -108,6 +108,21 @@ def score_point_cloud(points, cubes):
     return out
 
 
+def box3d_iou(gt_corners, corners, want_vol=False):
+    """iou_3d: gt_corners [8,3] with corners [n,8,3] -> [n]; or batched [G,8,3] with [G,n,8,3] -> [G,n]"""
+    single = gt_corners.dim() == 2
+    g = gt_corners.reshape(-1, 8, 3)
+    c = corners.reshape(g.shape[0], -1, 8, 3)
+    G, n = c.shape[0], c.shape[1]
+    out = torch.empty((G, n), dtype=f32, device=c.device)
+    vol = torch.empty((G, n), dtype=f32, device=c.device) if want_vol else None
+    L.check(L.lib().tdod_box3d_iou(L.ptr(g.contiguous(), f32, "gt_corners"), L.ptr(c.contiguous(), f32, "corners"), G, n,
+                                   L.ptr(out), L.ptr(vol), L.stream_ptr()))
+    if single:
+        out, vol = out[0], (vol[0] if want_vol else None)
+    return (out, vol) if want_vol else out
+
+
 def yaw_table(normals):
     """normals [F,3] fp32/fp64 -> [F,36,3,3] fp32"""
     F = normals.shape[0]
@@ -162,13 +177,14 @@ def ransac_plane(pts, n_pts, sample_ids=None, seed=0, iters=1000, thresh=0.05, w
 
 
 class PssOutputs:
-    __slots__ = ("best_idx", "best_score", "best_cube", "best_box", "all_cubes", "all_boxes", "all_scores", "stats")
+    __slots__ = ("best_idx", "best_score", "best_cube", "best_box", "all_cubes", "all_boxes", "all_scores", "stats",
+                 "noise", "yaw_idx", "seeds")
 
 
 def propose_score_select(depth, K, boxes, prior_mean, prior_std, obj_frame, rects, has_rect, n_prop, yaw_tab=None,
                          iou_boxes=None, noise=None, yaw_idx=None, rot=None, seed=None, obj_id_base=0,
                          return_all=False, cluster_size=0, out=None, propose_only=False, centre_mode=L.CENTRE_DEPTH,
-                         dims_mode=L.DIMS_PRIOR, aux=None, im_shape=None):
+                         dims_mode=L.DIMS_PRIOR, aux=None, im_shape=None, want_noise=False, want_seeds=False):
     """The fused hot path (csrc/fused.cu).  depth [F,H,W], K [F,3,3], boxes [N,4], priors [N,3], obj_frame [N] int32,
     rects [N,4,2], has_rect [N] uint8 | None, yaw_tab [F,36,3,3] | None.
     Parity RNG mode: noise [N,6,n] (+ yaw_idx [N,n] int16 | rot [N,n,9]); throughput mode: seed=int (Philox)."""
@@ -226,5 +242,10 @@ def propose_score_select(depth, K, boxes, prior_mean, prior_std, obj_frame, rect
     if aux is not None and tuple(aux.shape) != (N, 2):
         raise ValueError("aux must be [N,2]")
     a.aux = L.ptr(aux, f32, "aux")
+    # audit outputs: the numbers behind the proposal set (HOST-mode layout) and the centre seeds
+    o.noise = torch.empty((N, 6, n_prop), dtype=f32, device=dev) if want_noise else None
+    o.yaw_idx = torch.empty((N, n_prop), dtype=i16, device=dev) if (want_noise and yaw_tab is not None) else None
+    o.seeds = torch.empty((N, 3, n_prop), dtype=f32, device=dev) if want_seeds else None
+    a.out_noise, a.out_yaw_idx, a.out_seeds = L.ptr(o.noise), L.ptr(o.yaw_idx), L.ptr(o.seeds)
     L.check(L.lib().tdod_propose_score_select(C.byref(a), L.stream_ptr()))
     return o

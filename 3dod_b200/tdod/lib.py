@@ -33,6 +33,7 @@ class PssArgs(C.Structure):
         ("cluster_size", C.c_int32), ("propose_only", C.c_int32),
         ("centre_mode", C.c_int32), ("dims_mode", C.c_int32), ("im_w", C.c_int32), ("im_h", C.c_int32),
         ("aux", C.c_void_p),
+        ("out_noise", C.c_void_p), ("out_yaw_idx", C.c_void_p), ("out_seeds", C.c_void_p),
     ]
 
 
@@ -54,6 +55,7 @@ SIGNATURES = {
     "tdod_score_corners": (_I, [_P, _I, _P, _L, _P, _P]),
     "tdod_score_segmentation": (_I, [_P, _I, _I, _P, _L, _I, _P, _P]),
     "tdod_score_point_cloud": (_I, [_P, _I, _L, _P, _L, _P, _P]),
+    "tdod_box3d_iou": (_I, [_P, _P, _L, _L, _P, _P, _P]),
     "tdod_backproject": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P]),
     "tdod_ransac_workspace_bytes": (_L, [_I, _I, _I]),
     "tdod_ransac_plane": (_I, [_P, _I, _P, _I, _L, _P, _U64, _L, _I, _D, _P, _P, _P, _P, _P, _P, _L, _P]),

@@ -24,12 +24,18 @@ class FrameBatch:
 
     depth [F,H,W] f32 · ground [F,H,W] u8/bool or None · K [F,3,3] f32 · obj_off [F+1] (python list / CPU tensor)
     boxes [N,4] f32 xyxy · prior_mean/prior_std [N,3] f32 (w,h,l) · obj_frame [N] i32 · masks [N,H,W] u8/bool"""
-    __slots__ = ("depth", "ground", "K", "boxes", "prior_mean", "prior_std", "obj_frame", "masks", "frame_ids")
+    __slots__ = ("depth", "ground", "K", "boxes", "prior_mean", "prior_std", "obj_frame", "masks", "frame_ids",
+                 "has_ground")
 
-    def __init__(self, depth, ground, K, boxes, prior_mean, prior_std, obj_frame, masks, frame_ids=None):
+    def __init__(self, depth, ground, K, boxes, prior_mean, prior_std, obj_frame, masks, frame_ids=None,
+                 has_ground=None):
         self.depth, self.ground, self.K = depth, ground, K
         self.boxes, self.prior_mean, self.prior_std = boxes, prior_mean, prior_std
         self.obj_frame, self.masks, self.frame_ids = obj_frame, masks, frame_ids
+        # per-frame python bools, or None = every frame has a ground map (when `ground` is not None).  A frame without one
+        # carries an all-ones map: `ground > 0` then selects every strided point, which is what the reference fits the plane
+        # on when ground_maps is None (roi_heads.py:358-371, dataset_mapper.py:146)
+        self.has_ground = has_ground
 
     @property
     def n_frames(self):
@@ -46,12 +52,12 @@ class FrameBatch:
     def to(self, device, non_blocking=False):
         mv = lambda t: None if t is None else t.to(device, non_blocking=non_blocking)
         return FrameBatch(mv(self.depth), mv(self.ground), mv(self.K), mv(self.boxes), mv(self.prior_mean),
-                          mv(self.prior_std), mv(self.obj_frame), mv(self.masks), self.frame_ids)
+                          mv(self.prior_std), mv(self.obj_frame), mv(self.masks), self.frame_ids, self.has_ground)
 
     def pin(self):
         pm = lambda t: None if t is None else t.pin_memory()
         return FrameBatch(pm(self.depth), pm(self.ground), pm(self.K), pm(self.boxes), pm(self.prior_mean),
-                          pm(self.prior_std), pm(self.obj_frame), pm(self.masks), self.frame_ids)
+                          pm(self.prior_std), pm(self.obj_frame), pm(self.masks), self.frame_ids, self.has_ground)
 
     def input_bytes(self):
         ts = (self.depth, self.ground, self.K, self.boxes, self.prior_mean, self.prior_std, self.obj_frame, self.masks)
@@ -67,10 +73,15 @@ class FrameBatch:
         masks = None
         if frames[0].masks is not None:
             masks = torch.cat([f.masks for f in frames if f.n_obj() > 0]).to(dev)
-        ground = None if frames[0].ground is None else torch.stack([f.ground for f in frames]).to(dev)
+        has = [f.ground is not None for f in frames]
+        ground, has_ground = None, None
+        if any(has):
+            proto = next(f.ground for f in frames if f.ground is not None)
+            ground = torch.stack([f.ground if f.ground is not None else torch.ones_like(proto) for f in frames]).to(dev)
+            has_ground = None if all(has) else has
         return FrameBatch(torch.stack([f.depth for f in frames]).to(dev), ground,
                           torch.stack([f.K for f in frames]).to(dev), cat("boxes"), cat("prior_mean"),
-                          cat("prior_std"), obj_frame, masks, [f.frame_id for f in frames])
+                          cat("prior_std"), obj_frame, masks, [f.frame_id for f in frames], has_ground)
 
 
 class Selection:
@@ -156,7 +167,8 @@ def _select_split(batch, n_prop, seed, yaw_tab, side, main, obj_id_base, cluster
 
 def select(batch, n_prop, seed=0, noise=None, yaw_idx=None, rot=None, sample_ids=None, use_ground=True,
            ransac_iters=1000, ransac_thresh=0.05, flavour=L.BACKPROJECT_NUMPY, obj_id_base=0, frame_id_base=0,
-           return_all=False, cluster_size=0, overlap=True, marks=None, iou_boxes=None, splits=None):
+           return_all=False, cluster_size=0, overlap=True, marks=None, iou_boxes=None, splits=None, want_noise=False,
+           want_seeds=False):
     """Mode A (roi_heads.py:493-505) for every object of a device-resident batch.  Throughput RNG (in-kernel
     Philox keyed by global object id) unless `noise` (+ `yaw_idx` / `rot`) hands in host-drawn numbers.
     Launches only; does not synchronise.
@@ -176,7 +188,9 @@ def select(batch, n_prop, seed=0, noise=None, yaw_idx=None, rot=None, sample_ids
             ev.record(stream)
             marks[name] = ev
 
-    with_plane = use_ground and batch.ground is not None
+    # roi_heads.py:358-376: the plane is fitted whether or not the frame has a ground map (all strided points when it has
+    # none) and its normal always reaches `propose`; use_ground=False is the ablation without a normal (random rotations)
+    with_plane = bool(use_ground)
     side = _side_stream(batch.device) if (with_plane and overlap) else main
     if with_plane:
         if side is not main:
@@ -213,10 +227,10 @@ def select(batch, n_prop, seed=0, noise=None, yaw_idx=None, rot=None, sample_ids
                                  batch.obj_frame, s.rects, s.has_rect, n_prop, yaw_tab=yaw_tab, noise=noise,
                                  yaw_idx=yaw_idx, rot=rot, seed=None if noise is not None else seed,
                                  obj_id_base=obj_id_base, return_all=return_all, cluster_size=cluster_size,
-                                 iou_boxes=iou_boxes)
+                                 iou_boxes=iou_boxes, want_noise=want_noise, want_seeds=want_seeds)
     mark("kc1", main)
     s.best_idx, s.best_score, s.best_cube, s.best_box = o.best_idx, o.best_score, o.best_cube, o.best_box
-    s.all = o if return_all else None
+    s.all = o if (return_all or want_noise or want_seeds) else None
     return s
 
 
@@ -314,7 +328,7 @@ class Pipeline:
                 p[:, 20] = s.best_idx.to(f32)
                 out[o0:o1].copy_(p, non_blocking=True)
                 sl["done"].record(self.compute_stream)
-            self.launches += LAUNCHES_PER_SELECT if (self.use_ground and ground_h is not None) else LAUNCHES_PER_SELECT_NO_GROUND
+            self.launches += LAUNCHES_PER_SELECT if self.use_ground else LAUNCHES_PER_SELECT_NO_GROUND
             self.d2h_bytes += no * 21 * 4
         self.compute_stream.synchronize()
         return out

@@ -17,14 +17,16 @@ import torch
 from . import api, pipeline
 
 
-def forward_pseudo(batch, n_prop, seed=0, iou_boxes=None, box_from_object0=True, obj_id_base=0, frame_id_base=0, **kw):
+def forward_pseudo(batch, n_prop, seed=0, iou_boxes=None, box_from_object0=False, obj_id_base=0, frame_id_base=0, **kw):
     """batch: pipeline.FrameBatch on the device.  Returns (fields, selection) where fields is a dict of device tensors
     over all N objects: pred_boxes [N,4], scores [N], pred_bbox3D [N,8,3], pred_center_cam [N,3], pred_dimensions [N,3],
     pred_pose [N,3,3], pred_center_2D [N,2] (roi_heads.py:480-487).
 
     iou_boxes: [N,4] boxes the IoU term is scored against (the reference projects the GT cube, :466); default = the
     2D boxes.  box_from_object0 reproduces the reference's quirk that the winner's 2D box is read from the proposals of
-    the frame's FIRST object at the winning index (`pred_boxes[0][highest_score]`, :476); False returns the winner's own."""
+    the frame's FIRST object at the winning index (`pred_boxes[0][highest_score]`, :476) -- it needs every proposal's
+    box in HBM (return_all); the default False returns the winner's own box.  Neither reaches the pseudo-GT file: its
+    `bbox2D_proj` is the GT 2D box (`write_frames`)."""
     need_all = bool(box_from_object0)
     sel = pipeline.select(batch, n_prop, seed=seed, obj_id_base=obj_id_base, frame_id_base=frame_id_base,
                           return_all=need_all, iou_boxes=iou_boxes, **kw)
@@ -119,18 +121,54 @@ class PseudoGTWriter:
         return doc
 
 
-def write_frames(writer, fields, obj_off, frame_meta, class_ids, class_names, dataset_id=12):
+def postprocess_boxes(gt_boxes, net_hw, out_hw):
+    """What tools/eval_boxes.py:637-640 does to the GT 2D boxes before they are written as `bbox2D_proj`:
+    GeneralizedRCNN._postprocess -> detectron2 detector_postprocess rescales them from the network resolution
+    net_hw = (h, w) to the original image size out_hw = (height, width) in fp32 (x *= width / w, y *= height / h),
+    clips them to the image and flags boxes that lost their area (detectron2 drops those).
+    gt_boxes [n,4] (any device) -> (boxes [n,4] fp32, keep [n] bool)"""
+    b = gt_boxes.detach().to(torch.float32).clone()
+    out_h, out_w = float(out_hw[0]), float(out_hw[1])
+    b[:, 0::2] *= out_w / float(net_hw[1])
+    b[:, 1::2] *= out_h / float(net_hw[0])
+    b[:, 0::2] = b[:, 0::2].clamp(min=0, max=out_w)
+    b[:, 1::2] = b[:, 1::2].clamp(min=0, max=out_h)
+    keep = ((b[:, 2] - b[:, 0]) > 0) & ((b[:, 3] - b[:, 1]) > 0)
+    return b, keep
+
+
+def write_frames(writer, fields, obj_off, frame_meta, class_ids, class_names, gt_boxes=None, net_hw=None, dataset_id=12,
+                 empty_boxes="reference"):
     """fields: forward_pseudo's dict (device tensors, N objects); obj_off: CSR [F+1]; frame_meta: list of
     dict(id, width, height, file_path, K) per frame; class_ids / class_names: per-object category id / name.
+
+    gt_boxes [N,4] + net_hw = (h, w) of the network input: `bbox2D_proj` is the GROUND-TRUTH 2D box rescaled to the
+    original image size and clipped (tools/eval_boxes.py:637-640, written at :648) -- the training loader reads it as the
+    2D target when bbox2D_tight == -1 (cubercnn/data/datasets.py:108-109) -- NOT the winner's projected box.
+    empty_boxes: a GT box that loses its area in the clip is dropped by detectron2, after which the reference's
+    `zip(bboxes, gt_classes, centers, ...)` (:647) pairs the remaining boxes with the FIRST len(bboxes) cubes;
+    "reference" reproduces that, "skip" drops the object's whole record instead.
     One device->host copy per field for the whole batch, then pure Python."""
-    host = {k: v.detach().cpu().tolist() for k, v in fields.items()}
+    if gt_boxes is None or net_hw is None:
+        raise ValueError("write_frames needs gt_boxes [N,4] and net_hw=(h, w): bbox2D_proj is the rescaled GT 2D box "
+                         "(tools/eval_boxes.py:637-640), not the predicted one")
+    if empty_boxes not in ("reference", "skip"):
+        raise ValueError("empty_boxes must be 'reference' or 'skip'")
+    host = {k: v.detach().cpu().tolist() for k, v in fields.items() if k != "pred_boxes"}
     done = set(writer.done_images)
+    gt_boxes = gt_boxes.detach().cpu()
     for f, meta in enumerate(frame_meta):
         if meta["id"] in done:
             continue
+        o0, o1 = obj_off[f], obj_off[f + 1]
+        bx, keep = postprocess_boxes(gt_boxes[o0:o1], net_hw, (meta["height"], meta["width"]))
+        if empty_boxes == "reference":
+            pairs = list(zip(bx[keep].tolist(), range(o0, o1)))          # zip truncates to the surviving boxes
+        else:
+            pairs = [(bx[j].tolist(), o0 + j) for j in range(o1 - o0) if bool(keep[j])]
         anns = []
-        for i in range(obj_off[f], obj_off[f + 1]):
-            anns.append(annotation(None, meta["id"], dataset_id, class_ids[i], class_names[i], host["pred_boxes"][i],
+        for box, i in pairs:
+            anns.append(annotation(None, meta["id"], dataset_id, class_ids[i], class_names[i], box,
                                    host["pred_center_cam"][i], host["pred_dimensions"][i], host["pred_bbox3D"][i],
                                    host["pred_pose"][i]))
         writer.add_frame(image_record(meta["id"], meta["width"], meta["height"], meta["file_path"], meta["K"]), anns)

@@ -103,6 +103,13 @@ int tdod_score_segmentation(const uint8_t* mask, int H, int W, const float* corn
 int tdod_score_point_cloud(const void* points, int points_f64, int64_t P, const float* cubes, int64_t n,
                            int64_t* out, void* stream);
 
+/* iou_3d (ProposalNetwork/utils/utils.py:194-210 -> pytorch3d.ops.box3d_overlap; used by the MABO branch,
+ * cubercnn/modeling/roi_heads/roi_heads.py:518,526): exact IoU3D of oriented boxes given by their 8 corners in the
+ * vertex order of cubercnn/util/math_util.py:178-207.  gt_corners [G,8,3], corners [G,n,8,3] -> out_iou [G,n]
+ * (box g against its n proposals); out_vol [G,n] intersection volumes or NULL. */
+int tdod_box3d_iou(const float* gt_corners, const float* corners, int64_t G, int64_t n, float* out_iou, float* out_vol,
+                   void* stream);
+
 /* ---- plane ---------------------------------------------------------------------------------------------- */
 
 /* Depth -> strided point cloud (roi_heads.py:346-371 / :1084-1112), row-major compaction.
@@ -183,6 +190,12 @@ typedef struct tdod_pss_args {
     int32_t dims_mode;         /* TDOD_DIMS_* */
     int32_t im_w, im_h;        /* im_shape of pixel_to_normalised_space (PATCH modes); 0 -> W, H */
     const float* aux;          /* [n_obj,2]: DIMS_ASPECT (ratio_h, ratio_l); NULL otherwise */
+    /* replay / audit outputs (each may be NULL): the numbers behind the proposal set, in HOST-mode layout, so that a PHILOX
+     * run can be fed back through HOST mode (and through the oracle's cubes_from_noise) bit for bit */
+    float* out_noise;          /* [n_obj,6,n_prop]: accepted standard normals (or U[0,1) draws) for w,h,l,x,y,z */
+    int16_t* out_yaw_idx;      /* [n_obj,n_prop]: yaw bin (with yaw_table) */
+    float* out_seeds;          /* [n_obj,3,n_prop]: the centre seeds x, y, z_tmp + l/2 (proposals.py:366-375, :394) whose
+                                  median / std parameterise the centre draws */
 } tdod_pss_args;
 
 /* propose (proposals.py:338-424) + cubes_to_box + score_iou + score_dimensions + score_corners +

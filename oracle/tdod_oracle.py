@@ -48,7 +48,7 @@ def versions():
 def linspace_rows(lo, hi, n):
     """utils.py:170-177 vectorized_linspace: arange(n) * ((hi-lo)/(n-1)) + lo, fp32, per row."""
     step = (hi - lo) / (n - 1)
-    ramp = torch.arange(0, n, dtype=lo.dtype)
+    ramp = torch.arange(0, n, dtype=lo.dtype, device=lo.device)   # device-agnostic: the GPU tests run this on CUDA tensors
     return ramp[None, :] * step[:, None] + lo[:, None]
 
 
@@ -150,7 +150,7 @@ def cubes_from_noise(boxes, depth, prior_mean, prior_std, K, n, noise, normal=No
     y = sc(noise[4], cy[0] * torch.median(y0, dim=1).values + cy[1], torch.std(y0, dim=1) * 0.8)
     zt = z0 + l / 2
     z = sc(noise[5], cz[0] * torch.median(zt, dim=1).values + cz[1], torch.std(zt, dim=1) * 1.2)
-    R = rot if normal is None else yaw_table(normal)[yaw_idx.long()]
+    R = rot if normal is None else yaw_table(normal.cpu())[yaw_idx.long().cpu()].to(boxes.device)
     xyzwhl = torch.stack([x, y, z, w, h, l], 2)
     return torch.cat((xyzwhl, R.flatten(start_dim=2)), dim=2).to(torch.float32)          # spaces.py:143
 
@@ -309,7 +309,8 @@ def cube_corners(cubes):
     c = cubes[..., 0:3]
     w, h, l = cubes[..., 3], cubes[..., 4], cubes[..., 5]
     R = cubes[..., 6:15].reshape(cubes.shape[:-1] + (3, 3))
-    local = torch.stack([_SX * (l / 2)[..., None], _SY * (h / 2)[..., None], _SZ * (w / 2)[..., None]], -2)
+    sx, sy, sz = _SX.to(cubes.device), _SY.to(cubes.device), _SZ.to(cubes.device)
+    local = torch.stack([sx * (l / 2)[..., None], sy * (h / 2)[..., None], sz * (w / 2)[..., None]], -2)
     v = R @ local                                  # [...,3,8]
     v = v + c[..., :, None]
     return v.transpose(-1, -2)
@@ -342,7 +343,7 @@ def iou_score(ref_box, boxes):
     wh = torch.min(ref_box[None, 2:], boxes[:, 2:]) - torch.max(ref_box[None, :2], boxes[:, :2])
     wh = wh.clamp(min=0)
     inter = wh.prod(dim=1)
-    return torch.where(inter > 0, inter / (a1 + a2 - inter), torch.zeros(1, dtype=inter.dtype))
+    return torch.where(inter > 0, inter / (a1 + a2 - inter), torch.zeros(1, dtype=inter.dtype, device=inter.device))
 
 
 def dims_score(prior_mean, prior_std, dims, ref_box, boxes):
@@ -534,3 +535,79 @@ def rectify_normal(nv):
     if nv[1] < 0:
         nv = nv * -1
     return nv
+
+
+# ---- IoU3D / MABO ordering (MABO branch, roi_heads.py:277-281, :518-582) ----------------------------------------------
+_FACES = ((0, 1, 2, 3), (4, 5, 6, 7), (0, 1, 5, 4), (1, 2, 6, 5), (2, 3, 7, 6), (3, 0, 4, 7))  # math_util.py:178-207
+
+
+def _box_halfspaces(v):
+    """8 corners [8,3] (fp64) -> rows [a,b,c,d] with a x + b y + c z + d <= 0 inside (outward unit normals)"""
+    c = v.mean(0)
+    rows = []
+    for f in _FACES:
+        p0 = v[f[0]]
+        n = np.cross(v[f[1]] - p0, v[f[3]] - p0)
+        n = n / np.linalg.norm(n)
+        if n @ (c - p0) > 0:
+            n = -n
+        rows.append([n[0], n[1], n[2], -(n @ p0)])
+    return np.array(rows)
+
+
+def box3d_iou_np(gt_corners, corners):
+    """iou_3d (utils.py:194-210): IoU3D of one box [8,3] against n boxes [n,8,3].  The reference calls
+    pytorch3d.ops.box3d_overlap (absent here: unpinned third-party, exact convex intersection of two boxes); this is
+    the same quantity in fp64 through SciPy's half-space intersection (Qhull) -- pinned by the reference's known answer
+    ProposalNetwork/utils/tests/test_iou.py:3-27 (0.9944)."""
+    from scipy.optimize import linprog
+    from scipy.spatial import ConvexHull, HalfspaceIntersection
+    g = np.asarray(gt_corners, dtype=np.float64)
+    P = np.asarray(corners, dtype=np.float64)
+    vol_g = abs(np.dot(g[1] - g[0], np.cross(g[3] - g[0], g[4] - g[0])))
+    hg = _box_halfspaces(g)
+    out = np.zeros(len(P))
+    for i, b in enumerate(P):
+        vol_b = abs(np.dot(b[1] - b[0], np.cross(b[3] - b[0], b[4] - b[0])))
+        hs = np.vstack([hg, _box_halfspaces(b)])
+        # Chebyshev centre: max r s.t. n.x + d + r <= 0
+        res = linprog([0, 0, 0, -1], A_ub=np.hstack([hs[:, :3], np.ones((12, 1))]), b_ub=-hs[:, 3],
+                      bounds=[(None, None)] * 3 + [(0, None)])
+        vol = 0.0
+        if res.status == 0 and res.x[3] > 1e-9:
+            try:
+                vol = ConvexHull(HalfspaceIntersection(hs, res.x[:3]).intersections).volume
+            except Exception:
+                vol = 0.0
+        out[i] = vol / (vol_g + vol_b - vol)
+    return out
+
+
+def accumulate_scores(scores, iou3d):
+    """roi_heads.py:277-281: IoU3D reordered by descending score, then its running maximum"""
+    idx = np.argsort(scores)[::-1]
+    return np.maximum.accumulate(np.array([iou3d[i] for i in idx]))
+
+
+# ---- pseudo-GT record (tools/eval_boxes.py:637-655) ---------------------------------------------------------------
+def postprocess_boxes(boxes, net_hw, out_h, out_w):
+    """GeneralizedRCNN._postprocess -> detectron2 detector_postprocess as tools/eval_boxes.py:637-640 applies it to the
+    GT boxes (detectron2 is absent here: public behaviour restated): x *= out_w / net_w, y *= out_h / net_h in fp32,
+    clip to [0, out_w] x [0, out_h], then boxes with no positive area are DROPPED (`results[output_boxes.nonempty()]`)."""
+    b = _postprocess_scaled(boxes, net_hw, out_h, out_w)
+    return b[postprocess_keep(boxes, net_hw, out_h, out_w)]
+
+
+def _postprocess_scaled(boxes, net_hw, out_h, out_w):
+    b = torch.as_tensor(boxes, dtype=torch.float32).clone()
+    sx, sy = out_w / net_hw[1], out_h / net_hw[0]
+    b[:, 0::2] *= sx
+    b[:, 1::2] *= sy
+    b[:, 0].clamp_(min=0, max=out_w); b[:, 2].clamp_(min=0, max=out_w)
+    b[:, 1].clamp_(min=0, max=out_h); b[:, 3].clamp_(min=0, max=out_h)
+    return b
+
+
+def postprocess_keep(boxes, net_hw, out_h, out_w):
+    b = _postprocess_scaled(boxes, net_hw, out_h, out_w)
+    return ((b[:, 2] - b[:, 0]) > 0) & ((b[:, 3] - b[:, 1]) > 0)

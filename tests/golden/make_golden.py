@@ -349,8 +349,63 @@ def make_depth_losses(ver):
     print("z_box", out["z_box"][:8], "depth_range", out["depth_range"][:8])
 
 
+def make_pseudo_record(ver):
+    """one image record + its annotation records built by the UNMODIFIED record-building statements of
+    tools/eval_boxes.py (the `img = {...}` assignment :646 and the annotation loop :647-655), exec'd from the file where
+    they lie, on synthetic `instances` / `input_` stand-ins.  `bboxes` (:637-640) comes from
+    GeneralizedRCNN._postprocess -> detectron2's detector_postprocess (absent here: public behaviour restated in
+    oracle/tdod_oracle.py::postprocess_boxes)."""
+    import ast
+    import json
+    import textwrap
+    import types
+    path = os.path.join(ref_import.REF_ROOT, "tools/eval_boxes.py")
+    src = open(path).read()
+    tree = ast.parse(src)
+    img_stmt = loop_stmt = None
+    for node in ast.walk(tree):
+        if isinstance(node, ast.Assign) and isinstance(node.targets[0], ast.Name) and node.targets[0].id == "img" \
+                and isinstance(node.value, ast.Dict) and img_stmt is None and node.lineno > 600:
+            img_stmt = node
+        if isinstance(node, ast.For) and node.lineno > 600 and any(
+                isinstance(b, ast.Assign) and getattr(b.targets[0], "id", "") == "ann" for b in node.body):
+            loop_stmt = node
+    assert img_stmt is not None and loop_stmt is not None
+    code = textwrap.dedent(ast.get_source_segment(src, img_stmt)) + "\n" + textwrap.dedent(
+        " " * loop_stmt.col_offset + ast.get_source_segment(src, loop_stmt))
+    g = torch.Generator().manual_seed(5)
+    n = 4
+    net_h, net_w, H0, W0 = 512, 704, 530, 730                       # network resolution / original image size
+    gt = torch.tensor([[10.5, 20.25, 300.0, 400.0], [-4.0, 30.0, 720.0, 520.0], [100.0, 100.0, 100.0, 180.0],
+                       [50.0, 60.0, 200.0, 260.0]])
+    gt_classes = torch.tensor([3, 17, 5, 9])
+    cubes = torch.rand(n, 15, generator=g)
+    corners = torch.rand(n, 8, 3, generator=g)
+    inst = types.SimpleNamespace(pred_center_cam=cubes[:, :3], pred_dimensions=cubes[:, 3:6], pred_bbox3D=corners,
+                                 pred_pose=cubes[:, 6:].reshape(n, 3, 3))
+    input_ = {"image_id": 4711, "width": W0, "height": H0, "file_name": "datasets/SUNRGBD/kv2/x/image/0001.jpg",
+              "K": [[657.0, 0.0, 365.0], [0.0, 657.0, 265.0], [0.0, 0.0, 1.0]],
+              "instances": types.SimpleNamespace(gt_classes=gt_classes)}
+    thing = ["class%02d" % k for k in range(50)]
+    c2id = {k: 100 + k for k in range(50)}
+    util = types.SimpleNamespace(MetadataCatalog=types.SimpleNamespace(get=lambda name: types.SimpleNamespace(thing_classes=thing)))
+    bboxes = O.postprocess_boxes(gt, (net_h, net_w), H0, W0)        # all four kept here (the empty one is dropped there)
+    keep = O.postprocess_keep(gt, (net_h, net_w), H0, W0)
+    ns = {"input_": input_, "img_id": input_["image_id"], "instances": inst, "bboxes": bboxes, "util": util,
+          "contiguous_to_id": c2id, "global_id": 1, "idd": 12, "annotations": []}
+    exec(code, ns)
+    doc = {"versions": str(ver), "net_hw": [net_h, net_w], "gt_boxes": gt.tolist(), "gt_classes": gt_classes.tolist(),
+           "keep": keep.tolist(), "cubes": cubes.tolist(), "corners": corners.tolist(), "thing_classes": thing,
+           "input": {k: v for k, v in input_.items() if k != "instances"}, "image": ns["img"],
+           "annotations": ns["annotations"], "exec_lines": [img_stmt.lineno, loop_stmt.end_lineno]}
+    json.dump(doc, open(os.path.join(HERE, "pseudo_record.json"), "w"), indent=1)
+    print("pseudo_record.json", len(ns["annotations"]), "annotations; image", ns["img"])
+
+
 if __name__ == "__main__":
-    if len(sys.argv) > 1 and sys.argv[1] == "depth_losses":
+    if len(sys.argv) > 1 and sys.argv[1] == "pseudo_record":
+        make_pseudo_record(np.array(str(O.versions())))
+    elif len(sys.argv) > 1 and sys.argv[1] == "depth_losses":
         make_depth_losses(np.array(str(O.versions())))
     elif len(sys.argv) > 1 and sys.argv[1] == "variants":
         make_variants(np.array(str(O.versions())))

@@ -34,7 +34,8 @@ def _run(path, frames, resume, stop_after=None):
             w.flush()
             return None
         n = 2 + fid % 3
-        PG.write_frames(w, _fake_fields(n, fid), [0, n], [_meta(fid)], [18] * n, ["chair"] * n)
+        gt = torch.tensor([[10.0 + k, 20.0, 200.0 + k, 300.0] for k in range(n)])
+        PG.write_frames(w, _fake_fields(n, fid), [0, n], [_meta(fid)], [18] * n, ["chair"] * n, gt_boxes=gt, net_hw=(530, 730))
     return w.finalize()
 
 
@@ -64,6 +65,36 @@ def test_resume_after_interruption_gives_the_same_document(tmp_path):
     assert resumed == whole
 
 
+def test_records_equal_the_reference_built_records(tmp_path):
+    """tests/golden/pseudo_record.json holds the image + annotation records built by the UNMODIFIED statements of
+    tools/eval_boxes.py:645-655 (make_golden.py pseudo_record): bbox2D_proj is the GT 2D box after
+    GeneralizedRCNN._postprocess (:637-640), a box emptied by the clip is dropped and the zip truncates"""
+    ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    g = json.load(open(os.path.join(ROOT, "tests", "golden", "pseudo_record.json")))
+    cubes = torch.tensor(g["cubes"])
+    n = cubes.shape[0]
+    fields = dict(pred_boxes=torch.zeros(n, 4), scores=torch.zeros(n), pred_bbox3D=torch.tensor(g["corners"]),
+                  pred_center_cam=cubes[:, :3], pred_dimensions=cubes[:, 3:6], pred_pose=cubes[:, 6:].reshape(n, 3, 3),
+                  pred_center_2D=torch.zeros(n, 2))
+    inp = g["input"]
+    meta = dict(id=inp["image_id"], width=inp["width"], height=inp["height"], file_path=inp["file_name"][9:], K=inp["K"])
+    cls = g["gt_classes"]
+    w = PG.PseudoGTWriter(str(tmp_path / "p.json"), {}, [], resume=False)
+    PG.write_frames(w, fields, [0, n], [meta], [100 + c for c in cls], [g["thing_classes"][c] for c in cls],
+                    gt_boxes=torch.tensor(g["gt_boxes"]), net_hw=tuple(g["net_hw"]))
+    doc = w.finalize()
+    assert doc["images"] == [g["image"]]
+    assert len(doc["annotations"]) == len(g["annotations"]) == 3          # one GT box is emptied by the clip
+    for a, b in zip(doc["annotations"], g["annotations"]):
+        assert list(a) == list(b)
+        assert a == b, (a, b)
+
+
+def test_write_frames_refuses_to_write_predicted_boxes():
+    with pytest.raises(ValueError):
+        PG.write_frames(None, _fake_fields(2, 0), [0, 2], [_meta(0)], [18, 18], ["chair"] * 2)
+
+
 @pytest.mark.gpu
 def test_batched_forward_equals_per_object_path():
     """forward_pseudo over several frames == roi_heads.py:453-489 frame by frame (same Philox keys), including the
@@ -73,7 +104,7 @@ def test_batched_forward_equals_per_object_path():
     frames = synth.make_frames("C2", range(3))
     batch = pipeline.FrameBatch.from_frames(frames, d)
     off = np.cumsum([0] + [f.n_obj() for f in frames]).tolist()
-    fields, sel = PG.forward_pseudo(batch, 1000, seed=4)
+    fields, sel = PG.forward_pseudo(batch, 1000, seed=4, box_from_object0=True)
     own, _ = PG.forward_pseudo(batch, 1000, seed=4, box_from_object0=False)
     torch.cuda.synchronize()
     assert torch.equal(own["pred_center_cam"], fields["pred_center_cam"])
