@@ -5,8 +5,11 @@
 // answer (ProposalNetwork/utils/tests/test_iou.py:3-27 -> 0.9944) pins it.
 //
 // Method (not pytorch3d's triangle clipping): the intersection of two boxes is the convex polytope bounded by their
-// 12 face planes.  Each of its faces is one box face clipped (Sutherland-Hodgman) by the six half-spaces of the OTHER
-// box, and V = 1/3 * sum_f (d_f - n_f . c) * area_f for any reference point c.  One lane per (pair, face): 16 lanes per
+// 12 face planes.  Each of its faces is a polygon in one of those planes: a quad spanning the box face generously,
+// clipped (Sutherland-Hodgman) by the four neighbouring half-spaces of its own box and the six of the OTHER box --
+// so the result depends on the planes alone and stays consistent when the 8 corners are not an exact cuboid (the
+// reference's known-answer vector has corners rounded to 1e-4) -- and V = 1/3 * sum_f (d_f - n_f . c) * area_f for any
+// reference point c.  One lane per (pair, face): 16 lanes per
 // pair (12 active), reduced with shuffles.  Coplanar faces: faces of box 1 are clipped inclusively, faces of box 2
 // strictly, so a shared face is counted once; c is the mean of the clipped polygons' vertices, which lies in the
 // intersection, so a flat (touching) intersection gives exactly 0.
@@ -47,7 +50,8 @@ __device__ __forceinline__ void box_planes(const V3* v, Planes& P, float& vol) {
     vol = fabsf(dot(e1, cross(e2, e3)));
 }
 
-constexpr int kMaxPoly = 12;
+constexpr int kMaxPoly = 16;
+__constant__ int kOpp[6] = {1, 0, 4, 5, 2, 3};   // the face opposite to face f
 
 // one pair per 16 lanes: gt box g against proposal i
 __global__ void __launch_bounds__(256) box3d_iou_kernel(const float* __restrict__ gt, const float* __restrict__ pr,
@@ -87,13 +91,27 @@ __global__ void __launch_bounds__(256) box3d_iou_kernel(const float* __restrict_
         const V3* own = first ? a : b;
         const Planes& CP = first ? PB : PA;
         const Planes& OP = first ? PA : PB;
-        const float tol = first ? eps : -eps;
+        const float tol2 = first ? eps : -eps;
         V3 poly[kMaxPoly], tmp[kMaxPoly];
         int m = 4;
-        for (int k = 0; k < 4; ++k) poly[k] = own[kFace[f][k]];
-        for (int c = 0; c < 6 && m > 0; ++c) {
-            const V3 nn = CP.n[c];
-            const float dd = CP.d[c];
+        {   // the face's corners dropped onto its plane and pushed out to twice their distance from their mean
+            const V3 nf = OP.n[f];
+            V3 cen = {0.f, 0.f, 0.f};
+            for (int k = 0; k < 4; ++k) {
+                const V3 p = own[kFace[f][k]];
+                const float h = dot(nf, p) - OP.d[f];
+                poly[k] = {p.x - h * nf.x, p.y - h * nf.y, p.z - h * nf.z};
+                cen.x += 0.25f * poly[k].x; cen.y += 0.25f * poly[k].y; cen.z += 0.25f * poly[k].z;
+            }
+            for (int k = 0; k < 4; ++k)
+                poly[k] = {2.f * poly[k].x - cen.x, 2.f * poly[k].y - cen.y, 2.f * poly[k].z - cen.z};
+        }
+        // clips 0..5: the own box's planes (the face's own and the opposite one are skipped), 6..11: the other box's
+        for (int c = 0; c < 12 && m > 0; ++c) {
+            if (c < 6 && (c == f || c == kOpp[f])) continue;
+            const V3 nn = c < 6 ? OP.n[c] : CP.n[c - 6];
+            const float dd = c < 6 ? OP.d[c] : CP.d[c - 6];
+            const float tol = c < 6 ? eps : tol2;
             int mo = 0;
             V3 prev = poly[m - 1];
             float dp = dot(nn, prev) - dd;

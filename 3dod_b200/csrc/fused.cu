@@ -30,6 +30,7 @@ struct Mail {               // per-CTA mailbox read by every CTA of the cluster 
     double m2[3];           // sum of squared deviations
     float fb[8];            // fallback rectangle: min/max over proposals of vertex 0 and vertex 1 (x, y)
     float maxdiff, maxd;
+    float sdv[3];           // std_mode TORCH_CUDA: the three standard deviations, published by rank 0
     int nanflag[3];
     float am_v;
     int am_i;
@@ -424,6 +425,28 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
         for (int w2 = 0; w2 < kWarps; ++w2) s += sh.red_d[w2][tid];
         sh.mail.m2[tid] = s;
     }
+    if (a.std_mode == TDOD_STD_TORCH_CUDA && rank == 0) {
+        // torch.std as torch's CUDA kernel rounds it (tdod_device.cuh, namespace tstd): the launch shape depends on how
+        // many objects the frame's `propose` call holds and the vector-load alignment on the object's row in it
+        if (tid == 0) {
+            int before = 0, after = 0;
+            if (a.obj_frame) {
+                while (obj - before - 1 >= 0 && a.obj_frame[obj - before - 1] == c.frame) ++before;
+                while (obj + after + 1 < a.n_obj && a.obj_frame[obj + after + 1] == c.frame) ++after;
+            } else { before = obj; after = a.n_obj - 1 - obj; }
+            sh.red_i[0] = before + after + 1; sh.red_i[1] = before;
+        }
+        __syncthreads();
+        const tstd::Cfg cfg = tstd::config(n, sh.red_i[0]);
+        const int shift = (int)(((long long)sh.red_i[1] * n) & 1);
+        tstd::W* scr = reinterpret_cast<tstd::W*>(&sh.mail.hist[0][0][0]);   // passes 0-2 are dead cluster-wide by now
+        for (int k = 0; k < 3; ++k) {
+            float* loc = k == 0 ? s_x : (k == 1 ? s_y : s_z);
+            const float sd = tstd::block_std([&](int i) { return *cl.remote(loc + (i % n_loc), i / n_loc); }, n, shift, cfg,
+                                             scr, tid, kThreads);
+            if (tid == 0) sh.mail.sdv[k] = sd;
+        }
+    }
     cl.sync();   // (5)
     float smean[3], ssd[3];
     {
@@ -432,7 +455,8 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
         for (int k = 0; k < 3; ++k) {
             double s = 0.0;
             for (int r = 0; r < S; ++r) s += *cl.remote(&sh.mail.m2[k], r);
-            const float sd = (float)sqrt(s / (double)(n - 1));              // torch.std: unbiased
+            float sd = (float)sqrt(s / (double)(n - 1));                    // torch.std: unbiased (fp64 == torch on CPU)
+            if (a.std_mode == TDOD_STD_TORCH_CUDA) sd = *cl.remote(&sh.mail.sdv[k], 0);
             smean[k] = __fadd_rn(__fmul_rn(coef_a[k], sh.med[k]), coef_b[k]);   // lin_fun, proposals.py:16-18
             ssd[k] = __fmul_rn(sd, coef_s[k]);
         }
@@ -643,6 +667,9 @@ extern "C" int tdod_propose_score_select(const tdod_pss_args* ap, void* stream) 
     if (a.dims_mode == TDOD_DIMS_ASPECT && !a.aux) return tdod_fail(TDOD_EINVAL, "dims_mode ASPECT needs aux [n_obj,2]");
     if (a.centre_mode == TDOD_CENTRE_PATCH_Z && a.rng_mode != TDOD_RNG_HOST)
         return tdod_fail(TDOD_EINVAL, "centre_mode PATCH_Z takes its z ramp from the caller (rng_mode HOST)");
+    if (a.std_mode != TDOD_STD_EXACT && a.std_mode != TDOD_STD_TORCH_CUDA) return tdod_fail(TDOD_EINVAL, "unknown std_mode");
+    if (a.std_mode == TDOD_STD_TORCH_CUDA && !tstd::config(a.n_prop, 1).ok)
+        return tdod_fail(TDOD_ERANGE, "std_mode TORCH_CUDA: n_prop so large that torch splits the reduction over several CTAs");
     int S = a.cluster_size;
     if (S == 0) {
         // one CTA handles up to 2048 proposals comfortably; spread larger objects, and small batches, over a cluster

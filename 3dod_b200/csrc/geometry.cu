@@ -301,3 +301,27 @@ extern "C" int tdod_resize_nearest(const void* src, int elem_bytes, int F, int h
     TDOD_CHECK_LAUNCH();
     return TDOD_OK;
 }
+
+// ---- torch.std with torch's CUDA rounding (tdod_device.cuh, namespace tstd), one CTA per row ----------------------
+namespace {
+__global__ void __launch_bounds__(256) torch_std_kernel(const float* __restrict__ x, int N, int n, float* __restrict__ out) {
+    __shared__ tstd::W scr[512];
+    const int row = blockIdx.x;
+    const tstd::Cfg cfg = tstd::config(n, N);
+    const float* p = x + (size_t)row * n;
+    const int shift = (int)(((long long)row * n) & 1);
+    const float sd = tstd::block_std([&](int i) { return p[i]; }, n, shift, cfg, scr, threadIdx.x, 256);
+    if (threadIdx.x == 0) out[row] = sd;
+}
+}  // namespace
+
+extern "C" int tdod_torch_std(const float* x, int64_t N, int n, float* out, void* stream) {
+    if (N == 0) return TDOD_OK;
+    if (N < 0 || N > 0x7fffffff || n <= 0) return tdod_fail(TDOD_EINVAL, "tdod_torch_std: bad shape");
+    if (!x || !out) return tdod_fail(TDOD_EINVAL, "tdod_torch_std: a pointer is NULL");
+    if (!tstd::config(n, (int)N).ok) return tdod_fail(TDOD_ERANGE, "tdod_torch_std: torch splits this reduction over several CTAs");
+    if ((reinterpret_cast<uintptr_t>(x) & 7) != 0) return tdod_fail(TDOD_EINVAL, "tdod_torch_std: x must be 8-byte aligned (torch tensors are)");
+    torch_std_kernel<<<(unsigned)N, 256, 0, (cudaStream_t)stream>>>(x, (int)N, n, out);
+    TDOD_CHECK_LAUNCH();
+    return TDOD_OK;
+}

@@ -235,3 +235,111 @@ __device__ __forceinline__ float chamfer4x8(const float* __restrict__ rect /*[4]
 }
 
 }  // namespace tdod
+
+// ------------------------------------------------------------------------------------------
+// torch.std(x, dim=1) of a contiguous fp32 [N, n] tensor AS TORCH'S CUDA KERNEL ROUNDS IT
+// ------------------------------------------------------------------------------------------
+// On CUDA tensors -- how the reference runs in production (proposals.py:386-396 on reference_box.device) -- torch.std
+// is a Welford reduction in fp32 (at::acc_type<float, true> is float) whose rounding depends on the launch
+// configuration: which elements each thread folds in, in which order the partial results are merged.  To reproduce the
+// proposal set of that flavour bit for bit the same tree is walked here.  Restated from the installed torch 2.11
+// headers: ATen/native/cuda/Reduce.cuh (setReduceConfig :1033-1179, set_block_dimension :100-108,
+// input_vectorized_thread_reduce_impl :500-557, thread_reduce_impl :559-622, block_x_reduce :624-663, block_y_reduce
+// :665-682), ATen/native/SharedReduceOps.h WelfordOps :99-162, and std_var_kernel_impl (vt0 = 2, hence two-element
+// vector loads and two accumulators per thread).  Checked against torch.std on the GPU (tests/test_gpu_parity.py).
+namespace tstd {
+
+struct W { float mean, m2, nf; };
+
+__device__ __forceinline__ W reduce(W a, float x) {           // WelfordOps::reduce; nvcc contracts m2 + delta * new_delta
+    const float nf = a.nf + 1.f;                              // counts stay far below 2^24: float(n + 1) == nf + 1
+    const float delta = __fsub_rn(x, a.mean);
+    const float mean = __fadd_rn(a.mean, __fdiv_rn(delta, nf));
+    const float nd = __fsub_rn(x, mean);
+    W r; r.mean = mean; r.m2 = __fmaf_rn(delta, nd, a.m2); r.nf = nf;
+    return r;
+}
+__device__ __forceinline__ W combine(W a, W b) {              // WelfordOps::combine
+    if (a.nf == 0.f) return b;
+    if (b.nf == 0.f) return a;
+    const float delta = __fsub_rn(b.mean, a.mean);
+    const float cnt = __fadd_rn(a.nf, b.nf);
+    const float r = __fdiv_rn(b.nf, cnt);
+    W o;
+    o.mean = __fmaf_rn(delta, r, a.mean);
+    o.m2 = __fmaf_rn(__fmul_rn(__fmul_rn(delta, delta), a.nf), r, __fadd_rn(a.m2, b.m2));
+    o.nf = cnt;
+    return o;
+}
+
+struct Cfg { int vec, bw, Y, im1, step, ok; };
+__host__ __device__ inline int last_pow2(int x) { int p = 1; while (2 * p <= x) p *= 2; return p; }
+// launch shape torch picks for an [N, n] fp32 tensor reduced over its contiguous inner dimension
+__host__ __device__ inline Cfg config(int n, int N) {
+    Cfg c;
+    c.vec = n >= 128;
+    const int dim0 = c.vec ? n / 2 : n;
+    const int d0 = dim0 < 512 ? last_pow2(dim0 < 1 ? 1 : dim0) : 512, d1 = N < 512 ? last_pow2(N < 1 ? 1 : N) : 512;
+    int bw = d0 < 32 ? d0 : 32;
+    const int bh = d1 < 512 / bw ? d1 : 512 / bw;
+    bw = d0 < 512 / bh ? d0 : 512 / bh;
+    c.bw = bw; c.step = bw;
+    const int vpt = (n + bw - 1) / bw;
+    const int thr = bh * 16 < 256 ? bh * 16 : 256;
+    c.Y = 1; c.im1 = 0;
+    if (vpt >= thr) { c.im1 = c.step; c.step *= bh; c.Y = bh; }
+    // a reduction split over several CTAs (values_per_thread >= 256 after the warp split) is not restated
+    c.ok = !(c.Y > 1 && (n + c.step - 1) / c.step >= 256);
+    return c;
+}
+
+// All `nthreads` threads of the CTA call this.  `at(i)` returns element i of the row; `shift` is the row's misalignment
+// in elements with respect to torch's 8-byte vector loads (row_index * n odd -> 1).  scratch: bw * Y entries.
+template <typename F>
+__device__ float block_std(F at, int n, int shift, const Cfg c, W* scratch, int tid, int nthreads) {
+    const int nv = c.bw * c.Y;
+    for (int v = tid; v < nv; v += nthreads) {
+        const int x = v % c.bw, y = v / c.bw;
+        const bool tail_ok = (c.Y == 1) || y == 0;             // should_reduce_tail()
+        W a0 = {0.f, 0.f, 0.f}, a1 = {0.f, 0.f, 0.f};
+        if (c.vec) {
+            int end = n, base = 0;
+            if (shift > 0) {                                   // unaligned head: torch steps back `shift` elements
+                end += shift;
+                if (x >= shift && x < 2 && tail_ok) a0 = reduce(a0, at(x - shift));
+                end -= 2; base = 2 - shift;
+            }
+            int idx = x + y * c.im1;
+            while (idx * 2 + 1 < end) {
+                a0 = reduce(a0, at(base + 2 * idx)); a1 = reduce(a1, at(base + 2 * idx + 1));
+                idx += c.step;
+            }
+            const int tail_start = end - end % 2;
+            if (tail_ok) { const int i = tail_start + x; if (i < end) a0 = reduce(a0, at(base + i)); }
+        } else {
+            int idx = x + y * c.im1;
+            while (idx + c.step < n) { a0 = reduce(a0, at(idx)); a1 = reduce(a1, at(idx + c.step)); idx += 2 * c.step; }
+            if (idx < n) { a0 = reduce(a0, at(idx)); idx += c.step; if (idx < n) a1 = reduce(a1, at(idx)); }
+        }
+        scratch[v] = combine(a0, a1);
+    }
+    __syncthreads();
+    for (int off = c.bw >> 1; off > 0; off >>= 1) {            // block_x_reduce: shared-memory levels, then the shuffle levels
+        for (int v = tid; v < nv; v += nthreads) {
+            const int x = v % c.bw;
+            if (x < off) scratch[v] = combine(scratch[v], scratch[v + off]);
+        }
+        __syncthreads();
+    }
+    for (int off = c.Y >> 1; off > 0; off >>= 1) {             // block_y_reduce
+        for (int y = tid; y < off; y += nthreads) scratch[y * c.bw] = combine(scratch[y * c.bw], scratch[(y + off) * c.bw]);
+        __syncthreads();
+    }
+    const W r = scratch[0];
+    const float div = r.nf > 1.f ? __fsub_rn(r.nf, 1.f) : 0.f; // correction = 1
+    const float sd = __fsqrt_rn(__fdiv_rn(r.m2, div));
+    __syncthreads();
+    return sd;
+}
+
+}  // namespace tstd

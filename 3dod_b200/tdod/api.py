@@ -123,6 +123,34 @@ def box3d_iou(gt_corners, corners, want_vol=False):
     return (out, vol) if want_vol else out
 
 
+def segmented_order(scores, k=None, want_val=False):
+    """K-D: scores [S,n] fp32 -> descending order per row, first k: idx [S,k] int32 (+ values)"""
+    S, n = scores.shape
+    k = n if k is None else int(k)
+    idx = torch.empty((S, k), dtype=i32, device=scores.device)
+    val = torch.empty((S, k), dtype=f32, device=scores.device) if want_val else None
+    L.check(L.lib().tdod_segmented_order(L.ptr(scores, f32, "scores"), S, n, k, L.ptr(idx), L.ptr(val), L.stream_ptr()))
+    return (idx, val) if want_val else idx
+
+
+def accumulate_scores(scores, iou3d, n_out=None):
+    """accumulate_scores (roi_heads.py:277-281): scores [S,C,n] fp64, iou3d [S,n] fp32 -> curves [S,C,n_out] fp32"""
+    S, Cn, n = scores.shape
+    n_out = n if n_out is None else int(n_out)
+    out = torch.empty((S, Cn, n_out), dtype=f32, device=scores.device)
+    L.check(L.lib().tdod_accumulate_scores(L.ptr(scores, f64, "scores"), L.ptr(iou3d, f32, "iou3d"), S, Cn, n, n_out,
+                                           L.ptr(out), L.stream_ptr()))
+    return out
+
+
+def torch_std(x):
+    """torch.std(x, dim=1) of a contiguous fp32 [N,n] CUDA tensor with the rounding of torch's own CUDA kernel"""
+    N, n = x.shape
+    out = torch.empty(N, dtype=f32, device=x.device)
+    L.check(L.lib().tdod_torch_std(L.ptr(x, f32, "x"), N, n, L.ptr(out), L.stream_ptr()))
+    return out
+
+
 def yaw_table(normals):
     """normals [F,3] fp32/fp64 -> [F,36,3,3] fp32"""
     F = normals.shape[0]
@@ -184,7 +212,8 @@ class PssOutputs:
 def propose_score_select(depth, K, boxes, prior_mean, prior_std, obj_frame, rects, has_rect, n_prop, yaw_tab=None,
                          iou_boxes=None, noise=None, yaw_idx=None, rot=None, seed=None, obj_id_base=0,
                          return_all=False, cluster_size=0, out=None, propose_only=False, centre_mode=L.CENTRE_DEPTH,
-                         dims_mode=L.DIMS_PRIOR, aux=None, im_shape=None, want_noise=False, want_seeds=False):
+                         dims_mode=L.DIMS_PRIOR, aux=None, im_shape=None, want_noise=False, want_seeds=False,
+                         std_mode=L.STD_EXACT):
     """The fused hot path (csrc/fused.cu).  depth [F,H,W], K [F,3,3], boxes [N,4], priors [N,3], obj_frame [N] int32,
     rects [N,4,2], has_rect [N] uint8 | None, yaw_tab [F,36,3,3] | None.
     Parity RNG mode: noise [N,6,n] (+ yaw_idx [N,n] int16 | rot [N,n,9]); throughput mode: seed=int (Philox)."""
@@ -242,6 +271,7 @@ def propose_score_select(depth, K, boxes, prior_mean, prior_std, obj_frame, rect
     if aux is not None and tuple(aux.shape) != (N, 2):
         raise ValueError("aux must be [N,2]")
     a.aux = L.ptr(aux, f32, "aux")
+    a.std_mode = int(std_mode)
     # audit outputs: the numbers behind the proposal set (HOST-mode layout) and the centre seeds
     o.noise = torch.empty((N, 6, n_prop), dtype=f32, device=dev) if want_noise else None
     o.yaw_idx = torch.empty((N, n_prop), dtype=i16, device=dev) if (want_noise and yaw_tab is not None) else None

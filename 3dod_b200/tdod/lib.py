@@ -13,6 +13,7 @@ RNG_HOST, RNG_PHILOX = 0, 1
 BACKPROJECT_NUMPY, BACKPROJECT_TORCH = 0, 1
 CENTRE_DEPTH, CENTRE_UNIFORM, CENTRE_PATCH, CENTRE_PATCH_Z = 0, 1, 2, 3
 DIMS_PRIOR, DIMS_UNIFORM, DIMS_ASPECT = 0, 1, 2
+STD_EXACT, STD_TORCH_CUDA = 0, 1
 
 _lib = None
 
@@ -33,6 +34,7 @@ class PssArgs(C.Structure):
         ("cluster_size", C.c_int32), ("propose_only", C.c_int32),
         ("centre_mode", C.c_int32), ("dims_mode", C.c_int32), ("im_w", C.c_int32), ("im_h", C.c_int32),
         ("aux", C.c_void_p),
+        ("std_mode", C.c_int32),
         ("out_noise", C.c_void_p), ("out_yaw_idx", C.c_void_p), ("out_seeds", C.c_void_p),
     ]
 
@@ -56,11 +58,14 @@ SIGNATURES = {
     "tdod_score_segmentation": (_I, [_P, _I, _I, _P, _L, _I, _P, _P]),
     "tdod_score_point_cloud": (_I, [_P, _I, _L, _P, _L, _P, _P]),
     "tdod_box3d_iou": (_I, [_P, _P, _L, _L, _P, _P, _P]),
+    "tdod_segmented_order": (_I, [_P, _L, _I, _I, _P, _P, _P]),
+    "tdod_accumulate_scores": (_I, [_P, _P, _L, _I, _I, _I, _P, _P]),
     "tdod_backproject": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P]),
     "tdod_ransac_workspace_bytes": (_L, [_I, _I, _I]),
     "tdod_ransac_plane": (_I, [_P, _I, _P, _I, _L, _P, _U64, _L, _I, _D, _P, _P, _P, _P, _P, _P, _L, _P]),
     "tdod_yaw_table": (_I, [_P, _I, _I, _P, _P]),
     "tdod_resize_nearest": (_I, [_P, _I, _I, _I, _I, _P, _P, _P, _I, _I, _P]),
+    "tdod_torch_std": (_I, [_P, _L, _I, _P, _P]),
     "tdod_propose_score_select": (_I, [C.POINTER(PssArgs), _P]),
     "tdod_cube_box_fwd": (_I, [_P, _P, _P, _P, _L, _P, _P, _P, _P, _P, _P, _P]),
     "tdod_cube_box_bwd": (_I, [_P, _P, _P, _P, _L, _P, _P, _P, _P, _P, _P, _P]),

@@ -41,6 +41,11 @@ extern "C" {
 #define TDOD_DIMS_UNIFORM 1    /* proposals.py:28-30 rescale_interval(u, 0.05, 2) for w, h, l */
 #define TDOD_DIMS_ASPECT 2     /* proposals.py:230-239 (propose_aspect_ratio): w uniform, h = w*aux[0], l = w*aux[1] */
 
+/* how torch.std of the centre seeds (proposals.py:386-396) is rounded (tdod_pss_args.std_mode) */
+#define TDOD_STD_EXACT 0       /* two-pass fp64, correctly rounded: what torch computes on CPU tensors */
+#define TDOD_STD_TORCH_CUDA 1  /* torch's CUDA kernel: fp32 Welford merged in the order of its launch configuration for the
+                                  frame's [N_objects_of_frame, n_prop] tensor -- the reference as it runs on the GPU */
+
 #define TDOD_BACKPROJECT_NUMPY 0 /* roi_heads.py:346-371: fp64, full-res intrinsics on the strided grid */
 #define TDOD_BACKPROJECT_TORCH 1 /* roi_heads.py:1084-1112: fp32, K // stride, centre of the strided grid */
 
@@ -110,6 +115,19 @@ int tdod_score_point_cloud(const void* points, int points_f64, int64_t P, const 
 int tdod_box3d_iou(const float* gt_corners, const float* corners, int64_t G, int64_t n, float* out_iou, float* out_vol,
                    void* stream);
 
+/* K-D, segmented order: per object the indices of its k best scores in descending order -- np.argsort(scores)[::-1][:k]
+ * (cubercnn/modeling/roi_heads/roi_heads.py:278; k = 10 is the top-10 refinement of :585-586, k = n the full order).
+ * NaN first (np.argsort sorts NaN last, [::-1] reverses), equal scores by descending index (NumPy leaves tie order
+ * unspecified).  scores [S,n] -> out_idx [S,k] int32, out_val [S,k] or NULL.  n <= 16384. */
+int tdod_segmented_order(const float* scores, int64_t S, int n, int k, int32_t* out_idx, float* out_val, void* stream);
+
+/* ROIHeads_Boxer.accumulate_scores (roi_heads.py:277-281) for C score channels per object sharing that object's IoU3D:
+ * out_curves[s,c,:n_out] = np.maximum.accumulate(iou3d[s][argsort(scores[s,c])[::-1]])[:n_out].  scores are fp64 (NumPy
+ * promotes the products with the int64 point-cloud score to float64, :556-579); n_out = n for the eight MABO curves
+ * (:543-550), 1 for the 26 score combinations (:553-579, which keep element [0]). */
+int tdod_accumulate_scores(const double* scores /*[S,C,n]*/, const float* iou3d /*[S,n]*/, int64_t S, int C, int n, int n_out,
+                           float* out_curves /*[S,C,n_out]*/, void* stream);
+
 /* ---- plane ---------------------------------------------------------------------------------------------- */
 
 /* Depth -> strided point cloud (roi_heads.py:346-371 / :1084-1112), row-major compaction.
@@ -146,6 +164,10 @@ int tdod_yaw_table(const void* normals, int normals_f64, int F, float* out_table
  * xmap [W], ymap [H] int32 source indices (Pillow's accumulating double-precision stepping, built by the caller). */
 int tdod_resize_nearest(const void* src, int elem_bytes, int F, int h, int w, const int32_t* xmap, const int32_t* ymap,
                         void* dst, int H, int W, void* stream);
+
+/* torch.std(x, dim=1) of a contiguous fp32 tensor x [N,n] exactly as torch's CUDA kernel rounds it (the TDOD_STD_TORCH_CUDA
+ * flavour above, exposed for checking it against torch itself).  out [N]. */
+int tdod_torch_std(const float* x, int64_t N, int n, float* out, void* stream);
 
 /* ---- fused propose + project + score + select (the hot kernel) --------------------------------------- */
 
@@ -190,6 +212,7 @@ typedef struct tdod_pss_args {
     int32_t dims_mode;         /* TDOD_DIMS_* */
     int32_t im_w, im_h;        /* im_shape of pixel_to_normalised_space (PATCH modes); 0 -> W, H */
     const float* aux;          /* [n_obj,2]: DIMS_ASPECT (ratio_h, ratio_l); NULL otherwise */
+    int32_t std_mode;          /* TDOD_STD_* */
     /* replay / audit outputs (each may be NULL): the numbers behind the proposal set, in HOST-mode layout, so that a PHILOX
      * run can be fed back through HOST mode (and through the oracle's cubes_from_noise) bit for bit */
     float* out_noise;          /* [n_obj,6,n_prop]: accepted standard normals (or U[0,1) draws) for w,h,l,x,y,z */

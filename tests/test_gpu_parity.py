@@ -2,10 +2,15 @@
 reference and against the oracle on identical inputs.
 
 Bars (BASELINE.json north_star): integer / index results bit-exact; fp32 scores within 1e-5 relative (absolute
-floor 1e-7) when the kernels are fed the reference's own cubes; selected index identical wherever the reference's
-top-2 gap exceeds the tolerance.  The fused kernel re-derives the cube centres on the GPU, whose atan2f / sinf differ
-from torch-CPU's (SLEEF) in the last ulp; its centres are therefore compared at 1e-5 relative + 1e-6 m and its scores
-at 2e-5 (w, h, l and R, which involve no transcendental, are bit-exact)."""
+floor 1e-7); selected index identical wherever the reference's top-2 gap exceeds the tolerance.
+
+The reference has two numerical flavours: run on CUDA tensors (production: proposals.py:354-396 on reference_box.device)
+and run on CPU tensors (how the fixtures in tests/golden/ were frozen in the GPU-less build container).  They differ from
+EACH OTHER in the last ulp of atan2 / sin (libdevice vs SLEEF) and of torch.std (fp32 Welford vs fp64), which moves a
+handful of scores per 10 000 across the 1e-5 / 1e-7 line.  Against the CUDA-tensor flavour the stated bars hold with no
+exception -- the whole proposal set bit for bit, every score strict (tests/test_gpu_round2.py).  Against the CPU-frozen
+fixtures in this file w, h, l and R are bit-exact, centres agree to 1e-5 relative + 1e-6 m, and scores are gated twice
+(`assert_scores_cpu_fixture`): at least 99.9 % of them strict, all of them within 2e-5 / 1e-6."""
 import hashlib
 import os
 
@@ -42,6 +47,19 @@ def assert_scores(got, ref, rtol=RTOL, atol=ATOL, what=""):
         what, int((~ok).sum()), ok.size, float(np.nanmax(np.abs(got - ref))))
 
 
+def assert_scores_cpu_fixture(got, ref, what=""):
+    """scores of the fused kernel against fixtures frozen from the reference run on CPU tensors (module docstring)"""
+    got = np.asarray(got, np.float64); ref = np.asarray(ref, np.float64)
+    assert np.array_equal(np.isnan(got), np.isnan(ref)), what + ": NaN pattern differs"
+    err = np.abs(got - ref)
+    strict = (err <= ATOL + RTOL * np.abs(ref)) | np.isnan(ref)
+    loose = (err <= 1e-6 + 2e-5 * np.abs(ref)) | np.isnan(ref)
+    assert loose.all(), "%s: %d / %d outside 2e-5 / 1e-6, worst abs %.3g" % (what, int((~loose).sum()), loose.size,
+                                                                                float(np.nanmax(err)))
+    assert (~strict).sum() <= max(1, strict.size // 1000), "%s: %d / %d outside 1e-5 / 1e-7" % (
+        what, int((~strict).sum()), strict.size)
+
+
 def run_fused(g, f, S, propose_only=False):
     d = dev()
     n, N = int(g["n"]), int(g["n_obj"])
@@ -76,7 +94,7 @@ def test_fused_kernel_against_reference_fixture(golden_dir, name, S):
     assert np.allclose(o.all_boxes.cpu().numpy(), g["boxes"], rtol=1e-5, atol=2e-3)
     sc = o.all_scores.cpu().numpy()
     for k, nm in enumerate(["iou", "dim", "cor", "combined"]):
-        assert_scores(sc[:, k], g[nm], rtol=2e-5, atol=1e-6, what=nm)
+        assert_scores_cpu_fixture(sc[:, k], g[nm], what=nm)
     best = o.best_idx.cpu().numpy()
     for i in range(len(best)):
         top2 = np.sort(g["combined"][i])[-2:]
@@ -582,7 +600,7 @@ def test_pipeline_matches_oracle_end_to_end(golden_dir):
     assert np.array_equal(sel.normal[0].cpu().numpy(), g["normal"])
     assert np.array_equal(sel.plane_eq[0].cpu().numpy(), g["plane_eq"])
     assert sel.best_idx.cpu().tolist() == g["best"].tolist()
-    assert_scores(sel.all.all_scores[:, 3].cpu().numpy(), g["combined"], rtol=2e-5, atol=1e-6, what="combined")
+    assert_scores_cpu_fixture(sel.all.all_scores[:, 3].cpu().numpy(), g["combined"], what="combined")
 
 
 def _oracle_chain(f, n, W, H, seed, iters=1000):
@@ -626,7 +644,7 @@ def test_selection_parity_on_the_named_configs(cfg, n_obj, n):
     assert np.allclose(sel.plane_eq[0].cpu().numpy(), r["eq"], rtol=1e-13, atol=0)     # NumPy's norm goes through BLAS
     assert np.allclose(sel.normal[0].cpu().numpy(), r["normal"], rtol=0, atol=1e-12)
     comb = sel.all.all_scores[:, 3].cpu().numpy()
-    assert_scores(comb, r["comb"], rtol=2e-5, atol=1e-6, what=cfg + " combined")
+    assert_scores_cpu_fixture(comb, r["comb"], what=cfg + " combined")
     got = sel.best_idx.cpu().tolist()
     for i in range(f.n_obj()):
         ref = r["comb"][i]
@@ -762,7 +780,7 @@ def test_philox_mode_winner_is_the_argmax_of_what_it_scored():
         r = O.select(O.iou_score(b.boxes[i].cpu(), pb),
                      O.dims_score(b.prior_mean[i].cpu(), b.prior_std[i].cpu(), cc[:, 3:6], b.boxes[i].cpu(), pb),
                      O.corners_score(b.masks[i].cpu(), c2))[0]
-        assert_scores(comb[i].cpu().numpy(), r, rtol=2e-5, atol=1e-6, what="combined vs oracle")
+        assert_scores_cpu_fixture(comb[i].cpu().numpy(), r, what="combined vs oracle")
 
 
 def test_host_streaming_pipeline_equals_resident_run():
