@@ -681,13 +681,14 @@ extern "C" int tdod_propose_score_select(const tdod_pss_args* ap, void* stream) 
     const size_t smem = ((sizeof(Shared) + 15) & ~size_t(15)) + (size_t)7 * n_loc * sizeof(float);
     if (smem > 227 * 1024) return tdod_fail(TDOD_ERANGE, "n_prop too large for shared memory at this cluster size");
     cudaError_t e;
+    static tdod_smem_cache sm_cta, sm_cluster;
     if (S == 1) {
-        e = cudaFuncSetAttribute(pss_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        e = tdod_smem_opt_in((const void*)pss_kernel<false>, smem, &sm_cta);
         if (e != cudaSuccess) return (int)e;
         pss_kernel<false><<<(unsigned)a.n_obj, kThreads, smem, (cudaStream_t)stream>>>(a, n_loc);
         return (int)cudaGetLastError();
     }
-    e = cudaFuncSetAttribute(pss_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    e = tdod_smem_opt_in((const void*)pss_kernel<true>, smem, &sm_cluster);
     if (e != cudaSuccess) return (int)e;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)((int64_t)a.n_obj * S), 1, 1);

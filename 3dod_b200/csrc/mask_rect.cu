@@ -246,6 +246,25 @@ __global__ void __launch_bounds__(kPackT) pack_tma_kernel(const uint8_t* __restr
     }
 }
 
+// Where the labelling reads a mask's bits from.  GlobalBits: the row-padded 1 bit/px bitmap the pack kernels write
+// (word w of row r at r * Wp + w).  StreamBits: the fused front kernel's shared-memory bit stream -- bit i of the
+// stream is byte i of the mask's 16-byte-aligned chunk range, rows are NOT padded, so a row word is a 32-bit window at
+// bit offset off0 + r * W + 32 w (one funnel shift over two shared-memory words).
+struct GlobalBits {
+    const uint32_t* bm; int Wp;
+    __device__ __forceinline__ uint32_t word(int r, int w) const { return bm[(size_t)r * Wp + w]; }
+};
+struct StreamBits {
+    const uint32_t* s32; int off0, W;
+    __device__ __forceinline__ uint32_t word(int r, int w) const {
+        const int o = off0 + r * W + 32 * w;
+        uint32_t v = __funnelshift_r(s32[o >> 5], s32[(o >> 5) + 1], o & 31);
+        const int nb = W - 32 * w;
+        if (nb < 32) v &= (1u << nb) - 1u;
+        return v;
+    }
+};
+
 __device__ __forceinline__ int uf_find(const int* parent, int x) {
     int p = parent[x];
     while (p != x) { x = p; p = parent[x]; }
@@ -296,14 +315,14 @@ __device__ int scan_rows(int* row_off, int H, int* scratch /*[kT/32 + 1]*/) {
 // starts where a set bit follows a clear one and ends where a set bit precedes a clear one; the k-th start of a row
 // pairs with its k-th end, so lanes can write starts and ends independently at prefix-summed positions.
 // emit == false: returns the row's run count (valid in every lane).
-template <bool kEmit>
-__device__ __forceinline__ int row_runs_warp(const uint32_t* __restrict__ bm, int Wp, int r, const RunSet& rs, int base, int cap) {
+template <bool kEmit, typename Bits>
+__device__ __forceinline__ int row_runs_warp(const Bits& bm, int Wp, int r, const RunSet& rs, int base, int cap) {
     const int lane = threadIdx.x & 31;
     int S = 0, E = 0;
     uint32_t carry = 0;
     for (int w0 = 0; w0 < Wp; w0 += 32) {
         const int w = w0 + lane;
-        const uint32_t m = (w < Wp) ? bm[(size_t)r * Wp + w] : 0u;
+        const uint32_t m = (w < Wp) ? bm.word(r, w) : 0u;
         uint32_t prev = __shfl_up_sync(0xffffffffu, m >> 31, 1);
         if (lane == 0) prev = carry;
         carry = __shfl_sync(0xffffffffu, m >> 31, 31);
@@ -311,7 +330,7 @@ __device__ __forceinline__ int row_runs_warp(const uint32_t* __restrict__ bm, in
         const int ns = __popc(starts);
         if (!kEmit) { S += ns; continue; }
         uint32_t next = __shfl_down_sync(0xffffffffu, m & 1u, 1);
-        if (lane == 31) next = (w0 + 32 < Wp) ? (bm[(size_t)r * Wp + w0 + 32] & 1u) : 0u;
+        if (lane == 31) next = (w0 + 32 < Wp) ? (bm.word(r, w0 + 32) & 1u) : 0u;
         const uint32_t ends = m & ~((m >> 1) | (next << 31));
         const int ne = __popc(ends);
         int ps = ns, pe = ne;                                   // inclusive warp prefix sums
@@ -337,7 +356,10 @@ __device__ __forceinline__ int row_runs_warp(const uint32_t* __restrict__ bm, in
 
 // label the runs of rows [r0, r1] of `bm` (8-connectivity; the rows outside are empty), accumulate twice the
 // cell-formula area at each root.  returns the number of runs, or -1 if they exceed the capacity.
-__device__ int label_runs(const uint32_t* bm, int H, int W, int Wp, RunSet rs, int* scratch, int cap, int r0, int r1) {
+__device__ int label_from_runs(RunSet rs, int R);
+
+template <typename Bits>
+__device__ int label_runs(const Bits bm, int H, int W, int Wp, RunSet rs, int* scratch, int cap, int r0, int r1) {
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int r = threadIdx.x; r <= H; r += kT) rs.row_off[r] = 0;
     __syncthreads();
@@ -346,7 +368,7 @@ __device__ int label_runs(const uint32_t* bm, int H, int W, int Wp, RunSet rs, i
         for (int rb = r0 + wid * kU; rb <= r1; rb += kWarps * kU) {
             uint32_t m[kU];
 #pragma unroll
-            for (int u = 0; u < kU; ++u) m[u] = (rb + u <= r1 && lane < Wp) ? bm[(size_t)(rb + u) * Wp + lane] : 0u;
+            for (int u = 0; u < kU; ++u) m[u] = (rb + u <= r1 && lane < Wp) ? bm.word(rb + u, lane) : 0u;
 #pragma unroll
             for (int u = 0; u < kU; ++u) {
                 uint32_t prev = __shfl_up_sync(0xffffffffu, m[u] >> 31, 1);
@@ -357,7 +379,7 @@ __device__ int label_runs(const uint32_t* bm, int H, int W, int Wp, RunSet rs, i
         }
     } else {
         for (int r = r0 + wid; r <= r1; r += kWarps) {
-            const int c = row_runs_warp<false>(bm, Wp, r, rs, 0, 0);
+            const int c = row_runs_warp<false, Bits>(bm, Wp, r, rs, 0, 0);
             if (lane == 0) rs.row_off[r] = c;
         }
     }
@@ -370,7 +392,7 @@ __device__ int label_runs(const uint32_t* bm, int H, int W, int Wp, RunSet rs, i
         for (int rb = r0 + wid * kU; rb <= r1; rb += kWarps * kU) {
             uint32_t m[kU];
 #pragma unroll
-            for (int u = 0; u < kU; ++u) m[u] = (rb + u <= r1 && lane < Wp) ? bm[(size_t)(rb + u) * Wp + lane] : 0u;
+            for (int u = 0; u < kU; ++u) m[u] = (rb + u <= r1 && lane < Wp) ? bm.word(rb + u, lane) : 0u;
 #pragma unroll
             for (int u = 0; u < kU; ++u) {
                 const int r = rb + u;
@@ -406,8 +428,15 @@ __device__ int label_runs(const uint32_t* bm, int H, int W, int Wp, RunSet rs, i
             }
         }
     } else {
-        for (int r = r0 + wid; r <= r1; r += kWarps) row_runs_warp<true>(bm, Wp, r, rs, rs.row_off[r], cap);
+        for (int r = r0 + wid; r <= r1; r += kWarps) row_runs_warp<true, Bits>(bm, Wp, r, rs, rs.row_off[r], cap);
     }
+    __syncthreads();                                    // the runs were written by other warps
+    return label_from_runs(rs, R);
+}
+
+// Labels the R runs in `rs` (row_off filled for every row) and accumulates twice the cell-formula area at each root.
+// Called by all threads; returns R.
+__device__ int label_from_runs(RunSet rs, int R) {
     // Labelling (8-connectivity).  A blob is a chain of one run per row, so hanging run i under the run above it
     // through union-find makes every later find walk the whole chain (quadratic in the rows).  Instead:
     //   1. every run points straight at the FIRST run of the previous row it touches (no find, no atomics): a forest
@@ -415,7 +444,6 @@ __device__ int label_runs(const uint32_t* bm, int H, int W, int Wp, RunSet rs, i
     //   2. pointer jumping flattens the forest (each round walks up to 8 links: 3-4 rounds for 500 rows);
     //   3. the remaining adjacencies -- a run touching several runs of the previous row -- are unions of roots;
     //   4. one short walk per run gives the final root = smallest run index of the component, as before.
-    __syncthreads();                                    // the runs were written by other warps
     for (int i = threadIdx.x; i < R; i += kT) {
         const int r = rs.row[i];
         int first = i;
@@ -478,6 +506,34 @@ __device__ int label_runs(const uint32_t* bm, int H, int W, int Wp, RunSet rs, i
     return R;
 }
 
+// The hull / calipers stage runs either on a whole CTA (the exact passes) or on ONE WARP per mask (the tail kernel of the
+// fused path, where many masks' serial chains overlap on an SM instead of stalling a CTA at barriers).
+template <int G> struct Grp {
+    static __device__ __forceinline__ int tid() { return G == 32 ? (int)(threadIdx.x & 31) : (int)threadIdx.x; }
+    static __device__ __forceinline__ void sync() { if (G == 32) __syncwarp(); else __syncthreads(); }
+    static __device__ __forceinline__ int sync_or(int p) { return G == 32 ? __any_sync(0xffffffffu, p) : __syncthreads_or(p); }
+};
+// exclusive scan of n ints in place (+ total at [n]) by one warp
+__device__ __forceinline__ int scan_rows_warp(int* a, int n) {
+    const int lane = threadIdx.x & 31;
+    int carry = 0;
+    for (int base = 0; base < n; base += 32) {
+        const int i = base + lane;
+        const int v = (i < n) ? a[i] : 0;
+        int inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (i < n) a[i] = carry + inc - v;
+        carry += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    if (lane == 0) a[n] = carry;
+    __syncwarp();
+    return carry;
+}
+
 // ---- hull + rotating calipers of the component `root` ----------------------------------------------------------
 // Only two things are inherently sequential: the monotone-chain stacks (one thread per chain, top of stack in
 // registers) and the calipers' walk around the hull (one thread, everything it reads precomputed in parallel).
@@ -492,12 +548,13 @@ struct HullBuf { int16_t* rx; int16_t* ry; int16_t* lx; int16_t* ly; float* hx; 
 // and the cosines that decide which caliper advances in double, everything else fp32 with every product / sum
 // rounded on its own (no FMA contraction), then minAreaRect's centre/size/angle and RotatedRect::points (boxPoints).
 // Called by all threads; `ext` = {left, right, top, bottom} start indices (first extreme in hull order).
+template <int G>
 __device__ void calipers_box(const HullBuf& hb, int n, int* ext /*[4] smem*/, float* out8) {
     const float* px = hb.hx; const float* py = hb.hy;
-    const int tid = threadIdx.x;
+    const int tid = Grp<G>::tid();
     if (n >= 3) {
         // edge vectors and inverse lengths (double sqrt + divide each): one edge per thread
-        for (int i = tid; i < n; i += kT) {
+        for (int i = tid; i < n; i += G) {
             const int j = (i + 1 < n) ? i + 1 : 0;
             const double dx = (double)px[j] - (double)px[i], dy = (double)py[j] - (double)py[i];
             hb.vx[i] = (float)dx; hb.vy[i] = (float)dy;
@@ -505,8 +562,9 @@ __device__ void calipers_box(const HullBuf& hb, int n, int* ext /*[4] smem*/, fl
             hb.inv[i] = iv; hb.invf[i] = (float)iv;
         }
         // extremes with the serial scan's semantics (strict compares from index 0: the FIRST extreme wins)
-        if (tid < 128) {
-            const int which = tid >> 5, lane = tid & 31;     // 0 left (min x), 1 right (max x), 2 top (max y), 3 bottom (min y)
+        for (int which = (G == 32 ? 0 : (tid >> 5)); which < 4; which += (G == 32 ? 1 : 4)) {
+            if (G != 32 && tid >= 128) break;
+            const int lane = tid & 31;                       // 0 left (min x), 1 right (max x), 2 top (max y), 3 bottom (min y)
             const float* src = (which < 2) ? px : py;
             const bool want_min = (which == 0 || which == 3);
             float bv = src[0]; int bi = 0;
@@ -523,7 +581,7 @@ __device__ void calipers_box(const HullBuf& hb, int n, int* ext /*[4] smem*/, fl
             if (lane == 0) ext[which] = bi;
         }
     }
-    __syncthreads();
+    Grp<G>::sync();
     KB_T(8);
     if (tid != 0) return;
     if (n == 1) {
@@ -634,11 +692,9 @@ __device__ void calipers_box(const HullBuf& hb, int n, int* ext /*[4] smem*/, fl
     out8[6] = __fsub_rn(__fmul_rn(2.f, cx), p1x); out8[7] = __fsub_rn(__fmul_rn(2.f, cy), p1y);
 }
 
-// Strict convex hull of the component `root` from its per-row extremes, in cv2.convexHull's output order
-// (start at (max x, max y), then image-clockwise), followed by the calipers.  Called by all threads.
-// counts: int[8] shared scratch.  Returns false if a chain outgrew kChainCap (cannot happen below 1024^2 pixels).
-__device__ bool component_rect(const RunSet& rs, int R, int root, int H, int* rowL, int* rowR, const HullBuf& hb,
-                               int* counts, float* out8) {
+// Per-row extremes of the component `root` (its runs' leftmost start / rightmost end per row) and its row range ->
+// rowL / rowR [H], counts[2] = first row, counts[3] = last row.  Called by all threads of the CTA.
+__device__ void component_rows(const RunSet& rs, int R, int root, int H, int* rowL, int* rowR, int* counts) {
     const int tid = threadIdx.x;
     if (tid == 0) { counts[0] = 0; counts[1] = 0; counts[2] = 0x7fffffff; counts[3] = -1; }
     for (int r = tid; r < H; r += kT) { rowL[r] = 0x7fffffff; rowR[r] = -1; }
@@ -650,46 +706,61 @@ __device__ bool component_rect(const RunSet& rs, int R, int root, int H, int* ro
             atomicMin(&counts[2], r); atomicMax(&counts[3], r);
         }
     __syncthreads();
-    const int rmin = counts[2], rmax = counts[3];      // a connected component occupies every row in between
+}
+
+// Strict convex hull of a component from its per-row extremes (rows rmin..rmax, every row occupied: a connected
+// component has no empty row in between), in cv2.convexHull's output order (start at (max x, max y), then
+// image-clockwise), followed by the calipers.  Called by all G threads of the group (a CTA of kT threads, or one warp).
+// keep: int[nrows + 1] scratch; counts: int[>= 8 + kT/32 + 2] scratch.  Returns false if the hull outgrew `hull_cap`
+// vertices (cannot happen below 1024^2 pixels with the CTA capacities).
+template <int G, typename RT>
+__device__ bool hull_rect(int rmin, int rmax, const RT* rowL, const RT* rowR, int* keep, const HullBuf& hb, int hull_cap,
+                          int chain_cap, int* counts, float* out8) {
+    const int tid = Grp<G>::tid();
     KB_T(4);
     const int nrows = rmax - rmin + 1;
     // Candidates of the two chains are the per-row extremes.  A candidate that lies on or inside ANY chord between two
     // other candidates of its chain is not a strict hull vertex, so a cheap parallel sieve (chords to the rows
     // +-1, 2, 4, ... 32 away) removes most of them exactly; the survivors are compacted in row order and the
     // monotone-chain stack -- the only sequential step -- runs over those, in place, one thread per chain.
-    int* keep = rs.row_off;                            // [H+1] ints, free from here on: low half right, high half left
-    for (int r = tid; r < H + 1; r += kT) keep[r] = 0;
-    __syncthreads();
-    for (int it = tid; it < 2 * nrows; it += kT) {
+    for (int r = tid; r < nrows + 1; r += G) keep[r] = 0;    // low half: right chain, high half: left chain
+    if (tid == 0) { counts[0] = 0; counts[1] = 0; }
+    Grp<G>::sync();
+    for (int it = tid; it < 2 * nrows; it += G) {
         const int side = it >= nrows;                  // 0 right chain, 1 left chain
         const int r = rmin + (side ? it - nrows : it);
-        const int* src = side ? rowL : rowR;
+        const RT* src = side ? rowL : rowR;
         const int xi = src[r];
         bool kp = true;
         if (r != rmin && r != rmax) {
 #pragma unroll
             for (int d = 1; d <= 32; d <<= 1) {
                 const int a = max(r - d, rmin), c = min(r + d, rmax);
-                const int cr = (xi - src[a]) * (c - r) - (r - a) * (src[c] - xi);
+                const int cr = (xi - (int)src[a]) * (c - r) - (r - a) * ((int)src[c] - xi);
                 kp &= side ? (cr < 0) : (cr > 0);      // same sign test as the stack's pop condition below
             }
         }
         if (kp) atomicAdd(&keep[r - rmin], side ? 0x10000 : 1);
     }
-    __syncthreads();
+    Grp<G>::sync();
     KB_T(5);
-    const int packed = scan_rows(keep, nrows, counts + 8);        // exclusive scan of both survivor counts at once
+    // exclusive scan of both survivor counts at once
+    const int packed = (G == 32) ? scan_rows_warp(keep, nrows) : scan_rows(keep, nrows, counts + 8);
     const int sr_ = packed & 0xffff, sl_ = packed >> 16;
-    for (int k = tid; k < nrows; k += kT) {
+    if (sr_ > chain_cap || sl_ > chain_cap) return false;    // more sieve survivors than the group's chain buffers hold
+    for (int k = tid; k < nrows; k += G) {
         const int before = keep[k], after = keep[k + 1];
         const int r = rmin + k;
         if ((after & 0xffff) != (before & 0xffff)) { hb.rx[before & 0xffff] = (int16_t)rowR[r]; hb.ry[before & 0xffff] = (int16_t)r; }
         if ((after >> 16) != (before >> 16)) { hb.lx[before >> 16] = (int16_t)rowL[r]; hb.ly[before >> 16] = (int16_t)r; }
     }
-    __syncthreads();
+    Grp<G>::sync();
     KB_T(6);
-    if (tid == 0 || tid == 32) {
-        // tid 0: right chain, tid 32: left chain, top -> bottom; pop while the turn is not strictly convex.  The stack
+    // the two chains walk the same code with different data: as two lanes of one warp they stay converged (the group's
+    // cost is the longer chain, not the sum); on a CTA they sit in two different warps
+    const int chain_b = (G == 32) ? 1 : 32;
+    if (tid == 0 || tid == chain_b) {
+        // right chain / left chain, top -> bottom; pop while the turn is not strictly convex.  The stack
         // is written over the survivor list itself (it never gets ahead of the read position); (ax,ay) / (bx,by)
         // mirror its two topmost entries so that a push costs no shared-memory read.
         const bool right = tid == 0;
@@ -710,8 +781,8 @@ __device__ bool component_rect(const RunSet& rs, int R, int root, int H, int* ro
         }
         counts[right ? 0 : 1] = n;
     }
-    __syncthreads();
-    if (counts[0] + counts[1] > kHullCap) return false;
+    Grp<G>::sync();
+    if (counts[0] + counts[1] > hull_cap) return false;
     const int nr = counts[0], nl = counts[1];
     // cyclic order: right chain downward, then left chain upward (dropping duplicated end points)
     const bool dup_bottom = hb.lx[nl - 1] == hb.rx[nr - 1] && hb.ly[nl - 1] == hb.ry[nr - 1];
@@ -719,21 +790,22 @@ __device__ bool component_rect(const RunSet& rs, int R, int root, int H, int* ro
     // left-chain entries kept: indices [lo, hi] walked downward from hi
     const int hi = nl - 1 - (dup_bottom ? 1 : 0), lo = dup_top ? 1 : 0;
     int n = nr + max(0, hi - lo + 1);
-    for (int i = tid; i < n; i += kT) {
+    Grp<G>::sync();        // (the float hull may alias the sieve's scratch: everybody is done with `keep`)
+    for (int i = tid; i < n; i += G) {
         if (i < nr) { hb.hx[i] = (float)hb.rx[i]; hb.hy[i] = (float)hb.ry[i]; }
         else { const int k = hi - (i - nr); hb.hx[i] = (float)hb.lx[k]; hb.hy[i] = (float)hb.ly[k]; }
     }
-    __syncthreads();
+    Grp<G>::sync();
     // collinear triples can only survive across the chain joins of degenerate (1- or 2-row, needle-like) components:
     // detect in parallel, repair serially only then
     int bad = 0;
     if (n > 2)
-        for (int i = tid; i < n; i += kT) {
+        for (int i = tid; i < n; i += G) {
             const int a = (i + n - 1) % n, c = (i + 1) % n;
             const float cr = (hb.hx[i] - hb.hx[a]) * (hb.hy[c] - hb.hy[i]) - (hb.hy[i] - hb.hy[a]) * (hb.hx[c] - hb.hx[i]);
             bad |= (cr == 0.f);
         }
-    if (__syncthreads_or(bad)) {
+    if (Grp<G>::sync_or(bad)) {
         if (tid == 0) {
             bool changed = n > 2;
             while (changed) {
@@ -749,7 +821,7 @@ __device__ bool component_rect(const RunSet& rs, int R, int root, int H, int* ro
             }
             counts[4] = n;
         }
-        __syncthreads();
+        Grp<G>::sync();
         n = counts[4];
     }
     // rotate so that the start is (max x, max y among those): first such index in a serial scan == the unique argmax
@@ -767,23 +839,33 @@ __device__ bool component_rect(const RunSet& rs, int R, int root, int H, int* ro
         }
         if (tid == 0) counts[5] = bi;
     }
-    __syncthreads();
+    Grp<G>::sync();
     const int s0 = counts[5];
     if (s0) {   // rotate left by s0 through the (still unused) vx/vy scratch
-        for (int i = tid; i < n; i += kT) { hb.vx[i] = hb.hx[(i + s0) % n]; hb.vy[i] = hb.hy[(i + s0) % n]; }
-        __syncthreads();
-        for (int i = tid; i < n; i += kT) { hb.hx[i] = hb.vx[i]; hb.hy[i] = hb.vy[i]; }
-        __syncthreads();
+        for (int i = tid; i < n; i += G) { hb.vx[i] = hb.hx[(i + s0) % n]; hb.vy[i] = hb.hy[(i + s0) % n]; }
+        Grp<G>::sync();
+        for (int i = tid; i < n; i += G) { hb.hx[i] = hb.vx[i]; hb.hy[i] = hb.vy[i]; }
+        Grp<G>::sync();
     }
     if (n == 2 && hb.hx[0] == hb.hx[1] && hb.hy[0] == hb.hy[1]) n = 1;
     KB_T(7);
-    calipers_box(hb, n, counts, out8);
-    __syncthreads();
+    calipers_box<G>(hb, n, counts, out8);
+    Grp<G>::sync();
     KB_T(9);
 #ifdef TDOD_KB_TIMING
-    if (threadIdx.x == 0 && blockIdx.x < 8192) { g_kb_t[blockIdx.x * 32 + 10] = n; g_kb_t[blockIdx.x * 32 + 11] = nrows; g_kb_t[blockIdx.x * 32 + 12] = R; }
+    if (threadIdx.x == 0 && blockIdx.x < 8192) { g_kb_t[blockIdx.x * 32 + 10] = n; g_kb_t[blockIdx.x * 32 + 11] = nrows; }
 #endif
     return true;
+}
+
+// the CTA form used by the rectangle kernels: rows of the component `root`, then its hull and calipers
+__device__ bool component_rect(const RunSet& rs, int R, int root, int H, int* rowL, int* rowR, const HullBuf& hb,
+                               int* counts, float* out8) {
+    component_rows(rs, R, root, H, rowL, rowR, counts);
+    const int rmin = counts[2], rmax = counts[3];
+    __syncthreads();
+    // rs.row_off [H+1] is free from here on: the sieve's scratch
+    return hull_rect<kT, int>(rmin, rmax, rowL, rowR, rs.row_off, hb, kHullCap, 0x7fff, counts, out8);
 }
 
 struct Smem {
@@ -1016,7 +1098,7 @@ __global__ void __launch_bounds__(kT, kExact ? 1 : TDOD_KB_MINB) rect_kernel(con
             comp_bm = s.bmB;
         }
         KB_T(1);
-        const int R = label_runs(comp_bm, H, W, Wp, s.rs, s.scratch, cap, r0, r1);
+        const int R = label_runs(GlobalBits{comp_bm, Wp}, H, W, Wp, s.rs, s.scratch, cap, r0, r1);
         KB_T(2);
         if (R < 0) {                                    // more runs than shared memory holds -> overflow pass
             if (threadIdx.x == 0) { out_has[mi] = 3; list3[atomicAdd(&lists[1], 1)] = (int)mi; }
@@ -1035,6 +1117,321 @@ __global__ void __launch_bounds__(kT, kExact ? 1 : TDOD_KB_MINB) rect_kernel(con
     }
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// Fused path (masks whose bit stream and run arrays fit in shared memory): the 1 bit/px copy never leaves the SM.
+//
+//   front kernel  persistent CTAs, two per SM.  Per mask: the raw bytes arrive tile by tile through a two-deep TMA ring
+//                 (cp.async.bulk + mbarrier, the load of the next tile -- also the next mask's first -- in flight while
+//                 this one is turned into bits), 16 bytes -> 16 bits -> one half-word store into a FLAT bit stream in
+//                 shared memory; then run extraction, labelling, cell-formula areas and the choice of the component
+//                 straight from that stream (StreamBits).  What leaves the SM is the winner's per-row extremes: two
+//                 int16 per occupied row (~1 KB per mask instead of a 48 KB bitmap written and read back).
+//                 While one CTA of an SM labels, the other streams.
+//   tail kernel   ONE WARP per mask: sieve, monotone-chain stacks, rotating calipers from those extremes.  The serial
+//                 chains of 12-16 masks overlap on an SM; nothing waits at a CTA barrier.
+// Masks the front kernel cannot decide (hole filling could change the winner; more runs than shared memory holds) go
+// to the work lists; a list-driven pack writes only THEIR bitmaps and the exact passes (rect_kernel<true, *>) finish them.
+// ------------------------------------------------------------------------------------------------------------
+constexpr int kRing = 4;                // TMA ring slots of a front CTA (loads of three tiles in flight behind the one being packed)
+constexpr int kTailHullCap = 192;       // hull vertices one tail warp holds (beyond: the overflow pass)
+constexpr int kTailChainCap = 256;      // sieve survivors per chain it holds (beyond: the overflow pass)
+constexpr int kTailWarps = 4;
+constexpr uint8_t kPending = 0xF0;      // state byte between the front and the tail kernel
+
+__host__ __device__ inline size_t cand_stride(int H) { return align16(8 + (size_t)H * 4); }   // {rmin, rmax} + int16 L/R per row
+
+struct FrontSmem {
+    unsigned char* raw0; size_t raw_stride; uint16_t* sb16;     // ring slot k at raw0 + k * raw_stride; bit stream of a row group
+    RunSet rs; int* rowL; int* rowR; int* scratch;
+};
+constexpr int kGroupRows = kT;          // rows whose bits are held at a time: one thread per row extracts their runs
+
+// rows: mask rows per TMA tile (divides kGroupRows); raw_cap: bytes of one ring slot
+__host__ __device__ inline size_t front_layout(int H, int W, int raw_cap, FrontSmem* f, unsigned char* base) {
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = (off + bytes + 127) & ~size_t(127); return o; };
+    const size_t o_raw = take(raw_cap);
+    const size_t raw_stride = off - o_raw;
+    for (int k = 1; k < kRing; ++k) take(raw_cap);
+    const size_t o_sb = take(((size_t)kGroupRows * W + 15 + 7) / 8 + 48);   // misalignment in front, funnel over-read behind
+    const size_t o_xs = take(kRunCap * 2), o_xe = take(kRunCap * 2), o_row = take(kRunCap * 2);
+    const size_t o_par = take(kRunCap * 4), o_area = take(kRunCap * 4);
+    const size_t o_roff = take((size_t)(H + 1) * 4), o_rl = take((size_t)H * 4), o_rr = take((size_t)H * 4);
+    const size_t o_scr = take((2 * (kT / 32) + 48) * 4);
+    if (f) {
+        f->raw0 = base + o_raw; f->raw_stride = raw_stride;
+        f->sb16 = (uint16_t*)(base + o_sb);
+        f->rs.xs = (uint16_t*)(base + o_xs); f->rs.xe = (uint16_t*)(base + o_xe); f->rs.row = (uint16_t*)(base + o_row);
+        f->rs.parent = (int*)(base + o_par); f->rs.area2 = (int*)(base + o_area); f->rs.row_off = (int*)(base + o_roff);
+        f->rowL = (int*)(base + o_rl); f->rowR = (int*)(base + o_rr); f->scratch = (int*)(base + o_scr);
+    }
+    return off;
+}
+
+// 16 mask bytes that are all 0 or 1 (torch.bool storage) -> 16 bits: one multiply per word gathers its four flags (byte j's
+// bit 0 sits at bit 8j; the multiplier 2^24 + 2^17 + 2^10 + 2^3 moves it to bit 24 + j, all partial products on distinct
+// bits).  `other` collects every bit that is NOT a bit 0 of a byte: non-zero means the mask holds bytes above 1 and must
+// take the general (normalising) path.
+__device__ __forceinline__ uint32_t bits16_of_01(const uint4 v, uint32_t& other) {
+    other |= (v.x | v.y) | (v.z | v.w);
+    const uint32_t p0 = v.x * 0x01020408u, p1 = v.y * 0x01020408u, p2 = v.z * 0x01020408u, p3 = v.w * 0x01020408u;
+    return ((p0 >> 24) & 0xFu) | ((p1 >> 20) & 0xF0u) | ((p2 >> 16) & 0xF00u) | ((p3 >> 12) & 0xF000u);
+}
+
+// Wp <= 32 (W <= 1024)
+__global__ void __launch_bounds__(kT, 2) kb_front_kernel(const uint8_t* __restrict__ masks, int64_t n_masks, int H, int W,
+                                                        unsigned char* __restrict__ cand, uint8_t* __restrict__ out_has,
+                                                        int* __restrict__ lists, int rows, int raw_cap) {
+    extern __shared__ __align__(128) unsigned char fs_raw[];
+    __shared__ __align__(8) uint64_t mbar[kRing];
+    __shared__ int s_warp[kT / 32];
+    __shared__ uint32_t s_other;
+    FrontSmem f;
+    front_layout(H, W, raw_cap, &f, fs_raw);
+    const uint32_t* sb32 = reinterpret_cast<const uint32_t*>(f.sb16);
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int Wp = (W + 31) >> 5;
+    const uintptr_t base = reinterpret_cast<uintptr_t>(masks);
+    const int64_t mis = (int64_t)(base & 15);
+    const unsigned char* vbase = reinterpret_cast<const unsigned char*>(base - mis);
+    const int64_t HW = (int64_t)H * W;
+    const int tiles = (H + rows - 1) / rows;
+    int* list2 = lists + 4;
+    int* list3 = lists + 4 + n_masks;
+    const int64_t my_masks = ((int64_t)blockIdx.x < n_masks) ? (n_masks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const int64_t my_tiles = my_masks * tiles;
+    // g-th tile of this CTA's sequence: (mask, first row, chunk range in 16-byte units of the aligned mask array)
+    auto issue = [&](int64_t g) {
+        const int64_t m = blockIdx.x + (g / tiles) * gridDim.x;
+        const int r0 = (int)(g % tiles) * rows, r1 = min(H, r0 + rows);
+        const int64_t b0 = mis + m * HW + (int64_t)r0 * W, b1 = mis + m * HW + (int64_t)r1 * W;
+        const int64_t c0 = b0 >> 4;
+        const uint32_t bytes = (uint32_t)(((b1 + 15) >> 4) - c0) * 16u;
+        const int slot = (int)(g % kRing);
+        mbar_expect_tx(&mbar[slot], bytes);
+        bulk_load(f.raw0 + slot * f.raw_stride, vbase + (c0 << 4), bytes, &mbar[slot]);
+    };
+    if (tid == 0) {
+        for (int k = 0; k < kRing; ++k) mbar_init(&mbar[k], 1);
+        s_other = 0u;
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncthreads();
+    if (tid == 0)
+        for (int64_t g = 0; g < kRing - 1 && g < my_tiles; ++g) issue(g);
+    int64_t g = 0;                                     // running tile counter of this CTA
+    for (int64_t m = blockIdx.x; m < n_masks; m += gridDim.x) {
+        int Rbase = 0;                                 // runs emitted so far (uniform over the CTA)
+        uint32_t other = 0u;
+        for (int gr0 = 0; gr0 < H; gr0 += kGroupRows) {
+            // ---- a group of up to kGroupRows rows: its tiles arrive through the ring and become one flat bit stream ----
+            const int gr1 = min(H, gr0 + kGroupRows);
+            const int64_t gb0 = mis + m * HW + (int64_t)gr0 * W;
+            const int64_t gc0 = gb0 >> 4;                            // chunk that holds bit 0 of the stream
+            const int off0 = (int)(gb0 & 15);                        // position of pixel (gr0, 0) in it
+            for (int r0 = gr0; r0 < gr1; r0 += rows, ++g) {
+                const int slot = (int)(g % kRing);
+                // the slot of tile g + kRing - 1 was read during iteration g - 1; its readers passed that iteration's barrier
+                if (tid == 0 && g + kRing - 1 < my_tiles) issue(g + kRing - 1);
+                const int r1 = min(H, r0 + rows);
+                const int64_t b0 = mis + m * HW + (int64_t)r0 * W, b1 = mis + m * HW + (int64_t)r1 * W;
+                const int64_t c0 = b0 >> 4;
+                const int nch = (int)(((b1 + 15) >> 4) - c0);
+                mbar_wait(&mbar[slot], (uint32_t)(g / kRing) & 1u);
+                const uint4* rv = reinterpret_cast<const uint4*>(f.raw0 + slot * f.raw_stride);
+                uint16_t* dst = f.sb16 + (c0 - gc0);
+                for (int c = tid; c < nch; c += kT) dst[c] = (uint16_t)bits16_of_01(rv[c], other);
+                if (r1 == gr1 && tid < 4) dst[nch + tid] = 0;        // the funnel reads one word past the last chunk
+                __syncthreads();
+            }
+            // ---- runs of the group's rows, ONE THREAD PER ROW (a warp per row spends 32 issue slots on what is mostly empty
+            // or solid words): count, scan over the rows, emit ----
+            const StreamBits bits{sb32, off0, W};
+            const int r = gr0 + tid;
+            const bool live = r < gr1;
+            int cnt = 0;
+            if (live) {
+                uint32_t carry = 0u;
+                for (int w = 0; w < Wp; ++w) {
+                    const uint32_t mw = bits.word(tid, w);
+                    cnt += __popc(mw & ~((mw << 1) | carry));
+                    carry = mw >> 31;
+                }
+            }
+            int inc = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t2 = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += t2;
+            }
+            if (lane == 31) s_warp[wid] = inc;
+            __syncthreads();
+            int before = Rbase, total = 0;
+#pragma unroll
+            for (int w2 = 0; w2 < kT / 32; ++w2) { if (w2 < wid) before += s_warp[w2]; total += s_warp[w2]; }
+            const int rbase = before + inc - cnt;
+            if (live) {
+                f.rs.row_off[r] = rbase;
+                if (cnt) {
+                    int ks = rbase, ke = rbase;
+                    uint32_t carry = 0u, mw = bits.word(tid, 0);
+                    for (int w = 0; w < Wp; ++w) {
+                        const uint32_t nx = (w + 1 < Wp) ? bits.word(tid, w + 1) : 0u;
+                        uint32_t st = mw & ~((mw << 1) | carry), en = mw & ~((mw >> 1) | (nx << 31));
+                        for (; st; st &= st - 1, ++ks)
+                            if (ks < kRunCap) { f.rs.xs[ks] = (uint16_t)(32 * w + __ffs(st) - 1); f.rs.row[ks] = (uint16_t)r; }
+                        for (; en; en &= en - 1, ++ke)
+                            if (ke < kRunCap) f.rs.xe[ke] = (uint16_t)(32 * w + __ffs(en) - 1);
+                        carry = mw >> 31; mw = nx;
+                    }
+                }
+            }
+            Rbase += total;
+            __syncthreads();                           // s_warp and the stream are free again
+        }
+        const int R = Rbase;
+        // bytes above 1 anywhere in the mask (a uint8 mask that is not torch.bool storage): the general path normalises
+        other &= 0xFEFEFEFEu;
+        if (__any_sync(0xffffffffu, other != 0u) && lane == 0) atomicOr(&s_other, 1u);
+        if (tid == 0) f.rs.row_off[H] = R;
+        __syncthreads();
+        const bool not01 = s_other != 0u;
+        __syncthreads();
+        if (tid == 0) s_other = 0u;
+        if (not01 || R == 0 || R > kRunCap) {
+            if (tid == 0) {
+                if (not01 || R > kRunCap) { out_has[m] = 3; list3[atomicAdd(&lists[1], 1)] = (int)m; }   // general / overflow pass
+                else out_has[m] = 0;                                                        // empty mask: scorefunction.py:69-75
+            }
+            __syncthreads();
+            continue;
+        }
+        label_from_runs(f.rs, R);
+        bool ambiguous = false;
+        const int root = select_component(f.rs, R, true, f.scratch, &ambiguous);
+        if (ambiguous) {                               // hole filling could change the winner: the exact pass decides
+            if (tid == 0) { out_has[m] = 2; list2[atomicAdd(&lists[0], 1)] = (int)m; }
+            __syncthreads();
+            continue;
+        }
+        component_rows(f.rs, R, root, H, f.rowL, f.rowR, f.scratch + 32);
+        const int rmin = f.scratch[32 + 2], rmax = f.scratch[32 + 3];
+        unsigned char* rec = cand + (size_t)m * cand_stride(H);
+        int16_t* lr = reinterpret_cast<int16_t*>(rec + 8);
+        const int nrows = rmax - rmin + 1;
+        for (int rr = tid; rr < nrows; rr += kT) {
+            lr[2 * rr] = (int16_t)f.rowL[rmin + rr]; lr[2 * rr + 1] = (int16_t)f.rowR[rmin + rr];
+        }
+        if (tid == 0) { reinterpret_cast<int*>(rec)[0] = rmin; reinterpret_cast<int*>(rec)[1] = rmax; out_has[m] = kPending; }
+        __syncthreads();
+    }
+}
+
+struct TailSmem { int16_t* L; int16_t* R; int* keep; HullBuf hb; int* counts; float* out8; };
+__host__ __device__ inline size_t tail_layout(int H, TailSmem* t, unsigned char* base) {
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = align16(off + bytes); return o; };
+    const size_t o_cnt = take(24 * 4), o_out = take(8 * 4);
+    const size_t cc = (size_t)(H < kTailChainCap ? H : kTailChainCap);
+    const size_t o_rx = take(cc * 2), o_ry = take(cc * 2), o_lx = take(cc * 2), o_ly = take(cc * 2);
+    const size_t region = off;
+    const size_t o_L = take((size_t)H * 2), o_R = take((size_t)H * 2), o_keep = take((size_t)(H + 1) * 4);
+    const size_t end_a = off;
+    off = region;                                      // the float hull aliases the sieve's inputs (dead once compacted)
+    const size_t hn = (size_t)kTailHullCap;
+    const size_t o_inv = take(hn * 8), o_hx = take(hn * 4), o_hy = take(hn * 4), o_vx = take(hn * 4), o_vy = take(hn * 4), o_invf = take(hn * 4);
+    off = off > end_a ? off : end_a;
+    if (t) {
+        t->counts = (int*)(base + o_cnt); t->out8 = (float*)(base + o_out);
+        t->hb.rx = (int16_t*)(base + o_rx); t->hb.ry = (int16_t*)(base + o_ry); t->hb.lx = (int16_t*)(base + o_lx); t->hb.ly = (int16_t*)(base + o_ly);
+        t->L = (int16_t*)(base + o_L); t->R = (int16_t*)(base + o_R); t->keep = (int*)(base + o_keep);
+        t->hb.inv = (double*)(base + o_inv); t->hb.hx = (float*)(base + o_hx); t->hb.hy = (float*)(base + o_hy);
+        t->hb.vx = (float*)(base + o_vx); t->hb.vy = (float*)(base + o_vy); t->hb.invf = (float*)(base + o_invf);
+    }
+    return off;
+}
+
+__global__ void __launch_bounds__(32 * kTailWarps) kb_tail_kernel(const unsigned char* __restrict__ cand, int64_t n_masks, int H,
+                                                                float* __restrict__ out_rects, uint8_t* __restrict__ out_has,
+                                                                int* __restrict__ lists, size_t per_warp) {
+    extern __shared__ __align__(16) unsigned char ts_raw[];
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t m = (int64_t)blockIdx.x * kTailWarps + wid;
+    if (m >= n_masks) return;
+    if (out_has[m] != kPending) return;                // empty, or handed to the exact passes
+    TailSmem t;
+    tail_layout(H, &t, ts_raw + (size_t)wid * per_warp);
+    const unsigned char* rec = cand + (size_t)m * cand_stride(H);
+    const int rmin = reinterpret_cast<const int*>(rec)[0], rmax = reinterpret_cast<const int*>(rec)[1];
+    const int nrows = rmax - rmin + 1;
+    const uint32_t* lr = reinterpret_cast<const uint32_t*>(rec + 8);
+    for (int r = lane; r < nrows; r += 32) {
+        const uint32_t v = lr[r];
+        t.L[r] = (int16_t)(v & 0xffffu); t.R[r] = (int16_t)(v >> 16);
+    }
+    __syncwarp();
+    // the hull code indexes the extremes by absolute row
+    const bool ok = hull_rect<32, int16_t>(rmin, rmax, t.L - rmin, t.R - rmin, t.keep, t.hb, kTailHullCap, kTailChainCap, t.counts,
+                                           t.out8);
+    if (ok) {
+        if (lane < 8) out_rects[m * 8 + lane] = t.out8[lane];
+        if (lane == 0) out_has[m] = 1;
+    } else if (lane == 0) {                             // a hull beyond the warp's capacity: the overflow pass has room
+        int* list3 = lists + 4 + n_masks;
+        out_has[m] = 3; list3[atomicAdd(&lists[1], 1)] = (int)m;
+    }
+}
+
+// pack only the masks on the two work lists (what the exact passes will read); grid-stride over (listed mask, tile)
+__global__ void __launch_bounds__(kPackT, 8) pack_list_kernel(const uint8_t* __restrict__ masks, int64_t n_masks, int H, int W, int Wp,
+                                                             uint32_t* __restrict__ bitmap, int* __restrict__ rowrange,
+                                                             const int* __restrict__ lists, int tiles_per_mask) {
+    extern __shared__ __align__(16) unsigned char pk_raw[];
+    uint16_t* sb16 = reinterpret_cast<uint16_t*>(pk_raw);
+    const uint32_t* sb32 = reinterpret_cast<const uint32_t*>(pk_raw);
+    __shared__ int s_lo, s_hi;
+    const int tid = threadIdx.x;
+    const uintptr_t base = reinterpret_cast<uintptr_t>(masks);
+    const int64_t mis = (int64_t)(base & 15);
+    const uint4* v = reinterpret_cast<const uint4*>(base - mis);
+    const int64_t HW = (int64_t)H * W;
+    const int n2 = lists[0], n3 = lists[1];
+    const int* list2 = lists + 4;
+    const int* list3 = lists + 4 + n_masks;
+    const int64_t n_tiles = (int64_t)(n2 + n3) * tiles_per_mask;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int li = (int)(tile / tiles_per_mask);
+        const int64_t m = li < n2 ? list2[li] : list3[li - n2];
+        const int r0 = (int)(tile - (int64_t)li * tiles_per_mask) * kPackRows, r1 = min(H, r0 + kPackRows);
+        const int64_t b0 = mis + m * HW + (int64_t)r0 * W, b1 = mis + m * HW + (int64_t)r1 * W;
+        const int64_t c0 = b0 >> 4;
+        const int nch = (int)(((b1 + 15) >> 4) - c0);
+        if (tid == 0) { s_lo = 0x7fffffff; s_hi = -1; }
+        for (int c = tid; c < nch; c += kPackT) sb16[c] = (uint16_t)nz_bits16(__ldcs(v + c0 + c));
+        if (tid < 4) sb16[nch + tid] = 0;
+        __syncthreads();
+        const int nwords = (r1 - r0) * Wp;
+        int lo = 0x7fffffff, hi = -1;
+        for (int q = tid; q < nwords; q += kPackT) {
+            const int rr = q / Wp, w = q - rr * Wp, r = r0 + rr;
+            const int o = (int)(b0 - (c0 << 4)) + rr * W + 32 * w;
+            uint32_t word = __funnelshift_r(sb32[o >> 5], sb32[(o >> 5) + 1], o & 31);
+            const int nb = W - 32 * w;
+            if (nb < 32) word &= (1u << nb) - 1u;
+            bitmap[((size_t)m * H + r) * Wp + w] = word;
+            if (word) { lo = min(lo, r); hi = max(hi, r); }
+        }
+        lo = __reduce_min_sync(0xffffffffu, lo); hi = __reduce_max_sync(0xffffffffu, hi);
+        if ((tid & 31) == 0 && hi >= 0) { atomicMin(&s_lo, lo); atomicMax(&s_hi, hi); }
+        __syncthreads();
+        if (tid == 0 && s_hi >= 0) {
+            atomicMin(&rowrange[2 * m], s_lo);
+            atomicMin(&rowrange[2 * m + 1], H - 1 - s_hi);
+        }
+        __syncthreads();
+    }
+}
+
 }  // namespace
 
 constexpr int kExactCtas = 148;   // persistent CTAs of the exact pass
@@ -1045,11 +1442,32 @@ static size_t ws_fill_bytes(int H, int W) {
     return exact_needs_global(H, W) ? (size_t)kExactCtas * align16((size_t)H * ((W + 31) >> 5) * 4) : 0;
 }
 
+// workspace up to (not including) the fused path's per-mask extreme records
+static size_t ws_base_bytes(int64_t n_masks, int H, int W) {
+    const int64_t slots = n_masks < kSlots ? n_masks : kSlots;
+    return ws_bitmap_bytes(n_masks, H, W) + ws_range_bytes(n_masks) + ws_list_bytes(n_masks) + slots * slot_bytes(H, W) +
+           ws_fill_bytes(H, W);
+}
+
 extern "C" int64_t tdod_mask_rect_workspace_bytes(int64_t n_masks, int H, int W) {
     if (n_masks <= 0 || H <= 0 || W <= 0) return 16;
-    const int64_t slots = n_masks < kSlots ? n_masks : kSlots;
-    return (int64_t)(ws_bitmap_bytes(n_masks, H, W) + ws_range_bytes(n_masks) + ws_list_bytes(n_masks) + slots * slot_bytes(H, W) +
-                     ws_fill_bytes(H, W));
+    return (int64_t)(ws_base_bytes(n_masks, H, W) + (size_t)n_masks * cand_stride(H));
+}
+
+// shape of the fused path for an H x W mask: rows per TMA tile, ring slot capacity, shared memory of a front CTA, CTAs per
+// SM (0: does not fit -- wider than 1024 px, or the run arrays + ring exceed an SM)
+static int fused_plan(int H, int W, int* rows, int* raw_cap, size_t* smem) {
+    if (getenv("TDOD_KB_NO_FUSED") != nullptr || W > 1024) return 0;
+    const int try_rows[3] = {32, 16, 8};                // divisors of kGroupRows
+    for (int pass = 0; pass < 2; ++pass)                // first choice: two CTAs per SM with the deepest tiles that allow it
+        for (int k = 0; k < 3; ++k) {
+            const int r = try_rows[k];
+            const int max_chunks = (int)(((int64_t)r * W + 30) / 16 + 1);
+            const int cap = ((max_chunks * 16 + 127) / 128) * 128;
+            const size_t sm = front_layout(H, W, cap, nullptr, nullptr);
+            if (sm <= (pass == 0 ? 113u : 227u) * 1024) { *rows = r; *raw_cap = cap; *smem = sm; return pass == 0 ? 2 : 1; }
+        }
+    return 0;
 }
 
 namespace {
@@ -1082,6 +1500,8 @@ int kb_plan(int64_t n_masks, int H, int W, void* workspace, int64_t workspace_by
 }
 }  // namespace
 
+static tdod_smem_cache g_sm_front, g_sm_tail, g_sm_r0, g_sm_r1, g_sm_r2, g_sm_pack;
+
 extern "C" int tdod_mask_pack(const uint8_t* masks, int64_t n_masks, int H, int W, void* workspace, int64_t workspace_bytes,
                               void* stream) {
     if (n_masks == 0) return TDOD_OK;
@@ -1103,7 +1523,7 @@ extern "C" int tdod_mask_pack(const uint8_t* masks, int64_t n_masks, int H, int 
     const bool use_tma = tma_smem <= 100 * 1024 && n_tiles + 148 * 8 < 0x7fffffffll &&    // tile ids are divided in 32 bits
                          getenv("TDOD_PACK_NO_TMA") == nullptr;
     if (use_tma) {
-        e = cudaFuncSetAttribute(pack_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tma_smem);
+        e = tdod_smem_opt_in((const void*)pack_tma_kernel, tma_smem, &g_sm_pack);
         if (e != cudaSuccess) return (int)e;
         int per_sm = (int)((220 * 1024) / (tma_smem + 1024));
         per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
@@ -1127,11 +1547,11 @@ extern "C" int tdod_mask_rect_packed(int64_t n_masks, int H, int W, float* out_r
     const int rc = kb_plan(n_masks, H, W, workspace, workspace_bytes, &p, "rect");
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    cudaError_t e = cudaFuncSetAttribute(rect_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem1);
+    cudaError_t e = tdod_smem_opt_in((const void*)rect_kernel<false, false>, p.smem1, &g_sm_r0);
     if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(rect_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem2);
+    e = tdod_smem_opt_in((const void*)rect_kernel<true, false>, p.smem2, &g_sm_r1);
     if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(rect_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem2);
+    e = tdod_smem_opt_in((const void*)rect_kernel<true, true>, p.smem2, &g_sm_r2);
     if (e != cudaSuccess) return (int)e;
     // the state byte doubles as the work list of the later passes: every mask starts undecided
     e = cudaMemsetAsync(out_has_rect, 0xff, (size_t)n_masks, st);
@@ -1153,7 +1573,48 @@ extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int 
                               uint8_t* out_has_rect, void* workspace, int64_t workspace_bytes, void* stream) {
     if (n_masks == 0) return TDOD_OK;
     if (!masks || !out_rects || !out_has_rect) return tdod_fail(TDOD_EINVAL, "tdod_mask_rect: a pointer is NULL");
-    const int rc = tdod_mask_pack(masks, n_masks, H, W, workspace, workspace_bytes, stream);
+    int rows, raw_cap; size_t fsmem;
+    const int per_sm = fused_plan(H, W, &rows, &raw_cap, &fsmem);
+    if (per_sm == 0) {                                  // masks too large for the shared-memory bit stream: two-kernel path
+        const int rc = tdod_mask_pack(masks, n_masks, H, W, workspace, workspace_bytes, stream);
+        if (rc) return rc;
+        return tdod_mask_rect_packed(n_masks, H, W, out_rects, out_has_rect, workspace, workspace_bytes, stream);
+    }
+    KbPlan p;
+    const int rc = kb_plan(n_masks, H, W, workspace, workspace_bytes, &p, "fused");
     if (rc) return rc;
-    return tdod_mask_rect_packed(n_masks, H, W, out_rects, out_has_rect, workspace, workspace_bytes, stream);
+    if (n_masks > 0x7fffffff / 4) return tdod_fail(TDOD_ERANGE, "tdod_mask_rect: too many masks for one call");
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned char* cand = (unsigned char*)workspace + ws_base_bytes(n_masks, H, W);
+    const size_t per_warp = tail_layout(H, nullptr, nullptr);
+    const size_t tsmem = per_warp * kTailWarps;
+    if (tsmem > 227 * 1024) return tdod_fail(TDOD_ERANGE, "tdod_mask_rect: image too tall for the tail kernel");
+    cudaError_t e;
+    if ((e = tdod_smem_opt_in((const void*)kb_front_kernel, fsmem, &g_sm_front)) != cudaSuccess) return (int)e;
+    if ((e = tdod_smem_opt_in((const void*)kb_tail_kernel, tsmem, &g_sm_tail)) != cudaSuccess) return (int)e;
+    if ((e = tdod_smem_opt_in((const void*)rect_kernel<true, false>, p.smem2, &g_sm_r1)) != cudaSuccess) return (int)e;
+    if ((e = tdod_smem_opt_in((const void*)rect_kernel<true, true>, p.smem2, &g_sm_r2)) != cudaSuccess) return (int)e;
+    // rowrange = "no row seen" for the list-driven pack; work-list counters = 0
+    if ((e = cudaMemsetAsync(p.rowrange, 0x7f, (size_t)n_masks * 8, st)) != cudaSuccess) return (int)e;
+    if ((e = cudaMemsetAsync(p.lists, 0, 16, st)) != cudaSuccess) return (int)e;
+    const int64_t cap = (int64_t)148 * per_sm;
+    kb_front_kernel<<<(unsigned)(n_masks < cap ? n_masks : cap), kT, fsmem, st>>>(masks, n_masks, H, W, cand, out_has_rect, p.lists,
+                                                                                 rows, raw_cap);
+    TDOD_CHECK_LAUNCH();
+    kb_tail_kernel<<<(unsigned)((n_masks + kTailWarps - 1) / kTailWarps), 32 * kTailWarps, tsmem, st>>>(cand, n_masks, H, out_rects,
+                                                                                                      out_has_rect, p.lists, per_warp);
+    TDOD_CHECK_LAUNCH();
+    // the undecided rest (usually nobody): their bitmaps only, then the exact passes
+    const int tiles_per_mask = (H + kPackRows - 1) / kPackRows;
+    const size_t pk_smem = (size_t)(((int64_t)kPackRows * W + 30) / 16 + 8) * 2;
+    pack_list_kernel<<<148 * 2, kPackT, pk_smem, st>>>(masks, n_masks, H, W, p.Wp, p.bitmap, p.rowrange, p.lists, tiles_per_mask);
+    TDOD_CHECK_LAUNCH();
+    rect_kernel<true, false><<<(unsigned)(n_masks < kExactCtas ? n_masks : kExactCtas), kT, p.smem2, st>>>(
+        p.bitmap, p.rowrange, n_masks, H, W, out_rects, out_has_rect, nullptr, p.lists, p.fill_slots);
+    TDOD_CHECK_LAUNCH();
+    const unsigned nslots = (unsigned)(n_masks < kSlots ? n_masks : kSlots);
+    rect_kernel<true, true><<<nslots, kT, p.smem2, st>>>(p.bitmap, p.rowrange, n_masks, H, W, out_rects, out_has_rect, p.slots,
+                                                        p.lists, p.fill_slots);
+    TDOD_CHECK_LAUNCH();
+    return TDOD_OK;
 }

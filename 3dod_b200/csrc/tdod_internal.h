@@ -11,3 +11,18 @@ int tdod_fail(int code, const char* msg);
         cudaError_t e__ = cudaGetLastError();              \
         if (e__ != cudaSuccess) return (int)e__;           \
     } while (0)
+
+// Opt-in to more than 48 KB of dynamic shared memory for kernel `fn`, once per device and only ever upwards:
+// cudaFuncSetAttribute is a driver call (not something to pay on every launch), and setting a smaller value later would
+// lower the limit for a concurrent caller.  One cache object per kernel.
+struct tdod_smem_cache { size_t seen[64]; };
+inline cudaError_t tdod_smem_opt_in(const void* fn, size_t bytes, tdod_smem_cache* c) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    dev &= 63;
+    if (bytes <= c->seen[dev]) return cudaSuccess;
+    e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e == cudaSuccess) c->seen[dev] = bytes;
+    return e;
+}

@@ -69,9 +69,26 @@ def score_corners(rect, corners2d):
     return out
 
 
-def mask_rect(masks, mark=None, out=None):
-    """masks [n,H,W] bool/uint8 -> (rects [n,4,2] fp32, has_rect [n] uint8).  Two launches groups: the streaming pack
-    (mask bytes -> bitmap) and the rectangle passes; `mark(name)` is called between them ("kb_mid") when given."""
+_KB_WS = {}
+
+
+def _kb_workspace(n, H, W, dev):
+    """K-B scratch, cached per (device, stream, shape): the rectangle kernels allocate nothing, and asking torch for 0.2 GB
+    on every call costs more than the small-batch kernels themselves.  A cached block is only ever used on the stream it
+    was created for, so reuse is ordered like any other kernel of that stream."""
+    wsb = int(L.lib().tdod_mask_rect_workspace_bytes(n, H, W))
+    key = (dev.index if dev.index is not None else torch.cuda.current_device(), torch.cuda.current_stream(dev).cuda_stream)
+    ws = _KB_WS.get(key)
+    if ws is None or ws.numel() < wsb:
+        ws = torch.empty(max(wsb, 16), dtype=u8, device=dev)
+        _KB_WS[key] = ws
+    return ws, wsb
+
+
+def mask_rect(masks, mark=None, out=None, two_kernel=False):
+    """masks [n,H,W] bool/uint8 -> (rects [n,4,2] fp32, has_rect [n] uint8).  One call of tdod_mask_rect: the fused path
+    (bit stream in shared memory, extremes out, one warp per hull) when the mask fits, else pack + rectangle passes.
+    two_kernel=True forces the latter through its two entry points; `mark("kb_mid")` is then called between them."""
     m = _as_u8(masks)
     n, H, W = m.shape
     if out is not None:
@@ -79,8 +96,12 @@ def mask_rect(masks, mark=None, out=None):
     else:
         rects = torch.empty((n, 4, 2), dtype=f32, device=m.device)
         has = torch.empty(n, dtype=u8, device=m.device)
-    wsb = L.lib().tdod_mask_rect_workspace_bytes(n, H, W)
-    ws = torch.empty(max(int(wsb), 16), dtype=u8, device=m.device)
+    if n == 0:
+        return rects, has
+    ws, wsb = _kb_workspace(n, H, W, m.device)
+    if not two_kernel:
+        L.check(L.lib().tdod_mask_rect(L.ptr(m, u8, "masks"), n, H, W, L.ptr(rects), L.ptr(has), L.ptr(ws), wsb, L.stream_ptr()))
+        return rects, has
     L.check(L.lib().tdod_mask_pack(L.ptr(m, u8, "masks"), n, H, W, L.ptr(ws), wsb, L.stream_ptr()))
     if mark is not None:
         mark("kb_mid")
