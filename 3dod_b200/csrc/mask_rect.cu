@@ -943,8 +943,12 @@ __device__ int select_component(const RunSet& rs, int R, bool bounds_mode, int* 
             bool have_prev = false;
             long long ub2 = 0;
             for (int j = i + 1; j <= R; ++j) {
-                const bool mine = j < R && rs.parent[j] == i;
-                if (j < R && !mine) continue;
+                bool mine = j < R && rs.parent[j] == i;
+                if (j < R && !mine) {
+                    // runs are in raster order and a component has no empty row inside: a foreign run two rows below the
+                    // component's last one means it is complete -- flush as at the end of the list
+                    if ((int)rs.row[j] > crow + 1) j = R; else continue;
+                }
                 if (mine && (int)rs.row[j] == crow) { cl = min(cl, (int)rs.xs[j]); cr = max(cr, (int)rs.xe[j]); continue; }
                 // row `crow` is complete: pair it with the previous one
                 if (have_prev && pl <= cr && pr >= cl) ub2 += 2 * (min(cr, pr) - max(cl, pl)) + (cl != pl) + (cr != pr);
@@ -1146,7 +1150,7 @@ struct FrontSmem {
 };
 constexpr int kGroupRows = kT;          // rows whose bits are held at a time: one thread per row extracts their runs
 
-// rows: mask rows per TMA tile (divides kGroupRows); raw_cap: bytes of one ring slot
+// raw_cap: bytes of one ring slot
 __host__ __device__ inline size_t front_layout(int H, int W, int raw_cap, FrontSmem* f, unsigned char* base) {
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off = (off + bytes + 127) & ~size_t(127); return o; };
@@ -1178,38 +1182,51 @@ __device__ __forceinline__ uint32_t bits16_of_01(const uint4 v, uint32_t& other)
     return ((p0 >> 24) & 0xFu) | ((p1 >> 20) & 0xF0u) | ((p2 >> 16) & 0xF00u) | ((p3 >> 12) & 0xF000u);
 }
 
-// Wp <= 32 (W <= 1024)
+constexpr int kTileChunks = 3 * kT;     // 16-byte chunks per TMA tile (12 KB): three per thread, fixed trip count
+
+// Wp <= 32 (W <= 1024).  All positions inside a mask are 32-bit byte offsets from its 16-byte-aligned base `mptr`.
 __global__ void __launch_bounds__(kT, 2) kb_front_kernel(const uint8_t* __restrict__ masks, int64_t n_masks, int H, int W,
                                                         unsigned char* __restrict__ cand, uint8_t* __restrict__ out_has,
-                                                        int* __restrict__ lists, int rows, int raw_cap) {
+                                                        int* __restrict__ lists) {
     extern __shared__ __align__(128) unsigned char fs_raw[];
     __shared__ __align__(8) uint64_t mbar[kRing];
     __shared__ int s_warp[kT / 32];
     __shared__ uint32_t s_other;
     FrontSmem f;
-    front_layout(H, W, raw_cap, &f, fs_raw);
+    front_layout(H, W, kTileChunks * 16, &f, fs_raw);
     const uint32_t* sb32 = reinterpret_cast<const uint32_t*>(f.sb16);
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int Wp = (W + 31) >> 5;
     const uintptr_t base = reinterpret_cast<uintptr_t>(masks);
-    const int64_t mis = (int64_t)(base & 15);
-    const unsigned char* vbase = reinterpret_cast<const unsigned char*>(base - mis);
     const int64_t HW = (int64_t)H * W;
-    const int tiles = (H + rows - 1) / rows;
     int* list2 = lists + 4;
     int* list3 = lists + 4 + n_masks;
-    const int64_t my_masks = ((int64_t)blockIdx.x < n_masks) ? (n_masks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-    const int64_t my_tiles = my_masks * tiles;
-    // g-th tile of this CTA's sequence: (mask, first row, chunk range in 16-byte units of the aligned mask array)
-    auto issue = [&](int64_t g) {
-        const int64_t m = blockIdx.x + (g / tiles) * gridDim.x;
-        const int r0 = (int)(g % tiles) * rows, r1 = min(H, r0 + rows);
-        const int64_t b0 = mis + m * HW + (int64_t)r0 * W, b1 = mis + m * HW + (int64_t)r1 * W;
-        const int64_t c0 = b0 >> 4;
-        const uint32_t bytes = (uint32_t)(((b1 + 15) >> 4) - c0) * 16u;
-        const int slot = (int)(g % kRing);
-        mbar_expect_tx(&mbar[slot], bytes);
-        bulk_load(f.raw0 + slot * f.raw_stride, vbase + (c0 << 4), bytes, &mbar[slot]);
+    // ---- producer state (thread 0): the next tile to request, walking (mask, row group, tile) in the order it is consumed ----
+    int64_t pm = blockIdx.x;                            // mask
+    int pgr0 = 0, pc = 0, pn = 0;                       // group's first row; next chunk within the group; chunks of the group
+    const unsigned char* pptr = nullptr;                // address of the group's first chunk
+    int issued = 0;
+    auto group_of = [&](int64_t m, int gr0, const unsigned char*& gptr, int& nG) {
+        const uintptr_t a = base + (uintptr_t)(m * HW);
+        const int off_m = (int)(a & 15);
+        const int gr1 = min(H, gr0 + kGroupRows);
+        const int gc0 = (off_m + gr0 * W) >> 4, gc1 = (off_m + gr1 * W + 15) >> 4;
+        gptr = reinterpret_cast<const unsigned char*>(a - off_m) + ((size_t)gc0 << 4);
+        nG = gc1 - gc0;
+    };
+    auto issue_next = [&]() {                           // thread 0 only
+        if (pm >= n_masks) return;
+        const int nch = min(kTileChunks, pn - pc);
+        const int slot = issued & (kRing - 1);
+        mbar_expect_tx(&mbar[slot], (uint32_t)nch * 16u);
+        bulk_load(f.raw0 + slot * f.raw_stride, pptr + ((size_t)pc << 4), (uint32_t)nch * 16u, &mbar[slot]);
+        ++issued;
+        pc += kTileChunks;
+        if (pc >= pn) {
+            pc = 0; pgr0 += kGroupRows;
+            if (pgr0 >= H) { pgr0 = 0; pm += gridDim.x; }
+            if (pm < n_masks) group_of(pm, pgr0, pptr, pn);
+        }
     };
     if (tid == 0) {
         for (int k = 0; k < kRing; ++k) mbar_init(&mbar[k], 1);
@@ -1217,43 +1234,51 @@ __global__ void __launch_bounds__(kT, 2) kb_front_kernel(const uint8_t* __restri
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
-    if (tid == 0)
-        for (int64_t g = 0; g < kRing - 1 && g < my_tiles; ++g) issue(g);
-    int64_t g = 0;                                     // running tile counter of this CTA
+    if (tid == 0 && pm < n_masks) {
+        group_of(pm, 0, pptr, pn);
+        for (int k = 0; k < kRing - 1; ++k) issue_next();
+    }
+    int g = 0;                                          // tiles consumed by this CTA (ring slot g & 3, phase (g >> 2) & 1)
+    const int nb_last = W - 32 * (Wp - 1);              // valid bits of a row's last word
+    const uint32_t last_mask = nb_last < 32 ? ((1u << nb_last) - 1u) : 0xffffffffu;
     for (int64_t m = blockIdx.x; m < n_masks; m += gridDim.x) {
-        int Rbase = 0;                                 // runs emitted so far (uniform over the CTA)
+        int Rbase = 0;                                  // runs emitted so far (uniform over the CTA)
         uint32_t other = 0u;
+        const int off_m = (int)((base + (uintptr_t)(m * HW)) & 15);
         for (int gr0 = 0; gr0 < H; gr0 += kGroupRows) {
             // ---- a group of up to kGroupRows rows: its tiles arrive through the ring and become one flat bit stream ----
             const int gr1 = min(H, gr0 + kGroupRows);
-            const int64_t gb0 = mis + m * HW + (int64_t)gr0 * W;
-            const int64_t gc0 = gb0 >> 4;                            // chunk that holds bit 0 of the stream
-            const int off0 = (int)(gb0 & 15);                        // position of pixel (gr0, 0) in it
-            for (int r0 = gr0; r0 < gr1; r0 += rows, ++g) {
-                const int slot = (int)(g % kRing);
+            const int gb0 = off_m + gr0 * W;
+            const int gc0 = gb0 >> 4, nG = ((off_m + gr1 * W + 15) >> 4) - gc0;
+            const int off0 = gb0 & 15;                  // position of pixel (gr0, 0) in the stream
+            for (int tc = 0; tc < nG; tc += kTileChunks, ++g) {
+                const int slot = g & (kRing - 1);
                 // the slot of tile g + kRing - 1 was read during iteration g - 1; its readers passed that iteration's barrier
-                if (tid == 0 && g + kRing - 1 < my_tiles) issue(g + kRing - 1);
-                const int r1 = min(H, r0 + rows);
-                const int64_t b0 = mis + m * HW + (int64_t)r0 * W, b1 = mis + m * HW + (int64_t)r1 * W;
-                const int64_t c0 = b0 >> 4;
-                const int nch = (int)(((b1 + 15) >> 4) - c0);
-                mbar_wait(&mbar[slot], (uint32_t)(g / kRing) & 1u);
+                if (tid == 0) issue_next();
+                const int nch = min(kTileChunks, nG - tc);
+                mbar_wait(&mbar[slot], (uint32_t)(g >> 2) & 1u);
                 const uint4* rv = reinterpret_cast<const uint4*>(f.raw0 + slot * f.raw_stride);
-                uint16_t* dst = f.sb16 + (c0 - gc0);
-                for (int c = tid; c < nch; c += kT) dst[c] = (uint16_t)bits16_of_01(rv[c], other);
-                if (r1 == gr1 && tid < 4) dst[nch + tid] = 0;        // the funnel reads one word past the last chunk
+                uint16_t* dst = f.sb16 + tc;
+#pragma unroll
+                for (int u = 0; u < kTileChunks / kT; ++u) {
+                    const int c = tid + u * kT;
+                    if (c < nch) dst[c] = (uint16_t)bits16_of_01(rv[c], other);
+                }
+                if (tc + kTileChunks >= nG && tid < 4) dst[nch + tid] = 0;   // the funnel reads one word past the last chunk
                 __syncthreads();
             }
             // ---- runs of the group's rows, ONE THREAD PER ROW (a warp per row spends 32 issue slots on what is mostly empty
             // or solid words): count, scan over the rows, emit ----
-            const StreamBits bits{sb32, off0, W};
             const int r = gr0 + tid;
             const bool live = r < gr1;
+            const int o0 = off0 + tid * W;              // bit offset of this thread's row in the stream
             int cnt = 0;
             if (live) {
                 uint32_t carry = 0u;
-                for (int w = 0; w < Wp; ++w) {
-                    const uint32_t mw = bits.word(tid, w);
+                int o = o0;
+                for (int w = 0; w < Wp; ++w, o += 32) {
+                    uint32_t mw = __funnelshift_r(sb32[o >> 5], sb32[(o >> 5) + 1], o & 31);
+                    if (w == Wp - 1) mw &= last_mask;
                     cnt += __popc(mw & ~((mw << 1) | carry));
                     carry = mw >> 31;
                 }
@@ -1273,10 +1298,17 @@ __global__ void __launch_bounds__(kT, 2) kb_front_kernel(const uint8_t* __restri
             if (live) {
                 f.rs.row_off[r] = rbase;
                 if (cnt) {
-                    int ks = rbase, ke = rbase;
-                    uint32_t carry = 0u, mw = bits.word(tid, 0);
+                    int ks = rbase, ke = rbase, o = o0;
+                    uint32_t carry = 0u;
+                    uint32_t mw = __funnelshift_r(sb32[o >> 5], sb32[(o >> 5) + 1], o & 31);
+                    if (Wp == 1) mw &= last_mask;
                     for (int w = 0; w < Wp; ++w) {
-                        const uint32_t nx = (w + 1 < Wp) ? bits.word(tid, w + 1) : 0u;
+                        o += 32;
+                        uint32_t nx = 0u;
+                        if (w + 1 < Wp) {
+                            nx = __funnelshift_r(sb32[o >> 5], sb32[(o >> 5) + 1], o & 31);
+                            if (w + 2 == Wp) nx &= last_mask;
+                        }
                         uint32_t st = mw & ~((mw << 1) | carry), en = mw & ~((mw >> 1) | (nx << 31));
                         for (; st; st &= st - 1, ++ks)
                             if (ks < kRunCap) { f.rs.xs[ks] = (uint16_t)(32 * w + __ffs(st) - 1); f.rs.row[ks] = (uint16_t)r; }
@@ -1287,7 +1319,7 @@ __global__ void __launch_bounds__(kT, 2) kb_front_kernel(const uint8_t* __restri
                 }
             }
             Rbase += total;
-            __syncthreads();                           // s_warp and the stream are free again
+            __syncthreads();                            // s_warp and the stream are free again
         }
         const int R = Rbase;
         // bytes above 1 anywhere in the mask (a uint8 mask that is not torch.bool storage): the general path normalises
@@ -1309,7 +1341,7 @@ __global__ void __launch_bounds__(kT, 2) kb_front_kernel(const uint8_t* __restri
         label_from_runs(f.rs, R);
         bool ambiguous = false;
         const int root = select_component(f.rs, R, true, f.scratch, &ambiguous);
-        if (ambiguous) {                               // hole filling could change the winner: the exact pass decides
+        if (ambiguous) {                                // hole filling could change the winner: the exact pass decides
             if (tid == 0) { out_has[m] = 2; list2[atomicAdd(&lists[0], 1)] = (int)m; }
             __syncthreads();
             continue;
@@ -1454,19 +1486,14 @@ extern "C" int64_t tdod_mask_rect_workspace_bytes(int64_t n_masks, int H, int W)
     return (int64_t)(ws_base_bytes(n_masks, H, W) + (size_t)n_masks * cand_stride(H));
 }
 
-// shape of the fused path for an H x W mask: rows per TMA tile, ring slot capacity, shared memory of a front CTA, CTAs per
-// SM (0: does not fit -- wider than 1024 px, or the run arrays + ring exceed an SM)
-static int fused_plan(int H, int W, int* rows, int* raw_cap, size_t* smem) {
+// shape of the fused path for an H x W mask: shared memory of a front CTA and CTAs per SM (0: does not fit -- wider than
+// 1024 px, or the row tables + run arrays + ring exceed an SM)
+static int fused_plan(int H, int W, size_t* smem) {
     if (getenv("TDOD_KB_NO_FUSED") != nullptr || W > 1024) return 0;
-    const int try_rows[3] = {32, 16, 8};                // divisors of kGroupRows
-    for (int pass = 0; pass < 2; ++pass)                // first choice: two CTAs per SM with the deepest tiles that allow it
-        for (int k = 0; k < 3; ++k) {
-            const int r = try_rows[k];
-            const int max_chunks = (int)(((int64_t)r * W + 30) / 16 + 1);
-            const int cap = ((max_chunks * 16 + 127) / 128) * 128;
-            const size_t sm = front_layout(H, W, cap, nullptr, nullptr);
-            if (sm <= (pass == 0 ? 113u : 227u) * 1024) { *rows = r; *raw_cap = cap; *smem = sm; return pass == 0 ? 2 : 1; }
-        }
+    if ((int64_t)H * W + 64 > 0x7fffffff) return 0;       // positions inside a mask are 32-bit
+    *smem = front_layout(H, W, kTileChunks * 16, nullptr, nullptr);
+    if (*smem <= 113u * 1024) return 2;
+    if (*smem <= 227u * 1024) return 1;
     return 0;
 }
 
@@ -1573,8 +1600,8 @@ extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int 
                               uint8_t* out_has_rect, void* workspace, int64_t workspace_bytes, void* stream) {
     if (n_masks == 0) return TDOD_OK;
     if (!masks || !out_rects || !out_has_rect) return tdod_fail(TDOD_EINVAL, "tdod_mask_rect: a pointer is NULL");
-    int rows, raw_cap; size_t fsmem;
-    const int per_sm = fused_plan(H, W, &rows, &raw_cap, &fsmem);
+    size_t fsmem;
+    const int per_sm = fused_plan(H, W, &fsmem);
     if (per_sm == 0) {                                  // masks too large for the shared-memory bit stream: two-kernel path
         const int rc = tdod_mask_pack(masks, n_masks, H, W, workspace, workspace_bytes, stream);
         if (rc) return rc;
@@ -1598,8 +1625,8 @@ extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int 
     if ((e = cudaMemsetAsync(p.rowrange, 0x7f, (size_t)n_masks * 8, st)) != cudaSuccess) return (int)e;
     if ((e = cudaMemsetAsync(p.lists, 0, 16, st)) != cudaSuccess) return (int)e;
     const int64_t cap = (int64_t)148 * per_sm;
-    kb_front_kernel<<<(unsigned)(n_masks < cap ? n_masks : cap), kT, fsmem, st>>>(masks, n_masks, H, W, cand, out_has_rect, p.lists,
-                                                                                 rows, raw_cap);
+    kb_front_kernel<<<(unsigned)(n_masks < cap ? n_masks : cap), kT, fsmem, st>>>(masks, n_masks, H, W, cand, out_has_rect,
+                                                                                 p.lists);
     TDOD_CHECK_LAUNCH();
     kb_tail_kernel<<<(unsigned)((n_masks + kTailWarps - 1) / kTailWarps), 32 * kTailWarps, tsmem, st>>>(cand, n_masks, H, out_rects,
                                                                                                       out_has_rect, p.lists, per_warp);
