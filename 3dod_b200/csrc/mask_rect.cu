@@ -356,7 +356,27 @@ __device__ __forceinline__ int row_runs_warp(const Bits& bm, int Wp, int r, cons
 
 // label the runs of rows [r0, r1] of `bm` (8-connectivity; the rows outside are empty), accumulate twice the
 // cell-formula area at each root.  returns the number of runs, or -1 if they exceed the capacity.
-__device__ int label_from_runs(RunSet rs, int R);
+// A group of threads that synchronises among itself: the whole CTA, or a warp-aligned subset on a named barrier (the
+// extract / label half of a front CTA, while the other half keeps turning incoming bytes into bits).
+struct CtaGrp {
+    static __device__ __forceinline__ int tid() { return (int)threadIdx.x; }
+    static __device__ __forceinline__ int size() { return (int)blockDim.x; }
+    static __device__ __forceinline__ void sync() { __syncthreads(); }
+    static __device__ __forceinline__ int sync_or(int p) { return __syncthreads_or(p); }
+};
+template <int ID, int N, int T0> struct SubGrp {           // threads T0 .. T0 + N - 1 on named barrier ID
+    static __device__ __forceinline__ int tid() { return (int)threadIdx.x - T0; }
+    static __device__ __forceinline__ int size() { return N; }
+    static __device__ __forceinline__ void sync() { asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(N) : "memory"); }
+    static __device__ __forceinline__ int sync_or(int p) {
+        int r;
+        asm volatile("{\n.reg .pred pi, po;\nsetp.ne.s32 pi, %1, 0;\nbar.red.or.pred po, %2, %3, pi;\nselp.s32 %0, 1, 0, po;\n}"
+                     : "=r"(r) : "r"(p), "n"(ID), "n"(N) : "memory");
+        return r;
+    }
+};
+
+template <typename TG> __device__ int label_from_runs(RunSet rs, int R);
 
 template <typename Bits>
 __device__ int label_runs(const Bits bm, int H, int W, int Wp, RunSet rs, int* scratch, int cap, int r0, int r1) {
@@ -431,11 +451,12 @@ __device__ int label_runs(const Bits bm, int H, int W, int Wp, RunSet rs, int* s
         for (int r = r0 + wid; r <= r1; r += kWarps) row_runs_warp<true, Bits>(bm, Wp, r, rs, rs.row_off[r], cap);
     }
     __syncthreads();                                    // the runs were written by other warps
-    return label_from_runs(rs, R);
+    return label_from_runs<CtaGrp>(rs, R);
 }
 
 // Labels the R runs in `rs` (row_off filled for every row) and accumulates twice the cell-formula area at each root.
 // Called by all threads; returns R.
+template <typename TG>
 __device__ int label_from_runs(RunSet rs, int R) {
     // Labelling (8-connectivity).  A blob is a chain of one run per row, so hanging run i under the run above it
     // through union-find makes every later find walk the whole chain (quadratic in the rows).  Instead:
@@ -444,7 +465,7 @@ __device__ int label_from_runs(RunSet rs, int R) {
     //   2. pointer jumping flattens the forest (each round walks up to 8 links: 3-4 rounds for 500 rows);
     //   3. the remaining adjacencies -- a run touching several runs of the previous row -- are unions of roots;
     //   4. one short walk per run gives the final root = smallest run index of the component, as before.
-    for (int i = threadIdx.x; i < R; i += kT) {
+    for (int i = TG::tid(); i < R; i += TG::size()) {
         const int r = rs.row[i];
         int first = i;
         if (r != 0) {
@@ -457,20 +478,20 @@ __device__ int label_from_runs(RunSet rs, int R) {
         rs.parent[i] = first;
         rs.area2[i] = 0;
     }
-    __syncthreads();
+    TG::sync();
     KB_T(18);
     while (true) {
         int changed = 0;
-        for (int i = threadIdx.x; i < R; i += kT) {
+        for (int i = TG::tid(); i < R; i += TG::size()) {
             const int p0 = rs.parent[i];
             int p = p0;
 #pragma unroll
             for (int k = 0; k < 8; ++k) p = rs.parent[p];          // any value read is an ancestor: races are benign
             if (p != p0) { rs.parent[i] = p; changed = 1; }
         }
-        if (!__syncthreads_or(changed)) break;
+        if (!TG::sync_or(changed)) break;
     }
-    for (int i = threadIdx.x; i < R; i += kT) {
+    for (int i = TG::tid(); i < R; i += TG::size()) {
         const int r = rs.row[i];
         if (r == 0) continue;
         const int s = rs.xs[i], e = rs.xe[i];
@@ -483,13 +504,13 @@ __device__ int label_from_runs(RunSet rs, int R) {
             }
         }
     }
-    __syncthreads();
+    TG::sync();
     KB_T(19);
-    for (int i = threadIdx.x; i < R; i += kT) rs.parent[i] = uf_find(rs.parent, i);
-    __syncthreads();
+    for (int i = TG::tid(); i < R; i += TG::size()) rs.parent[i] = uf_find(rs.parent, i);
+    TG::sync();
     KB_T(20);
     // cell formula on pairs of overlapping runs in adjacent rows: 2*full + (#3-corner end cells)
-    for (int i = threadIdx.x; i < R; i += kT) {
+    for (int i = TG::tid(); i < R; i += TG::size()) {
         const int r = rs.row[i];
         if (r == 0) continue;
         const int s = rs.xs[i], e = rs.xe[i];
@@ -502,7 +523,7 @@ __device__ int label_from_runs(RunSet rs, int R) {
         }
         if (acc) atomicAdd(&rs.area2[rs.parent[i]], acc);
     }
-    __syncthreads();
+    TG::sync();
     return R;
 }
 
@@ -694,18 +715,19 @@ __device__ void calipers_box(const HullBuf& hb, int n, int* ext /*[4] smem*/, fl
 
 // Per-row extremes of the component `root` (its runs' leftmost start / rightmost end per row) and its row range ->
 // rowL / rowR [H], counts[2] = first row, counts[3] = last row.  Called by all threads of the CTA.
+template <typename TG>
 __device__ void component_rows(const RunSet& rs, int R, int root, int H, int* rowL, int* rowR, int* counts) {
-    const int tid = threadIdx.x;
+    const int tid = TG::tid();
     if (tid == 0) { counts[0] = 0; counts[1] = 0; counts[2] = 0x7fffffff; counts[3] = -1; }
-    for (int r = tid; r < H; r += kT) { rowL[r] = 0x7fffffff; rowR[r] = -1; }
-    __syncthreads();
-    for (int i = tid; i < R; i += kT)
+    for (int r = tid; r < H; r += TG::size()) { rowL[r] = 0x7fffffff; rowR[r] = -1; }
+    TG::sync();
+    for (int i = tid; i < R; i += TG::size())
         if (rs.parent[i] == root) {
             const int r = rs.row[i];
             atomicMin(&rowL[r], (int)rs.xs[i]); atomicMax(&rowR[r], (int)rs.xe[i]);
             atomicMin(&counts[2], r); atomicMax(&counts[3], r);
         }
-    __syncthreads();
+    TG::sync();
 }
 
 // Strict convex hull of a component from its per-row extremes (rows rmin..rmax, every row occupied: a connected
@@ -861,7 +883,7 @@ __device__ bool hull_rect(int rmin, int rmax, const RT* rowL, const RT* rowR, in
 // the CTA form used by the rectangle kernels: rows of the component `root`, then its hull and calipers
 __device__ bool component_rect(const RunSet& rs, int R, int root, int H, int* rowL, int* rowR, const HullBuf& hb,
                                int* counts, float* out8) {
-    component_rows(rs, R, root, H, rowL, rowR, counts);
+    component_rows<CtaGrp>(rs, R, root, H, rowL, rowR, counts);
     const int rmin = counts[2], rmax = counts[3];
     __syncthreads();
     // rs.row_off [H+1] is free from here on: the sieve's scratch
@@ -918,14 +940,15 @@ __host__ __device__ inline size_t smem_layout(int H, int Wp, bool two_bitmaps, S
 // pick the component with the largest area2 (ties: the larger root index = later first pixel in raster order).
 // In bounds mode also reports whether any OTHER component's hole-filled area could reach the winner's hole-free
 // area (then hole filling could change the answer and pass 2 must decide).
+template <typename TG>
 __device__ int select_component(const RunSet& rs, int R, bool bounds_mode, int* scratch, bool* ambiguous) {
     // scratch[0] = best key hi (area2), scratch[1] = best root, via a two-step atomicMax on a packed 64-bit key
     unsigned long long* key = reinterpret_cast<unsigned long long*>(scratch + 20);   // 8-byte aligned slot
-    if (threadIdx.x == 0) { *key = 0ull; scratch[24] = 0; }
-    __syncthreads();
-    for (int i = threadIdx.x; i < R; i += kT)
+    if (TG::tid() == 0) { *key = 0ull; scratch[24] = 0; }
+    TG::sync();
+    for (int i = TG::tid(); i < R; i += TG::size())
         if (rs.parent[i] == i) atomicMax(key, ((unsigned long long)(unsigned)rs.area2[i] << 32) | (unsigned)i);
-    __syncthreads();
+    TG::sync();
     const int best = (int)(*key & 0xffffffffu);
     const int best_a2 = (int)(*key >> 32);
     if (bounds_mode) {
@@ -937,7 +960,7 @@ __device__ int select_component(const RunSet& rs, int R, bool bounds_mode, int* 
         // Upper bound on a rival's hole-filled area: filling holes never leaves the per-row extent [L_r, R_r] of the
         // component, and the cell formula is monotone in the pixel set, so the area of the row-convexified component
         // bounds it.  One thread per rival walks the runs (raster order) once.
-        for (int i = threadIdx.x; i < R; i += kT) {
+        for (int i = TG::tid(); i < R; i += TG::size()) {
             if (rs.parent[i] != i || i == best) continue;
             int pl = 0, pr = -1, cl = rs.xs[i], cr = rs.xe[i], crow = rs.row[i];
             bool have_prev = false;
@@ -958,12 +981,12 @@ __device__ int select_component(const RunSet& rs, int R, bool bounds_mode, int* 
             // a rival that can at most TIE at area 0 cannot win either: ties go to the later component, which `best` is
             if (ub2 > (long long)best_a2 || (ub2 == (long long)best_a2 && ub2 > 0)) atomicOr(&scratch[24], 1);
         }
-        __syncthreads();
+        TG::sync();
         *ambiguous = scratch[24] != 0;
     } else {
         *ambiguous = false;
     }
-    __syncthreads();
+    TG::sync();
     return best;
 }
 
@@ -1109,7 +1132,7 @@ __global__ void __launch_bounds__(kT, kExact ? 1 : TDOD_KB_MINB) rect_kernel(con
             continue;
         }
         bool ambiguous = false;
-        const int root = select_component(s.rs, R, !kExact, s.scratch, &ambiguous);
+        const int root = select_component<CtaGrp>(s.rs, R, !kExact, s.scratch, &ambiguous);
         KB_T(3);
         if (ambiguous) {
             if (threadIdx.x == 0) { out_has[mi] = 2; list2[atomicAdd(&lists[0], 1)] = (int)mi; }
@@ -1144,27 +1167,36 @@ constexpr uint8_t kPending = 0xF0;      // state byte between the front and the 
 
 __host__ __device__ inline size_t cand_stride(int H) { return align16(8 + (size_t)H * 4); }   // {rmin, rmax} + int16 L/R per row
 
+// Front CTA = two halves that never meet at a CTA barrier.  PACK half (threads 0..127, thread 0 also drives the TMA ring):
+// bytes -> bits, group of rows after group of rows, into one of two bit-stream buffers.  EXTRACT half (threads 128..255):
+// runs of a finished group (one thread per row), and after a mask's last group its labels, areas, winner and the record.
+// The halves hand over through mbarriers (stream full / stream free), so while the extract half works on mask k the pack
+// half keeps HBM streaming for mask k + 1: the kernel's loads never pause for the labelling.
+constexpr int kHalf = 128;              // threads per half
+constexpr int kGroupRows = kHalf;       // rows per bit-stream buffer: one extract thread per row
+constexpr int kTileChunks = 768;        // 16-byte chunks per TMA tile (12 KB): six per pack thread
+using ExGrp = SubGrp<1, kHalf, kHalf>;
+
 struct FrontSmem {
-    unsigned char* raw0; size_t raw_stride; uint16_t* sb16;     // ring slot k at raw0 + k * raw_stride; bit stream of a row group
+    unsigned char* raw0; size_t raw_stride;            // ring slot k at raw0 + k * raw_stride
+    unsigned char* sb0; size_t sb_stride;               // two bit-stream buffers (a group of rows each): sb0 + b * sb_stride
     RunSet rs; int* rowL; int* rowR; int* scratch;
 };
-constexpr int kGroupRows = kT;          // rows whose bits are held at a time: one thread per row extracts their runs
-
-// raw_cap: bytes of one ring slot
-__host__ __device__ inline size_t front_layout(int H, int W, int raw_cap, FrontSmem* f, unsigned char* base) {
+__host__ __device__ inline size_t front_layout(int H, int W, FrontSmem* f, unsigned char* base) {
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off = (off + bytes + 127) & ~size_t(127); return o; };
-    const size_t o_raw = take(raw_cap);
+    const size_t o_raw = take((size_t)kTileChunks * 16);
     const size_t raw_stride = off - o_raw;
-    for (int k = 1; k < kRing; ++k) take(raw_cap);
-    const size_t o_sb = take(((size_t)kGroupRows * W + 15 + 7) / 8 + 48);   // misalignment in front, funnel over-read behind
+    for (int k = 1; k < kRing; ++k) take((size_t)kTileChunks * 16);
+    const size_t sbytes = ((size_t)kGroupRows * W + 15 + 7) / 8 + 48;       // misalignment in front, funnel over-read behind
+    const size_t o_sb0 = take(sbytes), o_sb1 = take(sbytes);
     const size_t o_xs = take(kRunCap * 2), o_xe = take(kRunCap * 2), o_row = take(kRunCap * 2);
     const size_t o_par = take(kRunCap * 4), o_area = take(kRunCap * 4);
     const size_t o_roff = take((size_t)(H + 1) * 4), o_rl = take((size_t)H * 4), o_rr = take((size_t)H * 4);
     const size_t o_scr = take((2 * (kT / 32) + 48) * 4);
     if (f) {
         f->raw0 = base + o_raw; f->raw_stride = raw_stride;
-        f->sb16 = (uint16_t*)(base + o_sb);
+        f->sb0 = base + o_sb0; f->sb_stride = o_sb1 - o_sb0;
         f->rs.xs = (uint16_t*)(base + o_xs); f->rs.xe = (uint16_t*)(base + o_xe); f->rs.row = (uint16_t*)(base + o_row);
         f->rs.parent = (int*)(base + o_par); f->rs.area2 = (int*)(base + o_area); f->rs.row_off = (int*)(base + o_roff);
         f->rowL = (int*)(base + o_rl); f->rowR = (int*)(base + o_rr); f->scratch = (int*)(base + o_scr);
@@ -1172,106 +1204,137 @@ __host__ __device__ inline size_t front_layout(int H, int W, int raw_cap, FrontS
     return off;
 }
 
-// 16 mask bytes that are all 0 or 1 (torch.bool storage) -> 16 bits: one multiply per word gathers its four flags (byte j's
-// bit 0 sits at bit 8j; the multiplier 2^24 + 2^17 + 2^10 + 2^3 moves it to bit 24 + j, all partial products on distinct
-// bits).  `other` collects every bit that is NOT a bit 0 of a byte: non-zero means the mask holds bytes above 1 and must
-// take the general (normalising) path.
+// 16 mask bytes that are all 0 or 1 (torch.bool storage) -> 16 bits.  Two words are merged first (word b's flags moved
+// to bit 4 of each byte: a + 16 b), then ONE multiply gathers the eight flags: a flag at bit 8k (+4) goes to bit 24 + k
+// (28 + k) through the multiplier term 2^(24 - 7k); every other partial product lands below bit 24 or above bit 31, on
+// pairwise distinct bits, so nothing carries into the byte.  `other` collects every bit that is NOT a bit 0 of a byte:
+// non-zero means the mask holds bytes above 1 and must take the general (normalising) path.
 __device__ __forceinline__ uint32_t bits16_of_01(const uint4 v, uint32_t& other) {
     other |= (v.x | v.y) | (v.z | v.w);
-    const uint32_t p0 = v.x * 0x01020408u, p1 = v.y * 0x01020408u, p2 = v.z * 0x01020408u, p3 = v.w * 0x01020408u;
-    return ((p0 >> 24) & 0xFu) | ((p1 >> 20) & 0xF0u) | ((p2 >> 16) & 0xF00u) | ((p3 >> 12) & 0xF000u);
+    const uint32_t p01 = (v.y * 16u + v.x) * 0x01020408u, p23 = (v.w * 16u + v.z) * 0x01020408u;
+    return (p01 >> 24) | ((p23 >> 16) & 0xFF00u);
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* b) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
 }
 
-constexpr int kTileChunks = 3 * kT;     // 16-byte chunks per TMA tile (12 KB): three per thread, fixed trip count
-
-// Wp <= 32 (W <= 1024).  All positions inside a mask are 32-bit byte offsets from its 16-byte-aligned base `mptr`.
-__global__ void __launch_bounds__(kT, 2) kb_front_kernel(const uint8_t* __restrict__ masks, int64_t n_masks, int H, int W,
-                                                        unsigned char* __restrict__ cand, uint8_t* __restrict__ out_has,
-                                                        int* __restrict__ lists) {
+// Wp <= 32 (W <= 1024).  All positions inside a mask are 32-bit byte offsets from its 16-byte-aligned base.
+__global__ void __launch_bounds__(2 * kHalf, 2) kb_front_kernel(const uint8_t* __restrict__ masks, int64_t n_masks, int H, int W,
+                                                               unsigned char* __restrict__ cand, uint8_t* __restrict__ out_has,
+                                                               int* __restrict__ lists) {
     extern __shared__ __align__(128) unsigned char fs_raw[];
-    __shared__ __align__(8) uint64_t mbar[kRing];
-    __shared__ int s_warp[kT / 32];
-    __shared__ uint32_t s_other;
+    __shared__ __align__(8) uint64_t mb_full[kRing];   // the tile's bytes have landed (TMA transaction count)
+    __shared__ __align__(8) uint64_t mb_free[kRing];   // all pack threads have turned the slot's bytes into bits
+    __shared__ __align__(8) uint64_t sb_full[2];       // the group's bit stream is complete (pack threads arrive)
+    __shared__ __align__(8) uint64_t sb_free[2];       // its runs have been extracted (extract threads arrive)
+    __shared__ int s_warp[kHalf / 32];
+    __shared__ uint32_t s_other[4];                     // per mask (index m' & 3): some byte of the mask is above 1
     FrontSmem f;
-    front_layout(H, W, kTileChunks * 16, &f, fs_raw);
-    const uint32_t* sb32 = reinterpret_cast<const uint32_t*>(f.sb16);
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    front_layout(H, W, &f, fs_raw);
+    const int tid = threadIdx.x;
     const int Wp = (W + 31) >> 5;
     const uintptr_t base = reinterpret_cast<uintptr_t>(masks);
     const int64_t HW = (int64_t)H * W;
-    int* list2 = lists + 4;
-    int* list3 = lists + 4 + n_masks;
-    // ---- producer state (thread 0): the next tile to request, walking (mask, row group, tile) in the order it is consumed ----
-    int64_t pm = blockIdx.x;                            // mask
-    int pgr0 = 0, pc = 0, pn = 0;                       // group's first row; next chunk within the group; chunks of the group
-    const unsigned char* pptr = nullptr;                // address of the group's first chunk
-    int issued = 0;
-    auto group_of = [&](int64_t m, int gr0, const unsigned char*& gptr, int& nG) {
-        const uintptr_t a = base + (uintptr_t)(m * HW);
-        const int off_m = (int)(a & 15);
-        const int gr1 = min(H, gr0 + kGroupRows);
-        const int gc0 = (off_m + gr0 * W) >> 4, gc1 = (off_m + gr1 * W + 15) >> 4;
-        gptr = reinterpret_cast<const unsigned char*>(a - off_m) + ((size_t)gc0 << 4);
-        nG = gc1 - gc0;
-    };
-    auto issue_next = [&]() {                           // thread 0 only
-        if (pm >= n_masks) return;
-        const int nch = min(kTileChunks, pn - pc);
-        const int slot = issued & (kRing - 1);
-        mbar_expect_tx(&mbar[slot], (uint32_t)nch * 16u);
-        bulk_load(f.raw0 + slot * f.raw_stride, pptr + ((size_t)pc << 4), (uint32_t)nch * 16u, &mbar[slot]);
-        ++issued;
-        pc += kTileChunks;
-        if (pc >= pn) {
-            pc = 0; pgr0 += kGroupRows;
-            if (pgr0 >= H) { pgr0 = 0; pm += gridDim.x; }
-            if (pm < n_masks) group_of(pm, pgr0, pptr, pn);
-        }
-    };
     if (tid == 0) {
-        for (int k = 0; k < kRing; ++k) mbar_init(&mbar[k], 1);
-        s_other = 0u;
+        for (int k = 0; k < kRing; ++k) { mbar_init(&mb_full[k], 1); mbar_init(&mb_free[k], kHalf); }
+        for (int k = 0; k < 2; ++k) { mbar_init(&sb_full[k], kHalf); mbar_init(&sb_free[k], kHalf); }
+        for (int k = 0; k < 4; ++k) s_other[k] = 0u;
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
-    if (tid == 0 && pm < n_masks) {
-        group_of(pm, 0, pptr, pn);
-        for (int k = 0; k < kRing - 1; ++k) issue_next();
+
+    if (tid < kHalf) {
+        // =============================== PACK half ===============================
+        // producer state (thread 0): the next tile to request, walking (mask, row group, tile) in the order it is consumed
+        int64_t pm = blockIdx.x;
+        int pgr0 = 0, pc = 0, pn = 0, issued = 0;
+        const unsigned char* pptr = nullptr;
+        auto group_of = [&](int64_t m, int gr0, const unsigned char*& gptr, int& nG) {
+            const uintptr_t a = base + (uintptr_t)(m * HW);
+            const int off_m = (int)(a & 15);
+            const int gr1 = min(H, gr0 + kGroupRows);
+            const int gc0 = (off_m + gr0 * W) >> 4, gc1 = (off_m + gr1 * W + 15) >> 4;
+            gptr = reinterpret_cast<const unsigned char*>(a - off_m) + ((size_t)gc0 << 4);
+            nG = gc1 - gc0;
+        };
+        auto issue_next = [&]() {                       // thread 0 only
+            if (pm >= n_masks) return;
+            const int nch = min(kTileChunks, pn - pc);
+            const int slot = issued & (kRing - 1);
+            // refilling a slot: its previous tile (number issued - kRing) must have been packed by every pack thread
+            if (issued >= kRing) mbar_wait(&mb_free[slot], (uint32_t)((issued >> 2) - 1) & 1u);
+            mbar_expect_tx(&mb_full[slot], (uint32_t)nch * 16u);
+            bulk_load(f.raw0 + slot * f.raw_stride, pptr + ((size_t)pc << 4), (uint32_t)nch * 16u, &mb_full[slot]);
+            ++issued;
+            pc += kTileChunks;
+            if (pc >= pn) {
+                pc = 0; pgr0 += kGroupRows;
+                if (pgr0 >= H) { pgr0 = 0; pm += gridDim.x; }
+                if (pm < n_masks) group_of(pm, pgr0, pptr, pn);
+            }
+        };
+        if (tid == 0 && pm < n_masks) {
+            group_of(pm, 0, pptr, pn);
+            for (int k = 0; k < kRing - 1; ++k) issue_next();
+        }
+        int g = 0, gs = 0;                              // tiles / groups handled so far by this CTA
+        int mi = 0;                                     // masks handled so far
+        for (int64_t m = blockIdx.x; m < n_masks; m += gridDim.x, ++mi) {
+            uint32_t other = 0u;
+            const int off_m = (int)((base + (uintptr_t)(m * HW)) & 15);
+            for (int gr0 = 0; gr0 < H; gr0 += kGroupRows, ++gs) {
+                const int gr1 = min(H, gr0 + kGroupRows);
+                const int gc0 = (off_m + gr0 * W) >> 4, nG = ((off_m + gr1 * W + 15) >> 4) - gc0;
+                const int b = gs & 1;
+                // the buffer's previous group (two back) must have been read by the extract half
+                if (gs >= 2) mbar_wait(&sb_free[b], (uint32_t)((gs >> 1) - 1) & 1u);
+                uint16_t* stream = reinterpret_cast<uint16_t*>(f.sb0 + b * f.sb_stride);
+                for (int tc = 0; tc < nG; tc += kTileChunks, ++g) {
+                    const int slot = g & (kRing - 1);
+                    if (tid == 0) issue_next();         // tile g + kRing - 1
+                    const int nch = min(kTileChunks, nG - tc);
+                    mbar_wait(&mb_full[slot], (uint32_t)(g >> 2) & 1u);
+                    const uint4* rv = reinterpret_cast<const uint4*>(f.raw0 + slot * f.raw_stride);
+                    uint16_t* dst = stream + tc;
+#pragma unroll
+                    for (int u = 0; u < kTileChunks / kHalf; ++u) {
+                        const int c = tid + u * kHalf;
+                        if (c < nch) dst[c] = (uint16_t)bits16_of_01(rv[c], other);
+                    }
+                    if (tc + kTileChunks >= nG && tid < 4) dst[nch + tid] = 0;   // the funnel reads one word past the last chunk
+                    mbar_arrive(&mb_free[slot]);
+                }
+                if (gr1 == H) {                         // last group of the mask: publish whether any byte was above 1
+                    other &= 0xFEFEFEFEu;
+                    if (__any_sync(0xffffffffu, other != 0u) && (tid & 31) == 0) atomicOr(&s_other[mi & 3], 1u);
+                }
+                mbar_arrive(&sb_full[b]);               // (release: the stream and the flag are visible to whoever waits)
+            }
+        }
+        return;
     }
-    int g = 0;                                          // tiles consumed by this CTA (ring slot g & 3, phase (g >> 2) & 1)
+
+    // =============================== EXTRACT half ===============================
+    const int et = tid - kHalf, lane = et & 31, wid = et >> 5;
+    int* list2 = lists + 4;
+    int* list3 = lists + 4 + n_masks;
     const int nb_last = W - 32 * (Wp - 1);              // valid bits of a row's last word
     const uint32_t last_mask = nb_last < 32 ? ((1u << nb_last) - 1u) : 0xffffffffu;
-    for (int64_t m = blockIdx.x; m < n_masks; m += gridDim.x) {
-        int Rbase = 0;                                  // runs emitted so far (uniform over the CTA)
-        uint32_t other = 0u;
+    int gs = 0, mi = 0;
+    for (int64_t m = blockIdx.x; m < n_masks; m += gridDim.x, ++mi) {
+        int Rbase = 0;                                  // runs emitted so far (uniform over the half)
         const int off_m = (int)((base + (uintptr_t)(m * HW)) & 15);
-        for (int gr0 = 0; gr0 < H; gr0 += kGroupRows) {
-            // ---- a group of up to kGroupRows rows: its tiles arrive through the ring and become one flat bit stream ----
+        for (int gr0 = 0; gr0 < H; gr0 += kGroupRows, ++gs) {
             const int gr1 = min(H, gr0 + kGroupRows);
-            const int gb0 = off_m + gr0 * W;
-            const int gc0 = gb0 >> 4, nG = ((off_m + gr1 * W + 15) >> 4) - gc0;
-            const int off0 = gb0 & 15;                  // position of pixel (gr0, 0) in the stream
-            for (int tc = 0; tc < nG; tc += kTileChunks, ++g) {
-                const int slot = g & (kRing - 1);
-                // the slot of tile g + kRing - 1 was read during iteration g - 1; its readers passed that iteration's barrier
-                if (tid == 0) issue_next();
-                const int nch = min(kTileChunks, nG - tc);
-                mbar_wait(&mbar[slot], (uint32_t)(g >> 2) & 1u);
-                const uint4* rv = reinterpret_cast<const uint4*>(f.raw0 + slot * f.raw_stride);
-                uint16_t* dst = f.sb16 + tc;
-#pragma unroll
-                for (int u = 0; u < kTileChunks / kT; ++u) {
-                    const int c = tid + u * kT;
-                    if (c < nch) dst[c] = (uint16_t)bits16_of_01(rv[c], other);
-                }
-                if (tc + kTileChunks >= nG && tid < 4) dst[nch + tid] = 0;   // the funnel reads one word past the last chunk
-                __syncthreads();
-            }
+            const int off0 = (off_m + gr0 * W) & 15;    // position of pixel (gr0, 0) in the stream
+            const int b = gs & 1;
+            mbar_wait(&sb_full[b], (uint32_t)(gs >> 1) & 1u);
+            const uint32_t* sb32 = reinterpret_cast<const uint32_t*>(f.sb0 + b * f.sb_stride);
             // ---- runs of the group's rows, ONE THREAD PER ROW (a warp per row spends 32 issue slots on what is mostly empty
             // or solid words): count, scan over the rows, emit ----
-            const int r = gr0 + tid;
+            const int r = gr0 + et;
             const bool live = r < gr1;
-            const int o0 = off0 + tid * W;              // bit offset of this thread's row in the stream
+            const int o0 = off0 + et * W;               // bit offset of this thread's row in the stream
             int cnt = 0;
             if (live) {
                 uint32_t carry = 0u;
@@ -1290,10 +1353,10 @@ __global__ void __launch_bounds__(kT, 2) kb_front_kernel(const uint8_t* __restri
                 if (lane >= o) inc += t2;
             }
             if (lane == 31) s_warp[wid] = inc;
-            __syncthreads();
+            ExGrp::sync();
             int before = Rbase, total = 0;
 #pragma unroll
-            for (int w2 = 0; w2 < kT / 32; ++w2) { if (w2 < wid) before += s_warp[w2]; total += s_warp[w2]; }
+            for (int w2 = 0; w2 < kHalf / 32; ++w2) { if (w2 < wid) before += s_warp[w2]; total += s_warp[w2]; }
             const int rbase = before + inc - cnt;
             if (live) {
                 f.rs.row_off[r] = rbase;
@@ -1319,43 +1382,40 @@ __global__ void __launch_bounds__(kT, 2) kb_front_kernel(const uint8_t* __restri
                 }
             }
             Rbase += total;
-            __syncthreads();                            // s_warp and the stream are free again
+            mbar_arrive(&sb_free[b]);                   // this thread is done with the stream buffer
+            ExGrp::sync();                              // s_warp is free again; the runs are visible to the half
         }
         const int R = Rbase;
-        // bytes above 1 anywhere in the mask (a uint8 mask that is not torch.bool storage): the general path normalises
-        other &= 0xFEFEFEFEu;
-        if (__any_sync(0xffffffffu, other != 0u) && lane == 0) atomicOr(&s_other, 1u);
-        if (tid == 0) f.rs.row_off[H] = R;
-        __syncthreads();
-        const bool not01 = s_other != 0u;
-        __syncthreads();
-        if (tid == 0) s_other = 0u;
+        const bool not01 = s_other[mi & 3] != 0u;       // (visible: ordered by the wait on the last group's sb_full)
+        if (et == 0) f.rs.row_off[H] = R;
+        ExGrp::sync();
+        if (et == 0) s_other[mi & 3] = 0u;              // reused four masks on; the pack half is at most two groups ahead
         if (not01 || R == 0 || R > kRunCap) {
-            if (tid == 0) {
+            if (et == 0) {
                 if (not01 || R > kRunCap) { out_has[m] = 3; list3[atomicAdd(&lists[1], 1)] = (int)m; }   // general / overflow pass
                 else out_has[m] = 0;                                                        // empty mask: scorefunction.py:69-75
             }
-            __syncthreads();
+            ExGrp::sync();
             continue;
         }
-        label_from_runs(f.rs, R);
+        label_from_runs<ExGrp>(f.rs, R);
         bool ambiguous = false;
-        const int root = select_component(f.rs, R, true, f.scratch, &ambiguous);
+        const int root = select_component<ExGrp>(f.rs, R, true, f.scratch, &ambiguous);
         if (ambiguous) {                                // hole filling could change the winner: the exact pass decides
-            if (tid == 0) { out_has[m] = 2; list2[atomicAdd(&lists[0], 1)] = (int)m; }
-            __syncthreads();
+            if (et == 0) { out_has[m] = 2; list2[atomicAdd(&lists[0], 1)] = (int)m; }
+            ExGrp::sync();
             continue;
         }
-        component_rows(f.rs, R, root, H, f.rowL, f.rowR, f.scratch + 32);
+        component_rows<ExGrp>(f.rs, R, root, H, f.rowL, f.rowR, f.scratch + 32);
         const int rmin = f.scratch[32 + 2], rmax = f.scratch[32 + 3];
         unsigned char* rec = cand + (size_t)m * cand_stride(H);
         int16_t* lr = reinterpret_cast<int16_t*>(rec + 8);
         const int nrows = rmax - rmin + 1;
-        for (int rr = tid; rr < nrows; rr += kT) {
+        for (int rr = et; rr < nrows; rr += kHalf) {
             lr[2 * rr] = (int16_t)f.rowL[rmin + rr]; lr[2 * rr + 1] = (int16_t)f.rowR[rmin + rr];
         }
-        if (tid == 0) { reinterpret_cast<int*>(rec)[0] = rmin; reinterpret_cast<int*>(rec)[1] = rmax; out_has[m] = kPending; }
-        __syncthreads();
+        if (et == 0) { reinterpret_cast<int*>(rec)[0] = rmin; reinterpret_cast<int*>(rec)[1] = rmax; out_has[m] = kPending; }
+        ExGrp::sync();
     }
 }
 
@@ -1491,7 +1551,7 @@ extern "C" int64_t tdod_mask_rect_workspace_bytes(int64_t n_masks, int H, int W)
 static int fused_plan(int H, int W, size_t* smem) {
     if (getenv("TDOD_KB_NO_FUSED") != nullptr || W > 1024) return 0;
     if ((int64_t)H * W + 64 > 0x7fffffff) return 0;       // positions inside a mask are 32-bit
-    *smem = front_layout(H, W, kTileChunks * 16, nullptr, nullptr);
+    *smem = front_layout(H, W, nullptr, nullptr);
     if (*smem <= 113u * 1024) return 2;
     if (*smem <= 227u * 1024) return 1;
     return 0;
@@ -1625,7 +1685,7 @@ extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int 
     if ((e = cudaMemsetAsync(p.rowrange, 0x7f, (size_t)n_masks * 8, st)) != cudaSuccess) return (int)e;
     if ((e = cudaMemsetAsync(p.lists, 0, 16, st)) != cudaSuccess) return (int)e;
     const int64_t cap = (int64_t)148 * per_sm;
-    kb_front_kernel<<<(unsigned)(n_masks < cap ? n_masks : cap), kT, fsmem, st>>>(masks, n_masks, H, W, cand, out_has_rect,
+    kb_front_kernel<<<(unsigned)(n_masks < cap ? n_masks : cap), 2 * kHalf, fsmem, st>>>(masks, n_masks, H, W, cand, out_has_rect,
                                                                                  p.lists);
     TDOD_CHECK_LAUNCH();
     kb_tail_kernel<<<(unsigned)((n_masks + kTailWarps - 1) / kTailWarps), 32 * kTailWarps, tsmem, st>>>(cand, n_masks, H, out_rects,
