@@ -1172,10 +1172,11 @@ __host__ __device__ inline size_t cand_stride(int H) { return align16(8 + (size_
 // runs of a finished group (one thread per row), and after a mask's last group its labels, areas, winner and the record.
 // The halves hand over through mbarriers (stream full / stream free), so while the extract half works on mask k the pack
 // half keeps HBM streaming for mask k + 1: the kernel's loads never pause for the labelling.
-constexpr int kHalf = 128;              // threads per half
-constexpr int kGroupRows = kHalf;       // rows per bit-stream buffer: one extract thread per row
+constexpr int kHalf = 128;              // pack threads
+constexpr int kExT = 256;               // extract / label threads
+constexpr int kGroupRows = kExT / 2;    // rows per bit-stream buffer: two extract threads per row
 constexpr int kTileChunks = 768;        // 16-byte chunks per TMA tile (12 KB): six per pack thread
-using ExGrp = SubGrp<1, kHalf, kHalf>;
+using ExGrp = SubGrp<1, kExT, kHalf>;
 
 struct FrontSmem {
     unsigned char* raw0; size_t raw_stride;            // ring slot k at raw0 + k * raw_stride
@@ -1219,7 +1220,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* b) {
 }
 
 // Wp <= 32 (W <= 1024).  All positions inside a mask are 32-bit byte offsets from its 16-byte-aligned base.
-__global__ void __launch_bounds__(2 * kHalf, 2) kb_front_kernel(const uint8_t* __restrict__ masks, int64_t n_masks, int H, int W,
+__global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t* __restrict__ masks, int64_t n_masks, int H, int W,
                                                                unsigned char* __restrict__ cand, uint8_t* __restrict__ out_has,
                                                                int* __restrict__ lists) {
     extern __shared__ __align__(128) unsigned char fs_raw[];
@@ -1227,7 +1228,7 @@ __global__ void __launch_bounds__(2 * kHalf, 2) kb_front_kernel(const uint8_t* _
     __shared__ __align__(8) uint64_t mb_free[kRing];   // all pack threads have turned the slot's bytes into bits
     __shared__ __align__(8) uint64_t sb_full[2];       // the group's bit stream is complete (pack threads arrive)
     __shared__ __align__(8) uint64_t sb_free[2];       // its runs have been extracted (extract threads arrive)
-    __shared__ int s_warp[kHalf / 32];
+    __shared__ int s_warp[kExT / 32];
     __shared__ uint32_t s_other[4];                     // per mask (index m' & 3): some byte of the mask is above 1
     FrontSmem f;
     front_layout(H, W, &f, fs_raw);
@@ -1237,7 +1238,7 @@ __global__ void __launch_bounds__(2 * kHalf, 2) kb_front_kernel(const uint8_t* _
     const int64_t HW = (int64_t)H * W;
     if (tid == 0) {
         for (int k = 0; k < kRing; ++k) { mbar_init(&mb_full[k], 1); mbar_init(&mb_free[k], kHalf); }
-        for (int k = 0; k < 2; ++k) { mbar_init(&sb_full[k], kHalf); mbar_init(&sb_free[k], kHalf); }
+        for (int k = 0; k < 2; ++k) { mbar_init(&sb_full[k], kHalf); mbar_init(&sb_free[k], kExT); }
         for (int k = 0; k < 4; ++k) s_other[k] = 0u;
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -1296,10 +1297,15 @@ __global__ void __launch_bounds__(2 * kHalf, 2) kb_front_kernel(const uint8_t* _
                     mbar_wait(&mb_full[slot], (uint32_t)(g >> 2) & 1u);
                     const uint4* rv = reinterpret_cast<const uint4*>(f.raw0 + slot * f.raw_stride);
                     uint16_t* dst = stream + tc;
+                    // all six loads first (index clamped, so always inside the tile): six LDS.128 in flight per thread
+                    uint4 v[kTileChunks / kHalf];
+#pragma unroll
+                    for (int u = 0; u < kTileChunks / kHalf; ++u) v[u] = rv[min(tid + u * kHalf, nch - 1)];
 #pragma unroll
                     for (int u = 0; u < kTileChunks / kHalf; ++u) {
                         const int c = tid + u * kHalf;
-                        if (c < nch) dst[c] = (uint16_t)bits16_of_01(rv[c], other);
+                        const uint32_t bits = bits16_of_01(v[u], other);     // (a clamped duplicate only repeats a chunk of the mask)
+                        if (c < nch) dst[c] = (uint16_t)bits;
                     }
                     if (tc + kTileChunks >= nG && tid < 4) dst[nch + tid] = 0;   // the funnel reads one word past the last chunk
                     mbar_arrive(&mb_free[slot]);
@@ -1330,23 +1336,36 @@ __global__ void __launch_bounds__(2 * kHalf, 2) kb_front_kernel(const uint8_t* _
             const int b = gs & 1;
             mbar_wait(&sb_full[b], (uint32_t)(gs >> 1) & 1u);
             const uint32_t* sb32 = reinterpret_cast<const uint32_t*>(f.sb0 + b * f.sb_stride);
-            // ---- runs of the group's rows, ONE THREAD PER ROW (a warp per row spends 32 issue slots on what is mostly empty
-            // or solid words): count, scan over the rows, emit ----
-            const int r = gr0 + et;
+            // ---- runs of the group's rows, TWO THREADS PER ROW, each walking half of the row's words (a warp per row spends 32
+            // issue slots on what is mostly empty or solid words).  Thread order = raster order of the segments, so one scan
+            // of the packed (starts, ends) counts places every segment in the run arrays: the k-th start of a row pairs
+            // with its k-th end wherever the segment boundary falls ----
+            const int rloc = et >> 1, half = et & 1;
+            const int r = gr0 + rloc;
             const bool live = r < gr1;
-            const int o0 = off0 + et * W;               // bit offset of this thread's row in the stream
-            int cnt = 0;
-            if (live) {
-                uint32_t carry = 0u;
-                int o = o0;
-                for (int w = 0; w < Wp; ++w, o += 32) {
-                    uint32_t mw = __funnelshift_r(sb32[o >> 5], sb32[(o >> 5) + 1], o & 31);
+            const int Wh = (Wp + 1) >> 1;
+            const int w0 = half ? Wh : 0, w1 = half ? Wp : Wh;
+            const int o0 = off0 + rloc * W;             // bit offset of this thread's row in the stream
+            auto sbit = [&](int pos) { return (sb32[pos >> 5] >> (pos & 31)) & 1u; };
+            int ns = 0, ne = 0;
+            uint32_t carry_in = 0u;
+            if (live && w0 < w1) {
+                carry_in = w0 ? sbit(o0 + 32 * w0 - 1) : 0u;
+                uint32_t carry = carry_in, first = 0u, mw = 0u;
+                int o = o0 + 32 * w0;
+                for (int w = w0; w < w1; ++w, o += 32) {
+                    mw = __funnelshift_r(sb32[o >> 5], sb32[(o >> 5) + 1], o & 31);
                     if (w == Wp - 1) mw &= last_mask;
-                    cnt += __popc(mw & ~((mw << 1) | carry));
+                    if (w == w0) first = mw & 1u;
+                    ns += __popc(mw & ~((mw << 1) | carry));
                     carry = mw >> 31;
                 }
+                // ends inside the segment = starts inside it + a run open at its left edge - a run open at its right edge
+                const uint32_t after = (w1 < Wp) ? sbit(o0 + 32 * w1) : 0u;     // (bit 0 of a row's last word is always a pixel)
+                ne = ns + (int)(carry_in & first) - (int)(carry & after);
             }
-            int inc = cnt;
+            const int pk = ns | (ne << 16);
+            int inc = pk;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const int t2 = __shfl_up_sync(0xffffffffu, inc, o);
@@ -1354,18 +1373,19 @@ __global__ void __launch_bounds__(2 * kHalf, 2) kb_front_kernel(const uint8_t* _
             }
             if (lane == 31) s_warp[wid] = inc;
             ExGrp::sync();
-            int before = Rbase, total = 0;
+            int before = 0, total = 0;
 #pragma unroll
-            for (int w2 = 0; w2 < kHalf / 32; ++w2) { if (w2 < wid) before += s_warp[w2]; total += s_warp[w2]; }
-            const int rbase = before + inc - cnt;
+            for (int w2 = 0; w2 < kExT / 32; ++w2) { if (w2 < wid) before += s_warp[w2]; total += s_warp[w2]; }
+            total &= 0xffff;                            // starts == ends over whole rows
+            const int excl = before + inc - pk;
             if (live) {
-                f.rs.row_off[r] = rbase;
-                if (cnt) {
-                    int ks = rbase, ke = rbase, o = o0;
-                    uint32_t carry = 0u;
+                if (half == 0) f.rs.row_off[r] = Rbase + (excl & 0xffff);
+                if (pk) {
+                    int ks = Rbase + (excl & 0xffff), ke = Rbase + (excl >> 16), o = o0 + 32 * w0;
+                    uint32_t carry = carry_in;
                     uint32_t mw = __funnelshift_r(sb32[o >> 5], sb32[(o >> 5) + 1], o & 31);
-                    if (Wp == 1) mw &= last_mask;
-                    for (int w = 0; w < Wp; ++w) {
+                    if (w0 == Wp - 1) mw &= last_mask;
+                    for (int w = w0; w < w1; ++w) {
                         o += 32;
                         uint32_t nx = 0u;
                         if (w + 1 < Wp) {
@@ -1411,7 +1431,7 @@ __global__ void __launch_bounds__(2 * kHalf, 2) kb_front_kernel(const uint8_t* _
         unsigned char* rec = cand + (size_t)m * cand_stride(H);
         int16_t* lr = reinterpret_cast<int16_t*>(rec + 8);
         const int nrows = rmax - rmin + 1;
-        for (int rr = et; rr < nrows; rr += kHalf) {
+        for (int rr = et; rr < nrows; rr += kExT) {
             lr[2 * rr] = (int16_t)f.rowL[rmin + rr]; lr[2 * rr + 1] = (int16_t)f.rowR[rmin + rr];
         }
         if (et == 0) { reinterpret_cast<int*>(rec)[0] = rmin; reinterpret_cast<int*>(rec)[1] = rmax; out_has[m] = kPending; }
@@ -1685,7 +1705,7 @@ extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int 
     if ((e = cudaMemsetAsync(p.rowrange, 0x7f, (size_t)n_masks * 8, st)) != cudaSuccess) return (int)e;
     if ((e = cudaMemsetAsync(p.lists, 0, 16, st)) != cudaSuccess) return (int)e;
     const int64_t cap = (int64_t)148 * per_sm;
-    kb_front_kernel<<<(unsigned)(n_masks < cap ? n_masks : cap), 2 * kHalf, fsmem, st>>>(masks, n_masks, H, W, cand, out_has_rect,
+    kb_front_kernel<<<(unsigned)(n_masks < cap ? n_masks : cap), kHalf + kExT, fsmem, st>>>(masks, n_masks, H, W, cand, out_has_rect,
                                                                                  p.lists);
     TDOD_CHECK_LAUNCH();
     kb_tail_kernel<<<(unsigned)((n_masks + kTailWarps - 1) / kTailWarps), 32 * kTailWarps, tsmem, st>>>(cand, n_masks, H, out_rects,
