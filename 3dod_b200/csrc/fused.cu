@@ -593,7 +593,7 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
         const float cor = __fsub_rn(1.f, __fdiv_rn(d, maxd));                        // :85
         const float comb = __fmul_rn(__fmul_rn(iou, dim), cor);                      // roi_heads.py:499
         if (a.all_scores) {
-            float* os = a.all_scores + (size_t)obj * 4 * n;
+            float* os = a.all_scores + (size_t)obj * (a.score_channels ? a.score_channels : 4) * n;
             os[i] = iou; os[n + i] = dim; os[2 * n + i] = cor; os[3 * n + i] = comb;
         }
         if (argmax_better(best.v, best.i, comb, i)) { best.v = comb; best.i = i; }
@@ -668,6 +668,9 @@ extern "C" int tdod_propose_score_select(const tdod_pss_args* ap, void* stream) 
     if (a.centre_mode == TDOD_CENTRE_PATCH_Z && a.rng_mode != TDOD_RNG_HOST)
         return tdod_fail(TDOD_EINVAL, "centre_mode PATCH_Z takes its z ramp from the caller (rng_mode HOST)");
     if (a.std_mode != TDOD_STD_EXACT && a.std_mode != TDOD_STD_TORCH_CUDA) return tdod_fail(TDOD_EINVAL, "unknown std_mode");
+    if (a.score_channels != 0 && a.score_channels != 4 && a.score_channels != 6) return tdod_fail(TDOD_EINVAL, "score_channels must be 0, 4 or 6");
+    if (a.mode_flags & ~(TDOD_MODEB_SEG | TDOD_MODEB_PC)) return tdod_fail(TDOD_EINVAL, "unknown mode_flags");
+    if (a.mode_flags && a.propose_only) return tdod_fail(TDOD_EINVAL, "mode B scores need the scoring pass (propose_only is set)");
     if (a.std_mode == TDOD_STD_TORCH_CUDA && !tstd::config(a.n_prop, 1).ok)
         return tdod_fail(TDOD_ERANGE, "std_mode TORCH_CUDA: n_prop so large that torch splits the reduction over several CTAs");
     int S = a.cluster_size;
@@ -686,7 +689,9 @@ extern "C" int tdod_propose_score_select(const tdod_pss_args* ap, void* stream) 
         e = tdod_smem_opt_in((const void*)pss_kernel<false>, smem, &sm_cta);
         if (e != cudaSuccess) return (int)e;
         pss_kernel<false><<<(unsigned)a.n_obj, kThreads, smem, (cudaStream_t)stream>>>(a, n_loc);
-        return (int)cudaGetLastError();
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return (int)e;
+        return a.mode_flags ? tdod_modeb_launch(a, stream) : TDOD_OK;
     }
     e = tdod_smem_opt_in((const void*)pss_kernel<true>, smem, &sm_cluster);
     if (e != cudaSuccess) return (int)e;
@@ -700,5 +705,6 @@ extern "C" int tdod_propose_score_select(const tdod_pss_args* ap, void* stream) 
     at[0].val.clusterDim.x = S; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
     e = cudaLaunchKernelEx(&cfg, pss_kernel<true>, a, n_loc);
-    return (int)e;
+    if (e != cudaSuccess) return (int)e;
+    return a.mode_flags ? tdod_modeb_launch(a, stream) : TDOD_OK;
 }

@@ -12,6 +12,9 @@ int tdod_fail(int code, const char* msg);
         if (e__ != cudaSuccess) return (int)e__;           \
     } while (0)
 
+// mode B of the fused entry (modeb.cu), launched by tdod_propose_score_select on the same stream
+int tdod_modeb_launch(const tdod_pss_args& a, void* stream);
+
 // Opt-in to more than 48 KB of dynamic shared memory for kernel `fn`, once per device and only ever upwards:
 // cudaFuncSetAttribute is a driver call (not something to pay on every launch), and setting a smaller value later would
 // lower the limit for a concurrent caller.  One cache object per kernel.

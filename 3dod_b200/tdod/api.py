@@ -227,23 +227,27 @@ def ransac_plane(pts, n_pts, sample_ids=None, seed=0, iters=1000, thresh=0.05, w
 
 class PssOutputs:
     __slots__ = ("best_idx", "best_score", "best_cube", "best_box", "all_cubes", "all_boxes", "all_scores", "stats",
-                 "noise", "yaw_idx", "seeds")
+                 "noise", "yaw_idx", "seeds", "all_pc")
 
 
 def propose_score_select(depth, K, boxes, prior_mean, prior_std, obj_frame, rects, has_rect, n_prop, yaw_tab=None,
                          iou_boxes=None, noise=None, yaw_idx=None, rot=None, seed=None, obj_id_base=0,
                          return_all=False, cluster_size=0, out=None, propose_only=False, centre_mode=L.CENTRE_DEPTH,
                          dims_mode=L.DIMS_PRIOR, aux=None, im_shape=None, want_noise=False, want_seeds=False,
-                         std_mode=L.STD_EXACT):
+                         std_mode=L.STD_EXACT, masks=None, points=None, n_points=None):
     """The fused hot path (csrc/fused.cu).  depth [F,H,W], K [F,3,3], boxes [N,4], priors [N,3], obj_frame [N] int32,
     rects [N,4,2], has_rect [N] uint8 | None, yaw_tab [F,36,3,3] | None.
-    Parity RNG mode: noise [N,6,n] (+ yaw_idx [N,n] int16 | rot [N,n,9]); throughput mode: seed=int (Philox)."""
+    Parity RNG mode: noise [N,6,n] (+ yaw_idx [N,n] int16 | rot [N,n,9]); throughput mode: seed=int (Philox).
+    Mode B (MABO branch, roi_heads.py:535-538): masks [N,H,W] adds the segmentation and mod-segmentation scores as
+    channels 4, 5 of all_scores; points [F,3,P] (+ n_points [F] int32: the frames' non-ground points as `backproject`
+    returns them) adds all_pc [N,n] int32.  Both imply return_all."""
     F, H, W = depth.shape
     N = boxes.shape[0]
     dev = depth.device
     o = out if out is not None else PssOutputs()
-    if propose_only:
+    if propose_only or masks is not None or points is not None:
         return_all = True
+    n_ch = 6 if masks is not None else 4
     if out is None:
         o.best_idx = o.best_score = o.best_cube = o.best_box = None
         if not propose_only:
@@ -253,7 +257,7 @@ def propose_score_select(depth, K, boxes, prior_mean, prior_std, obj_frame, rect
             o.best_box = torch.empty((N, 4), dtype=f32, device=dev)
         o.all_cubes = torch.empty((N, n_prop, 15), dtype=f32, device=dev) if return_all else None
         o.all_boxes = torch.empty((N, n_prop, 4), dtype=f32, device=dev) if return_all else None
-        o.all_scores = torch.empty((N, 4, n_prop), dtype=f32, device=dev) if (return_all and not propose_only) else None
+        o.all_scores = torch.empty((N, n_ch, n_prop), dtype=f32, device=dev) if (return_all and not propose_only) else None
         o.stats = torch.empty((N, 6), dtype=f32, device=dev) if return_all else None
     a = L.PssArgs()
     a.depth = L.ptr(depth, f32, "depth")
@@ -293,6 +297,22 @@ def propose_score_select(depth, K, boxes, prior_mean, prior_std, obj_frame, rect
         raise ValueError("aux must be [N,2]")
     a.aux = L.ptr(aux, f32, "aux")
     a.std_mode = int(std_mode)
+    a.mode_flags = (L.MODEB_SEG if masks is not None else 0) | (L.MODEB_PC if points is not None else 0)
+    a.score_channels = n_ch
+    m8 = _as_u8(masks)
+    if m8 is not None and tuple(m8.shape) != (N, H, W):
+        raise ValueError("masks must be [N,H,W]")
+    a.masks = L.ptr(m8, u8, "masks")
+    o.all_pc = None
+    if points is not None:
+        if points.dim() != 3 or points.shape[0] != F or points.shape[1] != 3 or points.dtype not in (f32, f64):
+            raise ValueError("points must be [F,3,P] fp32 / fp64 (SoA, as backproject returns them)")
+        if n_points is None:
+            raise ValueError("points need n_points [F] int32")
+        a.points, a.n_points = L.ptr(points, None, "points"), L.ptr(n_points, i32, "n_points")
+        a.P_cap, a.points_f64 = int(points.shape[2]), 1 if points.dtype == f64 else 0
+        o.all_pc = torch.empty((N, n_prop), dtype=i32, device=dev)
+        a.all_pc = L.ptr(o.all_pc)
     # audit outputs: the numbers behind the proposal set (HOST-mode layout) and the centre seeds
     o.noise = torch.empty((N, 6, n_prop), dtype=f32, device=dev) if want_noise else None
     o.yaw_idx = torch.empty((N, n_prop), dtype=i16, device=dev) if (want_noise and yaw_tab is not None) else None

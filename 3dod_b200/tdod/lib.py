@@ -14,6 +14,7 @@ BACKPROJECT_NUMPY, BACKPROJECT_TORCH = 0, 1
 CENTRE_DEPTH, CENTRE_UNIFORM, CENTRE_PATCH, CENTRE_PATCH_Z = 0, 1, 2, 3
 DIMS_PRIOR, DIMS_UNIFORM, DIMS_ASPECT = 0, 1, 2
 STD_EXACT, STD_TORCH_CUDA = 0, 1
+MODEB_SEG, MODEB_PC = 1, 2
 
 _lib = None
 
@@ -35,6 +36,9 @@ class PssArgs(C.Structure):
         ("centre_mode", C.c_int32), ("dims_mode", C.c_int32), ("im_w", C.c_int32), ("im_h", C.c_int32),
         ("aux", C.c_void_p),
         ("std_mode", C.c_int32),
+        ("mode_flags", C.c_int32), ("score_channels", C.c_int32),
+        ("masks", C.c_void_p), ("points", C.c_void_p), ("n_points", C.c_void_p), ("P_cap", C.c_int64),
+        ("points_f64", C.c_int32), ("all_pc", C.c_void_p),
         ("out_noise", C.c_void_p), ("out_yaw_idx", C.c_void_p), ("out_seeds", C.c_void_p),
     ]
 

@@ -168,7 +168,7 @@ def _select_split(batch, n_prop, seed, yaw_tab, side, main, obj_id_base, cluster
 def select(batch, n_prop, seed=0, noise=None, yaw_idx=None, rot=None, sample_ids=None, use_ground=True,
            ransac_iters=1000, ransac_thresh=0.05, flavour=L.BACKPROJECT_NUMPY, obj_id_base=0, frame_id_base=0,
            return_all=False, cluster_size=0, overlap=True, marks=None, iou_boxes=None, splits=None, want_noise=False,
-           want_seeds=False):
+           want_seeds=False, mode_b=False, std_mode=L.STD_EXACT):
     """Mode A (roi_heads.py:493-505) for every object of a device-resident batch.  Throughput RNG (in-kernel
     Philox keyed by global object id) unless `noise` (+ `yaw_idx` / `rot`) hands in host-drawn numbers.
     Launches only; does not synchronise.
@@ -176,7 +176,11 @@ def select(batch, n_prop, seed=0, noise=None, yaw_idx=None, rot=None, sample_ids
     K-A (depth -> plane -> yaw table) and K-B (masks -> rectangles) are independent until K-C needs both: with
     `overlap` K-A is launched on an auxiliary stream so that its FP-bound hypothesis scoring shares the SMs with
     K-B's bandwidth-bound mask pass.  `marks`: optional dict that receives CUDA events
-    (kb0/kb1 around K-B and kc0/kc1 around K-C on the caller's stream, ka0/ka1 around K-A on its stream)."""
+    (kb0/kb1 around K-B and kc0/kc1 around K-C on the caller's stream, ka0/ka1 around K-A on its stream).
+
+    mode_b: also the three scores of the MABO branch (roi_heads.py:535-538) for every proposal -- segmentation and
+    mod-segmentation IoU against the object's mask, points of the frame's non-ground cloud inside the cube's intervals --
+    in the same fused call (`s.all.all_scores` channels 4, 5 and `s.all.all_pc`); implies return_all."""
     s = Selection()
     yaw_tab = None
     s.normal = s.plane_eq = s.inlier_count = None
@@ -197,15 +201,26 @@ def select(batch, n_prop, seed=0, noise=None, yaw_idx=None, rot=None, sample_ids
             side.wait_stream(main)
         with torch.cuda.stream(side):
             mark("ka0", side)
-            s.normal, s.plane_eq, s.inlier_count, _, _, _ = ground_normals(
+            s.normal, s.plane_eq, s.inlier_count, pts_plane, pts_other, pt_counts = ground_normals(
                 batch.depth, batch.ground, batch.K, seed=seed, sample_ids=sample_ids, iters=ransac_iters,
-                thresh=ransac_thresh, flavour=flavour, frame_id_base=frame_id_base)
+                thresh=ransac_thresh, flavour=flavour, frame_id_base=frame_id_base, want_other=mode_b)
             yaw_tab = api.yaw_table(s.normal)
+            if mode_b:
+                # roi_heads.py:371-384: the cloud the point score sees is the non-ground points, or every point when the
+                # frame has no ground map
+                if batch.ground is None:
+                    cloud, cloud_n = pts_plane, pt_counts[:, 0].contiguous()
+                elif batch.has_ground is None:
+                    cloud, cloud_n = pts_other, pt_counts[:, 1].contiguous()
+                else:
+                    hg = torch.tensor(batch.has_ground, device=batch.device)
+                    cloud = torch.where(hg[:, None, None], pts_other, pts_plane)
+                    cloud_n = torch.where(hg, pt_counts[:, 1], pt_counts[:, 0]).contiguous()
             mark("ka1", side)
     if splits is None:       # measured on C2 (B200): two ranges in flight 1.42 ms vs one range 1.34 ms -> off by default
         splits = 1
     if splits > 1:
-        if noise is not None or return_all:
+        if noise is not None or return_all or mode_b:
             raise ValueError("splits > 1 needs the throughput RNG and select mode (no return_all)")
         if with_plane and side is not main:
             for t in (s.normal, s.plane_eq, s.inlier_count, yaw_tab):
@@ -216,36 +231,41 @@ def select(batch, n_prop, seed=0, noise=None, yaw_idx=None, rot=None, sample_ids
         s.all = None
         return s
     mark("kb0", main)
-    s.rects, s.has_rect = api.mask_rect(batch.masks, mark=(lambda name: mark(name, main)) if marks is not None else None)
+    s.rects, s.has_rect = api.mask_rect(batch.masks)
     mark("kb1", main)
     if with_plane and side is not main:
         main.wait_stream(side)
         for t in (s.normal, s.plane_eq, s.inlier_count, yaw_tab):
             t.record_stream(main)        # allocated on the auxiliary stream, consumed on the caller's
+    if mode_b and not with_plane:
+        raise ValueError("mode_b scores the frame's point cloud: use_ground must be on")
+    if mode_b and side is not main:
+        cloud.record_stream(main); cloud_n.record_stream(main)
     mark("kc0", main)
     o = api.propose_score_select(batch.depth, batch.K, batch.boxes, batch.prior_mean, batch.prior_std,
                                  batch.obj_frame, s.rects, s.has_rect, n_prop, yaw_tab=yaw_tab, noise=noise,
                                  yaw_idx=yaw_idx, rot=rot, seed=None if noise is not None else seed,
                                  obj_id_base=obj_id_base, return_all=return_all, cluster_size=cluster_size,
-                                 iou_boxes=iou_boxes, want_noise=want_noise, want_seeds=want_seeds)
+                                 iou_boxes=iou_boxes, want_noise=want_noise, want_seeds=want_seeds, std_mode=std_mode,
+                                 masks=batch.masks if mode_b else None, points=cloud if mode_b else None,
+                                 n_points=cloud_n if mode_b else None)
     mark("kc1", main)
     s.best_idx, s.best_score, s.best_cube, s.best_box = o.best_idx, o.best_score, o.best_cube, o.best_box
-    s.all = o if (return_all or want_noise or want_seeds) else None
+    s.all = o if (return_all or want_noise or want_seeds or mode_b) else None
     return s
 
 
-# kernels launched by one `select` call (K-A: backproject, hypotheses, count, select; yaw table; K-B: pack + 3 rectangle
-# passes; K-C)
-LAUNCHES_PER_SELECT = 10
-LAUNCHES_PER_SELECT_NO_GROUND = 5
+# kernels launched by one `select` call: K-A 5 (back-projection, hypotheses, count, best, yaw table); K-B 5 (front, tail,
+# list-driven pack, two exact passes -- the last three find empty work lists on ordinary masks); K-C 1
+LAUNCHES_PER_SELECT = 11
+LAUNCHES_PER_SELECT_NO_GROUND = 6
 
 
 def launches_per_select(n_obj, with_plane=True, splits=None):
-    """libtdod kernels one `select` call launches: K-A 5 (back-projection, hypotheses, count, best, yaw table) + per
-    object range 5 (pack, three rectangle passes, fused kernel)"""
+    """libtdod kernels one `select` call launches (masks that fit the fused K-B path)"""
     if splits is None:
         splits = 1
-    return (5 if with_plane else 0) + 5 * splits
+    return (5 if with_plane else 0) + 6 * splits
 
 
 class Pipeline:

@@ -46,6 +46,11 @@ extern "C" {
 #define TDOD_STD_TORCH_CUDA 1  /* torch's CUDA kernel: fp32 Welford merged in the order of its launch configuration for the
                                   frame's [N_objects_of_frame, n_prop] tensor -- the reference as it runs on the GPU */
 
+/* mode B: the scores the MABO branch adds (roi_heads.py:535-538), computed for all objects by the same call
+ * (tdod_pss_args.mode_flags) */
+#define TDOD_MODEB_SEG 1       /* score_segmentation + score_mod_segmentation (scorefunction.py:88-126) -> all_scores channels 4, 5 */
+#define TDOD_MODEB_PC 2        /* score_point_cloud (scorefunction.py:9-43) -> all_pc */
+
 #define TDOD_BACKPROJECT_NUMPY 0 /* roi_heads.py:346-371: fp64, full-res intrinsics on the strided grid */
 #define TDOD_BACKPROJECT_TORCH 1 /* roi_heads.py:1084-1112: fp32, K // stride, centre of the strided grid */
 
@@ -202,7 +207,7 @@ typedef struct tdod_pss_args {
     /* outputs: everything (each may be NULL) */
     float* all_cubes;          /* [n_obj,n_prop,15] */
     float* all_boxes;          /* [n_obj,n_prop,4] */
-    float* all_scores;         /* [n_obj,4,n_prop]: iou, dim, corners, combined */
+    float* all_scores;         /* [n_obj,score_channels,n_prop]: iou, dim, corners, combined (, segmentation, mod-segmentation) */
     float* stats;              /* [n_obj,6]: mean/std of the x, y, z samplers */
     int32_t cluster_size;      /* CTAs per object: 0 = auto, else 1,2,4,8 */
     int32_t propose_only;      /* != 0: sample + project only (proposals.propose / cubes_to_box): fills all_cubes /
@@ -213,6 +218,16 @@ typedef struct tdod_pss_args {
     int32_t im_w, im_h;        /* im_shape of pixel_to_normalised_space (PATCH modes); 0 -> W, H */
     const float* aux;          /* [n_obj,2]: DIMS_ASPECT (ratio_h, ratio_l); NULL otherwise */
     int32_t std_mode;          /* TDOD_STD_* */
+    /* mode B (all zero / NULL = mode A only).  Needs all_cubes (in this mode every cube is an output of the call: the caller
+     * scores them against the ground truth, roi_heads.py:526); corners, hulls and polygons are never materialised */
+    int32_t mode_flags;        /* TDOD_MODEB_* */
+    int32_t score_channels;    /* channels of all_scores: 0 or 4 = iou, dim, corners, combined; 6 = + segmentation, mod-segmentation */
+    const uint8_t* masks;      /* [n_obj,H,W] 1 B/px (TDOD_MODEB_SEG) */
+    const void* points;        /* [F,3,P_cap] SoA, the frames' non-ground points as tdod_backproject writes them (TDOD_MODEB_PC) */
+    const int32_t* n_points;   /* [F] */
+    int64_t P_cap;
+    int32_t points_f64;        /* points are fp64 (NumPy flavour, roi_heads.py:535) or fp32 */
+    int32_t* all_pc;           /* [n_obj,n_prop] points strictly inside each proposal's intervals (int64 in the reference) */
     /* replay / audit outputs (each may be NULL): the numbers behind the proposal set, in HOST-mode layout, so that a PHILOX
      * run can be fed back through HOST mode (and through the oracle's cubes_from_noise) bit for bit */
     float* out_noise;          /* [n_obj,6,n_prop]: accepted standard normals (or U[0,1) draws) for w,h,l,x,y,z */

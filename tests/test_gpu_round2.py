@@ -291,3 +291,99 @@ def test_segmented_order_and_accumulate_scores(n):
             assert np.array_equal(cur[s, ch], ref) and first[s, ch, 0] == ref[0]
     # tied scores: the curve is a running maximum whatever the order of the tie, so its END value is order-free
     assert np.array_equal(cur[:, :, -1], np.repeat(iou.numpy().max(1)[:, None], 2, 1))
+
+
+# ---- mode B inside the fused entry, and the MABO branch on top of it (roi_heads.py:512-582) ---------------------------
+def test_mode_b_scores_of_the_fused_entry(golden_dir):
+    """segmentation / mod-segmentation IoU and points-in-cube for all objects from ONE call (masks + the frame's non-ground
+    cloud handed to tdod_propose_score_select): identical to the per-function kernels on the cubes the call emitted, to the
+    oracle (cv2.fillPoly per proposal, P x n comparisons) on those cubes, and -- up to the last-ulp CPU-vs-CUDA difference
+    of the centres -- to the scores the unmodified reference computed for its own cubes"""
+    d = dev()
+    g = np.load(os.path.join(golden_dir, "c1_modeB.npz"))
+    f = synth.make_frame(int(g["frame_id"]), int(g["H"]), int(g["W"]), int(g["n_obj"]))
+    n, N, H, W = int(g["n"]), int(g["n_obj"]), int(g["H"]), int(g["W"])
+    gd = lambda t: t.to(d)
+    pts, other, cnt = api.backproject(gd(f.depth)[None], gd(f.ground)[None], gd(f.K)[None], 5, L.BACKPROJECT_NUMPY, want_other=True)
+    rects, has = api.mask_rect(gd(f.masks))
+    o = api.propose_score_select(gd(f.depth)[None], gd(f.K)[None], gd(f.boxes), gd(f.prior_mean), gd(f.prior_std),
+                                 torch.zeros(N, dtype=torch.int32, device=d), rects, has, n,
+                                 yaw_tab=api.yaw_table(torch.from_numpy(g["normal"]).to(d)[None]),
+                                 noise=torch.from_numpy(g["noise"]).permute(1, 0, 2).contiguous().to(d),
+                                 yaw_idx=torch.from_numpy(g["yaw_idx"]).to(d), masks=gd(f.masks), points=other,
+                                 n_points=cnt[:, 1].contiguous())
+    torch.cuda.synchronize()
+    assert o.all_scores.shape == (N, 6, n) and o.all_pc.shape == (N, n)
+    cloud = other[0, :, :int(cnt[0, 1])].t().contiguous()
+    for i in range(N):
+        c2d, _ = api.project_cubes(o.all_cubes[i], gd(f.K), W, H, boxes=False)
+        assert torch.equal(o.all_scores[i, 4], api.score_segmentation(gd(f.masks[i]), c2d))
+        assert torch.equal(o.all_scores[i, 5], api.score_segmentation(gd(f.masks[i]), c2d, power5=True))
+        assert torch.equal(o.all_pc[i].long(), api.score_point_cloud(cloud, o.all_cubes[i]))
+        # the reference's own numbers (its cubes differ from ours in the last ulp of the centres at most)
+        seg_ref, mod_ref, pc_ref = g["seg_%d" % i], g["modseg_%d" % i], g["pc"][i]
+        assert (o.all_scores[i, 4].cpu().numpy() == seg_ref).mean() > 0.98
+        assert (o.all_scores[i, 5].cpu().numpy() == mod_ref).mean() > 0.98
+        assert np.abs(o.all_pc[i].cpu().numpy() - pc_ref).max() <= 2 and (o.all_pc[i].cpu().numpy() == pc_ref).mean() > 0.98
+    # oracle on the emitted cubes of one object
+    i = 1
+    cc = o.all_cubes[i].cpu()
+    c2 = O.project_corners(O.cube_corners(cc), f.K, W, H)
+    assert torch.equal(o.all_scores[i, 4].cpu(), O.segmentation_score(f.masks[i], c2))
+    assert torch.equal(o.all_scores[i, 5].cpu(), O.segmentation_score(f.masks[i], c2, power5=True))
+    pc_o = O.point_cloud_score(cloud.cpu(), cc).numpy()
+    assert np.abs(o.all_pc[i].cpu().numpy() - pc_o).max() <= 1 and (o.all_pc[i].cpu().numpy() == pc_o).mean() > 0.995
+    # mode A channels are untouched by the mode-B pass
+    for k, nm in enumerate(["iou", "dim", "cor", "combined"]):
+        assert np.allclose(o.all_scores[:, k].cpu().numpy(), g[nm], rtol=2e-5, atol=1e-6, equal_nan=True)
+
+
+def _block_ends(score_sorted):
+    """positions where the descending ranking leaves a block of exactly tied scores (NaN ties with NaN)"""
+    a = np.asarray(score_sorted, dtype=np.float64)
+    nxt = np.r_[a[1:], np.nan]
+    same = (nxt == a) | (np.isnan(nxt) & np.isnan(a))
+    same[-1] = False
+    return np.nonzero(~same)[0]
+
+
+def test_mabo_branch_curves_and_combinations():
+    """tdod.mabo.mabo == the MABO branch of the reference (roi_heads.py:512-582) evaluated with NumPy on the same score
+    channels: accumulate_scores for the eight curves and the 26 products; compared wherever the ranking is determined
+    (NumPy's argsort leaves the order inside a block of exactly tied scores unspecified)"""
+    from tdod import mabo
+    d = dev()
+    c = synth.CONFIGS["C1"]
+    frames = [synth.make_frame(fid, c["H"], c["W"], 3) for fid in (2, 5)]
+    b = pipeline.FrameBatch.from_frames(frames, d)
+    n = 300
+    # ground-truth cubes: the winners of another seed, nudged
+    gt = pipeline.select(b, n, seed=99).best_cube.clone()
+    gt[:, :3] += 0.05
+    r = mabo.mabo(b, gt, n, seed=5)
+    torch.cuda.synchronize()
+    o = r["selection"].all
+    iou3d = r["iou3d"].cpu().numpy()
+    # IoU3D itself: fp64 half-space oracle on the emitted cubes
+    c_gt = O.cube_corners(gt.cpu()).numpy()
+    c_pr = O.cube_corners(o.all_cubes[0].cpu()).numpy()
+    assert np.abs(iou3d[0] - O.box3d_iou_np(c_gt[0], c_pr)).max() < 1e-5
+    ch = {k: v.cpu().numpy() for k, v in r["channels"].items()}
+    assert ch["point_c"].dtype == np.int64 and ch["IoU2D"].dtype == np.float32
+    curves, comb = r["curves"].cpu().numpy(), r["combinations"].cpu().numpy()
+    for i in range(b.n_obj):
+        for k, name in enumerate(mabo.CURVES):
+            s = ch[name][i]
+            ref = O.accumulate_scores(s, iou3d[i]).astype(np.float32)
+            ends = _block_ends(np.sort(s.astype(np.float64))[::-1])
+            assert np.array_equal(curves[i, k][ends], ref[ends]), (i, name)
+            assert curves[i, k, -1] == iou3d[i].max()
+        for k, names in enumerate(mabo.COMBINATIONS):
+            prod = ch[names[0]][i]
+            for nm in names[1:]:
+                prod = prod * ch[nm][i]                                  # NumPy promotion, left to right (roi_heads.py:553-579)
+            assert prod.dtype == (np.float64 if "point_c" in names else np.float32)
+            best = np.nonzero(prod == np.nanmax(prod))[0] if not np.isnan(prod).any() else np.nonzero(np.isnan(prod))[0]
+            assert comb[i, k] in iou3d[i][best].astype(np.float32), (i, names)
+    # the winner is the mode-A argmax scored against the projected GT cube
+    assert torch.equal(r["selection"].best_idx.cpu(), torch.from_numpy(np.array([int(np.argmax(x)) for x in ch["combined"]])).int())
