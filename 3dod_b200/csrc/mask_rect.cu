@@ -1544,6 +1544,25 @@ __global__ void __launch_bounds__(kPackT, 8) pack_list_kernel(const uint8_t* __r
     }
 }
 
+// occupied row range of every mask of a caller-supplied bitmap (what the pack kernels record on the fly)
+__global__ void __launch_bounds__(256) rowrange_kernel(const uint32_t* __restrict__ bitmap, int H, int Wp, int* __restrict__ rowrange) {
+    const int64_t m = blockIdx.x;
+    const uint32_t* bm = bitmap + (size_t)m * H * Wp;
+    int lo = 0x7fffffff, hi = -1;
+    for (int i = threadIdx.x; i < H * Wp; i += 256)
+        if (bm[i]) { const int r = i / Wp; lo = min(lo, r); hi = max(hi, r); }
+    lo = __reduce_min_sync(0xffffffffu, lo); hi = __reduce_max_sync(0xffffffffu, hi);
+    __shared__ int s_lo, s_hi;
+    if (threadIdx.x == 0) { s_lo = 0x7fffffff; s_hi = -1; }
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0 && hi >= 0) { atomicMin(&s_lo, lo); atomicMax(&s_hi, hi); }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        rowrange[2 * m] = s_hi >= 0 ? s_lo : 0x7f7f7f7f;
+        rowrange[2 * m + 1] = s_hi >= 0 ? H - 1 - s_hi : 0x7f7f7f7f;
+    }
+}
+
 }  // namespace
 
 constexpr int kExactCtas = 148;   // persistent CTAs of the exact pass
@@ -1646,14 +1665,9 @@ extern "C" int tdod_mask_pack(const uint8_t* masks, int64_t n_masks, int H, int 
     return TDOD_OK;
 }
 
-extern "C" int tdod_mask_rect_packed(int64_t n_masks, int H, int W, float* out_rects, uint8_t* out_has_rect, void* workspace,
-                                     int64_t workspace_bytes, void* stream) {
-    if (n_masks == 0) return TDOD_OK;
-    if (!out_rects || !out_has_rect) return tdod_fail(TDOD_EINVAL, "tdod_mask_rect_packed: an output pointer is NULL");
-    KbPlan p;
-    const int rc = kb_plan(n_masks, H, W, workspace, workspace_bytes, &p, "rect");
-    if (rc) return rc;
-    cudaStream_t st = (cudaStream_t)stream;
+// the three rectangle passes over a row-padded bitmap (the workspace's, or a caller's) whose row ranges are in p.rowrange
+static int rect_passes(const KbPlan& p, const uint32_t* bitmap, int64_t n_masks, int H, int W, float* out_rects, uint8_t* out_has_rect,
+                       cudaStream_t st) {
     cudaError_t e = tdod_smem_opt_in((const void*)rect_kernel<false, false>, p.smem1, &g_sm_r0);
     if (e != cudaSuccess) return (int)e;
     e = tdod_smem_opt_in((const void*)rect_kernel<true, false>, p.smem2, &g_sm_r1);
@@ -1663,17 +1677,43 @@ extern "C" int tdod_mask_rect_packed(int64_t n_masks, int H, int W, float* out_r
     // the state byte doubles as the work list of the later passes: every mask starts undecided
     e = cudaMemsetAsync(out_has_rect, 0xff, (size_t)n_masks, st);
     if (e != cudaSuccess) return (int)e;
-    rect_kernel<false, false><<<(unsigned)n_masks, kT, p.smem1, st>>>(p.bitmap, p.rowrange, n_masks, H, W, out_rects, out_has_rect,
+    rect_kernel<false, false><<<(unsigned)n_masks, kT, p.smem1, st>>>(bitmap, p.rowrange, n_masks, H, W, out_rects, out_has_rect,
                                                                    nullptr, p.lists, nullptr);
     TDOD_CHECK_LAUNCH();
     rect_kernel<true, false><<<(unsigned)(n_masks < kExactCtas ? n_masks : kExactCtas), kT, p.smem2, st>>>(
-        p.bitmap, p.rowrange, n_masks, H, W, out_rects, out_has_rect, nullptr, p.lists, p.fill_slots);
+        bitmap, p.rowrange, n_masks, H, W, out_rects, out_has_rect, nullptr, p.lists, p.fill_slots);
     TDOD_CHECK_LAUNCH();
     const unsigned nslots = (unsigned)(n_masks < kSlots ? n_masks : kSlots);
-    rect_kernel<true, true><<<nslots, kT, p.smem2, st>>>(p.bitmap, p.rowrange, n_masks, H, W, out_rects, out_has_rect, p.slots,
+    rect_kernel<true, true><<<nslots, kT, p.smem2, st>>>(bitmap, p.rowrange, n_masks, H, W, out_rects, out_has_rect, p.slots,
                                                         p.lists, p.fill_slots);
     TDOD_CHECK_LAUNCH();
     return TDOD_OK;
+}
+
+extern "C" int tdod_mask_rect_packed(int64_t n_masks, int H, int W, float* out_rects, uint8_t* out_has_rect, void* workspace,
+                                     int64_t workspace_bytes, void* stream) {
+    if (n_masks == 0) return TDOD_OK;
+    if (!out_rects || !out_has_rect) return tdod_fail(TDOD_EINVAL, "tdod_mask_rect_packed: an output pointer is NULL");
+    KbPlan p;
+    const int rc = kb_plan(n_masks, H, W, workspace, workspace_bytes, &p, "rect");
+    if (rc) return rc;
+    return rect_passes(p, p.bitmap, n_masks, H, W, out_rects, out_has_rect, (cudaStream_t)stream);
+}
+
+extern "C" int tdod_mask_rect_bitmap(const uint32_t* bitmap, int64_t n_masks, int H, int W, float* out_rects,
+                                     uint8_t* out_has_rect, void* workspace, int64_t workspace_bytes, void* stream) {
+    if (n_masks == 0) return TDOD_OK;
+    if (!bitmap || !out_rects || !out_has_rect) return tdod_fail(TDOD_EINVAL, "tdod_mask_rect_bitmap: a pointer is NULL");
+    if (n_masks > 0x7fffffff) return tdod_fail(TDOD_ERANGE, "tdod_mask_rect_bitmap: too many masks for one call");
+    KbPlan p;
+    const int rc = kb_plan(n_masks, H, W, workspace, workspace_bytes, &p, "bitmap");
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const cudaError_t e = cudaMemsetAsync(p.lists, 0, 16, st);
+    if (e != cudaSuccess) return (int)e;
+    rowrange_kernel<<<(unsigned)n_masks, 256, 0, st>>>(bitmap, H, p.Wp, p.rowrange);
+    TDOD_CHECK_LAUNCH();
+    return rect_passes(p, bitmap, n_masks, H, W, out_rects, out_has_rect, st);
 }
 
 extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int W, float* out_rects,

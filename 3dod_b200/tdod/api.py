@@ -109,6 +109,25 @@ def mask_rect(masks, mark=None, out=None, two_kernel=False):
     return rects, has
 
 
+def mask_rect_bitmap(bitmap, W, out=None):
+    """masks already packed 1 bit/px: bitmap [n,H,ceil(W/32)] int32 (bit c & 31 of word c >> 5 = pixel c) ->
+    (rects [n,4,2], has_rect [n])"""
+    n, H, Wp = bitmap.shape
+    if Wp != (W + 31) // 32 or bitmap.dtype != i32:
+        raise ValueError("bitmap must be int32 [n,H,ceil(W/32)]")
+    if out is not None:
+        rects, has = out
+    else:
+        rects = torch.empty((n, 4, 2), dtype=f32, device=bitmap.device)
+        has = torch.empty(n, dtype=u8, device=bitmap.device)
+    if n == 0:
+        return rects, has
+    ws, wsb = _kb_workspace(n, H, W, bitmap.device)
+    L.check(L.lib().tdod_mask_rect_bitmap(L.ptr(bitmap, i32, "bitmap"), n, H, W, L.ptr(rects), L.ptr(has), L.ptr(ws), wsb,
+                                          L.stream_ptr()))
+    return rects, has
+
+
 def score_segmentation(mask, corners2d, power5=False):
     m = _as_u8(mask)
     H, W = m.shape

@@ -56,6 +56,7 @@ SIGNATURES = {
     "tdod_score_dimensions": (_I, [_P, _P, _P, _L, _P, _P, _L, _P, _P]),
     "tdod_mask_rect_workspace_bytes": (_L, [_L, _I, _I]),
     "tdod_mask_rect": (_I, [_P, _L, _I, _I, _P, _P, _P, _L, _P]),
+    "tdod_mask_rect_bitmap": (_I, [_P, _L, _I, _I, _P, _P, _P, _L, _P]),
     "tdod_mask_pack": (_I, [_P, _L, _I, _I, _P, _L, _P]),
     "tdod_mask_rect_packed": (_I, [_L, _I, _I, _P, _P, _P, _L, _P]),
     "tdod_score_corners": (_I, [_P, _I, _P, _L, _P, _P]),

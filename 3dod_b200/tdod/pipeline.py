@@ -25,10 +25,10 @@ class FrameBatch:
     depth [F,H,W] f32 · ground [F,H,W] u8/bool or None · K [F,3,3] f32 · obj_off [F+1] (python list / CPU tensor)
     boxes [N,4] f32 xyxy · prior_mean/prior_std [N,3] f32 (w,h,l) · obj_frame [N] i32 · masks [N,H,W] u8/bool"""
     __slots__ = ("depth", "ground", "K", "boxes", "prior_mean", "prior_std", "obj_frame", "masks", "frame_ids",
-                 "has_ground")
+                 "has_ground", "masks_packed")
 
     def __init__(self, depth, ground, K, boxes, prior_mean, prior_std, obj_frame, masks, frame_ids=None,
-                 has_ground=None):
+                 has_ground=None, masks_packed=None):
         self.depth, self.ground, self.K = depth, ground, K
         self.boxes, self.prior_mean, self.prior_std = boxes, prior_mean, prior_std
         self.obj_frame, self.masks, self.frame_ids = obj_frame, masks, frame_ids
@@ -36,6 +36,9 @@ class FrameBatch:
         # carries an all-ones map: `ground > 0` then selects every strided point, which is what the reference fits the plane
         # on when ground_maps is None (roi_heads.py:358-371, dataset_mapper.py:146)
         self.has_ground = has_ground
+        # optional alternative to `masks` (then None): the masks at 1 bit per pixel, int32 [N,H,ceil(W/32)], see `pack_masks`
+        # -- an eighth of the bytes to keep in host memory and to move over PCIe
+        self.masks_packed = masks_packed
 
     @property
     def n_frames(self):
@@ -52,15 +55,18 @@ class FrameBatch:
     def to(self, device, non_blocking=False):
         mv = lambda t: None if t is None else t.to(device, non_blocking=non_blocking)
         return FrameBatch(mv(self.depth), mv(self.ground), mv(self.K), mv(self.boxes), mv(self.prior_mean),
-                          mv(self.prior_std), mv(self.obj_frame), mv(self.masks), self.frame_ids, self.has_ground)
+                          mv(self.prior_std), mv(self.obj_frame), mv(self.masks), self.frame_ids, self.has_ground,
+                          mv(self.masks_packed))
 
     def pin(self):
         pm = lambda t: None if t is None else t.pin_memory()
         return FrameBatch(pm(self.depth), pm(self.ground), pm(self.K), pm(self.boxes), pm(self.prior_mean),
-                          pm(self.prior_std), pm(self.obj_frame), pm(self.masks), self.frame_ids, self.has_ground)
+                          pm(self.prior_std), pm(self.obj_frame), pm(self.masks), self.frame_ids, self.has_ground,
+                          pm(self.masks_packed))
 
     def input_bytes(self):
-        ts = (self.depth, self.ground, self.K, self.boxes, self.prior_mean, self.prior_std, self.obj_frame, self.masks)
+        ts = (self.depth, self.ground, self.K, self.boxes, self.prior_mean, self.prior_std, self.obj_frame, self.masks,
+              self.masks_packed)
         return sum(t.numel() * t.element_size() for t in ts if t is not None)
 
     @staticmethod
@@ -84,6 +90,25 @@ class FrameBatch:
                           cat("prior_std"), obj_frame, masks, [f.frame_id for f in frames], has_ground)
 
 
+def pack_masks(masks):
+    """masks [N,H,W] bool / uint8 (any device) -> int32 [N,H,ceil(W/32)]: bit (c & 31) of word (c >> 5) of a row = pixel c
+    (the layout tdod_mask_rect_bitmap reads).  Host-side convenience for callers that want to keep or ship masks packed."""
+    m = (masks != 0)
+    N, H, W = m.shape
+    Wp = (W + 31) // 32
+    pad = Wp * 32 - W
+    if pad:
+        m = torch.nn.functional.pad(m, (0, pad))
+    w = torch.tensor([1 << k for k in range(31)] + [-(1 << 31)], dtype=torch.int64, device=m.device)
+    return (m.reshape(N, H, Wp, 32).to(torch.int64) * w).sum(-1).to(torch.int32)
+
+
+def with_packed_masks(batch):
+    """the same batch with its masks at 1 bit per pixel only"""
+    return FrameBatch(batch.depth, batch.ground, batch.K, batch.boxes, batch.prior_mean, batch.prior_std, batch.obj_frame,
+                      None, batch.frame_ids, batch.has_ground, pack_masks(batch.masks))
+
+
 class Selection:
     """winners per object (+ per-frame plane outputs)"""
     __slots__ = ("best_idx", "best_score", "best_cube", "best_box", "normal", "plane_eq", "inlier_count", "rects",
@@ -99,6 +124,51 @@ def ground_normals(depth, ground, K, seed=0, sample_ids=None, iters=1000, thresh
     r = api.ransac_plane(pts, counts[:, 0].contiguous(), sample_ids, seed=seed, iters=iters, thresh=thresh,
                          frame_id_base=frame_id_base)
     return r["normal"], r["eq"], r["count"], pts, other, counts
+
+
+def draw_reference_noise(batch, obj_off, n_prop, generator=None, cpu_generator=None, with_normal=True):
+    """The random numbers of `propose` (ProposalNetwork/proposals/proposals.py:377-407) drawn WITH TORCH'S GENERATORS IN THE
+    REFERENCE'S PROGRAM ORDER, frame by frame as the reference calls it: per frame three truncated draws for w, h, l --
+    each a whole-tensor redraw loop over the frame's [N_f, n] block until no entry is out of range
+    (sample_normal_in_range, ProposalNetwork/utils/utils.py:42-60) -- then x, y, z, all from the device generator; the
+    yaw bins from `torch.randint` on the CPU generator (the reference builds that index tensor on the host, :407).
+    Returns (noise [N,6,n] accepted standard normals, yaw_idx [N,n] int16 | None): what HOST mode consumes, so that a
+    seeded run reproduces the reference's proposal set (with std_mode TORCH_CUDA: bit for bit).
+    The redraw loop synchronises with the host once per pass, as the reference's does."""
+    dev = batch.device
+    N = batch.n_obj
+    noise = torch.empty((N, 6, n_prop), dtype=f32, device=dev)
+    yaw = torch.empty((N, n_prop), dtype=torch.int16) if with_normal else None
+    mu, sg = batch.prior_mean, batch.prior_std
+    hs = torch.tensor([1.0, 1.1, 1.0], device=dev)
+    hk = torch.tensor([2.0, 2.2, 2.0], device=dev)
+    for f in range(batch.n_frames):
+        o0, o1 = obj_off[f], obj_off[f + 1]
+        if o1 == o0:
+            continue
+        nf = o1 - o0
+        for k in range(3):
+            mean, std = mu[o0:o1, k], sg[o0:o1, k] * hs[k]
+            hi = (mu[o0:o1, k] + hk[k] * sg[o0:o1, k])[:, None]
+            z = torch.randn((nf, n_prop), generator=generator, device=dev)
+            v = z * std[:, None] + mean[:, None]
+            tries = 0
+            while True:
+                bad = (v < 0.05) | (v > hi)
+                if not bool(torch.any(bad)):
+                    break
+                z2 = torch.randn((nf, n_prop), generator=generator, device=dev)
+                v = torch.where(bad, z2 * std[:, None] + mean[:, None], v)
+                z = torch.where(bad, z2, z)
+                tries += 1
+                if tries == 10000:
+                    break
+            noise[o0:o1, k] = z
+        for k in range(3, 6):
+            noise[o0:o1, k] = torch.randn((nf, n_prop), generator=generator, device=dev)
+        if with_normal:
+            yaw[o0:o1] = torch.randint(36, (nf, n_prop), generator=cpu_generator).to(torch.int16)
+    return noise, (yaw.to(dev, non_blocking=True) if with_normal else None)
 
 
 _SIDE = {}
@@ -231,7 +301,12 @@ def select(batch, n_prop, seed=0, noise=None, yaw_idx=None, rot=None, sample_ids
         s.all = None
         return s
     mark("kb0", main)
-    s.rects, s.has_rect = api.mask_rect(batch.masks)
+    if batch.masks is None and batch.masks_packed is not None:
+        if mode_b:
+            raise ValueError("mode_b samples the masks at 1 byte per pixel: pass `masks`, not `masks_packed`")
+        s.rects, s.has_rect = api.mask_rect_bitmap(batch.masks_packed, int(batch.depth.shape[2]))
+    else:
+        s.rects, s.has_rect = api.mask_rect(batch.masks)
     mark("kb1", main)
     if with_plane and side is not main:
         main.wait_stream(side)
@@ -273,13 +348,14 @@ class Pipeline:
     stream and a compute stream.  The result (winners [N, 15+4+1+1] packed as fp32) is read back per chunk."""
 
     def __init__(self, H, W, n_prop, chunk_frames=32, max_obj_per_chunk=None, device="cuda", seed=0,
-                 use_ground=True):
+                 use_ground=True, packed_masks=False):
         self.H, self.W, self.n_prop = H, W, n_prop
         self.dev = torch.device(device)
         self.chunk = chunk_frames
         self.max_obj = max_obj_per_chunk or chunk_frames * 40
         self.seed = seed
         self.use_ground = use_ground
+        self.packed_masks = packed_masks      # host batches carry `masks_packed` (1 bit/px) instead of `masks`
         self.copy_stream = torch.cuda.Stream(self.dev)
         self.compute_stream = torch.cuda.Stream(self.dev)
         d = self.dev
@@ -293,7 +369,8 @@ class Pipeline:
                 pm=torch.empty((self.max_obj, 3), dtype=f32, device=d),
                 ps=torch.empty((self.max_obj, 3), dtype=f32, device=d),
                 of=torch.empty((self.max_obj,), dtype=i32, device=d),
-                masks=torch.empty((self.max_obj, H, W), dtype=u8, device=d),
+                masks=None if packed_masks else torch.empty((self.max_obj, H, W), dtype=u8, device=d),
+                mpk=torch.empty((self.max_obj, H, (W + 31) // 32), dtype=i32, device=d) if packed_masks else None,
                 packed=torch.empty((self.max_obj, 21), dtype=f32, device=d),
                 copied=torch.cuda.Event(), done=torch.cuda.Event()))
         self.launches = 0
@@ -306,7 +383,12 @@ class Pipeline:
         F, N = hb.n_frames, hb.n_obj
         if out is None:
             out = torch.empty((N, 21), dtype=f32).pin_memory()
-        masks_h = hb.masks.view(u8) if hb.masks.dtype == torch.bool else hb.masks
+        if self.packed_masks:
+            if hb.masks_packed is None:
+                raise ValueError("this Pipeline was built for packed masks: the host batch needs masks_packed")
+            masks_h = hb.masks_packed
+        else:
+            masks_h = hb.masks.view(u8) if hb.masks.dtype == torch.bool else hb.masks
         ground_h = None
         if hb.ground is not None:
             ground_h = hb.ground.view(u8) if hb.ground.dtype == torch.bool else hb.ground
@@ -330,15 +412,18 @@ class Pipeline:
                     sl["pm"][:no].copy_(hb.prior_mean[o0:o1], non_blocking=True)
                     sl["ps"][:no].copy_(hb.prior_std[o0:o1], non_blocking=True)
                     sl["of"][:no].copy_(hb.obj_frame[o0:o1], non_blocking=True)
-                    sl["masks"][:no].copy_(masks_h[o0:o1], non_blocking=True)
+                    sl["mpk" if self.packed_masks else "masks"][:no].copy_(masks_h[o0:o1], non_blocking=True)
                 sl["copied"].record(self.copy_stream)
-            self.h2d_bytes += nf * self.H * self.W * (5 if ground_h is not None else 4) + nf * 36 + no * (44 + self.H * self.W)
+            mask_bytes = self.H * ((self.W + 31) // 32) * 4 if self.packed_masks else self.H * self.W
+            self.h2d_bytes += nf * self.H * self.W * (5 if ground_h is not None else 4) + nf * 36 + no * (44 + mask_bytes)
             if no == 0:
                 continue
             with torch.cuda.stream(self.compute_stream):
                 self.compute_stream.wait_event(sl["copied"])
                 b = FrameBatch(sl["depth"][:nf], sl["ground"][:nf] if ground_h is not None else None, sl["K"][:nf],
-                               sl["boxes"][:no], sl["pm"][:no], sl["ps"][:no], sl["of"][:no] - f0, sl["masks"][:no])
+                               sl["boxes"][:no], sl["pm"][:no], sl["ps"][:no], sl["of"][:no] - f0,
+                               None if self.packed_masks else sl["masks"][:no],
+                               masks_packed=sl["mpk"][:no] if self.packed_masks else None)
                 s = select(b, self.n_prop, seed=self.seed, use_ground=self.use_ground,
                            obj_id_base=obj_id_base + o0, frame_id_base=frame_id_base + f0)
                 p = sl["packed"][:no]

@@ -45,6 +45,29 @@ def forward_pseudo(batch, n_prop, seed=0, iou_boxes=None, box_from_object0=False
     return fields, sel
 
 
+def _fields(cubes, boxes, scores):
+    """the fields the reference stores on its `Instances` (roi_heads.py:480-487, :649-659)"""
+    return dict(pred_boxes=boxes, scores=scores, pred_bbox3D=api.cube_corners(cubes), pred_center_cam=cubes[:, 0:3],
+                pred_dimensions=cubes[:, 3:6], pred_pose=cubes[:, 6:15].reshape(-1, 3, 3),
+                pred_center_2D=(boxes[:, :2] + boxes[:, 2:]) / 2)
+
+
+def forward_pred(batch, n_prop, seed=0, obj_id_base=0, frame_id_base=0, **kw):
+    """Batched form of the `use_pred_boxes` (AP evaluation) branch of _forward_cube (roi_heads.py:493-505, :646-659): the
+    IoU term is scored against the 2D box itself, the winner's cube and score are kept, and `pred_boxes` is the input box
+    (`instances_i.pred_boxes = gt_boxes`, :650).  Returns (fields, selection)."""
+    sel = pipeline.select(batch, n_prop, seed=seed, obj_id_base=obj_id_base, frame_id_base=frame_id_base, **kw)
+    return _fields(sel.best_cube, batch.boxes, sel.best_score), sel
+
+
+def forward_learn(batch, n_prop, seed=0, obj_id_base=0, frame_id_base=0, **kw):
+    """Batched form of the `pseudo_gt == 'learn'` branch (roi_heads.py:460-464): EVERY proposal is returned, its score
+    the IoU of its projected box with the object's 2D box.  Returns (cubes [N,n,15], scores [N,n], selection)."""
+    sel = pipeline.select(batch, n_prop, seed=seed, obj_id_base=obj_id_base, frame_id_base=frame_id_base, return_all=True,
+                          **kw)
+    return sel.all.all_cubes, sel.all.all_scores[:, 0], sel
+
+
 def annotation(ann_id, image_id, dataset_id, category_id, category_name, bbox2d, center, dims, bbox3d, rot):
     """one record of tools/eval_boxes.py:648-653 (field names, constants and order as the reference writes them)"""
     return {'behind_camera': False, 'truncation': 0, 'bbox2D_proj': bbox2d, 'bbox2D_tight': -1, 'visibility': 1.0,
@@ -60,9 +83,11 @@ def image_record(image_id, width, height, file_path, K):
 
 
 class PseudoGTWriter:
-    """Append-only part file `<path>.part.jsonl` (one line per frame: {"image": ..., "annotations": [...]}), fsync'ed per
-    flush; `done_images` is the resume point.  Annotation ids continue from the part file (reference: one global
-    counter starting at 1, eval_boxes.py:622)."""
+    """Append-only part file `<path>.part.jsonl`, two lines per frame -- the image record (plus the id range of its
+    annotations) and the frame's annotation objects already serialised -- flushed and fsync'ed per `flush`; the image lines
+    are the resume point (a frame counts only when both of its lines are complete).  Annotation ids continue from the part
+    file (reference: one global counter starting at 1, eval_boxes.py:622).  `finalize` assembles the reference's single
+    document from the serialised pieces without parsing them again."""
 
     def __init__(self, path, info, categories, resume=True):
         self.path = path
@@ -73,17 +98,18 @@ class PseudoGTWriter:
         if resume and os.path.exists(self.part):
             good = 0
             with open(self.part, "rb") as f:
-                for line in f:
+                while True:
+                    l1 = f.readline()
+                    l2 = f.readline()
+                    if not l1 or not l2 or not l1.endswith(b"\n") or not l2.endswith(b"\n"):
+                        break                      # torn tail of an interrupted run
                     try:
-                        rec = json.loads(line)
+                        head = json.loads(l1)
                     except ValueError:
-                        break                      # torn last line of an interrupted run
-                    if not line.endswith(b"\n"):
                         break
-                    self.done_images.append(rec["image"]["id"])
-                    if rec["annotations"]:
-                        self.next_id = rec["annotations"][-1]["id"] + 1
-                    good += len(line)
+                    self.done_images.append(head["image"]["id"])
+                    self.next_id = head["next_id"]
+                    good += len(l1) + len(l2)
             with open(self.part, "r+b") as f:      # drop a torn tail
                 f.truncate(good)
         elif os.path.exists(self.part):
@@ -95,30 +121,45 @@ class PseudoGTWriter:
         for a in anns:
             a['id'] = self.next_id
             self.next_id += 1
-        self._f.write((json.dumps({"image": image, "annotations": anns}) + "\n").encode())
+        body = json.dumps(anns)[1:-1]              # the objects, comma separated, without the list brackets
+        self._f.write((json.dumps({"image": image, "next_id": self.next_id}) + "\n" + body + "\n").encode())
         self.done_images.append(image["id"])
 
     def flush(self):
         self._f.flush()
         os.fsync(self._f.fileno())
 
-    def finalize(self):
-        """the reference's single document (eval_boxes.py:658-661)"""
+    def finalize(self, return_doc=True):
+        """the reference's single document (eval_boxes.py:658-661): {categories, info, images, annotations}"""
         self.flush()
         self._f.close()
-        images, anns = [], []
-        with open(self.part, "rb") as f:
-            for line in f:
-                rec = json.loads(line)
-                images.append(rec["image"])
-                anns.extend(rec["annotations"])
-        doc = {"categories": self.categories, "info": self.info, "images": images, "annotations": anns}
         tmp = self.path + ".tmp"
-        with open(tmp, "w") as f:
-            json.dump(doc, f)
+        with open(tmp, "w") as out:
+            out.write('{"categories": ' + json.dumps(self.categories) + ', "info": ' + json.dumps(self.info) + ', "images": [')
+            first = True
+            with open(self.part, "r") as f:
+                while True:
+                    l1 = f.readline()
+                    if not l1:
+                        break
+                    f.readline()
+                    img = json.dumps(json.loads(l1)["image"])
+                    out.write(("" if first else ", ") + img)
+                    first = False
+            out.write('], "annotations": [')
+            first = True
+            with open(self.part, "r") as f:
+                while True:
+                    if not f.readline():
+                        break
+                    body = f.readline().rstrip("\n")
+                    if body:
+                        out.write(("" if first else ", ") + body)
+                        first = False
+            out.write("]}")
         os.replace(tmp, self.path)
         os.remove(self.part)
-        return doc
+        return json.load(open(self.path)) if return_doc else None
 
 
 def postprocess_boxes(gt_boxes, net_hw, out_hw):

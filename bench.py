@@ -35,13 +35,6 @@ import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
 WORKLOAD = "C2"
-# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of this workload
-# (profiles/r01_f_ncu_full_raw_c2.csv): pack_tma_kernel 1.4878 GB + 0.1818 GB, rect_kernel passes 0.0955 GB + 0.0041 GB
-TRAFFIC = {"K-B pack": 1.4878e9 + 0.1818e9, "K-B rect": 0.0955e9 + 0.0041e9}
-# what binds each stage: only the pack kernel moves gigabytes; the others are issue- / latency-bound
-BOUND = {"K-A backproject+ransac": "fp32 fma issue (hypothesis scoring)", "K-B pack": "hbm",
-         "K-B rect": "latency (serial hull / calipers chains on L2-resident bitmaps)",
-         "K-C propose_score_select": "fp32 / sfu issue"}
 N_PROP = 1000
 METRIC = "scored cube proposals/sec"
 UNIT = "proposals/s"
@@ -56,6 +49,9 @@ def parse():
     ap.add_argument("--frames", type=int, default=256, help="frames per GPU (BASELINE configs[1]: 256)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the C1 / C3 / C5 / mode-B / C4 sub-records")
+    ap.add_argument("--no-parity-rng", action="store_true", help="skip the reference-order RNG figure")
+    ap.add_argument("--c4-frames", type=int, default=10000, help="frames of BASELINE configs[3] (all ranks together)")
     ap.add_argument("--profile", action="store_true",
                     help="cudaProfilerStart/Stop around the timed region (ncu --profile-from-start off)")
     return ap.parse_args()
@@ -72,21 +68,50 @@ def peaks():
 # clocks during the timed region
 # ----------------------------------------------------------------------------------------------------------------------
 class ClockSampler:
+    """SM clock and throttle reasons every ~5 ms through NVML (a `nvidia-smi` process per sample takes longer than the
+    whole timed region); falls back to polling nvidia-smi when pynvml is missing."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
         self.index, self.rows, self.stop, self.t = index, [], threading.Event(), None
+        self.nv = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(self._physical_index(index))
+            self.max_sm = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nv = None
+
+    @staticmethod
+    def _physical_index(index):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            parts = [p for p in vis.split(",") if p.strip() != ""]
+            if index < len(parts) and parts[index].strip().isdigit():
+                return int(parts[index])
+        return index
 
     def _run(self):
+        nv = self.nv
         while not self.stop.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                self.rows.append([c.strip() for c in out.strip().split(",")])
+                if nv is not None:
+                    sm = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                    r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+                        else int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                    self.rows.append((sm, self.max_sm, r))
+                else:
+                    out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                    c = [x.strip() for x in out.strip().split(",")]
+                    bits = sum((1 << k) for k in range(4) if c[2 + k].lower().startswith("active"))
+                    self.rows.append((float(c[0]), float(c[1]), -bits))     # negative: nvidia-smi flag order
             except Exception:
                 pass
-            self.stop.wait(0.1)
+            self.stop.wait(0.005 if nv is not None else 0.1)
 
     def __enter__(self):
         self.t = threading.Thread(target=self._run, daemon=True)
@@ -98,12 +123,22 @@ class ClockSampler:
         self.t.join(timeout=6)
 
     def summary(self):
-        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for k, n in enumerate(names) if any(len(r) >= 6 and r[2 + k].lower().startswith("active") for r in self.rows)]
+        sm = [r[0] for r in self.rows]
+        mx = [r[1] for r in self.rows]
+        reasons = []
+        if self.nv is not None:
+            nv = self.nv
+            names = (("hw_slowdown", "nvmlClocksThrottleReasonHwSlowdown"), ("hw_thermal_slowdown", "nvmlClocksThrottleReasonHwThermalSlowdown"),
+                     ("sw_thermal_slowdown", "nvmlClocksThrottleReasonSwThermalSlowdown"), ("sw_power_cap", "nvmlClocksThrottleReasonSwPowerCap"))
+            for n, attr in names:
+                bit = getattr(nv, attr, None)
+                if bit is not None and any(r[2] >= 0 and (r[2] & bit) for r in self.rows):
+                    reasons.append(n)
+        else:
+            names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+            reasons = [n for k, n in enumerate(names) if any((-r[2]) & (1 << k) for r in self.rows if r[2] <= 0)]
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "source": "nvml, 5 ms" if self.nv is not None else "nvidia-smi, 100 ms"}
 
 
 # ----------------------------------------------------------------------------------------------------------------------
@@ -195,6 +230,15 @@ def run_reference(args):
 # ----------------------------------------------------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------------------------------------------------
+# what binds each stage; ncu evidence under profiles/r02_*
+BOUND = {"K-A backproject+ransac": "fp32 fma issue (hypothesis scoring); overlapped with K-B on a second stream",
+         "K-B mask_rect": "hbm (every mask byte once; bit stream, runs and labels stay in shared memory)",
+         "K-C propose_score_select": "fp32 / sfu issue (ncu: issue-active 65 %)"}
+# dram__bytes_read.sum + dram__bytes_write.sum per launch, `ncu --set full` of this workload (profiles/r02_b_ncu_kb_raw.csv):
+# kb_front_kernel 1.4881 GB read + 0.0067 GB written, kb_tail_kernel 0.0034 GB
+TRAFFIC = {"K-B mask_rect": 1.4881e9 + 0.0067e9 + 0.0034e9}
+
+
 def algorithmic_bytes(batch, n_prop, stride=5):
     """compulsory HBM traffic per stage for one pass over `batch` (every needed input element read
     once, every required output written once)."""
@@ -202,10 +246,183 @@ def algorithmic_bytes(batch, n_prop, stride=5):
     N = batch.n_obj
     P = ((H + stride - 1) // stride) * ((W + stride - 1) // stride)
     ka = F * (P * 4 + P * 1 + 36 + 12 + 16)                       # strided depth + ground samples, K, normal, plane
-    kb1 = N * (H * W)                                             # every mask pixel once (the bitmap is an intermediate)
-    kb2 = N * 33                                                  # rectangle + flag out
+    kb = N * (H * W + 33)                                         # every mask pixel once; rectangle + flag out
     kc = N * (4 * n_prop + 44 + 32 + 84)                          # diagonal depth gather, box/priors, rect, winner record
-    return {"K-A backproject+ransac": ka, "K-B pack": kb1, "K-B rect": kb2, "K-C propose_score_select": kc}
+    return {"K-A backproject+ransac": ka, "K-B mask_rect": kb, "K-C propose_score_select": kc}
+
+
+def _events(n):
+    return [torch.cuda.Event(enable_timing=True) for _ in range(n)]
+
+
+def bench_small_configs(dev, steps, peak):
+    """BASELINE configs 0, 2 and 4 (C1, C3, C5) on this GPU, device-resident, L2 flushed between iterations (their inputs
+    fit in L2).  C1 also replayed as a CUDA graph: ten launches of microseconds each are launch-bound otherwise."""
+    from tdod import api, pipeline, synth, lib as L
+    out = {}
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def timed(fn, k):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize(dev)
+        tot = 0.0
+        for _ in range(k):
+            flush.zero_()
+            a, b = _events(2)
+            a.record(); fn(); b.record()
+            torch.cuda.synchronize(dev)
+            tot += a.elapsed_time(b)
+        return tot / k
+    for name in ("C1", "C3"):
+        c = synth.CONFIGS[name]
+        fr = [synth.make_frame(i, c["H"], c["W"], c["n_obj"], device=dev) for i in range(c["frames"])]
+        b = pipeline.FrameBatch.from_frames(fr, dev)
+        n = c["n_prop"]
+        ms = timed(lambda: pipeline.select(b, n, seed=7), steps)
+        ab = sum(algorithmic_bytes(b, n).values())
+        rec = {"frames": c["frames"], "objects": b.n_obj, "n_prop": n, "ms_per_step": ms, "value": b.n_obj * n / (ms * 1e-3),
+               "unit": UNIT, "hbm_frac_step": ab / (ms * 1e-3) / 1e9 / peak,
+               "bound": "launch latency (11 launches)" if name == "C1" else "fp32 issue in K-C (400 CTAs, one wave)"}
+        if name == "C1":
+            try:
+                st = torch.cuda.Stream(dev)
+                with torch.cuda.stream(st):
+                    for _ in range(3):
+                        pipeline.select(b, n, seed=7, overlap=False)
+                torch.cuda.synchronize(dev)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=st):
+                    sg = pipeline.select(b, n, seed=7, overlap=False)
+                ms_g = timed(g.replay, steps)
+                ref = pipeline.select(b, n, seed=7)
+                torch.cuda.synchronize(dev)
+                rec["cuda_graph_ms_per_step"] = ms_g
+                rec["cuda_graph_value"] = b.n_obj * n / (ms_g * 1e-3)
+                rec["cuda_graph_same_winners"] = bool(torch.equal(ref.best_idx, sg.best_idx))
+            except Exception as e:                                  # a capture problem must not cost the bench line
+                rec["cuda_graph_error"] = repr(e)[:200]
+        out[name] = rec
+        del fr, b
+    # C5: K-A alone, 1080p
+    c = synth.CONFIGS["C5"]
+    F = 64
+    H, W = c["H"], c["W"]
+    depth = torch.empty((F, H, W), dtype=torch.float32, device=dev)
+    ground = torch.empty((F, H, W), dtype=torch.bool, device=dev)
+    K = torch.empty((F, 3, 3), dtype=torch.float32, device=dev)
+    for i in range(F):
+        f = synth.make_frame(i, H, W, 6, device=dev, with_masks=False)
+        depth[i], ground[i], K[i] = f.depth, f.ground, f.K
+    ev = _events(3)
+
+    def ka():
+        ev[0].record()
+        pts, _, cnt = api.backproject(depth, ground, K, 5, L.BACKPROJECT_NUMPY, want_other=False)
+        ev[1].record()
+        api.ransac_plane(pts, cnt[:, 0].contiguous(), None, seed=7, iters=1000, thresh=0.05)
+        ev[2].record()
+    ms = timed(ka, steps)
+    P = ((H + 4) // 5) * ((W + 4) // 5)
+    out["C5"] = {"frames": F, "of": c["frames"], "ms_per_step": ms, "value": F / (ms * 1e-3), "unit": "frames/s",
+                 "backproject_ms": ev[0].elapsed_time(ev[1]), "ransac_ms": ev[1].elapsed_time(ev[2]),
+                 "hbm_frac_strict": F * (5 * P + 16) / (ms * 1e-3) / 1e9 / peak,
+                 "bound": "fp32 fma issue (1000 hypotheses x P points); the back-projection half alone is sector-bound"}
+    return out
+
+
+def bench_mode_b(dev, peak, frames=8):
+    """mode B (MABO branch): all six scores + IoU3D + K-D curves for a few C2-shaped frames"""
+    from tdod import mabo, pipeline, synth
+    c = synth.CONFIGS["C2"]
+    fr = synth.make_frames("C2", range(frames), device=dev)
+    b = pipeline.FrameBatch.from_frames(fr, dev)
+    gt = pipeline.select(b, N_PROP, seed=99).best_cube.clone()
+    for _ in range(2):
+        mabo.mabo(b, gt, N_PROP, seed=5)
+    torch.cuda.synchronize(dev)
+    a, e = _events(2)
+    a.record()
+    r = mabo.mabo(b, gt, N_PROP, seed=5)
+    e.record()
+    torch.cuda.synchronize(dev)
+    ms = a.elapsed_time(e)
+    return {"frames": frames, "objects": b.n_obj, "n_prop": N_PROP, "ms_per_step": ms, "value": b.n_obj * N_PROP / (ms * 1e-3),
+            "unit": UNIT, "scores": "IoU2D, dims, corners, segmentation, mod-segmentation, points-in-cube, IoU3D, 8 curves, 26 products",
+            "bound": "int / fp32 issue (closed-form fillPoly spans per sampled row; point-in-interval compares)",
+            "mean_best_iou3d": float(r["iou3d"].max(1).values.mean())}
+
+
+def bench_c4(args, rank, world, dev):
+    """BASELINE configs[3]: pseudo-GT generation over a synthetic 10 000-frame split, STRONG scaling -- rank r owns the
+    contiguous block shard.frame_range(total, r, world).  Frames are produced on the device chunk by chunk (never 77 GB on
+    the host); per chunk the PRED-branch forward (tdod.pseudo_gt.forward_pred) and the Omni3D annotation records through the
+    resumable writer; the winners are gathered at the end.  Philox keys are global frame / object ids, so the winners do
+    not depend on the world size."""
+    import tempfile
+    import torch.distributed as dist
+    from tdod import pseudo_gt as PG, shard, synth
+    c = synth.CONFIGS["C4"]
+    H, W, total = c["H"], c["W"], args.c4_frames
+    lo, hi = shard.frame_range(total, rank, world)
+    counts = synth.object_counts(range(total), c["n_obj"])
+    obj_base = int(np.sum(counts[:lo]))
+    chunk = 256
+    tmp = tempfile.mkdtemp(prefix="tdod_c4_")
+    w = PG.PseudoGTWriter(os.path.join(tmp, "pseudo_gt_rank%d.json" % rank), {"id": 12, "name": "synthetic C4"}, [], resume=False)
+    t_gen = t_write = 0.0
+    gpu_ms = 0.0
+    n_obj = 0
+    recs = []
+    t_all0 = time.perf_counter()
+    for f0 in range(lo, hi, chunk):
+        f1 = min(hi, f0 + chunk)
+        t0 = time.perf_counter()
+        batch, off, cls = synth.make_batch(range(f0, f1), H, W, c["n_obj"], dev)
+        torch.cuda.synchronize(dev)
+        t_gen += time.perf_counter() - t0
+        a, e = _events(2)
+        a.record()
+        fields, sel = PG.forward_pred(batch, N_PROP, seed=7, obj_id_base=obj_base + n_obj, frame_id_base=f0)
+        e.record()
+        recs.append(shard.pack_winners(sel))
+        t0 = time.perf_counter()
+        cl = cls.tolist()
+        meta = [dict(id=fid, width=W, height=H, file_path="synthetic/%06d.jpg" % fid, K=batch.K[k].tolist())
+                for k, fid in enumerate(range(f0, f1))]
+        PG.write_frames(w, fields, off, meta, cl, ["class%d" % k for k in cl], gt_boxes=batch.boxes, net_hw=(H, W))
+        t_write += time.perf_counter() - t0
+        gpu_ms += a.elapsed_time(e)
+        n_obj += batch.n_obj
+        del batch, fields, sel
+    t0 = time.perf_counter()
+    w.finalize(return_doc=False)
+    n_ann = w.next_id - 1
+    t_write += time.perf_counter() - t0
+    wall = time.perf_counter() - t_all0
+    local = torch.cat(recs) if recs else torch.zeros((0, shard.WINNER_COLS), device=dev)
+    t0 = time.perf_counter()
+    allw = shard.gather_winners(local)
+    torch.cuda.synchronize(dev)
+    t_gather = time.perf_counter() - t0
+    v = torch.tensor([gpu_ms, wall - t_gen, t_write, t_gen, float(n_obj), float(hi - lo)], dtype=torch.float64, device=dev)
+    if world > 1:
+        vmax = v.clone(); dist.all_reduce(vmax, op=dist.ReduceOp.MAX)
+        vsum = v.clone(); dist.all_reduce(vsum, op=dist.ReduceOp.SUM)
+    else:
+        vmax = vsum = v
+    props = float(vsum[4]) * N_PROP
+    import shutil
+    shutil.rmtree(tmp, ignore_errors=True)
+    return {"frames": total, "frames_rank0": hi - lo, "objects": int(vsum[4]), "scaling": "strong",
+            "path_ms_max_rank": float(vmax[0]), "value": props / (float(vmax[0]) * 1e-3), "unit": UNIT,
+            "frames_per_s_path": float(vsum[5]) / (float(vmax[0]) * 1e-3),
+            "with_writer_s_max_rank": float(vmax[1]), "value_with_writer": props / float(vmax[1]),
+            "writer_s_max_rank": float(vmax[2]), "writer_share": float(vmax[2]) / max(float(vmax[1]), 1e-9),
+            "synthetic_generation_s_max_rank": float(vmax[3]), "annotations_rank0": n_ann,
+            "final_gather": {"records": int(allw.shape[0]), "ms": t_gather * 1e3},
+            "note": "value = proposals of all ranks / device time of the slowest rank (CUDA events around the per-chunk forward); "
+                    "with_writer adds the Python json records (host-bound); frame generation is outside both"}
 
 
 def run_tdod(args):
@@ -225,21 +442,14 @@ def run_tdod(args):
     H, W = c["H"], c["W"]
     F = args.frames
     # weak scaling: rank r owns global frames [r*F, (r+1)*F); no data-path collective
-    frame_ids = range(rank * F, (rank + 1) * F)
-    frames = [synth.make_frame(i, H, W, c["n_obj"], device=dev) for i in frame_ids]
-    batch = pipeline.FrameBatch.from_frames(frames, dev)
-    off = [0]
-    for f in frames:
-        off.append(off[-1] + f.n_obj())
-    del frames
+    batch, off, _ = synth.make_batch(range(rank * F, (rank + 1) * F), H, W, c["n_obj"], dev)
     N = batch.n_obj
     props = N * N_PROP
     obj_base = rank * F * 64          # any injective global id works for the Philox keying
     abytes = algorithmic_bytes(batch, N_PROP)
-
     stream = torch.cuda.current_stream(dev)
     stage_names = list(abytes)
-    stage_marks = [("ka0", "ka1"), ("kb0", "kb_mid"), ("kb_mid", "kb1"), ("kc0", "kc1")]
+    stage_marks = [("ka0", "ka1"), ("kb0", "kb1"), ("kc0", "kc1")]
 
     def step(marks=None, overlap=True):
         """one pass of the hot path (tdod.pipeline.select): K-A -> yaw table on the auxiliary stream, K-B on the current
@@ -252,13 +462,10 @@ def run_tdod(args):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    def stage_times(all_marks):
-        return [float(np.mean([m[a].elapsed_time(m[b]) for m in all_marks])) for a, b in stage_marks]
-
     for _ in range(max(args.warmup, 3)):
         o = step()
     barrier()
-    t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_start, t_end = _events(2)
     with ClockSampler(local) as clk:
         barrier()
         if args.profile:
@@ -270,23 +477,45 @@ def run_tdod(args):
         barrier()
         if args.profile:
             torch.cuda.profiler.stop()
-    total_ms = t_start.elapsed_time(t_end)
-    # the same K steps once more on ONE stream with events between the stages: stage times free of contention (inside the
-    # timed region K-A runs on an auxiliary stream and two object ranges are in flight on two more, so kernels overlap)
-    marks_serial = [dict() for _ in range(args.steps)]
-    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    s0.record(stream)
-    for k in range(args.steps):
-        step(marks_serial[k], overlap=False)
-    s1.record(stream)
-    barrier()
+        total_ms = t_start.elapsed_time(t_end)
+        # the same K steps once more on ONE stream with events between the stages: stage times free of contention (inside the
+        # timed region K-A runs on an auxiliary stream beside K-B).  Still under the clock sampler.
+        marks_serial = [dict() for _ in range(args.steps)]
+        s0, s1 = _events(2)
+        barrier()
+        s0.record(stream)
+        for k in range(args.steps):
+            step(marks_serial[k], overlap=False)
+        s1.record(stream)
+        barrier()
     serial_ms_step = s0.elapsed_time(s1) / args.steps
-    stage_ms_serial = stage_times(marks_serial)
+    stage_ms_serial = [float(np.mean([m[a].elapsed_time(m[b]) for m in marks_serial])) for a, b in stage_marks]
     # np.argmax returns the first NaN (roi_heads.py:501): objects whose proposals include a zero-height projected box
     # have a NaN winner in the reference too; everything else must be finite
     winners_nan = int(torch.isnan(o.best_score).sum().item())
     winners_ok = bool((torch.isfinite(o.best_score) | torch.isnan(o.best_score)).all().item())
+
+    # ---- the proposal set DEFINED BY THE REFERENCE: torch's generators in its draw order, inside the timed region ----
+    parity = None
+    if not args.no_parity_rng:
+        gd_, gc_ = torch.Generator(device=dev).manual_seed(1000 + rank), torch.Generator().manual_seed(2000 + rank)
+        p_steps = 3
+        barrier()
+        a0, a1 = _events(2)
+        t0 = time.perf_counter()
+        a0.record(stream)
+        for _ in range(p_steps):
+            nz, yw = pipeline.draw_reference_noise(batch, off, N_PROP, generator=gd_, cpu_generator=gc_)
+            pipeline.select(batch, N_PROP, noise=nz, yaw_idx=yw, frame_id_base=rank * F, std_mode=L.STD_TORCH_CUDA)
+        a1.record(stream)
+        barrier()
+        p_ms = a0.elapsed_time(a1) / p_steps
+        parity = {"value": props / (p_ms * 1e-3), "unit": UNIT, "ms_per_step": p_ms,
+                  "host_ms_per_step": (time.perf_counter() - t0) * 1e3 / p_steps,
+                  "what": "normals from torch's CUDA generator and yaw bins from its CPU generator in the reference's program "
+                          "order (per frame, whole-tensor redraw loops with their host synchronisation), fed through HOST mode "
+                          "with std_mode TORCH_CUDA: the proposal set is bit-equal to the reference's on CUDA tensors "
+                          "(tests/test_gpu_round2.py); the draws, not the kernels, take the time"}
 
     # ---- final gather of the 84-byte winner records (the only exchange; outside the timed region) ----
     from tdod import shard
@@ -313,25 +542,60 @@ def run_tdod(args):
         e_ms = (time.perf_counter() - t0) * 1e3 / e_steps
         e2e = {"ms": e_ms, "h2d": pipe.h2d_bytes // e_steps, "d2h": pipe.d2h_bytes // e_steps,
                "same_winners": bool(torch.equal(out[:, 20].int(), o.best_idx.cpu()))}
+        del pipe
+        # the OPTIONAL host format with the masks at 1 bit per pixel (pipeline.pack_masks; tdod_mask_rect_bitmap): reported
+        # beside the headline, never instead of it -- the reference's callers hold bool masks
+        hp = pipeline.FrameBatch(hb.depth, hb.ground, hb.K, hb.boxes, hb.prior_mean, hb.prior_std, hb.obj_frame, None,
+                                 hb.frame_ids, hb.has_ground, pipeline.pack_masks(hb.masks).pin_memory())
+        pipe = pipeline.Pipeline(H, W, N_PROP, chunk_frames=32, device=dev, seed=7, packed_masks=True)
+        out2 = torch.empty((N, 21), dtype=torch.float32).pin_memory()
+        for _ in range(2):
+            pipe.run_host(hp, off, out=out2, obj_id_base=obj_base, frame_id_base=rank * F)
+        pipe.h2d_bytes = pipe.d2h_bytes = 0
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e_steps):
+            pipe.run_host(hp, off, out=out2, obj_id_base=obj_base, frame_id_base=rank * F)
+        barrier()
+        e2e["packed_ms"] = (time.perf_counter() - t0) * 1e3 / e_steps
+        e2e["packed_h2d"] = pipe.h2d_bytes // e_steps
+        e2e["packed_same_winners"] = bool(torch.equal(out2[:, 20].int(), o.best_idx.cpu()))
+        del hb, hp, pipe
+
+    # ---- the other BASELINE configs (sub-records; C2 stays the headline) ----
+    peak, peak_src = peaks()
+    configs = {}
+    if not args.no_configs:
+        del batch
+        torch.cuda.empty_cache()
+        if rank == 0:
+            try:
+                configs.update(bench_small_configs(dev, 10, peak))
+                configs["C2 mode B"] = bench_mode_b(dev, peak)
+            except Exception as e:
+                configs["error"] = repr(e)[:300]
+        torch.cuda.empty_cache()
+        barrier()
+        try:
+            configs["C4"] = bench_c4(args, rank, world, dev)
+        except Exception as e:
+            configs["C4"] = {"error": repr(e)[:300]}
 
     # ---- max over ranks ----
-    t = torch.tensor([total_ms, e2e["ms"] if e2e else 0.0, float(props)], dtype=torch.float64, device=dev)
+    t = torch.tensor([total_ms, e2e["ms"] if e2e else 0.0, float(props), parity["ms_per_step"] if parity else 0.0,
+                      e2e["packed_ms"] if e2e else 0.0], dtype=torch.float64, device=dev)
     if world > 1:
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        total_ms, e_ms_max, props_all = float(tmax[0]), float(tmax[1]), float(tsum[2])
+        total_ms, e_ms_max, props_all, p_ms_max, ep_ms_max = float(tmax[0]), float(tmax[1]), float(tsum[2]), float(tmax[3]), float(tmax[4])
     else:
-        e_ms_max, props_all = float(t[1]), float(props)
+        e_ms_max, props_all, p_ms_max, ep_ms_max = float(t[1]), float(props), float(t[3]), float(t[4])
     if rank == 0:
-        peak, peak_src = peaks()
         ms_step = total_ms / args.steps
-        # the roofline object describes the kernel that moves the step's bytes (98 % of the compulsory traffic): the
-        # HBM-bound stage with the longest duration; every stage's time, bound and HBM fraction is listed beside it
-        hbm = [k for k, nme in enumerate(stage_names) if BOUND[nme] == "hbm"]
-        j = max(hbm, key=lambda k: stage_ms_serial[k])
-        dom = stage_names[j]
-        ach = abytes[dom] / (stage_ms_serial[j] * 1e-3) / 1e9
         step_bytes = sum(abytes.values())
+        j = int(np.argmax(stage_ms_serial))                # the roofline object describes the stage that takes longest
+        dom = stage_names[j]
+        ach = step_bytes / (ms_step * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": props_all / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
@@ -339,23 +603,39 @@ def run_tdod(args):
             "config": {"workload": "BASELINE configs[1]: %d frames %dx%d per GPU, %d objects (~15/frame) x %d proposals, mode A "
                                    "(back-projection + RANSAC plane, mask rectangle, fused propose/project/IoU x dims x corners/argmax)"
                                    % (F, W, H, N, N_PROP),
-                       "frames_per_gpu": F, "objects_rank0": N, "rng": "in-kernel Philox4x32-10",
-                       "l2": "inputs (%.2f GB per pass) are larger than the 126 MB L2" % (batch.input_bytes() / 1e9)},
+                       "frames_per_gpu": F, "objects_rank0": N, "rng": "in-kernel Philox4x32-10 (replayed bit for bit through the "
+                       "reference-pinned HOST mode in tests/test_gpu_round2.py)",
+                       "l2": "inputs (1.98 GB per pass) are larger than the 126 MB L2"},
             "gpu_launches": pipeline.launches_per_select(N) * args.steps,
             "stages_ms_serial": dict(zip(stage_names, stage_ms_serial)), "ms_per_step_serial": serial_ms_step,
-            "roofline": {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                         "traffic": TRAFFIC.get(dom), "peak_source": peak_src, "algorithmic_bytes_per_launch": abytes[dom],
-                         "timed": "stages_ms_serial: the same K steps once more on one stream, CUDA events between the stages "
-                                  "(in the timed region the stages overlap on several streams)",
-                         "step_algorithmic_bytes": step_bytes, "step_frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak,
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                         "traffic": sum(TRAFFIC.values()), "peak_source": peak_src,
+                         "what": "the whole step: SURVEY 8(d) algorithmic bytes of all stages / measured step time (98 % of the "
+                                 "bytes are mask bytes, read once by K-B)",
+                         "step_algorithmic_bytes": step_bytes,
+                         "kernel": dom, "kernel_ms": stage_ms_serial[j], "kernel_bound": BOUND[dom],
+                         "kernel_hbm_frac": abytes[dom] / (stage_ms_serial[j] * 1e-3) / 1e9 / peak,
+                         "kernel_algorithmic_bytes_per_launch": abytes[dom], "kernel_traffic": TRAFFIC.get(dom),
+                         "timed": "stages_ms_serial: the same K steps once more on one stream, CUDA events between the stages",
                          "all_stages": {n: {"ms": m, "bound": BOUND[n], "hbm_frac": abytes[n] / (m * 1e-3) / 1e9 / peak}
                                         for n, m in zip(stage_names, stage_ms_serial)}},
             "clocks": clk.summary(), "winners_ok": winners_ok, "winners_nan": winners_nan,
             "final_gather": {"records": int(gathered.shape[0]), "bytes": int(gathered.numel() * 4), "ms": gather_ms},
         }
+        if parity:
+            parity["value"] = props_all / (p_ms_max * 1e-3)
+            line["value_parity_rng"] = parity
         if e2e:
             line["e2e"] = {"value": props_all / (e_ms_max * 1e-3), "unit": UNIT, "h2d_bytes_per_step": e2e["h2d"],
-                           "d2h_bytes_per_step": e2e["d2h"], "ms_per_step": e_ms_max, "same_winners_as_resident": e2e["same_winners"]}
+                           "d2h_bytes_per_step": e2e["d2h"], "ms_per_step": e_ms_max, "same_winners_as_resident": e2e["same_winners"],
+                           "host_masks": "torch.bool, 1 byte per pixel (what the reference's callers hold)",
+                           "optional_packed_masks": {"value": props_all / (ep_ms_max * 1e-3), "unit": UNIT, "ms_per_step": ep_ms_max,
+                                                     "h2d_bytes_per_step": e2e["packed_h2d"],
+                                                     "same_winners_as_resident": e2e["packed_same_winners"],
+                                                     "what": "host batch with masks at 1 bit per pixel (pipeline.pack_masks, "
+                                                             "packed outside the timed region); labelled, not the headline"}}
+        if configs:
+            line["configs"] = configs
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_single()
         print(json.dumps(line), file=_JSON_OUT, flush=True)

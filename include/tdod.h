@@ -82,8 +82,12 @@ int tdod_score_dimensions(const float* prior_mean, const float* prior_std, const
 
 /* first half of score_corners (scorefunction.py:59-68): per mask, the largest external contour's minimum-area
  * rectangle (cv2.findContours RETR_EXTERNAL -> max contourArea -> minAreaRect -> boxPoints).
- * masks [n_masks,H,W] 1 B/px; out_rects [n_masks,4,2]; out_has_rect [n_masks] (0 when the mask is empty).
- * workspace: tdod_mask_rect_workspace_bytes(n_masks,H,W) bytes of device scratch. */
+ * masks [n_masks,H,W] 1 B/px; out_rects [n_masks,4,2]; out_has_rect [n_masks]: 1 = rectangle written, 0 = empty mask (the
+ * caller applies the fallback rectangle of :69-75).  The masks are read as aligned 16-byte chunks: up to 15 bytes before
+ * the first and after the last mask byte are touched (never interpreted); torch allocations always cover them.
+ * Masks up to 1024 px wide whose run tables fit in shared memory take the fused path (bits never leave the SM);
+ * larger ones are packed to a 1 bit/px workspace copy first.  Bytes other than 0 / 1 are valid (non-zero = set) and
+ * take the general path.  workspace: tdod_mask_rect_workspace_bytes(n_masks,H,W) bytes of device scratch. */
 int64_t tdod_mask_rect_workspace_bytes(int64_t n_masks, int H, int W);
 int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int W, float* out_rects, uint8_t* out_has_rect,
                    void* workspace, int64_t workspace_bytes, void* stream);
@@ -96,6 +100,12 @@ int tdod_mask_pack(const uint8_t* masks, int64_t n_masks, int H, int W, void* wo
                    void* stream);
 int tdod_mask_rect_packed(int64_t n_masks, int H, int W, float* out_rects, uint8_t* out_has_rect, void* workspace,
                           int64_t workspace_bytes, void* stream);
+
+/* The same rectangles from masks the caller already holds at 1 bit per pixel: bitmap [n_masks,H,Wp] 32-bit words, Wp =
+ * ceil(W/32), bit (c & 31) of word (c >> 5) of a row = pixel c, unused high bits of a row's last word zero.  For hosts
+ * that store or ship masks packed (1/8 of the PCIe bytes of torch.bool masks); same workspace query. */
+int tdod_mask_rect_bitmap(const uint32_t* bitmap, int64_t n_masks, int H, int W, float* out_rects, uint8_t* out_has_rect,
+                          void* workspace, int64_t workspace_bytes, void* stream);
 
 /* second half of score_corners (scorefunction.py:69-85 + modified_chamfer_distance :51-56).
  * rect [4,2] (ignored when has_rect == 0: the fallback rectangle of :69-75 is computed from the corners). */

@@ -79,14 +79,15 @@ def draw_normal_rows(mean, std, n, lo=None, hi=None, generator=None):
     standard-normal stream is consumed identically, which lets us also return the ACCEPTED
     standard normal per element (what the CUDA parity mode is fed).  Returns (samples, z, tries)."""
     N = mean.shape[0]
-    z = torch.randn((N, n), generator=generator)
+    dev = mean.device                      # CUDA tensors + a CUDA generator: the reference's production flavour
+    z = torch.randn((N, n), generator=generator, device=dev)
     s = z * std[:, None] + mean[:, None]
     tries = 0
     if lo is not None and hi is not None:
         hi_b = hi[:, None].expand_as(s)
         while bool(torch.any((s < lo) | (s > hi_b))):
             bad = (s < lo) | (s > hi_b)
-            z2 = torch.randn((N, n), generator=generator)
+            z2 = torch.randn((N, n), generator=generator, device=dev)
             s2 = z2 * std[:, None] + mean[:, None]
             s = torch.where(bad, s2, s)
             z = torch.where(bad, z2, z)
@@ -155,8 +156,10 @@ def cubes_from_noise(boxes, depth, prior_mean, prior_std, K, n, noise, normal=No
     return torch.cat((xyzwhl, R.flatten(start_dim=2)), dim=2).to(torch.float32)          # spaces.py:143
 
 
-def propose(boxes, depth, prior_mean, prior_std, K, n, normal=None, generator=None):
-    """proposals.py:338-424 `propose` on raw tensors.  Returns dict with
+def propose(boxes, depth, prior_mean, prior_std, K, n, normal=None, generator=None, host_generator=None):
+    """proposals.py:338-424 `propose` on raw tensors.  `generator` feeds the six normal draws (on the tensors' device);
+    `host_generator` (default: `generator`) the draws the reference makes on the HOST whatever the device: the yaw bins
+    (torch.randint without a device, :407) and the random rotations (utils.py:62-69).  Returns dict with
     cubes [N,n,15] fp32, noise [6,N,n] accepted standard normals in draw order (w,h,l,x,y,z),
     yaw_idx [N,n] int64 (or None), rot [N,n,3,3] (or None), tries [3]."""
     N = boxes.shape[0]
@@ -178,12 +181,13 @@ def propose(boxes, depth, prior_mean, prior_std, K, n, normal=None, generator=No
     xyzwhl = torch.stack([x, y, z, w, h, l], 2)
     yaw_idx = None
     rot = None
+    hg = generator if host_generator is None else host_generator
     if normal is None:
-        R = rot = random_rotations(N, n, generator)
+        R = rot = random_rotations(N, n, hg).to(boxes.device)
     else:
-        tab = yaw_table(normal)
-        yaw_idx = torch.randint(N_YAW, (N, n), generator=generator)
-        R = tab[yaw_idx]
+        tab = yaw_table(normal.cpu())
+        yaw_idx = torch.randint(N_YAW, (N, n), generator=hg)
+        R = tab[yaw_idx].to(boxes.device)
     cubes = torch.cat((xyzwhl, R.flatten(start_dim=2)), dim=2).to(torch.float32)  # spaces.py:143
     return dict(cubes=cubes, noise=torch.stack([zw, zh, zl, zx, zy, zz], 0), yaw_idx=yaw_idx, rot=rot,
                 tries=(tw, th, tl), seeds=(x0, y0, z0))

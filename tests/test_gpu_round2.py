@@ -387,3 +387,76 @@ def test_mabo_branch_curves_and_combinations():
             assert comb[i, k] in iou3d[i][best].astype(np.float32), (i, names)
     # the winner is the mode-A argmax scored against the projected GT cube
     assert torch.equal(r["selection"].best_idx.cpu(), torch.from_numpy(np.array([int(np.argmax(x)) for x in ch["combined"]])).int())
+
+
+def test_reference_order_draws_reproduce_the_cuda_tensor_reference():
+    """pipeline.draw_reference_noise consumes torch's CUDA generator (normals) and CPU generator (yaw bins) exactly as the
+    reference's `propose` does on CUDA tensors (proposals.py:377-407, utils.py:42-60 incl. the whole-tensor redraw loops):
+    the oracle's `propose` run on CUDA tensors with the same two seeds and K-C fed the drawn numbers (std_mode TORCH_CUDA)
+    give the same proposal set, bit for bit"""
+    d = dev()
+    # torch.normal(mean_t, std_t) == randn * std + mean on CUDA, same generator consumption (what both sides rely on)
+    g1 = torch.Generator(device=d).manual_seed(5); g2 = torch.Generator(device=d).manual_seed(5)
+    m, s = torch.rand(7, device=d) + 0.5, torch.rand(7, device=d) + 0.1
+    a = torch.normal(m[:, None].expand(7, 333), s[:, None].expand(7, 333), generator=g1)
+    b2 = torch.randn((7, 333), generator=g2, device=d) * s[:, None] + m[:, None]
+    assert torch.equal(bits(a), bits(b2))
+    assert torch.equal(bits(torch.randn(11, generator=g1, device=d)), bits(torch.randn(11, generator=g2, device=d)))
+    frames = synth.make_frames("C2", range(3))
+    b = pipeline.FrameBatch.from_frames(frames, d)
+    off = np.cumsum([0] + [f.n_obj() for f in frames]).tolist()
+    n = 1000
+    s0 = pipeline.select(b, n, seed=1)                       # planes (Philox sample ids) -> normals for both sides
+    torch.cuda.synchronize()
+    gd_, gc_ = torch.Generator(device=d).manual_seed(77), torch.Generator().manual_seed(78)
+    noise, yaw = pipeline.draw_reference_noise(b, off, n, generator=gd_, cpu_generator=gc_)
+    k = api.propose_score_select(b.depth, b.K, b.boxes, b.prior_mean, b.prior_std, b.obj_frame, s0.rects, s0.has_rect, n,
+                                 yaw_tab=api.yaw_table(s0.normal), noise=noise, yaw_idx=yaw, return_all=True,
+                                 std_mode=L.STD_TORCH_CUDA)
+    torch.cuda.synchronize()
+    gd_, gc_ = torch.Generator(device=d).manual_seed(77), torch.Generator().manual_seed(78)
+    for fi, f in enumerate(frames):
+        o = O.propose(f.boxes.to(d), f.depth.to(d), f.prior_mean.to(d), f.prior_std.to(d), f.K.to(d), n,
+                      s0.normal[fi].cpu(), generator=gd_, host_generator=gc_)
+        assert torch.equal(bits(k.all_cubes[off[fi]:off[fi + 1]]), bits(o["cubes"])), fi
+
+
+def test_packed_masks_give_the_same_rectangles_and_winners():
+    """tdod_mask_rect_bitmap (masks the host already holds at 1 bit per pixel) == tdod_mask_rect on the byte masks, on
+    ordinary masks and on the families that need the exact passes; and the streaming pipeline fed packed masks returns the
+    winners of the resident run"""
+    d = dev()
+    frames = synth.make_frames("C2", range(6))
+    b = pipeline.FrameBatch.from_frames(frames, d)
+    r1, h1 = api.mask_rect(b.masks)
+    bp = pipeline.pack_masks(b.masks)
+    assert bp.dtype == torch.int32 and bp.shape == (b.n_obj, 530, 23)
+    r2, h2 = api.mask_rect_bitmap(bp, 730)
+    torch.cuda.synchronize()
+    assert torch.equal(h1, h2) and torch.equal(bits(r1[h1 == 1]), bits(r2[h2 == 1]))
+    rs = np.random.RandomState(3)
+    yy, xx = np.mgrid[0:200, 0:240]
+    ms = []
+    for t in range(24):                                   # rings with a rival square (hole filling decides), speckle, empty
+        if t % 3 == 0:
+            cx, cy, a_, b_ = rs.uniform(60, 180), rs.uniform(60, 140), rs.uniform(20, 50), rs.uniform(20, 50)
+            m = (((xx - cx) / a_) ** 2 + ((yy - cy) / b_) ** 2 <= 1) & ~(((xx - cx) / (0.7 * a_)) ** 2 + ((yy - cy) / (0.7 * b_)) ** 2 <= 1)
+            m[0:30, 0:30] = True
+        elif t % 3 == 1:
+            m = rs.rand(200, 240) < 0.3
+        else:
+            m = np.zeros((200, 240), bool)
+        ms.append(m)
+    mt = torch.from_numpy(np.stack(ms)).to(d)
+    ra, ha = api.mask_rect(mt)
+    rb, hb_ = api.mask_rect_bitmap(pipeline.pack_masks(mt), 240)
+    torch.cuda.synchronize()
+    assert torch.equal(ha, hb_) and torch.equal(bits(ra[ha == 1]), bits(rb[hb_ == 1])) and set(ha.tolist()) <= {0, 1}
+    hbatch = pipeline.with_packed_masks(pipeline.FrameBatch.from_frames(frames, "cpu")).pin()
+    off = np.cumsum([0] + [f.n_obj() for f in frames]).tolist()
+    p = pipeline.Pipeline(530, 730, 1000, chunk_frames=4, seed=3, packed_masks=True)
+    out = p.run_host(hbatch, off)
+    s = pipeline.select(b, 1000, seed=3)
+    torch.cuda.synchronize()
+    assert torch.equal(out[:, 20].int(), s.best_idx.cpu())
+    assert p.h2d_bytes < 0.4 * b.input_bytes()

@@ -57,7 +57,7 @@ def test_resume_after_interruption_gives_the_same_document(tmp_path):
     p = str(tmp_path / "r.json")
     assert _run(p, range(7), resume=False, stop_after=3) is None
     with open(p + ".part.jsonl", "ab") as f:                 # a torn line, as a killed process leaves it
-        f.write(b'{"image": {"id": 99')
+        f.write(b'{"image": {"id": 99, "wid')
     w = PG.PseudoGTWriter(p, {}, [], resume=True)
     assert w.done_images == [1000, 1001, 1002]
     w._f.close()
@@ -120,3 +120,70 @@ def test_batched_forward_equals_per_object_path():
         assert torch.equal(quirk, fields["pred_boxes"][sl])
         eq = (s1.best_box == own["pred_boxes"][sl]) | (s1.best_box.isnan() & own["pred_boxes"][sl].isnan())
         assert bool(eq.all())
+
+
+def _oracle_frame(f, n, gen_seed, iou_ref_boxes):
+    """the oracle's chain for one frame with host-drawn randomness; iou_ref_boxes [N,4]: what the IoU term is scored
+    against (the 2D boxes in the PRED branch, roi_heads.py:496; the projected GT cubes in the pseudo branch, :466)"""
+    import random
+    import tdod_oracle as O
+    pg, _ = O.backproject_np(f.depth.numpy(), f.K.numpy(), f.ground.numpy())
+    ids = O.draw_sample_ids(len(pg), 300, random.Random(gen_seed))
+    eq, _, _ = O.ransac_np(pg, ids, 0.05)
+    nv = torch.from_numpy(O.rectify_normal(np.array(eq[:3])))
+    o = O.propose(f.boxes, f.depth, f.prior_mean, f.prior_std, f.K, n, nv, torch.Generator().manual_seed(gen_seed))
+    c2d = O.project_corners(O.cube_corners(o["cubes"]), f.K, f.W, f.H)
+    pb = O.boxes_from_corners(c2d)
+    best, comb, iou = [], [], []
+    for i in range(f.n_obj()):
+        s_iou = O.iou_score(iou_ref_boxes[i], pb[i])
+        s_dim = O.dims_score(f.prior_mean[i], f.prior_std[i], o["cubes"][i, :, 3:6], f.boxes[i], pb[i])
+        s_cor = O.corners_score(f.masks[i], c2d[i])
+        c, b = O.select(s_iou, s_dim, s_cor)
+        best.append(b); comb.append(c); iou.append(s_iou.numpy())
+    return o, ids, pb, np.array(best), np.stack(comb), np.stack(iou)
+
+
+@pytest.mark.gpu
+def test_batched_branches_against_the_oracle_chain():
+    """forward_pseudo (roi_heads.py:466-489: IoU against the PROJECTED GT CUBE, the `pred_boxes[0][highest_score]` quirk for
+    the 2D box), forward_pred (:493-505) and forward_learn (:460-464) against the oracle run object by object"""
+    import tdod_oracle as O
+    from tdod import pipeline, synth
+    d = torch.device("cuda:0")
+    n = 256
+    f = synth.make_frame(4, 480, 640, 5)
+    b = pipeline.FrameBatch.from_frames([f], d)
+    # "ground-truth" cubes: plausible cubes in front of the camera, projected like cubes_to_box(gt_cubes[i], K, im_shape)
+    g = torch.Generator().manual_seed(1)
+    gt = torch.zeros(5, 15)
+    gt[:, 0:2] = torch.rand(5, 2, generator=g) - 0.5
+    gt[:, 2] = 3.0 + torch.rand(5, generator=g)
+    gt[:, 3:6] = 0.5 + torch.rand(5, 3, generator=g)
+    gt[:, 6:] = torch.eye(3).reshape(9)
+    gt_boxes = O.boxes_from_corners(O.project_corners(O.cube_corners(gt), f.K, f.W, f.H))
+    for branch, ref_boxes in (("pseudo", gt_boxes), ("pred", f.boxes)):
+        o, ids, pb, best, comb, iou = _oracle_frame(f, n, 7, ref_boxes)
+        kw = dict(noise=o["noise"].permute(1, 0, 2).contiguous().to(d), yaw_idx=o["yaw_idx"].to(torch.int16).to(d),
+                  sample_ids=torch.from_numpy(ids.astype(np.int32))[None].contiguous().to(d), ransac_iters=300)
+        if branch == "pseudo":
+            fields, sel = PG.forward_pseudo(b, n, iou_boxes=gt_boxes.to(d), box_from_object0=True, **kw)
+        else:
+            fields, sel = PG.forward_pred(b, n, **kw)
+        torch.cuda.synchronize()
+        got = sel.best_idx.cpu().numpy()
+        for i in range(5):
+            top2 = np.sort(comb[i][~np.isnan(comb[i])])[-2:]
+            if np.isnan(comb[i]).any() or (len(top2) == 2 and top2[1] - top2[0] > 1e-5 * abs(top2[1])):
+                assert got[i] == best[i], (branch, i)
+                assert torch.allclose(fields["pred_center_cam"][i].cpu(), o["cubes"][i, best[i], :3], rtol=1e-5, atol=1e-6)
+                assert torch.equal(fields["pred_dimensions"][i].cpu(), o["cubes"][i, best[i], 3:6])
+                if branch == "pseudo":        # the 2D box is read from OBJECT 0's proposals at the winner's index (:476)
+                    assert torch.allclose(fields["pred_boxes"][i].cpu(), pb[0][best[i]], rtol=1e-5, atol=2e-3)
+        if branch == "pred":
+            assert torch.equal(fields["pred_boxes"].cpu(), f.boxes)          # instances_i.pred_boxes = gt_boxes (:650)
+            cubes, scores, _ = PG.forward_learn(b, n, **kw)
+            torch.cuda.synchronize()
+            assert cubes.shape == (5, n, 15)
+            assert np.allclose(scores.cpu().numpy(), iou, rtol=2e-5, atol=1e-6)
+            assert torch.equal(cubes[..., 3:].cpu(), o["cubes"][..., 3:])
