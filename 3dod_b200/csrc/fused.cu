@@ -227,9 +227,23 @@ template <> struct ClusterCtx<false> {
     template <typename T> __device__ __forceinline__ T* remote(T* p, int) { return p; }
 };
 
-template <bool kCluster>
-__global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const tdod_pss_args a, const int n_loc) {
+// kHot: the configuration of the throughput path -- in-kernel Philox, depth-seeded centres, prior dimensions, a yaw table,
+// winners only.  Every mode switch of the argument block becomes a compile-time constant there, which removes the code of
+// the other samplers, of the audit / return-all outputs and of the fallback sweep's bookkeeping from the instruction
+// stream (ncu: the general kernel is 107 KB of SASS and stalls on instruction fetch for 1.2 warp-cycles per issue).
+template <bool kCluster, bool kHot>
+__global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const tdod_pss_args a_in, const int n_loc) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    tdod_pss_args a = a_in;
+    if (kHot) {
+        a.rng_mode = TDOD_RNG_PHILOX; a.centre_mode = TDOD_CENTRE_DEPTH; a.dims_mode = TDOD_DIMS_PRIOR;
+        a.propose_only = 0; a.std_mode = TDOD_STD_EXACT;
+        a.noise = nullptr; a.yaw_idx = nullptr; a.rot = nullptr; a.aux = nullptr;
+        a.all_cubes = nullptr; a.all_boxes = nullptr; a.all_scores = nullptr; a.stats = nullptr;
+        a.out_noise = nullptr; a.out_yaw_idx = nullptr; a.out_seeds = nullptr;
+        __builtin_assume(a.yaw_table != nullptr);
+        __builtin_assume(a.obj_frame != nullptr);
+    }
     ClusterCtx<kCluster> cl;
     const int S = cl.size();
     const int rank = cl.rank();
@@ -684,16 +698,25 @@ extern "C" int tdod_propose_score_select(const tdod_pss_args* ap, void* stream) 
     const size_t smem = ((sizeof(Shared) + 15) & ~size_t(15)) + (size_t)7 * n_loc * sizeof(float);
     if (smem > 227 * 1024) return tdod_fail(TDOD_ERANGE, "n_prop too large for shared memory at this cluster size");
     cudaError_t e;
-    static tdod_smem_cache sm_cta, sm_cluster;
+    static tdod_smem_cache sm_cta, sm_cluster, sm_hot;
+    const bool hot = a.rng_mode == TDOD_RNG_PHILOX && a.centre_mode == TDOD_CENTRE_DEPTH && a.dims_mode == TDOD_DIMS_PRIOR &&
+                     a.yaw_table && a.obj_frame && !a.propose_only && a.std_mode == TDOD_STD_EXACT && !a.all_cubes && !a.all_boxes &&
+                     !a.all_scores && !a.stats && !a.out_noise && !a.out_yaw_idx && !a.out_seeds && !a.mode_flags;
     if (S == 1) {
-        e = tdod_smem_opt_in((const void*)pss_kernel<false>, smem, &sm_cta);
+        if (hot) {
+            e = tdod_smem_opt_in((const void*)pss_kernel<false, true>, smem, &sm_hot);
+            if (e != cudaSuccess) return (int)e;
+            pss_kernel<false, true><<<(unsigned)a.n_obj, kThreads, smem, (cudaStream_t)stream>>>(a, n_loc);
+            return (int)cudaGetLastError();
+        }
+        e = tdod_smem_opt_in((const void*)pss_kernel<false, false>, smem, &sm_cta);
         if (e != cudaSuccess) return (int)e;
-        pss_kernel<false><<<(unsigned)a.n_obj, kThreads, smem, (cudaStream_t)stream>>>(a, n_loc);
+        pss_kernel<false, false><<<(unsigned)a.n_obj, kThreads, smem, (cudaStream_t)stream>>>(a, n_loc);
         e = cudaGetLastError();
         if (e != cudaSuccess) return (int)e;
         return a.mode_flags ? tdod_modeb_launch(a, stream) : TDOD_OK;
     }
-    e = tdod_smem_opt_in((const void*)pss_kernel<true>, smem, &sm_cluster);
+    e = tdod_smem_opt_in((const void*)pss_kernel<true, false>, smem, &sm_cluster);
     if (e != cudaSuccess) return (int)e;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)((int64_t)a.n_obj * S), 1, 1);
@@ -704,7 +727,7 @@ extern "C" int tdod_propose_score_select(const tdod_pss_args* ap, void* stream) 
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = S; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
-    e = cudaLaunchKernelEx(&cfg, pss_kernel<true>, a, n_loc);
+    e = cudaLaunchKernelEx(&cfg, pss_kernel<true, false>, a, n_loc);
     if (e != cudaSuccess) return (int)e;
     return a.mode_flags ? tdod_modeb_launch(a, stream) : TDOD_OK;
 }
