@@ -510,18 +510,27 @@ __device__ int label_from_runs(RunSet rs, int R) {
     TG::sync();
     KB_T(20);
     // cell formula on pairs of overlapping runs in adjacent rows: 2*full + (#3-corner end cells)
-    for (int i = TG::tid(); i < R; i += TG::size()) {
-        const int r = rs.row[i];
-        if (r == 0) continue;
-        const int s = rs.xs[i], e = rs.xe[i];
-        int acc = 0;
-        for (int j = rs.row_off[r - 1]; j < rs.row_off[r]; ++j) {
-            const int s2 = rs.xs[j], e2 = rs.xe[j];
-            if (s2 > e) break;
-            if (e2 < s) continue;
-            acc += 2 * (min(e, e2) - max(s, s2)) + (s != s2) + (e != e2);
+    // (the runs of a blob sit next to each other in the list and share their root: lanes with the same root are summed with
+    // match.any + a masked reduction, one shared-memory add per root and warp instead of thirty-two on one address)
+    for (int i0 = 0; i0 < R; i0 += TG::size()) {
+        const int i = i0 + TG::tid();
+        int acc = 0, root = -1;
+        if (i < R) {
+            const int r = rs.row[i];
+            if (r != 0) {
+                const int s = rs.xs[i], e = rs.xe[i];
+                for (int j = rs.row_off[r - 1]; j < rs.row_off[r]; ++j) {
+                    const int s2 = rs.xs[j], e2 = rs.xe[j];
+                    if (s2 > e) break;
+                    if (e2 < s) continue;
+                    acc += 2 * (min(e, e2) - max(s, s2)) + (s != s2) + (e != e2);
+                }
+            }
+            if (acc) root = rs.parent[i];
         }
-        if (acc) atomicAdd(&rs.area2[rs.parent[i]], acc);
+        const unsigned peers = __match_any_sync(0xffffffffu, root);
+        const int sum = __reduce_add_sync(peers, acc);
+        if (root >= 0 && (int)(__ffs(peers) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&rs.area2[root], sum);
     }
     TG::sync();
     return R;
@@ -721,12 +730,17 @@ __device__ void component_rows(const RunSet& rs, int R, int root, int H, int* ro
     if (tid == 0) { counts[0] = 0; counts[1] = 0; counts[2] = 0x7fffffff; counts[3] = -1; }
     for (int r = tid; r < H; r += TG::size()) { rowL[r] = 0x7fffffff; rowR[r] = -1; }
     TG::sync();
-    for (int i = tid; i < R; i += TG::size())
-        if (rs.parent[i] == root) {
+    for (int i0 = 0; i0 < R; i0 += TG::size()) {
+        const int i = i0 + tid;
+        int rlo = 0x7fffffff, rhi = -1;
+        if (i < R && rs.parent[i] == root) {
             const int r = rs.row[i];
             atomicMin(&rowL[r], (int)rs.xs[i]); atomicMax(&rowR[r], (int)rs.xe[i]);
-            atomicMin(&counts[2], r); atomicMax(&counts[3], r);
+            rlo = rhi = r;
         }
+        rlo = __reduce_min_sync(0xffffffffu, rlo); rhi = __reduce_max_sync(0xffffffffu, rhi);   // one pair of atomics per warp
+        if ((threadIdx.x & 31) == 0 && rhi >= 0) { atomicMin(&counts[2], rlo); atomicMax(&counts[3], rhi); }
+    }
     TG::sync();
 }
 
@@ -1172,6 +1186,16 @@ __host__ __device__ inline size_t cand_stride(int H) { return align16(8 + (size_
 // runs of a finished group (one thread per row), and after a mask's last group its labels, areas, winner and the record.
 // The halves hand over through mbarriers (stream full / stream free), so while the extract half works on mask k the pack
 // half keeps HBM streaming for mask k + 1: the kernel's loads never pause for the labelling.
+#ifdef TDOD_KB_PROF
+__device__ unsigned long long g_kb_prof[16];
+#define KBP_DECL long long kbp_t = clock64(); long long kbp_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#define KBP(k) do { const long long t__ = clock64(); kbp_acc[k] += t__ - kbp_t; kbp_t = t__; } while (0)
+#define KBP_FLUSH(base, leader) do { if (leader) for (int q__ = 0; q__ < 8; ++q__) atomicAdd(&g_kb_prof[(base) + q__], (unsigned long long)kbp_acc[q__]); } while (0)
+#else
+#define KBP_DECL
+#define KBP(k) do { } while (0)
+#define KBP_FLUSH(base, leader) do { } while (0)
+#endif
 constexpr int kHalf = 128;              // pack threads
 constexpr int kExT = 256;               // extract / label threads
 constexpr int kGroupRows = kExT / 2;    // rows per bit-stream buffer: two extract threads per row
@@ -1280,6 +1304,7 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
         }
         int g = 0, gs = 0;                              // tiles / groups handled so far by this CTA
         int mi = 0;                                     // masks handled so far
+        KBP_DECL
         for (int64_t m = blockIdx.x; m < n_masks; m += gridDim.x, ++mi) {
             uint32_t other = 0u;
             const int off_m = (int)((base + (uintptr_t)(m * HW)) & 15);
@@ -1288,13 +1313,17 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
                 const int gc0 = (off_m + gr0 * W) >> 4, nG = ((off_m + gr1 * W + 15) >> 4) - gc0;
                 const int b = gs & 1;
                 // the buffer's previous group (two back) must have been read by the extract half
+                KBP(0);
                 if (gs >= 2) mbar_wait(&sb_free[b], (uint32_t)((gs >> 1) - 1) & 1u);
+                KBP(1);                                 // 1: waiting for the extract half to free a stream buffer
                 uint16_t* stream = reinterpret_cast<uint16_t*>(f.sb0 + b * f.sb_stride);
                 for (int tc = 0; tc < nG; tc += kTileChunks, ++g) {
                     const int slot = g & (kRing - 1);
                     if (tid == 0) issue_next();         // tile g + kRing - 1
                     const int nch = min(kTileChunks, nG - tc);
+                    KBP(0);
                     mbar_wait(&mb_full[slot], (uint32_t)(g >> 2) & 1u);
+                    KBP(2);                             // 2: waiting for the tile's bytes
                     const uint4* rv = reinterpret_cast<const uint4*>(f.raw0 + slot * f.raw_stride);
                     uint16_t* dst = stream + tc;
                     // all six loads first (index clamped, so always inside the tile): six LDS.128 in flight per thread
@@ -1317,6 +1346,8 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
                 mbar_arrive(&sb_full[b]);               // (release: the stream and the flag are visible to whoever waits)
             }
         }
+        KBP(0);                                         // 0: packing (and issuing)
+        KBP_FLUSH(0, tid == 32);
         return;
     }
 
@@ -1327,6 +1358,7 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
     const int nb_last = W - 32 * (Wp - 1);              // valid bits of a row's last word
     const uint32_t last_mask = nb_last < 32 ? ((1u << nb_last) - 1u) : 0xffffffffu;
     int gs = 0, mi = 0;
+    KBP_DECL
     for (int64_t m = blockIdx.x; m < n_masks; m += gridDim.x, ++mi) {
         int Rbase = 0;                                  // runs emitted so far (uniform over the half)
         const int off_m = (int)((base + (uintptr_t)(m * HW)) & 15);
@@ -1334,7 +1366,9 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
             const int gr1 = min(H, gr0 + kGroupRows);
             const int off0 = (off_m + gr0 * W) & 15;    // position of pixel (gr0, 0) in the stream
             const int b = gs & 1;
+            KBP(3);
             mbar_wait(&sb_full[b], (uint32_t)(gs >> 1) & 1u);
+            KBP(4);                                     // 4: waiting for the pack half
             const uint32_t* sb32 = reinterpret_cast<const uint32_t*>(f.sb0 + b * f.sb_stride);
             // ---- runs of the group's rows, TWO THREADS PER ROW, each walking half of the row's words (a warp per row spends 32
             // issue slots on what is mostly empty or solid words).  Thread order = raster order of the segments, so one scan
@@ -1349,7 +1383,17 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
             auto sbit = [&](int pos) { return (sb32[pos >> 5] >> (pos & 31)) & 1u; };
             int ns = 0, ne = 0;
             uint32_t carry_in = 0u;
+            // most segments are empty (rows above / below the object, words beside it): OR the aligned words that cover the
+            // segment first -- independent loads, no funnel shifts -- and walk it only when something is set.  The edge words
+            // also hold bits of the neighbouring rows: a false "non-empty" only costs the walk.
+            bool any = false;
             if (live && w0 < w1) {
+                const int a0 = (o0 + 32 * w0) >> 5, a1 = (o0 + 32 * w1 - 1) >> 5;
+                uint32_t acc = 0u;
+                for (int a = a0; a <= a1; ++a) acc |= sb32[a];
+                any = acc != 0u;
+            }
+            if (any) {
                 carry_in = w0 ? sbit(o0 + 32 * w0 - 1) : 0u;
                 uint32_t carry = carry_in, first = 0u, mw = 0u;
                 int o = o0 + 32 * w0;
@@ -1404,6 +1448,7 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
             Rbase += total;
             mbar_arrive(&sb_free[b]);                   // this thread is done with the stream buffer
             ExGrp::sync();                              // s_warp is free again; the runs are visible to the half
+            KBP(5);                                     // 5: run extraction
         }
         const int R = Rbase;
         const bool not01 = s_other[mi & 3] != 0u;       // (visible: ordered by the wait on the last group's sb_full)
@@ -1418,9 +1463,12 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
             ExGrp::sync();
             continue;
         }
+        KBP(3);
         label_from_runs<ExGrp>(f.rs, R);
+        KBP(6);                                         // 6: labelling
         bool ambiguous = false;
         const int root = select_component<ExGrp>(f.rs, R, true, f.scratch, &ambiguous);
+        KBP(7);                                         // 7: winner + rival bounds
         if (ambiguous) {                                // hole filling could change the winner: the exact pass decides
             if (et == 0) { out_has[m] = 2; list2[atomicAdd(&lists[0], 1)] = (int)m; }
             ExGrp::sync();
@@ -1436,7 +1484,9 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
         }
         if (et == 0) { reinterpret_cast<int*>(rec)[0] = rmin; reinterpret_cast<int*>(rec)[1] = rmax; out_has[m] = kPending; }
         ExGrp::sync();
+        KBP(3);                                         // 3: labels, winner, extremes
     }
+    KBP_FLUSH(8, et == 0);
 }
 
 struct TailSmem { int16_t* L; int16_t* R; int* keep; HullBuf hb; int* counts; float* out8; };
@@ -1699,6 +1749,16 @@ extern "C" int tdod_mask_rect_packed(int64_t n_masks, int H, int W, float* out_r
     if (rc) return rc;
     return rect_passes(p, p.bitmap, n_masks, H, W, out_rects, out_has_rect, (cudaStream_t)stream);
 }
+
+#ifdef TDOD_KB_PROF
+extern "C" int tdod_debug_kb_prof(unsigned long long* out16_host, int reset) {
+    unsigned long long z[16] = {0};
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out16_host, g_kb_prof, sizeof(z));
+    if (reset) cudaMemcpyToSymbol(g_kb_prof, z, sizeof(z));
+    return 0;
+}
+#endif
 
 extern "C" int tdod_mask_rect_bitmap(const uint32_t* bitmap, int64_t n_masks, int H, int W, float* out_rects,
                                      uint8_t* out_has_rect, void* workspace, int64_t workspace_bytes, void* stream) {

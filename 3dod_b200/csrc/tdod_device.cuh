@@ -113,7 +113,11 @@ struct Philox {
     __device__ __forceinline__ Philox(uint64_t seed) : k0((uint32_t)seed), k1((uint32_t)(seed >> 32)) {}
     __device__ __forceinline__ uint4 operator()(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3) const {
         uint32_t a = k0, b = k1;
-#pragma unroll
+#ifndef TDOD_PHILOX_UNROLL
+#define TDOD_PHILOX_UNROLL 10
+#endif
+        constexpr int kUnroll = TDOD_PHILOX_UNROLL;      // build knob: rolled rounds shrink the fused kernel's code
+#pragma unroll kUnroll
         for (int r = 0; r < 10; ++r) {
             const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
             const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
