@@ -10,7 +10,7 @@ int tdod_fail(int code, const char* msg) {
     return code;
 }
 
-extern "C" int tdod_version(void) { return 100; }
+extern "C" int tdod_version(void) { return 200; }
 
 extern "C" const char* tdod_last_error_string(void) { return g_last_error; }
 

@@ -4,12 +4,15 @@ an Omni3D / SUN-RGBD-shaped batch of 256 synthetic frames 730x530, ~15 objects p
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--frames F]
 
 A step = one pass of the hot path over the batch: K-A (back-projection + RANSAC ground plane + yaw table),
-K-B (mask -> min-area rectangle) and the fused K-C (propose + project + score + select) for every object.
+K-B (mask -> min-area rectangle, fused front + tail kernels) and the fused K-C (propose + project + score + select).
   value     device-resident inputs, CUDA events on the launching stream, max over ranks (weak scaling: every rank
             owns its own 256 frames)
-  e2e       the same batch through tdod.pipeline.Pipeline.run_host: pinned HOST inputs, H2D copies and the D2H read
-            of the winners inside the timed region
-  roofline  the stage that dominates the step, algorithmic bytes / its CUDA-event time over the timed region
+  e2e       the same batch through tdod.pipeline.Pipeline.run_host: pinned HOST inputs (bool masks), H2D copies and the
+            D2H read of the winners inside the timed region; e2e.optional_packed_masks: host masks at 1 bit per pixel
+  roofline  the WHOLE STEP against the measured HBM peak (algorithmic bytes of all stages / step time); the longest stage
+            is named with its own fraction and binding resource, every stage is listed
+  value_parity_rng  the proposal set defined by the reference: torch's generators in its draw order inside the timed region
+  configs   BASELINE configs 0, 2, 3, 4 as sub-records (C1, C3, C4 strong-scaled over the ranks, C5) + mode B
   cpu_baseline  the oracle (CPU restatement of the reference's torch/NumPy/OpenCV/SciPy path) on a bounded sample
 `--impl reference` times that CPU path on all host cores (the reference is Python: nothing to compile; the
 oracle port is the only form in which it travels to the GPU box)."""
