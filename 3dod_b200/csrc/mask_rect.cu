@@ -1202,6 +1202,19 @@ constexpr int kGroupRows = kExT / 2;    // rows per bit-stream buffer: two extra
 constexpr int kTileChunks = 768;        // 16-byte chunks per TMA tile (12 KB): six per pack thread
 using ExGrp = SubGrp<1, kExT, kHalf>;
 
+// Row slots of the bit stream: row r of a mask starts at byte off_m + r W of the 16-byte-aligned base, i.e. at bit
+// dl = (off_m + r W) & 15 of the 16-byte chunk that holds its first pixel.  The pack half converts, for every row, the
+// chunks that cover it (first to last, the straddling chunk of two neighbouring rows twice) into that row's OWN slot of
+// 16 QH half-words, so the row's pixels sit at bits [dl, dl + W) of a 16-byte-aligned slot: the extract half reads whole
+// quads with LDS.128 and never funnel-shifts; the bits outside the row are cleared in registers.
+__host__ __device__ inline int front_slot_hw(int W) { return (((W + 30) >> 4) + 15) & ~15; }
+__host__ __device__ inline int front_tile_rows(int W) {             // rows per TMA tile: 768 (row, chunk) pairs, 12 KB of bytes
+    int tr = kTileChunks / front_slot_hw(W);
+    const int by_bytes = (kTileChunks * 16 - 32) / W;
+    if (by_bytes < tr) tr = by_bytes;
+    return tr < kGroupRows ? tr : kGroupRows;
+}
+
 struct FrontSmem {
     unsigned char* raw0; size_t raw_stride;            // ring slot k at raw0 + k * raw_stride
     unsigned char* sb0; size_t sb_stride;               // two bit-stream buffers (a group of rows each): sb0 + b * sb_stride
@@ -1213,7 +1226,7 @@ __host__ __device__ inline size_t front_layout(int H, int W, FrontSmem* f, unsig
     const size_t o_raw = take((size_t)kTileChunks * 16);
     const size_t raw_stride = off - o_raw;
     for (int k = 1; k < kRing; ++k) take((size_t)kTileChunks * 16);
-    const size_t sbytes = ((size_t)kGroupRows * W + 15 + 7) / 8 + 48;       // misalignment in front, funnel over-read behind
+    const size_t sbytes = (size_t)kGroupRows * front_slot_hw(W) * 2;        // one 16-byte-aligned slot per row
     const size_t o_sb0 = take(sbytes), o_sb1 = take(sbytes);
     const size_t o_xs = take(kRunCap * 2), o_xe = take(kRunCap * 2), o_row = take(kRunCap * 2);
     const size_t o_par = take(kRunCap * 4), o_area = take(kRunCap * 4);
@@ -1243,10 +1256,14 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* b) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
 }
 
-// Wp <= 32 (W <= 1024).  All positions inside a mask are 32-bit byte offsets from its 16-byte-aligned base.
+// W <= 1024.  All positions inside a mask are 32-bit byte offsets from its 16-byte-aligned base.  QH = quads (16 bytes of
+// bit stream) per half row: a row slot is 2 QH quads = 16 QH half-words = front_slot_hw(W).
+template <int QH>
 __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t* __restrict__ masks, int64_t n_masks, int H, int W,
                                                                unsigned char* __restrict__ cand, uint8_t* __restrict__ out_has,
                                                                int* __restrict__ lists) {
+    constexpr int CR = 16 * QH;                         // half-words (= chunks) per row slot
+    constexpr int WH = 4 * QH;                          // words per half row
     extern __shared__ __align__(128) unsigned char fs_raw[];
     __shared__ __align__(8) uint64_t mb_full[kRing];   // the tile's bytes have landed (TMA transaction count)
     __shared__ __align__(8) uint64_t mb_free[kRing];   // all pack threads have turned the slot's bytes into bits
@@ -1257,9 +1274,9 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
     FrontSmem f;
     front_layout(H, W, &f, fs_raw);
     const int tid = threadIdx.x;
-    const int Wp = (W + 31) >> 5;
     const uintptr_t base = reinterpret_cast<uintptr_t>(masks);
     const int64_t HW = (int64_t)H * W;
+    const int TR = front_tile_rows(W);                  // rows per tile
     if (tid == 0) {
         for (int k = 0; k < kRing; ++k) { mbar_init(&mb_full[k], 1); mbar_init(&mb_free[k], kHalf); }
         for (int k = 0; k < 2; ++k) { mbar_init(&sb_full[k], kHalf); mbar_init(&sb_free[k], kExT); }
@@ -1270,37 +1287,35 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
 
     if (tid < kHalf) {
         // =============================== PACK half ===============================
-        // producer state (thread 0): the next tile to request, walking (mask, row group, tile) in the order it is consumed
+        // producer state (thread 0): the next tile to request, walking (mask, rows) in the order the tiles are consumed.
+        // A tile = up to TR rows of one row group = ONE contiguous run of chunks (neighbouring tiles share a chunk).
         int64_t pm = blockIdx.x;
-        int pgr0 = 0, pc = 0, pn = 0, issued = 0;
-        const unsigned char* pptr = nullptr;
-        auto group_of = [&](int64_t m, int gr0, const unsigned char*& gptr, int& nG) {
-            const uintptr_t a = base + (uintptr_t)(m * HW);
-            const int off_m = (int)(a & 15);
-            const int gr1 = min(H, gr0 + kGroupRows);
-            const int gc0 = (off_m + gr0 * W) >> 4, gc1 = (off_m + gr1 * W + 15) >> 4;
-            gptr = reinterpret_cast<const unsigned char*>(a - off_m) + ((size_t)gc0 << 4);
-            nG = gc1 - gc0;
-        };
+        int pr0 = 0, issued = 0;
         auto issue_next = [&]() {                       // thread 0 only
             if (pm >= n_masks) return;
-            const int nch = min(kTileChunks, pn - pc);
+            const uintptr_t a = base + (uintptr_t)(pm * HW);
+            const int off_m = (int)(a & 15);
+            const int r1 = min(min(H, (pr0 / kGroupRows + 1) * kGroupRows), pr0 + TR);
+            const int c0 = (off_m + pr0 * W) >> 4, c1 = (off_m + r1 * W + 15) >> 4;
             const int slot = issued & (kRing - 1);
             // refilling a slot: its previous tile (number issued - kRing) must have been packed by every pack thread
             if (issued >= kRing) mbar_wait(&mb_free[slot], (uint32_t)((issued >> 2) - 1) & 1u);
-            mbar_expect_tx(&mb_full[slot], (uint32_t)nch * 16u);
-            bulk_load(f.raw0 + slot * f.raw_stride, pptr + ((size_t)pc << 4), (uint32_t)nch * 16u, &mb_full[slot]);
+            mbar_expect_tx(&mb_full[slot], (uint32_t)(c1 - c0) * 16u);
+            bulk_load(f.raw0 + slot * f.raw_stride, reinterpret_cast<const unsigned char*>(a - off_m) + ((size_t)c0 << 4),
+                      (uint32_t)(c1 - c0) * 16u, &mb_full[slot]);
             ++issued;
-            pc += kTileChunks;
-            if (pc >= pn) {
-                pc = 0; pgr0 += kGroupRows;
-                if (pgr0 >= H) { pgr0 = 0; pm += gridDim.x; }
-                if (pm < n_masks) group_of(pm, pgr0, pptr, pn);
-            }
+            pr0 = r1;
+            if (pr0 >= H) { pr0 = 0; pm += gridDim.x; }
         };
-        if (tid == 0 && pm < n_masks) {
-            group_of(pm, 0, pptr, pn);
+        if (tid == 0)
             for (int k = 0; k < kRing - 1; ++k) issue_next();
+        // this thread's six (row of the tile, chunk of the row) pairs: the same in every tile
+        constexpr int kPairs = kTileChunks / kHalf;
+        int rw_u[kPairs], k_u[kPairs];
+#pragma unroll
+        for (int u = 0; u < kPairs; ++u) {
+            const int pp = tid + u * kHalf, rr = pp / CR;
+            k_u[u] = pp - rr * CR; rw_u[u] = rr * W;
         }
         int g = 0, gs = 0;                              // tiles / groups handled so far by this CTA
         int mi = 0;                                     // masks handled so far
@@ -1310,33 +1325,34 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
             const int off_m = (int)((base + (uintptr_t)(m * HW)) & 15);
             for (int gr0 = 0; gr0 < H; gr0 += kGroupRows, ++gs) {
                 const int gr1 = min(H, gr0 + kGroupRows);
-                const int gc0 = (off_m + gr0 * W) >> 4, nG = ((off_m + gr1 * W + 15) >> 4) - gc0;
                 const int b = gs & 1;
                 // the buffer's previous group (two back) must have been read by the extract half
                 KBP(0);
                 if (gs >= 2) mbar_wait(&sb_free[b], (uint32_t)((gs >> 1) - 1) & 1u);
                 KBP(1);                                 // 1: waiting for the extract half to free a stream buffer
                 uint16_t* stream = reinterpret_cast<uint16_t*>(f.sb0 + b * f.sb_stride);
-                for (int tc = 0; tc < nG; tc += kTileChunks, ++g) {
+                for (int tr0 = gr0; tr0 < gr1; tr0 += TR, ++g) {
+                    const int tr1 = min(gr1, tr0 + TR);
                     const int slot = g & (kRing - 1);
                     if (tid == 0) issue_next();         // tile g + kRing - 1
-                    const int nch = min(kTileChunks, nG - tc);
+                    const int t0 = off_m + tr0 * W;
+                    const int nch = ((off_m + tr1 * W + 15) >> 4) - (t0 >> 4), off_t = t0 & 15;
+                    const int np = (tr1 - tr0) * CR;    // pairs of this tile
                     KBP(0);
                     mbar_wait(&mb_full[slot], (uint32_t)(g >> 2) & 1u);
                     KBP(2);                             // 2: waiting for the tile's bytes
                     const uint4* rv = reinterpret_cast<const uint4*>(f.raw0 + slot * f.raw_stride);
-                    uint16_t* dst = stream + tc;
+                    uint16_t* dst = stream + (tr0 - gr0) * CR;
                     // all six loads first (index clamped, so always inside the tile): six LDS.128 in flight per thread
-                    uint4 v[kTileChunks / kHalf];
+                    uint4 v[kPairs];
 #pragma unroll
-                    for (int u = 0; u < kTileChunks / kHalf; ++u) v[u] = rv[min(tid + u * kHalf, nch - 1)];
+                    for (int u = 0; u < kPairs; ++u) v[u] = rv[min(((off_t + rw_u[u]) >> 4) + k_u[u], nch - 1)];
 #pragma unroll
-                    for (int u = 0; u < kTileChunks / kHalf; ++u) {
-                        const int c = tid + u * kHalf;
-                        const uint32_t bits = bits16_of_01(v[u], other);     // (a clamped duplicate only repeats a chunk of the mask)
-                        if (c < nch) dst[c] = (uint16_t)bits;
+                    for (int u = 0; u < kPairs; ++u) {
+                        const int pp = tid + u * kHalf;
+                        const uint32_t bits = bits16_of_01(v[u], other);     // (chunks past the row's end: cleared by the reader)
+                        if (pp < np) dst[pp] = (uint16_t)bits;
                     }
-                    if (tc + kTileChunks >= nG && tid < 4) dst[nch + tid] = 0;   // the funnel reads one word past the last chunk
                     mbar_arrive(&mb_free[slot]);
                 }
                 if (gr1 == H) {                         // last group of the mask: publish whether any byte was above 1
@@ -1355,8 +1371,6 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
     const int et = tid - kHalf, lane = et & 31, wid = et >> 5;
     int* list2 = lists + 4;
     int* list3 = lists + 4 + n_masks;
-    const int nb_last = W - 32 * (Wp - 1);              // valid bits of a row's last word
-    const uint32_t last_mask = nb_last < 32 ? ((1u << nb_last) - 1u) : 0xffffffffu;
     int gs = 0, mi = 0;
     KBP_DECL
     for (int64_t m = blockIdx.x; m < n_masks; m += gridDim.x, ++mi) {
@@ -1364,49 +1378,60 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
         const int off_m = (int)((base + (uintptr_t)(m * HW)) & 15);
         for (int gr0 = 0; gr0 < H; gr0 += kGroupRows, ++gs) {
             const int gr1 = min(H, gr0 + kGroupRows);
-            const int off0 = (off_m + gr0 * W) & 15;    // position of pixel (gr0, 0) in the stream
             const int b = gs & 1;
             KBP(3);
             mbar_wait(&sb_full[b], (uint32_t)(gs >> 1) & 1u);
             KBP(4);                                     // 4: waiting for the pack half
             const uint32_t* sb32 = reinterpret_cast<const uint32_t*>(f.sb0 + b * f.sb_stride);
-            // ---- runs of the group's rows, TWO THREADS PER ROW, each walking half of the row's words (a warp per row spends 32
-            // issue slots on what is mostly empty or solid words).  Thread order = raster order of the segments, so one scan
-            // of the packed (starts, ends) counts places every segment in the run arrays: the k-th start of a row pairs
-            // with its k-th end wherever the segment boundary falls ----
+            // ---- runs of the group's rows, TWO THREADS PER ROW, each holding its half of the row's slot (QH quads) in
+            // registers.  Thread order = raster order of the halves, so one scan of the packed (starts, ends) counts places
+            // every half in the run arrays: the k-th start of a row pairs with its k-th end wherever the halves meet ----
             const int rloc = et >> 1, half = et & 1;
             const int r = gr0 + rloc;
             const bool live = r < gr1;
-            const int Wh = (Wp + 1) >> 1;
-            const int w0 = half ? Wh : 0, w1 = half ? Wp : Wh;
-            const int o0 = off0 + rloc * W;             // bit offset of this thread's row in the stream
-            auto sbit = [&](int pos) { return (sb32[pos >> 5] >> (pos & 31)) & 1u; };
-            int ns = 0, ne = 0;
-            uint32_t carry_in = 0u;
-            // most segments are empty (rows above / below the object, words beside it): OR the aligned words that cover the
-            // segment first -- independent loads, no funnel shifts -- and walk it only when something is set.  The edge words
-            // also hold bits of the neighbouring rows: a false "non-empty" only costs the walk.
-            bool any = false;
-            if (live && w0 < w1) {
-                const int a0 = (o0 + 32 * w0) >> 5, a1 = (o0 + 32 * w1 - 1) >> 5;
-                uint32_t acc = 0u;
-                for (int a = a0; a <= a1; ++a) acc |= sb32[a];
-                any = acc != 0u;
-            }
-            if (any) {
-                carry_in = w0 ? sbit(o0 + 32 * w0 - 1) : 0u;
-                uint32_t carry = carry_in, first = 0u, mw = 0u;
-                int o = o0 + 32 * w0;
-                for (int w = w0; w < w1; ++w, o += 32) {
-                    mw = __funnelshift_r(sb32[o >> 5], sb32[(o >> 5) + 1], o & 31);
-                    if (w == Wp - 1) mw &= last_mask;
-                    if (w == w0) first = mw & 1u;
-                    ns += __popc(mw & ~((mw << 1) | carry));
-                    carry = mw >> 31;
+            const int dl = (off_m + r * W) & 15;        // the row's pixels are bits [dl, dl + W) of its slot
+            const int lim = dl + W;
+            const uint32_t* slot32 = sb32 + rloc * (2 * WH);
+            uint32_t mw[WH];
+            uint32_t acc = 0u;
+            if (live) {
+                const uint4* sq = reinterpret_cast<const uint4*>(slot32) + half * QH;
+#pragma unroll
+                for (int q = 0; q < QH; ++q) {
+                    const uint4 v4 = sq[q];
+                    mw[4 * q] = v4.x; mw[4 * q + 1] = v4.y; mw[4 * q + 2] = v4.z; mw[4 * q + 3] = v4.w;
+                    acc |= (v4.x | v4.y) | (v4.z | v4.w);
                 }
-                // ends inside the segment = starts inside it + a run open at its left edge - a run open at its right edge
-                const uint32_t after = (w1 < Wp) ? sbit(o0 + 32 * w1) : 0u;     // (bit 0 of a row's last word is always a pixel)
-                ne = ns + (int)(carry_in & first) - (int)(carry & after);
+            }
+            // most halves are empty (rows above / below the object, words beside it); bits of the neighbouring rows in the
+            // edge words can only make a half look occupied, which costs the walk and nothing else
+            int ns = 0, ne = 0;
+            uint32_t carry_in = 0u, after = 0u;
+            if (acc != 0u) {
+                // clear what is not this row: bits below dl in the slot's first word, bits from lim on (a real branch per
+                // quad: only the last quad(s) of the second half can reach lim)
+                if (half == 0) mw[0] &= 0xffffffffu << dl;
+#pragma unroll
+                for (int q = 0; q < QH; ++q) {
+                    const int w0 = half * WH + 4 * q;   // slot word of the quad's first word
+                    if (32 * w0 + 128 > lim) {
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const int rem = lim - 32 * (w0 + k);
+                            if (rem < 32) mw[4 * q + k] = rem <= 0 ? 0u : (mw[4 * q + k] & ((1u << rem) - 1u));
+                        }
+                    }
+                }
+                if (half) carry_in = (32 * WH - 1 < lim) ? slot32[WH - 1] >> 31 : 0u;     // (bit 32 WH - 1 >= 127 > dl)
+                uint32_t carry = carry_in;
+#pragma unroll
+                for (int k = 0; k < WH; ++k) {
+                    ns += __popc(mw[k] & ~((mw[k] << 1) | carry));
+                    carry = mw[k] >> 31;
+                }
+                // ends inside the half = starts inside it + a run open at its left edge - a run open at its right edge
+                if (carry && half == 0 && 32 * WH < lim) after = slot32[WH] & 1u;
+                ne = ns + (int)(carry_in & mw[0] & 1u) - (int)(carry & after);
             }
             const int pk = ns | (ne << 16);
             int inc = pk;
@@ -1425,23 +1450,18 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
             if (live) {
                 if (half == 0) f.rs.row_off[r] = Rbase + (excl & 0xffff);
                 if (pk) {
-                    int ks = Rbase + (excl & 0xffff), ke = Rbase + (excl >> 16), o = o0 + 32 * w0;
+                    int ks = Rbase + (excl & 0xffff), ke = Rbase + (excl >> 16);
                     uint32_t carry = carry_in;
-                    uint32_t mw = __funnelshift_r(sb32[o >> 5], sb32[(o >> 5) + 1], o & 31);
-                    if (w0 == Wp - 1) mw &= last_mask;
-                    for (int w = w0; w < w1; ++w) {
-                        o += 32;
-                        uint32_t nx = 0u;
-                        if (w + 1 < Wp) {
-                            nx = __funnelshift_r(sb32[o >> 5], sb32[(o >> 5) + 1], o & 31);
-                            if (w + 2 == Wp) nx &= last_mask;
-                        }
-                        uint32_t st = mw & ~((mw << 1) | carry), en = mw & ~((mw >> 1) | (nx << 31));
+                    const int xb = 32 * half * WH - dl - 1;                  // x of bit i of word k = xb + 32 k + ffs
+#pragma unroll
+                    for (int k = 0; k < WH; ++k) {
+                        const uint32_t w = mw[k], nx = k + 1 < WH ? mw[k + 1 < WH ? k + 1 : k] : after;
+                        uint32_t st = w & ~((w << 1) | carry), en = w & ~((w >> 1) | (nx << 31));
                         for (; st; st &= st - 1, ++ks)
-                            if (ks < kRunCap) { f.rs.xs[ks] = (uint16_t)(32 * w + __ffs(st) - 1); f.rs.row[ks] = (uint16_t)r; }
+                            if (ks < kRunCap) { f.rs.xs[ks] = (uint16_t)(xb + 32 * k + __ffs(st)); f.rs.row[ks] = (uint16_t)r; }
                         for (; en; en &= en - 1, ++ke)
-                            if (ke < kRunCap) f.rs.xe[ke] = (uint16_t)(32 * w + __ffs(en) - 1);
-                        carry = mw >> 31; mw = nx;
+                            if (ke < kRunCap) f.rs.xe[ke] = (uint16_t)(xb + 32 * k + __ffs(en));
+                        carry = w >> 31;
                     }
                 }
             }
@@ -1638,7 +1658,7 @@ extern "C" int64_t tdod_mask_rect_workspace_bytes(int64_t n_masks, int H, int W)
 // shape of the fused path for an H x W mask: shared memory of a front CTA and CTAs per SM (0: does not fit -- wider than
 // 1024 px, or the row tables + run arrays + ring exceed an SM)
 static int fused_plan(int H, int W, size_t* smem) {
-    if (getenv("TDOD_KB_NO_FUSED") != nullptr || W > 1024) return 0;
+    if (getenv("TDOD_KB_NO_FUSED") != nullptr || W > 1024 || W < 32) return 0;
     if ((int64_t)H * W + 64 > 0x7fffffff) return 0;       // positions inside a mask are 32-bit
     *smem = front_layout(H, W, nullptr, nullptr);
     if (*smem <= 113u * 1024) return 2;
@@ -1676,7 +1696,7 @@ int kb_plan(int64_t n_masks, int H, int W, void* workspace, int64_t workspace_by
 }
 }  // namespace
 
-static tdod_smem_cache g_sm_front, g_sm_tail, g_sm_r0, g_sm_r1, g_sm_r2, g_sm_pack;
+static tdod_smem_cache g_sm_front[5], g_sm_tail, g_sm_r0, g_sm_r1, g_sm_r2, g_sm_pack;
 
 extern "C" int tdod_mask_pack(const uint8_t* masks, int64_t n_masks, int H, int W, void* workspace, int64_t workspace_bytes,
                               void* stream) {
@@ -1797,7 +1817,10 @@ extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int 
     const size_t tsmem = per_warp * kTailWarps;
     if (tsmem > 227 * 1024) return tdod_fail(TDOD_ERANGE, "tdod_mask_rect: image too tall for the tail kernel");
     cudaError_t e;
-    if ((e = tdod_smem_opt_in((const void*)kb_front_kernel, fsmem, &g_sm_front)) != cudaSuccess) return (int)e;
+    typedef void (*front_fn)(const uint8_t*, int64_t, int, int, unsigned char*, uint8_t*, int*);
+    static const front_fn fronts[5] = {kb_front_kernel<1>, kb_front_kernel<2>, kb_front_kernel<3>, kb_front_kernel<4>, kb_front_kernel<5>};
+    const int qh = front_slot_hw(W) / 16;               // 1..5 for 32 <= W <= 1024
+    if ((e = tdod_smem_opt_in((const void*)fronts[qh - 1], fsmem, &g_sm_front[qh - 1])) != cudaSuccess) return (int)e;
     if ((e = tdod_smem_opt_in((const void*)kb_tail_kernel, tsmem, &g_sm_tail)) != cudaSuccess) return (int)e;
     if ((e = tdod_smem_opt_in((const void*)rect_kernel<true, false>, p.smem2, &g_sm_r1)) != cudaSuccess) return (int)e;
     if ((e = tdod_smem_opt_in((const void*)rect_kernel<true, true>, p.smem2, &g_sm_r2)) != cudaSuccess) return (int)e;
@@ -1805,8 +1828,8 @@ extern "C" int tdod_mask_rect(const uint8_t* masks, int64_t n_masks, int H, int 
     if ((e = cudaMemsetAsync(p.rowrange, 0x7f, (size_t)n_masks * 8, st)) != cudaSuccess) return (int)e;
     if ((e = cudaMemsetAsync(p.lists, 0, 16, st)) != cudaSuccess) return (int)e;
     const int64_t cap = (int64_t)148 * per_sm;
-    kb_front_kernel<<<(unsigned)(n_masks < cap ? n_masks : cap), kHalf + kExT, fsmem, st>>>(masks, n_masks, H, W, cand, out_has_rect,
-                                                                                 p.lists);
+    fronts[qh - 1]<<<(unsigned)(n_masks < cap ? n_masks : cap), kHalf + kExT, fsmem, st>>>(masks, n_masks, H, W, cand, out_has_rect,
+                                                                                p.lists);
     TDOD_CHECK_LAUNCH();
     kb_tail_kernel<<<(unsigned)((n_masks + kTailWarps - 1) / kTailWarps), 32 * kTailWarps, tsmem, st>>>(cand, n_masks, H, out_rects,
                                                                                                       out_has_rect, p.lists, per_warp);

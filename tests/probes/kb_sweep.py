@@ -61,7 +61,7 @@ def family(k, rs, H, W):
 
 
 tot = bad = 0
-for (H, W) in ((200, 240), (530, 730), (480, 640), (97, 1031)):
+for (H, W) in ((200, 240), (530, 730), (480, 640), (97, 1031), (120, 400), (90, 900), (70, 1024)):
     rs = np.random.RandomState(H + W)
     ms = [family(t % 7, rs, H, W) for t in range(n_per)]
     rects, has = api.mask_rect(torch.from_numpy(np.stack(ms)).to(dev))

@@ -460,3 +460,55 @@ def test_packed_masks_give_the_same_rectangles_and_winners():
     torch.cuda.synchronize()
     assert torch.equal(out[:, 20].int(), s.best_idx.cpu())
     assert p.h2d_bytes < 0.4 * b.input_bytes()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("H,W", [(64, 33), (130, 240), (120, 400), (260, 730), (90, 900), (70, 1024)])
+def test_mask_rect_row_slot_widths_and_base_offsets(H, W):
+    """The fused K-B front kernel keeps every row in its own 16-byte-aligned slot of 1..5 quads per half row (one template
+    instance per width class) and handles any byte offset of the mask base (rows then start at any bit 0..15 of their
+    slot).  Each width class, with the masks at an odd offset inside a larger byte buffer, against the two-kernel path
+    (bit-equal rectangles and state bytes) and against cv2 through the oracle."""
+    from scipy import ndimage as ndi
+    d = torch.device("cuda:0")
+    rs = np.random.RandomState(H * 7 + W)
+    yy, xx = np.mgrid[0:H, 0:W]
+    ms = []
+    for t in range(40):
+        k = t % 5
+        if k == 0:
+            m = ndi.gaussian_filter(rs.randn(H, W), rs.uniform(1.5, 6)) > rs.uniform(-0.05, 0.1)
+        elif k == 1:
+            cx, cy = rs.uniform(0.2, 0.8) * W, rs.uniform(0.2, 0.8) * H
+            m = ((xx - cx) / (rs.uniform(0.1, 0.5) * W)) ** 2 + ((yy - cy) / (rs.uniform(0.1, 0.5) * H)) ** 2 <= 1
+        elif k == 2:
+            m = np.zeros((H, W), bool)
+            m[:, 0] = True; m[:, W - 1] = rs.rand(H) < 0.7; m[rs.randint(0, H), :] = True     # first / last column, a full row
+        elif k == 3:
+            m = rs.rand(H, W) < rs.choice([0.02, 0.4])                                     # speckle
+        else:
+            m = np.zeros((H, W), bool)
+            m[rs.randint(0, H):, rs.randint(0, W):] = True                                 # block touching the last row / column
+        ms.append(m)
+    ms.append(np.zeros((H, W), bool))
+    ms.append(np.ones((H, W), bool))
+    stack = torch.from_numpy(np.stack(ms))
+    n = stack.numel()
+    for off in (0, 5, 11):
+        buf = torch.zeros(n + 64, dtype=torch.bool, device=d)
+        view = buf[off:off + n].view(len(ms), H, W)
+        view.copy_(stack.to(d))
+        assert view.data_ptr() % 16 == (buf.data_ptr() + off) % 16
+        r1, h1 = api.mask_rect(view)
+        r0, h0 = api.mask_rect(view, two_kernel=True)
+        assert torch.equal(h0, h1), (off, h0.tolist(), h1.tolist())
+        ok = h0 == 1
+        assert torch.equal(r0[ok].view(torch.int32), r1[ok].view(torch.int32)), off
+    rects, has = r1.cpu().numpy(), h1.cpu().numpy()
+    assert has[-2] == 0 and has[-1] == 1
+    for t, m in enumerate(ms):
+        ref = O.mask_rect(m.astype(np.uint8))
+        assert (ref is None) == (has[t] == 0), t
+        if ref is not None:
+            dev_px = max(min(float(np.hypot(*(p - q))) for q in ref) for p in rects[t])
+            assert dev_px < 1e-3, (t, rects[t], ref)
