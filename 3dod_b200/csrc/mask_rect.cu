@@ -1004,6 +1004,53 @@ __device__ int select_component(const RunSet& rs, int R, bool bounds_mode, int* 
     return best;
 }
 
+// Front kernel: select_component (bounds mode) and component_rows in ONE sweep over the runs and two barriers.  The caller has
+// already set *key = 0, scratch[24] = 0, counts[2] = INT_MAX, counts[3] = -1 and rowL / rowR to their sentinels, with a
+// barrier of the group since (the labelling's).  Every run of the winner updates the per-row extremes; every other root
+// walks its component once for the hole-filled upper bound (see select_component).
+template <typename TG>
+__device__ int pick_component_rows(const RunSet& rs, int R, int* rowL, int* rowR, int* scratch, bool* ambiguous) {
+    unsigned long long* key = reinterpret_cast<unsigned long long*>(scratch + 20);
+    int* counts = scratch + 32;
+    for (int i = TG::tid(); i < R; i += TG::size())
+        if (rs.parent[i] == i) atomicMax(key, ((unsigned long long)(unsigned)rs.area2[i] << 32) | (unsigned)i);
+    TG::sync();
+    const int best = (int)(*key & 0xffffffffu);
+    const int best_a2 = (int)(*key >> 32);
+    for (int i0 = 0; i0 < R; i0 += TG::size()) {
+        const int i = i0 + TG::tid();
+        int rlo = 0x7fffffff, rhi = -1;
+        if (i < R) {
+            const int par = rs.parent[i];
+            if (par == best) {
+                const int r = rs.row[i];
+                atomicMin(&rowL[r], (int)rs.xs[i]); atomicMax(&rowR[r], (int)rs.xe[i]);
+                rlo = rhi = r;
+            } else if (par == i) {
+                int pl = 0, pr = -1, cl = rs.xs[i], cr = rs.xe[i], crow = rs.row[i];
+                bool have_prev = false;
+                long long ub2 = 0;
+                for (int j = i + 1; j <= R; ++j) {
+                    const bool mine = j < R && rs.parent[j] == i;
+                    if (j < R && !mine) {
+                        if ((int)rs.row[j] > crow + 1) j = R; else continue;
+                    }
+                    if (mine && (int)rs.row[j] == crow) { cl = min(cl, (int)rs.xs[j]); cr = max(cr, (int)rs.xe[j]); continue; }
+                    if (have_prev && pl <= cr && pr >= cl) ub2 += 2 * (min(cr, pr) - max(cl, pl)) + (cl != pl) + (cr != pr);
+                    pl = cl; pr = cr; have_prev = true;
+                    if (mine) { cl = rs.xs[j]; cr = rs.xe[j]; crow = rs.row[j]; }
+                }
+                if (ub2 > (long long)best_a2 || (ub2 == (long long)best_a2 && ub2 > 0)) atomicOr(&scratch[24], 1);
+            }
+        }
+        rlo = __reduce_min_sync(0xffffffffu, rlo); rhi = __reduce_max_sync(0xffffffffu, rhi);   // one pair of atomics per warp
+        if ((threadIdx.x & 31) == 0 && rhi >= 0) { atomicMin(&counts[2], rlo); atomicMax(&counts[3], rhi); }
+    }
+    TG::sync();
+    *ambiguous = scratch[24] != 0;
+    return best;
+}
+
 // ---- exact hole filling: outside = 4-connected flood of the background from the (virtual) image border ----
 // Bit-parallel, iterated to convergence.  `out` starts from everything visible from the border along a row or a
 // column (exact already for hole-free convex-ish blobs); every sweep lets the frontier run through a whole word
@@ -1173,7 +1220,14 @@ __global__ void __launch_bounds__(kT, kExact ? 1 : TDOD_KB_MINB) rect_kernel(con
 // Masks the front kernel cannot decide (hole filling could change the winner; more runs than shared memory holds) go
 // to the work lists; a list-driven pack writes only THEIR bitmaps and the exact passes (rect_kernel<true, *>) finish them.
 // ------------------------------------------------------------------------------------------------------------
-constexpr int kRing = 4;                // TMA ring slots of a front CTA (loads of three tiles in flight behind the one being packed)
+#ifndef TDOD_KB_RING
+#define TDOD_KB_RING 3
+#endif
+#ifndef TDOD_KB_STREAMS
+#define TDOD_KB_STREAMS 3
+#endif
+constexpr int kRing = TDOD_KB_RING;     // TMA ring slots of a front CTA (loads of kRing - 1 tiles in flight behind the one being packed)
+constexpr int kSB = TDOD_KB_STREAMS;    // bit-stream buffers (row groups the pack half may run ahead of the extract half)
 constexpr int kTailHullCap = 192;       // hull vertices one tail warp holds (beyond: the overflow pass)
 constexpr int kTailChainCap = 256;      // sieve survivors per chain it holds (beyond: the overflow pass)
 constexpr int kTailWarps = 4;
@@ -1228,6 +1282,7 @@ __host__ __device__ inline size_t front_layout(int H, int W, FrontSmem* f, unsig
     for (int k = 1; k < kRing; ++k) take((size_t)kTileChunks * 16);
     const size_t sbytes = (size_t)kGroupRows * front_slot_hw(W) * 2;        // one 16-byte-aligned slot per row
     const size_t o_sb0 = take(sbytes), o_sb1 = take(sbytes);
+    for (int k = 2; k < kSB; ++k) take(sbytes);
     const size_t o_xs = take(kRunCap * 2), o_xe = take(kRunCap * 2), o_row = take(kRunCap * 2);
     const size_t o_par = take(kRunCap * 4), o_area = take(kRunCap * 4);
     const size_t o_roff = take((size_t)(H + 1) * 4), o_rl = take((size_t)H * 4), o_rr = take((size_t)H * 4);
@@ -1267,10 +1322,10 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
     extern __shared__ __align__(128) unsigned char fs_raw[];
     __shared__ __align__(8) uint64_t mb_full[kRing];   // the tile's bytes have landed (TMA transaction count)
     __shared__ __align__(8) uint64_t mb_free[kRing];   // all pack threads have turned the slot's bytes into bits
-    __shared__ __align__(8) uint64_t sb_full[2];       // the group's bit stream is complete (pack threads arrive)
-    __shared__ __align__(8) uint64_t sb_free[2];       // its runs have been extracted (extract threads arrive)
+    __shared__ __align__(8) uint64_t sb_full[kSB];       // the group's bit stream is complete (pack threads arrive)
+    __shared__ __align__(8) uint64_t sb_free[kSB];       // its runs have been extracted (extract threads arrive)
     __shared__ int s_warp[kExT / 32];
-    __shared__ uint32_t s_other[4];                     // per mask (index m' & 3): some byte of the mask is above 1
+    __shared__ uint32_t s_other[8];                     // per mask (index m' & 7): some byte of the mask is above 1
     FrontSmem f;
     front_layout(H, W, &f, fs_raw);
     const int tid = threadIdx.x;
@@ -1279,8 +1334,8 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
     const int TR = front_tile_rows(W);                  // rows per tile
     if (tid == 0) {
         for (int k = 0; k < kRing; ++k) { mbar_init(&mb_full[k], 1); mbar_init(&mb_free[k], kHalf); }
-        for (int k = 0; k < 2; ++k) { mbar_init(&sb_full[k], kHalf); mbar_init(&sb_free[k], kExT); }
-        for (int k = 0; k < 4; ++k) s_other[k] = 0u;
+        for (int k = 0; k < kSB; ++k) { mbar_init(&sb_full[k], kHalf); mbar_init(&sb_free[k], kExT); }
+        for (int k = 0; k < 8; ++k) s_other[k] = 0u;
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
@@ -1297,9 +1352,9 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
             const int off_m = (int)(a & 15);
             const int r1 = min(min(H, (pr0 / kGroupRows + 1) * kGroupRows), pr0 + TR);
             const int c0 = (off_m + pr0 * W) >> 4, c1 = (off_m + r1 * W + 15) >> 4;
-            const int slot = issued & (kRing - 1);
+            const int slot = issued % kRing;
             // refilling a slot: its previous tile (number issued - kRing) must have been packed by every pack thread
-            if (issued >= kRing) mbar_wait(&mb_free[slot], (uint32_t)((issued >> 2) - 1) & 1u);
+            if (issued >= kRing) mbar_wait(&mb_free[slot], (uint32_t)(issued / kRing - 1) & 1u);
             mbar_expect_tx(&mb_full[slot], (uint32_t)(c1 - c0) * 16u);
             bulk_load(f.raw0 + slot * f.raw_stride, reinterpret_cast<const unsigned char*>(a - off_m) + ((size_t)c0 << 4),
                       (uint32_t)(c1 - c0) * 16u, &mb_full[slot]);
@@ -1325,21 +1380,21 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
             const int off_m = (int)((base + (uintptr_t)(m * HW)) & 15);
             for (int gr0 = 0; gr0 < H; gr0 += kGroupRows, ++gs) {
                 const int gr1 = min(H, gr0 + kGroupRows);
-                const int b = gs & 1;
-                // the buffer's previous group (two back) must have been read by the extract half
+                const int b = gs % kSB;
+                // the buffer's previous group (kSB back) must have been read by the extract half
                 KBP(0);
-                if (gs >= 2) mbar_wait(&sb_free[b], (uint32_t)((gs >> 1) - 1) & 1u);
+                if (gs >= kSB) mbar_wait(&sb_free[b], (uint32_t)(gs / kSB - 1) & 1u);
                 KBP(1);                                 // 1: waiting for the extract half to free a stream buffer
                 uint16_t* stream = reinterpret_cast<uint16_t*>(f.sb0 + b * f.sb_stride);
                 for (int tr0 = gr0; tr0 < gr1; tr0 += TR, ++g) {
                     const int tr1 = min(gr1, tr0 + TR);
-                    const int slot = g & (kRing - 1);
+                    const int slot = g % kRing;
                     if (tid == 0) issue_next();         // tile g + kRing - 1
                     const int t0 = off_m + tr0 * W;
                     const int nch = ((off_m + tr1 * W + 15) >> 4) - (t0 >> 4), off_t = t0 & 15;
                     const int np = (tr1 - tr0) * CR;    // pairs of this tile
                     KBP(0);
-                    mbar_wait(&mb_full[slot], (uint32_t)(g >> 2) & 1u);
+                    mbar_wait(&mb_full[slot], (uint32_t)(g / kRing) & 1u);
                     KBP(2);                             // 2: waiting for the tile's bytes
                     const uint4* rv = reinterpret_cast<const uint4*>(f.raw0 + slot * f.raw_stride);
                     uint16_t* dst = stream + (tr0 - gr0) * CR;
@@ -1357,7 +1412,7 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
                 }
                 if (gr1 == H) {                         // last group of the mask: publish whether any byte was above 1
                     other &= 0xFEFEFEFEu;
-                    if (__any_sync(0xffffffffu, other != 0u) && (tid & 31) == 0) atomicOr(&s_other[mi & 3], 1u);
+                    if (__any_sync(0xffffffffu, other != 0u) && (tid & 31) == 0) atomicOr(&s_other[mi & 7], 1u);
                 }
                 mbar_arrive(&sb_full[b]);               // (release: the stream and the flag are visible to whoever waits)
             }
@@ -1378,9 +1433,9 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
         const int off_m = (int)((base + (uintptr_t)(m * HW)) & 15);
         for (int gr0 = 0; gr0 < H; gr0 += kGroupRows, ++gs) {
             const int gr1 = min(H, gr0 + kGroupRows);
-            const int b = gs & 1;
+            const int b = gs % kSB;
             KBP(3);
-            mbar_wait(&sb_full[b], (uint32_t)(gs >> 1) & 1u);
+            mbar_wait(&sb_full[b], (uint32_t)(gs / kSB) & 1u);
             KBP(4);                                     // 4: waiting for the pack half
             const uint32_t* sb32 = reinterpret_cast<const uint32_t*>(f.sb0 + b * f.sb_stride);
             // ---- runs of the group's rows, TWO THREADS PER ROW, each holding its half of the row's slot (QH quads) in
@@ -1471,10 +1526,10 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
             KBP(5);                                     // 5: run extraction
         }
         const int R = Rbase;
-        const bool not01 = s_other[mi & 3] != 0u;       // (visible: ordered by the wait on the last group's sb_full)
+        const bool not01 = s_other[mi & 7] != 0u;       // (visible: ordered by the wait on the last group's sb_full)
         if (et == 0) f.rs.row_off[H] = R;
         ExGrp::sync();
-        if (et == 0) s_other[mi & 3] = 0u;              // reused four masks on; the pack half is at most two groups ahead
+        if (et == 0) s_other[mi & 7] = 0u;              // reused eight masks on; the pack half is at most kSB groups ahead
         if (not01 || R == 0 || R > kRunCap) {
             if (et == 0) {
                 if (not01 || R > kRunCap) { out_has[m] = 3; list3[atomicAdd(&lists[1], 1)] = (int)m; }   // general / overflow pass
@@ -1484,17 +1539,22 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
             continue;
         }
         KBP(3);
+        // state of the winner search: set here, published by the labelling's barriers; the previous mask's readers of
+        // rowL / rowR / scratch are at least one extraction barrier behind
+        if (et == 0) {
+            *reinterpret_cast<unsigned long long*>(f.scratch + 20) = 0ull;
+            f.scratch[24] = 0; f.scratch[32 + 2] = 0x7fffffff; f.scratch[32 + 3] = -1;
+        }
+        for (int rr = et; rr < H; rr += kExT) { f.rowL[rr] = 0x7fffffff; f.rowR[rr] = -1; }
         label_from_runs<ExGrp>(f.rs, R);
         KBP(6);                                         // 6: labelling
         bool ambiguous = false;
-        const int root = select_component<ExGrp>(f.rs, R, true, f.scratch, &ambiguous);
-        KBP(7);                                         // 7: winner + rival bounds
+        pick_component_rows<ExGrp>(f.rs, R, f.rowL, f.rowR, f.scratch, &ambiguous);
+        KBP(7);                                         // 7: winner, rival bounds, per-row extremes
         if (ambiguous) {                                // hole filling could change the winner: the exact pass decides
             if (et == 0) { out_has[m] = 2; list2[atomicAdd(&lists[0], 1)] = (int)m; }
-            ExGrp::sync();
             continue;
         }
-        component_rows<ExGrp>(f.rs, R, root, H, f.rowL, f.rowR, f.scratch + 32);
         const int rmin = f.scratch[32 + 2], rmax = f.scratch[32 + 3];
         unsigned char* rec = cand + (size_t)m * cand_stride(H);
         int16_t* lr = reinterpret_cast<int16_t*>(rec + 8);
@@ -1503,8 +1563,7 @@ __global__ void __launch_bounds__(kHalf + kExT, 2) kb_front_kernel(const uint8_t
             lr[2 * rr] = (int16_t)f.rowL[rmin + rr]; lr[2 * rr + 1] = (int16_t)f.rowR[rmin + rr];
         }
         if (et == 0) { reinterpret_cast<int*>(rec)[0] = rmin; reinterpret_cast<int*>(rec)[1] = rmax; out_has[m] = kPending; }
-        ExGrp::sync();
-        KBP(3);                                         // 3: labels, winner, extremes
+        KBP(3);                                         // 3: the record
     }
     KBP_FLUSH(8, et == 0);
 }

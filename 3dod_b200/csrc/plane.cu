@@ -262,14 +262,18 @@ __global__ void __launch_bounds__(256) count_kernel(const T* __restrict__ pts, c
 // Layout: a CTA owns one tile of <= kTilePts points of one frame (fp32 copies in shared memory, each value
 // duplicated so that it feeds both halves of a packed f32x2 FMA) and ALL hypotheses of the frame, four per thread in
 // registers.  The inner loop broadcasts one point to the CTA and every thread advances its four hypotheses:
-//   s   = a x + b y + c z + k                      (FFMA2: two hypotheses per instruction)
-//   t   = sat((bound^2 - s^2) * G + 1/2)           1 = certainly in, 0 = certainly out, between = inside the band
-//   S  += t ; S2 += t*t                            S - S2 > 0 only if some t was fractional
+//   s'  = (a x + b y + c z + k) / 2e               (FFMA2: two hypotheses per instruction; the plane is pre-scaled)
+//   t   = sat((bound + e) / 2e - |s'|)             one FADD.SAT: 1 = certainly in, 0 = certainly out, between = in the band
+//   S  += t                                        (packed add)
+//   mn  = min(mn, bits(t) - 1)  (unsigned)         one VIADDMNMX on the ALU pipe: below 0x3f7fffff iff some t was fractional
+// The fma pipe issues one warp instruction every other cycle and was the limiter (three packed FMAs, a packed square, two
+// FFMA.SAT, a packed add and a packed FMA per pair of hypotheses); the band test now runs on the otherwise idle ALU pipe
+// and the ramp is linear in |s|, which takes the fma pipe from eight to six instructions per pair and point.
 // The band: the fp32 value differs from the separately rounded fp64 / fp32 value of the reference by at most
-// E = 5e-7 (max|x|+|y|+|z| + max|k| + bound) (inputs rounded once, three fused operations, |a|,|b|,|c| <= 1);
-// with e = 2E and 1/(2G) = 2 bound e - e^2, |s| <= bound - e gives t = 1, |s| >= bound + e gives t = 0, and any t
-// outside [1/4, 3/4] already decides the point; a tile whose S - S2 stays below 0.05 therefore has no undecided point
-// and rint(S) is its count (sums of <= 1024 terms).  Tiles that fail the test are recounted exactly.
+// E = 5e-7 (max|x|+|y|+|z| + max|k| + bound) (inputs and the scaled plane rounded once, three fused operations,
+// |a|,|b|,|c| <= 1, two roundings in the ramp's constant); with e = 2E, |s| <= bound - e gives t = 1 and |s| >= bound + e
+// gives t = 0, both exactly (bit patterns 0x3f800000 and 0), so a tile without a fractional t has no undecided point and
+// rint(S) is its count (sums of <= 1024 ones are exact).  Tiles with one are recounted exactly.
 // ------------------------------------------------------------------------------------------------
 constexpr int kTilePts = 1024;     // points per CTA tile
 constexpr int kFiltT = 256;        // threads
@@ -346,8 +350,11 @@ __global__ void __launch_bounds__(kFiltT) count_filter_kernel(const T* __restric
     for (int h0 = 0; h0 < iters; h0 += kFiltT * kHypT) {
         if (tid == 0) s_nlist = 0;
         // ---- this thread's hypotheses: h0 + tid + j * kFiltT ----
-        float2 a2[kHypT / 2], b2[kHypT / 2], c2[kHypT / 2], k2[kHypT / 2], S[kHypT / 2], S2[kHypT / 2];
-        float nG[kHypT], C[kHypT];
+        float2 a2[kHypT / 2], b2[kHypT / 2], c2[kHypT / 2], k2[kHypT / 2], S[kHypT / 2];
+        float C[kHypT];
+        uint32_t mn[kHypT];                                       // min over the points of bits(t) - 1 (unsigned)
+        const float inv = 0.5f / e;
+        const bool band_ok = (e < CUDART_INF_F) && (e > 1e-20f);
 #pragma unroll
         for (int j = 0; j < kHypT; ++j) {
             const int h = h0 + tid + j * kFiltT;
@@ -356,17 +363,19 @@ __global__ void __launch_bounds__(kFiltT) count_filter_kernel(const T* __restric
                 const PlaneHyp<T> p = hf[h];
                 a = (float)p.a; b = (float)p.b; c = (float)p.c; k = (float)p.k; bd = (float)p.bound;
             }
+            // t = sat((bound + e - |s|) / 2e): the plane is scaled by 1 / 2e once, the ramp is one FADD.SAT per point
+            if (bd < 0.f) { a = b = c = k = 0.f; C[j] = 0.f; }                          // no plane: t = 0 everywhere
+            else if (!band_ok || !(bd == bd)) { a = b = c = k = 0.f; C[j] = 0.5f; }     // no usable band: t = 1/2, recount
+            else { a *= inv; b *= inv; c *= inv; k *= inv; C[j] = (bd + e) * inv; }
             (j & 1 ? a2[j / 2].y : a2[j / 2].x) = a; (j & 1 ? b2[j / 2].y : b2[j / 2].x) = b;
             (j & 1 ? c2[j / 2].y : c2[j / 2].x) = c; (j & 1 ? k2[j / 2].y : k2[j / 2].x) = k;
-            const float D = 2.f * bd * e - e * e;                 // 1 / (2G)
-            if (bd < 0.f) { nG[j] = 0.f; C[j] = 0.f; }            // no plane: t = 0 everywhere
-            else if (!(bd > 2.f * e) || !(D > 0.f) || !(e < CUDART_INF_F)) { nG[j] = 0.f; C[j] = 0.5f; }   // no usable band: recount
-            else { const float G = 0.5f / D; nG[j] = -G; C[j] = fmaf(bd * bd, G, 0.5f); }
+            mn[j] = 0xffffffffu;
         }
 #pragma unroll
-        for (int j = 0; j < kHypT / 2; ++j) { S[j] = make_float2(0.f, 0.f); S2[j] = make_float2(0.f, 0.f); }
+        for (int j = 0; j < kHypT / 2; ++j) S[j] = make_float2(0.f, 0.f);
         __syncthreads();
-        // ---- main loop: broadcast a point, advance four hypotheses ----
+        // ---- main loop: broadcast a point, advance four hypotheses.  Per pair of hypotheses the fma pipe sees three packed
+        // FMAs, two FADD.SAT and one packed add; whether any t was fractional is tracked on the ALU pipe (VIADDMNMX) ----
 #pragma unroll 4
         for (int i = 0; i < np; ++i) {
             const float4 q = s_xy[i];
@@ -377,21 +386,23 @@ __global__ void __launch_bounds__(kFiltT) count_filter_kernel(const T* __restric
                 float2 s = ffma2(c2[j], z, k2[j]);
                 s = ffma2(b2[j], qy, s);
                 s = ffma2(a2[j], qx, s);
-                const float2 w = fmul2(s, s);
                 float2 t;
-                t.x = __saturatef(fmaf(w.x, nG[2 * j], C[2 * j]));
-                t.y = __saturatef(fmaf(w.y, nG[2 * j + 1], C[2 * j + 1]));
+                t.x = __saturatef(C[2 * j] - fabsf(s.x));
+                t.y = __saturatef(C[2 * j + 1] - fabsf(s.y));
                 S[j] = fadd2(S[j], t);
-                S2[j] = ffma2(t, t, S2[j]);
+                mn[2 * j] = __viaddmin_u32(__float_as_uint(t.x), 0xffffffffu, mn[2 * j]);
+                mn[2 * j + 1] = __viaddmin_u32(__float_as_uint(t.y), 0xffffffffu, mn[2 * j + 1]);
             }
         }
-        // ---- decided hypotheses go straight to the counters; the others are queued for the exact recount ----
+        // ---- decided hypotheses go straight to the counters; the others are queued for the exact recount.  t is exactly
+        // 0 or 1 for a decided point (bits 0 / 0x3f800000), so a minimum of bits(t) - 1 below 0x3f7fffff means some point
+        // sat inside the band ----
 #pragma unroll
         for (int j = 0; j < kHypT; ++j) {
             const int h = h0 + tid + j * kFiltT;
-            const float s1 = (j & 1) ? S[j / 2].y : S[j / 2].x, s2 = (j & 1) ? S2[j / 2].y : S2[j / 2].x;
+            const float s1 = (j & 1) ? S[j / 2].y : S[j / 2].x;
             if (h < iters) {
-                if (s1 - s2 > 0.05f) s_list[atomicAdd(&s_nlist, 1)] = h;
+                if (mn[j] < 0x3f7fffffu) s_list[atomicAdd(&s_nlist, 1)] = h;
                 else {
                     const int c = __float2int_rn(s1);
                     if (c) atomicAdd(&counts[(size_t)f * iters + h], c);
