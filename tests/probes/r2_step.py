@@ -1,0 +1,23 @@
+"""Step time of the C2 hot path (pipeline.select, K-A beside K-B) and the stage times on one stream; TDOD_LIB picks the build."""
+import os, sys, numpy as np, torch
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.join(ROOT, "3dod_b200"))
+from tdod import pipeline, synth
+d = torch.device("cuda:0")
+c = synth.CONFIGS["C2"]
+batch, off, _ = synth.make_batch(range(256), c["H"], c["W"], c["n_obj"], d)
+def run(k, overlap, marks=None):
+    for i in range(k):
+        o = pipeline.select(batch, 1000, seed=7, overlap=overlap, marks=None if marks is None else marks[i])
+    return o
+run(3, True); torch.cuda.synchronize()
+res = []
+for rep in range(3):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); o = run(20, True); e1.record(); torch.cuda.synchronize()
+    res.append(e0.elapsed_time(e1) / 20)
+marks = [dict() for _ in range(10)]
+run(10, False, marks); torch.cuda.synchronize()
+st = [float(np.mean([m[a].elapsed_time(m[b]) for m in marks])) for a, b in (("ka0", "ka1"), ("kb0", "kb1"), ("kc0", "kc1"))]
+print("step ms (3 x 20): %s   serial stages K-A %.3f K-B %.3f K-C %.3f   best idx checksum %d"
+      % (" ".join("%.4f" % r for r in res), st[0], st[1], st[2], int(o.best_idx.sum().item())))
