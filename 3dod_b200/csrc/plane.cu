@@ -42,11 +42,15 @@ template <> struct Ar<double> {
 // distributed shared memory, so every CTA knows where its slice starts in the two compacted outputs; pass B reads
 // depth (once) and ground (again, now from L1/L2), back-projects and writes each point at its final position.
 // ------------------------------------------------------------------------------------------------
+#ifndef TDOD_BP_MINB
+#define TDOD_BP_MINB 3
+#endif
 constexpr int kBpCluster = 8;
 constexpr int kBpT = 512;
+constexpr int kBpRegIt = 4;             // strided samples per thread the one-pass variant keeps in registers
 
 template <typename T, int FLAVOUR>
-__global__ void __cluster_dims__(kBpCluster, 1, 1) __launch_bounds__(kBpT)
+__global__ void __cluster_dims__(kBpCluster, 1, 1) __launch_bounds__(kBpT, TDOD_BP_MINB)
     backproject_kernel(const float* __restrict__ depth, const uint8_t* __restrict__ ground, const float* __restrict__ Kall,
                        int H, int W, int stride, int iters, T* __restrict__ plane_pts, T* __restrict__ other_pts,
                        int32_t* __restrict__ counts) {
@@ -67,6 +71,91 @@ __global__ void __cluster_dims__(kBpCluster, 1, 1) __launch_bounds__(kBpT)
     const uint8_t* gp = ground ? ground + (size_t)f * H * W : nullptr;
     int* c_on = bp_cnt;
     int* c_off = bp_cnt + iters * kW;
+    if (iters <= kBpRegIt) {
+        // ---- frames of up to kBpRegIt * 4096 samples (every BASELINE shape but 1920 x 1080): ONE pass.  All ground loads
+        // are issued together, then all depth loads; the points wait in registers for the slice offsets, so a CTA pays two
+        // load latencies instead of eight and the second read of the ground map disappears ----
+        T fx, fy, cx, cy;
+        if (FLAVOUR == TDOD_BACKPROJECT_NUMPY) {
+            fx = (T)K[0]; fy = (T)K[4]; cx = (T)K[2]; cy = (T)K[5];
+        } else {
+            fx = (T)floorf(__fdiv_rn(K[0], (float)stride)); fy = (T)floorf(__fdiv_rn(K[4], (float)stride));
+            cx = (T)((double)Ws / 2.0); cy = (T)((double)Hs / 2.0);
+        }
+        const bool want_off = other_pts != nullptr;
+        bool valid[kBpRegIt], on[kBpRegIt];
+        int uu[kBpRegIt], vv[kBpRegIt];
+        uint8_t g[kBpRegIt];
+        float zf[kBpRegIt];
+#pragma unroll
+        for (int it = 0; it < kBpRegIt; ++it) {
+            const int64_t idx = lo + (int64_t)it * kBpT + tid;
+            valid[it] = it < iters && idx < hi;
+            const uint32_t i32 = valid[it] ? (uint32_t)idx : 0u;
+            vv[it] = (int)(i32 / (uint32_t)Ws); uu[it] = (int)(i32 - (uint32_t)vv[it] * (uint32_t)Ws);
+            g[it] = 1;
+            if (valid[it] && gp) g[it] = __ldg(gp + (size_t)(vv[it] * stride) * W + (size_t)(uu[it] * stride));
+        }
+#pragma unroll
+        for (int it = 0; it < kBpRegIt; ++it) {
+            on[it] = valid[it] && g[it] > 0;
+            zf[it] = 0.f;
+            if (valid[it] && (on[it] || want_off)) zf[it] = __ldg(dp + (size_t)(vv[it] * stride) * W + (size_t)(uu[it] * stride));
+        }
+        unsigned m_on[kBpRegIt], m_off[kBpRegIt];
+#pragma unroll
+        for (int it = 0; it < kBpRegIt; ++it) {
+            m_on[it] = __ballot_sync(0xffffffffu, on[it]); m_off[it] = __ballot_sync(0xffffffffu, valid[it] && !on[it]);
+            if (lane == 0 && it < iters) { c_on[it * kW + wid] = __popc(m_on[it]); c_off[it * kW + wid] = __popc(m_off[it]); }
+        }
+        __syncthreads();
+        if (wid < 2) {                               // iters * kW <= 64 entries per list: two rounds of a warp scan
+            int* c = wid == 0 ? c_on : c_off;
+            const int n = iters * kW;
+            int carry = 0;
+            for (int b0 = 0; b0 < n; b0 += 32) {
+                const int v = (b0 + lane < n) ? c[b0 + lane] : 0;
+                int inc = v;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int t = __shfl_up_sync(0xffffffffu, inc, o);
+                    if (lane >= o) inc += t;
+                }
+                if (b0 + lane < n) c[b0 + lane] = carry + inc - v;
+                carry += __shfl_sync(0xffffffffu, inc, 31);
+            }
+            if (lane == 0) s_tot[wid] = carry;
+        }
+        cl.sync();
+        if (tid < 2) {
+            int base = 0;
+            for (int r = 0; r < rank; ++r) base += *cl.map_shared_rank(&s_tot[tid], r);
+            s_base[tid] = base;
+            if (rank == kBpCluster - 1) counts[(size_t)tid * (gridDim.x / kBpCluster) + f] = base + s_tot[tid];   // [2,F]
+        }
+        cl.barrier_arrive();                         // (peers may leave once everybody has read their totals)
+        __syncthreads();
+        T* po = plane_pts + (size_t)f * 3 * P;
+        T* oo = other_pts ? other_pts + (size_t)f * 3 * P : nullptr;
+        const int base_on = s_base[0], base_off = s_base[1];
+        const unsigned lt = (1u << lane) - 1u;
+#pragma unroll
+        for (int it = 0; it < kBpRegIt; ++it) {
+            if (!valid[it] || !(on[it] || want_off)) continue;
+            const T z = (T)zf[it];
+            const T x = Ar<T>::div(Ar<T>::mul(Ar<T>::sub((T)uu[it], cx), z), fx);
+            const T y = Ar<T>::div(Ar<T>::mul(Ar<T>::sub((T)vv[it], cy), z), fy);
+            if (on[it]) {
+                const int p = base_on + c_on[it * kW + wid] + __popc(m_on[it] & lt);
+                po[p] = x; po[P + p] = y; po[2 * P + p] = z;
+            } else {
+                const int p = base_off + c_off[it * kW + wid] + __popc(m_off[it] & lt);
+                oo[p] = x; oo[P + p] = y; oo[2 * P + p] = z;
+            }
+        }
+        cl.barrier_wait();
+        return;
+    }
     // ---- pass A: counts ----
     for (int it = 0; it < iters; ++it) {
         const int64_t idx = lo + (int64_t)it * kBpT + tid;
@@ -430,6 +519,7 @@ __global__ void __launch_bounds__(kFiltT) count_filter_kernel(const T* __restric
             }
             __syncthreads();
         }
+        __syncthreads();                                // (more than 1024 iterations: s_nlist is reset by the next pass)
     }
 }
 

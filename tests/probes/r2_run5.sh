@@ -1,1 +1,1 @@
-for v in a; do echo $v; TDOD_LIB=build_exp/$v/libtdod.so python tests/probes/r2_corun.py 2>&1 | tail -3;  TDOD_LIB=build_exp/$v/libtdod.so python tests/probes/r2_step.py 2>&1 | tail -1; done
+for o in 1 3; do echo over $o; TDOD_CF_OVER=$o python tests/probes/r2_step.py 2>&1 | tail -4; done

@@ -21,3 +21,9 @@ run(10, False, marks); torch.cuda.synchronize()
 st = [float(np.mean([m[a].elapsed_time(m[b]) for m in marks])) for a, b in (("ka0", "ka1"), ("kb0", "kb1"), ("kc0", "kc1"))]
 print("step ms (3 x 20): %s   serial stages K-A %.3f K-B %.3f K-C %.3f   best idx checksum %d"
       % (" ".join("%.4f" % r for r in res), st[0], st[1], st[2], int(o.best_idx.sum().item())))
+# timeline of overlapped steps: stage marks of both streams against the step's first mark
+marks = [dict() for _ in range(6)]
+run(6, True, marks); torch.cuda.synchronize()
+for m in marks[2:5]:
+    o0 = m["kb0"]
+    print("timeline (ms from kb0): " + "  ".join("%s %.3f" % (k, o0.elapsed_time(m[k])) for k in ("ka0", "ka1", "kb0", "kb1", "kc0", "kc1")))
