@@ -343,6 +343,35 @@ def launches_per_select(n_obj, with_plane=True, splits=None):
     return (5 if with_plane else 0) + 6 * splits
 
 
+class GraphedSelect:
+    """`select` on a resident FrameBatch captured ONCE into a CUDA graph (the 11 kernel nodes of a step, K-A forked onto
+    the auxiliary stream inside the capture) and replayed: one driver call per step instead of eleven launches and their
+    Python, so the GPU never waits for the host.  The graph reads the batch's buffers in place (refill them with copy_ to
+    process new frames of the same shape) and writes the same output tensors at every replay.
+
+        gs = GraphedSelect(batch, 1000, seed=7)
+        out = gs.replay()            # out is gs.out: valid after the current stream reaches this point
+    """
+
+    def __init__(self, batch, n_prop, warmup=3, **kw):
+        dev = batch.device
+        self.batch = batch
+        self.launches = launches_per_select(batch.n_obj, with_plane=kw.get("use_ground", True))
+        self.stream = torch.cuda.Stream(dev)
+        self.stream.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(self.stream):
+            for _ in range(max(int(warmup), 1)):     # first calls size the cached workspaces: nothing allocates outside the pool later
+                select(batch, n_prop, **kw)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph, stream=self.stream):
+            self.out = select(batch, n_prop, **kw)
+
+    def replay(self):
+        self.graph.replay()
+        return self.out
+
+
 class Pipeline:
     """Streams pinned-host batches through one GPU: chunks of `chunk_frames` frames, two device slots, a copy
     stream and a compute stream.  The result (winners [N, 15+4+1+1] packed as fp32) is read back per chunk."""

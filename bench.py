@@ -54,6 +54,7 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-configs", action="store_true", help="skip the C1 / C3 / C5 / mode-B / C4 sub-records")
     ap.add_argument("--no-parity-rng", action="store_true", help="skip the reference-order RNG figure")
+    ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of CUDA-graph replays of the step")
     ap.add_argument("--c4-frames", type=int, default=10000, help="frames of BASELINE configs[3] (all ranks together)")
     ap.add_argument("--profile", action="store_true",
                     help="cudaProfilerStart/Stop around the timed region (ncu --profile-from-start off)")
@@ -85,6 +86,9 @@ class ClockSampler:
             self.nv = pynvml
             self.h = pynvml.nvmlDeviceGetHandleByIndex(self._physical_index(index))
             self.max_sm = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            pynvml.nvmlDeviceGetClockInfo(self.h, pynvml.NVML_CLOCK_SM)      # first queries are slow: not inside the timed region
+            if hasattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons"):
+                pynvml.nvmlDeviceGetCurrentClocksEventReasons(self.h)
         except Exception:
             self.nv = None
 
@@ -468,19 +472,38 @@ def run_tdod(args):
     for _ in range(max(args.warmup, 3)):
         o = step()
     barrier()
-    t_start, t_end = _events(2)
+    # The timed steps replay ONE CUDA graph of the step (pipeline.GraphedSelect: the same 11 kernels, K-A forked onto the
+    # auxiliary stream inside the capture): the GPU never waits for Python, so a host hiccup cannot leak into a
+    # 20 ms timed region.  The same K steps launched eagerly are timed right after and reported beside it.
+    gs, graph_note = None, "eager launches (capture unavailable)"
+    if not args.no_graph:
+        try:
+            gs = pipeline.GraphedSelect(batch, N_PROP, warmup=max(args.warmup, 3), seed=7, obj_id_base=obj_base, frame_id_base=rank * F)
+            graph_note = "one CUDA graph per step (%d kernel nodes, K-A on a forked stream), replayed" % gs.launches
+        except Exception as e:                      # a capture problem must not cost the bench line
+            gs, graph_note = None, "eager launches (graph capture failed: %s)" % repr(e)[:120]
+    barrier()
+    t_start, t_end, g_start, g_end = _events(4)
     with ClockSampler(local) as clk:
         barrier()
         if args.profile:
             torch.cuda.profiler.start()
         t_start.record(stream)
         for k in range(args.steps):
-            o = step()
+            o = gs.replay() if gs is not None else step()
         t_end.record(stream)
         barrier()
         if args.profile:
             torch.cuda.profiler.stop()
         total_ms = t_start.elapsed_time(t_end)
+        eager_ms = total_ms
+        if gs is not None:
+            g_start.record(stream)
+            for k in range(args.steps):
+                o = step()
+            g_end.record(stream)
+            barrier()
+            eager_ms = g_start.elapsed_time(g_end)
         # the same K steps once more on ONE stream with events between the stages: stage times free of contention (inside the
         # timed region K-A runs on an auxiliary stream beside K-B).  Still under the clock sampler.
         marks_serial = [dict() for _ in range(args.steps)]
@@ -586,11 +609,12 @@ def run_tdod(args):
 
     # ---- max over ranks ----
     t = torch.tensor([total_ms, e2e["ms"] if e2e else 0.0, float(props), parity["ms_per_step"] if parity else 0.0,
-                      e2e["packed_ms"] if e2e else 0.0], dtype=torch.float64, device=dev)
+                      e2e["packed_ms"] if e2e else 0.0, eager_ms], dtype=torch.float64, device=dev)
     if world > 1:
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
         total_ms, e_ms_max, props_all, p_ms_max, ep_ms_max = float(tmax[0]), float(tmax[1]), float(tsum[2]), float(tmax[3]), float(tmax[4])
+        eager_ms = float(tmax[5])
     else:
         e_ms_max, props_all, p_ms_max, ep_ms_max = float(t[1]), float(props), float(t[3]), float(t[4])
     if rank == 0:
@@ -608,7 +632,10 @@ def run_tdod(args):
                                    % (F, W, H, N, N_PROP),
                        "frames_per_gpu": F, "objects_rank0": N, "rng": "in-kernel Philox4x32-10 (replayed bit for bit through the "
                        "reference-pinned HOST mode in tests/test_gpu_round2.py)",
-                       "l2": "inputs (1.98 GB per pass) are larger than the 126 MB L2"},
+                       "l2": "inputs (1.98 GB per pass) are larger than the 126 MB L2",
+                       "launch": graph_note},
+            "eager": {"ms_per_step": eager_ms / args.steps, "value": props_all / (eager_ms / args.steps * 1e-3), "unit": UNIT,
+                      "what": "the same K steps as eleven eager launches per step from Python (pipeline.select)"},
             "gpu_launches": pipeline.launches_per_select(N) * args.steps,
             "stages_ms_serial": dict(zip(stage_names, stage_ms_serial)), "ms_per_step_serial": serial_ms_step,
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,

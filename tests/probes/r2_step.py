@@ -27,3 +27,24 @@ run(6, True, marks); torch.cuda.synchronize()
 for m in marks[2:5]:
     o0 = m["kb0"]
     print("timeline (ms from kb0): " + "  ".join("%s %.3f" % (k, o0.elapsed_time(m[k])) for k in ("ka0", "ka1", "kb0", "kb1", "kc0", "kc1")))
+# one step captured in a CUDA graph (K-A forked onto the auxiliary stream inside the capture), replayed
+for ov in (True, False):
+    try:
+        st = torch.cuda.Stream(d)
+        st.wait_stream(torch.cuda.current_stream(d))
+        with torch.cuda.stream(st):
+            for _ in range(3):
+                pipeline.select(batch, 1000, seed=7, overlap=ov)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=st):
+            og = pipeline.select(batch, 1000, seed=7, overlap=ov)
+        for _ in range(3): g.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(20): g.replay()
+        e1.record(); torch.cuda.synchronize()
+        print("graph overlap=%s: %.4f ms per step, same winners %s" % (ov, e0.elapsed_time(e1) / 20, bool(torch.equal(og.best_idx, o.best_idx))))
+    except Exception as ex:
+        print("graph overlap=%s failed: %r" % (ov, ex))

@@ -512,3 +512,28 @@ def test_mask_rect_row_slot_widths_and_base_offsets(H, W):
         if ref is not None:
             dev_px = max(min(float(np.hypot(*(p - q))) for q in ref) for p in rects[t])
             assert dev_px < 1e-3, (t, rects[t], ref)
+
+
+@pytest.mark.gpu
+def test_graphed_select_replays_the_eager_step():
+    """pipeline.GraphedSelect: one step captured into a CUDA graph (K-A forked onto the auxiliary stream inside the capture)
+    gives the eager call's winners, and a replay after the batch was refilled IN PLACE follows the new frames."""
+    d = torch.device("cuda:0")
+    c = synth.CONFIGS["C2"]
+    b1, _, _ = synth.make_batch(range(0, 6), c["H"], c["W"], c["n_obj"], d)
+    b2, _, _ = synth.make_batch(range(0, 6), c["H"], c["W"], c["n_obj"], d)      # same layout, different content
+    b2.depth.mul_(1.07)
+    b2.masks.copy_(torch.roll(b2.masks, shifts=(9, -13), dims=(1, 2)))
+    b2.boxes[:, 0::2] = (b2.boxes[:, 0::2] - 13).clamp_(0, c["W"] - 1)
+    b2.boxes[:, 1::2] = (b2.boxes[:, 1::2] + 9).clamp_(0, c["H"] - 1)
+    e1 = pipeline.select(b1, 500, seed=3)
+    e2 = pipeline.select(b2, 500, seed=3)
+    gs = pipeline.GraphedSelect(b1, 500, seed=3)
+    o = gs.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(o.best_idx, e1.best_idx) and torch.equal(o.best_cube.view(torch.int32), e1.best_cube.view(torch.int32))
+    for name in ("depth", "ground", "K", "boxes", "prior_mean", "prior_std", "obj_frame", "masks"):
+        getattr(b1, name).copy_(getattr(b2, name))
+    o = gs.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(o.best_idx, e2.best_idx) and torch.equal(o.best_cube.view(torch.int32), e2.best_cube.view(torch.int32))
