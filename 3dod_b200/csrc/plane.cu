@@ -672,3 +672,54 @@ extern "C" int tdod_ransac_plane(const void* pts, int pts_f64, const int32_t* n_
                               out_best_iter, out_count, (float*)out_normal, out_inlier_mask, workspace, workspace_bytes,
                               st, /*negate=*/1);
 }
+
+// ------------------------------------------------------------------------------------------------
+// tdod_ransac_plane_static: tdod_ransac_plane without a caller-provided workspace and without any allocation.
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The scratch (hypotheses, inlier
+// counts, best-iteration temporaries) lives in ONE file-scope device array of fixed size that every GPU loading the
+// library holds until exit.  All calls on a device share it: calls that overlap on the GPU (different streams) race,
+// and the array keeps the last call's contents -- the only part that must start at zero, the inlier counts, is cleared
+// by hypotheses_kernel (counts[f, it] = 0) at the start of every call, on the call's stream.
+// ------------------------------------------------------------------------------------------------
+constexpr size_t kStaticHyps = TDOD_RANSAC_STATIC_MAX_HYPS;       // F * iters
+constexpr size_t kStaticFrames = TDOD_RANSAC_STATIC_MAX_FRAMES;   // F
+constexpr size_t kStaticBytes = ((kStaticHyps * sizeof(PlaneHyp<double>) + 255) & ~size_t(255)) + kStaticHyps * 4 + kStaticFrames * 4;
+static __device__ __align__(256) unsigned char g_ransac_scratch[kStaticBytes];   // 2 887 680 B
+
+// In host code `g_ransac_scratch` is a host-side stand-in for the symbol, NOT a device address: the address comes from
+// cudaGetSymbolAddress, once per device with that device current, and is what the kernels receive.
+static void* g_ransac_scratch_ptr[64] = {nullptr};
+
+extern "C" int tdod_ransac_plane_static(const void* pts, int pts_f64, const int32_t* n_pts, int F, int64_t P_cap,
+                                        const int32_t* sample_ids, uint64_t seed, int64_t frame_id_base, int iters,
+                                        double thresh, void* out_eq, int32_t* out_best_iter, int32_t* out_count,
+                                        void* out_normal, uint8_t* out_inlier_mask, void* stream) {
+    if (F == 0) return TDOD_OK;
+    if (!pts || !n_pts || F < 0 || P_cap <= 0 || iters <= 0)
+        return tdod_fail(TDOD_EINVAL, "tdod_ransac_plane_static: bad argument");
+    if ((size_t)F > kStaticFrames || (size_t)F * (size_t)iters > kStaticHyps)
+        return tdod_fail(TDOD_ERANGE, "tdod_ransac_plane_static: F > 1024 or F * iters > 65536 exceeds the static scratch; "
+                                      "use tdod_ransac_plane with a caller-provided workspace");
+    if ((size_t)tdod_ransac_workspace_bytes(F, iters, pts_f64) > kStaticBytes)
+        return tdod_fail(TDOD_ERANGE, "tdod_ransac_plane_static: workspace larger than the static scratch");
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= 64) return tdod_fail(TDOD_ERANGE, "tdod_ransac_plane_static: device index beyond 63");
+    void* ws = g_ransac_scratch_ptr[dev];
+    if (!ws) {                                          // set-up: once per device, that device being current
+        e = cudaGetSymbolAddress(&ws, g_ransac_scratch);
+        if (e != cudaSuccess) return (int)e;
+        if (!ws) return tdod_fail(TDOD_EINVAL, "tdod_ransac_plane_static: cudaGetSymbolAddress returned NULL");
+        g_ransac_scratch_ptr[dev] = ws;                 // (racing first calls store the same value)
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    if (pts_f64)
+        return ransac_impl<double>((const double*)pts, n_pts, F, P_cap, sample_ids, seed, frame_id_base, iters, thresh, (double*)out_eq,
+                                   out_best_iter, out_count, (double*)out_normal, out_inlier_mask, ws, (int64_t)kStaticBytes, st,
+                                   /*negate=*/0);
+    return ransac_impl<float>((const float*)pts, n_pts, F, P_cap, sample_ids, seed, frame_id_base, iters, thresh, (float*)out_eq,
+                              out_best_iter, out_count, (float*)out_normal, out_inlier_mask, ws, (int64_t)kStaticBytes, st,
+                              /*negate=*/1);
+}

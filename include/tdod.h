@@ -168,6 +168,25 @@ int tdod_ransac_plane(const void* pts, int pts_f64, const int32_t* n_pts, int F,
                       void* out_eq, int32_t* out_best_iter, int32_t* out_count, void* out_normal, uint8_t* out_inlier_mask,
                       void* workspace, int64_t workspace_bytes, void* stream);
 
+/* tdod_ransac_plane with NO workspace argument and NO allocation of any kind (no cudaMalloc / cudaFree, no allocating
+ * library call): its scratch is a fixed device array inside the library (2 887 680 bytes, held by every GPU that loads
+ * libtdod until the process exits).  This entry point has no counterpart in the reference; it was added
+ * for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  Same arguments, outputs and results as tdod_ransac_plane.
+ * Limits: F <= TDOD_RANSAC_STATIC_MAX_FRAMES and F * iters <= TDOD_RANSAC_STATIC_MAX_HYPS (e.g. 64 frames x 1000
+ * iterations); beyond them the call returns TDOD_ERANGE and launches nothing.
+ * Sharing: every call on a device uses the same array.  Calls that overlap on the GPU (different streams without an
+ * ordering between them) race; calls ordered on one stream, or by events, are safe.  The array keeps the previous call's
+ * contents; the part that must start at zero (the inlier counts) is cleared by the call itself on its stream.
+ * The first call on a device resolves the array's device address (cudaGetSymbolAddress, that device being current):
+ * make that first call outside a stream capture. */
+#define TDOD_RANSAC_STATIC_MAX_HYPS 65536
+#define TDOD_RANSAC_STATIC_MAX_FRAMES 1024
+int tdod_ransac_plane_static(const void* pts, int pts_f64, const int32_t* n_pts, int F, int64_t P_cap,
+                             const int32_t* sample_ids, uint64_t seed, int64_t frame_id_base, int iters, double thresh,
+                             void* out_eq, int32_t* out_best_iter, int32_t* out_count, void* out_normal,
+                             uint8_t* out_inlier_mask, void* stream);
+
 /* orthobasis_from_normal_t over linspace(0, pi, 36) (utils.py:112-146, proposals.py:405-406).
  * normals [F,3] fp64 (normals_f64) or fp32 -> out_table [F,36,9] fp32 (row-major 3x3, columns x, n, n x x). */
 int tdod_yaw_table(const void* normals, int normals_f64, int F, float* out_table, void* stream);
