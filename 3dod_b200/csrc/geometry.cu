@@ -46,6 +46,32 @@ __global__ void project_kernel(const float* __restrict__ cubes, int64_t M, const
     if (boxes) *reinterpret_cast<float4*>(boxes + m * 4) = make_float4(x0, y0, x1, y1);
 }
 
+// one K per cube, picked through cube_frame (the MABO branch projects every object's GT cube with its frame's intrinsics)
+__global__ void project_indexed_kernel(const float* __restrict__ cubes, int64_t M, const float* __restrict__ Kall,
+                                       const int32_t* __restrict__ cube_frame, Clamp cl, float* __restrict__ c2d,
+                                       float* __restrict__ boxes) {
+    const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= M) return;
+    float K[9];
+    const float* Kp = Kall + (size_t)cube_frame[m] * 9;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) K[k] = __ldg(Kp + k);
+    float q[15];
+#pragma unroll
+    for (int k = 0; k < 15; ++k) q[k] = cubes[m * 15 + k];
+    float X[8], Y[8], Z[8];
+    cube_corners(q, X, Y, Z);
+    float x0 = CUDART_INF_F, y0 = CUDART_INF_F, x1 = -CUDART_INF_F, y1 = -CUDART_INF_F;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        float u, v;
+        project(K, cl, X[j], Y[j], Z[j], u, v);
+        if (c2d) { c2d[m * 16 + 2 * j] = u; c2d[m * 16 + 2 * j + 1] = v; }
+        x0 = min_nan(x0, u); x1 = max_nan(x1, u); y0 = min_nan(y0, v); y1 = max_nan(y1, v);
+    }
+    if (boxes) *reinterpret_cast<float4*>(boxes + m * 4) = make_float4(x0, y0, x1, y1);
+}
+
 __global__ void iou_kernel(const float* __restrict__ ref, const float* __restrict__ boxes, int64_t n,
                            float* __restrict__ out) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -225,6 +251,19 @@ extern "C" int tdod_project_cubes(const float* cubes, int64_t M, const float* K,
         return tdod_fail(TDOD_EINVAL, "tdod_project_cubes: clamp (image width, height) is mandatory (spaces.py:240-243)");
     project_kernel<<<blocks_for(M, kT), kT, 0, (cudaStream_t)stream>>>(cubes, M, K, make_clamp(clamp_w, clamp_h),
                                                                       out_corners2d, out_boxes);
+    TDOD_CHECK_LAUNCH();
+    return TDOD_OK;
+}
+
+extern "C" int tdod_project_cubes_indexed(const float* cubes, int64_t M, const float* K, const int32_t* cube_frame, int clamp_w,
+                                          int clamp_h, float* out_corners2d, float* out_boxes, void* stream) {
+    if (M == 0) return TDOD_OK;
+    if (!cubes || !K || !cube_frame || M < 0 || (!out_corners2d && !out_boxes))
+        return tdod_fail(TDOD_EINVAL, "tdod_project_cubes_indexed: bad argument");
+    if (clamp_w <= 0 || clamp_h <= 0)
+        return tdod_fail(TDOD_EINVAL, "tdod_project_cubes_indexed: clamp (image width, height) is mandatory (spaces.py:240-243)");
+    project_indexed_kernel<<<blocks_for(M, kT), kT, 0, (cudaStream_t)stream>>>(cubes, M, K, cube_frame, make_clamp(clamp_w, clamp_h),
+                                                                              out_corners2d, out_boxes);
     TDOD_CHECK_LAUNCH();
     return TDOD_OK;
 }

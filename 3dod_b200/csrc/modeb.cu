@@ -21,6 +21,9 @@ using namespace tdod_raster;
 
 namespace {
 
+#ifndef TDOD_MODEB_MINB
+#define TDOD_MODEB_MINB 3
+#endif
 constexpr int kMT = 256;                // threads per CTA
 constexpr int kMW = kMT / 32;
 constexpr int kPtChunk = 2048;          // points examined per round
@@ -102,7 +105,7 @@ __device__ __forceinline__ void point_cloud_phase(const tdod_pss_args& a, int ob
                 }
             }
         }
-        for (int p0 = 0; p0 < P; p0 += kPtChunk) {
+        for (int p0 = (int)blockIdx.y * kPtChunk; p0 < P; p0 += (int)gridDim.y * kPtChunk) {   // chunks dealt round-robin to the splits
             __syncthreads();
             if (tid == 0) sh.n_kept = 0;
             __syncthreads();
@@ -136,12 +139,15 @@ __device__ __forceinline__ void point_cloud_phase(const tdod_pss_args& a, int ob
 #pragma unroll
         for (int u = 0; u < kPerThread; ++u) {
             const int i = i0 + u * kMT + tid;
-            if (i < n) a.all_pc[(size_t)obj * n + i] = cnt[u];
+            if (i < n) {
+                if (gridDim.y == 1) a.all_pc[(size_t)obj * n + i] = cnt[u];
+                else if (cnt[u]) atomicAdd(&a.all_pc[(size_t)obj * n + i], cnt[u]);     // (zeroed by the launcher)
+            }
         }
     }
 }
 
-__global__ void __launch_bounds__(kMT) modeb_kernel(const tdod_pss_args a) {
+__global__ void __launch_bounds__(kMT, TDOD_MODEB_MINB) modeb_kernel(const tdod_pss_args a) {
     extern __shared__ __align__(16) unsigned char dyn[];
     __shared__ ModeBShared sh;
     const int obj = blockIdx.x;
@@ -162,7 +168,7 @@ __global__ void __launch_bounds__(kMT) modeb_kernel(const tdod_pss_args a) {
         const int mask_total = sh.mask_total;
         float* os = a.all_scores + (size_t)obj * a.score_channels * n;
         Edge* ed = sh.edges[wid];
-        for (int i = wid; i < n; i += kMW) {                  // one warp per proposal
+        for (int i = wid + kMW * (int)blockIdx.y; i < n; i += kMW * (int)gridDim.y) {   // one warp per proposal
             float q[15];
 #pragma unroll
             for (int k = 0; k < 15; ++k) q[k] = cubes[(size_t)i * 15 + k];
@@ -225,7 +231,15 @@ int tdod_modeb_launch(const tdod_pss_args& a, void* stream) {
     if (smem > 200 * 1024) return tdod_fail(TDOD_ERANGE, "mode B: sampled mask does not fit in shared memory");
     const cudaError_t e = tdod_smem_opt_in((const void*)modeb_kernel, smem, &g_sm_modeb);
     if (e != cudaSuccess) return (int)e;
-    modeb_kernel<<<(unsigned)a.n_obj, kMT, smem, (cudaStream_t)stream>>>(a);
+    // few objects: an object's proposals (segmentation) and point chunks (point cloud) are dealt to `splits` CTAs, so that a
+    // small batch still fills the device (one CTA per object takes ~3 ms at n = 1000 whatever the batch size)
+    int splits = 1;
+    while (splits < 8 && (int64_t)a.n_obj * splits < 4 * 148 && kMW * splits * 2 <= a.n_prop) splits *= 2;
+    if (splits > 1 && (a.mode_flags & TDOD_MODEB_PC)) {
+        const cudaError_t em = cudaMemsetAsync(a.all_pc, 0, (size_t)a.n_obj * a.n_prop * sizeof(int32_t), (cudaStream_t)stream);
+        if (em != cudaSuccess) return (int)em;
+    }
+    modeb_kernel<<<dim3((unsigned)a.n_obj, (unsigned)splits), kMT, smem, (cudaStream_t)stream>>>(a);
     TDOD_CHECK_LAUNCH();
     return TDOD_OK;
 }

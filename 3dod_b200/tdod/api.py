@@ -39,6 +39,17 @@ def project_cubes(cubes, K, W, H, corners=True, boxes=True):
     return (c2d.reshape(lead + (8, 2)) if corners else None, bx.reshape(lead + (4,)) if boxes else None)
 
 
+def project_cubes_indexed(cubes, K, cube_frame, W, H, corners=True, boxes=True):
+    """project_cubes for cubes of different frames: cubes [M,15], K [F,3,3], cube_frame [M] int32 -> ([M,8,2] | None, [M,4] | None)"""
+    M = cubes.shape[0]
+    c2d = torch.empty((M, 8, 2), dtype=f32, device=cubes.device) if corners else None
+    bx = torch.empty((M, 4), dtype=f32, device=cubes.device) if boxes else None
+    L.check(L.lib().tdod_project_cubes_indexed(L.ptr(cubes, f32, "cubes"), M, L.ptr(K.reshape(-1, 9), f32, "K"),
+                                               L.ptr(cube_frame, i32, "cube_frame"), int(W), int(H), L.ptr(c2d), L.ptr(bx),
+                                               L.stream_ptr()))
+    return c2d, bx
+
+
 def score_iou(ref_box, boxes):
     n = boxes.shape[0]
     out = torch.empty(n, dtype=f32, device=boxes.device)

@@ -52,6 +52,7 @@ SIGNATURES = {
     "tdod_last_error_string": (C.c_char_p, []),
     "tdod_cube_corners": (_I, [_P, _L, _P, _P]),
     "tdod_project_cubes": (_I, [_P, _L, _P, _I, _I, _P, _P, _P]),
+    "tdod_project_cubes_indexed": (_I, [_P, _L, _P, _P, _I, _I, _P, _P, _P]),
     "tdod_score_iou": (_I, [_P, _P, _L, _P, _P]),
     "tdod_score_dimensions": (_I, [_P, _P, _P, _L, _P, _P, _L, _P, _P]),
     "tdod_mask_rect_workspace_bytes": (_L, [_L, _I, _I]),

@@ -53,11 +53,8 @@ def mabo(batch, gt_cubes, n_prop, seed=0, random_scores=None, **kw):
     N = batch.n_obj
     K_obj = batch.K[batch.obj_frame.long()]
     H, W = int(batch.depth.shape[1]), int(batch.depth.shape[2])
-    # cubes_to_box(gt_cubes[i], K, im_shape): one K per frame -> project per frame group; K differs per object here
-    gt_boxes = torch.empty((N, 4), dtype=torch.float32, device=dev)
-    for f in torch.unique(batch.obj_frame).tolist():
-        m = batch.obj_frame == f
-        gt_boxes[m] = api.project_cubes(gt_cubes[m].contiguous(), batch.K[f], W, H, corners=False)[1]
+    # cubes_to_box(gt_cubes[i], K, im_shape) per object (roi_heads.py:532): one launch, the frame of each object picks its K
+    gt_boxes = api.project_cubes_indexed(gt_cubes.contiguous(), batch.K.contiguous(), batch.obj_frame, W, H, corners=False)[1]
     sel = pipeline.select(batch, n_prop, seed=seed, iou_boxes=gt_boxes, mode_b=True, **kw)
     o = sel.all
     iou3d = api.box3d_iou(api.cube_corners(gt_cubes.contiguous()), api.cube_corners(o.all_cubes))

@@ -70,6 +70,12 @@ int tdod_cube_corners(const float* cubes, int64_t M, float* out_corners3d, void*
 int tdod_project_cubes(const float* cubes, int64_t M, const float* K, int clamp_w, int clamp_h,
                        float* out_corners2d, float* out_boxes, void* stream);
 
+/* The same for cubes of DIFFERENT frames in one launch: K [F,9], cube_frame [M] int32 picks the intrinsics of each cube.
+ * Replaces the per-object loop of the MABO branch, cubes_to_box(gt_cube, K, im_shape) once per object
+ * (cubercnn/modeling/roi_heads/roi_heads.py:532), when a batch holds the objects of many frames. */
+int tdod_project_cubes_indexed(const float* cubes, int64_t M, const float* K, const int32_t* cube_frame, int clamp_w,
+                               int clamp_h, float* out_corners2d, float* out_boxes, void* stream);
+
 /* ---- scores (ProposalNetwork/scoring/scorefunction.py) ------------------------------------------------ */
 
 /* score_iou (scorefunction.py:47-49 -> utils.py:186-192 -> detectron2 pairwise_iou). */

@@ -537,3 +537,28 @@ def test_graphed_select_replays_the_eager_step():
     o = gs.replay()
     torch.cuda.synchronize()
     assert torch.equal(o.best_idx, e2.best_idx) and torch.equal(o.best_cube.view(torch.int32), e2.best_cube.view(torch.int32))
+
+
+@pytest.mark.gpu
+def test_project_cubes_indexed_equals_the_per_frame_calls():
+    """tdod_project_cubes_indexed (one launch, K picked per cube) against tdod_project_cubes called frame by frame"""
+    d = torch.device("cuda:0")
+    g = torch.Generator(device="cpu").manual_seed(5)
+    F, M, W, H = 5, 333, 730, 530
+    K = torch.zeros((F, 3, 3))
+    for f in range(F):
+        K[f] = torch.tensor([[500.0 + 20 * f, 0, W / 2 + f], [0, 480.0 + 10 * f, H / 2 - f], [0, 0, 1]])
+    cubes = torch.zeros((M, 15))
+    cubes[:, 0:2] = torch.randn((M, 2), generator=g)
+    cubes[:, 2] = torch.rand(M, generator=g) * 6 - 1.0                # some behind the camera
+    cubes[:, 3:6] = torch.rand((M, 3), generator=g) + 0.1
+    q, _ = torch.linalg.qr(torch.randn((M, 3, 3), generator=g))
+    cubes[:, 6:] = q.reshape(M, 9)
+    frame = torch.randint(0, F, (M,), generator=g, dtype=torch.int32)
+    cubes, K, frame = cubes.to(d), K.to(d), frame.to(d)
+    c2d, bx = api.project_cubes_indexed(cubes, K, frame, W, H)
+    for f in range(F):
+        m = frame == f
+        c_ref, b_ref = api.project_cubes(cubes[m].contiguous(), K[f], W, H)
+        assert torch.equal(c2d[m].view(torch.int32), c_ref.view(torch.int32))
+        assert torch.equal(bx[m].view(torch.int32), b_ref.view(torch.int32))
