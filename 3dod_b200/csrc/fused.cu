@@ -32,6 +32,7 @@ struct Mail {               // per-CTA mailbox read by every CTA of the cluster 
     float maxdiff, maxd;
     float sdv[3];           // std_mode TORCH_CUDA: the three standard deviations, published by rank 0
     int nanflag[3];
+    int nfail;              // Philox dimensions: proposals whose first draw fell outside the truncation bounds
     float am_v;
     int am_i;
 };
@@ -80,6 +81,19 @@ __device__ __forceinline__ float philox_xn(const tdod_pss_args& a, const ObjCtx&
 // `xn`: Philox mode only -- the standard normal of the x draw (fourth normal of the first try's Philox block)
 // `zn`: the three numbers behind (w,h,l) as HOST mode would be fed them (accepted standard normals, or the U[0,1) draws of
 // the uniform-dimension modes) -- what out_noise records so that a PHILOX run can be replayed in HOST mode
+// one round of the rejection loop of draw_whl (Philox stream, prior dimensions): redraws the components that are not ok yet
+__device__ __forceinline__ void draw_whl_try(const tdod_pss_args& a, const ObjCtx& c, int i, uint32_t t, float& w, float& h, float& l,
+                                             bool& okw, bool& okh, bool& okl, float& xn, float (&zn)[3]) {
+    const Philox ph(a.seed);
+    const uint64_t gid = (uint64_t)(a.obj_id_base + c.obj);
+    const uint4 r = ph((uint32_t)i, (uint32_t)gid, (uint32_t)(gid >> 32) ^ 0x57484Cu, t);
+    const float2 n01 = box_muller(r.x, r.y), n23 = box_muller(r.z, r.w);
+    if (t == 0) xn = n23.y;
+    if (!okw) { zn[0] = n01.x; w = scale_normal(n01.x, c.mu[0], c.sg[0]); okw = !(w < TDOD_MIN_PROP_S || w > c.hi[0]); }
+    if (!okh) { zn[1] = n01.y; h = scale_normal(n01.y, c.mu[1], c.sgh);   okh = !(h < TDOD_MIN_PROP_S || h > c.hi[1]); }
+    if (!okl) { zn[2] = n23.x; l = scale_normal(n23.x, c.mu[2], c.sg[2]); okl = !(l < TDOD_MIN_PROP_S || l > c.hi[2]); }
+}
+
 __device__ __forceinline__ void draw_whl(const tdod_pss_args& a, const ObjCtx& c, int i, float& w, float& h, float& l, float& xn,
                                          float (&zn)[3]) {
     xn = 0.f;
@@ -111,18 +125,9 @@ __device__ __forceinline__ void draw_whl(const tdod_pss_args& a, const ObjCtx& c
     }
     // utils.py:49-58: invalid entries are replaced by fresh draws until all are in [0.05, mean + k std];
     // per element that is an independent rejection loop (same distribution, Philox stream).
-    const Philox ph(a.seed);
-    const uint64_t gid = (uint64_t)(a.obj_id_base + c.obj);
     bool okw = false, okh = false, okl = false;
     w = h = l = 0.f;
-    for (uint32_t t = 0; t < 10001u && !(okw && okh && okl); ++t) {
-        const uint4 r = ph((uint32_t)i, (uint32_t)gid, (uint32_t)(gid >> 32) ^ 0x57484Cu, t);
-        const float2 n01 = box_muller(r.x, r.y), n23 = box_muller(r.z, r.w);
-        if (t == 0) xn = n23.y;
-        if (!okw) { zn[0] = n01.x; w = scale_normal(n01.x, c.mu[0], c.sg[0]); okw = !(w < TDOD_MIN_PROP_S || w > c.hi[0]); }
-        if (!okh) { zn[1] = n01.y; h = scale_normal(n01.y, c.mu[1], c.sgh);   okh = !(h < TDOD_MIN_PROP_S || h > c.hi[1]); }
-        if (!okl) { zn[2] = n23.x; l = scale_normal(n23.x, c.mu[2], c.sg[2]); okl = !(l < TDOD_MIN_PROP_S || l > c.hi[2]); }
-    }
+    for (uint32_t t = 0; t < 10001u && !(okw && okh && okl); ++t) draw_whl_try(a, c, i, t, w, h, l, okw, okh, okl, xn, zn);
 }
 
 // standard normals for x,y,z and the rotation of proposal i -> q[0..2], q[6..14]
@@ -311,11 +316,48 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
     if (tid < 8) sh.rect[tid] = (has_rect && a.rects) ? a.rects[(size_t)obj * 8 + tid] : 0.f;
     for (int t = tid; t < 4 * 3 * 256; t += kThreads) (&sh.mail.hist[0][0][0])[t] = 0;
     if (tid < 3) { sh.prefix[tid] = 0u; sh.kth[tid] = (n - 1) / 2; sh.mail.nanflag[tid] = 0; }
+    if (tid == 0) sh.mail.nfail = 0;
     __syncthreads();
 
     // ---------------- phase 1: centre seeds + dimensions ----------------
     const float* depth = a.depth + (size_t)c.frame * a.H * a.W;
     const float fx = sh.K[0], cx = sh.K[2], cy = sh.K[5];
+    // Philox dimensions (utils.py:49-58 as an independent rejection loop per element): 13 % of the proposals need a second
+    // draw, and a warp that loops until its last lane is done spends 2.2 rounds per proposal.  Round 0 runs for everybody,
+    // the proposals that are not done are queued and their redraws run densely packed (one queued proposal per thread).
+    const bool split_draw = a.rng_mode == TDOD_RNG_PHILOX && a.dims_mode == TDOD_DIMS_PRIOR;
+    if (split_draw) {
+        constexpr int kFailCap = 3 * 256;
+        int* fail = &sh.mail.hist[3][0][0];            // free until the last radix pass; every used entry is zeroed again
+        float* on = a.out_noise ? a.out_noise + (size_t)obj * 6 * n : nullptr;
+        for (int j = tid; j < cnt; j += kThreads) {
+            const int i = i0 + j;
+            float w = 0.f, h = 0.f, l = 0.f, xn = 0.f, zn[3];
+            bool okw = false, okh = false, okl = false;
+            draw_whl_try(a, c, i, 0u, w, h, l, okw, okh, okl, xn, zn);
+            if (!(okw && okh && okl)) {
+                const int slot = atomicAdd(&sh.mail.nfail, 1);
+                if (slot < kFailCap) fail[slot] = j | (okw ? 0x10000 : 0) | (okh ? 0x20000 : 0) | (okl ? 0x40000 : 0);
+                else for (uint32_t t = 1; t < 10001u && !(okw && okh && okl); ++t) draw_whl_try(a, c, i, t, w, h, l, okw, okh, okl, xn, zn);
+            }
+            s_w[j] = w; s_h[j] = h; s_l[j] = l; s_d[j] = xn;
+            if (on) { on[i] = zn[0]; on[n + i] = zn[1]; on[2 * n + i] = zn[2]; }
+        }
+        __syncthreads();
+        const int nf = min(sh.mail.nfail, kFailCap);
+        for (int f = tid; f < nf; f += kThreads) {
+            const int e = fail[f];
+            fail[f] = 0;
+            const int j = e & 0xffff, i = i0 + j;
+            float w = s_w[j], h = s_h[j], l = s_l[j], xn = 0.f, zn[3] = {0.f, 0.f, 0.f};
+            bool okw = (e & 0x10000) != 0, okh = (e & 0x20000) != 0, okl = (e & 0x40000) != 0;
+            const bool hw = !okw, hh = !okh, hl = !okl;
+            for (uint32_t t = 1; t < 10001u && !(okw && okh && okl); ++t) draw_whl_try(a, c, i, t, w, h, l, okw, okh, okl, xn, zn);
+            s_w[j] = w; s_h[j] = h; s_l[j] = l;
+            if (on) { if (hw) on[i] = zn[0]; if (hh) on[n + i] = zn[1]; if (hl) on[2 * n + i] = zn[2]; }
+        }
+        __syncthreads();
+    }
     double lsum[3] = {0.0, 0.0, 0.0};
     int lnan[3] = {0, 0, 0};
     for (int j = tid; j < cnt; j += kThreads) {
@@ -331,14 +373,17 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
             const float d = __ldg(depth + (size_t)iy * a.W + ix);
             centre_seed(gx, gy, d, fx, cx, cy, x, y, zt);
         }
-        float zn[3];
-        draw_whl(a, c, i, w, h, l, xn, zn);
-        s_d[j] = xn;                                                       // parked until phase 2 reads it back
-        const float z = __fadd_rn(zt, __fdiv_rn(l, 2.f));                  // proposals.py:394
-        if (a.out_noise) {
-            float* on = a.out_noise + (size_t)obj * 6 * n;
-            on[i] = zn[0]; on[n + i] = zn[1]; on[2 * n + i] = zn[2];
+        if (split_draw) { w = s_w[j]; h = s_h[j]; l = s_l[j]; }
+        else {
+            float zn[3];
+            draw_whl(a, c, i, w, h, l, xn, zn);
+            s_d[j] = xn;                                                   // parked until phase 2 reads it back
+            if (a.out_noise) {
+                float* on = a.out_noise + (size_t)obj * 6 * n;
+                on[i] = zn[0]; on[n + i] = zn[1]; on[2 * n + i] = zn[2];
+            }
         }
+        const float z = __fadd_rn(zt, __fdiv_rn(l, 2.f));                  // proposals.py:394
         if (a.out_seeds) {
             float* os = a.out_seeds + (size_t)obj * 3 * n;
             os[i] = x; os[n + i] = y; os[2 * n + i] = z;
