@@ -600,7 +600,8 @@ int ransac_impl(const T* pts, const int32_t* n_pts, int F, int64_t P_cap, const 
         constexpr int PT = 4;
         const size_t smem = (size_t)iters * (sizeof(PlaneHyp<T>) + sizeof(int));
         if (smem > 200 * 1024) return tdod_fail(TDOD_ERANGE, "tdod_ransac_plane: too many iterations for shared memory");
-        cudaError_t e = cudaFuncSetAttribute(count_kernel<T, PT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        static tdod_smem_cache sm_count;
+        cudaError_t e = tdod_smem_opt_in((const void*)count_kernel<T, PT>, smem, &sm_count);
         if (e != cudaSuccess) return (int)e;
         const unsigned tiles = (unsigned)((P_cap + 256 * PT - 1) / (256 * PT));
         count_kernel<T, PT><<<dim3(tiles, F), 256, smem, st>>>(pts, n_pts, P_cap, hyps, iters, counts);
@@ -635,12 +636,14 @@ extern "C" int tdod_backproject(const float* depth, const uint8_t* ground, const
     const unsigned grid = (unsigned)F * kBpCluster;
     cudaError_t e;
     if (flavour == TDOD_BACKPROJECT_NUMPY) {
-        e = cudaFuncSetAttribute(backproject_kernel<double, TDOD_BACKPROJECT_NUMPY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        static tdod_smem_cache sm_bp64;
+        e = tdod_smem_opt_in((const void*)backproject_kernel<double, TDOD_BACKPROJECT_NUMPY>, smem, &sm_bp64);
         if (e != cudaSuccess) return (int)e;
         backproject_kernel<double, TDOD_BACKPROJECT_NUMPY><<<grid, kBpT, smem, st>>>(depth, ground, K, H, W, stride, iters,
                                                                                       (double*)plane_pts, (double*)other_pts, counts);
     } else if (flavour == TDOD_BACKPROJECT_TORCH) {
-        e = cudaFuncSetAttribute(backproject_kernel<float, TDOD_BACKPROJECT_TORCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        static tdod_smem_cache sm_bp32;
+        e = tdod_smem_opt_in((const void*)backproject_kernel<float, TDOD_BACKPROJECT_TORCH>, smem, &sm_bp32);
         if (e != cudaSuccess) return (int)e;
         backproject_kernel<float, TDOD_BACKPROJECT_TORCH><<<grid, kBpT, smem, st>>>(depth, ground, K, H, W, stride, iters,
                                                                                     (float*)plane_pts, (float*)other_pts, counts);

@@ -290,7 +290,8 @@ extern "C" int tdod_score_segmentation(const uint8_t* mask, int H, int W, const 
     const int Hs = (H + 3) >> 2, Ws = (W + 3) >> 2;
     const size_t smem = (size_t)Hs * (Ws + 1) * sizeof(uint16_t);
     if (smem > 200 * 1024) return tdod_fail(TDOD_ERANGE, "tdod_score_segmentation: sampled mask does not fit in shared memory");
-    cudaError_t e = cudaFuncSetAttribute(seg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    static tdod_smem_cache sm_seg;
+    cudaError_t e = tdod_smem_opt_in((const void*)seg_kernel, smem, &sm_seg);
     if (e != cudaSuccess) return (int)e;
     seg_kernel<<<(unsigned)((n + kSegWarps - 1) / kSegWarps), kSegWarps * 32, smem, (cudaStream_t)stream>>>(mask, H, W, corners2d, n, power5, out);
     TDOD_CHECK_LAUNCH();

@@ -350,3 +350,26 @@ def propose_score_select(depth, K, boxes, prior_mean, prior_std, obj_frame, rect
     a.out_noise, a.out_yaw_idx, a.out_seeds = L.ptr(o.noise), L.ptr(o.yaw_idx), L.ptr(o.seeds)
     L.check(L.lib().tdod_propose_score_select(C.byref(a), L.stream_ptr()))
     return o
+
+
+def _on_tensor_device(fn):
+    """Every public call runs with the device of its first CUDA tensor argument current, so the launch, the stream
+    (lib.stream_ptr) and the outputs all belong to that device whatever device the caller had selected."""
+    import functools
+
+    @functools.wraps(fn)
+    def call(*args, **kw):
+        for x in args + tuple(kw.values()):
+            if isinstance(x, torch.Tensor) and x.is_cuda:
+                if x.device.index == torch.cuda.current_device():
+                    break
+                with torch.cuda.device(x.device):
+                    return fn(*args, **kw)
+        return fn(*args, **kw)
+    return call
+
+
+for _name, _fn in list(globals().items()):
+    if callable(_fn) and not _name.startswith("_") and getattr(_fn, "__module__", None) == __name__ and not isinstance(_fn, type):
+        globals()[_name] = _on_tensor_device(_fn)
+del _name, _fn

@@ -123,6 +123,10 @@ def ptr(t, dtype=None, name="tensor"):
         raise TypeError("%s must be a torch.Tensor" % name)
     if not t.is_cuda:
         raise ValueError("%s must be a CUDA tensor (libtdod has no CPU path)" % name)
+    if t.device.index != torch.cuda.current_device():
+        # the launch goes to the CURRENT device's stream: a foreign pointer would fault there (tdod.api switches the device)
+        raise ValueError("%s lives on %s while cuda:%d is current: call under torch.cuda.device(%s)"
+                         % (name, t.device, torch.cuda.current_device(), t.device))
     if not t.is_contiguous():
         raise ValueError("%s must be contiguous" % name)
     if dtype is not None and t.dtype != dtype:

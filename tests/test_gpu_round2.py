@@ -562,3 +562,25 @@ def test_project_cubes_indexed_equals_the_per_frame_calls():
         c_ref, b_ref = api.project_cubes(cubes[m].contiguous(), K[f], W, H)
         assert torch.equal(c2d[m].view(torch.int32), c_ref.view(torch.int32))
         assert torch.equal(bx[m].view(torch.int32), b_ref.view(torch.int32))
+
+
+@pytest.mark.gpu
+def test_api_calls_follow_the_device_of_their_tensors():
+    """tensors on cuda:1 while cuda:0 is current: tdod.api switches the device for the call (launch, stream and outputs on
+    cuda:1, same results as on cuda:0); a raw pointer handed to the library on the wrong device is refused loudly"""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    c = synth.CONFIGS["C2"]
+    b0, _, _ = synth.make_batch(range(3), c["H"], c["W"], c["n_obj"], torch.device("cuda:0"))
+    b1 = b0.to("cuda:1")
+    torch.cuda.set_device(0)
+    r0, h0 = api.mask_rect(b0.masks)
+    r1, h1 = api.mask_rect(b1.masks)
+    assert r1.device.index == 1 and torch.cuda.current_device() == 0
+    assert torch.equal(h0.cpu(), h1.cpu()) and torch.equal(r0.cpu().view(torch.int32), r1.cpu().view(torch.int32))
+    s0 = pipeline.select(b0, 300, seed=3)
+    s1 = pipeline.select(b1, 300, seed=3)
+    assert s1.best_idx.device.index == 1
+    assert torch.equal(s0.best_idx.cpu(), s1.best_idx.cpu())
+    with pytest.raises(ValueError):
+        L.ptr(b1.depth, torch.float32, "depth")
