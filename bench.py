@@ -55,6 +55,7 @@ def parse():
     ap.add_argument("--no-configs", action="store_true", help="skip the C1 / C3 / C5 / mode-B / C4 sub-records")
     ap.add_argument("--no-parity-rng", action="store_true", help="skip the reference-order RNG figure")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of CUDA-graph replays of the step")
+    ap.add_argument("--graph-depth", type=int, default=2, help="copies of the step graph replayed round-robin (1: steps back to back)")
     ap.add_argument("--c4-frames", type=int, default=10000, help="frames of BASELINE configs[3] (all ranks together)")
     ap.add_argument("--profile", action="store_true",
                     help="cudaProfilerStart/Stop around the timed region (ncu --profile-from-start off)")
@@ -478,8 +479,11 @@ def run_tdod(args):
     gs, graph_note = None, "eager launches (capture unavailable)"
     if not args.no_graph:
         try:
-            gs = pipeline.GraphedSelect(batch, N_PROP, warmup=max(args.warmup, 3), seed=7, obj_id_base=obj_base, frame_id_base=rank * F)
-            graph_note = "one CUDA graph per step (%d kernel nodes, K-A on a forked stream), replayed" % gs.launches
+            gs = pipeline.GraphedSelect(batch, N_PROP, warmup=max(args.warmup, 3), depth=args.graph_depth, seed=7, obj_id_base=obj_base,
+                                        frame_id_base=rank * F)
+            graph_note = ("one CUDA graph per step (%d kernel nodes, K-A on a forked stream), replayed; %d copies of the graph on %d "
+                          "streams round-robin, so that step i+1's mask kernel runs beside step i's proposal kernel (every step "
+                          "complete, own outputs)" % (gs.launches, gs.depth, gs.depth))
         except Exception as e:                      # a capture problem must not cost the bench line
             gs, graph_note = None, "eager launches (graph capture failed: %s)" % repr(e)[:120]
     barrier()
@@ -491,12 +495,23 @@ def run_tdod(args):
         t_start.record(stream)
         for k in range(args.steps):
             o = gs.replay() if gs is not None else step()
+        if gs is not None:
+            gs.join()
         t_end.record(stream)
         barrier()
         if args.profile:
             torch.cuda.profiler.stop()
         total_ms = t_start.elapsed_time(t_end)
         eager_ms = total_ms
+        single_ms = None
+        if gs is not None and gs.depth > 1:            # the same K replays of ONE graph on one stream: steps back to back
+            q0, q1 = _events(2)
+            q0.record(stream)
+            for k in range(args.steps):
+                gs.graphs[0].replay()
+            q1.record(stream)
+            barrier()
+            single_ms = q0.elapsed_time(q1)
         if gs is not None:
             g_start.record(stream)
             for k in range(args.steps):
@@ -636,6 +651,8 @@ def run_tdod(args):
                        "launch": graph_note},
             "eager": {"ms_per_step": eager_ms / args.steps, "value": props_all / (eager_ms / args.steps * 1e-3), "unit": UNIT,
                       "what": "the same K steps as eleven eager launches per step from Python (pipeline.select)"},
+            "graph_back_to_back": None if single_ms is None else {"ms_per_step": single_ms / args.steps,
+                                                                   "what": "K replays of one graph on one stream (no overlap between steps), this rank"},
             "gpu_launches": pipeline.launches_per_select(N) * args.steps,
             "stages_ms_serial": dict(zip(stage_names, stage_ms_serial)), "ms_per_step_serial": serial_ms_step,
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,

@@ -48,3 +48,26 @@ for ov in (True, False):
         print("graph overlap=%s: %.4f ms per step, same winners %s" % (ov, e0.elapsed_time(e1) / 20, bool(torch.equal(og.best_idx, o.best_idx))))
     except Exception as ex:
         print("graph overlap=%s failed: %r" % (ov, ex))
+# NG graphs of the step replayed round-robin on NG streams: step i+1's K-A / K-B overlap step i's K-C
+for NG in (2, 3, 4):
+    try:
+        g2 = [pipeline.GraphedSelect(batch, 1000, seed=7) for _ in range(NG)]
+        ss = [torch.cuda.Stream(d) for _ in range(NG)]
+        def pingpong(k):
+            cur = torch.cuda.current_stream(d)
+            for s_ in ss: s_.wait_stream(cur)
+            for i in range(k):
+                with torch.cuda.stream(ss[i % NG]):
+                    g2[i % NG].replay()
+            for s_ in ss: cur.wait_stream(s_)
+        pingpong(2 * NG); torch.cuda.synchronize()
+        res2 = []
+        for rep in range(3):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); pingpong(24); e1.record(); torch.cuda.synchronize()
+            res2.append(e0.elapsed_time(e1) / 24)
+        print("%d graphs, round-robin streams: %s ms per step, same winners %s"
+              % (NG, " ".join("%.4f" % r for r in res2), all(bool(torch.equal(g.out.best_idx, o.best_idx)) for g in g2)))
+        del g2
+    except Exception as ex:
+        print("round-robin %d failed: %r" % (NG, ex))

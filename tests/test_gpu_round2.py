@@ -584,3 +584,27 @@ def test_api_calls_follow_the_device_of_their_tensors():
     assert torch.equal(s0.best_idx.cpu(), s1.best_idx.cpu())
     with pytest.raises(ValueError):
         L.ptr(b1.depth, torch.float32, "depth")
+
+
+@pytest.mark.gpu
+def test_graphed_select_depth_two_overlaps_steps_and_keeps_the_winners():
+    """GraphedSelect(depth=2): two copies of the step graph on two streams, replayed round-robin; every replay gives the
+    eager call's winners in its own output slot, and join() orders the caller's stream after all of them"""
+    d = torch.device("cuda:0")
+    c = synth.CONFIGS["C2"]
+    b, _, _ = synth.make_batch(range(0, 8), c["H"], c["W"], c["n_obj"], d)
+    e = pipeline.select(b, 400, seed=3)
+    gs = pipeline.GraphedSelect(b, 400, depth=2, seed=3)
+    outs = [gs.replay() for _ in range(5)]
+    gs.join()
+    torch.cuda.synchronize()
+    assert outs[0] is outs[2] and outs[0] is not outs[1]
+    for o in outs[:2]:
+        assert torch.equal(o.best_idx, e.best_idx) and torch.equal(o.best_cube.view(torch.int32), e.best_cube.view(torch.int32))
+    # refill in place after join(): both slots follow
+    b.depth.mul_(1.05)
+    e2 = pipeline.select(b, 400, seed=3)
+    o1, o2 = gs.replay(), gs.replay()
+    gs.join()
+    torch.cuda.synchronize()
+    assert torch.equal(o1.best_idx, e2.best_idx) and torch.equal(o2.best_idx, e2.best_idx)
