@@ -394,7 +394,7 @@ __device__ __forceinline__ float2 fadd2(const float2 a, const float2 b) {
 template <typename T>
 __global__ void __launch_bounds__(kFiltT) count_filter_kernel(const T* __restrict__ pts, const int32_t* __restrict__ n_pts,
                                                              int64_t P_cap, const PlaneHyp<T>* __restrict__ hyps,
-                                                             int iters, int32_t* __restrict__ counts) {
+                                                             int iters, int32_t* __restrict__ counts, int tile_pts) {
     __shared__ float4 s_xy[kTilePts];      // (x, x, y, y)
     __shared__ float2 s_z[kTilePts];       // (z, z)
     __shared__ int s_list[kFiltT * kHypT];
@@ -402,9 +402,9 @@ __global__ void __launch_bounds__(kFiltT) count_filter_kernel(const T* __restric
     __shared__ int s_cnt[kFiltT / 32];
     const int f = blockIdx.y, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int P = n_pts[f];
-    const int tile0 = blockIdx.x * kTilePts;
+    const int tile0 = blockIdx.x * tile_pts;          // tile_pts <= kTilePts: small batches use smaller tiles, more CTAs
     if (tile0 >= P) return;
-    const int np = min(kTilePts, P - tile0);
+    const int np = min(tile_pts, P - tile0);
     const T* X = pts + (size_t)f * 3 * P_cap;
     const T* Y = X + P_cap;
     const T* Z = Y + P_cap;
@@ -606,8 +606,11 @@ int ransac_impl(const T* pts, const int32_t* n_pts, int F, int64_t P_cap, const 
         const unsigned tiles = (unsigned)((P_cap + 256 * PT - 1) / (256 * PT));
         count_kernel<T, PT><<<dim3(tiles, F), 256, smem, st>>>(pts, n_pts, P_cap, hyps, iters, counts);
     } else {
-        const unsigned tiles = (unsigned)((P_cap + kTilePts - 1) / kTilePts);
-        count_filter_kernel<T><<<dim3(tiles, F), kFiltT, 0, st>>>(pts, n_pts, P_cap, hyps, iters, counts);
+        // few frames: smaller point tiles, so that the (tile, frame) grid still covers the device about twice over
+        int tile_pts = kTilePts;
+        while (tile_pts > 128 && (int64_t)F * ((P_cap + tile_pts - 1) / tile_pts) < 2 * 148 * 5) tile_pts >>= 1;
+        const unsigned tiles = (unsigned)((P_cap + tile_pts - 1) / tile_pts);
+        count_filter_kernel<T><<<dim3(tiles, F), kFiltT, 0, st>>>(pts, n_pts, P_cap, hyps, iters, counts, tile_pts);
     }
     TDOD_CHECK_LAUNCH();
     select_kernel<T><<<F, 256, 0, st>>>(hyps, counts, iters, negate, out_eq, out_best, out_count, out_normal);

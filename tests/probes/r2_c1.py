@@ -1,0 +1,24 @@
+"""C1 (one 640x480 frame, 5 objects x 1000 proposals): eager / graph latency of one select; under ncu: the per-kernel list."""
+import os, sys, torch
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.join(ROOT, "3dod_b200"))
+from tdod import pipeline, synth
+d = torch.device("cuda:0")
+name = sys.argv[1] if len(sys.argv) > 1 else "C1"
+c = synth.CONFIGS[name]
+fr = synth.make_frames(name, range(1), device=d)
+b = pipeline.FrameBatch.from_frames(fr, d)
+n = c.get("n_prop", 1000)
+for _ in range(5): pipeline.select(b, n, seed=7)
+torch.cuda.synchronize()
+def timed(fn, k=50):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(k): fn()
+    e1.record(); torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / k
+print(name, "objects", b.n_obj, "n", n)
+print("eager overlap %.4f ms   eager one stream %.4f ms" % (timed(lambda: pipeline.select(b, n, seed=7)), timed(lambda: pipeline.select(b, n, seed=7, overlap=False))))
+for ov in (True, False):
+    gs = pipeline.GraphedSelect(b, n, seed=7, overlap=ov)
+    print("graph overlap=%s %.4f ms" % (ov, timed(gs.replay)))
