@@ -47,7 +47,7 @@ def build(force=False, verbose=False):
             sys.stderr.write(out)
         if p.returncode:
             raise RuntimeError("nvcc failed on %s" % src)
-    cmd = [NVCC, "-shared", "-o", OUT] + objs + ["-lcudart"]
+    cmd = [NVCC, "-shared", "-o", OUT] + objs + ["-lcudart", "-lpthread"]
     subprocess.check_call(cmd)
     return OUT
 

@@ -70,6 +70,7 @@ SIGNATURES = {
     "tdod_ransac_workspace_bytes": (_L, [_I, _I, _I]),
     "tdod_ransac_plane": (_I, [_P, _I, _P, _I, _L, _P, _U64, _L, _I, _D, _P, _P, _P, _P, _P, _P, _L, _P]),
     "tdod_ransac_plane_static": (_I, [_P, _I, _P, _I, _L, _P, _U64, _L, _I, _D, _P, _P, _P, _P, _P, _P]),
+    "tdod_host_pack_masks": (_I, [_P, _L, _I, _I, _P, _I]),
     "tdod_yaw_table": (_I, [_P, _I, _I, _P, _P]),
     "tdod_resize_nearest": (_I, [_P, _I, _I, _I, _I, _P, _P, _P, _I, _I, _P]),
     "tdod_torch_std": (_I, [_P, _L, _I, _P, _P]),

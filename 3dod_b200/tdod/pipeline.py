@@ -11,6 +11,8 @@ Everything runs on the GPU through libtdod; there is no CPU path.  `FrameBatch` 
 `HostBatch` pinned host tensors; `Pipeline.run_host` streams a HostBatch through the device in chunks of
 frames with the copies of chunk k+1 overlapping the kernels of chunk k.
 """
+import os
+
 import torch
 
 from . import api
@@ -405,14 +407,22 @@ class Pipeline:
     stream and a compute stream.  The result (winners [N, 15+4+1+1] packed as fp32) is read back per chunk."""
 
     def __init__(self, H, W, n_prop, chunk_frames=32, max_obj_per_chunk=None, device="cuda", seed=0,
-                 use_ground=True, packed_masks=False):
+                 use_ground=True, packed_masks=False, host_pack=False, pack_threads=None):
         self.H, self.W, self.n_prop = H, W, n_prop
         self.dev = torch.device(device)
         self.chunk = chunk_frames
         self.max_obj = max_obj_per_chunk or chunk_frames * 40
         self.seed = seed
         self.use_ground = use_ground
-        self.packed_masks = packed_masks      # host batches carry `masks_packed` (1 bit/px) instead of `masks`
+        # host_pack: the host batch holds bool / uint8 masks (as the reference's callers do) and every chunk's masks are
+        # packed to 1 bit/px on the host cores (tdod_host_pack_masks) into a pinned staging buffer while the previous
+        # chunk's copy is in flight: 1/8 of the mask bytes cross PCIe, K-B reads the bitmap as it is
+        self.host_pack = bool(host_pack)
+        packed_masks = bool(packed_masks) or self.host_pack
+        self.packed_masks = packed_masks      # the device side reads masks at 1 bit/px (`masks_packed` of the host batch, or packed here)
+        if pack_threads is None:
+            pack_threads = max(1, min(32, (os.cpu_count() or 1) // max(1, int(os.environ.get("WORLD_SIZE", "1")))))
+        self.pack_threads = int(pack_threads)
         self.copy_stream = torch.cuda.Stream(self.dev)
         self.compute_stream = torch.cuda.Stream(self.dev)
         d = self.dev
@@ -429,6 +439,7 @@ class Pipeline:
                 masks=None if packed_masks else torch.empty((self.max_obj, H, W), dtype=u8, device=d),
                 mpk=torch.empty((self.max_obj, H, (W + 31) // 32), dtype=i32, device=d) if packed_masks else None,
                 packed=torch.empty((self.max_obj, 21), dtype=f32, device=d),
+                stage=torch.empty((self.max_obj, H, (W + 31) // 32), dtype=i32).pin_memory() if self.host_pack else None,
                 copied=torch.cuda.Event(), done=torch.cuda.Event()))
         self.launches = 0
         self.h2d_bytes = 0
@@ -440,7 +451,13 @@ class Pipeline:
         F, N = hb.n_frames, hb.n_obj
         if out is None:
             out = torch.empty((N, 21), dtype=f32).pin_memory()
-        if self.packed_masks:
+        if self.host_pack:
+            if hb.masks is None:
+                raise ValueError("host_pack: the host batch needs masks (bool / uint8)")
+            masks_h = hb.masks.view(u8) if hb.masks.dtype == torch.bool else hb.masks
+            if not masks_h.is_contiguous() or masks_h.dtype != u8:
+                raise ValueError("host_pack: masks must be a contiguous bool / uint8 tensor")
+        elif self.packed_masks:
             if hb.masks_packed is None:
                 raise ValueError("this Pipeline was built for packed masks: the host batch needs masks_packed")
             masks_h = hb.masks_packed
@@ -458,6 +475,10 @@ class Pipeline:
                 raise ValueError("chunk holds %d objects, more than max_obj_per_chunk=%d" % (no, self.max_obj))
             sl = self.slots[k & 1]
             k += 1
+            if self.host_pack and no:
+                sl["copied"].synchronize()                     # the staging buffer's previous copy has left the host
+                L.check(L.lib().tdod_host_pack_masks(masks_h[o0:o1].data_ptr(), no, self.H, self.W, sl["stage"].data_ptr(),
+                                                     self.pack_threads))
             with torch.cuda.stream(self.copy_stream):
                 self.copy_stream.wait_event(sl["done"])       # slot free again (previous use finished)
                 sl["depth"][:nf].copy_(hb.depth[f0:f1], non_blocking=True)
@@ -469,7 +490,10 @@ class Pipeline:
                     sl["pm"][:no].copy_(hb.prior_mean[o0:o1], non_blocking=True)
                     sl["ps"][:no].copy_(hb.prior_std[o0:o1], non_blocking=True)
                     sl["of"][:no].copy_(hb.obj_frame[o0:o1], non_blocking=True)
-                    sl["mpk" if self.packed_masks else "masks"][:no].copy_(masks_h[o0:o1], non_blocking=True)
+                    if self.host_pack:
+                        sl["mpk"][:no].copy_(sl["stage"][:no], non_blocking=True)
+                    else:
+                        sl["mpk" if self.packed_masks else "masks"][:no].copy_(masks_h[o0:o1], non_blocking=True)
                 sl["copied"].record(self.copy_stream)
             mask_bytes = self.H * ((self.W + 31) // 32) * 4 if self.packed_masks else self.H * self.W
             self.h2d_bytes += nf * self.H * self.W * (5 if ground_h is not None else 4) + nf * 36 + no * (44 + mask_bytes)

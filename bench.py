@@ -587,6 +587,23 @@ def run_tdod(args):
         e2e = {"ms": e_ms, "h2d": pipe.h2d_bytes // e_steps, "d2h": pipe.d2h_bytes // e_steps,
                "same_winners": bool(torch.equal(out[:, 20].int(), o.best_idx.cpu()))}
         del pipe
+        # the same host batch (bool masks), but every chunk's masks are packed to 1 bit/px on the host cores while the previous
+        # chunk's copy is in flight (Pipeline(host_pack=True) -> tdod_host_pack_masks): the packing is inside the timed region
+        pipe = pipeline.Pipeline(H, W, N_PROP, chunk_frames=64, device=dev, seed=7, host_pack=True)
+        out3 = torch.empty((N, 21), dtype=torch.float32).pin_memory()
+        for _ in range(2):
+            pipe.run_host(hb, off, out=out3, obj_id_base=obj_base, frame_id_base=rank * F)
+        pipe.h2d_bytes = pipe.d2h_bytes = 0
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e_steps):
+            pipe.run_host(hb, off, out=out3, obj_id_base=obj_base, frame_id_base=rank * F)
+        barrier()
+        e2e["hp_ms"] = (time.perf_counter() - t0) * 1e3 / e_steps
+        e2e["hp_h2d"] = pipe.h2d_bytes // e_steps
+        e2e["hp_threads"] = pipe.pack_threads
+        e2e["hp_same_winners"] = bool(torch.equal(out3[:, 20].int(), o.best_idx.cpu()))
+        del pipe
         # the OPTIONAL host format with the masks at 1 bit per pixel (pipeline.pack_masks; tdod_mask_rect_bitmap): reported
         # beside the headline, never instead of it -- the reference's callers hold bool masks
         hp = pipeline.FrameBatch(hb.depth, hb.ground, hb.K, hb.boxes, hb.prior_mean, hb.prior_std, hb.obj_frame, None,
@@ -627,14 +644,14 @@ def run_tdod(args):
 
     # ---- max over ranks ----
     t = torch.tensor([total_ms, e2e["ms"] if e2e else 0.0, float(props), parity["ms_per_step"] if parity else 0.0,
-                      e2e["packed_ms"] if e2e else 0.0, eager_ms], dtype=torch.float64, device=dev)
+                      e2e["packed_ms"] if e2e else 0.0, eager_ms, e2e["hp_ms"] if e2e else 0.0], dtype=torch.float64, device=dev)
     if world > 1:
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
         total_ms, e_ms_max, props_all, p_ms_max, ep_ms_max = float(tmax[0]), float(tmax[1]), float(tsum[2]), float(tmax[3]), float(tmax[4])
-        eager_ms = float(tmax[5])
+        eager_ms, hp_ms_max = float(tmax[5]), float(tmax[6])
     else:
-        e_ms_max, props_all, p_ms_max, ep_ms_max = float(t[1]), float(props), float(t[3]), float(t[4])
+        e_ms_max, props_all, p_ms_max, ep_ms_max, hp_ms_max = float(t[1]), float(props), float(t[3]), float(t[4]), float(t[6])
     if rank == 0:
         ms_step = total_ms / args.steps
         step_bytes = sum(abytes.values())
@@ -676,9 +693,19 @@ def run_tdod(args):
             parity["value"] = props_all / (p_ms_max * 1e-3)
             line["value_parity_rng"] = parity
         if e2e:
-            line["e2e"] = {"value": props_all / (e_ms_max * 1e-3), "unit": UNIT, "h2d_bytes_per_step": e2e["h2d"],
-                           "d2h_bytes_per_step": e2e["d2h"], "ms_per_step": e_ms_max, "same_winners_as_resident": e2e["same_winners"],
+            # headline: the faster of the two ways to move the SAME host batch (bool masks); both are reported
+            use_hp = hp_ms_max < e_ms_max
+            best_ms = hp_ms_max if use_hp else e_ms_max
+            line["e2e"] = {"value": props_all / (best_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": e2e["hp_h2d"] if use_hp else e2e["h2d"],
+                           "d2h_bytes_per_step": e2e["d2h"], "ms_per_step": best_ms,
+                           "same_winners_as_resident": e2e["hp_same_winners"] if use_hp else e2e["same_winners"],
                            "host_masks": "torch.bool, 1 byte per pixel (what the reference's callers hold)",
+                           "transfer": ("masks packed to 1 bit/px on %d host threads per chunk inside the timed region, copied packed "
+                                        "(Pipeline(host_pack=True))" % e2e["hp_threads"]) if use_hp else "every tensor copied as it is",
+                           "variants": {"bool masks copied as they are": {"ms_per_step": e_ms_max, "value": props_all / (e_ms_max * 1e-3),
+                                                                            "h2d_bytes_per_step": e2e["h2d"]},
+                                        "bool masks packed on the host cores": {"ms_per_step": hp_ms_max, "value": props_all / (hp_ms_max * 1e-3),
+                                                                                "h2d_bytes_per_step": e2e["hp_h2d"], "threads": e2e["hp_threads"]}},
                            "optional_packed_masks": {"value": props_all / (ep_ms_max * 1e-3), "unit": UNIT, "ms_per_step": ep_ms_max,
                                                      "h2d_bytes_per_step": e2e["packed_h2d"],
                                                      "same_winners_as_resident": e2e["packed_same_winners"],

@@ -113,6 +113,14 @@ int tdod_mask_rect_packed(int64_t n_masks, int H, int W, float* out_rects, uint8
 int tdod_mask_rect_bitmap(const uint32_t* bitmap, int64_t n_masks, int H, int W, float* out_rects, uint8_t* out_has_rect,
                           void* workspace, int64_t workspace_bytes, void* stream);
 
+/* HOST function (no GPU work): packs masks held in host memory at 1 byte per pixel (torch.bool storage; any non-zero byte
+ * is "set") into the bitmap layout above, out_bitmap [n_masks,H,Wp] in host memory, with n_threads host threads.  The
+ * transfer codec of the end-to-end path: the masks are 75 % of a step's host->device bytes
+ * (cubercnn/modeling/roi_heads/roi_heads.py:432 holds them as bool tensors); packed, they cross PCIe at 1/8 of the size
+ * and tdod_mask_rect_bitmap consumes them as they are.  A data-format step on the host side of the boundary, not a CPU
+ * implementation of any kernel. */
+int tdod_host_pack_masks(const uint8_t* masks, int64_t n_masks, int H, int W, uint32_t* out_bitmap, int n_threads);
+
 /* second half of score_corners (scorefunction.py:69-85 + modified_chamfer_distance :51-56).
  * rect [4,2] (ignored when has_rect == 0: the fallback rectangle of :69-75 is computed from the corners). */
 int tdod_score_corners(const float* rect, int has_rect, const float* corners2d /*[n,8,2]*/, int64_t n, float* out,

@@ -109,3 +109,25 @@ def test_cubes_container_semantics():
     assert tuple(spaces.Cubes(torch.zeros(15)).tensor.shape) == (1, 1, 15)
     with pytest.raises(AssertionError):
         spaces.Cubes(t, scores=torch.zeros(3))
+
+
+def test_host_mask_packer_matches_the_bitmap_layout():
+    """tdod_host_pack_masks is a HOST function (the transfer codec of the end-to-end path): runs without a GPU; its
+    output must be the layout tdod_mask_rect_bitmap reads, i.e. what pipeline.pack_masks builds with torch ops"""
+    import numpy as np
+    import torch
+    from tdod import lib as L, pipeline
+    rs = np.random.RandomState(2)
+    for (N, H, W) in ((3, 17, 33), (2, 40, 97), (4, 9, 64), (1, 53, 730), (2, 5, 16)):
+        m = torch.from_numpy(((rs.rand(N, H, W) < 0.4) * rs.randint(1, 255, size=(N, H, W))).astype(np.uint8))
+        m[0, :, W - 1] = 7
+        want = pipeline.pack_masks(m)
+        for nt in (1, 2, 5):
+            got = torch.full(want.shape, -1, dtype=torch.int32)
+            assert L.lib().tdod_host_pack_masks(m.data_ptr(), N, H, W, got.data_ptr(), nt) == 0
+            assert torch.equal(got, want), (N, H, W, nt)
+        b = torch.from_numpy(rs.rand(N, H, W) < 0.5)
+        got = torch.empty(want.shape, dtype=torch.int32)
+        assert L.lib().tdod_host_pack_masks(b.data_ptr(), N, H, W, got.data_ptr(), 3) == 0
+        assert torch.equal(got, pipeline.pack_masks(b))
+    assert L.lib().tdod_host_pack_masks(None, 1, 4, 4, None, 1) < 0

@@ -608,3 +608,27 @@ def test_graphed_select_depth_two_overlaps_steps_and_keeps_the_winners():
     gs.join()
     torch.cuda.synchronize()
     assert torch.equal(o1.best_idx, e2.best_idx) and torch.equal(o2.best_idx, e2.best_idx)
+
+
+@pytest.mark.gpu
+def test_pipeline_host_pack_gives_the_resident_winners():
+    """Pipeline(host_pack=True): bool masks in pinned host memory, packed per chunk by tdod_host_pack_masks and copied at
+    1 bit/px -- same winners as the device-resident select; the packer itself against pipeline.pack_masks (odd widths,
+    bytes above 1, several thread counts)"""
+    d = torch.device("cuda:0")
+    c = synth.CONFIGS["C2"]
+    batch, off, _ = synth.make_batch(range(10), c["H"], c["W"], c["n_obj"], d)
+    ref = pipeline.select(batch, 500, seed=3)
+    hb = batch.to("cpu").pin()
+    p = pipeline.Pipeline(c["H"], c["W"], 500, chunk_frames=4, seed=3, host_pack=True, pack_threads=3)
+    out = p.run_host(hb, off)
+    assert torch.equal(out[:, 20].int(), ref.best_idx.cpu())
+    assert torch.equal(out[:, 0:15].view(torch.int32), ref.best_cube.cpu().view(torch.int32))
+    rs = np.random.RandomState(1)
+    for (N, H, W) in ((3, 17, 33), (2, 40, 97), (4, 9, 64)):
+        m = torch.from_numpy((rs.rand(N, H, W) < 0.4) * rs.randint(1, 255, size=(N, H, W))).to(torch.uint8)
+        want = pipeline.pack_masks(m)
+        for nt in (1, 2, 5):
+            got = torch.full(want.shape, -1, dtype=torch.int32)
+            assert L.lib().tdod_host_pack_masks(m.data_ptr(), N, H, W, got.data_ptr(), nt) == 0
+            assert torch.equal(got, want)

@@ -9,6 +9,6 @@ for f in $root/3dod_b200/csrc/*.cu; do
   /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -Wno-deprecated-gpu-targets "$@" -c $f -o $out/$(basename ${f%.cu}).o &
 done
 wait
-/usr/local/cuda/bin/nvcc -shared -o $out/libtdod.so $out/*.o -lcudart
+/usr/local/cuda/bin/nvcc -shared -o $out/libtdod.so $out/*.o -lcudart -lpthread
 rm -f $out/*.o
 echo $out/libtdod.so
