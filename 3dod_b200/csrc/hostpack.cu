@@ -39,28 +39,32 @@ inline void pack_row(const uint8_t* src, int W, uint32_t* dst, int Wp) {
 }
 
 // the same with 32-byte vectors where the host has AVX2 (checked once at run time): half the instructions per byte
+// staging words are written once and read by the DMA engine only: non-temporal stores skip the read-for-ownership
+#define NT(p, v) _mm_stream_si32(reinterpret_cast<int*>(p), (int)(v))
 __attribute__((target("avx2"))) inline void pack_row_avx2(const uint8_t* src, int W, uint32_t* dst, int Wp) {
     const __m256i zero = _mm256_setzero_si256();
     int x = 0, w = 0;
     for (; x + 64 <= W; x += 64, w += 2) {
         const __m256i a = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(src + x));
         const __m256i b = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(src + x + 32));
-        dst[w] = ~(uint32_t)_mm256_movemask_epi8(_mm256_cmpeq_epi8(a, zero));
-        dst[w + 1] = ~(uint32_t)_mm256_movemask_epi8(_mm256_cmpeq_epi8(b, zero));
+        NT(dst + w, ~(uint32_t)_mm256_movemask_epi8(_mm256_cmpeq_epi8(a, zero)));
+        NT(dst + w + 1, ~(uint32_t)_mm256_movemask_epi8(_mm256_cmpeq_epi8(b, zero)));
     }
     for (; x + 32 <= W; x += 32, ++w) {
         const __m256i a = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(src + x));
-        dst[w] = ~(uint32_t)_mm256_movemask_epi8(_mm256_cmpeq_epi8(a, zero));
+        NT(dst + w, ~(uint32_t)_mm256_movemask_epi8(_mm256_cmpeq_epi8(a, zero)));
     }
     if (x < W) {                                        // the row's last, partial word: never read past the row
         uint8_t tmp[32];
         std::memset(tmp, 0, sizeof(tmp));
         std::memcpy(tmp, src + x, (size_t)(W - x));
         const __m256i a = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(tmp));
-        dst[w++] = ~(uint32_t)_mm256_movemask_epi8(_mm256_cmpeq_epi8(a, zero));
+        NT(dst + w++, ~(uint32_t)_mm256_movemask_epi8(_mm256_cmpeq_epi8(a, zero)));
     }
-    for (; w < Wp; ++w) dst[w] = 0u;
+    for (; w < Wp; ++w) NT(dst + w, 0u);
 }
+
+#undef NT
 
 __attribute__((target("avx2"))) void pack_rows_avx2(const uint8_t* masks, int W, uint32_t* out, int Wp, int64_t r0, int64_t r1) {
     for (int64_t r = r0; r < r1; ++r) pack_row_avx2(masks + r * W, W, out + r * Wp, Wp);
@@ -88,6 +92,7 @@ extern "C" int tdod_host_pack_masks(const uint8_t* masks, int64_t n_masks, int H
     if ((int64_t)n_threads > rows) n_threads = (int)rows;
     if (n_threads == 1) {
         pack_rows(masks, W, out_bitmap, Wp, 0, rows);
+        _mm_sfence();
         return TDOD_OK;
     }
     std::vector<std::thread> pool;
@@ -99,5 +104,6 @@ extern "C" int tdod_host_pack_masks(const uint8_t* masks, int64_t n_masks, int H
     }
     pack_rows(masks, W, out_bitmap, Wp, 0, per < rows ? per : rows);
     for (auto& th : pool) th.join();
+    _mm_sfence();
     return TDOD_OK;
 }
