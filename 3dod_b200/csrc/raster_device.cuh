@@ -93,14 +93,28 @@ __device__ inline void make_edge(int W, int H, int ax, int ay, int bx, int by, E
 __device__ __forceinline__ bool line_row(const Edge& e, int y, int& xa, int& xb) {
     if (!e.lvalid) return false;
     const int J = (y - e.ly0) * e.lsy;
+    // extents below 2^14 pixels (every image the fused path accepts: clamped coordinates span at most 2.5 W): all products
+    // stay below 2^30 and the divisions are 32-bit (a 64-bit division is ~6 x the instructions on this machine)
+    const bool small = e.lmajor < 16384;
     if (e.lsteep) {
         if (J < 0 || J > e.lmajor) return false;
-        const int j = (int)((2ll * e.lminor * J + e.lmajor - 1) / (2ll * e.lmajor));
+        const int j = small ? (int)((2u * (unsigned)e.lminor * (unsigned)J + (unsigned)e.lmajor - 1u) / (2u * (unsigned)e.lmajor))
+                            : (int)((2ll * e.lminor * J + e.lmajor - 1) / (2ll * e.lmajor));
         xa = xb = e.lx0 + j;
         return true;
     }
     if (J < 0 || J > e.lminor) return false;
     if (e.lminor == 0) { xa = e.lx0; xb = e.lx0 + e.lmajor; return true; }
+    if (small) {
+        const int num32 = 2 * e.lmajor * J - e.lmajor + 1;
+        const unsigned den = 2u * (unsigned)e.lminor;
+        const int kmin32 = num32 <= 0 ? 0 : (int)(((unsigned)num32 + den - 1u) / den);
+        int kmax32 = (int)((unsigned)(2 * e.lmajor * (J + 1) - e.lmajor) / den);
+        kmax32 = min(kmax32, e.lmajor);
+        if (kmin32 > kmax32) return false;
+        xa = e.lx0 + kmin32; xb = e.lx0 + kmax32;
+        return true;
+    }
     const i64 num = 2ll * e.lmajor * J - e.lmajor + 1;
     const int kmin = num <= 0 ? 0 : (int)((num + 2ll * e.lminor - 1) / (2ll * e.lminor));
     int kmax = (int)((2ll * e.lmajor * (J + 1) - e.lmajor) / (2ll * e.lminor));
