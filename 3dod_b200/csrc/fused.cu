@@ -27,6 +27,7 @@ constexpr int kMaxCluster = 8;
 struct Mail {               // per-CTA mailbox read by every CTA of the cluster through DSMEM
     int hist[4][3][256];    // radix-select histograms, one buffer per pass (no WAR hazard)
     double sum[3];          // sum of seeds
+    double meanv[3];        // one CTA per object: the mean, formed once by the thread that owns the sum
     double m2[3];           // sum of squared deviations
     float fb[8];            // fallback rectangle: min/max over proposals of vertex 0 and vertex 1 (x, y)
     float maxdiff, maxd;
@@ -406,6 +407,7 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
         double s = 0.0;
         for (int w2 = 0; w2 < kWarps; ++w2) s += sh.red_d[w2][tid];
         sh.mail.sum[tid] = s;
+        if (S == 1) sh.mail.meanv[tid] = s / (double)n;
     }
     cl.sync();   // (1) pass-0 histograms, partial sums and NaN flags visible cluster-wide
 
@@ -466,6 +468,7 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
     double mean[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
+        if (S == 1) { mean[k] = sh.mail.meanv[k]; continue; }          // (same bits: the same division, done once)
         double s = 0.0;
         for (int r = 0; r < S; ++r) s += *cl.remote(&sh.mail.sum[k], r);
         mean[k] = s / (double)n;
@@ -483,6 +486,8 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
         double s = 0.0;
         for (int w2 = 0; w2 < kWarps; ++w2) s += sh.red_d[w2][tid];
         sh.mail.m2[tid] = s;
+        // one CTA per object: the unbiased std is formed here, once, instead of by all 256 threads after the barrier
+        if (S == 1 && a.std_mode != TDOD_STD_TORCH_CUDA) sh.mail.sdv[tid] = (float)sqrt(s / (double)(n - 1));
     }
     if (a.std_mode == TDOD_STD_TORCH_CUDA && rank == 0) {
         // torch.std as torch's CUDA kernel rounds it (tdod_device.cuh, namespace tstd): the launch shape depends on how
@@ -512,10 +517,13 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
         const float coef_a[3] = {1.15f, 1.1f, 0.85f}, coef_b[3] = {0.f, 0.f, 0.35f}, coef_s[3] = {1.2f, 0.8f, 1.2f};
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
-            double s = 0.0;
-            for (int r = 0; r < S; ++r) s += *cl.remote(&sh.mail.m2[k], r);
-            float sd = (float)sqrt(s / (double)(n - 1));                    // torch.std: unbiased (fp64 == torch on CPU)
-            if (a.std_mode == TDOD_STD_TORCH_CUDA) sd = *cl.remote(&sh.mail.sdv[k], 0);
+            float sd;
+            if (S == 1 || a.std_mode == TDOD_STD_TORCH_CUDA) sd = *cl.remote(&sh.mail.sdv[k], 0);
+            else {
+                double s = 0.0;
+                for (int r = 0; r < S; ++r) s += *cl.remote(&sh.mail.m2[k], r);
+                sd = (float)sqrt(s / (double)(n - 1));                      // torch.std: unbiased (fp64 == torch on CPU)
+            }
             smean[k] = __fadd_rn(__fmul_rn(coef_a[k], sh.med[k]), coef_b[k]);   // lin_fun, proposals.py:16-18
             ssd[k] = __fmul_rn(sd, coef_s[k]);
         }
