@@ -20,5 +20,6 @@ def run(label, **kw):
     ms = (time.perf_counter() - t0) * 1e3 / 5
     print("%-40s %7.2f ms per step  %.3e proposals/s  same winners %s" % (label, ms, N * 1000 / (ms * 1e-3), bool(torch.equal(out[:, 20].int(), ref))))
 run("bool masks over PCIe, chunk 32", chunk_frames=32)
-for rep in range(3):
-    run("host_pack, chunk 64, 16 threads", chunk_frames=64, host_pack=True)
+for rep in range(2):
+    for ch in (64, 32, 16):
+        run("host_pack, chunk %d, 16 threads" % ch, chunk_frames=ch, host_pack=True)
