@@ -227,7 +227,7 @@ __global__ void __launch_bounds__(kPackT) pack_tma_kernel(const uint8_t* __restr
         const int nwords = (r1 - r0) * Wp;
         int lo = 0x7fffffff, hi = -1;
         for (int q = tid; q < nwords; q += kPackT) {
-            const int rr = (int)__umulhi((uint32_t)q, wp_magic), w = q - rr * Wp, r = r0 + rr;
+            const int rr = Wp == 1 ? q : (int)__umulhi((uint32_t)q, wp_magic), w = q - rr * Wp, r = r0 + rr;   // (the magic is 2^32 for Wp = 1)
             const int o = (int)(b0 - (c0 << 4)) + rr * W + 32 * w;          // bit offset of the window in the stream
             uint32_t word = __funnelshift_r(sb32[o >> 5], sb32[(o >> 5) + 1], o & 31);
             const int nb = W - 32 * w;

@@ -632,3 +632,43 @@ def test_pipeline_host_pack_gives_the_resident_winners():
             got = torch.full(want.shape, -1, dtype=torch.int32)
             assert L.lib().tdod_host_pack_masks(m.data_ptr(), N, H, W, got.data_ptr(), nt) == 0
             assert torch.equal(got, want)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("H,W", [(40, 16), (37, 24), (50, 31), (1, 64), (2, 33), (3, 40), (129, 32), (257, 65)])
+def test_mask_rect_tiny_and_boundary_shapes(H, W):
+    """widths below 32 (two-kernel path), one- and two-row masks, heights one past a row group of the front kernel:
+    state bytes and rectangles against cv2 through the oracle, and fused against two-kernel where both apply"""
+    d = torch.device("cuda:0")
+    rs = np.random.RandomState(H * 131 + W)
+    ms = []
+    for t in range(24):
+        k = t % 4
+        m = np.zeros((H, W), bool)
+        if k == 0:
+            m[rs.randint(0, H):, rs.randint(0, W):] = True
+        elif k == 1:
+            m = rs.rand(H, W) < 0.35
+        elif k == 2:
+            m[:, :] = True
+            m[rs.randint(0, H), rs.randint(0, W)] = False
+        else:
+            y0, x0 = rs.randint(0, H), rs.randint(0, W)
+            m[y0:y0 + max(1, H // 3), x0:x0 + max(1, W // 3)] = True
+        ms.append(m)
+    ms.append(np.zeros((H, W), bool))
+    stack = torch.from_numpy(np.stack(ms)).to(d)
+    r1, h1 = api.mask_rect(stack)
+    r0, h0 = api.mask_rect(stack, two_kernel=True)
+    assert torch.equal(h0, h1)
+    ok = h0 == 1
+    assert torch.equal(r0[ok].view(torch.int32), r1[ok].view(torch.int32))
+    rects, has = r1.cpu().numpy(), h1.cpu().numpy()
+    assert has[-1] == 0
+    for t, m in enumerate(ms):
+        ref = O.mask_rect(m.astype(np.uint8))
+        assert has[t] in (0, 1), (t, has[t])
+        assert (ref is None) == (has[t] == 0), t
+        if ref is not None:
+            dev_px = max(min(float(np.hypot(*(p - q))) for q in ref) for p in rects[t])
+            assert dev_px < 1e-3, (t, rects[t], ref)
