@@ -672,3 +672,65 @@ def test_mask_rect_tiny_and_boundary_shapes(H, W):
         if ref is not None:
             dev_px = max(min(float(np.hypot(*(p - q))) for q in ref) for p in rects[t])
             assert dev_px < 1e-3, (t, rects[t], ref)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("H,W,stride", [(480, 640, 5), (640, 640, 5), (645, 640, 5), (641, 637, 5), (97, 131, 3), (33, 17, 5),
+                                        (5, 5, 5), (480, 640, 1), (203, 200, 2)])
+def test_backproject_shapes_across_the_one_pass_limit(H, W, stride):
+    """P = ceil(H/s) ceil(W/s) strided samples: up to 16 384 take the one-pass register-resident kernel, beyond it the
+    two-pass kernel; both flavours, with and without a ground map, several frames -- bit-equal to the oracle's NumPy /
+    torch restatements in count, order and value"""
+    d = torch.device("cuda:0")
+    rs = np.random.RandomState(H * 7 + W + stride)
+    F = 3
+    depth = torch.from_numpy(rs.uniform(0.5, 9.0, size=(F, H, W)).astype(np.float32))
+    ground = torch.from_numpy(rs.rand(F, H, W) < 0.4)
+    ground[1] = False                                            # a frame without any ground sample
+    K = torch.tensor([[[520.0, 0, W / 2.0], [0, 515.0, H / 2.0], [0, 0, 1]]] * F)
+    for fl, ofn in ((L.BACKPROJECT_NUMPY, O.backproject_np), (L.BACKPROJECT_TORCH, O.backproject_torch)):
+        for use_g in (True, False):
+            pts, other, cnt = api.backproject(depth.to(d), ground.to(d) if use_g else None, K.to(d), stride, fl)
+            for f in range(F):
+                if fl == L.BACKPROJECT_NUMPY:
+                    pg, pn = ofn(depth[f].numpy(), K[f].numpy(), ground[f].numpy() if use_g else None, stride)
+                    pg, pn = torch.from_numpy(np.asarray(pg)), (torch.from_numpy(np.asarray(pn)) if pn is not None else None)
+                else:
+                    r = ofn(depth[f], K[f], ground[f] if use_g else None, stride)
+                    pg, pn = (r, None) if not isinstance(r, tuple) else r
+                n_on = int(cnt[f, 0])
+                assert n_on == len(pg), (fl, use_g, f, n_on, len(pg))
+                assert torch.equal(pts[f, :, :n_on].t().cpu(), pg.reshape(-1, 3).to(pts.dtype))
+                if use_g and other is not None and pn is not None:
+                    n_off = int(cnt[f, 1])
+                    assert n_off == len(pn)
+                    assert torch.equal(other[f, :, :n_off].t().cpu(), pn.reshape(-1, 3).to(other.dtype))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("H,W", [(40, 32), (41, 33), (64, 64), (70, 95), (130, 240), (90, 1031)])
+def test_mask_rect_bitmap_equals_mask_rect_over_shapes(H, W):
+    """tdod_mask_rect_bitmap on pipeline.pack_masks(m) and on tdod_host_pack_masks(m) against tdod_mask_rect(m)"""
+    d = torch.device("cuda:0")
+    rs = np.random.RandomState(H + 3 * W)
+    yy, xx = np.mgrid[0:H, 0:W]
+    ms = []
+    for t in range(16):
+        cx, cy = rs.uniform(0.2, 0.8) * W, rs.uniform(0.2, 0.8) * H
+        m = ((xx - cx) / (rs.uniform(0.1, 0.5) * W)) ** 2 + ((yy - cy) / (rs.uniform(0.1, 0.5) * H)) ** 2 <= 1
+        if t % 3 == 0:
+            m |= rs.rand(H, W) < 0.02
+        if t % 4 == 1:
+            m[:, W - 1] = True
+        ms.append(m)
+    ms.append(np.zeros((H, W), bool))
+    m = torch.from_numpy(np.stack(ms))
+    r0, h0 = api.mask_rect(m.to(d))
+    bits = pipeline.pack_masks(m)
+    host = torch.empty(bits.shape, dtype=torch.int32)
+    assert L.lib().tdod_host_pack_masks(m.data_ptr(), m.shape[0], H, W, host.data_ptr(), 3) == 0
+    assert torch.equal(host, bits)
+    r1, h1 = api.mask_rect_bitmap(bits.to(d), W)
+    assert torch.equal(h0, h1)
+    ok = h0 == 1
+    assert torch.equal(r0[ok].view(torch.int32), r1[ok].view(torch.int32))
