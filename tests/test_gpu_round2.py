@@ -734,3 +734,34 @@ def test_mask_rect_bitmap_equals_mask_rect_over_shapes(H, W):
     assert torch.equal(h0, h1)
     ok = h0 == 1
     assert torch.equal(r0[ok].view(torch.int32), r1[ok].view(torch.int32))
+
+
+@pytest.mark.gpu
+def test_philox_redraw_queue_overflow_and_exhausted_rejection_loop():
+    """Priors under which most first draws of the dimensions fall outside [0.05, mean + k std] (more queued redraws than the
+    768-entry queue of K-C holds: the surplus loops in place) and one object whose bounds admit nothing (the loop gives up
+    after 10 000 redraws, utils.py:57): the winners-only kernel, the return-all kernel and the HOST-mode replay of the
+    dumped numbers must agree bit for bit"""
+    d = torch.device("cuda:0")
+    frames = synth.make_frames("C2", range(3))
+    b = pipeline.FrameBatch.from_frames(frames, d)
+    b.prior_mean[:] = 1.0
+    b.prior_std[:] = 5.0                      # valid window = (-0.19, 2) sigma: 45 % of the draws of a component fail
+    b.prior_mean[1] = 0.01
+    b.prior_std[1] = 0.005                    # upper bound 0.02 < 0.05: nothing is ever valid
+    hot = pipeline.select(b, 1000, seed=11)
+    s = pipeline.select(b, 1000, seed=11, want_noise=True, return_all=True)
+    torch.cuda.synchronize()
+    o = s.all
+    eq = lambda a, c: bool(((a == c) | (a.isnan() & c.isnan())).all())
+    assert torch.equal(hot.best_idx, s.best_idx) and eq(hot.best_cube, s.best_cube) and eq(hot.best_score, s.best_score)
+    k = api.propose_score_select(b.depth, b.K, b.boxes, b.prior_mean, b.prior_std, b.obj_frame, s.rects, s.has_rect, 1000,
+                                 yaw_tab=api.yaw_table(s.normal), noise=o.noise, yaw_idx=o.yaw_idx, return_all=True)
+    torch.cuda.synchronize()
+    assert eq(k.all_cubes, o.all_cubes) and eq(k.all_scores, o.all_scores) and torch.equal(k.best_idx, o.best_idx)
+    whl = o.all_cubes[..., 3:6]
+    ok = torch.ones(b.n_obj, dtype=torch.bool, device=d); ok[1] = False
+    hi = b.prior_mean + torch.tensor([2.0, 2.2, 2.0], device=d) * b.prior_std      # proposals.py:381-383
+    inside = ((whl >= 0.05) & (whl <= hi[:, None, :])).all(-1).all(-1)
+    assert bool(inside[ok].all())             # every accepted dimension lies inside the truncation window
+    assert not bool(inside[1])                # the hopeless object keeps its last draw
