@@ -765,3 +765,20 @@ def test_philox_redraw_queue_overflow_and_exhausted_rejection_loop():
     inside = ((whl >= 0.05) & (whl <= hi[:, None, :])).all(-1).all(-1)
     assert bool(inside[ok].all())             # every accepted dimension lies inside the truncation window
     assert not bool(inside[1])                # the hopeless object keeps its last draw
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("F", [30, 50, 100])
+def test_filtered_inlier_count_equals_exact_count_at_every_tile_size(F):
+    """the inlier filter picks its point-tile size from the batch (128 points for a few frames ... 1024 for >= 93 C2
+    frames): 30 / 50 / 100 frames run the 256 / 512 / 1024-point tiles; counts, winner and inlier mask against the
+    unfiltered kernel"""
+    from test_gpu_parity import _counts_both_ways
+    d = torch.device("cuda:0")
+    c = synth.CONFIGS["C2"]
+    batch, _, _ = synth.make_batch(range(F), c["H"], c["W"], c["n_obj"], d)
+    pts, _, cnt = api.backproject(batch.depth, batch.ground, batch.K, 5, L.BACKPROJECT_NUMPY, want_other=False)
+    a, b = _counts_both_ways(pts, cnt[:, 0].contiguous(), seed=5, iters=1000, thresh=0.05, frame_id_base=17)
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
+    assert int(a[0].max()) > 1000
