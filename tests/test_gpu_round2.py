@@ -782,3 +782,26 @@ def test_filtered_inlier_count_equals_exact_count_at_every_tile_size(F):
     for x, y in zip(a, b):
         assert torch.equal(x, y)
     assert int(a[0].max()) > 1000
+
+
+@pytest.mark.gpu
+def test_mode_b_scores_do_not_depend_on_how_objects_are_split_over_ctas():
+    """mode B deals an object's proposals / point chunks to 1..8 CTAs depending on the batch size: a 48-frame batch (one CTA
+    per object) and its first 6 frames alone (eight CTAs per object) must give the same segmentation, mod-segmentation and
+    points-in-cube values for the shared objects (Philox is keyed by global frame / object ids)"""
+    d = torch.device("cuda:0")
+    c = synth.CONFIGS["C2"]
+    big, off, _ = synth.make_batch(range(48), c["H"], c["W"], c["n_obj"], d)
+    n6 = int(off[6])                                            # the first six frames of the same batch, as a batch of their own
+    small = pipeline.FrameBatch(big.depth[:6], big.ground[:6], big.K[:6], big.boxes[:n6], big.prior_mean[:n6], big.prior_std[:n6],
+                                big.obj_frame[:n6], big.masks[:n6], big.frame_ids[:6] if big.frame_ids is not None else None)
+    assert big.n_obj >= 592 and small.n_obj * 4 < 592
+    sb = pipeline.select(big, 300, seed=4, mode_b=True)
+    ss = pipeline.select(small, 300, seed=4, mode_b=True)
+    torch.cuda.synchronize()
+    n = small.n_obj
+    eq = lambda a, b: bool(((a == b) | (a.isnan() & b.isnan())).all())
+    assert eq(sb.all.all_cubes[:n], ss.all.all_cubes)
+    assert eq(sb.all.all_scores[:n], ss.all.all_scores)
+    assert torch.equal(sb.all.all_pc[:n], ss.all.all_pc)
+    assert int(ss.all.all_pc.max()) > 0 and float(ss.all.all_scores[:, 4].max()) > 0
