@@ -805,3 +805,28 @@ def test_mode_b_scores_do_not_depend_on_how_objects_are_split_over_ctas():
     assert eq(sb.all.all_scores[:n], ss.all.all_scores)
     assert torch.equal(sb.all.all_pc[:n], ss.all.all_pc)
     assert int(ss.all.all_pc.max()) > 0 and float(ss.all.all_scores[:, 4].max()) > 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("H,W", [(64, 33), (130, 240), (200, 730)])
+def test_mask_rect_uint8_masks_with_bytes_above_one(H, W):
+    """uint8 masks whose set pixels hold 2..255 (the front kernel's 0/1 fast pack detects them and hands the mask to the
+    normalising path), mixed with 0/1 masks in one batch: same rectangles as the bool version of every mask"""
+    d = torch.device("cuda:0")
+    rs = np.random.RandomState(W)
+    yy, xx = np.mgrid[0:H, 0:W]
+    ms = []
+    for t in range(12):
+        cx, cy = rs.uniform(0.3, 0.7) * W, rs.uniform(0.3, 0.7) * H
+        ms.append(((xx - cx) / (rs.uniform(0.1, 0.4) * W)) ** 2 + ((yy - cy) / (rs.uniform(0.1, 0.4) * H)) ** 2 <= 1)
+    mb = np.stack(ms)
+    vals = rs.randint(2, 256, size=mb.shape).astype(np.uint8)
+    m8 = mb.astype(np.uint8)
+    m8[0::3] = (mb[0::3] * vals[0::3])                          # every third mask: all set bytes above 1
+    m8[1, 0, 0] = 0 if not mb[1, 0, 0] else 255                 # and one mask with a single such byte somewhere
+    ys, xs = np.nonzero(mb[1])
+    m8[1, ys[-1], xs[-1]] = 128
+    rb, hb = api.mask_rect(torch.from_numpy(mb).to(d))
+    r8, h8 = api.mask_rect(torch.from_numpy(m8).to(d))
+    assert torch.equal(hb, h8) and bool((hb == 1).all())
+    assert torch.equal(rb.view(torch.int32), r8.view(torch.int32))
