@@ -830,3 +830,24 @@ def test_mask_rect_uint8_masks_with_bytes_above_one(H, W):
     r8, h8 = api.mask_rect(torch.from_numpy(m8).to(d))
     assert torch.equal(hb, h8) and bool((hb == 1).all())
     assert torch.equal(rb.view(torch.int32), r8.view(torch.int32))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [2, 3, 33, 1000, 2048, 2049, 5000])
+def test_philox_mode_proposal_count_extremes(n):
+    """in-kernel Philox at the proposal counts where K-C changes shape (one CTA up to 2048, clusters beyond): the
+    winners-only kernel, the return-all kernel and the HOST-mode replay of the dumped numbers agree bit for bit"""
+    d = torch.device("cuda:0")
+    frames = synth.make_frames("C2", range(2))
+    b = pipeline.FrameBatch.from_frames(frames, d)
+    hot = pipeline.select(b, n, seed=21)
+    s = pipeline.select(b, n, seed=21, want_noise=True, return_all=True)
+    torch.cuda.synchronize()
+    o = s.all
+    eq = lambda a, c: bool(((a == c) | (a.isnan() & c.isnan())).all())
+    assert torch.equal(hot.best_idx, s.best_idx) and eq(hot.best_cube, s.best_cube) and eq(hot.best_score, s.best_score)
+    k = api.propose_score_select(b.depth, b.K, b.boxes, b.prior_mean, b.prior_std, b.obj_frame, s.rects, s.has_rect, n,
+                                 yaw_tab=api.yaw_table(s.normal), noise=o.noise, yaw_idx=o.yaw_idx, return_all=True)
+    torch.cuda.synchronize()
+    assert eq(k.all_cubes, o.all_cubes) and eq(k.all_scores, o.all_scores) and torch.equal(k.best_idx, o.best_idx)
+    assert bool((hot.best_idx >= 0).all()) and bool((hot.best_idx < n).all())
