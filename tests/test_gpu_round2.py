@@ -851,3 +851,45 @@ def test_philox_mode_proposal_count_extremes(n):
     torch.cuda.synchronize()
     assert eq(k.all_cubes, o.all_cubes) and eq(k.all_scores, o.all_scores) and torch.equal(k.best_idx, o.best_idx)
     assert bool((hot.best_idx >= 0).all()) and bool((hot.best_idx < n).all())
+
+
+@pytest.mark.gpu
+def test_iou3d_coplanar_faces_and_degenerate_boxes():
+    """axis-aligned boxes that SHARE face planes (shifted along one or two axes, nested with common faces), rotated copies of
+    those configurations, a zero-width box and a NaN box: analytic answers, no NaN where none went in"""
+    d = torch.device("cuda:0")
+    def cube(x, y, z, w, h, l, R=None):
+        c = torch.zeros(15); c[:6] = torch.tensor([x, y, z, w, h, l]); c[6:] = (torch.eye(3) if R is None else R).reshape(9)
+        return c
+    A = cube(0.0, 0.0, 3.0, 1.0, 1.0, 1.0)
+    # (w, h, l) are the extents along local (z?, y, x) per math_util.py: use a cube so that the axis naming does not matter
+    cases = [
+        (cube(0.5, 0.0, 3.0, 1, 1, 1), 0.5 / 1.5),                 # shifted along x: four coplanar side faces
+        (cube(0.5, 0.5, 3.0, 1, 1, 1), 0.25 / 1.75),               # shifted along x and y: two coplanar faces
+        (cube(0.0, 0.0, 3.5, 1, 1, 1), 0.5 / 1.5),                 # shifted along z
+        (cube(1.0, 0.0, 3.0, 1, 1, 1), 0.0),                       # touching on a whole face
+        (cube(1.0, 1.0, 3.0, 1, 1, 1), 0.0),                       # touching on an edge
+        (cube(0.25, 0.25, 3.25, 0.5, 0.5, 0.5), 0.125),            # nested in a corner: three shared face planes
+        (cube(0.0, 0.0, 3.0, 1, 1, 1), 1.0),
+    ]
+    B = torch.stack([c for c, _ in cases])
+    want = np.array([v for _, v in cases])
+    ca = api.cube_corners(A[None].to(d))[0]
+    cb = api.cube_corners(B.to(d))
+    got = api.box3d_iou(ca, cb).cpu().numpy()
+    assert np.abs(got - want).max() < 1e-5, (got, want)
+    # the same configurations under a common rigid motion
+    g = torch.Generator().manual_seed(3)
+    R = O.random_rotations(1, 1, g)[0, 0]
+    t = torch.tensor([0.3, -0.2, 1.0])
+    rot = lambda c: (c - torch.tensor([0.0, 0.0, 3.0], device=d)) @ R.t().to(d) + torch.tensor([0.0, 0.0, 3.0], device=d) + t.to(d)
+    got_r = api.box3d_iou(rot(ca), rot(cb)).cpu().numpy()
+    assert np.abs(got_r - want).max() < 2e-5, (got_r, want)
+    # degenerate inputs
+    flat = api.cube_corners(cube(0.0, 0.0, 3.0, 0.0, 1.0, 1.0)[None].to(d))
+    assert float(api.box3d_iou(ca, flat)[0]) == 0.0
+    nanb = cb[:1].clone(); nanb[0, 3, 1] = float("nan")
+    v = float(api.box3d_iou(ca, nanb)[0])
+    assert v != v or 0.0 <= v <= 1.0                               # NaN in -> NaN or a bounded value, never a crash
+    both = api.box3d_iou(ca, torch.cat([cb, flat]))
+    assert bool(torch.isfinite(both).all())
