@@ -893,3 +893,23 @@ def test_iou3d_coplanar_faces_and_degenerate_boxes():
     assert v != v or 0.0 <= v <= 1.0                               # NaN in -> NaN or a bounded value, never a crash
     both = api.box3d_iou(ca, torch.cat([cb, flat]))
     assert bool(torch.isfinite(both).all())
+
+
+@pytest.mark.gpu
+def test_mask_rect_hulls_beyond_the_tail_warps_capacity():
+    """discs of radius ~500 px in 1024 x 1024 masks have more than 192 hull vertices: the tail warp hands them to the
+    overflow pass; smaller discs stay in the tail.  All against cv2 through the oracle."""
+    d = torch.device("cuda:0")
+    H = W = 1024
+    yy, xx = np.mgrid[0:H, 0:W]
+    ms = [((xx - 511.5) ** 2 + (yy - 511.5) ** 2 <= r * r) for r in (505.3, 480.0, 333.3, 120.0)]
+    ms.append(((xx - 500.0) / 490.0) ** 2 + ((yy - 520.0) / 300.0) ** 2 <= 1)
+    rects, has = api.mask_rect(torch.from_numpy(np.stack(ms)).to(d))
+    r2, h2 = api.mask_rect(torch.from_numpy(np.stack(ms)).to(d), two_kernel=True)
+    assert torch.equal(has, h2) and torch.equal(rects.view(torch.int32), r2.view(torch.int32))
+    rects, has = rects.cpu().numpy(), has.cpu().numpy()
+    for t, m in enumerate(ms):
+        ref = O.mask_rect(m.astype(np.uint8))
+        assert has[t] == 1, (t, has[t])
+        dev_px = max(min(float(np.hypot(*(p - q))) for q in ref) for p in rects[t])
+        assert dev_px < 2e-3, (t, rects[t], ref)
