@@ -319,6 +319,21 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
     if (tid < 3) { sh.prefix[tid] = 0u; sh.kth[tid] = (n - 1) / 2; sh.mail.nanflag[tid] = 0; }
     if (tid == 0) sh.mail.nfail = 0;
     __syncthreads();
+    if (S > 1) cl.sync();   // (0) every CTA's histograms are zero before a peer may add to rank 0's
+    // Clusters: each CTA counts into its own histograms and then ADDS its non-zero bins to rank 0's (DSMEM atomics), so
+    // that the warps that resolve a pass read one merged histogram -- two 16-byte loads per lane -- instead of walking all
+    // S mailboxes (ncu on C3, S = 8: 57 % of the kernel's stall samples sat in those 64 dependent remote loads per lane
+    // and in the peers waiting for them at the cluster barrier).
+    auto merge_hist = [&](int pass) {
+        if (S > 1 && rank != 0) {
+            const int* loc = &sh.mail.hist[pass][0][0];
+            int* dst = cl.remote(&sh.mail.hist[pass][0][0], 0);
+            for (int t = tid; t < 3 * 256; t += kThreads) {
+                const int v = loc[t];
+                if (v) atomicAdd(dst + t, v);
+            }
+        }
+    };
 
     // ---------------- phase 1: centre seeds + dimensions ----------------
     const float* depth = a.depth + (size_t)c.frame * a.H * a.W;
@@ -409,6 +424,7 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
         sh.mail.sum[tid] = s;
         if (S == 1) sh.mail.meanv[tid] = s / (double)n;
     }
+    merge_hist(0);           // (the barrier above closed this CTA's pass-0 counting)
     cl.sync();   // (1) pass-0 histograms, partial sums and NaN flags visible cluster-wide
 
     // ---------------- exact lower median (torch.median) by 4-pass radix select over the cluster ----------------
@@ -423,16 +439,16 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
                 if ((ky & himask) == p1) atomicAdd(&sh.mail.hist[pass][1][(ky >> shift) & 255u], 1);
                 if ((kz & himask) == p2) atomicAdd(&sh.mail.hist[pass][2][(kz >> shift) & 255u], 1);
             }
+            if (S > 1) { __syncthreads(); merge_hist(pass); }
             cl.sync();   // (2..4)
         }
         if (wid < 3) {   // warp `wid` resolves array `wid`: lane owns bins [8*lane, 8*lane+8)
             int bins[8];
-#pragma unroll
-            for (int b = 0; b < 8; ++b) bins[b] = 0;
-            for (int r = 0; r < S; ++r) {
-                const int* hr = cl.remote(&sh.mail.hist[pass][wid][0], r);
-#pragma unroll
-                for (int b = 0; b < 8; ++b) bins[b] += hr[8 * lane + b];
+            {
+                const int4* hr = reinterpret_cast<const int4*>(cl.remote(&sh.mail.hist[pass][wid][0], 0));   // rank 0 holds the sum
+                const int4 lo4 = hr[2 * lane], hi4 = hr[2 * lane + 1];
+                bins[0] = lo4.x; bins[1] = lo4.y; bins[2] = lo4.z; bins[3] = lo4.w;
+                bins[4] = hi4.x; bins[5] = hi4.y; bins[6] = hi4.z; bins[7] = hi4.w;
             }
             int tot = 0;
 #pragma unroll

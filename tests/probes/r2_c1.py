@@ -22,3 +22,10 @@ print("eager overlap %.4f ms   eager one stream %.4f ms" % (timed(lambda: pipeli
 for ov in (True, False):
     gs = pipeline.GraphedSelect(b, n, seed=7, overlap=ov)
     print("graph overlap=%s %.4f ms" % (ov, timed(gs.replay)))
+import numpy as np
+marks = [dict() for _ in range(10)]
+for i in range(10):
+    pipeline.select(b, n, seed=7, overlap=False, marks=marks[i])
+torch.cuda.synchronize()
+st = [float(np.mean([m[a].elapsed_time(m[c_]) for m in marks])) for a, c_ in (("ka0", "ka1"), ("kb0", "kb1"), ("kc0", "kc1"))]
+print("serial stages (eager, one stream): K-A %.3f  K-B %.3f  K-C %.3f ms" % tuple(st))
