@@ -48,6 +48,7 @@ struct Shared {
     uint32_t prefix[3];
     int kth[3];
     float med[3];
+    float sd_loc[3];        // clusters, exact std: formed by this CTA's owner threads from all ranks' partial sums
     float rect[8];
     float K[9];
     float yaw[TDOD_NYAW * 9];
@@ -479,15 +480,18 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
         int anynan = 0;
         for (int r = 0; r < S; ++r) anynan |= *cl.remote(&sh.mail.nanflag[tid], r);
         sh.med[tid] = anynan ? CUDART_NAN_F : key2f(sh.prefix[tid]);
+        if (S > 1) {                                    // clusters: the three owners gather the partial sums (in rank order)
+            double s = 0.0;
+            for (int r = 0; r < S; ++r) s += *cl.remote(&sh.mail.sum[tid], r);
+            sh.mail.meanv[tid] = s / (double)n;
+        }
     }
+    if (S > 1) __syncthreads();
     // mean over the cluster, then squared deviations (two-pass, fp64: torch CPU accumulates std in double)
     double mean[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        if (S == 1) { mean[k] = sh.mail.meanv[k]; continue; }          // (same bits: the same division, done once)
-        double s = 0.0;
-        for (int r = 0; r < S; ++r) s += *cl.remote(&sh.mail.sum[k], r);
-        mean[k] = s / (double)n;
+        mean[k] = sh.mail.meanv[k];                     // formed once by the thread that owns the sum (same operations, same bits)
     }
     double lm2[3] = {0.0, 0.0, 0.0};
     for (int j = tid; j < cnt; j += kThreads) {
@@ -528,6 +532,14 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
         }
     }
     cl.sync();   // (5)
+    if (S > 1 && a.std_mode != TDOD_STD_TORCH_CUDA) {   // clusters: the three owners gather the squared deviations (rank order)
+        if (tid < 3) {
+            double s = 0.0;
+            for (int r = 0; r < S; ++r) s += *cl.remote(&sh.mail.m2[tid], r);
+            sh.sd_loc[tid] = (float)sqrt(s / (double)(n - 1));             // torch.std: unbiased (fp64 == torch on CPU)
+        }
+        __syncthreads();
+    }
     float smean[3], ssd[3];
     {
         const float coef_a[3] = {1.15f, 1.1f, 0.85f}, coef_b[3] = {0.f, 0.f, 0.35f}, coef_s[3] = {1.2f, 0.8f, 1.2f};
@@ -535,11 +547,7 @@ __global__ void __launch_bounds__(kThreads, TDOD_PSS_MINBLOCKS) pss_kernel(const
         for (int k = 0; k < 3; ++k) {
             float sd;
             if (S == 1 || a.std_mode == TDOD_STD_TORCH_CUDA) sd = *cl.remote(&sh.mail.sdv[k], 0);
-            else {
-                double s = 0.0;
-                for (int r = 0; r < S; ++r) s += *cl.remote(&sh.mail.m2[k], r);
-                sd = (float)sqrt(s / (double)(n - 1));                      // torch.std: unbiased (fp64 == torch on CPU)
-            }
+            else sd = sh.sd_loc[k];
             smean[k] = __fadd_rn(__fmul_rn(coef_a[k], sh.med[k]), coef_b[k]);   // lin_fun, proposals.py:16-18
             ssd[k] = __fmul_rn(sd, coef_s[k]);
         }
