@@ -1208,13 +1208,13 @@ __global__ void __launch_bounds__(kT, kExact ? 1 : TDOD_KB_MINB) rect_kernel(con
 // ------------------------------------------------------------------------------------------------------------
 // Fused path (masks whose bit stream and run arrays fit in shared memory): the 1 bit/px copy never leaves the SM.
 //
-//   front kernel  persistent CTAs, two per SM.  Per mask: the raw bytes arrive tile by tile through a two-deep TMA ring
-//                 (cp.async.bulk + mbarrier, the load of the next tile -- also the next mask's first -- in flight while
-//                 this one is turned into bits), 16 bytes -> 16 bits -> one half-word store into a FLAT bit stream in
-//                 shared memory; then run extraction, labelling, cell-formula areas and the choice of the component
-//                 straight from that stream (StreamBits).  What leaves the SM is the winner's per-row extremes: two
-//                 int16 per occupied row (~1 KB per mask instead of a 48 KB bitmap written and read back).
-//                 While one CTA of an SM labels, the other streams.
+//   front kernel  persistent CTAs, two per SM.  Per mask: the raw bytes arrive in tiles of whole rows through a kRing-slot
+//                 TMA ring (cp.async.bulk + mbarrier; the loads of the next tiles -- also the next mask's first -- in flight
+//                 while this one is turned into bits), 16 bytes -> 16 bits -> one half-word store into the ROW SLOT of a
+//                 bit stream in shared memory (every row owns a 16-byte-aligned slot, see front_slot_hw); then run
+//                 extraction, labelling, cell-formula areas and the choice of the component straight from those slots.
+//                 What leaves the SM is the winner's per-row extremes: two int16 per occupied row (~1 KB per mask
+//                 instead of a 48 KB bitmap written and read back).
 //   tail kernel   ONE WARP per mask: sieve, monotone-chain stacks, rotating calipers from those extremes.  The serial
 //                 chains of 12-16 masks overlap on an SM; nothing waits at a CTA barrier.
 // Masks the front kernel cannot decide (hole filling could change the winner; more runs than shared memory holds) go
@@ -1236,8 +1236,8 @@ constexpr uint8_t kPending = 0xF0;      // state byte between the front and the 
 __host__ __device__ inline size_t cand_stride(int H) { return align16(8 + (size_t)H * 4); }   // {rmin, rmax} + int16 L/R per row
 
 // Front CTA = two halves that never meet at a CTA barrier.  PACK half (threads 0..127, thread 0 also drives the TMA ring):
-// bytes -> bits, group of rows after group of rows, into one of two bit-stream buffers.  EXTRACT half (threads 128..255):
-// runs of a finished group (one thread per row), and after a mask's last group its labels, areas, winner and the record.
+// bytes -> bits, group of rows after group of rows, into one of kSB bit-stream buffers.  EXTRACT half (threads 128..383):
+// runs of a finished group (two threads per row), and after a mask's last group its labels, areas, winner and the record.
 // The halves hand over through mbarriers (stream full / stream free), so while the extract half works on mask k the pack
 // half keeps HBM streaming for mask k + 1: the kernel's loads never pause for the labelling.
 #ifdef TDOD_KB_PROF
@@ -1271,7 +1271,7 @@ __host__ __device__ inline int front_tile_rows(int W) {             // rows per 
 
 struct FrontSmem {
     unsigned char* raw0; size_t raw_stride;            // ring slot k at raw0 + k * raw_stride
-    unsigned char* sb0; size_t sb_stride;               // two bit-stream buffers (a group of rows each): sb0 + b * sb_stride
+    unsigned char* sb0; size_t sb_stride;               // kSB bit-stream buffers (a group of rows each): sb0 + b * sb_stride
     RunSet rs; int* rowL; int* rowR; int* scratch;
 };
 __host__ __device__ inline size_t front_layout(int H, int W, FrontSmem* f, unsigned char* base) {
